@@ -143,7 +143,7 @@ __device__ __forceinline__ int fast_nms_emit(const FastWarpSmem& s, int sp, int 
 }
 
 __global__ void __launch_bounds__(FAST_WARPS * 32)
-k_fast_cells(const __grid_constant__ OrbxPlan P, const uint8_t* __restrict__ pyr,
+k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t* __restrict__ pyr,
              uint32_t* __restrict__ cellcnt, uint32_t* __restrict__ cellkeys, int tile_pitch,
              int score_pitch, int warp_smem_bytes) {
     extern __shared__ __align__(16) uint8_t smem[];
@@ -180,7 +180,8 @@ k_fast_cells(const __grid_constant__ OrbxPlan P, const uint8_t* __restrict__ pyr
     s.score = s.tile + tile_pitch * P.max_tile_h;
 
     // 1. stage the tile: aligned words covering [iniX & ~3, maxX)
-    const uint8_t* src = pyr + (size_t)frame * P.frame_stride + L.off;
+    int lpitch;
+    const uint8_t* src = orbx_level_ptr(P, isrc, pyr, frame, l, &lpitch);
     const int ax = iniX & ~3;
     const int xo = iniX - ax;  // tile x -> smem byte x + xo
     const int nw = (maxX - ax + 3) >> 2;
@@ -189,7 +190,7 @@ k_fast_cells(const __grid_constant__ OrbxPlan P, const uint8_t* __restrict__ pyr
     for (int i = lane; i < nwords; i += 32) {
         const int r = (int)(((uint32_t)i * nw_inv) >> 20);
         const int cw = i - r * nw;
-        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(iniY + r) * L.pitch + ax) + cw);
+        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(iniY + r) * lpitch + ax) + cw);
         reinterpret_cast<uint32_t*>(s.tile + r * tile_pitch)[cw] = v;
     }
     // zero the score map (frame included)
@@ -229,13 +230,13 @@ cudaError_t orbx_configure_fast(const OrbxPlan& P) {
                                 wb * FAST_WARPS);
 }
 
-cudaError_t orbx_launch_fast(const OrbxPlan& P, const uint8_t* pyr, uint32_t* cellcnt,
+cudaError_t orbx_launch_fast(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr, uint32_t* cellcnt,
                              uint32_t* cellkeys, int nframes, cudaStream_t st, int* launches) {
     int tp, sp, wb;
     orbx_fast_smem_layout(P, &tp, &sp, &wb);
     const int smem = wb * FAST_WARPS;
     dim3 grid((P.cells_total + FAST_WARPS - 1) / FAST_WARPS, nframes);
-    k_fast_cells<<<grid, FAST_WARPS * 32, smem, st>>>(P, pyr, cellcnt, cellkeys, tp, sp, wb);
+    k_fast_cells<<<grid, FAST_WARPS * 32, smem, st>>>(P, src, pyr, cellcnt, cellkeys, tp, sp, wb);
     ++*launches;
     return cudaGetLastError();
 }

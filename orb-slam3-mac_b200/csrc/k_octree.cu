@@ -1,0 +1,498 @@
+// k_octree.cu -- E3: ORBextractor::DistributeOctTree (src/ORBextractor.cc:537-761) and
+// ExtractorNode::DivideNode (:479-535) as a deterministic GPU quadtree.
+//
+// One CTA owns one (frame, level).  The reference's std::list algorithm is restated as array
+// passes (the formulation proven bit-identical to the verbatim reference by oracle/orb_oracle.cpp):
+//
+//   * the node list is an array in list order; a pass splits a set of nodes given in
+//     PROCESSING order; children are created in order n1..n4 per parent, and because the
+//     reference push_front()s them the new list is reverse(creation order) ++ untouched nodes;
+//   * full pass (:597-661): processing order = list order of all multi-key nodes;
+//   * careful pass (:671-735): processing order = multi-key children of the previous pass sorted
+//     by (key count, creation order) DESCENDING -- creation order is this project's canonical
+//     replacement for the reference's heap-address tie-break at :682 -- and the
+//     pass stops at the first node after which size >= N (prefix scan + atomicMin);
+//   * keys of a node stay contiguous: a split is a STABLE 4-way partition of the node's own key
+//     range (ballot/popc ranks), ping-ponged between two buffers (shared memory when the level's
+//     keys fit, HBM otherwise), so the reference's intra-node key order -- which decides
+//     response ties in the final first-maximum-wins scan (:740-758) -- is preserved.
+//
+// Small nodes are partitioned one per warp, nodes with >= OCT_BIG keys by the whole CTA.
+#include "orbx_device.cuh"
+
+#define OCT_THREADS 512
+#define OCT_WARPS (OCT_THREADS / 32)
+#define OCT_BIG 1024
+#define OCT_MAX_INI 8
+
+struct OctCtx {
+    // node list, double buffered (index = list position)
+    short4* nb[2];
+    uint32_t* nst[2];  // key range start | buffer bit << 31
+    uint32_t* ncn[2];  // key count
+    uint32_t* cc;      // [4 * NC] child counts by processing index
+    uint32_t* proc;    // [NC] list positions in processing order
+    uint32_t* expand[2];  // [NC] list positions of multi-key children, creation order
+    uint32_t* aux;     // [NC + 1] packed scans
+    uint32_t* flag;    // [NC + 1] processed flags / kept ranks
+    unsigned long long* sortk;  // [NCP2]
+    uint32_t* wc;      // [OCT_WARPS * 8] per-warp bin counts for CTA-wide partitions
+    uint32_t* tmp;     // [64] scan scratch + scalars
+    uint32_t* buf[2];  // key buffers
+};
+
+__device__ __forceinline__ int oct_quadrant(uint32_t key, int mx, int my) {
+    return (ORBX_KEY_X(key) < mx ? 0 : 1) + (ORBX_KEY_Y(key) < my ? 0 : 2);
+}
+
+// Stable 4-way partition of one node by ONE warp.  Returns the four child counts (all lanes).
+__device__ __forceinline__ void oct_warp_partition(const uint32_t* __restrict__ src,
+                                                   uint32_t* __restrict__ dst, uint32_t start,
+                                                   uint32_t cnt, int mx, int my, uint32_t c[4]) {
+    const int lane = orbx_lane();
+    const uint32_t lt = orbx_lanemask_lt();
+    c[0] = c[1] = c[2] = c[3] = 0;
+    for (uint32_t b = 0; b < cnt; b += 32) {
+        const uint32_t i = b + lane;
+        const int q = i < cnt ? oct_quadrant(src[start + i], mx, my) : 4;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) c[k] += __popc(__ballot_sync(ORBX_FULL, q == k));
+    }
+    uint32_t o[4] = {start, start + c[0], start + c[0] + c[1], start + c[0] + c[1] + c[2]};
+    for (uint32_t b = 0; b < cnt; b += 32) {
+        const uint32_t i = b + lane;
+        uint32_t key = 0;
+        int q = 4;
+        if (i < cnt) {
+            key = src[start + i];
+            q = oct_quadrant(key, mx, my);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t m = __ballot_sync(ORBX_FULL, q == k);
+            if (q == k) dst[o[k] + __popc(m & lt)] = key;
+            o[k] += __popc(m);
+        }
+    }
+}
+
+// Stable partition of src[start, start+cnt) into `nbins` (<= 8) bins by the whole CTA.
+// MODE 0: quadrant(mx, my); MODE 1: root index (int)(x / hx).  Writes the bin counts to
+// out_counts[0..nbins) (shared memory).  All threads must call; contains __syncthreads.
+template <int MODE>
+__device__ __forceinline__ void oct_block_partition(const OctCtx& C, const uint32_t* __restrict__ src,
+                                                    uint32_t* __restrict__ dst, uint32_t start,
+                                                    uint32_t cnt, int nbins, int mx, int my, float hx,
+                                                    uint32_t* out_counts) {
+    const int lane = orbx_lane(), warp = orbx_warp();
+    const uint32_t lt = orbx_lanemask_lt();
+    const uint32_t per = ((cnt + OCT_WARPS * 32 - 1) / (OCT_WARPS * 32)) * 32;  // keys per warp
+    const uint32_t b0 = min(cnt, warp * per), b1 = min(cnt, b0 + per);
+    uint32_t c[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) c[k] = 0;
+    for (uint32_t b = b0; b < b1; b += 32) {
+        const uint32_t i = b + lane;
+        int q = 8;
+        if (i < b1) {
+            const uint32_t key = src[start + i];
+            q = MODE == 0 ? oct_quadrant(key, mx, my) : (int)((float)ORBX_KEY_X(key) / hx);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            if (k < nbins) c[k] += __popc(__ballot_sync(ORBX_FULL, q == k));
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) C.wc[warp * 8 + k] = c[k];
+    }
+    __syncthreads();
+    // bin totals and this warp's base inside every bin
+    uint32_t o[8];
+    uint32_t run = start;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        uint32_t before = 0, tot = 0;
+        if (k < nbins) {
+            for (int w = 0; w < OCT_WARPS; ++w) {
+                const uint32_t v = C.wc[w * 8 + k];
+                if (w < warp) before += v;
+                tot += v;
+            }
+        }
+        o[k] = run + before;
+        run += tot;
+        if (threadIdx.x == 0 && k < nbins) out_counts[k] = tot;
+    }
+    for (uint32_t b = b0; b < b1; b += 32) {
+        const uint32_t i = b + lane;
+        uint32_t key = 0;
+        int q = 8;
+        if (i < b1) {
+            key = src[start + i];
+            q = MODE == 0 ? oct_quadrant(key, mx, my) : (int)((float)ORBX_KEY_X(key) / hx);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            if (k < nbins) {
+                const uint32_t m = __ballot_sync(ORBX_FULL, q == k);
+                if (q == k) dst[o[k] + __popc(m & lt)] = key;
+                o[k] += __popc(m);
+            }
+        }
+    }
+    __syncthreads();
+}
+
+// shared scalars inside C.tmp
+#define OT_EPROC 40
+#define OT_NBIG 41
+
+// One pass over the nodes proc[0..E) of list `cur` (S nodes).  Builds list cur^1.
+// careful == true applies the reference's early stop "size >= N" (:730-731).
+// Returns the new list size; *n_multi = number of multi-key children created (nToExpand).
+__device__ __forceinline__ int oct_pass(const OctCtx& C, int cur, int S, int E, bool careful, int N,
+                                        int* n_multi) {
+    const int nxt = cur ^ 1;
+    const int tid = threadIdx.x, lane = orbx_lane(), warp = orbx_warp();
+    uint32_t* biglist = reinterpret_cast<uint32_t*>(C.sortk);
+
+    // ---- (a) split every node of the pass: stable 4-way partition into the other buffer
+    if (tid == 0) {
+        C.tmp[OT_NBIG] = 0;
+        C.tmp[OT_EPROC] = (uint32_t)E;
+    }
+    __syncthreads();
+    for (int j = tid; j < E; j += OCT_THREADS)
+        if (C.ncn[cur][C.proc[j]] >= OCT_BIG) biglist[atomicAdd(&C.tmp[OT_NBIG], 1u)] = j;
+    __syncthreads();
+    const int nbig = (int)C.tmp[OT_NBIG];
+    for (int b = 0; b < nbig; ++b) {
+        const int j = biglist[b];
+        const int i = C.proc[j];
+        const short4 bb = C.nb[cur][i];
+        const uint32_t st = C.nst[cur][i];
+        const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
+        oct_block_partition<0>(C, C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu,
+                               C.ncn[cur][i], 4, mx, my, 0.f, &C.cc[4 * j]);
+    }
+    for (int j = warp; j < E; j += OCT_WARPS) {
+        const int i = C.proc[j];
+        const uint32_t cnt = C.ncn[cur][i];
+        if (cnt >= OCT_BIG) continue;
+        const short4 bb = C.nb[cur][i];
+        const uint32_t st = C.nst[cur][i];
+        const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
+        uint32_t c[4];
+        oct_warp_partition(C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu, cnt, mx, my, c);
+        if (lane < 4) C.cc[4 * j + lane] = lane == 0 ? c[0] : lane == 1 ? c[1] : lane == 2 ? c[2] : c[3];
+    }
+    __syncthreads();
+
+    // ---- (b) creation indices: exclusive scan of (#children | #multi-key children << 16)
+    for (int j = tid; j < E; j += OCT_THREADS) {
+        uint32_t v = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t c = C.cc[4 * j + q];
+            v += (c > 0 ? 1u : 0u) + (c > 1 ? 0x10000u : 0u);
+        }
+        C.aux[j] = v;
+    }
+    __syncthreads();
+    const uint32_t tot = block_excl_scan(C.aux, E, C.tmp);
+    if (tid == 0) C.aux[E] = tot;
+    if (careful) {
+        for (int j = tid; j < E; j += OCT_THREADS) {
+            uint32_t nch = 0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) nch += C.cc[4 * j + q] > 0 ? 1u : 0u;
+            const int size_after = S + (int)((C.aux[j] & 0xffffu) + nch) - (j + 1);
+            if (size_after >= N) atomicMin(&C.tmp[OT_EPROC], (uint32_t)(j + 1));
+        }
+    }
+    __syncthreads();
+    const int Eproc = (int)C.tmp[OT_EPROC];
+    const int M = (int)(C.aux[Eproc] & 0xffffu);
+    *n_multi = (int)(C.aux[Eproc] >> 16);
+
+    // ---- (c) rank of the untouched nodes
+    for (int i = tid; i < S; i += OCT_THREADS) C.flag[i] = 1;
+    __syncthreads();
+    for (int j = tid; j < Eproc; j += OCT_THREADS) C.flag[C.proc[j]] = 0;
+    __syncthreads();
+    const uint32_t kept = block_excl_scan(C.flag, S, C.tmp);
+    if (tid == 0) C.flag[S] = kept;
+    __syncthreads();
+
+    // ---- (d) new list = reverse(creation order) ++ untouched nodes
+    for (int j = tid; j < Eproc; j += OCT_THREADS) {
+        const int i = C.proc[j];
+        const short4 bb = C.nb[cur][i];
+        const uint32_t st = C.nst[cur][i];
+        const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
+        uint32_t run = (st & 0x7fffffffu);
+        const uint32_t bit = (st & 0x80000000u) ^ 0x80000000u;
+        int cidx = (int)(C.aux[j] & 0xffffu);
+        int midx = (int)(C.aux[j] >> 16);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t c = C.cc[4 * j + q];
+            if (c > 0) {
+                const int pos = M - 1 - cidx;
+                short4 nbv;
+                nbv.x = (q & 1) ? mx : bb.x;
+                nbv.y = (q & 1) ? bb.y : mx;
+                nbv.z = (q & 2) ? my : bb.z;
+                nbv.w = (q & 2) ? bb.w : my;
+                C.nb[nxt][pos] = nbv;
+                C.nst[nxt][pos] = run | bit;
+                C.ncn[nxt][pos] = c;
+                if (c > 1) C.expand[0][midx++] = pos;
+                ++cidx;
+            }
+            run += c;
+        }
+    }
+    for (int i = tid; i < S; i += OCT_THREADS) {
+        const uint32_t r = C.flag[i];
+        if (C.flag[i + 1] != r) {
+            const int pos = M + (int)r;
+            C.nb[nxt][pos] = C.nb[cur][i];
+            C.nst[nxt][pos] = C.nst[cur][i];
+            C.ncn[nxt][pos] = C.ncn[cur][i];
+        }
+    }
+    __syncthreads();
+    return M + (int)kept;
+}
+
+// Descending bitonic sort of C.sortk[0..P2) (P2 power of two).
+__device__ __forceinline__ void oct_bitonic_desc(unsigned long long* a, int P2) {
+    for (int k = 2; k <= P2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < P2; i += OCT_THREADS) {
+                const int p = i ^ j;
+                if (p > i) {
+                    const unsigned long long x = a[i], y = a[p];
+                    const bool desc = (i & k) == 0;
+                    if (desc ? (x < y) : (x > y)) {
+                        a[i] = y;
+                        a[p] = x;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// Shared memory carve-up (words).  NC = node capacity, NCP2 = next power of two >= NC,
+// CW = max(4 * NC, cells_max + 1) (cc[] doubles as the cell-offset table during the gather).
+__host__ __device__ inline size_t oct_fixed_words(int NC, int NCP2, int CW) {
+    return (size_t)2 * 2 * NC      // nb[2] (short4 = 2 words)
+           + 2 * NC + 2 * NC       // nst[2], ncn[2]
+           + CW                    // cc / cell offsets
+           + NC                    // proc
+           + NC                    // expand
+           + (NC + 2) + (NC + 2)   // aux, flag
+           + 2 * (size_t)NCP2      // sortk (u64)
+           + OCT_WARPS * 8 + 64;   // wc, tmp
+}
+
+__global__ void __launch_bounds__(OCT_THREADS)
+k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcnt,
+         const uint32_t* __restrict__ cellkeys, uint32_t* __restrict__ keysA,
+         uint32_t* __restrict__ keysB, uint32_t* __restrict__ surv, uint32_t* __restrict__ survcnt,
+         int NC, int NCP2, int CW, int key_words /* shared-memory words per key buffer */) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    const int level = blockIdx.x, frame = blockIdx.y;
+    const OrbxLevel& L = P.lvl[level];
+    const int tid = threadIdx.x, lane = orbx_lane(), warp = orbx_warp();
+
+    OctCtx C;
+    uint32_t* p = sm;
+    C.sortk = reinterpret_cast<unsigned long long*>(p); p += 2 * (size_t)NCP2;
+    C.nb[0] = reinterpret_cast<short4*>(p); p += 2 * NC;
+    C.nb[1] = reinterpret_cast<short4*>(p); p += 2 * NC;
+    C.nst[0] = p; p += NC;
+    C.nst[1] = p; p += NC;
+    C.ncn[0] = p; p += NC;
+    C.ncn[1] = p; p += NC;
+    C.cc = p; p += CW;
+    C.proc = p; p += NC;
+    C.expand[0] = p; C.expand[1] = p; p += NC;
+    C.aux = p; p += NC + 2;
+    C.flag = p; p += NC + 2;
+    C.wc = p; p += OCT_WARPS * 8;
+    C.tmp = p; p += 64;
+    uint32_t* smkeys = p;
+
+    // ---- gather the level's candidates in the reference's order (cells row-major) ----------
+    const int ncells = L.n_cols * L.n_rows;
+    const uint32_t* ccnt = cellcnt + (size_t)frame * P.cells_total + L.cell_off;
+    const uint32_t* ckeys = cellkeys + (size_t)frame * P.keys_total + L.key_off;
+    uint32_t* cofs = C.cc;
+    for (int c = tid; c < ncells; c += OCT_THREADS) cofs[c] = ccnt[c];
+    __syncthreads();
+    const uint32_t nk = block_excl_scan(cofs, ncells, C.tmp);
+    if (tid == 0) cofs[ncells] = nk;
+    __syncthreads();
+    if ((int)nk <= key_words) {
+        C.buf[0] = smkeys;
+        C.buf[1] = smkeys + key_words;
+    } else {
+        C.buf[0] = keysA + (size_t)frame * P.keys_total + L.key_off;
+        C.buf[1] = keysB + (size_t)frame * P.keys_total + L.key_off;
+    }
+    for (int c = warp; c < ncells; c += OCT_WARPS) {
+        const uint32_t o = cofs[c], n = cofs[c + 1] - o;
+        const uint32_t* s = ckeys + (size_t)c * L.cell_cap;
+        for (uint32_t k = lane; k < n; k += 32) C.buf[0][o + k] = s[k];
+    }
+    __syncthreads();
+
+    // ---- root nodes (:541-581): keys -> vpIniNodes[kp.pt.x / hX], empty roots erased --------
+    const int nIni = L.n_ini;
+    const int N = L.n_target;
+    const int Wd = L.max_bx - ORBX_FAST_BORDER, Hd = L.max_by - ORBX_FAST_BORDER;
+    (void)Wd;
+    uint32_t* rootcnt = C.tmp + 48;  // 8 words
+    oct_block_partition<1>(C, C.buf[0], C.buf[1], 0, nk, nIni, 0, 0, L.hx, rootcnt);
+    int S = 0;
+    if (tid == 0) {
+        uint32_t run = 0;
+        int s = 0;
+        for (int i = 0; i < nIni; ++i) {
+            const uint32_t c = rootcnt[i];
+            if (c > 0) {
+                short4 b;
+                b.x = (short)(int)(L.hx * (float)i);
+                b.y = (short)(int)(L.hx * (float)(i + 1));
+                b.z = 0;
+                b.w = (short)Hd;
+                C.nb[0][s] = b;
+                C.nst[0][s] = run | 0x80000000u;  // keys now live in buf[1]
+                C.ncn[0][s] = c;
+                ++s;
+            }
+            run += c;
+        }
+        C.tmp[42] = (uint32_t)s;
+    }
+    __syncthreads();
+    S = (int)C.tmp[42];
+    int cur = 0;
+
+    // ---- main loop (:583-736) -----------------------------------------------------------------
+    bool finish = false;
+    while (!finish) {
+        const int prevS = S;
+        // full pass: every multi-key node, in list order
+        for (int i = tid; i < S; i += OCT_THREADS) C.flag[i] = C.ncn[cur][i] > 1 ? 1u : 0u;
+        __syncthreads();
+        const int E = (int)block_excl_scan(C.flag, S, C.tmp);
+        if (tid == 0) C.flag[S] = (uint32_t)E;
+        __syncthreads();
+        for (int i = tid; i < S; i += OCT_THREADS)
+            if (C.flag[i + 1] != C.flag[i]) C.proc[C.flag[i]] = i;
+        __syncthreads();
+        int nToExpand = 0;
+        S = oct_pass(C, cur, S, E, false, N, &nToExpand);
+        cur ^= 1;
+        if (S >= N || S == prevS) {
+            finish = true;
+        } else if (S + 3 * nToExpand > N) {
+            int Ecur = nToExpand;
+            while (!finish) {
+                const int prev2 = S;
+                // sort the expandable nodes by (key count, creation order), largest first
+                for (int e = tid; e < NCP2; e += OCT_THREADS)
+                    C.sortk[e] = e < Ecur ? (((unsigned long long)C.ncn[cur][C.expand[0][e]] << 32) |
+                                             (unsigned long long)(uint32_t)(e + 1))
+                                          : 0ull;
+                __syncthreads();
+                int P2 = 1;
+                while (P2 < Ecur) P2 <<= 1;
+                oct_bitonic_desc(C.sortk, P2);
+                for (int j = tid; j < Ecur; j += OCT_THREADS)
+                    C.proc[j] = C.expand[0][(uint32_t)(C.sortk[j] & 0xffffffffull) - 1u];
+                __syncthreads();
+                int nm = 0;
+                S = oct_pass(C, cur, S, Ecur, true, N, &nm);
+                cur ^= 1;
+                Ecur = nm;
+                if (S >= N || S == prev2) finish = true;
+            }
+        }
+    }
+
+    // ---- best response per node, first maximum wins (:738-758) --------------------------------
+    uint32_t* out = surv + (size_t)frame * P.surv_total + L.surv_off;
+    const int Sout = min(S, L.surv_cap);
+    for (int i = warp; i < Sout; i += OCT_WARPS) {
+        const uint32_t st = C.nst[cur][i];
+        const uint32_t* src = C.buf[st >> 31] + (st & 0x7fffffffu);
+        const uint32_t cnt = C.ncn[cur][i];
+        unsigned long long best = 0;
+        for (uint32_t k = lane; k < cnt; k += 32) {
+            const unsigned long long v = ((unsigned long long)(src[k] >> 24) << 32) |
+                                         (unsigned long long)(0xffffffffu - k);
+            best = v > best ? v : best;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            const unsigned long long o = __shfl_xor_sync(ORBX_FULL, best, d);
+            best = o > best ? o : best;
+        }
+        if (lane == 0) out[i] = src[0xffffffffu - (uint32_t)(best & 0xffffffffull)];
+    }
+    if (tid == 0) survcnt[(size_t)frame * ORBX_MAX_LEVELS + level] = (uint32_t)S;
+}
+
+struct OctLaunchCfg {
+    int NC, NCP2, CW, key_words;
+    size_t smem;
+};
+
+OctLaunchCfg orbx_octree_cfg(const OrbxPlan& P) {
+    OctLaunchCfg c;
+    int nc = 8, cells = 1;
+    long long kmax = 0;
+    for (int l = 0; l < P.nlevels; ++l) {
+        nc = nc > P.lvl[l].node_cap ? nc : P.lvl[l].node_cap;
+        int cl = P.lvl[l].n_cols * P.lvl[l].n_rows;
+        cells = cells > cl ? cells : cl;
+        kmax = kmax > P.lvl[l].key_cap ? kmax : P.lvl[l].key_cap;
+    }
+    c.NC = nc;
+    c.NCP2 = 1;
+    while (c.NCP2 < nc) c.NCP2 <<= 1;
+    c.CW = 4 * nc > cells + 2 ? 4 * nc : cells + 2;
+    const size_t fixed = oct_fixed_words(c.NC, c.NCP2, c.CW) * 4;
+    // key buffers: as much shared memory as keeps >= 2 CTAs per SM, capped by the worst case
+    size_t budget = 100 * 1024;
+    long long kw = budget > fixed ? (long long)((budget - fixed) / 8) : 0;
+    if (kw > kmax) kw = kmax;
+    kw &= ~3ll;
+    c.key_words = (int)kw;
+    c.smem = fixed + (size_t)kw * 8;
+    return c;
+}
+
+cudaError_t orbx_configure_octree(const OrbxPlan& P) {
+    OctLaunchCfg c = orbx_octree_cfg(P);
+    if (c.smem > 227 * 1024) return cudaErrorInvalidConfiguration;
+    return cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c.smem);
+}
+
+cudaError_t orbx_launch_octree(const OrbxPlan& P, const uint32_t* cellcnt, const uint32_t* cellkeys,
+                               uint32_t* keysA, uint32_t* keysB, uint32_t* surv, uint32_t* survcnt,
+                               int nframes, cudaStream_t st, int* launches) {
+    OctLaunchCfg c = orbx_octree_cfg(P);
+    dim3 grid(P.nlevels, nframes);
+    k_octree<<<grid, OCT_THREADS, c.smem, st>>>(P, cellcnt, cellkeys, keysA, keysB, surv, survcnt, c.NC,
+                                               c.NCP2, c.CW, c.key_words);
+    ++*launches;
+    return cudaGetLastError();
+}

@@ -14,21 +14,22 @@
 #include "orbx_device.cuh"
 
 __global__ void __launch_bounds__(256)
-k_resize_level(const __grid_constant__ OrbxPlan P, int level, uint8_t* __restrict__ pyr) {
+k_resize_level(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, int level,
+               uint8_t* __restrict__ pyr) {
     const OrbxLevel& D = P.lvl[level];
     const OrbxLevel& S = P.lvl[level - 1];
     const int y = blockIdx.y;
     const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (x0 >= D.w) return;
-    uint8_t* frame = pyr + (size_t)blockIdx.z * P.frame_stride;
-    const uint8_t* src = frame + S.off;
-    uint8_t* dst = frame + D.off;
+    int spitch;
+    const uint8_t* src = orbx_level_ptr(P, isrc, pyr, blockIdx.z, level - 1, &spitch);
+    uint8_t* dst = pyr + (size_t)blockIdx.z * P.frame_stride + D.off;
 
     const int sy0 = D.yofs[y];
     const int sy1 = min(sy0 + 1, S.h - 1);
     const short2 bb = reinterpret_cast<const short2*>(D.ya)[y];
-    const uint8_t* r0 = src + (size_t)sy0 * S.pitch;
-    const uint8_t* r1 = src + (size_t)sy1 * S.pitch;
+    const uint8_t* r0 = src + (size_t)sy0 * spitch;
+    const uint8_t* r1 = src + (size_t)sy1 * spitch;
 
     uint32_t out = 0;
 #pragma unroll
@@ -47,12 +48,12 @@ k_resize_level(const __grid_constant__ OrbxPlan P, int level, uint8_t* __restric
     *reinterpret_cast<uint32_t*>(dst + (size_t)y * D.pitch + x0) = out;
 }
 
-void orbx_launch_pyramid(const OrbxPlan& P, uint8_t* pyr, int nframes, cudaStream_t st, int* launches) {
+void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes, cudaStream_t st, int* launches) {
     for (int l = 1; l < P.nlevels; ++l) {
         const OrbxLevel& D = P.lvl[l];
         dim3 block(128);
         dim3 grid((D.w + 4 * 128 - 1) / (4 * 128), D.h, nframes);
-        k_resize_level<<<grid, block, 0, st>>>(P, l, pyr);
+        k_resize_level<<<grid, block, 0, st>>>(P, src, l, pyr);
         ++*launches;
     }
 }

@@ -1,0 +1,730 @@
+// orbx_api.cu -- host runtime behind the C ABI of include/orbx.h.
+//
+// Mirrors the host side of ORB_SLAM3::ORBextractor (reference include/ORBextractor.h:43-109):
+// the constructor's tables (src/ORBextractor.cc:408-468), per-shape planning of everything the
+// reference recomputes per frame (level sizes :1156-1157, FAST cell grid :771-785, quadtree
+// roots :541-556) and the device pipeline  H2D -> pyramid -> FAST -> quadtree -> assemble ->
+// describe -> D2H  on one CUDA stream per pipeline slot.  No CPU implementation of any stage
+// exists here: without a CUDA device orbx_create fails.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "orbx_internal.h"
+
+// kernel launchers (k_*.cu)
+void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes,
+                         cudaStream_t st, int* launches);
+cudaError_t orbx_configure_fast(const OrbxPlan& P);
+cudaError_t orbx_launch_fast(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
+                             uint32_t* cellcnt, uint32_t* cellkeys, int nframes, cudaStream_t st,
+                             int* launches);
+cudaError_t orbx_configure_octree(const OrbxPlan& P);
+cudaError_t orbx_launch_octree(const OrbxPlan& P, const uint32_t* cellcnt, const uint32_t* cellkeys,
+                               uint32_t* keysA, uint32_t* keysB, uint32_t* surv, uint32_t* survcnt,
+                               int nframes, cudaStream_t st, int* launches);
+cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
+                                 const uint32_t* surv, const uint32_t* survcnt, const int* lap,
+                                 uint32_t* dest, int32_t* header, orbx_keypoint* kps, uint8_t* desc,
+                                 int nframes, cudaStream_t st, int* launches);
+
+namespace {
+
+thread_local std::string g_err = "";
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                        \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess)                                                                \
+            return fail(ORBX_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                        __FILE__, __LINE__);                                                  \
+    } while (0)
+
+inline int cv_round(float v) { return (int)lrintf(v); }  // cvRound: round half to even
+inline int cv_round(double v) { return (int)lrint(v); }
+inline int cv_floor(double v) { int i = (int)v; return i - (i > v); }
+inline int round_up(int v, int a) { return (v + a - 1) / a * a; }
+
+struct SlotCaps {  // bytes currently allocated per device buffer
+    size_t img_in = 0, pyr = 0, cellcnt = 0, cellkeys = 0, keysA = 0, keysB = 0, surv = 0, survcnt = 0,
+           dest = 0, header = 0, kps = 0, desc = 0, lap = 0;
+};
+
+struct Slot {
+    SlotCaps caps;
+    cudaStream_t st = nullptr;
+    uint8_t* img_in = nullptr;   // device staging of the H2D copy (level 0)
+    uint8_t* pyr = nullptr;
+    uint32_t *cellcnt = nullptr, *cellkeys = nullptr, *keysA = nullptr, *keysB = nullptr;
+    uint32_t *surv = nullptr, *survcnt = nullptr, *dest = nullptr;
+    int32_t* header = nullptr;
+    orbx_keypoint* kps = nullptr;
+    uint8_t* desc = nullptr;
+    int* lap_d = nullptr;
+    int32_t* h_header = nullptr;  // pinned
+    int* h_lap = nullptr;         // pinned
+    // in-flight bookkeeping
+    bool in_flight = false;
+    int nframes = 0, cap = 0, launches = 0;
+    int *u_n = nullptr, *u_mono = nullptr, *u_status = nullptr;
+    OrbxSrc src{};               // level-0 source of the last run (for the debug taps)
+    int run_w = 0, run_h = 0;
+};
+
+}  // namespace
+
+struct orbx_handle {
+    orbx_config cfg;
+    std::vector<float> sf, isf, s2, is2;
+    std::vector<int> nper;
+    OrbxPlan plan;       // for plan.w x plan.h (0 = none yet)
+    OrbxPlan cap_plan;   // for max_width x max_height: sizes every buffer
+    uint8_t* tables = nullptr;  // device resize tables of `plan`
+    size_t tables_bytes = 0;
+    int pitch0_cap = 0;
+    std::vector<Slot> slots;
+};
+
+namespace {
+
+// ---- ORBextractor::ORBextractor, src/ORBextractor.cc:408-444 ---------------------------------
+void build_tables(orbx_handle* h) {
+    const int nl = h->cfg.nlevels;
+    const double scaleFactor = (double)h->cfg.scale_factor;  // `double scaleFactor` member
+    h->sf.assign(nl, 1.f);
+    h->s2.assign(nl, 1.f);
+    h->isf.assign(nl, 1.f);
+    h->is2.assign(nl, 1.f);
+    for (int i = 1; i < nl; ++i) {
+        h->sf[i] = (float)(h->sf[i - 1] * scaleFactor);
+        h->s2[i] = h->sf[i] * h->sf[i];
+    }
+    for (int i = 0; i < nl; ++i) {
+        h->isf[i] = 1.0f / h->sf[i];
+        h->is2[i] = 1.0f / h->s2[i];
+    }
+    h->nper.assign(nl, 0);
+    const float factor = (float)(1.0f / scaleFactor);
+    float nDesired = (float)(h->cfg.nfeatures * (1 - factor) /
+                             (1 - (float)pow((double)factor, (double)nl)));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+        h->nper[l] = cv_round(nDesired);
+        sum += h->nper[l];
+        nDesired *= factor;
+    }
+    h->nper[nl - 1] = std::max(h->cfg.nfeatures - sum, 0);
+}
+
+// OpenCV's INTER_LINEAR tables for one axis (imgproc/resize.cpp): source offset and the two
+// 11-bit coefficients per destination index.  Filled into host vectors, uploaded by the caller.
+void linear_axis(int ssize, int dsize, std::vector<uint16_t>& ofs, std::vector<short>& coef) {
+    ofs.resize(dsize);
+    coef.resize((size_t)2 * dsize);
+    const double inv_scale = (double)dsize / ssize;
+    const double scale = 1. / inv_scale;
+    for (int d = 0; d < dsize; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = cv_floor(f);
+        f -= s;
+        if (s < 0) { f = 0; s = 0; }
+        if (s >= ssize - 1) { f = 0; s = ssize - 1; }
+        ofs[d] = (uint16_t)s;
+        coef[2 * d] = (short)cv_round((1.f - f) * 2048.f);
+        coef[2 * d + 1] = (short)cv_round(f * 2048.f);
+    }
+}
+
+// Everything that depends on the image shape.  Returns an orbx_status.
+int build_plan(const orbx_handle* h, int w, int hgt, OrbxPlan* out, std::vector<uint8_t>* tab_host) {
+    OrbxPlan& P = *out;
+    memset(&P, 0, sizeof P);
+    const int nl = h->cfg.nlevels;
+    P.nlevels = nl;
+    P.w = w;
+    P.h = hgt;
+    P.ini_th = std::min(std::max(h->cfg.ini_th_fast, 0), 255);
+    P.min_th = std::min(std::max(h->cfg.min_th_fast, 0), 255);
+    if (w > ORBX_MAX_DIM || hgt > ORBX_MAX_DIM) return fail(ORBX_E_UNSUPPORTED, "image larger than %d", ORBX_MAX_DIM);
+    long long off = 0, key_off = 0;
+    int cell_off = 0, surv_off = 0;
+    size_t tab_off = 0;
+    if (tab_host) tab_host->clear();
+    for (int l = 0; l < nl; ++l) {
+        OrbxLevel& L = P.lvl[l];
+        // ORBextractor.cc:1156-1157
+        L.w = cv_round((float)w * h->isf[l]);
+        L.h = cv_round((float)hgt * h->isf[l]);
+        L.scale = h->sf[l];
+        L.size = (float)(int)(31 * h->sf[l]);  // PATCH_SIZE * mvScaleFactor[level], :862
+        if (l == 0) {
+            L.pitch = 0;  // level 0 lives in the source buffer (OrbxSrc)
+            L.off = 0;
+        } else {
+            L.pitch = round_up(L.w, 64);
+            L.off = off;
+            off += (long long)L.pitch * L.h;
+            off = (off + 255) & ~255ll;
+        }
+        // ORBextractor.cc:771-785
+        L.max_bx = L.w - ORBX_FAST_BORDER;
+        L.max_by = L.h - ORBX_FAST_BORDER;
+        const float width = (float)(L.max_bx - ORBX_FAST_BORDER);
+        const float height = (float)(L.max_by - ORBX_FAST_BORDER);
+        L.n_cols = (int)(width / 30.f);
+        L.n_rows = (int)(height / 30.f);
+        if (L.n_cols < 1 || L.n_rows < 1)
+            return fail(ORBX_E_UNSUPPORTED, "level %d (%dx%d) has no 30-px FAST cell; the reference divides by zero here", l, L.w, L.h);
+        L.w_cell = (int)ceilf(width / L.n_cols);
+        L.h_cell = (int)ceilf(height / L.n_rows);
+        L.cell_cap = ((L.w_cell + 1) / 2) * ((L.h_cell + 1) / 2);
+        L.cell_off = cell_off;
+        cell_off += L.n_cols * L.n_rows;
+        L.key_off = key_off;
+        L.key_cap = L.n_cols * L.n_rows * L.cell_cap;
+        key_off += L.key_cap;
+        P.max_tile_w = std::max(P.max_tile_w, L.w_cell + 6);
+        P.max_tile_h = std::max(P.max_tile_h, L.h_cell + 6);
+        // ORBextractor.cc:541-543
+        L.n_target = h->nper[l];
+        const int Wd = L.max_bx - ORBX_FAST_BORDER, Hd = L.max_by - ORBX_FAST_BORDER;
+        L.n_ini = (int)roundf((float)Wd / Hd);
+        if (L.n_ini < 1 || L.n_ini > 8)
+            return fail(ORBX_E_UNSUPPORTED, "level %d: nIni=%d (aspect ratio outside [0.5, 8.5)); the reference divides by zero for nIni=0", l, L.n_ini);
+        L.hx = (float)Wd / L.n_ini;
+        L.node_cap = std::max(L.n_target + 3, 4 * L.n_ini) + 5;
+        if (L.node_cap > 8192) return fail(ORBX_E_UNSUPPORTED, "more than 8184 features on one level");
+        L.surv_off = surv_off;
+        L.surv_cap = L.node_cap;
+        surv_off += L.surv_cap;
+        // resize tables (level l from level l-1)
+        if (l > 0) {
+            std::vector<uint16_t> xo, yo;
+            std::vector<short> xa, ya;
+            linear_axis(P.lvl[l - 1].w, L.w, xo, xa);
+            linear_axis(P.lvl[l - 1].h, L.h, yo, ya);
+            auto put = [&](const void* p, size_t n) -> size_t {
+                size_t at = tab_off;
+                if (tab_host) {
+                    tab_host->resize(at + ((n + 15) & ~(size_t)15));
+                    memcpy(tab_host->data() + at, p, n);
+                }
+                tab_off += (n + 15) & ~(size_t)15;
+                return at;
+            };
+            // stored as offsets; patched to device pointers by the caller
+            L.xofs = (const uint16_t*)put(xo.data(), xo.size() * 2);
+            L.xa = (const short*)put(xa.data(), xa.size() * 2);
+            L.yofs = (const uint16_t*)put(yo.data(), yo.size() * 2);
+            L.ya = (const short*)put(ya.data(), ya.size() * 2);
+        }
+    }
+    P.frame_stride = std::max(off, 256ll);
+    P.cells_total = cell_off;
+    P.keys_total = key_off;
+    P.surv_total = surv_off;
+    P.out_cap = surv_off;
+    if (P.max_tile_w > 80 || P.max_tile_h > 80) return fail(ORBX_E_UNSUPPORTED, "FAST cell larger than 74 px");
+    return ORBX_OK;
+}
+
+size_t plan_table_bytes(const orbx_handle* h, int w, int hgt) {
+    // upper bound: 6 bytes per column and per row per level, 16-byte padded
+    size_t n = 0;
+    for (int l = 1; l < h->cfg.nlevels; ++l) n += (size_t)(w + hgt) * 6 + 64;
+    return n + 256;
+}
+
+void patch_tables(OrbxPlan& P, uint8_t* dev_base) {
+    for (int l = 1; l < P.nlevels; ++l) {
+        OrbxLevel& L = P.lvl[l];
+        L.xofs = (const uint16_t*)(dev_base + (size_t)L.xofs);
+        L.xa = (const short*)(dev_base + (size_t)L.xa);
+        L.yofs = (const uint16_t*)(dev_base + (size_t)L.yofs);
+        L.ya = (const short*)(dev_base + (size_t)L.ya);
+    }
+}
+
+}  // namespace
+
+// =================================================================================================
+// buffers
+// =================================================================================================
+namespace {
+
+struct Sizes {
+    size_t img_in, pyr, cellcnt, keys, surv, survcnt, header, kps, desc, lap;
+};
+
+Sizes sizes_for(const OrbxPlan& P, int B) {
+    Sizes z;
+    z.img_in = (size_t)B * round_up(P.w, 16) * P.h + 64;
+    z.pyr = (size_t)B * P.frame_stride + 64;
+    z.cellcnt = (size_t)B * P.cells_total * 4;
+    z.keys = (size_t)B * P.keys_total * 4;
+    z.surv = (size_t)B * P.surv_total * 4;
+    z.survcnt = (size_t)B * ORBX_MAX_LEVELS * 4;
+    z.header = (size_t)B * 16;
+    z.kps = (size_t)B * P.out_cap * sizeof(orbx_keypoint);
+    z.desc = (size_t)B * P.out_cap * 32;
+    z.lap = (size_t)B * 8;
+    return z;
+}
+
+template <typename T>
+int grow(T** p, size_t* have, size_t need) {
+    if (need <= *have && *p) return ORBX_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *have = 0;
+    need += need / 8;  // headroom for the next, slightly different shape
+    CUDA_TRY(cudaMalloc((void**)p, need));
+    *have = need;
+    return ORBX_OK;
+}
+
+int ensure_buffers(orbx_handle* h, const OrbxPlan& P) {
+    const Sizes z = sizes_for(P, h->cfg.max_batch);
+    for (size_t i = 0; i < h->slots.size(); ++i) {
+        Slot& s = h->slots[i];
+        SlotCaps& c = s.caps;
+        int r;
+        if ((r = grow(&s.img_in, &c.img_in, z.img_in))) return r;
+        if ((r = grow(&s.pyr, &c.pyr, z.pyr))) return r;
+        if ((r = grow(&s.cellcnt, &c.cellcnt, z.cellcnt))) return r;
+        if ((r = grow(&s.cellkeys, &c.cellkeys, z.keys))) return r;
+        if ((r = grow(&s.keysA, &c.keysA, z.keys))) return r;
+        if ((r = grow(&s.keysB, &c.keysB, z.keys))) return r;
+        if ((r = grow(&s.surv, &c.surv, z.surv))) return r;
+        if ((r = grow(&s.survcnt, &c.survcnt, z.survcnt))) return r;
+        if ((r = grow(&s.dest, &c.dest, z.surv))) return r;
+        if ((r = grow(&s.header, &c.header, z.header))) return r;
+        if ((r = grow(&s.kps, &c.kps, z.kps))) return r;
+        if ((r = grow(&s.desc, &c.desc, z.desc))) return r;
+        if ((r = grow(&s.lap_d, &c.lap, z.lap))) return r;
+    }
+    return ORBX_OK;
+}
+
+int sync_all(orbx_handle* h) {
+    for (Slot& s : h->slots) CUDA_TRY(cudaStreamSynchronize(s.st));
+    return ORBX_OK;
+}
+
+// Switch the handle to image shape (w, hgt): plan, tables upload, kernel attributes, buffers.
+int set_shape(orbx_handle* h, int w, int hgt) {
+    if (h->plan.w == w && h->plan.h == hgt) return ORBX_OK;
+    OrbxPlan P;
+    std::vector<uint8_t> tab;
+    int r = build_plan(h, w, hgt, &P, &tab);
+    if (r) return r;
+    if ((r = sync_all(h))) return r;
+    size_t need = std::max(tab.size(), (size_t)256);
+    if ((r = grow(&h->tables, &h->tables_bytes, need))) return r;
+    if (!tab.empty()) CUDA_TRY(cudaMemcpy(h->tables, tab.data(), tab.size(), cudaMemcpyHostToDevice));
+    patch_tables(P, h->tables);
+    CUDA_TRY(orbx_configure_fast(P));
+    cudaError_t e = orbx_configure_octree(P);
+    if (e != cudaSuccess)
+        return fail(ORBX_E_UNSUPPORTED, "quadtree working set exceeds shared memory (nfeatures too large)");
+    if ((r = ensure_buffers(h, P))) return r;
+    h->plan = P;
+    return ORBX_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+// pipeline
+// =================================================================================================
+namespace {
+
+// Enqueue the whole device pipeline for `nframes` frames whose level 0 is `src`.
+int enqueue_kernels(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes) {
+    const OrbxPlan& P = h->plan;
+    s.launches = 0;
+    orbx_launch_pyramid(P, src, s.pyr, nframes, s.st, &s.launches);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(orbx_launch_fast(P, src, s.pyr, s.cellcnt, s.cellkeys, nframes, s.st, &s.launches));
+    CUDA_TRY(orbx_launch_octree(P, s.cellcnt, s.cellkeys, s.keysA, s.keysB, s.surv, s.survcnt, nframes,
+                                s.st, &s.launches));
+    CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.surv, s.survcnt, s.lap_d, s.dest, s.header, s.kps,
+                                  s.desc, nframes, s.st, &s.launches));
+    s.src = src;
+    s.run_w = P.w;
+    s.run_h = P.h;
+    s.nframes = nframes;
+    return ORBX_OK;
+}
+
+int check_common(orbx_handle* h, int slot, int nframes, int w, int hgt) {
+    if (!h) return fail(ORBX_E_BAD_ARG, "null handle");
+    if (slot < 0 || slot >= (int)h->slots.size()) return fail(ORBX_E_BAD_ARG, "slot %d out of range", slot);
+    if (nframes < 1) return fail(ORBX_E_BAD_ARG, "nframes must be >= 1");
+    if (nframes > h->cfg.max_batch) return fail(ORBX_E_TOO_LARGE, "nframes %d > max_batch %d", nframes, h->cfg.max_batch);
+    if (w <= 0 || hgt <= 0) return fail(ORBX_E_EMPTY_IMAGE, "empty image");
+    if (w > h->cfg.max_width || hgt > h->cfg.max_height)
+        return fail(ORBX_E_TOO_LARGE, "%dx%d exceeds the handle's %dx%d", w, hgt, h->cfg.max_width, h->cfg.max_height);
+    if (h->slots[slot].in_flight) return fail(ORBX_E_BUSY, "slot %d has an un-waited submit", slot);
+    return ORBX_OK;
+}
+
+int upload_lap(Slot& s, const int* lap, int nframes) {
+    for (int i = 0; i < nframes; ++i) {
+        s.h_lap[2 * i] = lap ? lap[2 * i] : 0;
+        s.h_lap[2 * i + 1] = lap ? lap[2 * i + 1] : 0;
+    }
+    CUDA_TRY(cudaMemcpyAsync(s.lap_d, s.h_lap, (size_t)nframes * 8, cudaMemcpyHostToDevice, s.st));
+    return ORBX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbx_abi_version(void) { return ORBX_ABI_VERSION; }
+const char* orbx_last_error_string(void) { return g_err.c_str(); }
+
+int orbx_create(const orbx_config* cfg, orbx_handle** out) {
+    if (!cfg || !out) return fail(ORBX_E_BAD_ARG, "null argument");
+    *out = nullptr;
+    if (cfg->nlevels < 1 || cfg->nlevels > ORBX_MAX_LEVELS) return fail(ORBX_E_BAD_ARG, "nlevels must be 1..%d", ORBX_MAX_LEVELS);
+    if (cfg->nfeatures < 1) return fail(ORBX_E_BAD_ARG, "nfeatures must be >= 1");
+    if (!(cfg->scale_factor > 1.0f)) return fail(ORBX_E_BAD_ARG, "scale_factor must be > 1");
+    if (cfg->max_width < 1 || cfg->max_height < 1 || cfg->max_batch < 1) return fail(ORBX_E_BAD_ARG, "max_width/max_height/max_batch must be >= 1");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(ORBX_E_CUDA, "no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(e));
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(ORBX_E_BAD_ARG, "device %d out of range", cfg->device);
+    CUDA_TRY(cudaSetDevice(cfg->device));
+    orbx_handle* h = new orbx_handle();
+    h->cfg = *cfg;
+    if (h->cfg.n_slots <= 0) h->cfg.n_slots = 2;
+    memset(&h->plan, 0, sizeof h->plan);
+    build_tables(h);
+    h->slots.resize(h->cfg.n_slots);
+    int r = ORBX_OK;
+    for (Slot& s : h->slots) {
+        if (cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaMallocHost((void**)&s.h_header, (size_t)h->cfg.max_batch * 16) != cudaSuccess ||
+            cudaMallocHost((void**)&s.h_lap, (size_t)h->cfg.max_batch * 8) != cudaSuccess) {
+            r = fail(ORBX_E_CUDA, "stream / pinned allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+            break;
+        }
+    }
+    if (r == ORBX_OK) r = set_shape(h, cfg->max_width, cfg->max_height);
+    if (r != ORBX_OK) {
+        std::string keep = g_err;
+        orbx_destroy(h);
+        g_err = keep;
+        return r;
+    }
+    *out = h;
+    return ORBX_OK;
+}
+
+int orbx_destroy(orbx_handle* h) {
+    if (!h) return ORBX_OK;
+    cudaSetDevice(h->cfg.device);
+    for (Slot& s : h->slots) {
+        if (s.st) cudaStreamSynchronize(s.st);
+        cudaFree(s.img_in); cudaFree(s.pyr); cudaFree(s.cellcnt); cudaFree(s.cellkeys);
+        cudaFree(s.keysA); cudaFree(s.keysB); cudaFree(s.surv); cudaFree(s.survcnt);
+        cudaFree(s.dest); cudaFree(s.header); cudaFree(s.kps); cudaFree(s.desc); cudaFree(s.lap_d);
+        if (s.h_header) cudaFreeHost(s.h_header);
+        if (s.h_lap) cudaFreeHost(s.h_lap);
+        if (s.st) cudaStreamDestroy(s.st);
+    }
+    cudaFree(h->tables);
+    delete h;
+    return ORBX_OK;
+}
+
+int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_scale, float* sigma2,
+                    float* inv_sigma2, int32_t* n_per_level) {
+    if (!h) return fail(ORBX_E_BAD_ARG, "null handle");
+    for (int i = 0; i < h->cfg.nlevels; ++i) {
+        if (scale) scale[i] = h->sf[i];
+        if (inv_scale) inv_scale[i] = h->isf[i];
+        if (sigma2) sigma2[i] = h->s2[i];
+        if (inv_sigma2) inv_sigma2[i] = h->is2[i];
+        if (n_per_level) n_per_level[i] = h->nper[i];
+    }
+    return ORBX_OK;
+}
+
+int orbx_max_keypoints(const orbx_handle* h) { return h ? h->plan.out_cap : ORBX_E_BAD_ARG; }
+
+void* orbx_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) {
+        fail(ORBX_E_CUDA, "cudaMallocHost(%zu) failed", bytes);
+        return nullptr;
+    }
+    return p;
+}
+void orbx_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+void* orbx_slot_stream(orbx_handle* h, int slot) {
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return nullptr;
+    return (void*)h->slots[slot].st;
+}
+
+int orbx_last_launch_count(const orbx_handle* h, int slot) {
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return ORBX_E_BAD_ARG;
+    return h->slots[slot].launches;
+}
+
+int orbx_level_size(const orbx_handle* h, int w, int hgt, int level, int* lw, int* lh) {
+    if (!h || level < 0 || level >= h->cfg.nlevels) return fail(ORBX_E_BAD_ARG, "bad level");
+    if (lw) *lw = cv_round((float)w * h->isf[level]);
+    if (lh) *lh = cv_round((float)hgt * h->isf[level]);
+    return ORBX_OK;
+}
+
+int orbx_extract_device(orbx_handle* h, int slot, const uint8_t* d_imgs, int nframes, int w, int hgt,
+                        size_t pitch_bytes, size_t frame_stride_bytes, const int* lap,
+                        const int32_t** d_header, const orbx_keypoint** d_kps, const uint8_t** d_desc) {
+    int r = check_common(h, slot, nframes, w, hgt);
+    if (r) return r;
+    if (!d_imgs) return fail(ORBX_E_EMPTY_IMAGE, "null image");
+    if (((uintptr_t)d_imgs & 3) || (pitch_bytes & 3) || (frame_stride_bytes & 3) || pitch_bytes < (size_t)round_up(w, 4))
+        return fail(ORBX_E_BAD_ARG, "device images need 4-byte aligned pointer/pitch/stride and pitch >= round_up(w,4)");
+    CUDA_TRY(cudaSetDevice(h->cfg.device));
+    if ((r = set_shape(h, w, hgt))) return r;
+    Slot& s = h->slots[slot];
+    if ((r = upload_lap(s, lap, nframes))) return r;
+    OrbxSrc src;
+    src.img0 = d_imgs;
+    src.pitch0 = (int)pitch_bytes;
+    src.stride0 = (long long)frame_stride_bytes;
+    src._pad = 0;
+    if ((r = enqueue_kernels(h, s, src, nframes))) return r;
+    s.in_flight = true;
+    s.u_n = s.u_mono = s.u_status = nullptr;
+    s.cap = 0;
+    if (d_header) *d_header = s.header;
+    if (d_kps) *d_kps = s.kps;
+    if (d_desc) *d_desc = s.desc;
+    return ORBX_OK;
+}
+
+int orbx_submit_batch(orbx_handle* h, int slot, const uint8_t* const* imgs, int nframes, int w, int hgt,
+                      size_t stride_bytes, const int* lap, orbx_keypoint* kps, uint8_t* desc, int cap,
+                      int* n_out, int* mono_index, int* status) {
+    int r = check_common(h, slot, nframes, w, hgt);
+    if (r) return r;
+    if (!imgs || !kps || !desc || !n_out) return fail(ORBX_E_BAD_ARG, "null argument");
+    if (cap < 1) return fail(ORBX_E_BAD_ARG, "cap must be >= 1");
+    if (stride_bytes < (size_t)w) return fail(ORBX_E_BAD_ARG, "stride < width");
+    for (int i = 0; i < nframes; ++i)
+        if (!imgs[i]) return fail(ORBX_E_EMPTY_IMAGE, "frame %d is null", i);
+    CUDA_TRY(cudaSetDevice(h->cfg.device));
+    if ((r = set_shape(h, w, hgt))) return r;
+    Slot& s = h->slots[slot];
+    const OrbxPlan& P = h->plan;
+    // H2D: one copy when the frames are contiguous and tightly packed at the device pitch
+    const int pitch0 = round_up(w, 16);
+    const size_t fstride = (size_t)pitch0 * hgt;
+    bool contiguous = stride_bytes == (size_t)pitch0;
+    for (int i = 1; i < nframes && contiguous; ++i) contiguous = imgs[i] == imgs[0] + (size_t)i * fstride;
+    if (contiguous) {
+        CUDA_TRY(cudaMemcpyAsync(s.img_in, imgs[0], fstride * nframes, cudaMemcpyHostToDevice, s.st));
+    } else {
+        for (int i = 0; i < nframes; ++i)
+            CUDA_TRY(cudaMemcpy2DAsync(s.img_in + (size_t)i * fstride, pitch0, imgs[i], stride_bytes, w, hgt,
+                                       cudaMemcpyHostToDevice, s.st));
+    }
+    if ((r = upload_lap(s, lap, nframes))) return r;
+    OrbxSrc src;
+    src.img0 = s.img_in;
+    src.pitch0 = pitch0;
+    src.stride0 = (long long)fstride;
+    src._pad = 0;
+    if ((r = enqueue_kernels(h, s, src, nframes))) return r;
+    // D2H: header, keypoints, descriptors (device rows are out_cap apart, caller rows cap apart)
+    const int rows = std::min(cap, P.out_cap);
+    CUDA_TRY(cudaMemcpyAsync(s.h_header, s.header, (size_t)nframes * 16, cudaMemcpyDeviceToHost, s.st));
+    CUDA_TRY(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbx_keypoint), s.kps, (size_t)P.out_cap * sizeof(orbx_keypoint),
+                               (size_t)rows * sizeof(orbx_keypoint), nframes, cudaMemcpyDeviceToHost, s.st));
+    CUDA_TRY(cudaMemcpy2DAsync(desc, (size_t)cap * 32, s.desc, (size_t)P.out_cap * 32, (size_t)rows * 32, nframes,
+                               cudaMemcpyDeviceToHost, s.st));
+    s.in_flight = true;
+    s.cap = cap;
+    s.u_n = n_out;
+    s.u_mono = mono_index;
+    s.u_status = status;
+    return ORBX_OK;
+}
+
+int orbx_wait(orbx_handle* h, int slot) {
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(ORBX_E_BAD_ARG, "bad slot");
+    Slot& s = h->slots[slot];
+    if (!s.in_flight) return ORBX_OK;
+    s.in_flight = false;
+    CUDA_TRY(cudaStreamSynchronize(s.st));
+    int worst = ORBX_OK;
+    if (s.u_n) {
+        for (int i = 0; i < s.nframes; ++i) {
+            const int n = s.h_header[4 * i], mono = s.h_header[4 * i + 1];
+            int st = s.h_header[4 * i + 2];
+            if (n > s.cap) st = ORBX_E_CAPACITY;
+            s.u_n[i] = n;
+            if (s.u_mono) s.u_mono[i] = mono;
+            if (s.u_status) s.u_status[i] = st;
+            if (st != ORBX_OK && worst == ORBX_OK)
+                worst = fail(st, "frame %d: %d keypoints exceed the output capacity %d", i, n, s.cap);
+        }
+    }
+    return worst;
+}
+
+int orbx_extract_batch(orbx_handle* h, const uint8_t* const* imgs, int nframes, int w, int hgt,
+                       size_t stride_bytes, const int* lap, orbx_keypoint* kps, uint8_t* desc, int cap,
+                       int* n_out, int* mono_index, int* status) {
+    int r = orbx_submit_batch(h, 0, imgs, nframes, w, hgt, stride_bytes, lap, kps, desc, cap, n_out,
+                              mono_index, status);
+    if (r) return r;
+    return orbx_wait(h, 0);
+}
+
+int orbx_extract(orbx_handle* h, const uint8_t* img, int w, int hgt, size_t stride_bytes, int lap_x0,
+                 int lap_x1, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index) {
+    if (!img || w <= 0 || hgt <= 0) return fail(ORBX_E_EMPTY_IMAGE, "empty image");
+    const int lap[2] = {lap_x0, lap_x1};
+    const uint8_t* imgs[1] = {img};
+    return orbx_extract_batch(h, imgs, 1, w, hgt, stride_bytes, lap, kps, desc, cap, n_out, mono_index, nullptr);
+}
+
+}  // extern "C"
+
+// =================================================================================================
+// pyramid access and stage taps (results of the last run on a slot)
+// =================================================================================================
+namespace {
+
+inline int reflect101_host(int p, int len) {
+    if (len == 1) return 0;
+    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
+    return p;
+}
+
+int tap_ready(orbx_handle* h, int slot, int frame, int level) {
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(ORBX_E_BAD_ARG, "bad slot");
+    Slot& s = h->slots[slot];
+    if (s.in_flight) return fail(ORBX_E_BUSY, "slot %d not waited", slot);
+    if (frame < 0 || frame >= s.nframes) return fail(ORBX_E_BAD_ARG, "frame %d not in the last batch", frame);
+    if (level < 0 || level >= h->cfg.nlevels) return fail(ORBX_E_BAD_ARG, "bad level");
+    if (s.run_w != h->plan.w || s.run_h != h->plan.h) return fail(ORBX_E_BAD_ARG, "shape changed since the last run");
+    CUDA_TRY(cudaSetDevice(h->cfg.device));
+    return ORBX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbx_get_pyramid_level(orbx_handle* h, int slot, int frame, int level, int pad, uint8_t* dst,
+                           size_t dst_stride) {
+    int r = tap_ready(h, slot, frame, level);
+    if (r) return r;
+    if (!dst || pad < 0) return fail(ORBX_E_BAD_ARG, "bad argument");
+    Slot& s = h->slots[slot];
+    const OrbxLevel& L = h->plan.lvl[level];
+    const uint8_t* src;
+    size_t spitch;
+    if (level == 0) {
+        src = s.src.img0 + (size_t)frame * s.src.stride0;
+        spitch = (size_t)s.src.pitch0;
+    } else {
+        src = s.pyr + (size_t)frame * h->plan.frame_stride + L.off;
+        spitch = (size_t)L.pitch;
+    }
+    if (dst_stride < (size_t)(L.w + 2 * pad)) return fail(ORBX_E_BAD_ARG, "dst_stride too small");
+    CUDA_TRY(cudaMemcpy2D(dst + (size_t)pad * dst_stride + pad, dst_stride, src, spitch, L.w, L.h,
+                          cudaMemcpyDeviceToHost));
+    if (pad > 0) {
+        // the reference's copyMakeBorder(..., BORDER_REFLECT_101) around the level
+        // (ORBextractor.cc:1167-1173); a pure host-side re-indexing of the copied pixels
+        for (int y = 0; y < L.h; ++y) {
+            uint8_t* row = dst + (size_t)(y + pad) * dst_stride;
+            for (int x = 0; x < pad; ++x) {
+                row[x] = row[pad + reflect101_host(x - pad, L.w)];
+                row[pad + L.w + x] = row[pad + reflect101_host(L.w + x, L.w)];
+            }
+        }
+        for (int y = 0; y < pad; ++y) {
+            memcpy(dst + (size_t)y * dst_stride, dst + (size_t)(pad + reflect101_host(y - pad, L.h)) * dst_stride, L.w + 2 * pad);
+            memcpy(dst + (size_t)(pad + L.h + y) * dst_stride,
+                   dst + (size_t)(pad + reflect101_host(L.h + y, L.h)) * dst_stride, L.w + 2 * pad);
+        }
+    }
+    return ORBX_OK;
+}
+
+int orbx_debug_candidates(orbx_handle* h, int slot, int frame, int level, int32_t* xyr, int cap) {
+    int r = tap_ready(h, slot, frame, level);
+    if (r) return r;
+    Slot& s = h->slots[slot];
+    const OrbxPlan& P = h->plan;
+    const OrbxLevel& L = P.lvl[level];
+    const int ncells = L.n_cols * L.n_rows;
+    std::vector<uint32_t> cnt(ncells), keys((size_t)L.key_cap);
+    CUDA_TRY(cudaMemcpy(cnt.data(), s.cellcnt + (size_t)frame * P.cells_total + L.cell_off, (size_t)ncells * 4,
+                        cudaMemcpyDeviceToHost));
+    CUDA_TRY(cudaMemcpy(keys.data(), s.cellkeys + (size_t)frame * P.keys_total + L.key_off, (size_t)L.key_cap * 4,
+                        cudaMemcpyDeviceToHost));
+    int n = 0;
+    for (int c = 0; c < ncells; ++c) {
+        if ((int)cnt[c] > L.cell_cap) return fail(ORBX_E_CUDA, "cell %d count %u exceeds its slot", c, cnt[c]);
+        for (uint32_t k = 0; k < cnt[c]; ++k, ++n) {
+            if (xyr && n < cap) {
+                const uint32_t key = keys[(size_t)c * L.cell_cap + k];
+                xyr[3 * n] = ORBX_KEY_X(key);
+                xyr[3 * n + 1] = ORBX_KEY_Y(key);
+                xyr[3 * n + 2] = ORBX_KEY_R(key);
+            }
+        }
+    }
+    return n;
+}
+
+int orbx_debug_survivors(orbx_handle* h, int slot, int frame, int level, int32_t* xyr, int cap) {
+    int r = tap_ready(h, slot, frame, level);
+    if (r) return r;
+    Slot& s = h->slots[slot];
+    const OrbxPlan& P = h->plan;
+    const OrbxLevel& L = P.lvl[level];
+    uint32_t n = 0;
+    CUDA_TRY(cudaMemcpy(&n, s.survcnt + (size_t)frame * ORBX_MAX_LEVELS + level, 4, cudaMemcpyDeviceToHost));
+    if ((int)n > L.surv_cap) return fail(ORBX_E_CUDA, "level %d: %u nodes exceed the bound %d", level, n, L.surv_cap);
+    std::vector<uint32_t> keys(n);
+    if (n) CUDA_TRY(cudaMemcpy(keys.data(), s.surv + (size_t)frame * P.surv_total + L.surv_off, (size_t)n * 4,
+                               cudaMemcpyDeviceToHost));
+    for (uint32_t i = 0; i < n && xyr && (int)i < cap; ++i) {
+        xyr[3 * i] = ORBX_KEY_X(keys[i]);
+        xyr[3 * i + 1] = ORBX_KEY_Y(keys[i]);
+        xyr[3 * i + 2] = ORBX_KEY_R(keys[i]);
+    }
+    return (int)n;
+}
+
+}  // extern "C"

@@ -17,6 +17,18 @@ __device__ __forceinline__ uint32_t orbx_lanemask_lt() {
     return m;
 }
 
+// Base pointer and pitch of level l of one frame (level 0 lives in the caller's image buffer).
+__device__ __forceinline__ const uint8_t* orbx_level_ptr(const OrbxPlan& P, const OrbxSrc& src,
+                                                         const uint8_t* pyr, int frame, int l,
+                                                         int* pitch) {
+    if (l == 0) {
+        *pitch = src.pitch0;
+        return src.img0 + (size_t)frame * src.stride0;
+    }
+    *pitch = P.lvl[l].pitch;
+    return pyr + (size_t)frame * P.frame_stride + P.lvl[l].off;
+}
+
 __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {

@@ -1,7 +1,9 @@
 // orbx_internal.h -- structures shared by the host runtime (orbx_api.cu) and the kernels.
 //
 // Data layout in HBM (per pipeline slot, B = max_batch frames; all sizes for one image shape):
-//   pyr      u8   [B][frame_stride]          levels packed per frame; level l at lvl[l].off,
+//   img0     u8   [B][stride0]               level 0 = the input frames (device staging of the
+//                                            H2D copy, or the caller's device buffer), pitch0
+//   pyr      u8   [B][frame_stride]          levels 1.. packed per frame; level l at lvl[l].off,
 //                                            row pitch lvl[l].pitch; NO border is materialised
 //                                            (nothing on the path reads it)
 //   cellcnt  u32  [B][cells_total]           post-NMS corner count per 30-px FAST cell
@@ -71,6 +73,15 @@ struct OrbxPlan {
     int max_tile_w, max_tile_h;  // FAST tile (cell + 6) maxima over levels
     int _pad;
     OrbxLevel lvl[ORBX_MAX_LEVELS];
+};
+
+// Level 0 is the caller's image itself (never copied into the slab): device pointer to the
+// batch, row pitch and frame stride in bytes.  Pointer and pitch are 4-byte aligned.
+struct OrbxSrc {
+    const uint8_t* img0;
+    long long stride0;
+    int pitch0;
+    int _pad;
 };
 
 #endif  // ORBX_INTERNAL_H

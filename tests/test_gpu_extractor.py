@@ -1,0 +1,164 @@
+"""Parity of the CUDA extractor (through the C ABI) against the CPU oracle, stage by stage.
+
+Bars (BASELINE.json north_star): pyramid levels, FAST candidates, quadtree survivors, output
+order and every integer keypoint field bit-exact; orientation within 1e-4 rad; descriptor bit
+mismatch rate < 0.1 % (expected ~0: only cosf/sinf ulps at cvRound boundaries can differ).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ANGLE_TOL_DEG = 1e-4 * 180.0 / np.pi  # 1e-4 rad, stated in north_star
+
+CASES = [
+    # kind, h, w, nfeatures, lapping  (BASELINE.json configs C1..C5 + the mono-init extractor)
+    ("noise", 480, 752, 1000, (0, 1000)),
+    ("noise", 480, 752, 1200, (0, 0)),
+    ("noise", 512, 512, 1500, (0, 511)),
+    ("noise", 720, 1280, 2000, (0, 1000)),
+    ("noise", 1080, 1920, 4000, (0, 0)),
+    ("noise", 480, 752, 5000, (0, 1000)),
+    ("checker", 480, 752, 1000, (0, 1000)),
+    ("checker", 720, 1280, 2000, (0, 1000)),
+    ("lowtex", 480, 752, 1000, (0, 0)),
+    ("black", 480, 752, 1000, (0, 0)),
+    ("noise", 333, 517, 700, (100, 300)),   # odd sizes: unaligned rows, ragged cells
+    ("checker", 240, 1000, 500, (0, 0)),    # wide: nIni = 4
+    ("noise", 600, 400, 800, (0, 0)),       # portrait: nIni = 1
+]
+
+
+def _oracle(oracle_libs, nf):
+    kind = "ref" if oracle_libs.have_ref() else "port"
+    return oracle_libs.OracleExtractor(nf, 1.2, 8, 20, 7, kind=kind)
+
+
+def _compare_final(ref, got, tag):
+    mono_r, k_r, d_r = ref
+    mono_g, k_g, d_g = got
+    assert mono_g == mono_r, tag
+    assert len(k_g) == len(k_r), tag
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(k_g[f], k_r[f]), (tag, f)
+    if len(k_r):
+        da = np.abs(k_g["angle"].astype(np.float64) - k_r["angle"].astype(np.float64))
+        da = np.minimum(da, 360.0 - da)
+        assert da.max() <= ANGLE_TOL_DEG, (tag, da.max())
+        bits = np.unpackbits(d_g ^ d_r).sum()
+        rate = bits / (d_r.size * 8)
+        assert rate < 1e-3, (tag, rate)
+        return int((da > 0).sum()), int(bits), d_r.size * 8
+    return 0, 0, 0
+
+
+@pytest.mark.parametrize("kind,h,w,nf,lap", CASES)
+def test_extractor_parity_stagewise(oracle_libs, synth, kind, h, w, nf, lap):
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    ora = _oracle(oracle_libs, nf)
+    ex = ORBextractor(nf, 1.2, 8, 20, 7, max_size=(h, w), max_batch=1)
+    try:
+        for seed in (0, 1):
+            img = synth.frame(kind, h, w, seed)
+            tag = (kind, h, w, nf, seed)
+            ref = ora(img, lap)
+            got = ex(img, lap)
+            cands, survs = ora.stages(img)
+            for l in range(8):
+                assert np.array_equal(ex.pyramid_level(l, (h, w)), ora.level(l)), (tag, "pyramid", l)
+                assert np.array_equal(ex.debug_candidates(l), cands[l]), (tag, "fast", l)
+                s = survs[l]
+                exp = np.stack([s["x"].astype(np.int32) - 16, s["y"].astype(np.int32) - 16,
+                                s["response"].astype(np.int32)], axis=1).reshape(-1, 3)
+                assert np.array_equal(ex.debug_survivors(l), exp), (tag, "octree", l)
+            _compare_final(ref, got, tag)
+            assert np.array_equal(ex.pyramid_level(3, (h, w), pad=19), ora.level(3, 19)), (tag, "padded")
+    finally:
+        ex.close()
+
+
+def test_tables_match_reference(oracle_libs):
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    for nf, sf, nl in ((1000, 1.2, 8), (1200, 1.2, 8), (5000, 1.2, 8), (2000, 1.5, 5), (300, 1.1, 12)):
+        kind = "ref" if oracle_libs.have_ref() else "port"
+        ora = oracle_libs.OracleExtractor(nf, sf, nl, 20, 7, kind=kind)
+        ex = ORBextractor(nf, sf, nl, 20, 7, max_size=(480, 752))
+        t = ora.tables()
+        assert np.array_equal(ex.GetScaleFactors(), t["scale"])
+        assert np.array_equal(ex.GetInverseScaleFactors(), t["inv_scale"])
+        assert np.array_equal(ex.GetScaleSigmaSquares(), t["sigma2"])
+        assert np.array_equal(ex.GetInverseScaleSigmaSquares(), t["inv_sigma2"])
+        assert np.array_equal(ex.features_per_level(), t["n_per_level"])
+        assert ex.GetLevels() == nl
+        ex.close()
+
+
+def test_batch_matches_single_and_oracle(oracle_libs, synth):
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    ora = _oracle(oracle_libs, 1000)
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_size=(480, 752), max_batch=12)
+    kinds = ["noise", "checker", "lowtex", "black"]
+    imgs = [synth.frame(kinds[i % 4], 480, 752, i) for i in range(12)]
+    laps = [(0, 1000) if i % 2 else (0, 0) for i in range(12)]
+    res = ex.extract_batch(imgs, laps)
+    stats = np.zeros(3, np.int64)
+    for i in range(12):
+        stats += np.array(_compare_final(ora(imgs[i], laps[i]), res[i], ("batch", i)))
+    # the mismatch rates are part of the contract: report them
+    print(f"angles differing in the last bits: {stats[0]}, descriptor bits differing: {stats[1]} of {stats[2]}")
+    ex.close()
+
+
+def test_empty_and_bad_inputs():
+    from orb_slam3_mac_b200 import _lib
+    from orb_slam3_mac_b200.extractor import ORBextractor, OrbxError
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_size=(480, 752))
+    mono, k, d = ex(None)
+    assert mono == -1 and len(k) == 0 and d.shape == (0, 32)
+    with pytest.raises(OrbxError) as e:
+        ex(np.zeros((480, 752), np.float32))
+    assert e.value.code == _lib.ORBX_E_BAD_TYPE
+    with pytest.raises(OrbxError) as e:
+        ex(np.zeros((1000, 2000), np.uint8))
+    assert e.value.code == _lib.ORBX_E_TOO_LARGE
+    with pytest.raises(OrbxError) as e:
+        ex(np.random.default_rng(0).integers(0, 255, (480, 752), dtype=np.uint8), cap=10)
+    assert e.value.code == _lib.ORBX_E_CAPACITY
+    with pytest.raises(OrbxError) as e:
+        ex(np.zeros((480, 100), np.uint8))  # 100/1.2^7 = 28 px: no FAST cell on the top levels
+    assert e.value.code == _lib.ORBX_E_UNSUPPORTED
+    ex.close()
+
+
+def test_strided_input_and_shape_switch(oracle_libs, synth):
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    ora = _oracle(oracle_libs, 1000)
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_size=(720, 1280))
+    big = synth.textured_noise(720, 1280, 5)
+    view = big[100:580, 200:952]  # 480x752 view with stride 1280
+    _compare_final(ora(np.ascontiguousarray(view), (0, 0)), ex(view, (0, 0)), "strided")
+    _compare_final(ora(big, (0, 1000)), ex(big, (0, 1000)), "switch-up")
+    small = synth.checkerboard(512, 512, 2)
+    _compare_final(ora(small, (0, 511)), ex(small, (0, 511)), "switch-down")
+    ex.close()
+
+
+def test_two_handles_concurrently(oracle_libs, synth):
+    """Left/right extractors run on two threads in the reference (src/Frame.cc:109-112)."""
+    import threading
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    left, right = synth.stereo_pair(480, 752, 3)
+    exs = [ORBextractor(1200, 1.2, 8, 20, 7, max_size=(480, 752)) for _ in range(2)]
+    out = [None, None]
+
+    def run(i, img):
+        for _ in range(5):
+            out[i] = exs[i](img, (0, 0))
+
+    ts = [threading.Thread(target=run, args=(i, im)) for i, im in enumerate((left, right))]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    ora = _oracle(oracle_libs, 1200)
+    _compare_final(ora(left, (0, 0)), out[0], "left")
+    _compare_final(ora(right, (0, 0)), out[1], "right")
+    [e.close() for e in exs]
