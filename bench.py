@@ -1,0 +1,423 @@
+#!/usr/bin/env python
+"""bench.py -- ORB frames/s on B200 (BASELINE.json metric), one JSON line on stdout.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config C1..C5]
+
+A "step" is one pass of the hot path (pyramid -> FAST -> quadtree -> orientation -> blur+BRIEF)
+over one batch of synthetic frames of the named configuration (default C1: 752x480, 1000
+features, 8 levels -- the configuration the metric is quoted on).
+
+  value      frames/s with the frames already resident in HBM (CUDA events on the launching
+             stream, max over ranks)
+  e2e        frames/s through the reference-facing C ABI with pinned HOST buffers: H2D of the
+             frames and D2H of keypoints+descriptors inside the timed region (pipelined slots)
+  roofline   dominant kernel: algorithmic bytes / measured launch time vs MEASURED_PEAKS.json
+  cpu_baseline  the reference's own ORBextractor.cc (oracle/_ref) on the box's host cores
+
+N>1 (torchrun): frames are sharded over ranks as independent streams (weak scaling); NCCL is used
+only to gather the result slabs (north_star).  --impl reference times the CPU reference only.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "ORB frames/s (752x480, 1k kp, 8 lvl)"
+UNIT = "frames/s"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+def make_frames(cfg: str, count: int, distinct: int):
+    """`count` frames of config `cfg`; `distinct` of them are generated (seeds 0..), the rest are
+    those re-used with a horizontal roll so that no two frames are identical."""
+    import orb_slam3_mac_b200 as pkg
+    h, w = pkg.synth.SHAPES[cfg]
+    base = [pkg.synth.textured_noise(h, w, s) if s % 4 else pkg.synth.checkerboard(h, w, s)
+            for s in range(distinct)]
+    out = np.empty((count, h, w), np.uint8)
+    for i in range(count):
+        b = base[i % distinct]
+        k = i // distinct
+        out[i] = b if k == 0 else np.roll(b, 7 * k, axis=1)
+    return out
+
+
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception as e:  # nvidia-smi missing
+            log("clock sampling unavailable:", e)
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+class CpuReference:
+    """The reference's CPU extractor on the host cores: `threads` host threads, one extractor
+    instance each (how the reference itself runs two extractors: independent ORBextractor objects
+    on std::threads, src/Frame.cc:109-112).  ctypes releases the GIL during the calls."""
+
+    def __init__(self, cfg: str, threads: int):
+        from oracle import pyoracle as po
+        import orb_slam3_mac_b200 as pkg
+        self.kind = "ref" if po.have_ref() else "port"
+        if self.kind == "port" and not po.have_port():
+            po.build("port")
+        nf = pkg.synth.NFEATURES[cfg]
+        self.threads = threads
+        self.exs = [po.OracleExtractor(nf, 1.2, 8, 20, 7, kind=self.kind) for _ in range(threads)]
+
+    def run(self, frames: np.ndarray, nframes_total: int) -> float:
+        """Extracts nframes_total frames; returns the elapsed seconds of the threaded region."""
+        per = [list(range(t, nframes_total, self.threads)) for t in range(self.threads)]
+
+        def work(t):
+            ex = self.exs[t]
+            for i in per[t]:
+                ex(frames[i % len(frames)], (0, 1000))
+
+        ts = [threading.Thread(target=work, args=(t,)) for t in range(self.threads)]
+        t0 = time.perf_counter()
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        return time.perf_counter() - t0
+
+    def describe(self, sample: str):
+        return {"cores": self.threads, "kind": "reference" if self.kind == "ref" else "port",
+                "sample": sample + "; reference src/ORBextractor.cc compiled verbatim (-O3 -march=x86-64-v3), "
+                          "its OpenCV primitives restated in oracle/cvprims.h (scalar FAST/resize/blur)"}
+
+
+def workload_name(cfg: str, h: int, w: int) -> str:
+    import orb_slam3_mac_b200 as pkg
+    return (f"{cfg}: {w}x{h} u8 mono, nFeatures={pkg.synth.NFEATURES[cfg]}, 8 levels, scale 1.2, "
+            f"iniThFAST 20 / minThFAST 7, vLappingArea {{0,1000}}")
+
+
+def run_reference_arm(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cfg = args.config
+    threads = os.cpu_count() or 1
+    frames = make_frames(cfg, 32, 8)
+    h, w = frames.shape[1:]
+    per_step = threads * 8
+    ref = CpuReference(cfg, threads)
+    for _ in range(args.warmup):
+        ref.run(frames, threads * 2)
+    dt = sum(ref.run(frames, per_step) for _ in range(args.steps))
+    fps = args.steps * per_step / dt
+    cb = ref.describe(f"{per_step} frames per step")
+    cb.update({"value": fps, "unit": UNIT})
+    line = {
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": workload_name(cfg, h, w), "frames_per_step": per_step},
+        "cpu_baseline": cb,
+        "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+class _DevArray:
+    """Zero-copy view of a device pointer owned by liborbx_b200 for torch.as_tensor."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                         "version": 2}
+
+
+def algorithmic_bytes(level_sizes, n_kp: float, n_cand: float, n_cells: int):
+    """Per-frame algorithmic bytes per kernel (DESIGN.md 'Roofline')."""
+    px = [w * h for w, h in level_sizes]
+    P = sum(px)
+    return {
+        "pyramid": (P - px[-1]) + (P - px[0]),        # read L0..L6 once, write L1..L7 once
+        "fast": P + 4 * n_cand + 4 * n_cells,         # every level read once; 4 B per candidate/cell
+        "octree": 8 * n_cand + 4 * n_kp,              # latency-bound; reported for completeness
+        "assemble": 12 * n_kp,
+        "describe": P + 48 * n_kp,                    # every level read once + 32 B desc + 16 B kp record
+    }
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import orb_slam3_mac_b200 as pkg
+    from orb_slam3_mac_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    cfg = args.config
+    h, w = pkg.synth.SHAPES[cfg]
+    nf = pkg.synth.NFEATURES[cfg]
+    B = args.batch or max(16, int(384 * (752 * 480) / (w * h)))
+    n_slots = 3
+    lib = _lib.load()
+    conf = _lib.OrbxConfig(nf, 1.2, 8, 20, 7, w, h, B, n_slots, local, 1)  # flags: stage timing
+    hd = C.c_void_p()
+    _lib.check(lib.orbx_create(C.byref(conf), C.byref(hd)))
+    cap = lib.orbx_max_keypoints(hd)
+
+    # ---- inputs: distinct frames per rank, pinned on the host and resident on the device ----------
+    frames = make_frames(cfg, B, min(B, 24))
+    if rank:
+        frames = np.roll(frames, 13 * rank, axis=2)
+    fbytes = B * h * w
+    h_in = lib.orbx_host_alloc(fbytes)
+    C.memmove(h_in, frames.ctypes.data, fbytes)
+    d_in = torch.from_numpy(frames).cuda()
+    lap = np.tile(np.array([0, 1000], np.int32), (B, 1))
+    ptrs = (C.c_void_p * B)(*[h_in + i * h * w for i in range(B)])
+
+    stream_ptr = lib.orbx_slot_stream(hd, 0)
+    ext = torch.cuda.ExternalStream(stream_ptr, device=torch.device("cuda", local))
+    d_hdr, d_kps, d_desc = C.c_void_p(), C.c_void_p(), C.c_void_p()
+
+    def step_device():
+        _lib.check(lib.orbx_extract_device(hd, 0, d_in.data_ptr(), B, w, h, w, h * w, lap.ctypes.data,
+                                           C.byref(d_hdr), C.byref(d_kps), C.byref(d_desc)))
+        _lib.check(lib.orbx_wait(hd, 0))
+
+    # result slab views for the NCCL gather (N > 1)
+    step_device()
+    gather = None
+    if world > 1:
+        kp_t = torch.as_tensor(_DevArray(d_kps.value, B * cap * 28), device=f"cuda:{local}")
+        de_t = torch.as_tensor(_DevArray(d_desc.value, B * cap * 32), device=f"cuda:{local}")
+        hd_t = torch.as_tensor(_DevArray(d_hdr.value, B * 16), device=f"cuda:{local}")
+        g_kp = torch.empty(world * kp_t.numel(), dtype=torch.uint8, device=kp_t.device)
+        g_de = torch.empty(world * de_t.numel(), dtype=torch.uint8, device=kp_t.device)
+        g_hd = torch.empty(world * hd_t.numel(), dtype=torch.uint8, device=kp_t.device)
+
+        def gather():
+            with torch.cuda.stream(ext):
+                dist.all_gather_into_tensor(g_hd, hd_t)
+                dist.all_gather_into_tensor(g_kp, kp_t)
+                dist.all_gather_into_tensor(g_de, de_t)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: frames resident in HBM, CUDA events on the launching stream ------------------------
+    for _ in range(args.warmup):
+        step_device()
+        if gather:
+            gather()
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stage = np.zeros(6, np.float64)
+    ms6 = np.zeros(6, np.float32)
+    launches = 0
+    ev0.record(ext)
+    for _ in range(args.steps):
+        step_device()
+        if gather:
+            gather()
+        lib.orbx_last_stage_ms(hd, 0, ms6.ctypes.data, 6)
+        stage += ms6
+        launches += lib.orbx_last_launch_count(hd, 0)
+    ev1.record(ext)
+    barrier()
+    dev_ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    stage /= args.steps
+
+    # keypoint / candidate statistics of the batch (for the algorithmic-byte figures)
+    hdr = torch.as_tensor(_DevArray(d_hdr.value, B * 16), device=f"cuda:{local}").cpu().numpy().view(np.int32).reshape(B, 4)
+    n_kp = float(hdr[:, 0].mean())
+    n_cand = 0.0
+    n_cells = 0
+    for l in range(8):
+        n_cand += sum(lib.orbx_debug_candidates(hd, 0, f, l, None, 0) for f in range(0, B, max(1, B // 8))) / len(range(0, B, max(1, B // 8)))
+    level_sizes = []
+    for l in range(8):
+        lw, lh = C.c_int(), C.c_int()
+        lib.orbx_level_size(hd, w, h, l, C.byref(lw), C.byref(lh))
+        level_sizes.append((lw.value, lh.value))
+        n_cells += int((lw.value - 32) / 30) * int((lh.value - 32) / 30)
+
+    # ---- e2e: pinned host buffers through the C ABI, pipelined over the slots -----------------------
+    outs = []
+    for sl in range(n_slots):
+        outs.append(dict(kps=lib.orbx_host_alloc(B * cap * 28), desc=lib.orbx_host_alloc(B * cap * 32),
+                         n=np.zeros(B, np.int32), mono=np.zeros(B, np.int32), st=np.zeros(B, np.int32)))
+
+    def submit(sl):
+        o = outs[sl]
+        _lib.check(lib.orbx_submit_batch(hd, sl, ptrs, B, w, h, w, lap.ctypes.data, o["kps"], o["desc"], cap,
+                                         o["n"].ctypes.data, o["mono"].ctypes.data, o["st"].ctypes.data))
+
+    for i in range(max(args.warmup, n_slots)):
+        sl = i % n_slots
+        _lib.check(lib.orbx_wait(hd, sl))
+        submit(sl)
+    for sl in range(n_slots):
+        _lib.check(lib.orbx_wait(hd, sl))
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        sl = i % n_slots
+        _lib.check(lib.orbx_wait(hd, sl))
+        submit(sl)
+    for sl in range(n_slots):
+        _lib.check(lib.orbx_wait(hd, sl))
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    assert int(outs[0]["n"][0]) == int(hdr[0, 0]), "e2e result differs from the device-resident run"
+
+    # ---- max over ranks ------------------------------------------------------------------------------
+    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    total_frames = args.steps * B * world
+
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+        else:
+            peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+        ab = algorithmic_bytes(level_sizes, n_kp, n_cand, n_cells)
+        names = ["pyramid", "fast", "octree", "assemble", "describe"]
+        kernels = {}
+        for k, nm in enumerate(names):
+            gbs = ab[nm] * B / (stage[k] * 1e-3) / 1e9 if stage[k] > 0 else 0.0
+            kernels[nm] = {"ms_per_launch_batch": round(float(stage[k]), 4), "alg_bytes_per_frame": int(ab[nm]),
+                           "achieved_gbs": round(gbs, 1), "frac": round(gbs / peak, 4)}
+        dom = max(names, key=lambda nm: kernels[nm]["ms_per_launch_batch"])
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
+                    "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                    "kernels": kernels, "stage_ms_sum": round(float(stage[:5].sum()), 4),
+                    "step_ms_device": round(dev_ms / args.steps, 4)}
+        line = {
+            "metric": METRIC, "value": total_frames / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic",
+            "config": {"workload": workload_name(cfg, h, w), "frames_per_step_per_gpu": B,
+                       "l2_policy": f"inputs larger than L2: {B} distinct frames = {fbytes / 1e6:.0f} MB of input "
+                                    f"plus {B} pyramids/scratch per step (126 MB L2)",
+                       "parallelism": f"frames sharded over {world} GPU(s), independent streams; NCCL all_gather of result slabs only"
+                       if world > 1 else "1 GPU, batched launches",
+                       "keypoints_per_frame": round(n_kp, 1), "fast_candidates_per_frame": round(n_cand, 1)},
+            "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": fbytes + B * 8,
+                    "d2h_bytes_per_step": B * (16 + cap * 60), "ms_per_step": e2e_ms / args.steps,
+                    "pipeline_slots": n_slots},
+            "gpu_launches": int(launches),
+            "roofline": roofline,
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            ref = CpuReference(cfg, threads)
+            ref.run(frames, threads)
+            nfr = threads * 24
+            dt = ref.run(frames, nfr)
+            cb = ref.describe(f"{nfr} frames of the same workload over {threads} host threads, one extractor "
+                              f"instance per thread")
+            cb.update({"value": nfr / dt, "unit": UNIT})
+            one = CpuReference(cfg, 1)
+            one.run(frames, 2)
+            cb["single_thread_value"] = 16 / one.run(frames, 16)
+            line["cpu_baseline"] = cb
+        print(json.dumps(line), flush=True)
+
+    for o in outs:
+        lib.orbx_host_free(o["kps"])
+        lib.orbx_host_free(o["desc"])
+    lib.orbx_host_free(h_in)
+    lib.orbx_destroy(hd)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C1", choices=["C1", "C2", "C3", "C4", "C5"])
+    ap.add_argument("--batch", type=int, default=0, help="frames per step per GPU (default: by config)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

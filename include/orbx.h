@@ -73,6 +73,7 @@ typedef struct orbx_config {
 
 #define ORBX_MAX_LEVELS 16
 #define ORBX_FLAG_NONE 0u
+#define ORBX_FLAG_STAGE_TIMING 1u /* record CUDA events at the stage boundaries (bench.py) */
 
 typedef struct orbx_handle orbx_handle;
 
@@ -154,6 +155,11 @@ int orbx_debug_candidates(orbx_handle* h, int slot, int frame, int level, int32_
 /* Quadtree survivors of one level in DistributeOctTree's output order (ORBextractor.cc:738-758):
  * int32 triplets {x, y, response}, same coordinate convention.  Returns the count (or <0). */
 int orbx_debug_survivors(orbx_handle* h, int slot, int frame, int level, int32_t* xyr, int cap);
+
+/* With ORBX_FLAG_STAGE_TIMING: device milliseconds of the last run on `slot`, measured with CUDA
+ * events on the slot's stream: ms[0..4] = pyramid, FAST, quadtree, assemble, describe; ms[5] =
+ * all kernels.  Returns the number of values written. */
+int orbx_last_stage_ms(orbx_handle* h, int slot, float* ms, int n);
 
 /* How many kernels the last submit on `slot` launched (bench.py's gpu_launches). */
 int orbx_last_launch_count(const orbx_handle* h, int slot);

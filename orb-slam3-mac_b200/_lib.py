@@ -65,6 +65,7 @@ ORBX_SYMBOLS = {
     "orbx_debug_candidates": (_i, [_vp, _i, _i, _i, _vp, _i]),
     "orbx_debug_survivors": (_i, [_vp, _i, _i, _i, _vp, _i]),
     "orbx_last_launch_count": (_i, [_vp, _i]),
+    "orbx_last_stage_ms": (_i, [_vp, _i, _vp, _i]),
 }
 
 

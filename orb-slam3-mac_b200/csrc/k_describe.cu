@@ -234,13 +234,19 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
     }
 }
 
-cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr, const uint32_t* surv,
-                                 const uint32_t* survcnt, const int* lap, uint32_t* dest,
-                                 int32_t* header, orbx_keypoint* kps, uint8_t* desc, int nframes,
+cudaError_t orbx_launch_assemble(const OrbxPlan& P, const uint32_t* surv, const uint32_t* survcnt,
+                                 const int* lap, uint32_t* dest, int32_t* header, int nframes,
                                  cudaStream_t st, int* launches) {
     const size_t sm_a = (size_t)(P.surv_total + 2 + 64) * 4;
     k_assemble<<<nframes, 256, sm_a, st>>>(P, surv, survcnt, lap, dest, header);
     ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
+                                 const uint32_t* surv, const uint32_t* survcnt, const uint32_t* dest,
+                                 orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
+                                 int* launches) {
     dim3 grid((P.surv_total + DESC_WARPS - 1) / DESC_WARPS, nframes);
     k_describe<<<grid, DESC_WARPS * 32, 0, st>>>(P, src, pyr, surv, survcnt, dest, kps, desc);
     ++*launches;

@@ -30,10 +30,13 @@ cudaError_t orbx_configure_octree(const OrbxPlan& P);
 cudaError_t orbx_launch_octree(const OrbxPlan& P, const uint32_t* cellcnt, const uint32_t* cellkeys,
                                uint32_t* keysA, uint32_t* keysB, uint32_t* surv, uint32_t* survcnt,
                                int nframes, cudaStream_t st, int* launches);
+cudaError_t orbx_launch_assemble(const OrbxPlan& P, const uint32_t* surv, const uint32_t* survcnt,
+                                 const int* lap, uint32_t* dest, int32_t* header, int nframes,
+                                 cudaStream_t st, int* launches);
 cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
-                                 const uint32_t* surv, const uint32_t* survcnt, const int* lap,
-                                 uint32_t* dest, int32_t* header, orbx_keypoint* kps, uint8_t* desc,
-                                 int nframes, cudaStream_t st, int* launches);
+                                 const uint32_t* surv, const uint32_t* survcnt, const uint32_t* dest,
+                                 orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
+                                 int* launches);
 
 namespace {
 
@@ -58,7 +61,6 @@ int fail(int code, const char* fmt, ...) {
     } while (0)
 
 inline int cv_round(float v) { return (int)lrintf(v); }  // cvRound: round half to even
-inline int cv_round(double v) { return (int)lrint(v); }
 inline int cv_floor(double v) { int i = (int)v; return i - (i > v); }
 inline int round_up(int v, int a) { return (v + a - 1) / a * a; }
 
@@ -84,6 +86,7 @@ struct Slot {
     bool in_flight = false;
     int nframes = 0, cap = 0, launches = 0;
     int *u_n = nullptr, *u_mono = nullptr, *u_status = nullptr;
+    cudaEvent_t ev[6] = {};      // stage boundaries (ORBX_FLAG_STAGE_TIMING)
     OrbxSrc src{};               // level-0 source of the last run (for the debug taps)
     int run_w = 0, run_h = 0;
 };
@@ -245,13 +248,6 @@ int build_plan(const orbx_handle* h, int w, int hgt, OrbxPlan* out, std::vector<
     return ORBX_OK;
 }
 
-size_t plan_table_bytes(const orbx_handle* h, int w, int hgt) {
-    // upper bound: 6 bytes per column and per row per level, 16-byte padded
-    size_t n = 0;
-    for (int l = 1; l < h->cfg.nlevels; ++l) n += (size_t)(w + hgt) * 6 + 64;
-    return n + 256;
-}
-
 void patch_tables(OrbxPlan& P, uint8_t* dev_base) {
     for (int l = 1; l < P.nlevels; ++l) {
         OrbxLevel& L = P.lvl[l];
@@ -359,14 +355,23 @@ namespace {
 // Enqueue the whole device pipeline for `nframes` frames whose level 0 is `src`.
 int enqueue_kernels(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes) {
     const OrbxPlan& P = h->plan;
+    const bool timing = (h->cfg.flags & ORBX_FLAG_STAGE_TIMING) != 0;
     s.launches = 0;
+    if (timing) CUDA_TRY(cudaEventRecord(s.ev[0], s.st));
     orbx_launch_pyramid(P, src, s.pyr, nframes, s.st, &s.launches);
     CUDA_TRY(cudaGetLastError());
+    if (timing) CUDA_TRY(cudaEventRecord(s.ev[1], s.st));
     CUDA_TRY(orbx_launch_fast(P, src, s.pyr, s.cellcnt, s.cellkeys, nframes, s.st, &s.launches));
+    if (timing) CUDA_TRY(cudaEventRecord(s.ev[2], s.st));
     CUDA_TRY(orbx_launch_octree(P, s.cellcnt, s.cellkeys, s.keysA, s.keysB, s.surv, s.survcnt, nframes,
                                 s.st, &s.launches));
-    CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.surv, s.survcnt, s.lap_d, s.dest, s.header, s.kps,
-                                  s.desc, nframes, s.st, &s.launches));
+    if (timing) CUDA_TRY(cudaEventRecord(s.ev[3], s.st));
+    CUDA_TRY(orbx_launch_assemble(P, s.surv, s.survcnt, s.lap_d, s.dest, s.header, nframes, s.st,
+                                  &s.launches));
+    if (timing) CUDA_TRY(cudaEventRecord(s.ev[4], s.st));
+    CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.surv, s.survcnt, s.dest, s.kps, s.desc, nframes,
+                                  s.st, &s.launches));
+    if (timing) CUDA_TRY(cudaEventRecord(s.ev[5], s.st));
     s.src = src;
     s.run_w = P.w;
     s.run_h = P.h;
@@ -429,6 +434,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle** out) {
             r = fail(ORBX_E_CUDA, "stream / pinned allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
             break;
         }
+        for (int k = 0; k < 6; ++k) cudaEventCreate(&s.ev[k]);
     }
     if (r == ORBX_OK) r = set_shape(h, cfg->max_width, cfg->max_height);
     if (r != ORBX_OK) {
@@ -451,6 +457,7 @@ int orbx_destroy(orbx_handle* h) {
         cudaFree(s.dest); cudaFree(s.header); cudaFree(s.kps); cudaFree(s.desc); cudaFree(s.lap_d);
         if (s.h_header) cudaFreeHost(s.h_header);
         if (s.h_lap) cudaFreeHost(s.h_lap);
+        for (int k = 0; k < 6; ++k) if (s.ev[k]) cudaEventDestroy(s.ev[k]);
         if (s.st) cudaStreamDestroy(s.st);
     }
     cudaFree(h->tables);
@@ -491,6 +498,16 @@ void* orbx_slot_stream(orbx_handle* h, int slot) {
 int orbx_last_launch_count(const orbx_handle* h, int slot) {
     if (!h || slot < 0 || slot >= (int)h->slots.size()) return ORBX_E_BAD_ARG;
     return h->slots[slot].launches;
+}
+
+int orbx_last_stage_ms(orbx_handle* h, int slot, float* ms, int n) {
+    if (!h || slot < 0 || slot >= (int)h->slots.size() || !ms) return fail(ORBX_E_BAD_ARG, "bad argument");
+    if (!(h->cfg.flags & ORBX_FLAG_STAGE_TIMING)) return fail(ORBX_E_BAD_ARG, "handle created without ORBX_FLAG_STAGE_TIMING");
+    Slot& s = h->slots[slot];
+    if (s.in_flight) return fail(ORBX_E_BUSY, "slot %d not waited", slot);
+    for (int k = 0; k < 5 && k < n; ++k) CUDA_TRY(cudaEventElapsedTime(&ms[k], s.ev[k], s.ev[k + 1]));
+    if (n > 5) CUDA_TRY(cudaEventElapsedTime(&ms[5], s.ev[0], s.ev[5]));
+    return n < 6 ? n : 6;
 }
 
 int orbx_level_size(const orbx_handle* h, int w, int hgt, int level, int* lw, int* lh) {
