@@ -1,0 +1,147 @@
+/* include/orbm.h -- C ABI of the B200-native descriptor-distance search (liborbx_b200.so).
+ *
+ * Drop-in boundary for the Hamming searches of ORB-SLAM3 (reference: zhoujoey/ORB-SLAM3-Mac; cites
+ * are file:line relative to the reference tree).  Every ORBmatcher::Search* method walks pointer
+ * graphs (Frame&, MapPoint*, KeyFrame*; include/ORBmatcher.h:46-88), so the seam is cut INSIDE the
+ * methods: the caller snapshots the POD the method reads, all 256-bit distances are computed in
+ * one batched CUDA launch, and the method's own order-dependent accept/reject logic is replayed
+ * over those distances in the original order.
+ *
+ *   layer 1 (device primitives)
+ *     orbm_hamming_csr   ORBmatcher::DescriptorDistance          src/ORBmatcher.cc:2353-2369
+ *                        over every (query, candidate) pair of a CSR candidate list
+ *     orbm_knn2          cv::BFMatcher(NORM_HAMMING).knnMatch(k=2) src/Frame.cc:43,1146
+ *     orbm_stereo_rows   Frame::ComputeStereoMatches, Hamming part src/Frame.cc:802-885
+ *   layer 2 (whole searches on POD snapshots; grid + CSR on the host, distances on the GPU)
+ *     orbm_search_by_projection_points   ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&..)
+ *                                        src/ORBmatcher.cc:48-218 (monocular/rectified branch)
+ *     orbm_search_by_projection_frames   ORBmatcher::SearchByProjection(Frame&, const Frame&..)
+ *                                        src/ORBmatcher.cc:1965-2181 (Nleft == -1 branch)
+ *     orbm_search_for_initialization     ORBmatcher::SearchForInitialization src/ORBmatcher.cc:710-825
+ *     candidate generation               Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea
+ *                                        src/Frame.cc:377-408, 716-726, 645-714
+ *
+ * Plain C, POD only.  Contexts are independent and may be used concurrently from different
+ * threads (Tracking, LocalMapping and LoopClosing all construct ORBmatcher objects); one context
+ * is not re-entrant.  No CPU fallback: without a CUDA device orbm_create fails.
+ */
+#ifndef ORBM_H
+#define ORBM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "orbx.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBM_TH_HIGH 100     /* ORBmatcher::TH_HIGH, src/ORBmatcher.cc:40 */
+#define ORBM_TH_LOW 50       /* ORBmatcher::TH_LOW,  :41 */
+#define ORBM_HISTO_LENGTH 30 /* ORBmatcher::HISTO_LENGTH, :42 */
+#define ORBM_GRID_COLS 64    /* FRAME_GRID_COLS, include/Frame.h:39 */
+#define ORBM_GRID_ROWS 48    /* FRAME_GRID_ROWS, include/Frame.h:38 */
+
+typedef struct orbm_context orbm_context;
+
+int orbm_create(int device, orbm_context** out);
+int orbm_destroy(orbm_context* c);
+
+/* ---- layer 1 ---------------------------------------------------------------------------------- */
+/* dist_out[k] = Hamming(q[row(k)], t[cand[k]]) for every k in [0, nnz); row_ptr has nq+1 entries,
+ * row(k) is the r with row_ptr[r] <= k < row_ptr[r+1].  Order of candidates is preserved, which is
+ * what lets the caller replay the reference's first-strictly-smaller-wins loops.  q, t: rows of 32
+ * bytes (cv::Mat N x 32 CV_8U, 4-byte aligned as DescriptorDistance requires). */
+int orbm_hamming_csr(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t, int nt,
+                     const int32_t* row_ptr, const int32_t* cand, int nnz, uint16_t* dist_out);
+
+/* Two nearest train rows per query row, smallest distance first, LOWEST train index first on ties
+ * (verified against cv2 4.13).  idx_out / dist_out: nq x 2; with nt < 2 the missing
+ * entries are idx -1, dist -1 (the reference then fails its size()>=2 test, src/Frame.cc:1153). */
+int orbm_knn2(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx_out,
+              int32_t* dist_out);
+
+/* Rectified stereo (src/Frame.cc:812-885): for each left keypoint the right keypoint with the
+ * smallest distance < TH_HIGH among those whose row band [floor(y-r), ceil(y+r)], r = 2*scale[octave],
+ * contains row (int)yL, whose octave is within +-1 and whose x lies in [xL - max_d, xL - min_d];
+ * ties -> lowest right index.  best_idx[i] = -1 / best_dist[i] = TH_HIGH when there is none. */
+int orbm_stereo_rows(orbm_context* c, const orbx_keypoint* kps_l, const uint8_t* desc_l, int n_l,
+                     const orbx_keypoint* kps_r, const uint8_t* desc_r, int n_r,
+                     const float* scale_factors, int nlevels, float min_d, float max_d,
+                     int32_t* best_idx, int32_t* best_dist);
+
+/* ---- layer 2 ---------------------------------------------------------------------------------- */
+/* The parts of ORB_SLAM3::Frame the searches read (include/Frame.h). */
+typedef struct orbm_frame_view {
+    const orbx_keypoint* keys; /* mvKeysUn (N records) */
+    const uint8_t* desc;       /* mDescriptors, N x 32 */
+    int32_t n;                 /* N */
+    float min_x, min_y, max_x, max_y; /* mnMinX, mnMinY, mnMaxX, mnMaxY */
+    float grid_w_inv, grid_h_inv;     /* mfGridElementWidthInv / HeightInv */
+    const float* scale_factors;       /* mvScaleFactors */
+    int32_t nlevels;
+    const float* u_right;      /* mvuRight (N) or NULL when not stereo */
+} orbm_frame_view;
+
+/* One local map point as SearchByProjection(Frame&, vector<MapPoint*>&) sees it after
+ * Frame::isInFrustum filled the tracking fields (src/Frame.cc:483-572). */
+typedef struct orbm_map_point {
+    float proj_x, proj_y;   /* mTrackProjX, mTrackProjY */
+    float proj_xr;          /* mTrackProjXR */
+    float view_cos;         /* mTrackViewCos */
+    float depth;            /* mTrackDepth */
+    int32_t level;          /* mnTrackScaleLevel */
+    int32_t observations;   /* Observations() */
+    uint8_t in_view;        /* mbTrackInView */
+    uint8_t bad;            /* isBad() */
+    uint8_t _pad[2];
+} orbm_map_point;
+
+/* SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints), src/ORBmatcher.cc:48-147.
+ * mp_desc: M x 32 (MapPoint::GetDescriptor()).  kp_obs (in/out, N ints): Observations() of the map
+ * point currently attached to keypoint i, or -1 if none (F.mvpMapPoints[i] == NULL).
+ * kp_match (out, N ints): index of the map point this call attached to keypoint i, else -1.
+ * Returns nmatches (>= 0) or a negative orbx_status. */
+int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F,
+                                     const orbm_map_point* mps, const uint8_t* mp_desc, int m,
+                                     float th, int far_points, float th_far, float nn_ratio,
+                                     int32_t* kp_obs, int32_t* kp_match);
+
+/* One last-frame observation for SearchByProjection(CurrentFrame, LastFrame, th, bMono),
+ * src/ORBmatcher.cc:1965-2076: the caller projects the map point with the current pose
+ * (camera model stays on the host) and passes the result. */
+typedef struct orbm_last_obs {
+    float u, v;           /* CurrentFrame.mpCamera->project(x3Dc) */
+    float inv_z;          /* 1 / x3Dc.z */
+    float angle;          /* kpLF.angle */
+    int32_t octave;       /* nLastOctave */
+    int32_t observations; /* pMP->Observations() */
+    uint8_t valid;        /* LastFrame.mvpMapPoints[i] != NULL && !mvbOutlier[i] */
+    uint8_t _pad[3];
+} orbm_last_obs;
+
+/* forward / backward: bForward / bBackward (:1985-1986); bf = CurrentFrame.mbf.
+ * kp_obs / kp_match as above (kp_match[i] = index into `last`).  Applies the rotation-histogram
+ * consistency check when check_orientation != 0 (:2158-2178).  Returns nmatches. */
+int orbm_search_by_projection_frames(orbm_context* c, const orbm_frame_view* cur,
+                                     const orbm_last_obs* last, const uint8_t* last_desc, int n_last,
+                                     float th, int forward, int backward, float bf,
+                                     int check_orientation, int32_t* kp_obs, int32_t* kp_match);
+
+/* SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), src/ORBmatcher.cc:710-825.
+ * prev_matched: F1.n (x, y) pairs, in/out.  matches12: F1.n ints, out.  Returns nmatches. */
+int orbm_search_for_initialization(orbm_context* c, const orbm_frame_view* F1,
+                                   const orbm_frame_view* F2, float* prev_matched, int32_t* matches12,
+                                   int window_size, float nn_ratio, int check_orientation);
+
+/* Frame::GetFeaturesInArea (src/Frame.cc:645-714) on a frame view: writes up to cap indices in the
+ * reference's order (grid columns outer, rows inner, insertion order inside a cell); returns the
+ * count.  Exposed for parity tests of the candidate order. */
+int orbm_features_in_area(const orbm_frame_view* F, float x, float y, float r, int min_level,
+                          int max_level, int32_t* out, int cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBM_H */

@@ -1,4 +1,430 @@
 // oracle/match_oracle.cpp -- TEST INFRASTRUCTURE ONLY (CPU oracle for the ORBmatcher path).
-// Filled in below; see the per-function reference cites.
+//
+// PARITY UNPINNED BY THE REFERENCE BUILD: src/ORBmatcher.cc cannot be compiled here (it needs
+// Frame.h/KeyFrame.h -> Eigen, DBoW2, g2o, none installed), and the reference holds no tests or
+// golden vectors.  This file restates the reference loops line by line on POD snapshots of the
+// same data; what CAN be pinned is pinned in tests/: the distance against numpy popcount, the
+// 2-NN search against cv2.BFMatcher(NORM_HAMMING).knnMatch (the un-vendored OpenCV call at
+// src/Frame.cc:1146), the candidate order against a brute-force scan.
+//
+// Every distance here is computed inline with the reference's SWAR popcount, sequentially, per
+// candidate -- the opposite decomposition of the product (which batches all distances on the GPU
+// first and replays), so agreement is meaningful.
+//
+// Reference functions followed (file:line relative to /root/reference):
+//   descriptor_distance   ORBmatcher::DescriptorDistance          src/ORBmatcher.cc:2353-2369
+//   three_maxima          ORBmatcher::ComputeThreeMaxima          src/ORBmatcher.cc:2307-2348
+//   Frame grid            AssignFeaturesToGrid/PosInGrid/GetFeaturesInArea  src/Frame.cc:377-408,716-726,645-714
+//   sbp_points            SearchByProjection(Frame&, vector<MapPoint*>&,..) src/ORBmatcher.cc:48-147
+//   sbp_frames            SearchByProjection(Frame&, const Frame&,..)      src/ORBmatcher.cc:1965-2076,2158-2181
+//   search_init           SearchForInitialization                 src/ORBmatcher.cc:710-825
+//   stereo_rows           Frame::ComputeStereoMatches (Hamming part)      src/Frame.cc:802-885
+//   knn2                  BFMatcher(NORM_HAMMING).knnMatch(k=2)   src/Frame.cc:1146 (OpenCV semantics)
+#include <climits>
+#include <cmath>
 #include <cstdint>
-extern "C" int orbo_match_placeholder(void) { return 0; }
+#include <cstring>
+#include <vector>
+#include <algorithm>
+
+namespace {
+
+const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;
+const int GRID_COLS = 64, GRID_ROWS = 48;
+
+struct Kp {  // cv::KeyPoint layout
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+};
+
+struct FrameView {  // same layout as orbm_frame_view (include/orbm.h)
+    const Kp* keys;
+    const uint8_t* desc;
+    int32_t n;
+    float min_x, min_y, max_x, max_y;
+    float grid_w_inv, grid_h_inv;
+    const float* scale_factors;
+    int32_t nlevels;
+    const float* u_right;
+};
+
+struct MapPointPod {  // orbm_map_point
+    float proj_x, proj_y, proj_xr, view_cos, depth;
+    int32_t level, observations;
+    uint8_t in_view, bad, pad[2];
+};
+
+struct LastObs {  // orbm_last_obs
+    float u, v, inv_z, angle;
+    int32_t octave, observations;
+    uint8_t valid, pad[3];
+};
+
+int descriptor_distance(const uint8_t* a, const uint8_t* b) {
+    const int32_t* pa = (const int32_t*)a;
+    const int32_t* pb = (const int32_t*)b;
+    int dist = 0;
+    for (int i = 0; i < 8; i++, pa++, pb++) {
+        unsigned int v = *pa ^ *pb;
+        v = v - ((v >> 1) & 0x55555555);
+        v = (v & 0x33333333) + ((v >> 2) & 0x33333333);
+        dist += (((v + (v >> 4)) & 0xF0F0F0F) * 0x1010101) >> 24;
+    }
+    return dist;
+}
+
+void three_maxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3) {
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; i++) {
+        const int s = histo[i].size();
+        if (s > max1) {
+            max3 = max2; max2 = max1; max1 = s;
+            ind3 = ind2; ind2 = ind1; ind1 = i;
+        } else if (s > max2) {
+            max3 = max2; max2 = s;
+            ind3 = ind2; ind2 = i;
+        } else if (s > max3) {
+            max3 = s; ind3 = i;
+        }
+    }
+    if (max2 < 0.1f * (float)max1) {
+        ind2 = -1; ind3 = -1;
+    } else if (max3 < 0.1f * (float)max1) {
+        ind3 = -1;
+    }
+}
+
+struct GridO {
+    std::vector<size_t> cell[GRID_COLS][GRID_ROWS];
+    explicit GridO(const FrameView& F) {
+        for (int i = 0; i < F.n; i++) {
+            const Kp& kp = F.keys[i];
+            int posX = round((kp.x - F.min_x) * F.grid_w_inv);
+            int posY = round((kp.y - F.min_y) * F.grid_h_inv);
+            if (posX < 0 || posX >= GRID_COLS || posY < 0 || posY >= GRID_ROWS) continue;
+            cell[posX][posY].push_back(i);
+        }
+    }
+};
+
+std::vector<size_t> get_features_in_area(const FrameView& F, const GridO& G, const float& x, const float& y,
+                                         const float& r, const int minLevel = -1, const int maxLevel = -1) {
+    std::vector<size_t> vIndices;
+    float factorX = r, factorY = r;
+    const int nMinCellX = std::max(0, (int)floor((x - F.min_x - factorX) * F.grid_w_inv));
+    if (nMinCellX >= GRID_COLS) return vIndices;
+    const int nMaxCellX = std::min((int)GRID_COLS - 1, (int)ceil((x - F.min_x + factorX) * F.grid_w_inv));
+    if (nMaxCellX < 0) return vIndices;
+    const int nMinCellY = std::max(0, (int)floor((y - F.min_y - factorY) * F.grid_h_inv));
+    if (nMinCellY >= GRID_ROWS) return vIndices;
+    const int nMaxCellY = std::min((int)GRID_ROWS - 1, (int)ceil((y - F.min_y + factorY) * F.grid_h_inv));
+    if (nMaxCellY < 0) return vIndices;
+    const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+    for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
+        for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+            const std::vector<size_t>& vCell = G.cell[ix][iy];
+            for (size_t j = 0, jend = vCell.size(); j < jend; j++) {
+                const Kp& kpUn = F.keys[vCell[j]];
+                if (bCheckLevels) {
+                    if (kpUn.octave < minLevel) continue;
+                    if (maxLevel >= 0)
+                        if (kpUn.octave > maxLevel) continue;
+                }
+                const float distx = kpUn.x - x;
+                const float disty = kpUn.y - y;
+                if (fabs(distx) < factorX && fabs(disty) < factorY) vIndices.push_back(vCell[j]);
+            }
+        }
+    }
+    return vIndices;
+}
+
+float radius_by_viewing_cos(const float& viewCos) {
+    if (viewCos > 0.998) return 2.5;
+    else return 4.0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbo_descriptor_distance(const uint8_t* a, const uint8_t* b) { return descriptor_distance(a, b); }
+
+int orbo_features_in_area(const FrameView* F, float x, float y, float r, int minLevel, int maxLevel,
+                          int32_t* out, int cap) {
+    GridO G(*F);
+    std::vector<size_t> v = get_features_in_area(*F, G, x, y, r, minLevel, maxLevel);
+    for (size_t i = 0; i < v.size() && (int)i < cap; ++i) out[i] = (int32_t)v[i];
+    return (int)v.size();
+}
+
+// src/ORBmatcher.cc:48-147 (F.Nleft == -1)
+int orbo_search_by_projection_points(const FrameView* Fp, const MapPointPod* mps, const uint8_t* mp_desc, int m,
+                                     float th, int bFarPoints, float thFarPoints, float mfNNratio,
+                                     int32_t* kp_obs, int32_t* kp_match) {
+    const FrameView& F = *Fp;
+    GridO G(F);
+    for (int i = 0; i < F.n; ++i) kp_match[i] = -1;
+    int nmatches = 0;
+    const bool bFactor = th != 1.0;
+    for (int iMP = 0; iMP < m; iMP++) {
+        const MapPointPod& pMP = mps[iMP];
+        if (!pMP.in_view) continue;
+        if (bFarPoints && pMP.depth > thFarPoints) continue;
+        if (pMP.bad) continue;
+        const int& nPredictedLevel = pMP.level;
+        float r = radius_by_viewing_cos(pMP.view_cos);
+        if (bFactor) r *= th;
+        const std::vector<size_t> vIndices = get_features_in_area(
+            F, G, pMP.proj_x, pMP.proj_y, r * F.scale_factors[nPredictedLevel], nPredictedLevel - 1, nPredictedLevel);
+        if (vIndices.empty()) continue;
+        const uint8_t* MPdescriptor = mp_desc + (size_t)iMP * 32;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (std::vector<size_t>::const_iterator vit = vIndices.begin(), vend = vIndices.end(); vit != vend; vit++) {
+            const size_t idx = *vit;
+            if (kp_obs[idx] > 0) continue;
+            if (F.u_right && F.u_right[idx] > 0) {
+                const float er = fabs(pMP.proj_xr - F.u_right[idx]);
+                if (er > r * F.scale_factors[nPredictedLevel]) continue;
+            }
+            const int dist = descriptor_distance(MPdescriptor, F.desc + idx * 32);
+            if (dist < bestDist) {
+                bestDist2 = bestDist;
+                bestDist = dist;
+                bestLevel2 = bestLevel;
+                bestLevel = F.keys[idx].octave;
+                bestIdx = idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = F.keys[idx].octave;
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2) continue;
+            if (bestLevel != bestLevel2 || bestDist <= mfNNratio * bestDist2) {
+                kp_match[bestIdx] = iMP;
+                kp_obs[bestIdx] = pMP.observations;
+                nmatches++;
+            }
+        }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:1965-2076 + 2158-2181 (CurrentFrame.Nleft == -1)
+int orbo_search_by_projection_frames(const FrameView* Cp, const LastObs* last, const uint8_t* last_desc, int n_last,
+                                     float th, int bForward, int bBackward, float mbf, int mbCheckOrientation,
+                                     int32_t* kp_obs, int32_t* kp_match) {
+    const FrameView& CurrentFrame = *Cp;
+    GridO G(CurrentFrame);
+    for (int i = 0; i < CurrentFrame.n; ++i) kp_match[i] = -1;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) rotHist[i].reserve(500);
+    const float factor = 1.0f / HISTO_LENGTH;
+    for (int i = 0; i < n_last; i++) {
+        const LastObs& o = last[i];
+        if (!o.valid) continue;
+        const float invzc = o.inv_z;
+        if (invzc < 0) continue;
+        if (o.u < CurrentFrame.min_x || o.u > CurrentFrame.max_x) continue;
+        if (o.v < CurrentFrame.min_y || o.v > CurrentFrame.max_y) continue;
+        int nLastOctave = o.octave;
+        float radius = th * CurrentFrame.scale_factors[nLastOctave];
+        std::vector<size_t> vIndices2;
+        if (bForward) vIndices2 = get_features_in_area(CurrentFrame, G, o.u, o.v, radius, nLastOctave);
+        else if (bBackward) vIndices2 = get_features_in_area(CurrentFrame, G, o.u, o.v, radius, 0, nLastOctave);
+        else vIndices2 = get_features_in_area(CurrentFrame, G, o.u, o.v, radius, nLastOctave - 1, nLastOctave + 1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* dMP = last_desc + (size_t)i * 32;
+        int bestDist = 256;
+        int bestIdx2 = -1;
+        for (std::vector<size_t>::const_iterator vit = vIndices2.begin(), vend = vIndices2.end(); vit != vend; vit++) {
+            const size_t i2 = *vit;
+            if (kp_obs[i2] > 0) continue;
+            if (CurrentFrame.u_right && CurrentFrame.u_right[i2] > 0) {
+                const float ur = o.u - mbf * invzc;
+                const float er = fabs(ur - CurrentFrame.u_right[i2]);
+                if (er > radius) continue;
+            }
+            const int dist = descriptor_distance(dMP, CurrentFrame.desc + i2 * 32);
+            if (dist < bestDist) {
+                bestDist = dist;
+                bestIdx2 = i2;
+            }
+        }
+        if (bestDist <= TH_HIGH) {
+            kp_match[bestIdx2] = i;
+            kp_obs[bestIdx2] = o.observations;
+            nmatches++;
+            if (mbCheckOrientation) {
+                float rot = o.angle - CurrentFrame.keys[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i != ind1 && i != ind2 && i != ind3) {
+                for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                    kp_match[rotHist[i][j]] = -1;
+                    kp_obs[rotHist[i][j]] = -1;
+                    nmatches--;
+                }
+            }
+        }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:710-825
+int orbo_search_for_initialization(const FrameView* F1p, const FrameView* F2p, float* vbPrevMatched,
+                                   int32_t* vnMatches12, int windowSize, float mfNNratio, int mbCheckOrientation) {
+    const FrameView &F1 = *F1p, &F2 = *F2p;
+    GridO G2(F2);
+    int nmatches = 0;
+    for (int i = 0; i < F1.n; ++i) vnMatches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) rotHist[i].reserve(500);
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<int> vMatchedDistance(F2.n, INT_MAX);
+    std::vector<int> vnMatches21(F2.n, -1);
+    for (size_t i1 = 0, iend1 = F1.n; i1 < iend1; i1++) {
+        Kp kp1 = F1.keys[i1];
+        int level1 = kp1.octave;
+        if (level1 > 0) continue;
+        std::vector<size_t> vIndices2 = get_features_in_area(F2, G2, vbPrevMatched[2 * i1], vbPrevMatched[2 * i1 + 1],
+                                                             windowSize, level1, level1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* d1 = F1.desc + i1 * 32;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (std::vector<size_t>::iterator vit = vIndices2.begin(); vit != vIndices2.end(); vit++) {
+            size_t i2 = *vit;
+            int dist = descriptor_distance(d1, F2.desc + i2 * 32);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) {
+                bestDist2 = bestDist;
+                bestDist = dist;
+                bestIdx2 = i2;
+            } else if (dist < bestDist2) {
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * mfNNratio) {
+                if (vnMatches21[bestIdx2] >= 0) {
+                    vnMatches12[vnMatches21[bestIdx2]] = -1;
+                    nmatches--;
+                }
+                vnMatches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (mbCheckOrientation) {
+                    float rot = F1.keys[i1].angle - F2.keys[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                int idx1 = rotHist[i][j];
+                if (vnMatches12[idx1] >= 0) {
+                    vnMatches12[idx1] = -1;
+                    nmatches--;
+                }
+            }
+        }
+    }
+    for (size_t i1 = 0, iend1 = F1.n; i1 < iend1; i1++)
+        if (vnMatches12[i1] >= 0) {
+            vbPrevMatched[2 * i1] = F2.keys[vnMatches12[i1]].x;
+            vbPrevMatched[2 * i1 + 1] = F2.keys[vnMatches12[i1]].y;
+        }
+    return nmatches;
+}
+
+// src/Frame.cc:802-885: row table + per-left-keypoint Hamming argmin.  n_rows = mvImagePyramid[0].rows.
+int orbo_stereo_rows(const Kp* mvKeys, const uint8_t* mDescriptors, int N, const Kp* mvKeysRight,
+                     const uint8_t* mDescriptorsRight, int Nr, const float* mvScaleFactors, int n_rows,
+                     float minD, float maxD, int32_t* best_idx, int32_t* best_dist) {
+    std::vector<std::vector<size_t> > vRowIndices(n_rows, std::vector<size_t>());
+    for (int iR = 0; iR < Nr; iR++) {
+        const Kp& kp = mvKeysRight[iR];
+        const float& kpY = kp.y;
+        const float r = 2.0f * mvScaleFactors[mvKeysRight[iR].octave];
+        const int maxr = ceil(kpY + r);
+        const int minr = floor(kpY - r);
+        for (int yi = minr; yi <= maxr; yi++)
+            if (yi >= 0 && yi < n_rows) vRowIndices[yi].push_back(iR);  // (the reference indexes unchecked)
+    }
+    for (int iL = 0; iL < N; iL++) {
+        best_idx[iL] = -1;
+        best_dist[iL] = TH_HIGH;
+        const Kp& kpL = mvKeys[iL];
+        const int& levelL = kpL.octave;
+        const float& vL = kpL.y;
+        const float& uL = kpL.x;
+        const std::vector<size_t>& vCandidates = vRowIndices[(size_t)vL];
+        if (vCandidates.empty()) continue;
+        const float minU = uL - maxD;
+        const float maxU = uL - minD;
+        if (maxU < 0) continue;
+        int bestDist = TH_HIGH;
+        size_t bestIdxR = 0;
+        bool found = false;
+        const uint8_t* dL = mDescriptors + (size_t)iL * 32;
+        for (size_t iC = 0; iC < vCandidates.size(); iC++) {
+            const size_t iR = vCandidates[iC];
+            const Kp& kpR = mvKeysRight[iR];
+            if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+            const float& uR = kpR.x;
+            if (uR >= minU && uR <= maxU) {
+                const int dist = descriptor_distance(dL, mDescriptorsRight + iR * 32);
+                if (dist < bestDist) {
+                    bestDist = dist;
+                    bestIdxR = iR;
+                    found = true;
+                }
+            }
+        }
+        if (found) {
+            best_idx[iL] = (int32_t)bestIdxR;
+            best_dist[iL] = bestDist;
+        }
+    }
+    return 0;
+}
+
+// cv::BFMatcher(NORM_HAMMING).knnMatch(k = 2) semantics (verified against cv2 in tests): the two
+// smallest distances, lowest train index first on ties; missing entries are -1.
+int orbo_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx_out, int32_t* dist_out) {
+    for (int i = 0; i < nq; ++i) {
+        int b1 = INT_MAX, b2 = INT_MAX, i1 = -1, i2 = -1;
+        for (int j = 0; j < nt; ++j) {
+            const int d = descriptor_distance(q + (size_t)i * 32, t + (size_t)j * 32);
+            if (d < b1) { b2 = b1; i2 = i1; b1 = d; i1 = j; }
+            else if (d < b2) { b2 = d; i2 = j; }
+        }
+        idx_out[2 * i] = i1;
+        dist_out[2 * i] = i1 < 0 ? -1 : b1;
+        idx_out[2 * i + 1] = i2;
+        dist_out[2 * i + 1] = i2 < 0 ? -1 : b2;
+    }
+    return 0;
+}
+
+}  // extern "C"

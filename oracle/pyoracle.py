@@ -161,3 +161,70 @@ class OracleExtractor:
                 self._f("stage_survivors")(self.h, l, s.ctypes.data, n)
             survs.append(s)
         return cands, survs
+
+
+# ---- matcher oracle (oracle/match_oracle.cpp, in liborb_oracle.so) --------------------------------
+class MatchOracle:
+    """CPU restatement of the reference's Hamming searches on the same POD snapshots the product
+    takes (struct layouts of include/orbm.h).  Frame objects are orb_slam3_mac_b200.matcher.Frame."""
+
+    def __init__(self):
+        if not have_port():
+            build("port")
+        self.lib = C.CDLL(PORT_SO)
+
+    def distance(self, a, b):
+        return self.lib.orbo_descriptor_distance(C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data))
+
+    def features_in_area(self, F, x, y, r, minLevel=-1, maxLevel=-1):
+        out = np.zeros(max(1, F.N), np.int32)
+        v = F.view()
+        n = self.lib.orbo_features_in_area(C.byref(v), C.c_float(x), C.c_float(y), C.c_float(r), minLevel, maxLevel,
+                                           C.c_void_p(out.ctypes.data), len(out))
+        return out[:n].copy()
+
+    def search_by_projection_points(self, F, mps, mp_desc, th, far, th_far, nnratio, kp_obs=None):
+        obs = np.full(F.N, -1, np.int32) if kp_obs is None else np.ascontiguousarray(kp_obs, np.int32).copy()
+        match = np.zeros(F.N, np.int32)
+        v = F.view()
+        n = self.lib.orbo_search_by_projection_points(
+            C.byref(v), C.c_void_p(mps.ctypes.data), C.c_void_p(mp_desc.ctypes.data), len(mps), C.c_float(th),
+            int(far), C.c_float(th_far), C.c_float(nnratio), C.c_void_p(obs.ctypes.data), C.c_void_p(match.ctypes.data))
+        return n, match, obs
+
+    def search_by_projection_frames(self, cur, last_obs, last_desc, th, fwd, bwd, mbf, check_ori, kp_obs=None):
+        obs = np.full(cur.N, -1, np.int32) if kp_obs is None else np.ascontiguousarray(kp_obs, np.int32).copy()
+        match = np.zeros(cur.N, np.int32)
+        v = cur.view()
+        n = self.lib.orbo_search_by_projection_frames(
+            C.byref(v), C.c_void_p(last_obs.ctypes.data), C.c_void_p(last_desc.ctypes.data), len(last_obs),
+            C.c_float(th), int(fwd), int(bwd), C.c_float(mbf), int(check_ori), C.c_void_p(obs.ctypes.data),
+            C.c_void_p(match.ctypes.data))
+        return n, match, obs
+
+    def search_for_initialization(self, F1, F2, prev, window, nnratio, check_ori):
+        prev = np.ascontiguousarray(prev, np.float32).reshape(-1, 2).copy()
+        m12 = np.zeros(F1.N, np.int32)
+        v1, v2 = F1.view(), F2.view()
+        n = self.lib.orbo_search_for_initialization(C.byref(v1), C.byref(v2), C.c_void_p(prev.ctypes.data),
+                                                    C.c_void_p(m12.ctypes.data), int(window), C.c_float(nnratio),
+                                                    int(check_ori))
+        return n, m12, prev
+
+    def stereo_rows(self, left, right, n_rows, min_d, max_d):
+        bi = np.zeros(left.N, np.int32)
+        bd = np.zeros(left.N, np.int32)
+        self.lib.orbo_stereo_rows(C.c_void_p(left.keys.ctypes.data), C.c_void_p(left.desc.ctypes.data), left.N,
+                                  C.c_void_p(right.keys.ctypes.data), C.c_void_p(right.desc.ctypes.data), right.N,
+                                  C.c_void_p(left.scale_factors.ctypes.data), int(n_rows), C.c_float(min_d),
+                                  C.c_float(max_d), C.c_void_p(bi.ctypes.data), C.c_void_p(bd.ctypes.data))
+        return bi, bd
+
+    def knn2(self, q, t):
+        q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
+        t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
+        idx = np.zeros((len(q), 2), np.int32)
+        dist = np.zeros((len(q), 2), np.int32)
+        self.lib.orbo_knn2(C.c_void_p(q.ctypes.data), len(q), C.c_void_p(t.ctypes.data), len(t),
+                           C.c_void_p(idx.ctypes.data), C.c_void_p(dist.ctypes.data))
+        return idx, dist

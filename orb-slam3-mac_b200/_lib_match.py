@@ -1,0 +1,42 @@
+"""ctypes prototypes and POD structs of include/orbm.h."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+
+class FrameView(C.Structure):  # orbm_frame_view
+    _fields_ = [("keys", C.c_void_p), ("desc", C.c_void_p), ("n", C.c_int32),
+                ("min_x", C.c_float), ("min_y", C.c_float), ("max_x", C.c_float), ("max_y", C.c_float),
+                ("grid_w_inv", C.c_float), ("grid_h_inv", C.c_float),
+                ("scale_factors", C.c_void_p), ("nlevels", C.c_int32), ("u_right", C.c_void_p)]
+
+
+MAP_POINT_DTYPE = np.dtype([("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_xr", "<f4"), ("view_cos", "<f4"),
+                            ("depth", "<f4"), ("level", "<i4"), ("observations", "<i4"),
+                            ("in_view", "u1"), ("bad", "u1"), ("_pad", "u1", (2,))])
+LAST_OBS_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("inv_z", "<f4"), ("angle", "<f4"),
+                           ("octave", "<i4"), ("observations", "<i4"), ("valid", "u1"), ("_pad", "u1", (3,))])
+assert MAP_POINT_DTYPE.itemsize == 32 and LAST_OBS_DTYPE.itemsize == 28
+
+_vp, _i, _f = C.c_void_p, C.c_int, C.c_float
+_fv = C.POINTER(FrameView)
+ORBM_SYMBOLS = {
+    "orbm_create": (_i, [_i, C.POINTER(_vp)]),
+    "orbm_destroy": (_i, [_vp]),
+    "orbm_hamming_csr": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _i, _vp]),
+    "orbm_knn2": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp]),
+    "orbm_stereo_rows": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _f, _f, _vp, _vp]),
+    "orbm_search_by_projection_points": (_i, [_vp, _fv, _vp, _vp, _i, _f, _i, _f, _f, _vp, _vp]),
+    "orbm_search_by_projection_frames": (_i, [_vp, _fv, _vp, _vp, _i, _f, _i, _i, _f, _i, _vp, _vp]),
+    "orbm_search_for_initialization": (_i, [_vp, _fv, _fv, _vp, _vp, _i, _f, _i]),
+    "orbm_features_in_area": (_i, [_fv, _f, _f, _f, _i, _i, _vp, _i]),
+}
+
+
+def declare(lib):
+    for name, (res, args) in ORBM_SYMBOLS.items():
+        f = getattr(lib, name)
+        f.restype = res
+        f.argtypes = args

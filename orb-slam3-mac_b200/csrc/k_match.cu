@@ -1,0 +1,128 @@
+// k_match.cu -- M1/M5/M6: batched 256-bit Hamming distances (ORBmatcher::DescriptorDistance,
+// src/ORBmatcher.cc:2353-2369; identical to DBoW2 FORB::distance) as __popc over 8 words.
+// Nothing here is a dense contraction: descriptors are 32-byte rows read as two uint4, the
+// working sets (tens of KB to ~1 MB) live in L1/L2, and the kernels are popcount/LSU bound.
+//
+//   k_hamming_csr   one thread per (query, candidate) pair of a CSR candidate list; the row of a
+//                   pair is found by binary search in row_ptr (L1-resident); distances are written
+//                   in candidate order so the host can replay the reference's order-dependent
+//                   accept loops bit-exactly.
+//   k_knn2          cv::BFMatcher(NORM_HAMMING).knnMatch(k=2): one warp per query, lanes stride
+//                   the train rows keeping their two best (distance, index) pairs; shuffle merge;
+//                   ties resolve to the LOWEST train index (packed key = dist << 20 | idx).
+//   k_stereo_rows   Frame::ComputeStereoMatches' Hamming search (src/Frame.cc:840-885): one warp
+//                   per left keypoint, gates evaluated per right keypoint, warp-min reduction.
+#include "orbx_device.cuh"
+#include "../../include/orbm.h"
+
+__device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4* __restrict__ b) {
+    const uint4 b0 = __ldg(b), b1 = __ldg(b + 1);
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__global__ void __launch_bounds__(256)
+k_hamming_csr(const uint4* __restrict__ q, int nq, const uint4* __restrict__ t,
+              const int32_t* __restrict__ row_ptr, const int32_t* __restrict__ cand, int nnz,
+              uint16_t* __restrict__ dist) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nnz) return;
+    // largest r with row_ptr[r] <= k
+    int lo = 0, hi = nq;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(row_ptr + mid) <= k) lo = mid; else hi = mid;
+    }
+    const uint4 a0 = __ldg(q + 2 * lo), a1 = __ldg(q + 2 * lo + 1);
+    dist[k] = (uint16_t)hamming256(a0, a1, t + 2 * (size_t)__ldg(cand + k));
+}
+
+__global__ void __launch_bounds__(256)
+k_knn2(const uint4* __restrict__ q, int nq, const uint4* __restrict__ t, int nt,
+       int32_t* __restrict__ idx_out, int32_t* __restrict__ dist_out) {
+    const int qi = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
+    if (qi >= nq) return;
+    const int lane = orbx_lane();
+    const uint4 a0 = __ldg(q + 2 * qi), a1 = __ldg(q + 2 * qi + 1);
+    // packed key: distance (<= 256) above a 20-bit train index; smaller key = better, and equal
+    // distances order by index, i.e. lowest train index first
+    uint32_t b1 = 0xffffffffu, b2 = 0xffffffffu;
+    for (int j = lane; j < nt; j += 32) {
+        const uint32_t key = ((uint32_t)hamming256(a0, a1, t + 2 * (size_t)j) << 20) | (uint32_t)j;
+        if (key < b1) { b2 = b1; b1 = key; }
+        else if (key < b2) b2 = key;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        const uint32_t o1 = __shfl_xor_sync(ORBX_FULL, b1, d), o2 = __shfl_xor_sync(ORBX_FULL, b2, d);
+        // merge two sorted pairs, keep the two smallest
+        const uint32_t lo = min(b1, o1), hi = max(b1, o1);
+        b2 = min(hi, min(b2, o2));
+        b1 = lo;
+    }
+    if (lane == 0) {
+        idx_out[2 * qi] = b1 == 0xffffffffu ? -1 : (int32_t)(b1 & 0xfffffu);
+        dist_out[2 * qi] = b1 == 0xffffffffu ? -1 : (int32_t)(b1 >> 20);
+        idx_out[2 * qi + 1] = b2 == 0xffffffffu ? -1 : (int32_t)(b2 & 0xfffffu);
+        dist_out[2 * qi + 1] = b2 == 0xffffffffu ? -1 : (int32_t)(b2 >> 20);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_stereo_rows(const orbx_keypoint* __restrict__ kl, const uint4* __restrict__ dl, int nl,
+              const orbx_keypoint* __restrict__ kr, const uint4* __restrict__ dr, int nr,
+              const float* __restrict__ scale, float min_d, float max_d, int32_t* __restrict__ best_idx,
+              int32_t* __restrict__ best_dist) {
+    const int il = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
+    if (il >= nl) return;
+    const int lane = orbx_lane();
+    const orbx_keypoint L = kl[il];
+    const int row = (int)L.y;                  // vRowIndices[vL], Frame.cc:846
+    const float min_u = L.x - max_d, max_u = L.x - min_d;  // :851-852
+    uint32_t best = ((uint32_t)ORBM_TH_HIGH << 20) | 0xfffffu;  // bestDist = TH_HIGH, no index
+    if (!(max_u < 0)) {                        // :854
+        const uint4 a0 = __ldg(dl + 2 * il), a1 = __ldg(dl + 2 * il + 1);
+        for (int j = lane; j < nr; j += 32) {
+            const orbx_keypoint R = kr[j];
+            const float r = 2.0f * scale[R.octave];   // :823
+            const int maxr = (int)ceilf(R.y + r), minr = (int)floorf(R.y - r);
+            if (row < minr || row > maxr) continue;
+            if (R.octave < L.octave - 1 || R.octave > L.octave + 1) continue;  // :869
+            if (!(R.x >= min_u && R.x <= max_u)) continue;                       // :874
+            const uint32_t key = ((uint32_t)hamming256(a0, a1, dr + 2 * (size_t)j) << 20) | (uint32_t)j;
+            best = min(best, key);
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(ORBX_FULL, best, d));
+    if (lane == 0) {
+        const int dist = (int)(best >> 20);
+        const bool found = dist < ORBM_TH_HIGH;   // strict '<' against bestDist = TH_HIGH, :880
+        best_idx[il] = found ? (int32_t)(best & 0xfffffu) : -1;
+        best_dist[il] = found ? dist : ORBM_TH_HIGH;
+    }
+}
+
+cudaError_t orbm_launch_hamming_csr(const uint8_t* q, int nq, const uint8_t* t, const int32_t* row_ptr,
+                                    const int32_t* cand, int nnz, uint16_t* dist, cudaStream_t st) {
+    if (nnz <= 0) return cudaSuccess;
+    k_hamming_csr<<<(nnz + 255) / 256, 256, 0, st>>>((const uint4*)q, nq, (const uint4*)t, row_ptr, cand, nnz, dist);
+    return cudaGetLastError();
+}
+
+cudaError_t orbm_launch_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
+                             int32_t* dist, cudaStream_t st) {
+    if (nq <= 0) return cudaSuccess;
+    k_knn2<<<(nq + 7) / 8, 256, 0, st>>>((const uint4*)q, nq, (const uint4*)t, nt, idx, dist);
+    return cudaGetLastError();
+}
+
+cudaError_t orbm_launch_stereo_rows(const orbx_keypoint* kl, const uint8_t* dl, int nl,
+                                    const orbx_keypoint* kr, const uint8_t* dr, int nr,
+                                    const float* scale, float min_d, float max_d, int32_t* best_idx,
+                                    int32_t* best_dist, cudaStream_t st) {
+    if (nl <= 0) return cudaSuccess;
+    k_stereo_rows<<<(nl + 7) / 8, 256, 0, st>>>(kl, (const uint4*)dl, nl, kr, (const uint4*)dr, nr, scale, min_d,
+                                                max_d, best_idx, best_dist);
+    return cudaGetLastError();
+}

@@ -1,0 +1,500 @@
+// orbm_api.cu -- host runtime behind include/orbm.h: the Hamming searches of ORBmatcher / Frame.
+//
+// Layer 1 ships descriptors to the device, runs one batched distance kernel (k_match.cu) and
+// returns distances / arg-mins.  Layer 2 restates the reference's search methods on POD
+// snapshots: candidate generation on the 64x48 frame grid (Frame::GetFeaturesInArea order), ONE
+// batched orbm_hamming_csr over every (query, candidate) pair, then the method's own sequential
+// accept/reject loop replayed over the precomputed distances in the original order, so results
+// equal the reference's even where acceptance depends on earlier acceptances
+// (src/ORBmatcher.cc:93-95, 749-750, 2040-2042).  No distance is ever computed on the host.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/orbm.h"
+
+cudaError_t orbm_launch_hamming_csr(const uint8_t* q, int nq, const uint8_t* t, const int32_t* row_ptr,
+                                    const int32_t* cand, int nnz, uint16_t* dist, cudaStream_t st);
+cudaError_t orbm_launch_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
+                             int32_t* dist, cudaStream_t st);
+cudaError_t orbm_launch_stereo_rows(const orbx_keypoint* kl, const uint8_t* dl, int nl,
+                                    const orbx_keypoint* kr, const uint8_t* dr, int nr,
+                                    const float* scale, float min_d, float max_d, int32_t* best_idx,
+                                    int32_t* best_dist, cudaStream_t st);
+
+// error string shared with orbx_api.cu (orbx_last_error_string reads it)
+int orbx_set_error(int code, const char* fmt, ...);
+
+#define M_TRY(expr)                                                                              \
+    do {                                                                                         \
+        cudaError_t _e = (expr);                                                                 \
+        if (_e != cudaSuccess)                                                                   \
+            return orbx_set_error(ORBX_E_CUDA, "%s failed: %s (%s:%d)", #expr,                  \
+                                  cudaGetErrorString(_e), __FILE__, __LINE__);                   \
+    } while (0)
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t n) {
+        if (n <= cap) return ORBX_OK;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        n = std::max(n + n / 4, (size_t)4096);
+        M_TRY(cudaMalloc(&p, n));
+        cap = n;
+        return ORBX_OK;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct orbm_context {
+    int device = 0;
+    cudaStream_t st = nullptr;
+    DevBuf q, t, rowptr, cand, dist, aux1, aux2, kl, kr, sc;
+    std::vector<uint16_t> hdist;     // distances of the last layer-2 search
+    long long last_pairs = 0;        // number of (query, candidate) pairs of the last search
+};
+
+extern "C" {
+
+int orbm_create(int device, orbm_context** out) {
+    if (!out) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return orbx_set_error(ORBX_E_CUDA, "no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return orbx_set_error(ORBX_E_BAD_ARG, "device %d out of range", device);
+    M_TRY(cudaSetDevice(device));
+    orbm_context* c = new orbm_context();
+    c->device = device;
+    if (cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking) != cudaSuccess) {
+        delete c;
+        return orbx_set_error(ORBX_E_CUDA, "cudaStreamCreate failed");
+    }
+    *out = c;
+    return ORBX_OK;
+}
+
+int orbm_destroy(orbm_context* c) {
+    if (!c) return ORBX_OK;
+    cudaSetDevice(c->device);
+    if (c->st) cudaStreamSynchronize(c->st);
+    for (DevBuf* b : {&c->q, &c->t, &c->rowptr, &c->cand, &c->dist, &c->aux1, &c->aux2, &c->kl, &c->kr, &c->sc})
+        b->release();
+    if (c->st) cudaStreamDestroy(c->st);
+    delete c;
+    return ORBX_OK;
+}
+
+int orbm_hamming_csr(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t, int nt,
+                     const int32_t* row_ptr, const int32_t* cand, int nnz, uint16_t* dist_out) {
+    if (!c || nq < 0 || nt < 0 || nnz < 0) return orbx_set_error(ORBX_E_BAD_ARG, "bad argument");
+    if (nnz == 0) return ORBX_OK;
+    if (!q || !t || !row_ptr || !cand || !dist_out) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    M_TRY(cudaSetDevice(c->device));
+    int r;
+    if ((r = c->q.ensure((size_t)nq * 32)) || (r = c->t.ensure((size_t)nt * 32)) ||
+        (r = c->rowptr.ensure((size_t)(nq + 1) * 4)) || (r = c->cand.ensure((size_t)nnz * 4)) ||
+        (r = c->dist.ensure((size_t)nnz * 2)))
+        return r;
+    M_TRY(cudaMemcpyAsync(c->q.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice, c->st));
+    M_TRY(cudaMemcpyAsync(c->t.p, t, (size_t)nt * 32, cudaMemcpyHostToDevice, c->st));
+    M_TRY(cudaMemcpyAsync(c->rowptr.p, row_ptr, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, c->st));
+    M_TRY(cudaMemcpyAsync(c->cand.p, cand, (size_t)nnz * 4, cudaMemcpyHostToDevice, c->st));
+    M_TRY(orbm_launch_hamming_csr((const uint8_t*)c->q.p, nq, (const uint8_t*)c->t.p, (const int32_t*)c->rowptr.p,
+                                  (const int32_t*)c->cand.p, nnz, (uint16_t*)c->dist.p, c->st));
+    M_TRY(cudaMemcpyAsync(dist_out, c->dist.p, (size_t)nnz * 2, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaStreamSynchronize(c->st));
+    return ORBX_OK;
+}
+
+int orbm_knn2(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx_out,
+              int32_t* dist_out) {
+    if (!c || nq < 0 || nt < 0) return orbx_set_error(ORBX_E_BAD_ARG, "bad argument");
+    if (nq == 0) return ORBX_OK;
+    if (!q || (nt && !t) || !idx_out || !dist_out) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    if (nt >= (1 << 20)) return orbx_set_error(ORBX_E_TOO_LARGE, "more than 2^20 train descriptors");
+    M_TRY(cudaSetDevice(c->device));
+    int r;
+    if ((r = c->q.ensure((size_t)nq * 32)) || (r = c->t.ensure((size_t)std::max(nt, 1) * 32)) ||
+        (r = c->aux1.ensure((size_t)nq * 8)) || (r = c->aux2.ensure((size_t)nq * 8)))
+        return r;
+    M_TRY(cudaMemcpyAsync(c->q.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice, c->st));
+    if (nt) M_TRY(cudaMemcpyAsync(c->t.p, t, (size_t)nt * 32, cudaMemcpyHostToDevice, c->st));
+    M_TRY(orbm_launch_knn2((const uint8_t*)c->q.p, nq, (const uint8_t*)c->t.p, nt, (int32_t*)c->aux1.p,
+                           (int32_t*)c->aux2.p, c->st));
+    M_TRY(cudaMemcpyAsync(idx_out, c->aux1.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaMemcpyAsync(dist_out, c->aux2.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaStreamSynchronize(c->st));
+    return ORBX_OK;
+}
+
+int orbm_stereo_rows(orbm_context* c, const orbx_keypoint* kps_l, const uint8_t* desc_l, int n_l,
+                     const orbx_keypoint* kps_r, const uint8_t* desc_r, int n_r,
+                     const float* scale_factors, int nlevels, float min_d, float max_d,
+                     int32_t* best_idx, int32_t* best_dist) {
+    if (!c || n_l < 0 || n_r < 0 || nlevels < 1) return orbx_set_error(ORBX_E_BAD_ARG, "bad argument");
+    if (n_l == 0) return ORBX_OK;
+    if (!kps_l || !desc_l || (n_r && (!kps_r || !desc_r)) || !scale_factors || !best_idx || !best_dist)
+        return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    if (n_r >= (1 << 20)) return orbx_set_error(ORBX_E_TOO_LARGE, "more than 2^20 right keypoints");
+    for (int i = 0; i < n_r; ++i)
+        if (kps_r[i].octave < 0 || kps_r[i].octave >= nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "octave out of range");
+    M_TRY(cudaSetDevice(c->device));
+    int r;
+    if ((r = c->q.ensure((size_t)n_l * 32)) || (r = c->t.ensure((size_t)std::max(n_r, 1) * 32)) ||
+        (r = c->kl.ensure((size_t)n_l * sizeof(orbx_keypoint))) ||
+        (r = c->kr.ensure((size_t)std::max(n_r, 1) * sizeof(orbx_keypoint))) ||
+        (r = c->sc.ensure((size_t)nlevels * 4)) || (r = c->aux1.ensure((size_t)n_l * 4)) ||
+        (r = c->aux2.ensure((size_t)n_l * 4)))
+        return r;
+    M_TRY(cudaMemcpyAsync(c->q.p, desc_l, (size_t)n_l * 32, cudaMemcpyHostToDevice, c->st));
+    M_TRY(cudaMemcpyAsync(c->kl.p, kps_l, (size_t)n_l * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
+    if (n_r) {
+        M_TRY(cudaMemcpyAsync(c->t.p, desc_r, (size_t)n_r * 32, cudaMemcpyHostToDevice, c->st));
+        M_TRY(cudaMemcpyAsync(c->kr.p, kps_r, (size_t)n_r * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
+    }
+    M_TRY(cudaMemcpyAsync(c->sc.p, scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice, c->st));
+    M_TRY(orbm_launch_stereo_rows((const orbx_keypoint*)c->kl.p, (const uint8_t*)c->q.p, n_l,
+                                  (const orbx_keypoint*)c->kr.p, (const uint8_t*)c->t.p, n_r, (const float*)c->sc.p,
+                                  min_d, max_d, (int32_t*)c->aux1.p, (int32_t*)c->aux2.p, c->st));
+    M_TRY(cudaMemcpyAsync(best_idx, c->aux1.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaMemcpyAsync(best_dist, c->aux2.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaStreamSynchronize(c->st));
+    return ORBX_OK;
+}
+
+}  // extern "C"
+
+// =================================================================================================
+// layer 2: the reference's searches on POD snapshots
+// =================================================================================================
+namespace {
+
+// Frame::AssignFeaturesToGrid + PosInGrid (src/Frame.cc:377-408, 716-726): 64 x 48 buckets,
+// keypoint -> cell by ROUND (not floor); out-of-range keypoints are simply not inserted.
+struct Grid {
+    std::vector<int32_t> start;  // [64*48 + 1], cell index = ix * 48 + iy
+    std::vector<int32_t> items;  // keypoint indices, insertion (= index) order inside a cell
+};
+
+void build_grid(const orbm_frame_view* F, Grid& g) {
+    const int nc = ORBM_GRID_COLS * ORBM_GRID_ROWS;
+    std::vector<int32_t> cell(F->n, -1);
+    g.start.assign(nc + 1, 0);
+    for (int i = 0; i < F->n; ++i) {
+        const int px = (int)roundf((F->keys[i].x - F->min_x) * F->grid_w_inv);
+        const int py = (int)roundf((F->keys[i].y - F->min_y) * F->grid_h_inv);
+        if (px < 0 || px >= ORBM_GRID_COLS || py < 0 || py >= ORBM_GRID_ROWS) continue;
+        cell[i] = px * ORBM_GRID_ROWS + py;
+        ++g.start[cell[i] + 1];
+    }
+    for (int c = 0; c < nc; ++c) g.start[c + 1] += g.start[c];
+    g.items.assign(g.start[nc], 0);
+    std::vector<int32_t> fill(g.start.begin(), g.start.end() - 1);
+    for (int i = 0; i < F->n; ++i)
+        if (cell[i] >= 0) g.items[fill[cell[i]]++] = i;
+}
+
+// Frame::GetFeaturesInArea (src/Frame.cc:645-714); appends to `out` in the reference's order.
+void features_in_area(const orbm_frame_view* F, const Grid& g, float x, float y, float r, int minLevel,
+                      int maxLevel, std::vector<int32_t>& out) {
+    const float factorX = r, factorY = r;
+    const int nMinCellX = std::max(0, (int)floorf((x - F->min_x - factorX) * F->grid_w_inv));
+    if (nMinCellX >= ORBM_GRID_COLS) return;
+    const int nMaxCellX = std::min((int)ORBM_GRID_COLS - 1, (int)ceilf((x - F->min_x + factorX) * F->grid_w_inv));
+    if (nMaxCellX < 0) return;
+    const int nMinCellY = std::max(0, (int)floorf((y - F->min_y - factorY) * F->grid_h_inv));
+    if (nMinCellY >= ORBM_GRID_ROWS) return;
+    const int nMaxCellY = std::min((int)ORBM_GRID_ROWS - 1, (int)ceilf((y - F->min_y + factorY) * F->grid_h_inv));
+    if (nMaxCellY < 0) return;
+    const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+    for (int ix = nMinCellX; ix <= nMaxCellX; ++ix) {
+        for (int iy = nMinCellY; iy <= nMaxCellY; ++iy) {
+            const int c = ix * ORBM_GRID_ROWS + iy;
+            for (int k = g.start[c]; k < g.start[c + 1]; ++k) {
+                const int idx = g.items[k];
+                const orbx_keypoint& kp = F->keys[idx];
+                if (bCheckLevels) {
+                    if (kp.octave < minLevel) continue;
+                    if (maxLevel >= 0 && kp.octave > maxLevel) continue;
+                }
+                const float distx = kp.x - x, disty = kp.y - y;
+                if (fabsf(distx) < factorX && fabsf(disty) < factorY) out.push_back(idx);
+            }
+        }
+    }
+}
+
+// ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:2307-2348)
+void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3) {
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; i++) {
+        const int s = (int)histo[i].size();
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+int check_view(const orbm_frame_view* F) {
+    if (!F || F->n < 0 || (F->n && (!F->keys || !F->desc)) || !F->scale_factors || F->nlevels < 1)
+        return orbx_set_error(ORBX_E_BAD_ARG, "bad frame view");
+    return ORBX_OK;
+}
+
+// all (query, candidate) distances of a search, one batched launch
+int batched_distances(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t, int nt,
+                      const std::vector<int32_t>& row_ptr, const std::vector<int32_t>& cand) {
+    c->hdist.resize(cand.size());
+    c->last_pairs = (long long)cand.size();
+    if (cand.empty()) return ORBX_OK;
+    return orbm_hamming_csr(c, q, nq, t, nt, row_ptr.data(), cand.data(), (int)cand.size(), c->hdist.data());
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbm_features_in_area(const orbm_frame_view* F, float x, float y, float r, int min_level, int max_level,
+                          int32_t* out, int cap) {
+    int rc = check_view(F);
+    if (rc) return rc;
+    Grid g;
+    build_grid(F, g);
+    std::vector<int32_t> v;
+    features_in_area(F, g, x, y, r, min_level, max_level, v);
+    for (size_t i = 0; i < v.size() && out && (int)i < cap; ++i) out[i] = v[i];
+    return (int)v.size();
+}
+
+int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, const orbm_map_point* mps,
+                                     const uint8_t* mp_desc, int m, float th, int far_points, float th_far,
+                                     float nn_ratio, int32_t* kp_obs, int32_t* kp_match) {
+    int rc = check_view(F);
+    if (rc) return rc;
+    if (!c || m < 0 || (m && (!mps || !mp_desc)) || !kp_obs || !kp_match) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    Grid g;
+    build_grid(F, g);
+    for (int i = 0; i < F->n; ++i) kp_match[i] = -1;
+    const bool bFactor = th != 1.0;
+    // pass 1: candidate lists (state independent)
+    std::vector<int32_t> row_ptr(m + 1, 0), cand;
+    std::vector<float> rad(m, 0.f);
+    for (int i = 0; i < m; ++i) {
+        const orbm_map_point& p = mps[i];
+        row_ptr[i] = (int32_t)cand.size();
+        if (!p.in_view) continue;
+        if (far_points && p.depth > th_far) continue;
+        if (p.bad) continue;
+        if (p.level < 0 || p.level >= F->nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "map point %d: level out of range", i);
+        float r = ((double)p.view_cos > 0.998) ? 2.5f : 4.0f;  // RadiusByViewingCos, :220-226
+        if (bFactor) r *= th;
+        rad[i] = r * F->scale_factors[p.level];
+        features_in_area(F, g, p.proj_x, p.proj_y, rad[i], p.level - 1, p.level, cand);
+    }
+    row_ptr[m] = (int32_t)cand.size();
+    if ((rc = batched_distances(c, mp_desc, m, F->desc, F->n, row_ptr, cand))) return rc;
+    // pass 2: the reference's accept loop, original order (:54-147)
+    int nmatches = 0;
+    for (int i = 0; i < m; ++i) {
+        if (row_ptr[i + 1] == row_ptr[i]) continue;  // filtered out, or vIndices.empty()
+        const orbm_map_point& p = mps[i];
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int k = row_ptr[i]; k < row_ptr[i + 1]; ++k) {
+            const int idx = cand[k];
+            if (kp_obs[idx] > 0) continue;
+            if (F->u_right && F->u_right[idx] > 0) {
+                const float er = fabsf(p.proj_xr - F->u_right[idx]);
+                if (er > rad[i]) continue;
+            }
+            const int dist = c->hdist[k];
+            if (dist < bestDist) {
+                bestDist2 = bestDist;
+                bestDist = dist;
+                bestLevel2 = bestLevel;
+                bestLevel = F->keys[idx].octave;
+                bestIdx = idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = F->keys[idx].octave;
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= ORBM_TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > nn_ratio * bestDist2) continue;
+            if (bestLevel != bestLevel2 || bestDist <= nn_ratio * bestDist2) {
+                kp_match[bestIdx] = i;
+                kp_obs[bestIdx] = p.observations;
+                nmatches++;
+            }
+        }
+    }
+    return nmatches;
+}
+
+int orbm_search_by_projection_frames(orbm_context* c, const orbm_frame_view* cur, const orbm_last_obs* last,
+                                     const uint8_t* last_desc, int n_last, float th, int forward, int backward,
+                                     float bf, int check_orientation, int32_t* kp_obs, int32_t* kp_match) {
+    int rc = check_view(cur);
+    if (rc) return rc;
+    if (!c || n_last < 0 || (n_last && (!last || !last_desc)) || !kp_obs || !kp_match) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    Grid g;
+    build_grid(cur, g);
+    for (int i = 0; i < cur->n; ++i) kp_match[i] = -1;
+    std::vector<int> rotHist[ORBM_HISTO_LENGTH];
+    const float factor = 1.0f / ORBM_HISTO_LENGTH;
+    std::vector<int32_t> row_ptr(n_last + 1, 0), cand;
+    std::vector<float> rad(n_last, 0.f);
+    for (int i = 0; i < n_last; ++i) {
+        const orbm_last_obs& o = last[i];
+        row_ptr[i] = (int32_t)cand.size();
+        if (!o.valid) continue;
+        if (o.inv_z < 0) continue;
+        if (o.u < cur->min_x || o.u > cur->max_x) continue;
+        if (o.v < cur->min_y || o.v > cur->max_y) continue;
+        if (o.octave < 0 || o.octave >= cur->nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "observation %d: octave out of range", i);
+        rad[i] = th * cur->scale_factors[o.octave];
+        if (forward) features_in_area(cur, g, o.u, o.v, rad[i], o.octave, -1, cand);
+        else if (backward) features_in_area(cur, g, o.u, o.v, rad[i], 0, o.octave, cand);
+        else features_in_area(cur, g, o.u, o.v, rad[i], o.octave - 1, o.octave + 1, cand);
+    }
+    row_ptr[n_last] = (int32_t)cand.size();
+    if ((rc = batched_distances(c, last_desc, n_last, cur->desc, cur->n, row_ptr, cand))) return rc;
+    int nmatches = 0;
+    for (int i = 0; i < n_last; ++i) {
+        if (row_ptr[i + 1] == row_ptr[i]) continue;
+        const orbm_last_obs& o = last[i];
+        int bestDist = 256, bestIdx2 = -1;
+        for (int k = row_ptr[i]; k < row_ptr[i + 1]; ++k) {
+            const int i2 = cand[k];
+            if (kp_obs[i2] > 0) continue;
+            if (cur->u_right && cur->u_right[i2] > 0) {
+                const float ur = o.u - bf * o.inv_z;
+                const float er = fabsf(ur - cur->u_right[i2]);
+                if (er > rad[i]) continue;
+            }
+            const int dist = c->hdist[k];
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= ORBM_TH_HIGH) {
+            kp_match[bestIdx2] = i;
+            kp_obs[bestIdx2] = o.observations;
+            nmatches++;
+            if (check_orientation) {
+                float rot = o.angle - cur->keys[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)roundf(rot * factor);
+                if (bin == ORBM_HISTO_LENGTH) bin = 0;
+                if (bin < 0 || bin >= ORBM_HISTO_LENGTH) return orbx_set_error(ORBX_E_BAD_ARG, "angle outside [0,360)");
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, ORBM_HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+            if (i != ind1 && i != ind2 && i != ind3) {
+                for (size_t j = 0; j < rotHist[i].size(); j++) {
+                    kp_match[rotHist[i][j]] = -1;
+                    kp_obs[rotHist[i][j]] = -1;
+                    nmatches--;
+                }
+            }
+        }
+    }
+    return nmatches;
+}
+
+int orbm_search_for_initialization(orbm_context* c, const orbm_frame_view* F1, const orbm_frame_view* F2,
+                                   float* prev_matched, int32_t* matches12, int window_size, float nn_ratio,
+                                   int check_orientation) {
+    int rc = check_view(F1);
+    if (rc || (rc = check_view(F2))) return rc;
+    if (!c || !prev_matched || !matches12) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    Grid g;
+    build_grid(F2, g);
+    int nmatches = 0;
+    for (int i = 0; i < F1->n; ++i) matches12[i] = -1;
+    std::vector<int> rotHist[ORBM_HISTO_LENGTH];
+    const float factor = 1.0f / ORBM_HISTO_LENGTH;
+    std::vector<int> vMatchedDistance(F2->n, INT_MAX), vnMatches21(F2->n, -1);
+    std::vector<int32_t> row_ptr(F1->n + 1, 0), cand;
+    for (int i1 = 0; i1 < F1->n; ++i1) {
+        row_ptr[i1] = (int32_t)cand.size();
+        const int level1 = F1->keys[i1].octave;
+        if (level1 > 0) continue;
+        features_in_area(F2, g, prev_matched[2 * i1], prev_matched[2 * i1 + 1], (float)window_size, level1, level1, cand);
+    }
+    row_ptr[F1->n] = (int32_t)cand.size();
+    if ((rc = batched_distances(c, F1->desc, F1->n, F2->desc, F2->n, row_ptr, cand))) return rc;
+    for (int i1 = 0; i1 < F1->n; ++i1) {
+        if (row_ptr[i1 + 1] == row_ptr[i1]) continue;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int k = row_ptr[i1]; k < row_ptr[i1 + 1]; ++k) {
+            const int i2 = cand[k];
+            const int dist = c->hdist[k];
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= ORBM_TH_LOW) {
+            if (bestDist < (float)bestDist2 * nn_ratio) {
+                if (vnMatches21[bestIdx2] >= 0) {
+                    matches12[vnMatches21[bestIdx2]] = -1;
+                    nmatches--;
+                }
+                matches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (check_orientation) {
+                    float rot = F1->keys[i1].angle - F2->keys[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)roundf(rot * factor);
+                    if (bin == ORBM_HISTO_LENGTH) bin = 0;
+                    if (bin < 0 || bin >= ORBM_HISTO_LENGTH) return orbx_set_error(ORBX_E_BAD_ARG, "angle outside [0,360)");
+                    rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, ORBM_HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {
+                const int idx1 = rotHist[i][j];
+                if (matches12[idx1] >= 0) {
+                    matches12[idx1] = -1;
+                    nmatches--;
+                }
+            }
+        }
+    }
+    for (int i1 = 0; i1 < F1->n; ++i1)
+        if (matches12[i1] >= 0) {
+            prev_matched[2 * i1] = F2->keys[matches12[i1]].x;
+            prev_matched[2 * i1 + 1] = F2->keys[matches12[i1]].y;
+        }
+    return nmatches;
+}
+
+}  // extern "C"

@@ -42,13 +42,18 @@ namespace {
 
 thread_local std::string g_err = "";
 
-int fail(int code, const char* fmt, ...) {
+int vfail(int code, const char* fmt, va_list ap) {
     char buf[512];
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    g_err = buf;
+    return code;
+}
+
+int fail(int code, const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
-    vsnprintf(buf, sizeof buf, fmt, ap);
+    vfail(code, fmt, ap);
     va_end(ap);
-    g_err = buf;
     return code;
 }
 
@@ -63,6 +68,19 @@ int fail(int code, const char* fmt, ...) {
 inline int cv_round(float v) { return (int)lrintf(v); }  // cvRound: round half to even
 inline int cv_floor(double v) { int i = (int)v; return i - (i > v); }
 inline int round_up(int v, int a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+// used by orbm_api.cu so that both halves of the library share orbx_last_error_string()
+int orbx_set_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vfail(code, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+namespace {
 
 struct SlotCaps {  // bytes currently allocated per device buffer
     size_t img_in = 0, pyr = 0, cellcnt = 0, cellkeys = 0, keysA = 0, keysB = 0, surv = 0, survcnt = 0,

@@ -1,0 +1,150 @@
+"""Host-side mirror of the reference's Hamming searches over the C ABI of include/orbm.h.
+
+`Frame` is the POD snapshot of the parts of ORB_SLAM3::Frame the searches read (keypoints,
+descriptors, image bounds, grid pitch, scale factors; include/Frame.h); `ORBmatcher` carries
+mfNNratio / mbCheckOrientation like the reference class (include/ORBmatcher.h:36-44) and exposes
+the searches with the reference's names.  All distances run on the GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import KP_DTYPE, check
+from ._lib_match import FrameView, LAST_OBS_DTYPE, MAP_POINT_DTYPE  # noqa: F401
+
+FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48
+
+
+class Frame:
+    """Snapshot of a Frame: mvKeysUn, mDescriptors, mnMinX.., mfGridElement*Inv, mvScaleFactors, mvuRight."""
+
+    def __init__(self, keys, desc, width, height, scale_factors, u_right=None, bounds=None):
+        self.keys = np.ascontiguousarray(keys, KP_DTYPE)
+        self.desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        assert len(self.keys) == len(self.desc)
+        self.scale_factors = np.ascontiguousarray(scale_factors, np.float32)
+        self.u_right = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        # no distortion: bounds are the image (src/Frame.cc:773-800, ComputeImageBounds)
+        mnx, mny, mxx, mxy = bounds if bounds is not None else (0.0, 0.0, float(width), float(height))
+        self.bounds = (np.float32(mnx), np.float32(mny), np.float32(mxx), np.float32(mxy))
+        # src/Frame.cc:119-120: static_cast<float>(FRAME_GRID_COLS) / (mnMaxX - mnMinX)
+        self.grid_w_inv = np.float32(FRAME_GRID_COLS) / (self.bounds[2] - self.bounds[0])
+        self.grid_h_inv = np.float32(FRAME_GRID_ROWS) / (self.bounds[3] - self.bounds[1])
+
+    @property
+    def N(self):
+        return len(self.keys)
+
+    def view(self) -> FrameView:
+        return FrameView(self.keys.ctypes.data, self.desc.ctypes.data, len(self.keys), self.bounds[0],
+                         self.bounds[1], self.bounds[2], self.bounds[3], self.grid_w_inv, self.grid_h_inv,
+                         self.scale_factors.ctypes.data, len(self.scale_factors),
+                         None if self.u_right is None else self.u_right.ctypes.data)
+
+    def GetFeaturesInArea(self, x, y, r, minLevel=-1, maxLevel=-1):
+        lib = _lib.load()
+        out = np.zeros(max(1, self.N), np.int32)
+        v = self.view()
+        n = lib.orbm_features_in_area(C.byref(v), x, y, r, minLevel, maxLevel, out.ctypes.data, len(out))
+        if n < 0:
+            check(n)
+        return out[:n].copy()
+
+
+class ORBmatcher:
+    TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30
+
+    def __init__(self, nnratio: float = 0.6, checkOri: bool = True, device: int = 0):
+        self.lib = _lib.load()
+        self.mfNNratio, self.mbCheckOrientation = float(nnratio), bool(checkOri)
+        self.ctx = C.c_void_p()
+        check(self.lib.orbm_create(device, C.byref(self.ctx)))
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.orbm_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- layer 1 ------------------------------------------------------------------------------------
+    def hamming_csr(self, q, t, row_ptr, cand):
+        q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
+        t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
+        row_ptr = np.ascontiguousarray(row_ptr, np.int32)
+        cand = np.ascontiguousarray(cand, np.int32)
+        out = np.zeros(len(cand), np.uint16)
+        check(self.lib.orbm_hamming_csr(self.ctx, q.ctypes.data, len(q), t.ctypes.data, len(t),
+                                        row_ptr.ctypes.data, cand.ctypes.data, len(cand), out.ctypes.data))
+        return out
+
+    def knn2(self, q, t):
+        """BFMatcher(NORM_HAMMING).knnMatch(q, t, k=2) -> (idx[nq,2], dist[nq,2])."""
+        q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
+        t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
+        idx = np.zeros((len(q), 2), np.int32)
+        dist = np.zeros((len(q), 2), np.int32)
+        check(self.lib.orbm_knn2(self.ctx, q.ctypes.data, len(q), t.ctypes.data, len(t), idx.ctypes.data,
+                                 dist.ctypes.data))
+        return idx, dist
+
+    def stereo_rows(self, left: Frame, right: Frame, min_d: float, max_d: float):
+        """Hamming part of Frame::ComputeStereoMatches -> (best right index or -1, best distance)."""
+        bi = np.zeros(left.N, np.int32)
+        bd = np.zeros(left.N, np.int32)
+        check(self.lib.orbm_stereo_rows(self.ctx, left.keys.ctypes.data, left.desc.ctypes.data, left.N,
+                                        right.keys.ctypes.data, right.desc.ctypes.data, right.N,
+                                        left.scale_factors.ctypes.data, len(left.scale_factors), min_d, max_d,
+                                        bi.ctypes.data, bd.ctypes.data))
+        return bi, bd
+
+    # ---- layer 2 ------------------------------------------------------------------------------------
+    def SearchByProjection(self, F: Frame, map_points, mp_desc, th=1.0, bFarPoints=False, thFarPoints=50.0,
+                           kp_obs=None):
+        """SearchByProjection(Frame&, vector<MapPoint*>&, th, bFarPoints, thFarPoints).
+        Returns (nmatches, kp_match[N], kp_obs[N])."""
+        mps = np.ascontiguousarray(map_points, MAP_POINT_DTYPE)
+        mp_desc = np.ascontiguousarray(mp_desc, np.uint8).reshape(-1, 32)
+        obs = np.full(F.N, -1, np.int32) if kp_obs is None else np.ascontiguousarray(kp_obs, np.int32).copy()
+        match = np.zeros(F.N, np.int32)
+        v = F.view()
+        n = self.lib.orbm_search_by_projection_points(self.ctx, C.byref(v), mps.ctypes.data, mp_desc.ctypes.data,
+                                                      len(mps), th, int(bFarPoints), thFarPoints, self.mfNNratio,
+                                                      obs.ctypes.data, match.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, match, obs
+
+    def SearchByProjectionFrames(self, CurrentFrame: Frame, last_obs, last_desc, th, bForward=False,
+                                 bBackward=False, mbf=0.0, kp_obs=None):
+        """SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono)."""
+        lo = np.ascontiguousarray(last_obs, LAST_OBS_DTYPE)
+        last_desc = np.ascontiguousarray(last_desc, np.uint8).reshape(-1, 32)
+        obs = np.full(CurrentFrame.N, -1, np.int32) if kp_obs is None else np.ascontiguousarray(kp_obs, np.int32).copy()
+        match = np.zeros(CurrentFrame.N, np.int32)
+        v = CurrentFrame.view()
+        n = self.lib.orbm_search_by_projection_frames(self.ctx, C.byref(v), lo.ctypes.data, last_desc.ctypes.data,
+                                                      len(lo), th, int(bForward), int(bBackward), mbf,
+                                                      int(self.mbCheckOrientation), obs.ctypes.data, match.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, match, obs
+
+    def SearchForInitialization(self, F1: Frame, F2: Frame, vbPrevMatched, windowSize=10):
+        """Returns (nmatches, vnMatches12[N1], updated vbPrevMatched[N1,2])."""
+        prev = np.ascontiguousarray(vbPrevMatched, np.float32).reshape(-1, 2).copy()
+        m12 = np.zeros(F1.N, np.int32)
+        v1, v2 = F1.view(), F2.view()
+        n = self.lib.orbm_search_for_initialization(self.ctx, C.byref(v1), C.byref(v2), prev.ctypes.data,
+                                                    m12.ctypes.data, int(windowSize), self.mfNNratio,
+                                                    int(self.mbCheckOrientation))
+        if n < 0:
+            check(n)
+        return n, m12, prev

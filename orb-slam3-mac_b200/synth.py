@@ -118,3 +118,58 @@ def frame(kind: str, h: int, w: int, seed: int) -> np.ndarray:
     if kind == "black":
         return black(h, w)
     raise ValueError(kind)
+
+
+# ---- matcher inputs ------------------------------------------------------
+MAP_POINT_DTYPE = np.dtype([("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_xr", "<f4"), ("view_cos", "<f4"),
+                            ("depth", "<f4"), ("level", "<i4"), ("observations", "<i4"),
+                            ("in_view", "u1"), ("bad", "u1"), ("_pad", "u1", (2,))])
+LAST_OBS_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("inv_z", "<f4"), ("angle", "<f4"),
+                           ("octave", "<i4"), ("observations", "<i4"), ("valid", "u1"), ("_pad", "u1", (3,))])
+
+
+def flip_bits(desc: np.ndarray, p: float, rng) -> np.ndarray:
+    bits = np.unpackbits(desc, axis=1)
+    bits ^= (rng.random(bits.shape) < p).astype(np.uint8)
+    return np.packbits(bits, axis=1)
+
+
+def map_points_from_frame(keys, desc, width, height, total: int, seed: int, nlevels: int = 8):
+    """Map points that re-observe a frame's keypoints (descriptor bits flipped w.p. 0.04, projection
+    = keypoint + N(0, 1.5 px), predicted level = octave, viewCos ~ U(0.9, 1)), padded to `total` with
+    uniformly random descriptors at uniformly random in-image positions."""
+    rng = np.random.default_rng(seed + 49979687)
+    n = min(len(keys), total)
+    mps = np.zeros(total, MAP_POINT_DTYPE)
+    md = np.zeros((total, 32), np.uint8)
+    md[:n] = flip_bits(desc[:n], 0.04, rng)
+    mps["proj_x"][:n] = keys["x"][:n] + rng.normal(0, 1.5, n)
+    mps["proj_y"][:n] = keys["y"][:n] + rng.normal(0, 1.5, n)
+    mps["level"][:n] = keys["octave"][:n]
+    md[n:] = rng.integers(0, 256, (total - n, 32), dtype=np.uint8)
+    mps["proj_x"][n:] = rng.uniform(0, width, total - n)
+    mps["proj_y"][n:] = rng.uniform(0, height, total - n)
+    mps["level"][n:] = rng.integers(0, nlevels, total - n)
+    mps["view_cos"] = rng.uniform(0.9, 1.0, total)
+    mps["depth"] = rng.uniform(0.5, 60.0, total)
+    mps["proj_xr"] = mps["proj_x"] - rng.uniform(1.0, 40.0, total)
+    mps["observations"] = rng.integers(0, 6, total)
+    mps["in_view"] = (rng.random(total) < 0.9).astype(np.uint8)
+    mps["bad"] = (rng.random(total) < 0.02).astype(np.uint8)
+    perm = rng.permutation(total)  # acceptance is order dependent: interleave real and padding points
+    return mps[perm].copy(), md[perm].copy()
+
+
+def last_frame_obs(keys, desc, seed: int):
+    """Observations of a last frame re-projected into the current one (3 px shift + noise)."""
+    rng = np.random.default_rng(seed + 67867967)
+    n = len(keys)
+    lo = np.zeros(n, LAST_OBS_DTYPE)
+    lo["u"] = keys["x"] + 3.0 + rng.normal(0, 1.0, n)
+    lo["v"] = keys["y"] + rng.normal(0, 1.0, n)
+    lo["inv_z"] = rng.uniform(-0.02, 1.0, n)  # a few points behind the camera
+    lo["angle"] = keys["angle"]
+    lo["octave"] = keys["octave"]
+    lo["observations"] = rng.integers(0, 4, n)
+    lo["valid"] = (rng.random(n) < 0.8).astype(np.uint8)
+    return lo, flip_bits(desc, 0.03, rng)

@@ -1,0 +1,197 @@
+"""Parity of the CUDA Hamming searches (through the C ABI of include/orbm.h) against the CPU
+oracle on the same POD snapshots: distances, 2-NN, rectified-stereo arg-min, and the three
+order-dependent ORBmatcher searches.  Bar: bit-exact match indices and counts (north_star)."""
+import numpy as np
+import pytest
+
+from orb_slam3_mac_b200 import synth as S
+
+pytestmark = pytest.mark.gpu
+
+SF = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
+
+
+@pytest.fixture(scope="module")
+def mo(oracle_libs):
+    return oracle_libs.MatchOracle()
+
+
+@pytest.fixture(scope="module")
+def matcher():
+    from orb_slam3_mac_b200.matcher import ORBmatcher
+    m = ORBmatcher(0.8, True)
+    yield m
+    m.close()
+
+
+@pytest.fixture(scope="module")
+def extract(oracle_libs):
+    """Frames for the matcher tests come from the CPU oracle extractor (any extractor would do:
+    both sides of each comparison see identical snapshots)."""
+    cache = {}
+
+    def run(img, nf, lap=(0, 0)):
+        key = (hash(img.tobytes()), img.shape, nf, lap)
+        if key not in cache:
+            kind = "ref" if oracle_libs.have_ref() else "port"
+            ex = oracle_libs.OracleExtractor(nf, 1.2, 8, 20, 7, kind=kind)
+            cache[key] = ex(img, lap)
+        return cache[key]
+
+    return run
+
+
+def _frame(keys, desc, w, h, u_right=None):
+    from orb_slam3_mac_b200.matcher import Frame
+    return Frame(keys, desc, w, h, SF, u_right=u_right)
+
+
+def test_hamming_csr_matches_popcount(matcher):
+    rng = np.random.default_rng(0)
+    q = rng.integers(0, 256, (700, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (1300, 32), dtype=np.uint8)
+    counts = rng.integers(0, 40, 700)
+    counts[::7] = 0  # ragged: empty rows
+    row_ptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    cand = rng.integers(0, 1300, row_ptr[-1]).astype(np.int32)
+    got = matcher.hamming_csr(q, t, row_ptr, cand)
+    rows = np.repeat(np.arange(700), counts)
+    exp = np.unpackbits(q[rows] ^ t[cand], axis=1).sum(axis=1)
+    assert np.array_equal(got, exp.astype(np.uint16))
+    assert len(matcher.hamming_csr(q, t, np.zeros(701, np.int32), np.zeros(0, np.int32))) == 0
+
+
+def test_knn2_matches_oracle_and_cv2(matcher, mo):
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(2)
+    for nq, nt, lowent in ((1500, 1500, False), (300, 257, True), (64, 1, False), (10, 2, True), (33, 1564, False)):
+        if lowent:
+            q = (rng.integers(0, 2, (nq, 32), dtype=np.uint8) * 255).astype(np.uint8)
+            t = (rng.integers(0, 2, (nt, 32), dtype=np.uint8) * 255).astype(np.uint8)
+        else:
+            q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+            t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+        idx, dist = matcher.knn2(q, t)
+        oi, od = mo.knn2(q, t)
+        assert np.array_equal(idx, oi) and np.array_equal(dist, od)
+        ref = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q[:50], t, k=2)
+        for i, ms in enumerate(ref):
+            for k, m in enumerate(ms):
+                assert (idx[i, k], dist[i, k]) == (m.trainIdx, int(m.distance))
+
+
+def test_fisheye_stereo_knn2_c3(matcher, mo, extract):
+    """Config C3: 2 x 512x512, 1500 features, lapping {0,511} -> every keypoint is 'stereo'
+    (monoLeft = monoRight = 0), brute-force 2-NN + Lowe ratio 0.7 (src/Frame.cc:1146-1153)."""
+    l, r = S.fisheye_pair(512, 5)
+    ml, kl, dl = extract(l, 1500, (0, 511))
+    mr, kr, dr = extract(r, 1500, (0, 511))
+    assert ml == 0 and mr == 0
+    idx, dist = matcher.knn2(dl, dr)
+    oi, od = mo.knn2(dl, dr)
+    assert np.array_equal(idx, oi) and np.array_equal(dist, od)
+    good = dist[:, 0] < dist[:, 1] * np.float32(0.7)
+    assert good.sum() > 100  # the pair really overlaps
+
+
+def test_stereo_rows_c2(matcher, mo, extract):
+    """Config C2: EuRoC stereo pair, 1200 features per image, lapping {0,0}."""
+    for seed in (1, 2):
+        l, r = S.stereo_pair(480, 752, seed)
+        _, kl, dl = extract(l, 1200)
+        _, kr, dr = extract(r, 1200)
+        L, R = _frame(kl, dl, 752, 480), _frame(kr, dr, 752, 480)
+        for min_d, max_d in ((0.0, 80.0), (0.0, 20.0), (5.0, 400.0)):
+            bi, bd = matcher.stereo_rows(L, R, min_d, max_d)
+            oi, od = mo.stereo_rows(L, R, 480, min_d, max_d)
+            assert np.array_equal(bi, oi) and np.array_equal(bd, od)
+        bi, bd = matcher.stereo_rows(L, R, 0.0, 80.0)
+        assert (bd < 75).sum() > 200  # thOrbDist (src/Frame.cc:807): plenty of real matches
+
+
+@pytest.mark.parametrize("th,far,u_right", [(1.0, False, False), (3.0, True, False), (1.0, False, True)])
+def test_search_by_projection_points_c4(matcher, mo, extract, th, far, u_right):
+    """Config C4: 1280x720, 2000 features, 10,000 map points."""
+    img0 = S.textured_noise(720, 1280, 7)
+    img1 = np.roll(img0, 3, axis=1)  # same scene, 3-px shift
+    _, k0, d0 = extract(img0, 2000, (0, 1000))
+    _, k1, d1 = extract(img1, 2000, (0, 1000))
+    mps, md = S.map_points_from_frame(k0, d0, 1280, 720, 10000, 7)
+    rng = np.random.default_rng(3)
+    ur = None
+    if u_right:
+        ur = np.where(rng.random(len(k1)) < 0.6, k1["x"] - rng.uniform(1, 40, len(k1)), -1.0).astype(np.float32)
+    F = _frame(k1, d1, 1280, 720, u_right=ur)
+    obs0 = np.where(rng.random(len(k1)) < 0.2, rng.integers(0, 3, len(k1)), -1).astype(np.int32)
+    n, match, obs = matcher.SearchByProjection(F, mps, md, th, far, 30.0, kp_obs=obs0)
+    on, omatch, oobs = mo.search_by_projection_points(F, mps, md, th, far, 30.0, 0.8, kp_obs=obs0)
+    assert n == on and np.array_equal(match, omatch) and np.array_equal(obs, oobs)
+    assert n > 300
+
+
+@pytest.mark.parametrize("fwd,bwd,check,u_right", [(False, False, True, False), (True, False, True, False),
+                                                    (False, True, False, True)])
+def test_search_by_projection_frames(matcher, mo, extract, fwd, bwd, check, u_right):
+    from orb_slam3_mac_b200.matcher import ORBmatcher
+    img0 = S.textured_noise(480, 752, 11)
+    img1 = np.roll(img0, 3, axis=1)
+    _, k0, d0 = extract(img0, 1000, (0, 1000))
+    _, k1, d1 = extract(img1, 1000, (0, 1000))
+    lo, ld = S.last_frame_obs(k0, d0, 11)
+    rng = np.random.default_rng(5)
+    ur = (k1["x"] - rng.uniform(1, 30, len(k1))).astype(np.float32) if u_right else None
+    cur = _frame(k1, d1, 752, 480, u_right=ur)
+    m = ORBmatcher(0.9, check)
+    for th in (7.0, 15.0):
+        n, match, obs = m.SearchByProjectionFrames(cur, lo, ld, th, fwd, bwd, 40.0)
+        on, omatch, oobs = mo.search_by_projection_frames(cur, lo, ld, th, fwd, bwd, 40.0, check)
+        assert n == on and np.array_equal(match, omatch) and np.array_equal(obs, oobs)
+    assert n > 100
+    m.close()
+
+
+def test_search_for_initialization(mo, extract):
+    """Mono initialisation uses the 5 x nFeatures extractor (src/Tracking.cc:212) and 100-px
+    windows (src/Tracking.cc:1506-1507): hundreds of candidates per query."""
+    from orb_slam3_mac_b200.matcher import ORBmatcher
+    img0 = S.textured_noise(480, 752, 21)
+    img1 = np.roll(img0, 5, axis=1)
+    img1 = np.roll(img1, 2, axis=0)
+    _, k0, d0 = extract(img0, 5000, (0, 1000))
+    _, k1, d1 = extract(img1, 5000, (0, 1000))
+    F1, F2 = _frame(k0, d0, 752, 480), _frame(k1, d1, 752, 480)
+    prev = np.stack([k0["x"], k0["y"]], axis=1)
+    for ratio, check, win in ((0.9, True, 100), (0.9, False, 30)):
+        m = ORBmatcher(ratio, check)
+        n, m12, pv = m.SearchForInitialization(F1, F2, prev, win)
+        on, om12, opv = mo.search_for_initialization(F1, F2, prev, win, ratio, check)
+        assert n == on and np.array_equal(m12, om12) and np.array_equal(pv, opv)
+        assert n > 100
+        # second call with the updated vbPrevMatched, as Tracking does frame after frame
+        n2, m12b, _ = m.SearchForInitialization(F1, F2, pv, win)
+        on2, om12b, _ = mo.search_for_initialization(F1, F2, opv, win, ratio, check)
+        assert n2 == on2 and np.array_equal(m12b, om12b)
+        m.close()
+
+
+def test_matcher_contexts_are_concurrent(mo):
+    """Tracking, LocalMapping and LoopClosing construct ORBmatcher objects on three threads."""
+    import threading
+    from orb_slam3_mac_b200.matcher import ORBmatcher
+    rng = np.random.default_rng(9)
+    q = rng.integers(0, 256, (400, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (900, 32), dtype=np.uint8)
+    exp = mo.knn2(q, t)
+    res = [None] * 3
+
+    def work(i):
+        m = ORBmatcher(0.8, True)
+        for _ in range(10):
+            res[i] = m.knn2(q, t)
+        m.close()
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(3)]
+    [x.start() for x in ts]
+    [x.join() for x in ts]
+    for r in res:
+        assert np.array_equal(r[0], exp[0]) and np.array_equal(r[1], exp[1])

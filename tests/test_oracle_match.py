@@ -1,0 +1,94 @@
+"""Pins what can be pinned of the matcher oracle without a GPU (the reference's ORBmatcher.cc is
+not compilable here and holds no golden vectors -- parity is otherwise 'unpinned', see
+oracle/match_oracle.cpp): DescriptorDistance against numpy popcount, the 2-NN search against the
+real cv2.BFMatcher, GetFeaturesInArea against a brute-force scan, and the product's host-side
+candidate generation against the oracle's."""
+import numpy as np
+import pytest
+
+from orb_slam3_mac_b200 import synth as S
+
+
+@pytest.fixture(scope="module")
+def mo(oracle_libs):
+    return oracle_libs.MatchOracle()
+
+
+def _rand_frame(n, w, h, seed, nlevels=8):
+    from orb_slam3_mac_b200.matcher import Frame
+    from orb_slam3_mac_b200._lib import KP_DTYPE
+    rng = np.random.default_rng(seed)
+    k = np.zeros(n, KP_DTYPE)
+    k["x"] = rng.uniform(-5, w + 5, n)  # a few outside the image bounds (undistorted keypoints can be)
+    k["y"] = rng.uniform(-5, h + 5, n)
+    k["octave"] = rng.integers(0, nlevels, n)
+    k["angle"] = rng.uniform(0, 360, n)
+    d = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    sf = (np.float32(1.2) ** np.arange(nlevels)).astype(np.float32)
+    return Frame(k, d, w, h, sf)
+
+
+def test_descriptor_distance_is_popcount(mo):
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 256, (200, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (200, 32), dtype=np.uint8)
+    b[:20] = a[:20]
+    b[20:40] = ~a[20:40]
+    for i in range(200):
+        assert mo.distance(a[i], b[i]) == int(np.unpackbits(a[i] ^ b[i]).sum())
+
+
+def test_knn2_matches_cv2_bfmatcher_including_ties(mo):
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(1)
+    for nq, nt, lowent in ((300, 257, True), (100, 400, False), (5, 1, False), (7, 2, True)):
+        if lowent:  # low-entropy descriptors -> many distance ties
+            q = (rng.integers(0, 2, (nq, 32), dtype=np.uint8) * 255).astype(np.uint8)
+            t = (rng.integers(0, 2, (nt, 32), dtype=np.uint8) * 255).astype(np.uint8)
+        else:
+            q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+            t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+        idx, dist = mo.knn2(q, t)
+        ref = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q, t, k=2)
+        assert len(ref) == nq
+        for i, ms in enumerate(ref):
+            assert len(ms) == min(2, nt)
+            for k, m in enumerate(ms):
+                assert (idx[i, k], dist[i, k]) == (m.trainIdx, int(m.distance)), (i, k)
+            for k in range(len(ms), 2):
+                assert idx[i, k] == -1 and dist[i, k] == -1
+
+
+def test_features_in_area_oracle_vs_bruteforce_and_product(mo):
+    """Order = grid columns outer, rows inner, insertion order inside a cell (src/Frame.cc:682-684)."""
+    from orb_slam3_mac_b200.matcher import Frame  # noqa: F401
+    F = _rand_frame(3000, 752, 480, 3)
+    rng = np.random.default_rng(4)
+    k = F.keys
+    px = np.round((k["x"] - F.bounds[0]) * F.grid_w_inv).astype(np.int64)
+    py = np.round((k["y"] - F.bounds[1]) * F.grid_h_inv).astype(np.int64)
+    ingrid = (px >= 0) & (px < 64) & (py >= 0) & (py < 48)
+    total = 0
+    for it in range(300):
+        x, y = float(rng.uniform(-30, 780)), float(rng.uniform(-30, 510))
+        r = float(rng.choice([3.0, 10.0, 40.0, 100.0]))
+        mn, mx = [(-1, -1), (0, 0), (2, 3), (1, -1), (0, 7)][it % 5]
+        got = mo.features_in_area(F, x, y, r, mn, mx)
+        # brute force over all keypoints: window + level gates, restricted to visited cells
+        x32, y32, r32 = np.float32(x), np.float32(y), np.float32(r)
+        c0 = max(0, int(np.floor((x32 - F.bounds[0] - r32) * F.grid_w_inv)))
+        c1 = min(63, int(np.ceil((x32 - F.bounds[0] + r32) * F.grid_w_inv)))
+        r0 = max(0, int(np.floor((y32 - F.bounds[1] - r32) * F.grid_h_inv)))
+        r1 = min(47, int(np.ceil((y32 - F.bounds[1] + r32) * F.grid_h_inv)))
+        ok = ingrid & (px >= c0) & (px <= c1) & (py >= r0) & (py <= r1)
+        ok &= (np.abs(k["x"] - x32) < r32) & (np.abs(k["y"] - y32) < r32)
+        if mn > 0 or mx >= 0:
+            ok &= k["octave"] >= mn
+            if mx >= 0:
+                ok &= k["octave"] <= mx
+        idx = np.nonzero(ok)[0]
+        order = np.lexsort((idx, py[idx], px[idx]))
+        assert np.array_equal(got, idx[order].astype(np.int32)), it
+        assert np.array_equal(F.GetFeaturesInArea(x, y, r, mn, mx), got), it  # product host code
+        total += len(got)
+    assert total > 5000
