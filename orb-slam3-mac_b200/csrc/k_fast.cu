@@ -3,15 +3,22 @@
 // pinned in oracle/cvprims.h against cv2 4.13).
 //
 // One warp owns one 30-px cell of one level of one frame (all levels in a single launch):
-//   1. the (wCell+6) x (hCell+6) tile is staged in shared memory with aligned 32-bit loads;
-//   2. every detection pixel takes a 4-point rejection test; survivors are compacted through a
-//      64-entry shared-memory queue (ballot/popc) so that the exact score is always evaluated
-//      by 32 busy lanes;
-//   3. the exact score = max over the 16 arcs of 9 of min(ring - c) / min(c - ring), minus 1
-//      (cornerScore<16>), is computed for bright and dark arcs AT ONCE on packed s16x2 values
-//      (one IMAD builds {ring-c+256, c-ring+256}; __vimin3_s16x2 / __vimax3_s16x2 do the rest);
+//   1. the (wCell+6) x (hCell+6) tile is staged in shared memory with aligned 32-bit loads,
+//      a fixed lane -> (row offset, word) mapping (no per-word division);
+//   2. REJECTION TEST, 8 pixels per lane per step: 64-bit shared loads of the centre row and of
+//      the rows 3 above / below, funnel shifts for the +-3 column neighbours, VABSDIFF4.U8 for
+//      |ring - c| on four pixels at once, and a carry-free per-byte "> th" flag
+//      (((d >> 1) & 0x7f) + K, bit 7).  A 9-arc contains one pixel of every opposite ring pair,
+//      so (|r0-c|>th or |r8-c|>th) and (|r4-c|>th or |r12-c|>th) is necessary; ~7 % of the
+//      pixels of a textured frame pass (the sign-aware scalar test passes 5.3 %);
+//   3. passing pixels are pushed (raster order, ballot/popc ranks) into a shared-memory ring;
+//      whenever 32 are queued the exact score = max over the 16 arcs of 9 of min(ring - c) /
+//      min(c - ring), minus 1 (cornerScore<16>) is evaluated by 32 busy lanes, for bright and
+//      dark arcs AT ONCE on packed s16x2 values (one IMAD builds {ring-c+256, c-ring+256};
+//      VIMNMX3.S16x2 does the rest); corners go to the score map and to a raster-ordered list;
 //   4. 3x3 non-max suppression inside the cell only (scores outside the cell's detection region
-//      are 0 -- NMS never crosses a cell), strict '>' on all 8 neighbours;
+//      are 0 -- NMS never crosses a cell), strict '>' on all 8 neighbours, run over the corner
+//      list (a dense pass is kept for cells with more corners than the list holds);
 //   5. survivors are emitted in raster order (ballot/popc compaction) into the cell's
 //      fixed-capacity slot; if none survived, steps 2-5 repeat with minThFAST.
 // Order of candidates = cells row-major, raster inside a cell, which is what the quadtree
@@ -19,11 +26,15 @@
 #include "orbx_device.cuh"
 
 #define FAST_WARPS 8
+#define FAST_Q 512       // ring of queued pixels (u16): <= 31 left over + 256 pushed per step
+#define FAST_CLIST 256   // corners kept for the sparse NMS pass
 
 struct FastWarpSmem {
-    uint8_t* tile;   // tile_pitch * tile_h
-    uint8_t* score;  // score_pitch * (dh + 2), 1-px zero frame around the detection region
-    uint16_t* queue; // 64 entries
+    uint8_t* tile;    // tile_pitch * tile_h, rows 8-byte aligned
+    uint8_t* score;   // score_pitch * (dh + 2), 1-px zero frame around the detection region
+    uint16_t* queue;  // FAST_Q entries: (tile row << 7) | tile byte column
+    uint16_t* clist;  // FAST_CLIST entries, same encoding
+    int xo;           // tile byte column of tile x = 0 (alignment slack of the staged words)
 };
 
 __device__ __forceinline__ int fast_exact_score(const uint8_t* t, int tp) {
@@ -62,59 +73,127 @@ __device__ __forceinline__ int fast_exact_score(const uint8_t* t, int tp) {
     return max(bright, dark) - 1;
 }
 
-// Computes the score map for threshold `th` (s = raw-1 stored where raw > th, else 0 kept).
-__device__ __forceinline__ void fast_scores(const FastWarpSmem& s, int tp, int sp, int dw, int dh,
-                                            uint32_t dw_inv, int th) {
+// Exact score of up to 32 queued pixels (lane < take); corners (raw > th) go to the score map
+// and, in queue (= raster) order, to the corner list.
+__device__ __forceinline__ void fast_drain(const FastWarpSmem& s, int tp, int sp, int th, int qhead,
+                                           int take, int& ncorn) {
     const int lane = orbx_lane();
-    const int npix = dw * dh;
-    int qhead = 0, qn = 0;
-    for (int base = 0; base < npix; base += 32) {
-        const int p = base + lane;
-        bool pass = false;
-        if (p < npix) {
-            const int y = (int)(((uint32_t)p * dw_inv) >> 20);
-            const int x = p - y * dw;
-            const uint8_t* t = s.tile + (y + 3) * tp + (x + 3);
-            const int c = t[0];
-            const int r0 = t[3 * tp], r8 = t[-3 * tp], r4 = t[3], r12 = t[-3];
-            const int hi = c + th, lo = c - th;
-            const bool bright = (max(r0, r8) > hi) && (max(r4, r12) > hi);
-            const bool dark = (min(r0, r8) < lo) && (min(r4, r12) < lo);
-            pass = bright || dark;
-        }
-        const uint32_t m = __ballot_sync(ORBX_FULL, pass);
-        if (pass) s.queue[(qhead + qn + __popc(m & orbx_lanemask_lt())) & 63] = (uint16_t)p;
-        qn += __popc(m);
-        __syncwarp();
-        if (qn >= 32 || (base + 32 >= npix && qn > 0)) {
-            // drain up to 32 queued pixels with all lanes busy
-            const int take = min(qn, 32);
-            if (lane < take) {
-                const int q = s.queue[(qhead + lane) & 63];
-                const int y = (int)(((uint32_t)q * dw_inv) >> 20);
-                const int x = q - y * dw;
-                const int sc = fast_exact_score(s.tile + (y + 3) * tp + (x + 3), tp);
-                if (sc >= th) s.score[(y + 1) * sp + (x + 1)] = (uint8_t)sc;
-            }
-            qhead = (qhead + take) & 63;
-            qn -= take;
-            __syncwarp();
+    bool corner = false;
+    int e = 0;
+    if (lane < take) {
+        e = s.queue[(qhead + lane) & (FAST_Q - 1)];
+        const int r = e >> 7, bc = e & 127;
+        const int sc = fast_exact_score(s.tile + r * tp + bc, tp);
+        if (sc >= th) {
+            corner = true;
+            s.score[(r - 2) * sp + (bc - s.xo - 2)] = (uint8_t)sc;
         }
     }
-    // the loop's last iteration drains at most 32; a second drain covers 32 < qn < 64
-    if (qn > 0) {
-        if (lane < qn) {
-            const int q = s.queue[(qhead + lane) & 63];
-            const int y = (int)(((uint32_t)q * dw_inv) >> 20);
-            const int x = q - y * dw;
-            const int sc = fast_exact_score(s.tile + (y + 3) * tp + (x + 3), tp);
-            if (sc >= th) s.score[(y + 1) * sp + (x + 1)] = (uint8_t)sc;
-        }
-    }
-    __syncwarp();
+    const uint32_t m = __ballot_sync(ORBX_FULL, corner);
+    const int at = ncorn + __popc(m & orbx_lanemask_lt());
+    if (corner && at < FAST_CLIST) s.clist[at] = (uint16_t)e;
+    ncorn += __popc(m);
 }
 
-// NMS + ordered emission.  Returns the number of keypoints written.
+// Per-byte flag (bit 7) of d > th for four packed absolute differences; K4 = (128 - ((th+1)>>1))
+// replicated.  Conservative by at most one grey level for even th (d >= th passes).
+__device__ __forceinline__ uint32_t fast_gt4(uint32_t d, uint32_t K4) {
+    return ((d >> 1) & 0x7f7f7f7fu) + K4;
+}
+
+// Computes the score map for threshold `th` (s = raw-1 stored where raw > th, else 0 kept) and
+// the raster-ordered corner list.  Returns the number of corners (may exceed FAST_CLIST).
+__device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp, int dw, int dh, int th) {
+    const int lane = orbx_lane();
+    // detection bytes of a tile row: [b0, b1]; 8-byte pairs [plo, phi]
+    const int b0 = s.xo + 3, b1 = s.xo + 2 + dw;
+    const int plo = b0 >> 3, npair = (b1 >> 3) - plo + 1;
+    const int rpi = 32 / npair;              // rows per step
+    const int ro = lane / npair, pc = plo + (lane - ro * npair);
+    const bool active = ro < rpi;
+    // valid-byte masks (bit 7 of each detection byte) of this lane's pair
+    uint32_t vlo = 0, vhi = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int ba = pc * 8 + k, bb = pc * 8 + 4 + k;
+        if (ba >= b0 && ba <= b1) vlo |= 0x80u << (8 * k);
+        if (bb >= b0 && bb <= b1) vhi |= 0x80u << (8 * k);
+    }
+    const uint32_t K4 = (uint32_t)(128 - ((th + 1) >> 1)) * 0x01010101u;
+    int qhead = 0, qn = 0, ncorn = 0;
+    for (int rb = 3; rb < 3 + dh; rb += rpi) {
+        const int r = rb + ro;
+        uint32_t flo = 0, fhi = 0;
+        if (active && r < 3 + dh) {
+            const uint8_t* row = s.tile + r * tp + pc * 8;
+            const uint2 c = *reinterpret_cast<const uint2*>(row);
+            const uint2 up = *reinterpret_cast<const uint2*>(row - 3 * tp);
+            const uint2 dn = *reinterpret_cast<const uint2*>(row + 3 * tp);
+            const uint32_t l1 = *reinterpret_cast<const uint32_t*>(row - 4);
+            const uint32_t r1 = *reinterpret_cast<const uint32_t*>(row + 8);
+            // pixels x-3 and x+3 of the eight centres
+            const uint32_t wl = __funnelshift_r(l1, c.x, 8), wh = __funnelshift_r(c.x, c.y, 8);
+            const uint32_t el = __funnelshift_r(c.x, c.y, 24), eh = __funnelshift_r(c.y, r1, 24);
+            const uint32_t v_lo = fast_gt4(__vabsdiffu4(up.x, c.x), K4) | fast_gt4(__vabsdiffu4(dn.x, c.x), K4);
+            const uint32_t h_lo = fast_gt4(__vabsdiffu4(wl, c.x), K4) | fast_gt4(__vabsdiffu4(el, c.x), K4);
+            const uint32_t v_hi = fast_gt4(__vabsdiffu4(up.y, c.y), K4) | fast_gt4(__vabsdiffu4(dn.y, c.y), K4);
+            const uint32_t h_hi = fast_gt4(__vabsdiffu4(wh, c.y), K4) | fast_gt4(__vabsdiffu4(eh, c.y), K4);
+            flo = v_lo & h_lo & vlo;
+            fhi = v_hi & h_hi & vhi;
+        }
+        // 8-bit pass mask of this lane (bit k = pixel k of the pair), ranks by warp scan
+        uint32_t nib = (((flo >> 7) * 0x00204081u) >> 21 & 0xfu) | ((((fhi >> 7) * 0x00204081u) >> 21 & 0xfu) << 4);
+        const uint32_t cnt = __popc(nib);
+        const uint32_t incl = warp_incl_scan(cnt);
+        const int total = (int)__shfl_sync(ORBX_FULL, incl, 31);
+        if (total) {
+            int at = qhead + qn + (int)(incl - cnt);
+            const int ebase = (r << 7) | (pc * 8);
+            while (nib) {
+                const int k = __ffs(nib) - 1;
+                nib &= nib - 1;
+                s.queue[at & (FAST_Q - 1)] = (uint16_t)(ebase + k);
+                ++at;
+            }
+            qn += total;
+            __syncwarp();
+            while (qn >= 32) {
+                fast_drain(s, tp, sp, th, qhead, 32, ncorn);
+                qhead = (qhead + 32) & (FAST_Q - 1);
+                qn -= 32;
+            }
+        }
+    }
+    if (qn > 0) fast_drain(s, tp, sp, th, qhead, qn, ncorn);
+    __syncwarp();
+    return ncorn;
+}
+
+// NMS + ordered emission over the corner list.  Returns the number of keypoints written.
+__device__ __forceinline__ int fast_nms_sparse(const FastWarpSmem& s, int sp, int ncorn, int xadd,
+                                               int yadd, uint32_t* __restrict__ slot) {
+    const int lane = orbx_lane();
+    int count = 0;
+    for (int base = 0; base < ncorn; base += 32) {
+        bool keep = false;
+        int x = 0, y = 0, sc = 0;
+        if (base + lane < ncorn) {
+            const int e = s.clist[base + lane];
+            y = (e >> 7) - 3;
+            x = (e & 127) - s.xo - 3;
+            const uint8_t* c = s.score + (y + 1) * sp + (x + 1);
+            sc = c[0];
+            keep = sc > c[-1] && sc > c[1] && sc > c[-sp - 1] && sc > c[-sp] && sc > c[-sp + 1] &&
+                   sc > c[sp - 1] && sc > c[sp] && sc > c[sp + 1];
+        }
+        const uint32_t m = __ballot_sync(ORBX_FULL, keep);
+        if (keep) slot[count + __popc(m & orbx_lanemask_lt())] = ORBX_MAKE_KEY(x + xadd, y + yadd, sc);
+        count += __popc(m);
+    }
+    return count;
+}
+
+// Dense NMS + ordered emission (cells with more than FAST_CLIST corners).
 __device__ __forceinline__ int fast_nms_emit(const FastWarpSmem& s, int sp, int dw, int dh,
                                              uint32_t dw_inv, int xadd, int yadd,
                                              uint32_t* __restrict__ slot) {
@@ -176,49 +255,60 @@ k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8
     FastWarpSmem s;
     uint8_t* base = smem + (size_t)warp * warp_smem_bytes;
     s.queue = reinterpret_cast<uint16_t*>(base);
-    s.tile = base + 128;
-    s.score = s.tile + tile_pitch * P.max_tile_h;
+    s.clist = s.queue + FAST_Q;
+    s.tile = base + 2 * (FAST_Q + FAST_CLIST);
+    s.score = s.tile + tile_pitch * (P.max_tile_h + 1);
 
-    // 1. stage the tile: aligned words covering [iniX & ~3, maxX)
+    // 1. stage the tile: aligned words covering [iniX & ~3, maxX); lane -> (row offset, word)
     int lpitch;
     const uint8_t* src = orbx_level_ptr(P, isrc, pyr, frame, l, &lpitch);
     const int ax = iniX & ~3;
-    const int xo = iniX - ax;  // tile x -> smem byte x + xo
-    const int nw = (maxX - ax + 3) >> 2;
-    const int nwords = nw * th_;
-    const uint32_t nw_inv = (1u << 20) / (uint32_t)nw + 1;
-    for (int i = lane; i < nwords; i += 32) {
-        const int r = (int)(((uint32_t)i * nw_inv) >> 20);
-        const int cw = i - r * nw;
-        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(iniY + r) * lpitch + ax) + cw);
-        reinterpret_cast<uint32_t*>(s.tile + r * tile_pitch)[cw] = v;
+    s.xo = iniX - ax;  // tile x -> smem byte x + xo
+    {
+        const int nw = (maxX - ax + 3) >> 2;   // <= tile_pitch / 4 <= 21
+        const int rpi = 32 / nw;
+        const int ro = lane / nw, cw = lane - ro * nw;
+        if (ro < rpi) {
+            const uint32_t* gp = reinterpret_cast<const uint32_t*>(src + (size_t)(iniY + ro) * lpitch + ax) + cw;
+            uint32_t* tp_ = reinterpret_cast<uint32_t*>(s.tile + ro * tile_pitch) + cw;
+            const size_t gstep = (size_t)rpi * lpitch / 4;
+            const int tstep = rpi * tile_pitch / 4;
+            for (int r = ro; r < th_; r += rpi) {
+                *tp_ = __ldg(gp);
+                gp += gstep;
+                tp_ += tstep;
+            }
+        }
     }
     // zero the score map (frame included)
     const int swords = (score_pitch * (dh + 2)) >> 2;
     for (int i = lane; i < swords; i += 32) reinterpret_cast<uint32_t*>(s.score)[i] = 0;
     __syncwarp();
 
-    FastWarpSmem t = s;
-    t.tile = s.tile + xo;
-    const uint32_t dw_inv = (1u << 20) / (uint32_t)dw + 1;
     const int xadd = 3 + cj * L.w_cell, yadd = 3 + ci * L.h_cell;
+    const uint32_t dw_inv = (1u << 20) / (uint32_t)dw + 1;
 
-    fast_scores(t, tile_pitch, score_pitch, dw, dh, dw_inv, P.ini_th);
-    int n = fast_nms_emit(t, score_pitch, dw, dh, dw_inv, xadd, yadd, slot);
+    int nc = fast_scores(s, tile_pitch, score_pitch, dw, dh, P.ini_th);
+    int n = nc <= FAST_CLIST ? fast_nms_sparse(s, score_pitch, nc, xadd, yadd, slot)
+                             : fast_nms_emit(s, score_pitch, dw, dh, dw_inv, xadd, yadd, slot);
     if (n == 0) {
         // ORBextractor.cc:824-828: rerun the cell with minThFAST.  Scores already stored are
-        // threshold independent, so the map is only extended.
-        fast_scores(t, tile_pitch, score_pitch, dw, dh, dw_inv, P.min_th);
-        n = fast_nms_emit(t, score_pitch, dw, dh, dw_inv, xadd, yadd, slot);
+        // threshold independent, so the map is only extended; the corner list is rebuilt.
+        nc = fast_scores(s, tile_pitch, score_pitch, dw, dh, P.min_th);
+        n = nc <= FAST_CLIST ? fast_nms_sparse(s, score_pitch, nc, xadd, yadd, slot)
+                             : fast_nms_emit(s, score_pitch, dw, dh, dw_inv, xadd, yadd, slot);
     }
     if (lane == 0) *cnt_out = (uint32_t)n;
 }
 
 void orbx_fast_smem_layout(const OrbxPlan& P, int* tile_pitch, int* score_pitch, int* warp_bytes) {
-    // tile rows hold up to max_tile_w + 3 (alignment slack) bytes, rounded to words
-    *tile_pitch = ((P.max_tile_w + 3 + 3) / 4) * 4;
+    // tile rows hold up to max_tile_w + 3 (alignment slack) bytes plus the 8-byte pair / +-1 word
+    // reach of the rejection test, rounded to 8 bytes
+    *tile_pitch = ((P.max_tile_w + 3 + 7) / 8) * 8;
     *score_pitch = ((P.max_tile_w - 6 + 2 + 3) / 4) * 4;
-    int bytes = 128 + *tile_pitch * P.max_tile_h + *score_pitch * (P.max_tile_h - 6 + 2);
+    // one spare tile row: the test may read the word after the last staged one
+    int bytes = 2 * (FAST_Q + FAST_CLIST) + *tile_pitch * (P.max_tile_h + 1) +
+                *score_pitch * (P.max_tile_h - 6 + 2);
     *warp_bytes = (bytes + 15) & ~15;
 }
 
