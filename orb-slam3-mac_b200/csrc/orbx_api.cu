@@ -255,6 +255,14 @@ int build_plan(const orbx_handle* h, int w, int hgt, OrbxPlan* out, std::vector<
             L.xa = (const short*)put(xa.data(), xa.size() * 2);
             L.yofs = (const uint16_t*)put(yo.data(), yo.size() * 2);
             L.ya = (const short*)put(ya.data(), ya.size() * 2);
+            std::vector<uint32_t> yt((size_t)2 * L.h);
+            for (int y = 0; y < L.h; ++y) {
+                yt[2 * y] = yo[y];
+                yt[2 * y + 1] = (uint32_t)(uint16_t)ya[2 * y] | ((uint32_t)(uint16_t)ya[2 * y + 1] << 16);
+            }
+            L.ytab = (const uint2*)put(yt.data(), yt.size() * 4);
+            L.x_step_max = 0;
+            for (int x = 0; x + 1 < L.w; ++x) L.x_step_max = std::max(L.x_step_max, (int)xo[x + 1] - (int)xo[x]);
         }
     }
     P.frame_stride = std::max(off, 256ll);
@@ -273,6 +281,7 @@ void patch_tables(OrbxPlan& P, uint8_t* dev_base) {
         L.xa = (const short*)(dev_base + (size_t)L.xa);
         L.yofs = (const uint16_t*)(dev_base + (size_t)L.yofs);
         L.ya = (const short*)(dev_base + (size_t)L.ya);
+        L.ytab = (const uint2*)(dev_base + (size_t)L.ytab);
     }
 }
 

@@ -21,6 +21,7 @@
 #define ORBX_INTERNAL_H
 
 #include <stdint.h>
+#include <vector_types.h>
 
 #include "../../include/orbx.h"
 
@@ -57,6 +58,9 @@ struct OrbxLevel {
     const short* xa;       // [2*w] 11-bit coefficients (a0, a1) interleaved
     const uint16_t* yofs;  // [h]
     const short* ya;       // [2*h]
+    const uint2* ytab;     // [h]  {yofs, b0 | b1 << 16}: one 8-byte load per output row
+    int x_step_max;        // max over x of xofs[x+1] - xofs[x] (the fast kernel needs <= 3)
+    int _pad1;
     float scale;         // mvScaleFactor[l]
     float size;          // (int)(31 * mvScaleFactor[l]) as float
 };
