@@ -28,12 +28,15 @@
 #define FAST_WARPS 8
 #define FAST_Q 512       // ring of queued pixels (u16): <= 31 left over + 256 pushed per step
 #define FAST_CLIST 256   // corners kept for the sparse NMS pass
+#define FAST_HDR_BYTES (2 * (FAST_Q + FAST_CLIST) + 4 * FAST_WQ)
+#define FAST_WQ 64       // ring of flagged 8-pixel words (u32): <= 31 left over + 32 pushed per step
 
 struct FastWarpSmem {
     uint8_t* tile;    // tile_pitch * tile_h, rows 8-byte aligned
     uint8_t* score;   // score_pitch * (dh + 2), 1-px zero frame around the detection region
     uint16_t* queue;  // FAST_Q entries: (tile row << 7) | tile byte column
     uint16_t* clist;  // FAST_CLIST entries, same encoding
+    uint32_t* wq;     // FAST_WQ entries: ((row << 7 | pair * 8) << 8) | 8-bit pass mask
     int xo;           // tile byte column of tile x = 0 (alignment slack of the staged words)
 };
 
@@ -101,6 +104,33 @@ __device__ __forceinline__ uint32_t fast_gt4(uint32_t d, uint32_t K4) {
     return ((d >> 1) & 0x7f7f7f7fu) + K4;
 }
 
+// q = x / d for 0 <= x < 64, 1 <= d <= 32 without an integer division: M = 2^16/d rounded up
+// (MUFU.RCP), exact because x * d * (M - 2^16/d) < 2^16.
+__device__ __forceinline__ uint32_t fast_small_inv(int d) {
+    return (uint32_t)(__frcp_ru((float)d) * 65536.f) + 1u;
+}
+__device__ __forceinline__ int fast_small_div(int x, uint32_t inv) { return (int)(((uint32_t)x * inv) >> 16); }
+
+// Moves up to 32 word entries {row, pair, 8-bit pass mask} of the word ring into the pixel ring,
+// one entry per lane, pixels in raster order (warp scan of the popcounts).
+__device__ __forceinline__ int fast_expand(const FastWarpSmem& s, int wh, int take, int qtail) {
+    const int lane = orbx_lane();
+    uint32_t e = 0;
+    if (lane < take) e = s.wq[(wh + lane) & (FAST_WQ - 1)];
+    uint32_t nib = e & 0xffu;
+    const uint32_t cnt = __popc(nib);
+    const uint32_t incl = warp_incl_scan(cnt);
+    int at = qtail + (int)(incl - cnt);
+    const int ebase = (int)(e >> 8);  // (row << 7) | (pair * 8)
+    while (nib) {
+        const int k = __ffs(nib) - 1;
+        nib &= nib - 1;
+        s.queue[at & (FAST_Q - 1)] = (uint16_t)(ebase + k);
+        ++at;
+    }
+    return (int)__shfl_sync(ORBX_FULL, incl, 31);
+}
+
 // Computes the score map for threshold `th` (s = raw-1 stored where raw > th, else 0 kept) and
 // the raster-ordered corner list.  Returns the number of corners (may exceed FAST_CLIST).
 __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp, int dw, int dh, int th) {
@@ -108,63 +138,78 @@ __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp
     // detection bytes of a tile row: [b0, b1]; 8-byte pairs [plo, phi]
     const int b0 = s.xo + 3, b1 = s.xo + 2 + dw;
     const int plo = b0 >> 3, npair = (b1 >> 3) - plo + 1;
-    const int rpi = 32 / npair;              // rows per step
-    const int ro = lane / npair, pc = plo + (lane - ro * npair);
+    const uint32_t inv = fast_small_inv(npair);
+    const int rpi = fast_small_div(32, inv);   // rows per step
+    const int ro = fast_small_div(lane, inv), pc = plo + (lane - ro * npair);
     const bool active = ro < rpi;
-    // valid-byte masks (bit 7 of each detection byte) of this lane's pair
-    uint32_t vlo = 0, vhi = 0;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const int ba = pc * 8 + k, bb = pc * 8 + 4 + k;
-        if (ba >= b0 && ba <= b1) vlo |= 0x80u << (8 * k);
-        if (bb >= b0 && bb <= b1) vhi |= 0x80u << (8 * k);
+    // valid-byte mask (bit 7 of each detection byte) of this lane's pair
+    uint32_t vlo, vhi;
+    {
+        const int lo = max(b0 - pc * 8, 0), hi = min(b1 - pc * 8, 7);  // valid bytes [lo, hi]
+        unsigned long long m = 0x8080808080808080ull;
+        m = (m >> (8 * lo)) << (8 * lo);
+        m = (m << (8 * (7 - hi))) >> (8 * (7 - hi));
+        vlo = (uint32_t)m;
+        vhi = (uint32_t)(m >> 32);
     }
     const uint32_t K4 = (uint32_t)(128 - ((th + 1) >> 1)) * 0x01010101u;
-    int qhead = 0, qn = 0, ncorn = 0;
-    for (int rb = 3; rb < 3 + dh; rb += rpi) {
-        const int r = rb + ro;
+    int qhead = 0, qn = 0, wh = 0, wn = 0, ncorn = 0;
+    const uint8_t* row = s.tile + (3 + ro) * tp + pc * 8;
+    const int rstep = rpi * tp;
+    const int rend = 3 + dh;
+    for (int r = 3 + ro; r < rend + ro; r += rpi, row += rstep) {   // r - ro is warp-uniform
         uint32_t flo = 0, fhi = 0;
-        if (active && r < 3 + dh) {
-            const uint8_t* row = s.tile + r * tp + pc * 8;
+        if (active && r < rend) {
             const uint2 c = *reinterpret_cast<const uint2*>(row);
             const uint2 up = *reinterpret_cast<const uint2*>(row - 3 * tp);
             const uint2 dn = *reinterpret_cast<const uint2*>(row + 3 * tp);
             const uint32_t l1 = *reinterpret_cast<const uint32_t*>(row - 4);
             const uint32_t r1 = *reinterpret_cast<const uint32_t*>(row + 8);
             // pixels x-3 and x+3 of the eight centres
-            const uint32_t wl = __funnelshift_r(l1, c.x, 8), wh = __funnelshift_r(c.x, c.y, 8);
+            const uint32_t wl = __funnelshift_r(l1, c.x, 8), wh_ = __funnelshift_r(c.x, c.y, 8);
             const uint32_t el = __funnelshift_r(c.x, c.y, 24), eh = __funnelshift_r(c.y, r1, 24);
             const uint32_t v_lo = fast_gt4(__vabsdiffu4(up.x, c.x), K4) | fast_gt4(__vabsdiffu4(dn.x, c.x), K4);
             const uint32_t h_lo = fast_gt4(__vabsdiffu4(wl, c.x), K4) | fast_gt4(__vabsdiffu4(el, c.x), K4);
             const uint32_t v_hi = fast_gt4(__vabsdiffu4(up.y, c.y), K4) | fast_gt4(__vabsdiffu4(dn.y, c.y), K4);
-            const uint32_t h_hi = fast_gt4(__vabsdiffu4(wh, c.y), K4) | fast_gt4(__vabsdiffu4(eh, c.y), K4);
+            const uint32_t h_hi = fast_gt4(__vabsdiffu4(wh_, c.y), K4) | fast_gt4(__vabsdiffu4(eh, c.y), K4);
             flo = v_lo & h_lo & vlo;
             fhi = v_hi & h_hi & vhi;
         }
-        // 8-bit pass mask of this lane (bit k = pixel k of the pair), ranks by warp scan
-        uint32_t nib = (((flo >> 7) * 0x00204081u) >> 21 & 0xfu) | ((((fhi >> 7) * 0x00204081u) >> 21 & 0xfu) << 4);
-        const uint32_t cnt = __popc(nib);
-        const uint32_t incl = warp_incl_scan(cnt);
-        const int total = (int)__shfl_sync(ORBX_FULL, incl, 31);
-        if (total) {
-            int at = qhead + qn + (int)(incl - cnt);
-            const int ebase = (r << 7) | (pc * 8);
-            while (nib) {
-                const int k = __ffs(nib) - 1;
-                nib &= nib - 1;
-                s.queue[at & (FAST_Q - 1)] = (uint16_t)(ebase + k);
-                ++at;
+        // push the lane's word entry (bit k of the mask = pixel k of the pair); flags sit in bit
+        // 7 of each byte: one multiply gathers them into the top nibble
+        const bool has = (flo | fhi) != 0;
+        const uint32_t bal = __ballot_sync(ORBX_FULL, has);
+        if (bal) {
+            if (has) {
+                const uint32_t nib = ((flo * 0x00204081u) >> 28) | (((fhi * 0x00204081u) >> 24) & 0xf0u);
+                s.wq[(wh + wn + __popc(bal & orbx_lanemask_lt())) & (FAST_WQ - 1)] =
+                    ((uint32_t)((r << 7) | (pc * 8)) << 8) | nib;
             }
-            qn += total;
+            wn += __popc(bal);
             __syncwarp();
-            while (qn >= 32) {
-                fast_drain(s, tp, sp, th, qhead, 32, ncorn);
-                qhead = (qhead + 32) & (FAST_Q - 1);
-                qn -= 32;
+            if (wn >= 32) {
+                qn += fast_expand(s, wh, 32, qhead + qn);
+                wh = (wh + 32) & (FAST_WQ - 1);
+                wn -= 32;
+                __syncwarp();
+                while (qn >= 32) {
+                    fast_drain(s, tp, sp, th, qhead, 32, ncorn);
+                    qhead = (qhead + 32) & (FAST_Q - 1);
+                    qn -= 32;
+                }
             }
         }
     }
-    if (qn > 0) fast_drain(s, tp, sp, th, qhead, qn, ncorn);
+    if (wn > 0) {
+        qn += fast_expand(s, wh, wn, qhead + qn);
+        __syncwarp();
+    }
+    while (qn > 0) {
+        const int take = min(qn, 32);
+        fast_drain(s, tp, sp, th, qhead, take, ncorn);
+        qhead = (qhead + take) & (FAST_Q - 1);
+        qn -= take;
+    }
     __syncwarp();
     return ncorn;
 }
@@ -256,7 +301,8 @@ k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8
     uint8_t* base = smem + (size_t)warp * warp_smem_bytes;
     s.queue = reinterpret_cast<uint16_t*>(base);
     s.clist = s.queue + FAST_Q;
-    s.tile = base + 2 * (FAST_Q + FAST_CLIST);
+    s.wq = reinterpret_cast<uint32_t*>(base + 2 * (FAST_Q + FAST_CLIST));
+    s.tile = base + FAST_HDR_BYTES;
     s.score = s.tile + tile_pitch * (P.max_tile_h + 1);
 
     // 1. stage the tile: aligned words covering [iniX & ~3, maxX); lane -> (row offset, word)
@@ -307,7 +353,7 @@ void orbx_fast_smem_layout(const OrbxPlan& P, int* tile_pitch, int* score_pitch,
     *tile_pitch = ((P.max_tile_w + 3 + 7) / 8) * 8;
     *score_pitch = ((P.max_tile_w - 6 + 2 + 3) / 4) * 4;
     // one spare tile row: the test may read the word after the last staged one
-    int bytes = 2 * (FAST_Q + FAST_CLIST) + *tile_pitch * (P.max_tile_h + 1) +
+    int bytes = FAST_HDR_BYTES + *tile_pitch * (P.max_tile_h + 1) +
                 *score_pitch * (P.max_tile_h - 6 + 2);
     *warp_bytes = (bytes + 15) & ~15;
 }

@@ -58,101 +58,142 @@ k_resize_level(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, int level
 
 #define RZ_ROWS 16
 
-// Horizontal pass of one source row for the thread's 4 columns, pre-shifted by 4 (VResizeLinear
-// works on H >> 4).
-__device__ __forceinline__ void rz_hrow(const uint32_t* __restrict__ row, int wa0, int wa1, int wb0,
-                                        int wb1, const uint32_t (&sel)[4], const uint32_t (&cf)[4],
-                                        uint32_t (&H)[4]) {
-    const uint32_t A0 = __ldg(row + wa0), A1 = __ldg(row + wa1);
-    const uint32_t B0 = __ldg(row + wb0), B1 = __ldg(row + wb1);
-    H[0] = __dp2a_lo(cf[0], __byte_perm(A0, A1, sel[0]), 0u) >> 4;
-    H[1] = __dp2a_lo(cf[1], __byte_perm(A0, A1, sel[1]), 0u) >> 4;
-    H[2] = __dp2a_lo(cf[2], __byte_perm(B0, B1, sel[2]), 0u) >> 4;
-    H[3] = __dp2a_lo(cf[3], __byte_perm(B0, B1, sel[3]), 0u) >> 4;
+// Everything k_resize_rows needs about one (source level -> destination level) step, as plain
+// kernel-parameter scalars (constant-bank operands; no indexed loads from the plan).
+struct RzArgs {
+    const uint8_t* src;      // source level of frame 0
+    uint8_t* dst;            // destination level of frame 0
+    long long src_fstride;   // bytes between frames
+    long long dst_fstride;
+    const uint16_t* xofs;    // [dw]
+    const uint32_t* xa;      // [dw] a0 | a1 << 16
+    const uint2* ytab;       // [dh] {s0, b0 | b1 << 16}, bottom source row = s0 + 1
+    int spitch, dpitch;
+    int sw, sh, dw, dh;
+    int warps_x, nbands;
+};
+
+// Horizontal pass of one source row for the thread's 4 columns from its 4 loaded words,
+// pre-shifted by 4 (VResizeLinear works on H >> 4).
+__device__ __forceinline__ void rz_hrow(const uint32_t (&W)[4], const uint32_t (&sel)[4],
+                                        const uint32_t (&cf)[4], uint32_t (&H)[4]) {
+    H[0] = __dp2a_lo(cf[0], __byte_perm(W[0], W[1], sel[0]), 0u) >> 4;
+    H[1] = __dp2a_lo(cf[1], __byte_perm(W[0], W[1], sel[1]), 0u) >> 4;
+    H[2] = __dp2a_lo(cf[2], __byte_perm(W[2], W[3], sel[2]), 0u) >> 4;
+    H[3] = __dp2a_lo(cf[3], __byte_perm(W[2], W[3], sel[3]), 0u) >> 4;
+}
+
+// One output row: dst = ((b0*T>>16) + (b1*B>>16) + 2) >> 2 for the 4 columns, one 32-bit store.
+__device__ __forceinline__ void rz_emit(uint8_t* drow, uint32_t bw, const uint32_t (&T)[4],
+                                        const uint32_t (&B)[4]) {
+    const uint32_t b0 = bw << 16, b1 = bw & 0xffff0000u;
+    uint32_t t[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) t[k] = __umulhi(b0, T[k]) + (__umulhi(b1, B[k]) + 2u);
+    const uint32_t t01 = __byte_perm(t[0], t[1], 0x5410) >> 2;
+    const uint32_t t23 = __byte_perm(t[2], t[3], 0x5410) >> 2;
+    // pitch is a multiple of 16 and x0 of 4: the 32-bit store is aligned; bytes past w land in
+    // the row's padding.
+    *reinterpret_cast<uint32_t*>(drow) = __byte_perm(t01, t23, 0x6420);
 }
 
 __global__ void __launch_bounds__(256)
-k_resize_rows(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, int level, int warps_x,
-              int nbands, uint8_t* __restrict__ pyr) {
-    const OrbxLevel& D = P.lvl[level];
-    const OrbxLevel& S = P.lvl[level - 1];
+k_resize_rows(const __grid_constant__ RzArgs A) {
     const int gw = blockIdx.x * 8 + (threadIdx.x >> 5);   // warp -> (band, column chunk)
-    const int band = gw / warps_x, wx = gw - band * warps_x;
-    if (band >= nbands) return;
+    const int band = gw / A.warps_x, wx = gw - band * A.warps_x;
+    if (band >= A.nbands) return;
     const int x0 = (wx * 32 + (threadIdx.x & 31)) * 4;
-    if (x0 >= D.w) return;
-    int spitch;
-    const uint8_t* src = orbx_level_ptr(P, isrc, pyr, blockIdx.y, level - 1, &spitch);
-    uint8_t* dst = pyr + (size_t)blockIdx.y * P.frame_stride + D.off;
+    if (x0 >= A.dw) return;
 
     // per-thread column setup
     int sx[4];
     uint32_t cf[4], sel[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const int x = min(x0 + k, D.w - 1);
-        sx[k] = D.xofs[x];
-        cf[k] = reinterpret_cast<const uint32_t*>(D.xa)[x];  // a0 | a1 << 16
+        const int x = min(x0 + k, A.dw - 1);
+        sx[k] = A.xofs[x];
+        cf[k] = A.xa[x];  // a0 | a1 << 16
     }
-    const int wlast = (S.w - 1) >> 2;  // last source word holding valid bytes
-    const int wa0 = sx[0] >> 2, wa1 = min(wa0 + 1, wlast);
-    const int wb0 = sx[2] >> 2, wb1 = min(wb0 + 1, wlast);
+    // Word pair (w, w+1) of each pixel pair, kept inside the row's valid words; S[sx] sits at byte
+    // offset o <= 7 of the pair and S[sx+1] at o+1 (x_step_max <= 3 is checked by the launcher).
+    // o+1 == 8 only happens for sx == sw-1, whose second coefficient is 0.
+    const int wlast = (A.sw - 1) >> 2;
+    const int wa = min(sx[0] >> 2, wlast - 1), wb = min(sx[2] >> 2, wlast - 1);
     {
-        // byte offsets of S[sx] inside its word pair; S[sx+1] is the next byte (offset <= 6:
-        // x_step_max <= 3 is checked by the launcher).  A clamped upper word is only ever read
-        // for a byte whose coefficient is 0 (sx = S.w - 1).
-        const int o0 = sx[0] - 4 * wa0, o1 = sx[1] - 4 * wa0, o2 = sx[2] - 4 * wb0, o3 = sx[3] - 4 * wb0;
-        sel[0] = (uint32_t)o0 | ((uint32_t)(o0 + 1) << 4);
-        sel[1] = (uint32_t)o1 | ((uint32_t)(o1 + 1) << 4);
-        sel[2] = (uint32_t)o2 | ((uint32_t)(o2 + 1) << 4);
-        sel[3] = (uint32_t)o3 | ((uint32_t)(o3 + 1) << 4);
+        const int o0 = sx[0] - 4 * wa, o1 = sx[1] - 4 * wa, o2 = sx[2] - 4 * wb, o3 = sx[3] - 4 * wb;
+        sel[0] = (uint32_t)o0 | ((uint32_t)min(o0 + 1, 7) << 4);
+        sel[1] = (uint32_t)o1 | ((uint32_t)min(o1 + 1, 7) << 4);
+        sel[2] = (uint32_t)o2 | ((uint32_t)min(o2 + 1, 7) << 4);
+        sel[3] = (uint32_t)o3 | ((uint32_t)min(o3 + 1, 7) << 4);
     }
-    const int sp4 = spitch >> 2;
-    const uint32_t* src4 = reinterpret_cast<const uint32_t*>(src);
+    const int y0 = band * RZ_ROWS, y1 = min(y0 + RZ_ROWS, A.dh);
+    uint8_t* drow = A.dst + (size_t)blockIdx.y * A.dst_fstride + (size_t)y0 * A.dpitch + x0;
+    const uint2* yp = A.ytab + y0;
+    uint2 yt = __ldg(yp);
+    int y = y0;
+    // Source rows are visited once each, in increasing order, starting at an even row: even rows
+    // go through (W0 -> E), odd rows through (W1 -> O); two rows of loads are always in flight.
+    int s = (int)yt.x & ~1;
+    const uint8_t* sbase = A.src + (size_t)blockIdx.y * A.src_fstride;
+    const uint8_t* pa = sbase + 4 * wa;
+    const uint8_t* pb = sbase + 4 * wb;
+    uint32_t ro = (uint32_t)s * (uint32_t)A.spitch;             // byte offset of the row to load
+    const uint32_t ro_max = (uint32_t)(A.sh - 1) * (uint32_t)A.spitch;
 
-    const int y0 = band * RZ_ROWS, y1 = min(y0 + RZ_ROWS, D.h);
-    uint32_t HA[4], HB[4];
-    int ra = -1, rb = -1;  // source rows held in HA / HB
-    uint8_t* drow = dst + (size_t)y0 * D.pitch + x0;
-    for (int y = y0; y < y1; ++y, drow += D.pitch) {
-        const uint2 yt = __ldg(D.ytab + y);
-        const int s0 = (int)yt.x, s1 = min(s0 + 1, S.h - 1);
-        if (s0 != ra) {
-            if (s0 == rb) {
-#pragma unroll
-                for (int k = 0; k < 4; ++k) HA[k] = HB[k];
-            } else {
-                rz_hrow(src4 + (size_t)s0 * sp4, wa0, wa1, wb0, wb1, sel, cf, HA);
-            }
-            ra = s0;
-        }
-        if (s1 == ra) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) HB[k] = HA[k];
-            rb = ra;
-        } else if (s1 != rb) {
-            rz_hrow(src4 + (size_t)s1 * sp4, wa0, wa1, wb0, wb1, sel, cf, HB);
-            rb = s1;
-        }
-        const uint32_t b0 = yt.y << 16, b1 = yt.y & 0xffff0000u;
-        uint32_t t[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) t[k] = __umulhi(b0, HA[k]) + (__umulhi(b1, HB[k]) + 2u);
-        const uint32_t t01 = __byte_perm(t[0], t[1], 0x5410) >> 2;
-        const uint32_t t23 = __byte_perm(t[2], t[3], 0x5410) >> 2;
-        // pitch is a multiple of 16 and x0 of 4: the 32-bit store is aligned; bytes past w land
-        // in the row's padding.
-        *reinterpret_cast<uint32_t*>(drow) = __byte_perm(t01, t23, 0x6420);
+    uint32_t E[4], O[4], W0[4], W1[4];
+#define RZ_LOAD(W)                                                          \
+    {                                                                       \
+        const uint32_t* qa = reinterpret_cast<const uint32_t*>(pa + ro);    \
+        const uint32_t* qb = reinterpret_cast<const uint32_t*>(pb + ro);    \
+        W[0] = __ldg(qa); W[1] = __ldg(qa + 1);                             \
+        W[2] = __ldg(qb); W[3] = __ldg(qb + 1);                             \
+        ro = min(ro + (uint32_t)A.spitch, ro_max);                          \
     }
+    // After source row s is interpolated into CUR, the output row whose bottom source row is s
+    // (ytab: s0 + 1 == s; strictly increasing s0, checked by the launcher) is complete.
+#define RZ_STEP(CUR, PREV, W)                                               \
+    {                                                                       \
+        rz_hrow(W, sel, cf, CUR);                                           \
+        RZ_LOAD(W)                                                          \
+        if ((int)yt.x + 1 == s) {                                           \
+            rz_emit(drow, yt.y, PREV, CUR);                                 \
+            if (++y >= y1) break;                                           \
+            drow += A.dpitch;                                               \
+            yt = __ldg(++yp);                                               \
+        }                                                                   \
+        ++s;                                                                \
+    }
+    RZ_LOAD(W0)
+    RZ_LOAD(W1)
+#pragma unroll 1
+    while (s < A.sh) {   // the break above is the normal exit; this bound only guards bad tables
+        RZ_STEP(E, O, W0)
+        RZ_STEP(O, E, W1)
+    }
+#undef RZ_STEP
+#undef RZ_LOAD
 }
 
 void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes, cudaStream_t st, int* launches) {
     for (int l = 1; l < P.nlevels; ++l) {
         const OrbxLevel& D = P.lvl[l];
-        if (D.x_step_max <= 3) {
-            const int warps_x = (D.w + 127) / 128, nbands = (D.h + RZ_ROWS - 1) / RZ_ROWS;
-            dim3 grid((warps_x * nbands + 7) / 8, nframes);
-            k_resize_rows<<<grid, 256, 0, st>>>(P, src, l, warps_x, nbands, pyr);
+        const OrbxLevel& S = P.lvl[l - 1];
+        if (D.x_step_max <= 3 && D.y_monotone && S.w >= 8 && S.h >= 2) {
+            RzArgs A;
+            A.src = l == 1 ? src.img0 : pyr + S.off;
+            A.src_fstride = l == 1 ? src.stride0 : P.frame_stride;
+            A.spitch = l == 1 ? src.pitch0 : S.pitch;
+            A.dst = pyr + D.off;
+            A.dst_fstride = P.frame_stride;
+            A.dpitch = D.pitch;
+            A.xofs = D.xofs;
+            A.xa = reinterpret_cast<const uint32_t*>(D.xa);
+            A.ytab = D.ytab;
+            A.sw = S.w; A.sh = S.h; A.dw = D.w; A.dh = D.h;
+            A.warps_x = (D.w + 127) / 128;
+            A.nbands = (D.h + RZ_ROWS - 1) / RZ_ROWS;
+            dim3 grid((A.warps_x * A.nbands + 7) / 8, nframes);
+            k_resize_rows<<<grid, 256, 0, st>>>(A);
         } else {
             dim3 block(128);
             dim3 grid((D.w + 4 * 128 - 1) / (4 * 128), D.h, nframes);

@@ -256,9 +256,22 @@ int build_plan(const orbx_handle* h, int w, int hgt, OrbxPlan* out, std::vector<
             L.yofs = (const uint16_t*)put(yo.data(), yo.size() * 2);
             L.ya = (const short*)put(ya.data(), ya.size() * 2);
             std::vector<uint32_t> yt((size_t)2 * L.h);
+            // Row table of the walking kernel: {s0, b0 | b1 << 16}.  A row clamped to the last
+            // source row (s0 == s1 == sh-1, b1 == 0) is re-expressed as top = sh-2 with weight 0,
+            // bottom = sh-1 with weight b0: the same value, and "bottom row = s0 + 1" always holds.
+            const int sh_last = P.lvl[l - 1].h - 1;
+            L.y_monotone = 1;
             for (int y = 0; y < L.h; ++y) {
-                yt[2 * y] = yo[y];
-                yt[2 * y + 1] = (uint32_t)(uint16_t)ya[2 * y] | ((uint32_t)(uint16_t)ya[2 * y + 1] << 16);
+                int s0 = yo[y];
+                uint32_t b0 = (uint16_t)ya[2 * y], b1 = (uint16_t)ya[2 * y + 1];
+                if (s0 >= sh_last && sh_last >= 1) {
+                    s0 = sh_last - 1;
+                    b1 = b0;
+                    b0 = 0;
+                }
+                yt[2 * y] = (uint32_t)s0;
+                yt[2 * y + 1] = b0 | (b1 << 16);
+                if (y > 0 && yt[2 * y] <= yt[2 * (y - 1)]) L.y_monotone = 0;
             }
             L.ytab = (const uint2*)put(yt.data(), yt.size() * 4);
             L.x_step_max = 0;

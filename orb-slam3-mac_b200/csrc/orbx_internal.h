@@ -60,7 +60,7 @@ struct OrbxLevel {
     const short* ya;       // [2*h]
     const uint2* ytab;     // [h]  {yofs, b0 | b1 << 16}: one 8-byte load per output row
     int x_step_max;        // max over x of xofs[x+1] - xofs[x] (the fast kernel needs <= 3)
-    int _pad1;
+    int y_monotone;        // 1 if ytab's source rows strictly increase (the fast kernel needs it)
     float scale;         // mvScaleFactor[l]
     float size;          // (int)(31 * mvScaleFactor[l]) as float
 };
