@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "liborbx_b200.so")
+# ORBX_B200_LIB: developer override used for A/B runs of kernel variants (same ABI)
+LIB_PATH = os.environ.get("ORBX_B200_LIB") or os.path.join(HERE, "liborbx_b200.so")
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])

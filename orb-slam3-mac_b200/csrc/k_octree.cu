@@ -20,7 +20,12 @@
 // Small nodes are partitioned one per warp, nodes with >= OCT_BIG keys by the whole CTA.
 #include "orbx_device.cuh"
 
-#define OCT_THREADS 512
+#ifndef OCT_THREADS
+#define OCT_THREADS 256
+#endif
+#ifndef OCT_SMEM_KB
+#define OCT_SMEM_KB 36
+#endif
 #define OCT_WARPS (OCT_THREADS / 32)
 #define OCT_BIG 1024
 #define OCT_MAX_INI 8
@@ -470,8 +475,8 @@ OctLaunchCfg orbx_octree_cfg(const OrbxPlan& P) {
     while (c.NCP2 < nc) c.NCP2 <<= 1;
     c.CW = 4 * nc > cells + 2 ? 4 * nc : cells + 2;
     const size_t fixed = oct_fixed_words(c.NC, c.NCP2, c.CW) * 4;
-    // key buffers: as much shared memory as keeps >= 2 CTAs per SM, capped by the worst case
-    size_t budget = 100 * 1024;
+    // key buffers: sized so that 5 CTAs fit an SM (larger levels spill to the HBM ping-pong buffers), capped by the worst case
+    size_t budget = OCT_SMEM_KB * 1024;
     long long kw = budget > fixed ? (long long)((budget - fixed) / 8) : 0;
     if (kw > kmax) kw = kmax;
     kw &= ~3ll;

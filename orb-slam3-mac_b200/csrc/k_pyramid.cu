@@ -174,6 +174,117 @@ k_resize_rows(const __grid_constant__ RzArgs A) {
 #undef RZ_LOAD
 }
 
+// ---- cp.async-staged variant ------------------------------------------------------------------
+// Same arithmetic and walk as k_resize_rows, but the source rows a warp needs (its 128 output
+// columns = <= 256 source bytes) are streamed into a per-warp shared-memory ring by 16-byte
+// cp.async.cg copies, RZ_DEPTH rows ahead of their use, so that DRAM latency is covered by ~1.5 KB
+// of loads in flight per warp instead of two dependent row loads.  Needs 16-byte aligned source
+// rows (always true for pyramid levels; level 0 when the caller's pitch allows it).
+#define RZ_DEPTH 8
+#define RZ_SLOT_WORDS 64   // 256 B per staged row segment
+
+__device__ __forceinline__ void rz_cp16(uint32_t saddr, const void* g) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void rz_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void rz_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__global__ void __launch_bounds__(256)
+k_resize_rows_async(const __grid_constant__ RzArgs A) {
+    __shared__ __align__(16) uint32_t ring_all[8 * RZ_DEPTH * RZ_SLOT_WORDS];
+    const int lane = threadIdx.x & 31;
+    const int gw = blockIdx.x * 8 + (threadIdx.x >> 5);   // warp -> (band, column chunk)
+    const int band = gw / A.warps_x, wx = gw - band * A.warps_x;
+    if (band >= A.nbands) return;
+    uint32_t* ring = ring_all + (threadIdx.x >> 5) * (RZ_DEPTH * RZ_SLOT_WORDS);
+    const int x0 = (wx * 32 + lane) * 4;
+    const bool live = x0 < A.dw;              // dead lanes still help with the copies
+    const int xc = live ? x0 : ((A.dw - 1) & ~3);
+
+    int sx[4];
+    uint32_t cf[4], sel[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int x = min(xc + k, A.dw - 1);
+        sx[k] = A.xofs[x];
+        cf[k] = A.xa[x];
+    }
+    const int wlast = (A.sw - 1) >> 2;
+    int wa = min(sx[0] >> 2, wlast - 1), wb = min(sx[2] >> 2, wlast - 1);
+    {
+        const int o0 = sx[0] - 4 * wa, o1 = sx[1] - 4 * wa, o2 = sx[2] - 4 * wb, o3 = sx[3] - 4 * wb;
+        sel[0] = (uint32_t)o0 | ((uint32_t)min(o0 + 1, 7) << 4);
+        sel[1] = (uint32_t)o1 | ((uint32_t)min(o1 + 1, 7) << 4);
+        sel[2] = (uint32_t)o2 | ((uint32_t)min(o2 + 1, 7) << 4);
+        sel[3] = (uint32_t)o3 | ((uint32_t)min(o3 + 1, 7) << 4);
+    }
+    // staged segment of a source row: 16-byte chunks [c0, c0 + nchunk) covering every lane's words
+    const int w_first = __shfl_sync(ORBX_FULL, wa, 0) & ~3;
+    const int w_end = __reduce_max_sync(ORBX_FULL, wb + 2);       // one past the last word needed
+    const int nchunk = min((w_end - w_first + 3) >> 2, RZ_SLOT_WORDS / 4);
+    wa -= w_first;
+    wb -= w_first;
+
+    const int y0 = band * RZ_ROWS, y1 = min(y0 + RZ_ROWS, A.dh);
+    uint8_t* drow = A.dst + (size_t)blockIdx.y * A.dst_fstride + (size_t)y0 * A.dpitch + xc;
+    const uint2* yp = A.ytab + y0;
+    uint2 yt = __ldg(yp);
+    int y = y0;
+    int s = (int)yt.x & ~1;
+    const uint8_t* gsrc = A.src + (size_t)blockIdx.y * A.src_fstride + 4 * (size_t)w_first + 16 * lane;
+    uint32_t ro = (uint32_t)s * (uint32_t)A.spitch;
+    const uint32_t ro_max = (uint32_t)(A.sh - 1) * (uint32_t)A.spitch;
+    const uint32_t ring_sa = (uint32_t)__cvta_generic_to_shared(ring);
+    const uint32_t cp_sa = ring_sa + 16 * lane;          // this lane's 16-byte chunk of slot 0
+    const uint32_t wa_sa = ring_sa + 4 * wa, wb_sa = ring_sa + 4 * wb;
+    const bool copier = lane < nchunk;
+    uint32_t ioff = (uint32_t)(s & (RZ_DEPTH - 1)) * (RZ_SLOT_WORDS * 4);  // slot being staged
+    uint32_t soff = ioff;                                                  // slot being consumed
+    const uint32_t ring_mask = (RZ_DEPTH - 1) * (RZ_SLOT_WORDS * 4);
+
+#define RZ_ISSUE()                                                                          \
+    {                                                                                       \
+        if (copier) rz_cp16(cp_sa + ioff, gsrc + ro);                                       \
+        rz_commit();                                                                        \
+        ro = min(ro + (uint32_t)A.spitch, ro_max);                                          \
+        ioff = (ioff + RZ_SLOT_WORDS * 4) & ring_mask;                                      \
+    }
+#pragma unroll
+    for (int i = 0; i < RZ_DEPTH - 1; ++i) RZ_ISSUE()
+
+    uint32_t E[4], O[4], W[4];
+#define RZ_LDS(dst, addr) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(dst) : "r"(addr))
+#define RZ_STEP(CUR, PREV)                                                                  \
+    {                                                                                       \
+        rz_wait<RZ_DEPTH - 2>();                                                            \
+        __syncwarp();                                                                       \
+        RZ_LDS(W[0], wa_sa + soff);                                                         \
+        RZ_LDS(W[1], wa_sa + soff + 4);                                                     \
+        RZ_LDS(W[2], wb_sa + soff);                                                         \
+        RZ_LDS(W[3], wb_sa + soff + 4);                                                     \
+        soff = (soff + RZ_SLOT_WORDS * 4) & ring_mask;                                      \
+        RZ_ISSUE()                                                                          \
+        rz_hrow(W, sel, cf, CUR);                                                           \
+        if ((int)yt.x + 1 == s) {                                                           \
+            if (live) rz_emit(drow, yt.y, PREV, CUR);                                       \
+            if (++y >= y1) break;                                                           \
+            drow += A.dpitch;                                                               \
+            yt = __ldg(++yp);                                                               \
+        }                                                                                   \
+        ++s;                                                                                \
+    }
+#pragma unroll 1
+    while (s < A.sh) {
+        RZ_STEP(E, O)
+        RZ_STEP(O, E)
+    }
+#undef RZ_LDS
+#undef RZ_STEP
+#undef RZ_ISSUE
+    rz_wait<0>();
+}
+
 void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes, cudaStream_t st, int* launches) {
     for (int l = 1; l < P.nlevels; ++l) {
         const OrbxLevel& D = P.lvl[l];
@@ -193,7 +304,11 @@ void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, in
             A.warps_x = (D.w + 127) / 128;
             A.nbands = (D.h + RZ_ROWS - 1) / RZ_ROWS;
             dim3 grid((A.warps_x * A.nbands + 7) / 8, nframes);
-            k_resize_rows<<<grid, 256, 0, st>>>(A);
+            const bool aligned = ((uintptr_t)A.src % 16 == 0) && (A.spitch % 16 == 0) && (A.src_fstride % 16 == 0);
+            if (aligned && D.x_step_max <= 2 && (double)S.w / D.w <= 1.7)
+                k_resize_rows_async<<<grid, 256, 0, st>>>(A);
+            else
+                k_resize_rows<<<grid, 256, 0, st>>>(A);
         } else {
             dim3 block(128);
             dim3 grid((D.w + 4 * 128 - 1) / (4 * 128), D.h, nframes);
