@@ -23,7 +23,9 @@
 //                produces descriptor byte i.
 #include "orbx_device.cuh"
 
-#define DESC_WARPS 8
+#ifndef DESC_WARPS
+#define DESC_WARPS 4
+#endif
 #define DESC_SP 13                       // words per staged row (52 B; odd -> conflict-free rows)
 #define DESC_HP 22                       // words per H row (40 u16 + pad; even: 8-byte rows)
 #define DESC_BP 10                       // words per blurred row (40 B)
@@ -125,10 +127,12 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
     const int warp = orbx_warp(), lane = orbx_lane();
     {
         // pattern points 16*lane + 2k, 16*lane + 2k + 1 = one aligned word of the int8 table
-        const int e = threadIdx.x, k = e >> 5, i = e & 31;
-        const uint32_t w = reinterpret_cast<const uint32_t*>(g_pattern)[8 * i + k];
-        pat4[e] = make_float4((float)(int8_t)(w & 0xff), (float)(int8_t)((w >> 8) & 0xff),
-                              (float)(int8_t)((w >> 16) & 0xff), (float)(int8_t)(w >> 24));
+        for (int e = threadIdx.x; e < 256; e += DESC_WARPS * 32) {
+            const int k = e >> 5, i = e & 31;
+            const uint32_t w = reinterpret_cast<const uint32_t*>(g_pattern)[8 * i + k];
+            pat4[e] = make_float4((float)(int8_t)(w & 0xff), (float)(int8_t)((w >> 8) & 0xff),
+                                  (float)(int8_t)((w >> 16) & 0xff), (float)(int8_t)(w >> 24));
+        }
     }
     __syncthreads();
     const int frame = blockIdx.y;

@@ -25,7 +25,9 @@
 // needs to reproduce the reference's first-maximum-wins choice.
 #include "orbx_device.cuh"
 
-#define FAST_WARPS 8
+#ifndef FAST_WARPS
+#define FAST_WARPS 4
+#endif
 #define FAST_Q 512       // ring of queued pixels (u16): <= 31 left over + 256 pushed per step
 #define FAST_CLIST 256   // corners kept for the sparse NMS pass
 #define FAST_HDR_BYTES (2 * (FAST_Q + FAST_CLIST) + 4 * FAST_WQ)
@@ -244,6 +246,7 @@ __device__ __forceinline__ int fast_nms_emit(const FastWarpSmem& s, int sp, int 
                                              uint32_t* __restrict__ slot) {
     const int lane = orbx_lane();
     const int npix = dw * dh;
+    dw_inv = (1u << 20) / (uint32_t)dw + 1;
     int count = 0;
     for (int base = 0; base < npix; base += 32) {
         const int p = base + lane;
@@ -266,7 +269,10 @@ __device__ __forceinline__ int fast_nms_emit(const FastWarpSmem& s, int sp, int 
     return count;
 }
 
-__global__ void __launch_bounds__(FAST_WARPS * 32)
+#ifndef FAST_MINB
+#define FAST_MINB 10
+#endif
+__global__ void __launch_bounds__(FAST_WARPS * 32, FAST_MINB)
 k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t* __restrict__ pyr,
              uint32_t* __restrict__ cellcnt, uint32_t* __restrict__ cellkeys, int tile_pitch,
              int score_pitch, int warp_smem_bytes) {
@@ -280,7 +286,7 @@ k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8
     while (l + 1 < P.nlevels && g >= P.lvl[l + 1].cell_off) ++l;
     const OrbxLevel& L = P.lvl[l];
     const int c = g - L.cell_off;
-    const int ci = c / L.n_cols, cj = c - ci * L.n_cols;
+    const int ci = L.n_cols_inv ? (int)__umulhi((uint32_t)c, L.n_cols_inv) : c, cj = c - ci * L.n_cols;
 
     uint32_t* cnt_out = cellcnt + (size_t)frame * P.cells_total + g;
     uint32_t* slot = cellkeys + (size_t)frame * P.keys_total + L.key_off + (size_t)c * L.cell_cap;
@@ -303,7 +309,7 @@ k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8
     s.clist = s.queue + FAST_Q;
     s.wq = reinterpret_cast<uint32_t*>(base + 2 * (FAST_Q + FAST_CLIST));
     s.tile = base + FAST_HDR_BYTES;
-    s.score = s.tile + tile_pitch * (P.max_tile_h + 1);
+    s.score = s.tile + ((tile_pitch * (P.max_tile_h + 1) + 15) & ~15);
 
     // 1. stage the tile: aligned words covering [iniX & ~3, maxX); lane -> (row offset, word)
     int lpitch;
@@ -312,27 +318,32 @@ k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8
     s.xo = iniX - ax;  // tile x -> smem byte x + xo
     {
         const int nw = (maxX - ax + 3) >> 2;   // <= tile_pitch / 4 <= 21
-        const int rpi = 32 / nw;
-        const int ro = lane / nw, cw = lane - ro * nw;
+        const uint32_t inv = fast_small_inv(nw);
+        const int rpi = fast_small_div(32, inv);
+        const int ro = fast_small_div(lane, inv), cw = lane - ro * nw;
         if (ro < rpi) {
-            const uint32_t* gp = reinterpret_cast<const uint32_t*>(src + (size_t)(iniY + ro) * lpitch + ax) + cw;
-            uint32_t* tp_ = reinterpret_cast<uint32_t*>(s.tile + ro * tile_pitch) + cw;
-            const size_t gstep = (size_t)rpi * lpitch / 4;
-            const int tstep = rpi * tile_pitch / 4;
+            const uint8_t* gp = src + (size_t)(iniY + ro) * lpitch + ax + 4 * cw;
+            uint32_t sa = (uint32_t)__cvta_generic_to_shared(s.tile + ro * tile_pitch + 4 * cw);
+            const size_t gstep = (size_t)rpi * lpitch;
+            const uint32_t tstep = (uint32_t)(rpi * tile_pitch);
+#pragma unroll 4
             for (int r = ro; r < th_; r += rpi) {
-                *tp_ = __ldg(gp);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(gp) : "memory");
                 gp += gstep;
-                tp_ += tstep;
+                sa += tstep;
             }
         }
     }
-    // zero the score map (frame included)
-    const int swords = (score_pitch * (dh + 2)) >> 2;
-    for (int i = lane; i < swords; i += 32) reinterpret_cast<uint32_t*>(s.score)[i] = 0;
+    // zero the score map (frame included; 16-byte stores, the region is padded to 16)
+    {
+        const int sq = (score_pitch * (dh + 2) + 15) >> 4;
+        for (int i = lane; i < sq; i += 32) reinterpret_cast<uint4*>(s.score)[i] = make_uint4(0, 0, 0, 0);
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
     __syncwarp();
 
     const int xadd = 3 + cj * L.w_cell, yadd = 3 + ci * L.h_cell;
-    const uint32_t dw_inv = (1u << 20) / (uint32_t)dw + 1;
+    const uint32_t dw_inv = 0;  // computed inside the (rare) dense NMS path
 
     int nc = fast_scores(s, tile_pitch, score_pitch, dw, dh, P.ini_th);
     int n = nc <= FAST_CLIST ? fast_nms_sparse(s, score_pitch, nc, xadd, yadd, slot)
@@ -353,8 +364,8 @@ void orbx_fast_smem_layout(const OrbxPlan& P, int* tile_pitch, int* score_pitch,
     *tile_pitch = ((P.max_tile_w + 3 + 7) / 8) * 8;
     *score_pitch = ((P.max_tile_w - 6 + 2 + 3) / 4) * 4;
     // one spare tile row: the test may read the word after the last staged one
-    int bytes = FAST_HDR_BYTES + *tile_pitch * (P.max_tile_h + 1) +
-                *score_pitch * (P.max_tile_h - 6 + 2);
+    int bytes = FAST_HDR_BYTES + ((*tile_pitch * (P.max_tile_h + 1) + 15) & ~15) +
+                ((*score_pitch * (P.max_tile_h - 6 + 2) + 15) & ~15);
     *warp_bytes = (bytes + 15) & ~15;
 }
 

@@ -56,7 +56,9 @@ k_resize_level(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, int level
     *reinterpret_cast<uint32_t*>(dst + (size_t)y * D.pitch + x0) = out;
 }
 
+#ifndef RZ_ROWS
 #define RZ_ROWS 16
+#endif
 
 // Everything k_resize_rows needs about one (source level -> destination level) step, as plain
 // kernel-parameter scalars (constant-bank operands; no indexed loads from the plan).
@@ -180,7 +182,9 @@ k_resize_rows(const __grid_constant__ RzArgs A) {
 // cp.async.cg copies, RZ_DEPTH rows ahead of their use, so that DRAM latency is covered by ~1.5 KB
 // of loads in flight per warp instead of two dependent row loads.  Needs 16-byte aligned source
 // rows (always true for pyramid levels; level 0 when the caller's pitch allows it).
-#define RZ_DEPTH 8
+#ifndef RZ_DEPTH
+#define RZ_DEPTH 4
+#endif
 #define RZ_SLOT_WORDS 64   // 256 B per staged row segment
 
 __device__ __forceinline__ void rz_cp16(uint32_t saddr, const void* g) {

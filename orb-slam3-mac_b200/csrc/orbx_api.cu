@@ -213,6 +213,7 @@ int build_plan(const orbx_handle* h, int w, int hgt, OrbxPlan* out, std::vector<
         L.n_rows = (int)(height / 30.f);
         if (L.n_cols < 1 || L.n_rows < 1)
             return fail(ORBX_E_UNSUPPORTED, "level %d (%dx%d) has no 30-px FAST cell; the reference divides by zero here", l, L.w, L.h);
+        L.n_cols_inv = L.n_cols == 1 ? 0u : (uint32_t)(((1ull << 32) + L.n_cols - 1) / L.n_cols);
         L.w_cell = (int)ceilf(width / L.n_cols);
         L.h_cell = (int)ceilf(height / L.n_rows);
         L.cell_cap = ((L.w_cell + 1) / 2) * ((L.h_cell + 1) / 2);

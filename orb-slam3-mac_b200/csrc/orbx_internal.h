@@ -40,6 +40,8 @@ struct OrbxLevel {
     long long off;       // byte offset of the level inside a frame's slab
     // FAST cell grid (ORBextractor.cc:771-785)
     int n_cols, n_rows;  // cells
+    uint32_t n_cols_inv; // ceil(2^32 / n_cols), 0 for n_cols == 1: c / n_cols == umulhi(c, inv) for c < 2^16
+    int _pad2;
     int w_cell, h_cell;
     int max_bx, max_by;  // maxBorderX/Y = w - 16, h - 16
     int cell_cap;        // ceil(w_cell/2) * ceil(h_cell/2): NMS survivors cannot be 8-adjacent
