@@ -27,11 +27,10 @@
 #define DESC_WARPS 4
 #endif
 #define DESC_SP 13                       // words per staged row (52 B; odd -> conflict-free rows)
-#define DESC_HP 22                       // words per H row (40 u16 + pad; even: 8-byte rows)
 #define DESC_BP 10                       // words per blurred row (40 B)
-#define DESC_S_WORDS 560                 // 43 * DESC_SP rounded up; reused for 38 * DESC_BP
-#define DESC_H_WORDS (44 * DESC_HP)      // 43 rows + one the last odd output row reads
-#define DESC_WARP_WORDS (DESC_S_WORDS + DESC_H_WORDS)
+#define DESC_S_WORDS (44 * DESC_SP)      // 43 rows + one the last (unused) odd output row reads
+#define DESC_B_WORDS (38 * DESC_BP)
+#define DESC_WARP_WORDS (DESC_S_WORDS + DESC_B_WORDS)
 #define DESC_SMEM_BYTES ((DESC_WARPS * DESC_WARP_WORDS + 8 * 32 * 4) * 4)
 
 __device__ const int8_t g_pattern[1024] = {
@@ -97,11 +96,16 @@ k_assemble(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ surv
     const uint32_t nstereo = block_excl_scan(flags, n, tmp);
     if (tid == 0) flags[n] = nstereo;
     __syncthreads();
-    uint32_t* d = dest + (size_t)frame * P.surv_total;
+    // one record per keypoint for k_describe: {key, output row | level << 24}
+    uint2* d = reinterpret_cast<uint2*>(dest) + (size_t)frame * P.surv_total;
     for (int idx = tid; idx < n; idx += blockDim.x) {
         const uint32_t sb = flags[idx];
         const bool stereo = flags[idx + 1] != sb;
-        d[idx] = stereo ? (uint32_t)(n - 1) - sb : (uint32_t)idx - sb;
+        int l = 0;
+        while (idx >= off[l + 1]) ++l;
+        const uint32_t key = sv[P.lvl[l].surv_off + (idx - off[l])];
+        const uint32_t row = stereo ? (uint32_t)(n - 1) - sb : (uint32_t)idx - sb;
+        d[idx] = make_uint2(key, row | ((uint32_t)l << 24));
     }
     if (tid == 0) {
         int32_t* h = header + 4 * (size_t)frame;
@@ -119,9 +123,8 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 
 __global__ void __launch_bounds__(DESC_WARPS * 32)
 k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t* __restrict__ pyr,
-           const uint32_t* __restrict__ surv, const uint32_t* __restrict__ survcnt,
-           const uint32_t* __restrict__ dest, orbx_keypoint* __restrict__ kps,
-           uint8_t* __restrict__ desc) {
+           const int32_t* __restrict__ header, const uint32_t* __restrict__ dest,
+           orbx_keypoint* __restrict__ kps, uint8_t* __restrict__ desc) {
     extern __shared__ __align__(16) uint32_t sm[];
     float4* pat4 = reinterpret_cast<float4*>(sm);  // [8][32]: comparison k of lane i
     const int warp = orbx_warp(), lane = orbx_lane();
@@ -138,23 +141,17 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
     const int frame = blockIdx.y;
     const int idx = blockIdx.x * DESC_WARPS + warp;
 
-    // which (level, i) is keypoint idx of this frame (level-major order)?
-    const uint32_t* sc = survcnt + (size_t)frame * ORBX_MAX_LEVELS;
-    int l = 0, base = 0;
-    for (;; ++l) {
-        if (l == P.nlevels) return;  // idx >= n
-        const int nl = min((int)sc[l], P.lvl[l].surv_cap);
-        if (idx < base + nl) break;
-        base += nl;
-    }
-    const OrbxLevel& L = P.lvl[l];
-    const uint32_t key = surv[(size_t)frame * P.surv_total + L.surv_off + (idx - base)];
-    const uint32_t out_row = dest[(size_t)frame * P.surv_total + idx];
+    // the keypoint's record, written by k_assemble: {key, output row | level << 24}
+    if (idx >= min(header[4 * frame], P.surv_total)) return;
+    const uint2 rec = __ldg(reinterpret_cast<const uint2*>(dest) + (size_t)frame * P.surv_total + idx);
+    const uint32_t key = rec.x;
+    const uint32_t out_row = rec.y & 0xffffffu;
+    const int l = (int)(rec.y >> 24);
     if ((int)out_row >= P.out_cap) return;
+    const OrbxLevel& L = P.lvl[l];
     const int cx = ORBX_KEY_X(key) + ORBX_FAST_BORDER, cy = ORBX_KEY_Y(key) + ORBX_FAST_BORDER;
 
     uint32_t* S = sm + 8 * 32 * 4 + warp * DESC_WARP_WORDS;  // staged source rows, DESC_SP words each
-    uint32_t* Hs = S + DESC_S_WORDS;                         // 44 x 20 packed u16 pairs
     int lpitch;
     const uint8_t* src = orbx_level_ptr(P, isrc, pyr, frame, l, &lpitch);
 
@@ -186,72 +183,71 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
         }
     }
     __syncwarp();
-    const uint8_t* Sb = reinterpret_cast<const uint8_t*>(S) + xo;  // Sb[r * 52 + c], c in [0,43)
 
     // ---- E4: intensity centroid over the radius-15 disc --------------------------------------
+    // lane = row v of the disc; the row's bytes [21-d, 21+d] are read as words (rows are 13 words
+    // apart: conflict-free) and reduced with IDP.4A against 1 and against the biased column
+    // weights u + 32 (>= 0 in every byte, so the packed weights advance by 0x04040404 per word).
     int m10 = 0, m01 = 0;
     if (lane < 31) {
         const int v = lane - 15;
         const int av = v < 0 ? -v : v;
         const int d = (int)((0x3689ABCDDEEEFFFFull >> (4 * av)) & 15ull);  // umax[|v|], :452-467
-        const uint8_t* row = Sb + (21 + v) * (DESC_SP * 4) + 21;
-        int rs = 0;
-        for (int u = -d; u <= d; ++u) {
-            const int val = row[u];
-            rs += val;
-            m10 += u * val;
+        const int lo = xo + 21 - d, hi = xo + 21 + d;                      // staged byte columns
+        const int j0 = lo >> 2, j1 = hi >> 2;
+        const uint32_t* row = S + (21 + v) * DESC_SP;
+        // weight of staged byte b is b - xo - 21 + 32
+        uint32_t uw = (uint32_t)(11 - xo) * 0x01010101u + 0x03020100u + 0x04040404u * (uint32_t)j0;
+        uint32_t rs = 0, mu = 0;
+        for (int j = j0; j <= j1; ++j, uw += 0x04040404u) {
+            uint32_t w = row[j];
+            if (j == j0) w &= 0xffffffffu << (8 * (lo & 3));
+            if (j == j1) w &= 0xffffffffu >> (8 * (3 - (hi & 3)));
+            rs = __dp4a(w, 0x01010101u, rs);
+            mu = __dp4a(w, uw, mu);
         }
-        m01 = v * rs;
+        m10 = (int)mu - 32 * (int)rs;
+        m01 = v * (int)rs;
     }
     m10 = warp_sum(m10);
     m01 = warp_sum(m01);
     const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-    // ---- E5 (horizontal): H[r][b] = sum_k g[k] * S[r][b + k] for staged byte columns b < 40 ----
+    // ---- E5: 7x7 sigma-2 Gaussian, horizontal and vertical pass fused in registers -----------
+    // lane = (band, column group): 4 adjacent staged byte columns b = 4g .. 4g+3, 14 output rows.
+    // Walking down the source rows, H[r][b] = sum_k g[k] * S[r][b + k] comes from 3 staged words
+    // (6 funnel shifts + 8 IDP.4A); two consecutive rows are paired per column as u16x2 (PRMT) so
+    // that one IDP.2A applies two vertical taps: 8 IDP.2A give an even and an odd output row of
+    // B[r][b] = (sum_k g[k] * H[r + k][b] + 32768) >> 16.  Only B goes to shared memory.
+    uint32_t* Bw = S + DESC_S_WORDS;
     if (lane < 30) {
         const uint32_t GA = 0x38302212u, GB = 0x00122230u;  // {18,34,48,56}, {48,34,18,0}
-        const int ro = lane / 10, q = lane - ro * 10;
-        const uint32_t* sp = S + ro * DESC_SP + q;
-        uint2* hp = reinterpret_cast<uint2*>(Hs + ro * DESC_HP) + q;
-#pragma unroll 5
-        for (int r = ro; r < 43; r += 3) {
-            const uint32_t w0 = sp[0], w1 = sp[1], w2 = sp[2];
-            const uint32_t o0 = __dp4a(w0, GA, __dp4a(w1, GB, 0u));
-            const uint32_t o1 = __dp4a(__funnelshift_r(w0, w1, 8), GA, __dp4a(__funnelshift_r(w1, w2, 8), GB, 0u));
-            const uint32_t o2 = __dp4a(__funnelshift_r(w0, w1, 16), GA, __dp4a(__funnelshift_r(w1, w2, 16), GB, 0u));
-            const uint32_t o3 = __dp4a(__funnelshift_r(w0, w1, 24), GA, __dp4a(__funnelshift_r(w1, w2, 24), GB, 0u));
-            *hp = make_uint2(__byte_perm(o0, o1, 0x5410), __byte_perm(o2, o3, 0x5410));
-            sp += 3 * DESC_SP;
-            hp += 3 * DESC_HP / 2;
-        }
-    }
-    __syncwarp();
-
-    // ---- E5 (vertical): B[r][b] = (sum_k g[k] * H[r + k][b] + 32768) >> 16, r < 38 -------------
-    uint32_t* Bw = S;  // the source window is dead: reuse it for the blurred patch
-    if (lane < 30) {
         const int band = lane / 10, g = lane - band * 10;
-        const int m0 = 6 * band;  // pair rows m0 .. m0+6 (band 1/2 recompute one shared pair row)
-        const uint2* hp = reinterpret_cast<const uint2*>(Hs + 2 * m0 * DESC_HP) + g;
-        uint32_t* bp = Bw + 2 * m0 * DESC_BP + g;
+        const uint32_t* sp = S + (12 * band) * DESC_SP + g;   // source rows 12*band ..
+        uint32_t* bp = Bw + (12 * band) * DESC_BP + g;        // output rows 12*band ..
         uint32_t Q[4][4];  // Q[j][c] = {H[2(m+j)][c], H[2(m+j)+1][c]} as u16x2
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            const uint2 A = hp[0], Bv = hp[DESC_HP / 2];
-            Q[j][0] = __byte_perm(A.x, Bv.x, 0x5410);
-            Q[j][1] = __byte_perm(A.x, Bv.x, 0x7632);
-            Q[j][2] = __byte_perm(A.y, Bv.y, 0x5410);
-            Q[j][3] = __byte_perm(A.y, Bv.y, 0x7632);
-            hp += DESC_HP;
+#define DESC_HROW(h)                                                                              \
+        {                                                                                         \
+            const uint32_t w0 = sp[0], w1 = sp[1], w2 = sp[2];                                    \
+            sp += DESC_SP;                                                                        \
+            h[0] = __dp4a(w0, GA, __dp4a(w1, GB, 0u));                                            \
+            h[1] = __dp4a(__funnelshift_r(w0, w1, 8), GA, __dp4a(__funnelshift_r(w1, w2, 8), GB, 0u));   \
+            h[2] = __dp4a(__funnelshift_r(w0, w1, 16), GA, __dp4a(__funnelshift_r(w1, w2, 16), GB, 0u)); \
+            h[3] = __dp4a(__funnelshift_r(w0, w1, 24), GA, __dp4a(__funnelshift_r(w1, w2, 24), GB, 0u)); \
         }
+#define DESC_PAIR(q)                                                                              \
+        {                                                                                         \
+            uint32_t he[4], ho[4];                                                                \
+            DESC_HROW(he)                                                                         \
+            DESC_HROW(ho)                                                                         \
+            _Pragma("unroll") for (int c = 0; c < 4; ++c) q[c] = __byte_perm(he[c], ho[c], 0x5410); \
+        }
+        DESC_PAIR(Q[0])
+        DESC_PAIR(Q[1])
+        DESC_PAIR(Q[2])
 #pragma unroll
-        for (int s = 0; s < 7; ++s) {
-            const uint2 A = hp[0], Bv = hp[DESC_HP / 2];
-            Q[3][0] = __byte_perm(A.x, Bv.x, 0x5410);
-            Q[3][1] = __byte_perm(A.x, Bv.x, 0x7632);
-            Q[3][2] = __byte_perm(A.y, Bv.y, 0x5410);
-            Q[3][3] = __byte_perm(A.y, Bv.y, 0x7632);
-            hp += DESC_HP;
+        for (int st = 0; st < 7; ++st) {
+            DESC_PAIR(Q[3])
             uint32_t e[4], o[4];
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -268,6 +264,8 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
                 Q[2][c] = Q[3][c];
             }
         }
+#undef DESC_PAIR
+#undef DESC_HROW
     }
     __syncwarp();
 
@@ -325,7 +323,7 @@ cudaError_t orbx_launch_assemble(const OrbxPlan& P, const uint32_t* surv, const 
 }
 
 cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
-                                 const uint32_t* surv, const uint32_t* survcnt, const uint32_t* dest,
+                                 const int32_t* header, const uint32_t* dest,
                                  orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
                                  int* launches) {
     dim3 grid((P.surv_total + DESC_WARPS - 1) / DESC_WARPS, nframes);
@@ -335,7 +333,7 @@ cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const ui
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    k_describe<<<grid, DESC_WARPS * 32, DESC_SMEM_BYTES, st>>>(P, src, pyr, surv, survcnt, dest, kps, desc);
+    k_describe<<<grid, DESC_WARPS * 32, DESC_SMEM_BYTES, st>>>(P, src, pyr, header, dest, kps, desc);
     ++*launches;
     return cudaGetLastError();
 }

@@ -34,7 +34,7 @@ cudaError_t orbx_launch_assemble(const OrbxPlan& P, const uint32_t* surv, const 
                                  const int* lap, uint32_t* dest, int32_t* header, int nframes,
                                  cudaStream_t st, int* launches);
 cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
-                                 const uint32_t* surv, const uint32_t* survcnt, const uint32_t* dest,
+                                 const int32_t* header, const uint32_t* dest,
                                  orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
                                  int* launches);
 
@@ -351,7 +351,7 @@ int ensure_buffers(orbx_handle* h, const OrbxPlan& P) {
         if ((r = grow(&s.keysB, &c.keysB, z.keys))) return r;
         if ((r = grow(&s.surv, &c.surv, z.surv))) return r;
         if ((r = grow(&s.survcnt, &c.survcnt, z.survcnt))) return r;
-        if ((r = grow(&s.dest, &c.dest, z.surv))) return r;
+        if ((r = grow(&s.dest, &c.dest, 2 * z.surv))) return r;  // uint2 records
         if ((r = grow(&s.header, &c.header, z.header))) return r;
         if ((r = grow(&s.kps, &c.kps, z.kps))) return r;
         if ((r = grow(&s.desc, &c.desc, z.desc))) return r;
@@ -410,7 +410,7 @@ int enqueue_kernels(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes) {
     CUDA_TRY(orbx_launch_assemble(P, s.surv, s.survcnt, s.lap_d, s.dest, s.header, nframes, s.st,
                                   &s.launches));
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[4], s.st));
-    CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.surv, s.survcnt, s.dest, s.kps, s.desc, nframes,
+    CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.header, s.dest, s.kps, s.desc, nframes,
                                   s.st, &s.launches));
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[5], s.st));
     s.src = src;
