@@ -58,48 +58,78 @@ def make_frames(cfg: str, count: int, distinct: int):
 
 
 class ClockSampler:
-    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons DURING the timed region: NVML polled from a thread every ~2 ms
+    (the timed region lasts tens of ms, too short for `nvidia-smi -lms`); falls back to one
+    nvidia-smi query if NVML is unavailable."""
+    REASONS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+               "sw_power_cap": 0x4}
 
     def __init__(self, index: int):
         self.index = index
-        self.proc = None
-        self.lines = []
+        self.sm, self.mask, self.power = [], 0, []
+        self.run = False
+        self.thread = None
+        self.h = None
+        self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML enumerates all GPUs of the box: honour CUDA_VISIBLE_DEVICES
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                ent = vis.split(",")[index].strip()
+                if ent.isdigit():
+                    phys = int(ent)
+                else:
+                    self.h = pynvml.nvmlDeviceGetHandleByUUID(ent if isinstance(ent, bytes) else ent.encode())
+            if self.h is None:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nv = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:
+            log("NVML unavailable, falling back to nvidia-smi:", e)
+
+    def _poll(self):
+        nv = self.nv
+        while self.run:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.mask |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                                 if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons")
+                                 else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+            except Exception:
+                pass
+            time.sleep(0.002)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._pump, daemon=True).start()
-        except Exception as e:  # nvidia-smi missing
-            log("clock sampling unavailable:", e)
-
-    def _pump(self):
-        for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+        if self.nv is None:
+            return
+        self.run = True
+        self.thread = threading.Thread(target=self._poll, daemon=True)
+        self.thread.start()
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        self.proc.terminate()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1]))
-                mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        if self.nv is not None:
+            self.run = False
+            self.thread.join()
+            reasons = sorted(nm for nm, bit in self.REASONS.items() if self.mask & bit)
+            return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_mhz,
+                    "samples": len(self.sm), "power_w_max": max(self.power) if self.power else None,
+                    "reasons": reasons, "source": "NVML polled during the timed region"}
+        try:
+            q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+            out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                 capture_output=True, text=True, timeout=20).stdout
+            f = [x.strip() for x in out.strip().splitlines()[0].split(",")]
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            return {"sm_mhz": float(f[0]), "sm_max_mhz": float(f[1]), "samples": 1,
+                    "reasons": sorted(nm for nm, v in zip(names, f[2:6]) if v.lower().startswith("active")),
+                    "source": "nvidia-smi after the timed region"}
+        except Exception:
+            return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["unsampled"]}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -335,6 +365,22 @@ def run_ours(args):
     e2e_s = time.perf_counter() - t0
     assert int(outs[0]["n"][0]) == int(hdr[0, 0]), "e2e result differs from the device-resident run"
 
+    # ---- single-frame latency (BASELINE.json: "p50 us/frame"): synchronous orbx_extract of one pinned
+    # host frame, H2D + 11 launches + D2H, no batching -----------------------------------------------
+    lat = None
+    if rank == 0:
+        n1, m1 = C.c_int(), C.c_int()
+        o = outs[0]
+        ts = []
+        for i in range(60 + 300):
+            t1 = time.perf_counter()
+            _lib.check(lib.orbx_extract(hd, h_in + (i % B) * h * w, w, h, w, 0, 1000, o["kps"], o["desc"], cap,
+                                        C.byref(n1), C.byref(m1)))
+            ts.append(time.perf_counter() - t1)
+        ts = np.sort(np.array(ts[60:])) * 1e6
+        lat = {"p50_us": float(ts[len(ts) // 2]), "p90_us": float(ts[int(len(ts) * 0.9)]), "samples": len(ts),
+               "what": "orbx_extract, one frame, pinned host in/out, synchronous (H2D + kernels + D2H)"}
+
     # ---- max over ranks ------------------------------------------------------------------------------
     t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
@@ -356,8 +402,22 @@ def run_ours(args):
             kernels[nm] = {"ms_per_launch_batch": round(float(stage[k]), 4), "alg_bytes_per_frame": int(ab[nm]),
                            "achieved_gbs": round(gbs, 1), "frac": round(gbs / peak, 4)}
         dom = max(names, key=lambda nm: kernels[nm]["ms_per_launch_batch"])
+        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
+        # capture (profiles/traffic.json: per kernel, at the batch it was captured with)
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            tj = json.load(open(tpath))
+            ent = tj.get(dom)
+            if ent and ent.get("batch") == B and ent.get("config") == cfg:
+                traffic = ent["dram_bytes_per_launch"]
+            for nm in names:
+                e2 = tj.get(nm)
+                if e2 and e2.get("batch") == B and e2.get("config") == cfg:
+                    kernels[nm]["traffic_bytes_per_launch"] = e2["dram_bytes_per_launch"]
+                    kernels[nm]["alg_bytes_per_launch"] = int(ab[nm] * B)
         roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
-                    "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                    "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": traffic, "peak_source": peak_src,
                     "kernels": kernels, "stage_ms_sum": round(float(stage[:5].sum()), 4),
                     "step_ms_device": round(dev_ms / args.steps, 4)}
         line = {
@@ -377,6 +437,7 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "roofline": roofline,
             "clocks": clocks,
+            "latency": lat,
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
@@ -405,7 +466,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C1", choices=["C1", "C2", "C3", "C4", "C5"])
