@@ -263,31 +263,43 @@ def run_ours(args):
     lap = np.tile(np.array([0, 1000], np.int32), (B, 1))
     ptrs = (C.c_void_p * B)(*[h_in + i * h * w for i in range(B)])
 
-    stream_ptr = lib.orbx_slot_stream(hd, 0)
-    ext = torch.cuda.ExternalStream(stream_ptr, device=torch.device("cuda", local))
+    # N > 1: two pipeline slots alternate so that the NCCL gather of step i (dedicated stream)
+    # overlaps the kernels of step i+1 (north_star: NCCL only gathers results)
+    nsl = 2 if world > 1 else 1
+    dev = torch.device("cuda", local)
+    ext = [torch.cuda.ExternalStream(lib.orbx_slot_stream(hd, sl), device=dev) for sl in range(nsl)]
     d_hdr, d_kps, d_desc = C.c_void_p(), C.c_void_p(), C.c_void_p()
 
-    def step_device():
-        _lib.check(lib.orbx_extract_device(hd, 0, d_in.data_ptr(), B, w, h, w, h * w, lap.ctypes.data,
+    def step_device(sl=0):
+        _lib.check(lib.orbx_extract_device(hd, sl, d_in.data_ptr(), B, w, h, w, h * w, lap.ctypes.data,
                                            C.byref(d_hdr), C.byref(d_kps), C.byref(d_desc)))
-        _lib.check(lib.orbx_wait(hd, 0))
+        _lib.check(lib.orbx_wait(hd, sl))
 
-    # result slab views for the NCCL gather (N > 1)
-    step_device()
+    views = []
+    for sl in range(nsl):
+        step_device(sl)
+        views.append((torch.as_tensor(_DevArray(d_hdr.value, B * 16), device=dev),
+                      torch.as_tensor(_DevArray(d_kps.value, B * cap * 28), device=dev),
+                      torch.as_tensor(_DevArray(d_desc.value, B * cap * 32), device=dev)))
+    step_device(0)  # leaves d_hdr/d_kps/d_desc pointing at slot 0 for the statistics below
     gather = None
+    comm = None
     if world > 1:
-        kp_t = torch.as_tensor(_DevArray(d_kps.value, B * cap * 28), device=f"cuda:{local}")
-        de_t = torch.as_tensor(_DevArray(d_desc.value, B * cap * 32), device=f"cuda:{local}")
-        hd_t = torch.as_tensor(_DevArray(d_hdr.value, B * 16), device=f"cuda:{local}")
-        g_kp = torch.empty(world * kp_t.numel(), dtype=torch.uint8, device=kp_t.device)
-        g_de = torch.empty(world * de_t.numel(), dtype=torch.uint8, device=kp_t.device)
-        g_hd = torch.empty(world * hd_t.numel(), dtype=torch.uint8, device=kp_t.device)
+        comm = torch.cuda.Stream(device=dev)
+        g_hd = [torch.empty(world * B * 16, dtype=torch.uint8, device=dev) for _ in range(nsl)]
+        g_kp = [torch.empty(world * B * cap * 28, dtype=torch.uint8, device=dev) for _ in range(nsl)]
+        g_de = [torch.empty(world * B * cap * 32, dtype=torch.uint8, device=dev) for _ in range(nsl)]
+        gath_ev = [torch.cuda.Event() for _ in range(nsl)]
 
-        def gather():
-            with torch.cuda.stream(ext):
-                dist.all_gather_into_tensor(g_hd, hd_t)
-                dist.all_gather_into_tensor(g_kp, kp_t)
-                dist.all_gather_into_tensor(g_de, de_t)
+        def gather(sl):
+            # the slot's kernels are complete (orbx_wait); the gather runs on `comm` while the
+            # other slot computes, and the slot's next kernels wait for it (gath_ev)
+            hd_t, kp_t, de_t = views[sl]
+            with torch.cuda.stream(comm):
+                dist.all_gather_into_tensor(g_hd[sl], hd_t)
+                dist.all_gather_into_tensor(g_kp[sl], kp_t)
+                dist.all_gather_into_tensor(g_de[sl], de_t)
+                gath_ev[sl].record(comm)
 
     def barrier():
         torch.cuda.synchronize()
@@ -295,11 +307,17 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- value: frames resident in HBM, CUDA events on the launching stream ------------------------
-    for _ in range(args.warmup):
-        step_device()
+    def one_step(i):
+        sl = i % nsl
         if gather:
-            gather()
+            ext[sl].wait_event(gath_ev[sl])
+        step_device(sl)
+        if gather:
+            gather(sl)
+
+    # ---- value: frames resident in HBM, CUDA events on the launching stream ------------------------
+    for i in range(args.warmup):
+        one_step(i)
     sampler = ClockSampler(local)
     barrier()
     if rank == 0:
@@ -308,19 +326,22 @@ def run_ours(args):
     stage = np.zeros(6, np.float64)
     ms6 = np.zeros(6, np.float32)
     launches = 0
-    ev0.record(ext)
-    for _ in range(args.steps):
-        step_device()
-        if gather:
-            gather()
-        lib.orbx_last_stage_ms(hd, 0, ms6.ctypes.data, 6)
+    ev0.record(ext[0])
+    for i in range(args.steps):
+        one_step(i)
+        lib.orbx_last_stage_ms(hd, i % nsl, ms6.ctypes.data, 6)
         stage += ms6
-        launches += lib.orbx_last_launch_count(hd, 0)
-    ev1.record(ext)
+        launches += lib.orbx_last_launch_count(hd, i % nsl)
+    # ev1 closes the region on a stream that has waited for every slot stream and the gathers
+    fin = comm if comm is not None else ext[0]
+    for e in ext:
+        fin.wait_stream(e)
+    ev1.record(fin)
     barrier()
     dev_ms = ev0.elapsed_time(ev1)
     clocks = sampler.stop() if rank == 0 else None
     stage /= args.steps
+    step_device(0)
 
     # keypoint / candidate statistics of the batch (for the algorithmic-byte figures)
     hdr = torch.as_tensor(_DevArray(d_hdr.value, B * 16), device=f"cuda:{local}").cpu().numpy().view(np.int32).reshape(B, 4)

@@ -71,6 +71,20 @@ int orbm_stereo_rows(orbm_context* c, const orbx_keypoint* kps_l, const uint8_t*
                      const float* scale_factors, int nlevels, float min_d, float max_d,
                      int32_t* best_idx, int32_t* best_dist);
 
+/* Frame::ComputeStereoMatches, complete (src/Frame.cc:802-980): the row-band
+ * Hamming search above with minD = 0, maxD = mbf / mb (:831-833), then for matches better than
+ * thOrbDist = (TH_HIGH + TH_LOW) / 2 the 11x11 SAD search over +-5 px on level kpL.octave of BOTH
+ * extractors' pyramids (:888-934; the reference reads mvImagePyramid, a buffer with a 19-px
+ * BORDER_REFLECT_101 border -- here the two DEVICE-RESIDENT pyramids from orbx_device_pyramid, the
+ * reflection applied on the fly), the parabola fit (:936-947), the disparity gate (:950-963) and the
+ * median-based SAD outlier cut (:966-979).  u_right / depth: mvuRight / mvDepth (n_l floats, -1 =
+ * no stereo match).  The pyramid views must come from handles on the context's device. */
+int orbm_compute_stereo_matches(orbm_context* c, const orbx_keypoint* kps_l, const uint8_t* desc_l, int n_l,
+                                const orbx_keypoint* kps_r, const uint8_t* desc_r, int n_r,
+                                const float* scale_factors, const float* inv_scale_factors, int nlevels,
+                                const orbx_pyramid_view* pyr_l, const orbx_pyramid_view* pyr_r, float mb,
+                                float mbf, float* u_right, float* depth);
+
 /* ---- layer 2 ---------------------------------------------------------------------------------- */
 /* The parts of ORB_SLAM3::Frame the searches read (include/Frame.h). */
 typedef struct orbm_frame_view {

@@ -147,6 +147,21 @@ int orbx_level_size(const orbx_handle* h, int w, int hgt, int level, int* lw, in
 int orbx_get_pyramid_level(orbx_handle* h, int slot, int frame, int level, int pad, uint8_t* dst,
                            size_t dst_stride);
 
+/* Device-resident view of one frame's pyramid of the last batch run on `slot`: what a consumer on
+ * the same GPU (orbm_compute_stereo_matches: the SAD refinement of src/Frame.cc:888-963 reads
+ * BOTH extractors' mvImagePyramid[octave]) uses instead of copying levels to the host.  The
+ * pointers stay valid until the next run on that slot; no border is materialised (readers apply
+ * BORDER_REFLECT_101 themselves, as orbx_get_pyramid_level(pad) does). */
+typedef struct orbx_pyramid_view {
+    const uint8_t* data[ORBX_MAX_LEVELS];  /* device pointers */
+    int32_t pitch[ORBX_MAX_LEVELS];        /* bytes per row */
+    int32_t width[ORBX_MAX_LEVELS];
+    int32_t height[ORBX_MAX_LEVELS];
+    int32_t nlevels;
+    int32_t device;
+} orbx_pyramid_view;
+int orbx_device_pyramid(orbx_handle* h, int slot, int frame, orbx_pyramid_view* out);
+
 /* ---- stage taps for the parity tests (results of the last batch run on `slot`) ------------ */
 /* FAST candidates of one level in the reference's order (cells row-major, raster inside a
  * cell): int32 triplets {x, y, response}, coordinates relative to (16,16) as

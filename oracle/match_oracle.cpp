@@ -409,6 +409,111 @@ int orbo_stereo_rows(const Kp* mvKeys, const uint8_t* mDescriptors, int N, const
     return 0;
 }
 
+// src/Frame.cc:802-980, complete: the Hamming search above, then the SAD sub-pixel refinement on
+// the two padded pyramids (mvImagePyramid[l] is a view into a buffer with a 19-px
+// BORDER_REFLECT_101 border: pyr_l[l] / pyr_r[l] point at pixel (0,0) of level l inside such a
+// buffer with row stride stride_[l]), the parabola fit, the disparity gate and the median cut.
+// cv::Mat::convertTo(CV_16S), "IL - IL.at<short>(w,w)" and cv::norm(NORM_L1) are restated as
+// integer arithmetic (exact: |values| <= 510, 121 terms).
+int orbo_compute_stereo_matches(const Kp* mvKeys, const uint8_t* mDescriptors, int N, const Kp* mvKeysRight,
+                                const uint8_t* mDescriptorsRight, int Nr, const float* mvScaleFactors,
+                                const float* mvInvScaleFactors, const uint8_t* const* pyr_l,
+                                const int* stride_l, const uint8_t* const* pyr_r, const int* stride_r,
+                                const int* cols_r, int n_rows, float mb, float mbf, float* mvuRight,
+                                float* mvDepth) {
+    for (int i = 0; i < N; ++i) mvuRight[i] = mvDepth[i] = -1.0f;
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    const float minZ = mb;
+    const float minD = 0;
+    const float maxD = mbf / minZ;
+    std::vector<int32_t> best_idx(N), best_dist(N);
+    orbo_stereo_rows(mvKeys, mDescriptors, N, mvKeysRight, mDescriptorsRight, Nr, mvScaleFactors, n_rows, minD,
+                     maxD, best_idx.data(), best_dist.data());
+    std::vector<std::pair<int, int> > vDistIdx;
+    vDistIdx.reserve(N);
+    for (int iL = 0; iL < N; iL++) {
+        if (best_idx[iL] < 0) continue;
+        const Kp& kpL = mvKeys[iL];
+        const float& uL = kpL.x;
+        const int bestIdxR = best_idx[iL];
+        if (best_dist[iL] < thOrbDist) {
+            const float uR0 = mvKeysRight[bestIdxR].x;
+            const float scaleFactor = mvInvScaleFactors[kpL.octave];
+            const float scaleduL = round(kpL.x * scaleFactor);
+            const float scaledvL = round(kpL.y * scaleFactor);
+            const float scaleduR0 = round(uR0 * scaleFactor);
+            const int w = 5;
+            const uint8_t* PL = pyr_l[kpL.octave];
+            const int sl = stride_l[kpL.octave];
+            const uint8_t* PR = pyr_r[kpL.octave];
+            const int sr = stride_r[kpL.octave];
+            short IL[11][11];
+            {
+                const int y0 = (int)(scaledvL - w), x0 = (int)(scaleduL - w);
+                for (int r = 0; r < 11; ++r)
+                    for (int c = 0; c < 11; ++c) IL[r][c] = (short)PL[(y0 + r) * sl + (x0 + c)];
+                const short ctr = IL[w][w];
+                for (int r = 0; r < 11; ++r)
+                    for (int c = 0; c < 11; ++c) IL[r][c] = (short)(IL[r][c] - ctr);
+            }
+            int bestDist = INT_MAX;
+            int bestincR = 0;
+            const int L = 5;
+            std::vector<float> vDists;
+            vDists.resize(2 * L + 1);
+            const float iniu = scaleduR0 + L - w;
+            const float endu = scaleduR0 + L + w + 1;
+            if (iniu < 0 || endu >= cols_r[kpL.octave]) continue;
+            for (int incR = -L; incR <= +L; incR++) {
+                short IR[11][11];
+                const int y0 = (int)(scaledvL - w), x0 = (int)(scaleduR0 + incR - w);
+                for (int r = 0; r < 11; ++r)
+                    for (int c = 0; c < 11; ++c) IR[r][c] = (short)PR[(y0 + r) * sr + (x0 + c)];
+                const short ctr = IR[w][w];
+                int l1 = 0;
+                for (int r = 0; r < 11; ++r)
+                    for (int c = 0; c < 11; ++c) l1 += abs((int)IL[r][c] - (int)(short)(IR[r][c] - ctr));
+                float dist = (float)l1;
+                if (dist < bestDist) {
+                    bestDist = dist;
+                    bestincR = incR;
+                }
+                vDists[L + incR] = dist;
+            }
+            if (bestincR == -L || bestincR == L) continue;
+            const float dist1 = vDists[L + bestincR - 1];
+            const float dist2 = vDists[L + bestincR];
+            const float dist3 = vDists[L + bestincR + 1];
+            const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+            if (deltaR < -1 || deltaR > 1) continue;
+            float bestuR = mvScaleFactors[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
+            float disparity = (uL - bestuR);
+            if (disparity >= minD && disparity < maxD) {
+                if (disparity <= 0) {
+                    disparity = 0.01;
+                    bestuR = uL - 0.01;
+                }
+                mvDepth[iL] = mbf / disparity;
+                mvuRight[iL] = bestuR;
+                vDistIdx.push_back(std::pair<int, int>(bestDist, iL));
+            }
+        }
+    }
+    if (vDistIdx.empty()) return 0;  // (the reference indexes an empty vector here)
+    sort(vDistIdx.begin(), vDistIdx.end());
+    const float median = vDistIdx[vDistIdx.size() / 2].first;
+    const float thDist = 1.5f * 1.4f * median;
+    for (int i = vDistIdx.size() - 1; i >= 0; i--) {
+        if (vDistIdx[i].first < thDist)
+            break;
+        else {
+            mvuRight[vDistIdx[i].second] = -1;
+            mvDepth[vDistIdx[i].second] = -1;
+        }
+    }
+    return (int)vDistIdx.size();
+}
+
 // cv::BFMatcher(NORM_HAMMING).knnMatch(k = 2) semantics (verified against cv2 in tests): the two
 // smallest distances, lowest train index first on ties; missing entries are -1.
 int orbo_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx_out, int32_t* dist_out) {

@@ -220,6 +220,26 @@ class MatchOracle:
                                   C.c_float(max_d), C.c_void_p(bi.ctypes.data), C.c_void_p(bd.ctypes.data))
         return bi, bd
 
+    def compute_stereo_matches(self, left, right, pyr_l, pyr_r, mb, mbf):
+        """pyr_l / pyr_r: per level a uint8 array padded by 19 px (OracleExtractor.level(l, 19))."""
+        nl = len(pyr_l)
+        keep = [np.ascontiguousarray(a) for a in list(pyr_l) + list(pyr_r)]
+        pl = (C.c_void_p * nl)(*[a.ctypes.data + 19 * a.strides[0] + 19 for a in keep[:nl]])
+        pr = (C.c_void_p * nl)(*[a.ctypes.data + 19 * a.strides[0] + 19 for a in keep[nl:]])
+        sl = (C.c_int * nl)(*[a.strides[0] for a in keep[:nl]])
+        sr = (C.c_int * nl)(*[a.strides[0] for a in keep[nl:]])
+        cr = (C.c_int * nl)(*[a.shape[1] - 38 for a in keep[nl:]])
+        inv = np.ascontiguousarray(1.0 / left.scale_factors.astype(np.float32), np.float32)
+        u = np.zeros(left.N, np.float32)
+        d = np.zeros(left.N, np.float32)
+        n = self.lib.orbo_compute_stereo_matches(
+            C.c_void_p(left.keys.ctypes.data), C.c_void_p(left.desc.ctypes.data), left.N,
+            C.c_void_p(right.keys.ctypes.data), C.c_void_p(right.desc.ctypes.data), right.N,
+            C.c_void_p(left.scale_factors.ctypes.data), C.c_void_p(inv.ctypes.data), pl, sl, pr, sr, cr,
+            int(keep[0].shape[0] - 38), C.c_float(mb), C.c_float(mbf), C.c_void_p(u.ctypes.data),
+            C.c_void_p(d.ctypes.data))
+        return u, d, n
+
     def knn2(self, q, t):
         q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
         t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)

@@ -35,6 +35,12 @@ class OrbxConfig(C.Structure):
                 ("device", C.c_int32), ("flags", C.c_uint32)]
 
 
+class OrbxPyramidView(C.Structure):
+    """orbx_pyramid_view (include/orbx.h): device pointers of one frame's pyramid."""
+    _fields_ = [("data", C.c_void_p * 16), ("pitch", C.c_int32 * 16), ("width", C.c_int32 * 16),
+                ("height", C.c_int32 * 16), ("nlevels", C.c_int32), ("device", C.c_int32)]
+
+
 class OrbxError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"orbx status {code}: {msg}")
@@ -52,6 +58,7 @@ ORBX_SYMBOLS = {
     "orbx_abi_version": (_i, []),
     "orbx_get_tables": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "orbx_max_keypoints": (_i, [_vp]),
+    "orbx_device_pyramid": (_i, [_vp, _i, _i, C.POINTER(OrbxPyramidView)]),
     "orbx_extract": (_i, [_vp, _vp, _i, _i, _sz, _i, _i, _vp, _vp, _i, _ip, _ip]),
     "orbx_extract_batch": (_i, [_vp, _vp, _i, _i, _i, _sz, _vp, _vp, _vp, _i, _ip, _ip, _ip]),
     "orbx_submit_batch": (_i, [_vp, _i, _vp, _i, _i, _i, _sz, _vp, _vp, _vp, _i, _ip, _ip, _ip]),

@@ -28,6 +28,7 @@ ORBM_SYMBOLS = {
     "orbm_hamming_csr": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _i, _vp]),
     "orbm_knn2": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp]),
     "orbm_stereo_rows": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _f, _f, _vp, _vp]),
+    "orbm_compute_stereo_matches": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _f, _f, _vp, _vp]),
     "orbm_search_by_projection_points": (_i, [_vp, _fv, _vp, _vp, _i, _f, _i, _f, _f, _vp, _vp]),
     "orbm_search_by_projection_frames": (_i, [_vp, _fv, _vp, _vp, _i, _f, _i, _i, _f, _i, _vp, _vp]),
     "orbm_search_for_initialization": (_i, [_vp, _fv, _fv, _vp, _vp, _i, _f, _i]),

@@ -103,6 +103,127 @@ k_stereo_rows(const orbx_keypoint* __restrict__ kl, const uint4* __restrict__ dl
     }
 }
 
+// ---- N1: sub-pixel stereo refinement, Frame::ComputeStereoMatches src/Frame.cc:888-963 -----------
+// One warp per left keypoint whose Hamming match is better than thOrbDist.  The 11x11 left patch
+// and the 11x21 right strip (11 window positions, incR = -5..5) of level kpL.octave are staged in
+// shared memory straight from the two extractors' device-resident pyramids; the reference reads a
+// 19-px BORDER_REFLECT_101 border there (mvImagePyramid is a padded buffer), here the reflection
+// is applied while staging.  SAD of the centre-subtracted int16 patches (cv::norm L1), first
+// minimum wins, parabola fit in non-contracted float32.
+struct OrbmPyr {
+    const uint8_t* data[ORBX_MAX_LEVELS];
+    int pitch[ORBX_MAX_LEVELS], w[ORBX_MAX_LEVELS], h[ORBX_MAX_LEVELS];
+};
+
+__device__ __forceinline__ int orbm_reflect101(int p, int len) {
+    if (p < 0) p = -p;
+    if (p >= len) p = 2 * (len - 1) - p;
+    return p;
+}
+
+__global__ void __launch_bounds__(256)
+k_stereo_refine(const orbx_keypoint* __restrict__ kl, int nl, const orbx_keypoint* __restrict__ kr,
+                const int32_t* __restrict__ best_idx, const int32_t* __restrict__ best_dist,
+                const __grid_constant__ OrbmPyr PL, const __grid_constant__ OrbmPyr PR,
+                const float* __restrict__ scale, const float* __restrict__ inv_scale, int th_orb,
+                float min_d, float max_d, float bf, float* __restrict__ u_right,
+                float* __restrict__ depth, int32_t* __restrict__ sad) {
+    __shared__ int16_t sm[8][11 * 11 + 11 * 21];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int il = blockIdx.x * 8 + warp;
+    if (il >= nl) return;
+    if (lane == 0) {
+        u_right[il] = -1.0f;
+        depth[il] = -1.0f;
+        sad[il] = -1;
+    }
+    const int ir = best_idx[il];
+    if (ir < 0 || best_dist[il] >= th_orb) return;   // :889
+    const orbx_keypoint L = kl[il];
+    const int oct = L.octave;
+    const float uR0 = kr[ir].x;
+    const float sf = inv_scale[oct];
+    const float scaleduL = roundf(__fmul_rn(L.x, sf));       // :893-895 (round half away from zero)
+    const float scaledvL = roundf(__fmul_rn(L.y, sf));
+    const float scaleduR0 = roundf(__fmul_rn(uR0, sf));
+    const int w = 5, Lw = 5;
+    const float iniu = scaleduR0 + Lw - w, endu = scaleduR0 + Lw + w + 1;   // :911-912
+    if (iniu < 0 || endu >= (float)PR.w[oct]) return;                        // :913
+    const int xl = (int)scaleduL, yl = (int)scaledvL, xr = (int)scaleduR0;
+    int16_t* IL = sm[warp];
+    int16_t* IR = IL + 121;
+    const uint8_t* pl = PL.data[oct];
+    const uint8_t* pr = PR.data[oct];
+    const int cl = pl[(size_t)orbm_reflect101(yl, PL.h[oct]) * PL.pitch[oct] + orbm_reflect101(xl, PL.w[oct])];
+    for (int i = lane; i < 121; i += 32) {
+        const int r = i / 11, c = i - r * 11;
+        const int y = orbm_reflect101(yl - w + r, PL.h[oct]), x = orbm_reflect101(xl - w + c, PL.w[oct]);
+        IL[i] = (int16_t)((int)pl[(size_t)y * PL.pitch[oct] + x] - cl);      // IL - IL.at<short>(w,w)
+    }
+    for (int i = lane; i < 231; i += 32) {
+        const int r = i / 21, c = i - r * 21;
+        const int y = orbm_reflect101(yl - w + r, PR.h[oct]), x = orbm_reflect101(xr - Lw - w + c, PR.w[oct]);
+        IR[i] = (int16_t)pr[(size_t)y * PR.pitch[oct] + x];
+    }
+    __syncwarp();
+    // lane k < 11 owns window incR = k - 5: centre pixel IR[5][k + 5]
+    int dist = 0x7fffffff;
+    if (lane < 11) {
+        const int cr = IR[5 * 21 + lane + 5];
+        int acc = 0;
+        for (int r = 0; r < 11; ++r)
+            for (int c = 0; c < 11; ++c) {
+                const int d = (int)IL[r * 11 + c] - ((int)IR[r * 21 + lane + c] - cr);
+                acc += d < 0 ? -d : d;
+            }
+        dist = acc;
+    }
+    // first minimum (strict '<', :927-931): smallest (dist, incR)
+    int bd = dist, bk = lane;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        const int od = __shfl_xor_sync(ORBX_FULL, bd, d), ok = __shfl_xor_sync(ORBX_FULL, bk, d);
+        if (od < bd || (od == bd && ok < bk)) { bd = od; bk = ok; }
+    }
+    const int incR = bk - Lw;
+    if (incR == -Lw || incR == Lw) return;                                   // :936
+    const float dist1 = (float)__shfl_sync(ORBX_FULL, dist, bk - 1);
+    const float dist2 = (float)bd;
+    const float dist3 = (float)__shfl_sync(ORBX_FULL, dist, bk + 1);
+    if (lane != 0) return;
+    const float deltaR = __fdiv_rn(__fsub_rn(dist1, dist3),
+                                   __fmul_rn(2.0f, __fsub_rn(__fadd_rn(dist1, dist3), __fmul_rn(2.0f, dist2))));  // :944
+    if (deltaR < -1 || deltaR > 1) return;                                   // :946 (NaN passes, as in C++)
+    float bestuR = __fmul_rn(scale[oct], __fadd_rn(__fadd_rn(scaleduR0, (float)incR), deltaR));   // :950
+    float disparity = __fsub_rn(L.x, bestuR);
+    if (disparity >= min_d && disparity < max_d) {                           // :954
+        if (disparity <= 0) {
+            disparity = 0.01f;
+            bestuR = (float)((double)L.x - 0.01);                            // uL-0.01: double arithmetic
+        }
+        depth[il] = __fdiv_rn(bf, disparity);
+        u_right[il] = bestuR;
+        sad[il] = bd;
+    }
+}
+
+cudaError_t orbm_launch_stereo_refine(const orbx_keypoint* kl, int nl, const orbx_keypoint* kr,
+                                      const int32_t* best_idx, const int32_t* best_dist,
+                                      const orbx_pyramid_view* vl, const orbx_pyramid_view* vr,
+                                      const float* scale, const float* inv_scale, int th_orb, float min_d,
+                                      float max_d, float bf, float* u_right, float* depth, int32_t* sad,
+                                      cudaStream_t st) {
+    if (nl <= 0) return cudaSuccess;
+    OrbmPyr A, B;
+    for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
+        A.data[l] = vl->data[l]; A.pitch[l] = vl->pitch[l]; A.w[l] = vl->width[l]; A.h[l] = vl->height[l];
+        B.data[l] = vr->data[l]; B.pitch[l] = vr->pitch[l]; B.w[l] = vr->width[l]; B.h[l] = vr->height[l];
+    }
+    k_stereo_refine<<<(nl + 7) / 8, 256, 0, st>>>(kl, nl, kr, best_idx, best_dist, A, B, scale, inv_scale, th_orb,
+                                                  min_d, max_d, bf, u_right, depth, sad);
+    return cudaGetLastError();
+}
+
 cudaError_t orbm_launch_hamming_csr(const uint8_t* q, int nq, const uint8_t* t, const int32_t* row_ptr,
                                     const int32_t* cand, int nnz, uint16_t* dist, cudaStream_t st) {
     if (nnz <= 0) return cudaSuccess;

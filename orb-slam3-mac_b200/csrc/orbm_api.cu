@@ -24,6 +24,12 @@ cudaError_t orbm_launch_hamming_csr(const uint8_t* q, int nq, const uint8_t* t, 
                                     const int32_t* cand, int nnz, uint16_t* dist, cudaStream_t st);
 cudaError_t orbm_launch_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
                              int32_t* dist, cudaStream_t st);
+cudaError_t orbm_launch_stereo_refine(const orbx_keypoint* kl, int nl, const orbx_keypoint* kr,
+                                      const int32_t* best_idx, const int32_t* best_dist,
+                                      const orbx_pyramid_view* vl, const orbx_pyramid_view* vr,
+                                      const float* scale, const float* inv_scale, int th_orb, float min_d,
+                                      float max_d, float bf, float* u_right, float* depth, int32_t* sad,
+                                      cudaStream_t st);
 cudaError_t orbm_launch_stereo_rows(const orbx_keypoint* kl, const uint8_t* dl, int nl,
                                     const orbx_keypoint* kr, const uint8_t* dr, int nr,
                                     const float* scale, float min_d, float max_d, int32_t* best_idx,
@@ -63,7 +69,7 @@ struct DevBuf {
 struct orbm_context {
     int device = 0;
     cudaStream_t st = nullptr;
-    DevBuf q, t, rowptr, cand, dist, aux1, aux2, kl, kr, sc;
+    DevBuf q, t, rowptr, cand, dist, aux1, aux2, kl, kr, sc, isc, ur, dp, sd;
     std::vector<uint16_t> hdist;     // distances of the last layer-2 search
     long long last_pairs = 0;        // number of (query, candidate) pairs of the last search
 };
@@ -175,6 +181,80 @@ int orbm_stereo_rows(orbm_context* c, const orbx_keypoint* kps_l, const uint8_t*
     M_TRY(cudaMemcpyAsync(best_idx, c->aux1.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaMemcpyAsync(best_dist, c->aux2.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaStreamSynchronize(c->st));
+    return ORBX_OK;
+}
+
+// Frame::ComputeStereoMatches, complete (src/Frame.cc:802-980): row-band Hamming argmin
+// (k_stereo_rows), SAD sub-pixel refinement on the two device-resident pyramids
+// (k_stereo_refine), then the median-based outlier cut of :966-979 on the host (a k-th element
+// over <= N integers).
+int orbm_compute_stereo_matches(orbm_context* c, const orbx_keypoint* kps_l, const uint8_t* desc_l, int n_l,
+                                const orbx_keypoint* kps_r, const uint8_t* desc_r, int n_r,
+                                const float* scale_factors, const float* inv_scale_factors, int nlevels,
+                                const orbx_pyramid_view* pyr_l, const orbx_pyramid_view* pyr_r, float mb,
+                                float mbf, float* u_right, float* depth) {
+    if (!c || n_l < 0 || n_r < 0 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS)
+        return orbx_set_error(ORBX_E_BAD_ARG, "bad argument");
+    if (n_l == 0) return ORBX_OK;
+    if (!kps_l || !desc_l || (n_r && (!kps_r || !desc_r)) || !scale_factors || !inv_scale_factors ||
+        !pyr_l || !pyr_r || !u_right || !depth)
+        return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    if (pyr_l->device != c->device || pyr_r->device != c->device)
+        return orbx_set_error(ORBX_E_BAD_ARG, "pyramids live on another device than the matcher context");
+    if (pyr_l->nlevels < nlevels || pyr_r->nlevels < nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "pyramid has fewer levels");
+    if (n_r >= (1 << 20)) return orbx_set_error(ORBX_E_TOO_LARGE, "more than 2^20 right keypoints");
+    for (int i = 0; i < n_r; ++i)
+        if (kps_r[i].octave < 0 || kps_r[i].octave >= nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "octave out of range");
+    for (int i = 0; i < n_l; ++i)
+        if (kps_l[i].octave < 0 || kps_l[i].octave >= nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "octave out of range");
+    M_TRY(cudaSetDevice(c->device));
+    int r;
+    if ((r = c->q.ensure((size_t)n_l * 32)) || (r = c->t.ensure((size_t)std::max(n_r, 1) * 32)) ||
+        (r = c->kl.ensure((size_t)n_l * sizeof(orbx_keypoint))) ||
+        (r = c->kr.ensure((size_t)std::max(n_r, 1) * sizeof(orbx_keypoint))) ||
+        (r = c->sc.ensure((size_t)nlevels * 4)) || (r = c->isc.ensure((size_t)nlevels * 4)) ||
+        (r = c->aux1.ensure((size_t)n_l * 4)) || (r = c->aux2.ensure((size_t)n_l * 4)) ||
+        (r = c->ur.ensure((size_t)n_l * 4)) || (r = c->dp.ensure((size_t)n_l * 4)) ||
+        (r = c->sd.ensure((size_t)n_l * 4)))
+        return r;
+    M_TRY(cudaMemcpyAsync(c->q.p, desc_l, (size_t)n_l * 32, cudaMemcpyHostToDevice, c->st));
+    M_TRY(cudaMemcpyAsync(c->kl.p, kps_l, (size_t)n_l * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
+    if (n_r) {
+        M_TRY(cudaMemcpyAsync(c->t.p, desc_r, (size_t)n_r * 32, cudaMemcpyHostToDevice, c->st));
+        M_TRY(cudaMemcpyAsync(c->kr.p, kps_r, (size_t)n_r * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
+    }
+    M_TRY(cudaMemcpyAsync(c->sc.p, scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice, c->st));
+    M_TRY(cudaMemcpyAsync(c->isc.p, inv_scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice, c->st));
+    // :831-833
+    const float minZ = mb, minD = 0, maxD = mbf / minZ;
+    const int thOrbDist = (ORBM_TH_HIGH + ORBM_TH_LOW) / 2;   // :807
+    M_TRY(orbm_launch_stereo_rows((const orbx_keypoint*)c->kl.p, (const uint8_t*)c->q.p, n_l,
+                                  (const orbx_keypoint*)c->kr.p, (const uint8_t*)c->t.p, n_r, (const float*)c->sc.p,
+                                  minD, maxD, (int32_t*)c->aux1.p, (int32_t*)c->aux2.p, c->st));
+    M_TRY(orbm_launch_stereo_refine((const orbx_keypoint*)c->kl.p, n_l, (const orbx_keypoint*)c->kr.p,
+                                    (const int32_t*)c->aux1.p, (const int32_t*)c->aux2.p, pyr_l, pyr_r,
+                                    (const float*)c->sc.p, (const float*)c->isc.p, thOrbDist, minD, maxD, mbf,
+                                    (float*)c->ur.p, (float*)c->dp.p, (int32_t*)c->sd.p, c->st));
+    std::vector<int32_t> sad(n_l);
+    M_TRY(cudaMemcpyAsync(u_right, c->ur.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaMemcpyAsync(depth, c->dp.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaMemcpyAsync(sad.data(), c->sd.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaStreamSynchronize(c->st));
+    // :966-979: median of the accepted SAD distances, reject >= 1.5 * 1.4 * median
+    std::vector<int32_t> acc;
+    acc.reserve(n_l);
+    for (int i = 0; i < n_l; ++i)
+        if (sad[i] >= 0) acc.push_back(sad[i]);
+    if (!acc.empty()) {   // (the reference indexes an empty vector here)
+        std::nth_element(acc.begin(), acc.begin() + acc.size() / 2, acc.end());
+        const float median = (float)acc[acc.size() / 2];
+        const float thDist = 1.5f * 1.4f * median;
+        for (int i = 0; i < n_l; ++i)
+            if (sad[i] >= 0 && !((float)sad[i] < thDist)) {
+                u_right[i] = -1;
+                depth[i] = -1;
+            }
+    }
     return ORBX_OK;
 }
 

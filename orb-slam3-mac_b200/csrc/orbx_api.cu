@@ -738,6 +738,25 @@ int orbx_get_pyramid_level(orbx_handle* h, int slot, int frame, int level, int p
     return ORBX_OK;
 }
 
+int orbx_device_pyramid(orbx_handle* h, int slot, int frame, orbx_pyramid_view* out) {
+    int r = tap_ready(h, slot, frame, 0);
+    if (r) return r;
+    if (!out) return fail(ORBX_E_BAD_ARG, "null argument");
+    Slot& s = h->slots[slot];
+    memset(out, 0, sizeof *out);
+    out->nlevels = h->cfg.nlevels;
+    out->device = h->cfg.device;
+    for (int l = 0; l < h->cfg.nlevels; ++l) {
+        const OrbxLevel& L = h->plan.lvl[l];
+        out->data[l] = l == 0 ? s.src.img0 + (size_t)frame * s.src.stride0
+                              : s.pyr + (size_t)frame * h->plan.frame_stride + L.off;
+        out->pitch[l] = l == 0 ? s.src.pitch0 : L.pitch;
+        out->width[l] = L.w;
+        out->height[l] = L.h;
+    }
+    return ORBX_OK;
+}
+
 int orbx_debug_candidates(orbx_handle* h, int slot, int frame, int level, int32_t* xyr, int cap) {
     int r = tap_ready(h, slot, frame, level);
     if (r) return r;

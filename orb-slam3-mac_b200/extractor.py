@@ -130,6 +130,13 @@ class ORBextractor:
                                               out.strides[0]))
         return out
 
+    def device_pyramid(self, frame: int = 0, slot: int = 0):
+        """orbx_pyramid_view of the last run: device pointers for a same-GPU consumer
+        (ORBmatcher.ComputeStereoMatches)."""
+        v = _lib.OrbxPyramidView()
+        check(self.lib.orbx_device_pyramid(self.h, slot, frame, C.byref(v)))
+        return v
+
     # ---- stage taps ---------------------------------------------------------------------------------
     def debug_candidates(self, level: int, frame: int = 0, slot: int = 0):
         n = self.lib.orbx_debug_candidates(self.h, slot, frame, level, None, 0)

@@ -105,6 +105,20 @@ class ORBmatcher:
                                         bi.ctypes.data, bd.ctypes.data))
         return bi, bd
 
+    def ComputeStereoMatches(self, left: Frame, right: Frame, pyr_left, pyr_right, mb: float, mbf: float):
+        """Frame::ComputeStereoMatches (src/Frame.cc:802-980) -> (mvuRight, mvDepth).  pyr_left /
+        pyr_right: ORBextractor.device_pyramid() of the two extractions (device resident)."""
+        import ctypes as C
+        u = np.zeros(left.N, np.float32)
+        d = np.zeros(left.N, np.float32)
+        inv = np.ascontiguousarray(1.0 / left.scale_factors.astype(np.float32), np.float32) \
+            if getattr(left, "inv_scale_factors", None) is None else left.inv_scale_factors
+        check(self.lib.orbm_compute_stereo_matches(
+            self.ctx, left.keys.ctypes.data, left.desc.ctypes.data, left.N, right.keys.ctypes.data,
+            right.desc.ctypes.data, right.N, left.scale_factors.ctypes.data, inv.ctypes.data,
+            len(left.scale_factors), C.byref(pyr_left), C.byref(pyr_right), mb, mbf, u.ctypes.data, d.ctypes.data))
+        return u, d
+
     # ---- layer 2 ------------------------------------------------------------------------------------
     def SearchByProjection(self, F: Frame, map_points, mp_desc, th=1.0, bFarPoints=False, thFarPoints=50.0,
                            kp_obs=None):

@@ -188,3 +188,23 @@ def test_against_committed_goldens(synth):
             # and they are bounded in test_extractor_parity_stagewise; report them here
             print(f"{kind} {h}x{w}: keypoint/descriptor bytes differ from the golden hash")
         ex.close()
+
+
+@pytest.mark.parametrize("scale,nlevels,h,w", [(1.5, 5, 480, 640), (2.0, 3, 480, 640), (1.1, 8, 480, 752),
+                                               (1.2, 3, 250, 330)])
+def test_other_scale_factors_and_level_counts(oracle_libs, synth, scale, nlevels, h, w):
+    """Scale factors other than 1.2 take the other pyramid kernels (k_resize_rows for source steps
+    of 3 columns, k_resize_level beyond); results stay bit-exact."""
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    kind = "ref" if oracle_libs.have_ref() else "port"
+    ora = oracle_libs.OracleExtractor(600, scale, nlevels, 20, 7, kind=kind)
+    ex = ORBextractor(600, scale, nlevels, 20, 7, max_size=(h, w), max_batch=1)
+    try:
+        img = synth.frame("noise", h, w, 5)
+        ref = ora(img, (0, 0))
+        got = ex(img, (0, 0))
+        for l in range(nlevels):
+            assert np.array_equal(ex.pyramid_level(l, (h, w)), ora.level(l)), ("pyramid", l)
+        _compare_final(ref, got, (scale, nlevels))
+    finally:
+        ex.close()

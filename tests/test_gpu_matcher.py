@@ -195,3 +195,34 @@ def test_matcher_contexts_are_concurrent(mo):
     [x.join() for x in ts]
     for r in res:
         assert np.array_equal(r[0], exp[0]) and np.array_equal(r[1], exp[1])
+
+
+def test_compute_stereo_matches_full_c2(matcher, mo, oracle_libs):
+    """SURVEY 8(f) N1: the whole Frame::ComputeStereoMatches (Hamming rows + 11x11 SAD over +-5 px
+    on the two DEVICE-RESIDENT pyramids + parabola + median cut) against the CPU restatement that
+    reads the reference's padded pyramids.  Bar: mvuRight / mvDepth bit-identical floats."""
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    kind = "ref" if oracle_libs.have_ref() else "port"
+    exl = ORBextractor(1200, 1.2, 8, 20, 7, max_size=(480, 752), max_batch=1)
+    exr = ORBextractor(1200, 1.2, 8, 20, 7, max_size=(480, 752), max_batch=1)
+    ol = oracle_libs.OracleExtractor(1200, 1.2, 8, 20, 7, kind=kind)
+    orr = oracle_libs.OracleExtractor(1200, 1.2, 8, 20, 7, kind=kind)
+    try:
+        for seed in (1, 2, 3):
+            l, r = S.stereo_pair(480, 752, seed)
+            _, kl, dl = exl(l, (0, 0))
+            _, kr, dr = exr(r, (0, 0))
+            ol(l, (0, 0))
+            orr(r, (0, 0))
+            L, R = _frame(kl, dl, 752, 480), _frame(kr, dr, 752, 480)
+            pl = [ol.level(i, 19) for i in range(8)]
+            pr = [orr.level(i, 19) for i in range(8)]
+            for mb, mbf in ((40.0 * 0.11, 435.2 * 0.11 * 1.0), (1.0, 60.0), (0.5, 200.0)):
+                u, d = matcher.ComputeStereoMatches(L, R, exl.device_pyramid(), exr.device_pyramid(), mb, mbf)
+                ou, od, nacc = mo.compute_stereo_matches(L, R, pl, pr, mb, mbf)
+                assert np.array_equal(u.view(np.uint32), ou.view(np.uint32)), (seed, mb, mbf)
+                assert np.array_equal(d.view(np.uint32), od.view(np.uint32)), (seed, mb, mbf)
+            assert (u >= 0).sum() > 100  # the synthetic pair has real row-aligned matches
+    finally:
+        exl.close()
+        exr.close()
