@@ -56,6 +56,27 @@ __device__ __forceinline__ void oct_warp_partition(const uint32_t* __restrict__ 
                                                    uint32_t cnt, int mx, int my, uint32_t c[4]) {
     const int lane = orbx_lane();
     const uint32_t lt = orbx_lanemask_lt();
+    if (cnt <= 32) {
+        // one key per lane: counts and stable ranks from the same four ballots
+        uint32_t key = 0;
+        int q = 4;
+        if ((uint32_t)lane < cnt) {
+            key = src[start + lane];
+            q = oct_quadrant(key, mx, my);
+        }
+        uint32_t m[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            m[k] = __ballot_sync(ORBX_FULL, q == k);
+            c[k] = __popc(m[k]);
+        }
+        if (q < 4) {
+            const uint32_t base = start + (q > 0 ? c[0] : 0) + (q > 1 ? c[1] : 0) + (q > 2 ? c[2] : 0);
+            const uint32_t mine = q == 0 ? m[0] : q == 1 ? m[1] : q == 2 ? m[2] : m[3];
+            dst[base + __popc(mine & lt)] = key;
+        }
+        return;
+    }
     c[0] = c[1] = c[2] = c[3] = 0;
     for (uint32_t b = 0; b < cnt; b += 32) {
         const uint32_t i = b + lane;
@@ -350,10 +371,11 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
         C.buf[0] = keysA + (size_t)frame * P.keys_total + L.key_off;
         C.buf[1] = keysB + (size_t)frame * P.keys_total + L.key_off;
     }
-    for (int c = warp; c < ncells; c += OCT_WARPS) {
+    // thread per cell: a cell holds a handful of keys, and all cells' loads are in flight at once
+    for (int c = tid; c < ncells; c += OCT_THREADS) {
         const uint32_t o = cofs[c], n = cofs[c + 1] - o;
         const uint32_t* s = ckeys + (size_t)c * L.cell_cap;
-        for (uint32_t k = lane; k < n; k += 32) C.buf[0][o + k] = s[k];
+        for (uint32_t k = 0; k < n; ++k) C.buf[0][o + k] = s[k];
     }
     __syncthreads();
 
@@ -435,10 +457,24 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
     // ---- best response per node, first maximum wins (:738-758) --------------------------------
     uint32_t* out = surv + (size_t)frame * P.surv_total + L.surv_off;
     const int Sout = min(S, L.surv_cap);
-    for (int i = warp; i < Sout; i += OCT_WARPS) {
+    // thread per node (a final node holds a few keys); nodes with many keys take a warp each
+    for (int i = tid; i < Sout; i += OCT_THREADS) {
+        const uint32_t cnt = C.ncn[cur][i];
+        if (cnt > 64) continue;
         const uint32_t st = C.nst[cur][i];
         const uint32_t* src = C.buf[st >> 31] + (st & 0x7fffffffu);
+        uint32_t bestk = src[0];
+        for (uint32_t k = 1; k < cnt; ++k) {
+            const uint32_t v = src[k];
+            if ((v >> 24) > (bestk >> 24)) bestk = v;   // strict '>': the first maximum wins
+        }
+        out[i] = bestk;
+    }
+    for (int i = warp; i < Sout; i += OCT_WARPS) {
         const uint32_t cnt = C.ncn[cur][i];
+        if (cnt <= 64) continue;
+        const uint32_t st = C.nst[cur][i];
+        const uint32_t* src = C.buf[st >> 31] + (st & 0x7fffffffu);
         unsigned long long best = 0;
         for (uint32_t k = lane; k < cnt; k += 32) {
             const unsigned long long v = ((unsigned long long)(src[k] >> 24) << 32) |
