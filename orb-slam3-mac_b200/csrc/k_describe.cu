@@ -21,6 +21,8 @@
 //                The blurred patch lives only in shared memory (never written to HBM); lane i
 //                samples its 16 pattern points from it (cvRound by the 1.5*2^23 magic add) and
 //                produces descriptor byte i.
+#include <mutex>
+
 #include "orbx_device.cuh"
 
 #ifndef DESC_WARPS
@@ -31,11 +33,35 @@
 #define DESC_S_WORDS (44 * DESC_SP)      // 43 rows + one the last (unused) odd output row reads
 #define DESC_B_WORDS (38 * DESC_BP)
 #define DESC_WARP_WORDS (DESC_S_WORDS + DESC_B_WORDS)
-#define DESC_SMEM_BYTES ((DESC_WARPS * DESC_WARP_WORDS + 8 * 32 * 4) * 4)
+#define DESC_SMEM_BYTES (DESC_WARPS * DESC_WARP_WORDS * 4)
 
 __device__ const int8_t g_pattern[1024] = {
 #include "orb_pattern.inc"
 };
+
+// The pattern as floats, lane-major per comparison: g_pat4[k * 32 + i] = points 16i + 2k and
+// 16i + 2k + 1 (x0, y0, x1, y1) -- what lane i needs for bit k of descriptor byte i.  Filled once
+// per device by k_init_pattern; read through L1 (one coalesced 512-byte request per comparison).
+__device__ float4 g_pat4[256];
+
+__global__ void k_init_pattern() {
+    const int e = threadIdx.x, k = e >> 5, i = e & 31;
+    const uint32_t w = reinterpret_cast<const uint32_t*>(g_pattern)[8 * i + k];
+    g_pat4[e] = make_float4((float)(int8_t)(w & 0xff), (float)(int8_t)((w >> 8) & 0xff),
+                            (float)(int8_t)((w >> 16) & 0xff), (float)(int8_t)(w >> 24));
+}
+
+// PTX shifts clamp the amount: anything >= 32 yields 0 (C++ << / >> would be undefined)
+__device__ __forceinline__ uint32_t desc_shl(uint32_t x, uint32_t n) {
+    uint32_t r;
+    asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(n));
+    return r;
+}
+__device__ __forceinline__ uint32_t desc_shr(uint32_t x, uint32_t n) {
+    uint32_t r;
+    asm("shr.u32 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(n));
+    return r;
+}
 
 __device__ __forceinline__ int reflect101(int p, int len) {
     if (p < 0) p = -p;
@@ -126,18 +152,7 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
            const int32_t* __restrict__ header, const uint32_t* __restrict__ dest,
            orbx_keypoint* __restrict__ kps, uint8_t* __restrict__ desc) {
     extern __shared__ __align__(16) uint32_t sm[];
-    float4* pat4 = reinterpret_cast<float4*>(sm);  // [8][32]: comparison k of lane i
     const int warp = orbx_warp(), lane = orbx_lane();
-    {
-        // pattern points 16*lane + 2k, 16*lane + 2k + 1 = one aligned word of the int8 table
-        for (int e = threadIdx.x; e < 256; e += DESC_WARPS * 32) {
-            const int k = e >> 5, i = e & 31;
-            const uint32_t w = reinterpret_cast<const uint32_t*>(g_pattern)[8 * i + k];
-            pat4[e] = make_float4((float)(int8_t)(w & 0xff), (float)(int8_t)((w >> 8) & 0xff),
-                                  (float)(int8_t)((w >> 16) & 0xff), (float)(int8_t)(w >> 24));
-        }
-    }
-    __syncthreads();
     const int frame = blockIdx.y;
     const int idx = blockIdx.x * DESC_WARPS + warp;
 
@@ -151,7 +166,7 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
     const OrbxLevel& L = P.lvl[l];
     const int cx = ORBX_KEY_X(key) + ORBX_FAST_BORDER, cy = ORBX_KEY_Y(key) + ORBX_FAST_BORDER;
 
-    uint32_t* S = sm + 8 * 32 * 4 + warp * DESC_WARP_WORDS;  // staged source rows, DESC_SP words each
+    uint32_t* S = sm + warp * DESC_WARP_WORDS;  // staged source rows, DESC_SP words each
     int lpitch;
     const uint8_t* src = orbx_level_ptr(P, isrc, pyr, frame, l, &lpitch);
 
@@ -193,16 +208,16 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
         const int v = lane - 15;
         const int av = v < 0 ? -v : v;
         const int d = (int)((0x3689ABCDDEEEFFFFull >> (4 * av)) & 15ull);  // umax[|v|], :452-467
-        const int lo = xo + 21 - d, hi = xo + 21 + d;                      // staged byte columns
-        const int j0 = lo >> 2, j1 = hi >> 2;
+        const int lo8 = 8 * (xo + 21 - d), hi8 = 8 * (xo + 21 + d);   // staged byte columns [lo, hi], in bits
         const uint32_t* row = S + (21 + v) * DESC_SP;
-        // weight of staged byte b is b - xo - 21 + 32
-        uint32_t uw = (uint32_t)(11 - xo) * 0x01010101u + 0x03020100u + 0x04040404u * (uint32_t)j0;
+        // weight of staged byte b is b - xo - 21 + 32; the disc spans words 1..9 of a staged row
+        uint32_t uw = (uint32_t)(11 - xo) * 0x01010101u + 0x03020100u + 0x04040404u;
         uint32_t rs = 0, mu = 0;
-        for (int j = j0; j <= j1; ++j, uw += 0x04040404u) {
-            uint32_t w = row[j];
-            if (j == j0) w &= 0xffffffffu << (8 * (lo & 3));
-            if (j == j1) w &= 0xffffffffu >> (8 * (3 - (hi & 3)));
+#pragma unroll
+        for (int j = 1; j <= 9; ++j, uw += 0x04040404u) {
+            // keep the bytes of word j that lie in [lo, hi]: PTX shifts clamp (>= 32 gives 0)
+            const uint32_t w = row[j] & desc_shl(0xffffffffu, (uint32_t)max(lo8 - 32 * j, 0)) &
+                               desc_shr(0xffffffffu, (uint32_t)max(32 * j + 24 - hi8, 0));
             rs = __dp4a(w, 0x01010101u, rs);
             mu = __dp4a(w, uw, mu);
         }
@@ -284,7 +299,7 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
     uint32_t byte = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const float4 p = pat4[k * 32 + lane];
+        const float4 p = __ldg(&g_pat4[k * 32 + lane]);
         const uint32_t y0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(p.x, b), __fmul_rn(p.y, a)), MAGIC));
         const uint32_t x0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, b)), MAGIC));
         const uint32_t y1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(p.z, b), __fmul_rn(p.w, a)), MAGIC));
@@ -327,11 +342,20 @@ cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const ui
                                  orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
                                  int* launches) {
     dim3 grid((P.surv_total + DESC_WARPS - 1) / DESC_WARPS, nframes);
-    static bool configured = false;  // per process; the attribute is per function and device-wide
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, DESC_SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        configured = true;
+    // once per device: shared-memory opt-in and the float pattern table
+    static std::mutex mu;
+    static bool ready[64] = {false};
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        std::lock_guard<std::mutex> lk(mu);
+        if (dev >= 0 && dev < 64 && !ready[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(k_describe, cudaFuncAttributeMaxDynamicSharedMemorySize, DESC_SMEM_BYTES);
+            if (e != cudaSuccess) return e;
+            k_init_pattern<<<1, 256, 0, st>>>();
+            if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
+            ready[dev] = true;
+        }
     }
     k_describe<<<grid, DESC_WARPS * 32, DESC_SMEM_BYTES, st>>>(P, src, pyr, header, dest, kps, desc);
     ++*launches;

@@ -27,7 +27,9 @@
 #define OCT_SMEM_KB 36
 #endif
 #define OCT_WARPS (OCT_THREADS / 32)
+#ifndef OCT_BIG
 #define OCT_BIG 1024
+#endif
 #define OCT_MAX_INI 8
 
 struct OctCtx {

@@ -240,8 +240,12 @@ k_resize_rows_async(const __grid_constant__ RzArgs A) {
     uint32_t ro = (uint32_t)s * (uint32_t)A.spitch;
     const uint32_t ro_max = (uint32_t)(A.sh - 1) * (uint32_t)A.spitch;
     const uint32_t ring_sa = (uint32_t)__cvta_generic_to_shared(ring);
-    const uint32_t cp_sa = ring_sa + 16 * lane;          // this lane's 16-byte chunk of slot 0
-    const uint32_t wa_sa = ring_sa + 4 * wa, wb_sa = ring_sa + 4 * wb;
+    uint32_t cp_sa = ring_sa + 16 * lane;                // this lane's 16-byte chunk of slot 0
+    uint32_t wa_sa = ring_sa + 4 * wa, wb_sa = ring_sa + 4 * wb;
+    uint32_t spitch_r = (uint32_t)A.spitch;
+    // opaque to the compiler: otherwise it rematerialises the shared-window address arithmetic
+    // (S2R + LEA chain) inside every step of the loop
+    asm volatile("" : "+r"(cp_sa), "+r"(wa_sa), "+r"(wb_sa), "+r"(spitch_r));
     const bool copier = lane < nchunk;
     uint32_t ioff = (uint32_t)(s & (RZ_DEPTH - 1)) * (RZ_SLOT_WORDS * 4);  // slot being staged
     uint32_t soff = ioff;                                                  // slot being consumed
@@ -251,7 +255,7 @@ k_resize_rows_async(const __grid_constant__ RzArgs A) {
     {                                                                                       \
         if (copier) rz_cp16(cp_sa + ioff, gsrc + ro);                                       \
         rz_commit();                                                                        \
-        ro = min(ro + (uint32_t)A.spitch, ro_max);                                          \
+        ro = min(ro + spitch_r, ro_max);                                                    \
         ioff = (ioff + RZ_SLOT_WORDS * 4) & ring_mask;                                      \
     }
 #pragma unroll
