@@ -270,7 +270,7 @@ __device__ __forceinline__ int fast_nms_emit(const FastWarpSmem& s, int sp, int 
 }
 
 #ifndef FAST_MINB
-#define FAST_MINB 10
+#define FAST_MINB 8
 #endif
 __global__ void __launch_bounds__(FAST_WARPS * 32, FAST_MINB)
 k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t* __restrict__ pyr,

@@ -63,7 +63,7 @@ public:
         }
         // mvImagePyramid (read by Frame::ComputeStereoMatches, src/Frame.cc:809-918): ROI views into
         // buffers with the reference's 19-px BORDER_REFLECT_101 frame
-        for (int l = 0; l < nlevels; ++l) {
+        for (int l = 0; l < nlevels && mbCopyPyramid; ++l) {
             int lw = 0, lh = 0;
             orbx_level_size(handle, image.cols, image.rows, l, &lw, &lh);
             cv::Mat temp(lh + 38, lw + 38, CV_8UC1);
@@ -81,6 +81,13 @@ public:
     std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
 
     std::vector<cv::Mat> mvImagePyramid;
+
+    // Additions of the B200 build (not in the reference class).  Handle(): the C-ABI handle, for
+    // same-GPU consumers of the device-resident pyramid (orbx_device_pyramid ->
+    // orbm_compute_stereo_matches).  mbCopyPyramid = false skips the per-frame
+    // host copy of mvImagePyramid once Frame::ComputeStereoMatches runs on the device.
+    orbx_handle* Handle() const { return handle; }
+    bool mbCopyPyramid = true;
 
 protected:
     void ensure(int w, int h) {
