@@ -177,15 +177,17 @@ k_resize_rows(const __grid_constant__ RzArgs A) {
 }
 
 // ---- cp.async-staged variant ------------------------------------------------------------------
-// Same arithmetic and walk as k_resize_rows, but the source rows a warp needs (its 128 output
-// columns = <= 256 source bytes) are streamed into a per-warp shared-memory ring by 16-byte
-// cp.async.cg copies, RZ_DEPTH rows ahead of their use, so that DRAM latency is covered by ~1.5 KB
-// of loads in flight per warp instead of two dependent row loads.  Needs 16-byte aligned source
-// rows (always true for pyramid levels; level 0 when the caller's pitch allows it).
+// Same arithmetic and walk as k_resize_rows, with PX = 4 or 8 adjacent output columns per thread,
+// but the source rows a warp needs (its 32*PX output columns = <= 256 / 384 source bytes) are
+// streamed into a per-warp shared-memory ring by 16-byte cp.async.cg copies, RZ_DEPTH-1 rows
+// ahead of their use, so that DRAM latency is covered by ~1 KB of loads in flight per warp
+// instead of two dependent row loads.  PX = 8 halves the per-row bookkeeping per pixel (ring
+// wait, copy issue, row-table lookup, stores) and is used when the level is wide enough to fill
+// the lanes.  Needs 16-byte aligned source rows (always true for pyramid levels; level 0 when
+// the caller's pitch allows it).
 #ifndef RZ_DEPTH
 #define RZ_DEPTH 4
 #endif
-#define RZ_SLOT_WORDS 64   // 256 B per staged row segment
 
 __device__ __forceinline__ void rz_cp16(uint32_t saddr, const void* g) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
@@ -194,41 +196,44 @@ __device__ __forceinline__ void rz_commit() { asm volatile("cp.async.commit_grou
 template <int N>
 __device__ __forceinline__ void rz_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-__global__ void __launch_bounds__(256)
-k_resize_rows_async(const __grid_constant__ RzArgs A) {
-    __shared__ __align__(16) uint32_t ring_all[8 * RZ_DEPTH * RZ_SLOT_WORDS];
-    const int lane = threadIdx.x & 31;
-    const int gw = blockIdx.x * 8 + (threadIdx.x >> 5);   // warp -> (band, column chunk)
-    const int band = gw / A.warps_x, wx = gw - band * A.warps_x;
-    if (band >= A.nbands) return;
-    uint32_t* ring = ring_all + (threadIdx.x >> 5) * (RZ_DEPTH * RZ_SLOT_WORDS);
-    const int x0 = (wx * 32 + lane) * 4;
-    const bool live = x0 < A.dw;              // dead lanes still help with the copies
-    const int xc = live ? x0 : ((A.dw - 1) & ~3);
+template <int PX>
+struct RzCfg {
+    static constexpr int SLOT_BYTES = PX == 4 ? 256 : 384;   // staged segment of one source row
+    static constexpr int PAIRS = PX / 2;
+};
 
-    int sx[4];
-    uint32_t cf[4], sel[4];
+// One warp: 32*PX output columns starting at xbase, output rows of `band`.
+template <int PX>
+__device__ __forceinline__ void rz_walk(const RzArgs& A, int band, int xbase, uint8_t* ring) {
+    constexpr int SLOT = RzCfg<PX>::SLOT_BYTES, NP = RzCfg<PX>::PAIRS;
+    const int lane = threadIdx.x & 31;
+    const int x0 = xbase + lane * PX;
+    const bool live = x0 < A.dw;              // dead lanes still help with the copies
+    const int xc = live ? x0 : xbase + ((A.dw - 1 - xbase) / PX) * PX;
+
+    int sx[PX];
+    uint32_t cf[PX], sel[PX];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < PX; ++k) {
         const int x = min(xc + k, A.dw - 1);
         sx[k] = A.xofs[x];
         cf[k] = A.xa[x];
     }
+    // Word pair (w, w+1) of each pixel pair, kept inside the row's valid words; S[sx] sits at byte
+    // offset o <= 7 of the pair and S[sx+1] at o+1 (o+1 == 8 only for sx == sw-1: coefficient 0).
     const int wlast = (A.sw - 1) >> 2;
-    int wa = min(sx[0] >> 2, wlast - 1), wb = min(sx[2] >> 2, wlast - 1);
-    {
-        const int o0 = sx[0] - 4 * wa, o1 = sx[1] - 4 * wa, o2 = sx[2] - 4 * wb, o3 = sx[3] - 4 * wb;
-        sel[0] = (uint32_t)o0 | ((uint32_t)min(o0 + 1, 7) << 4);
-        sel[1] = (uint32_t)o1 | ((uint32_t)min(o1 + 1, 7) << 4);
-        sel[2] = (uint32_t)o2 | ((uint32_t)min(o2 + 1, 7) << 4);
-        sel[3] = (uint32_t)o3 | ((uint32_t)min(o3 + 1, 7) << 4);
+    int wp[NP];
+#pragma unroll
+    for (int q = 0; q < NP; ++q) {
+        wp[q] = min(sx[2 * q] >> 2, wlast - 1);
+        const int o0 = sx[2 * q] - 4 * wp[q], o1 = sx[2 * q + 1] - 4 * wp[q];
+        sel[2 * q] = (uint32_t)o0 | ((uint32_t)min(o0 + 1, 7) << 4);
+        sel[2 * q + 1] = (uint32_t)o1 | ((uint32_t)min(o1 + 1, 7) << 4);
     }
     // staged segment of a source row: 16-byte chunks [c0, c0 + nchunk) covering every lane's words
-    const int w_first = __shfl_sync(ORBX_FULL, wa, 0) & ~3;
-    const int w_end = __reduce_max_sync(ORBX_FULL, wb + 2);       // one past the last word needed
-    const int nchunk = min((w_end - w_first + 3) >> 2, RZ_SLOT_WORDS / 4);
-    wa -= w_first;
-    wb -= w_first;
+    const int w_first = __shfl_sync(ORBX_FULL, wp[0], 0) & ~3;
+    const int w_end = __reduce_max_sync(ORBX_FULL, wp[NP - 1] + 2);   // one past the last word needed
+    const int nchunk = min((w_end - w_first + 3) >> 2, SLOT / 16);
 
     const int y0 = band * RZ_ROWS, y1 = min(y0 + RZ_ROWS, A.dh);
     uint8_t* drow = A.dst + (size_t)blockIdx.y * A.dst_fstride + (size_t)y0 * A.dpitch + xc;
@@ -241,41 +246,61 @@ k_resize_rows_async(const __grid_constant__ RzArgs A) {
     const uint32_t ro_max = (uint32_t)(A.sh - 1) * (uint32_t)A.spitch;
     const uint32_t ring_sa = (uint32_t)__cvta_generic_to_shared(ring);
     uint32_t cp_sa = ring_sa + 16 * lane;                // this lane's 16-byte chunk of slot 0
-    uint32_t wa_sa = ring_sa + 4 * wa, wb_sa = ring_sa + 4 * wb;
+    uint32_t wsa[NP];
+#pragma unroll
+    for (int q = 0; q < NP; ++q) wsa[q] = ring_sa + 4 * (wp[q] - w_first);
     uint32_t spitch_r = (uint32_t)A.spitch;
     // opaque to the compiler: otherwise it rematerialises the shared-window address arithmetic
     // (S2R + LEA chain) inside every step of the loop
-    asm volatile("" : "+r"(cp_sa), "+r"(wa_sa), "+r"(wb_sa), "+r"(spitch_r));
+    asm volatile("" : "+r"(cp_sa), "+r"(spitch_r));
+#pragma unroll
+    for (int q = 0; q < NP; ++q) asm volatile("" : "+r"(wsa[q]));
     const bool copier = lane < nchunk;
-    uint32_t ioff = (uint32_t)(s & (RZ_DEPTH - 1)) * (RZ_SLOT_WORDS * 4);  // slot being staged
-    uint32_t soff = ioff;                                                  // slot being consumed
-    const uint32_t ring_mask = (RZ_DEPTH - 1) * (RZ_SLOT_WORDS * 4);
+    uint32_t ioff = (uint32_t)(s % RZ_DEPTH) * SLOT;     // slot being staged
+    uint32_t soff = ioff;                                // slot being consumed
 
 #define RZ_ISSUE()                                                                          \
     {                                                                                       \
         if (copier) rz_cp16(cp_sa + ioff, gsrc + ro);                                       \
         rz_commit();                                                                        \
         ro = min(ro + spitch_r, ro_max);                                                    \
-        ioff = (ioff + RZ_SLOT_WORDS * 4) & ring_mask;                                      \
+        ioff += SLOT;                                                                       \
+        if (ioff == RZ_DEPTH * SLOT) ioff = 0;                                              \
     }
 #pragma unroll
     for (int i = 0; i < RZ_DEPTH - 1; ++i) RZ_ISSUE()
 
-    uint32_t E[4], O[4], W[4];
+    uint32_t E[PX], O[PX], W[PX];
 #define RZ_LDS(dst, addr) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(dst) : "r"(addr))
 #define RZ_STEP(CUR, PREV)                                                                  \
     {                                                                                       \
         rz_wait<RZ_DEPTH - 2>();                                                            \
         __syncwarp();                                                                       \
-        RZ_LDS(W[0], wa_sa + soff);                                                         \
-        RZ_LDS(W[1], wa_sa + soff + 4);                                                     \
-        RZ_LDS(W[2], wb_sa + soff);                                                         \
-        RZ_LDS(W[3], wb_sa + soff + 4);                                                     \
-        soff = (soff + RZ_SLOT_WORDS * 4) & ring_mask;                                      \
+        _Pragma("unroll") for (int q = 0; q < NP; ++q) {                                    \
+            RZ_LDS(W[2 * q], wsa[q] + soff);                                                \
+            RZ_LDS(W[2 * q + 1], wsa[q] + soff + 4);                                        \
+        }                                                                                   \
+        soff += SLOT;                                                                       \
+        if (soff == RZ_DEPTH * SLOT) soff = 0;                                              \
         RZ_ISSUE()                                                                          \
-        rz_hrow(W, sel, cf, CUR);                                                           \
+        _Pragma("unroll") for (int q = 0; q < NP; ++q) {                                    \
+            CUR[2 * q] = __dp2a_lo(cf[2 * q], __byte_perm(W[2 * q], W[2 * q + 1], sel[2 * q]), 0u) >> 4;             \
+            CUR[2 * q + 1] = __dp2a_lo(cf[2 * q + 1], __byte_perm(W[2 * q], W[2 * q + 1], sel[2 * q + 1]), 0u) >> 4; \
+        }                                                                                   \
         if ((int)yt.x + 1 == s) {                                                           \
-            if (live) rz_emit(drow, yt.y, PREV, CUR);                                       \
+            if (live) {                                                                     \
+                const uint32_t b0 = yt.y << 16, b1 = yt.y & 0xffff0000u;                    \
+                uint32_t o[PX / 4];                                                         \
+                _Pragma("unroll") for (int g = 0; g < PX / 4; ++g) {                        \
+                    uint32_t t[4];                                                          \
+                    _Pragma("unroll") for (int k = 0; k < 4; ++k)                           \
+                        t[k] = __umulhi(b0, PREV[4 * g + k]) + (__umulhi(b1, CUR[4 * g + k]) + 2u); \
+                    o[g] = __byte_perm(__byte_perm(t[0], t[1], 0x5410) >> 2,                \
+                                       __byte_perm(t[2], t[3], 0x5410) >> 2, 0x6420);       \
+                }                                                                           \
+                if (PX == 4) *reinterpret_cast<uint32_t*>(drow) = o[0];                     \
+                else *reinterpret_cast<uint2*>(drow) = make_uint2(o[0], o[PX / 4 - 1]);     \
+            }                                                                               \
             if (++y >= y1) break;                                                           \
             drow += A.dpitch;                                                               \
             yt = __ldg(++yp);                                                               \
@@ -291,6 +316,19 @@ k_resize_rows_async(const __grid_constant__ RzArgs A) {
 #undef RZ_STEP
 #undef RZ_ISSUE
     rz_wait<0>();
+}
+
+// warps_x = n8 + n4 warps per band: the first n8 take 256 columns each (8 per thread), the rest
+// 128 columns each (4 per thread), so that a level's width never leaves most of a warp idle.
+__global__ void __launch_bounds__(256)
+k_resize_rows_async(const __grid_constant__ RzArgs A, int n8) {
+    __shared__ __align__(16) uint8_t ring_all[8 * RZ_DEPTH * RzCfg<8>::SLOT_BYTES];
+    const int gw = blockIdx.x * 8 + (threadIdx.x >> 5);   // warp -> (band, column chunk)
+    const int band = gw / A.warps_x, wx = gw - band * A.warps_x;
+    if (band >= A.nbands) return;
+    uint8_t* ring = ring_all + (threadIdx.x >> 5) * (RZ_DEPTH * RzCfg<8>::SLOT_BYTES);
+    if (wx < n8) rz_walk<8>(A, band, wx * 256, ring);
+    else rz_walk<4>(A, band, n8 * 256 + (wx - n8) * 128, ring);
 }
 
 void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes, cudaStream_t st, int* launches) {
@@ -309,12 +347,16 @@ void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, in
             A.xa = reinterpret_cast<const uint32_t*>(D.xa);
             A.ytab = D.ytab;
             A.sw = S.w; A.sh = S.h; A.dw = D.w; A.dh = D.h;
-            A.warps_x = (D.w + 127) / 128;
             A.nbands = (D.h + RZ_ROWS - 1) / RZ_ROWS;
-            dim3 grid((A.warps_x * A.nbands + 7) / 8, nframes);
             const bool aligned = ((uintptr_t)A.src % 16 == 0) && (A.spitch % 16 == 0) && (A.src_fstride % 16 == 0);
-            if (aligned && D.x_step_max <= 2 && (double)S.w / D.w <= 1.7)
-                k_resize_rows_async<<<grid, 256, 0, st>>>(A);
+            const double ratio = (double)S.w / D.w;
+            const bool async_ok = aligned && D.x_step_max <= 2 && ratio <= 1.7;
+            // 8 columns per thread need the 384-byte slot: 256 * ratio + 32 bytes
+            const int n8 = (async_ok && ratio <= 1.35) ? D.w / 256 : 0;
+            A.warps_x = async_ok ? n8 + (D.w - 256 * n8 + 127) / 128 : (D.w + 127) / 128;
+            dim3 grid((A.warps_x * A.nbands + 7) / 8, nframes);
+            if (async_ok)
+                k_resize_rows_async<<<grid, 256, 0, st>>>(A, n8);
             else
                 k_resize_rows<<<grid, 256, 0, st>>>(A);
         } else {
