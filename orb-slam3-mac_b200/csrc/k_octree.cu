@@ -39,7 +39,9 @@ struct OctCtx {
     uint32_t* ncn[2];  // key count
     uint32_t* cc;      // [4 * NC] child counts by processing index
     uint32_t* proc;    // [NC] list positions in processing order
-    uint32_t* expand[2];  // [NC] list positions of multi-key children, creation order
+    uint32_t* expand[2];  // [NC] each: multi-key children in creation order (full passes: creation
+                          // indices, ping-ponged; careful passes: list positions in expand[0])
+    uint32_t* done;    // [NC] key locations of the single-key nodes retired by the full passes
     uint32_t* aux;     // [NC + 1] packed scans
     uint32_t* flag;    // [NC + 1] processed flags / kept ranks
     unsigned long long* sortk;  // [NCP2]
@@ -175,35 +177,143 @@ __device__ __forceinline__ void oct_block_partition(const OctCtx& C, const uint3
 // shared scalars inside C.tmp
 #define OT_EPROC 40
 #define OT_NBIG 41
+#define OT_BIGNEXT 43
+
+// Exclusive scan of a[0..n) by the whole CTA, one barrier when n <= OCT_THREADS.  Returns the total.
+// The caller must put a barrier between this call and the next use of C.tmp[0..OCT_WARPS) or any
+// read of a[] by a thread other than the one that owns the element (thread i owns a[i]).
+__device__ __forceinline__ uint32_t oct_scan(uint32_t* a, int n, uint32_t* tmp) {
+    if (n > OCT_THREADS) return block_excl_scan(a, n, tmp);
+    const int t = threadIdx.x;
+    const uint32_t v = t < n ? a[t] : 0u;
+    const uint32_t incl = warp_incl_scan(v);
+    if (orbx_lane() == 31) tmp[orbx_warp()] = incl;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < OCT_WARPS; ++w) {
+        const uint32_t x = tmp[w];
+        base += w < orbx_warp() ? x : 0u;
+        tot += x;
+    }
+    if (t < n) a[t] = base + incl - v;
+    return tot;
+}
+
+__device__ __forceinline__ uint32_t oct_child_code(const uint32_t c[4]) {
+    uint32_t v = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) v += (c[q] > 0 ? 1u : 0u) + (c[q] > 1 ? 0x10000u : 0u);
+    return v;
+}
+
+// Full pass (:597-661) in CREATION-ORDER form.  While only full passes run, the list is always
+//     reverse(children of the last pass, creation order) ++ reverse(done[0..Dbefore))
+// because the untouched nodes of a full pass are exactly the single-key ones, which the reference
+// leaves in place behind the push_front()ed children.  So a pass needs no list positions at all:
+// the children go to nb/nst/ncn[nxt] by creation index, the multi-key ones are listed in
+// expand[nxt], the single-key ones are appended to done[].  Processing order = list order =
+// expand[cur] backwards.  Three barriers per pass.
+// In: E multi-key nodes of the previous pass.  Out: M children, *nm of them multi-key;
+// done[D .. D + M - *nm) appended.
+__device__ __forceinline__ int oct_full_pass(const OctCtx& C, int cur, int E, int D, bool maybe_big,
+                                             int* nm) {
+    const int nxt = cur ^ 1;
+    const int tid = threadIdx.x, lane = orbx_lane(), warp = orbx_warp();
+    const uint32_t* mul = C.expand[cur];
+    if (maybe_big) {
+        for (int j = 0; j < E; ++j) {   // CTA-uniform
+            const int i = mul[E - 1 - j];
+            const uint32_t cnt = C.ncn[cur][i];
+            if (cnt < OCT_BIG) continue;
+            const short4 bb = C.nb[cur][i];
+            const uint32_t st = C.nst[cur][i];
+            const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
+            oct_block_partition<0>(C, C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu, cnt, 4, mx,
+                                   my, 0.f, &C.cc[4 * j]);
+            if (tid == 0) C.aux[j] = oct_child_code(&C.cc[4 * j]);
+        }
+    }
+    for (int j = warp; j < E; j += OCT_WARPS) {
+        const int i = mul[E - 1 - j];
+        const uint32_t cnt = C.ncn[cur][i];
+        if (cnt >= OCT_BIG) continue;
+        const short4 bb = C.nb[cur][i];
+        const uint32_t st = C.nst[cur][i];
+        const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
+        uint32_t c[4];
+        oct_warp_partition(C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu, cnt, mx, my, c);
+        if (lane == 0) {
+            C.cc[4 * j] = c[0]; C.cc[4 * j + 1] = c[1]; C.cc[4 * j + 2] = c[2]; C.cc[4 * j + 3] = c[3];
+            C.aux[j] = oct_child_code(c);
+        }
+    }
+    __syncthreads();
+    if (tid == 0) C.tmp[OT_BIGNEXT] = 0;
+    const uint32_t tot = oct_scan(C.aux, E, C.tmp);
+    const int M = (int)(tot & 0xffffu);
+    *nm = (int)(tot >> 16);
+    if (E > OCT_THREADS) __syncthreads();
+    for (int j = tid; j < E; j += OCT_THREADS) {
+        const int i = mul[E - 1 - j];
+        const short4 bb = C.nb[cur][i];
+        const uint32_t st = C.nst[cur][i];
+        const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
+        uint32_t run = (st & 0x7fffffffu);
+        const uint32_t bit = (st & 0x80000000u) ^ 0x80000000u;
+        int cidx = (int)(C.aux[j] & 0xffffu);
+        int midx = (int)(C.aux[j] >> 16);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t c = C.cc[4 * j + q];
+            if (c > 0) {
+                short4 nbv;
+                nbv.x = (q & 1) ? mx : bb.x;
+                nbv.y = (q & 1) ? bb.y : mx;
+                nbv.z = (q & 2) ? my : bb.z;
+                nbv.w = (q & 2) ? bb.w : my;
+                C.nb[nxt][cidx] = nbv;
+                C.nst[nxt][cidx] = run | bit;
+                C.ncn[nxt][cidx] = c;
+                if (c > 1) {
+                    C.expand[nxt][midx++] = cidx;
+                    if (c >= OCT_BIG) C.tmp[OT_BIGNEXT] = 1;
+                } else {
+                    C.done[D + cidx - midx] = run | bit;
+                }
+                ++cidx;
+            }
+            run += c;
+        }
+    }
+    __syncthreads();
+    return M;
+}
 
 // One pass over the nodes proc[0..E) of list `cur` (S nodes).  Builds list cur^1.
 // careful == true applies the reference's early stop "size >= N" (:730-731).
 // Returns the new list size; *n_multi = number of multi-key children created (nToExpand).
 __device__ __forceinline__ int oct_pass(const OctCtx& C, int cur, int S, int E, bool careful, int N,
-                                        int* n_multi) {
+                                        int* n_multi, bool maybe_big) {
     const int nxt = cur ^ 1;
     const int tid = threadIdx.x, lane = orbx_lane(), warp = orbx_warp();
-    uint32_t* biglist = reinterpret_cast<uint32_t*>(C.sortk);
 
-    // ---- (a) split every node of the pass: stable 4-way partition into the other buffer
-    if (tid == 0) {
-        C.tmp[OT_NBIG] = 0;
-        C.tmp[OT_EPROC] = (uint32_t)E;
+    // ---- (a) split every node of the pass: stable 4-way partition into the other buffer;
+    //      aux[j] = #children | #multi-key children << 16
+    if (maybe_big) {
+        for (int j = 0; j < E; ++j) {   // CTA-uniform
+            const int i = C.proc[j];
+            const uint32_t cnt = C.ncn[cur][i];
+            if (cnt < OCT_BIG) continue;
+            const short4 bb = C.nb[cur][i];
+            const uint32_t st = C.nst[cur][i];
+            const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
+            oct_block_partition<0>(C, C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu, cnt, 4, mx,
+                                   my, 0.f, &C.cc[4 * j]);
+            if (tid == 0) C.aux[j] = oct_child_code(&C.cc[4 * j]);
+        }
     }
-    __syncthreads();
-    for (int j = tid; j < E; j += OCT_THREADS)
-        if (C.ncn[cur][C.proc[j]] >= OCT_BIG) biglist[atomicAdd(&C.tmp[OT_NBIG], 1u)] = j;
-    __syncthreads();
-    const int nbig = (int)C.tmp[OT_NBIG];
-    for (int b = 0; b < nbig; ++b) {
-        const int j = biglist[b];
-        const int i = C.proc[j];
-        const short4 bb = C.nb[cur][i];
-        const uint32_t st = C.nst[cur][i];
-        const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
-        oct_block_partition<0>(C, C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu,
-                               C.ncn[cur][i], 4, mx, my, 0.f, &C.cc[4 * j]);
-    }
+    if (tid == 0) C.tmp[OT_EPROC] = (uint32_t)E;
     for (int j = warp; j < E; j += OCT_WARPS) {
         const int i = C.proc[j];
         const uint32_t cnt = C.ncn[cur][i];
@@ -213,23 +323,17 @@ __device__ __forceinline__ int oct_pass(const OctCtx& C, int cur, int S, int E, 
         const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
         uint32_t c[4];
         oct_warp_partition(C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu, cnt, mx, my, c);
-        if (lane < 4) C.cc[4 * j + lane] = lane == 0 ? c[0] : lane == 1 ? c[1] : lane == 2 ? c[2] : c[3];
+        if (lane == 0) {
+            C.cc[4 * j] = c[0]; C.cc[4 * j + 1] = c[1]; C.cc[4 * j + 2] = c[2]; C.cc[4 * j + 3] = c[3];
+            C.aux[j] = oct_child_code(c);
+        }
     }
     __syncthreads();
 
-    // ---- (b) creation indices: exclusive scan of (#children | #multi-key children << 16)
-    for (int j = tid; j < E; j += OCT_THREADS) {
-        uint32_t v = 0;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const uint32_t c = C.cc[4 * j + q];
-            v += (c > 0 ? 1u : 0u) + (c > 1 ? 0x10000u : 0u);
-        }
-        C.aux[j] = v;
-    }
-    __syncthreads();
-    const uint32_t tot = block_excl_scan(C.aux, E, C.tmp);
+    // ---- (b) creation indices: exclusive scan; early stop "size >= N" of the careful pass
+    const uint32_t tot = oct_scan(C.aux, E, C.tmp);
     if (tid == 0) C.aux[E] = tot;
+    if (E > OCT_THREADS) __syncthreads();
     if (careful) {
         for (int j = tid; j < E; j += OCT_THREADS) {
             uint32_t nch = 0;
@@ -239,17 +343,16 @@ __device__ __forceinline__ int oct_pass(const OctCtx& C, int cur, int S, int E, 
             if (size_after >= N) atomicMin(&C.tmp[OT_EPROC], (uint32_t)(j + 1));
         }
     }
+    for (int i = tid; i < S; i += OCT_THREADS) C.flag[i] = 1;
     __syncthreads();
     const int Eproc = (int)C.tmp[OT_EPROC];
     const int M = (int)(C.aux[Eproc] & 0xffffu);
     *n_multi = (int)(C.aux[Eproc] >> 16);
 
     // ---- (c) rank of the untouched nodes
-    for (int i = tid; i < S; i += OCT_THREADS) C.flag[i] = 1;
-    __syncthreads();
     for (int j = tid; j < Eproc; j += OCT_THREADS) C.flag[C.proc[j]] = 0;
     __syncthreads();
-    const uint32_t kept = block_excl_scan(C.flag, S, C.tmp);
+    const uint32_t kept = oct_scan(C.flag, S, C.tmp);
     if (tid == 0) C.flag[S] = kept;
     __syncthreads();
 
@@ -315,6 +418,37 @@ __device__ __forceinline__ void oct_bitonic_desc(unsigned long long* a, int P2) 
     }
 }
 
+// proc[0..E) = the expandable nodes expand[0][0..E) sorted by (key count, creation order), largest
+// first (:680-682).  Small E: every thread ranks one element by counting the larger keys
+// (unique keys -> a permutation), one barrier instead of a bitonic network.
+__device__ __forceinline__ void oct_sort_expandable(const OctCtx& C, int cur, int E, int NCP2) {
+    const int tid = threadIdx.x;
+    if (E <= 2 * OCT_THREADS) {
+        for (int e = tid; e < E; e += OCT_THREADS)
+            C.sortk[e] = ((unsigned long long)C.ncn[cur][C.expand[0][e]] << 32) | (unsigned long long)(uint32_t)(e + 1);
+        __syncthreads();
+        for (int e = tid; e < E; e += OCT_THREADS) {
+            const unsigned long long mine = C.sortk[e];
+            int r = 0;
+            for (int k = 0; k < E; ++k) r += C.sortk[k] > mine ? 1 : 0;
+            C.proc[r] = C.expand[0][e];
+        }
+        __syncthreads();
+        return;
+    }
+    for (int e = tid; e < NCP2; e += OCT_THREADS)
+        C.sortk[e] = e < E ? (((unsigned long long)C.ncn[cur][C.expand[0][e]] << 32) |
+                              (unsigned long long)(uint32_t)(e + 1))
+                           : 0ull;
+    __syncthreads();
+    int P2 = 1;
+    while (P2 < E) P2 <<= 1;
+    oct_bitonic_desc(C.sortk, P2);
+    for (int j = tid; j < E; j += OCT_THREADS)
+        C.proc[j] = C.expand[0][(uint32_t)(C.sortk[j] & 0xffffffffull) - 1u];
+    __syncthreads();
+}
+
 // Shared memory carve-up (words).  NC = node capacity, NCP2 = next power of two >= NC,
 // CW = max(4 * NC, cells_max + 1) (cc[] doubles as the cell-offset table during the gather).
 __host__ __device__ inline size_t oct_fixed_words(int NC, int NCP2, int CW) {
@@ -322,7 +456,7 @@ __host__ __device__ inline size_t oct_fixed_words(int NC, int NCP2, int CW) {
            + 2 * NC + 2 * NC       // nst[2], ncn[2]
            + CW                    // cc / cell offsets
            + NC                    // proc
-           + NC                    // expand
+           + 3 * NC                // expand[2], done
            + (NC + 2) + (NC + 2)   // aux, flag
            + 2 * (size_t)NCP2      // sortk (u64)
            + OCT_WARPS * 8 + 64;   // wc, tmp
@@ -349,7 +483,9 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
     C.ncn[1] = p; p += NC;
     C.cc = p; p += CW;
     C.proc = p; p += NC;
-    C.expand[0] = p; C.expand[1] = p; p += NC;
+    C.expand[0] = p; p += NC;
+    C.expand[1] = p; p += NC;
+    C.done = p; p += NC;
     C.aux = p; p += NC + 2;
     C.flag = p; p += NC + 2;
     C.wc = p; p += OCT_WARPS * 8;
@@ -388,71 +524,86 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
     (void)Wd;
     uint32_t* rootcnt = C.tmp + 48;  // 8 words
     oct_block_partition<1>(C, C.buf[0], C.buf[1], 0, nk, nIni, 0, 0, L.hx, rootcnt);
-    int S = 0;
+    // roots in creation order = reversed list order (the list is rev(creation) ++ rev(done))
     if (tid == 0) {
-        uint32_t run = 0;
-        int s = 0;
-        for (int i = 0; i < nIni; ++i) {
+        uint32_t start[OCT_MAX_INI + 1];
+        start[0] = 0;
+        for (int i = 0; i < nIni; ++i) start[i + 1] = start[i] + rootcnt[i];
+        int s = 0, m = 0, d = 0;
+        for (int i = nIni - 1; i >= 0; --i) {
             const uint32_t c = rootcnt[i];
-            if (c > 0) {
-                short4 b;
-                b.x = (short)(int)(L.hx * (float)i);
-                b.y = (short)(int)(L.hx * (float)(i + 1));
-                b.z = 0;
-                b.w = (short)Hd;
-                C.nb[0][s] = b;
-                C.nst[0][s] = run | 0x80000000u;  // keys now live in buf[1]
-                C.ncn[0][s] = c;
-                ++s;
-            }
-            run += c;
+            if (c == 0) continue;
+            short4 b;
+            b.x = (short)(int)(L.hx * (float)i);
+            b.y = (short)(int)(L.hx * (float)(i + 1));
+            b.z = 0;
+            b.w = (short)Hd;
+            C.nb[0][s] = b;
+            C.nst[0][s] = start[i] | 0x80000000u;  // keys now live in buf[1]
+            C.ncn[0][s] = c;
+            if (c > 1) C.expand[0][m++] = (uint32_t)s;
+            else C.done[d++] = start[i] | 0x80000000u;
+            ++s;
         }
         C.tmp[42] = (uint32_t)s;
+        C.tmp[44] = (uint32_t)m;
     }
     __syncthreads();
-    S = (int)C.tmp[42];
+    int M = (int)C.tmp[42];   // children of the last pass (creation-order arrays [cur])
+    int E = (int)C.tmp[44];   // ... of which multi-key
+    int Dbefore = 0;          // done[] entries older than that pass
+    int S = M;
     int cur = 0;
+    bool maybe_big = nk >= OCT_BIG;
 
-    // ---- main loop (:583-736) -----------------------------------------------------------------
-    bool finish = false;
-    while (!finish) {
-        const int prevS = S;
-        // full pass: every multi-key node, in list order
-        for (int i = tid; i < S; i += OCT_THREADS) C.flag[i] = C.ncn[cur][i] > 1 ? 1u : 0u;
-        __syncthreads();
-        const int E = (int)block_excl_scan(C.flag, S, C.tmp);
-        if (tid == 0) C.flag[S] = (uint32_t)E;
-        __syncthreads();
-        for (int i = tid; i < S; i += OCT_THREADS)
-            if (C.flag[i + 1] != C.flag[i]) C.proc[C.flag[i]] = i;
-        __syncthreads();
-        int nToExpand = 0;
-        S = oct_pass(C, cur, S, E, false, N, &nToExpand);
+    // ---- full passes (:583-661), list kept implicit -------------------------------------------
+    bool careful = false;
+    while (true) {
+        const int D = Dbefore + M - E;
+        int nm = 0;
+        const int Mn = oct_full_pass(C, cur, E, D, maybe_big, &nm);
+        const int Sn = S - E + Mn;
+        const bool stalled = Sn == S;
+        maybe_big = maybe_big && C.tmp[OT_BIGNEXT] != 0;
         cur ^= 1;
-        if (S >= N || S == prevS) {
-            finish = true;
-        } else if (S + 3 * nToExpand > N) {
-            int Ecur = nToExpand;
-            while (!finish) {
-                const int prev2 = S;
-                // sort the expandable nodes by (key count, creation order), largest first
-                for (int e = tid; e < NCP2; e += OCT_THREADS)
-                    C.sortk[e] = e < Ecur ? (((unsigned long long)C.ncn[cur][C.expand[0][e]] << 32) |
-                                             (unsigned long long)(uint32_t)(e + 1))
-                                          : 0ull;
-                __syncthreads();
-                int P2 = 1;
-                while (P2 < Ecur) P2 <<= 1;
-                oct_bitonic_desc(C.sortk, P2);
-                for (int j = tid; j < Ecur; j += OCT_THREADS)
-                    C.proc[j] = C.expand[0][(uint32_t)(C.sortk[j] & 0xffffffffull) - 1u];
-                __syncthreads();
-                int nm = 0;
-                S = oct_pass(C, cur, S, Ecur, true, N, &nm);
-                cur ^= 1;
-                Ecur = nm;
-                if (S >= N || S == prev2) finish = true;
+        S = Sn; M = Mn; E = nm; Dbefore = D;
+        if (S >= N || stalled) break;
+        if (S + 3 * E > N) {
+            careful = true;
+            break;
+        }
+    }
+    // ---- materialise the list: rev(children) ++ rev(done) into the free array set ---------------
+    {
+        const int nxt = cur ^ 1;
+        for (int p2 = tid; p2 < S; p2 += OCT_THREADS) {
+            if (p2 < M) {
+                const int c = M - 1 - p2;
+                C.nb[nxt][p2] = C.nb[cur][c];
+                C.nst[nxt][p2] = C.nst[cur][c];
+                C.ncn[nxt][p2] = C.ncn[cur][c];
+            } else {
+                C.nst[nxt][p2] = C.done[Dbefore - 1 - (p2 - M)];
+                C.ncn[nxt][p2] = 1;
             }
+        }
+        for (int e = tid; e < E; e += OCT_THREADS) C.expand[0][e] = (uint32_t)(M - 1) - C.expand[cur][e];
+        __syncthreads();
+        cur = nxt;
+    }
+
+    // ---- careful passes (:663-736) --------------------------------------------------------------
+    if (careful) {
+        int Ecur = E;
+        bool finish = false;
+        while (!finish) {
+            const int prev2 = S;
+            oct_sort_expandable(C, cur, Ecur, NCP2);
+            int nm = 0;
+            S = oct_pass(C, cur, S, Ecur, true, N, &nm, nk >= OCT_BIG);
+            cur ^= 1;
+            Ecur = nm;
+            if (S >= N || S == prev2) finish = true;
         }
     }
 
