@@ -31,15 +31,25 @@
 #define OCT_BIG 1024
 #endif
 #define OCT_MAX_INI 8
+#ifndef OCT_MINB
+#define OCT_MINB 4
+#endif
 
 struct OctCtx {
     // node list, double buffered (index = list position)
-    short4* nb[2];
-    uint32_t* nst[2];  // key range start | buffer bit << 31
-    uint32_t* ncn[2];  // key count
+    // (pairs are picked with a select, never indexed: a dynamically indexed pointer array would
+    // put the whole context into local memory)
+    short4 *nb0, *nb1;
+    uint32_t *nst0, *nst1;  // key range start | buffer bit << 31
+    uint32_t *ncn0, *ncn1;  // key count
+    __device__ __forceinline__ short4* nb(int i) const { return i ? nb1 : nb0; }
+    __device__ __forceinline__ uint32_t* nst(int i) const { return i ? nst1 : nst0; }
+    __device__ __forceinline__ uint32_t* ncn(int i) const { return i ? ncn1 : ncn0; }
+    __device__ __forceinline__ uint32_t* expand(int i) const { return i ? ex1 : ex0; }
+    __device__ __forceinline__ uint32_t* buf(uint32_t i) const { return i ? buf1 : buf0; }
     uint32_t* cc;      // [4 * NC] child counts by processing index
     uint32_t* proc;    // [NC] list positions in processing order
-    uint32_t* expand[2];  // [NC] each: multi-key children in creation order (full passes: creation
+    uint32_t *ex0, *ex1;  // [NC] each: multi-key children in creation order (full passes: creation
                           // indices, ping-ponged; careful passes: list positions in expand[0])
     uint32_t* done;    // [NC] key locations of the single-key nodes retired by the full passes
     uint32_t* aux;     // [NC + 1] packed scans
@@ -47,7 +57,7 @@ struct OctCtx {
     unsigned long long* sortk;  // [NCP2]
     uint32_t* wc;      // [OCT_WARPS * 8] per-warp bin counts for CTA-wide partitions
     uint32_t* tmp;     // [64] scan scratch + scalars
-    uint32_t* buf[2];  // key buffers
+    uint32_t *buf0, *buf1;  // key buffers
 };
 
 __device__ __forceinline__ int oct_quadrant(uint32_t key, int mx, int my) {
@@ -220,29 +230,29 @@ __device__ __forceinline__ int oct_full_pass(const OctCtx& C, int cur, int E, in
                                              int* nm) {
     const int nxt = cur ^ 1;
     const int tid = threadIdx.x, lane = orbx_lane(), warp = orbx_warp();
-    const uint32_t* mul = C.expand[cur];
+    const uint32_t* mul = C.expand(cur);
     if (maybe_big) {
         for (int j = 0; j < E; ++j) {   // CTA-uniform
             const int i = mul[E - 1 - j];
-            const uint32_t cnt = C.ncn[cur][i];
+            const uint32_t cnt = C.ncn(cur)[i];
             if (cnt < OCT_BIG) continue;
-            const short4 bb = C.nb[cur][i];
-            const uint32_t st = C.nst[cur][i];
+            const short4 bb = C.nb(cur)[i];
+            const uint32_t st = C.nst(cur)[i];
             const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
-            oct_block_partition<0>(C, C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu, cnt, 4, mx,
+            oct_block_partition<0>(C, C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, 4, mx,
                                    my, 0.f, &C.cc[4 * j]);
             if (tid == 0) C.aux[j] = oct_child_code(&C.cc[4 * j]);
         }
     }
     for (int j = warp; j < E; j += OCT_WARPS) {
         const int i = mul[E - 1 - j];
-        const uint32_t cnt = C.ncn[cur][i];
+        const uint32_t cnt = C.ncn(cur)[i];
         if (cnt >= OCT_BIG) continue;
-        const short4 bb = C.nb[cur][i];
-        const uint32_t st = C.nst[cur][i];
+        const short4 bb = C.nb(cur)[i];
+        const uint32_t st = C.nst(cur)[i];
         const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
         uint32_t c[4];
-        oct_warp_partition(C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu, cnt, mx, my, c);
+        oct_warp_partition(C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, mx, my, c);
         if (lane == 0) {
             C.cc[4 * j] = c[0]; C.cc[4 * j + 1] = c[1]; C.cc[4 * j + 2] = c[2]; C.cc[4 * j + 3] = c[3];
             C.aux[j] = oct_child_code(c);
@@ -256,8 +266,8 @@ __device__ __forceinline__ int oct_full_pass(const OctCtx& C, int cur, int E, in
     if (E > OCT_THREADS) __syncthreads();
     for (int j = tid; j < E; j += OCT_THREADS) {
         const int i = mul[E - 1 - j];
-        const short4 bb = C.nb[cur][i];
-        const uint32_t st = C.nst[cur][i];
+        const short4 bb = C.nb(cur)[i];
+        const uint32_t st = C.nst(cur)[i];
         const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
         uint32_t run = (st & 0x7fffffffu);
         const uint32_t bit = (st & 0x80000000u) ^ 0x80000000u;
@@ -272,11 +282,11 @@ __device__ __forceinline__ int oct_full_pass(const OctCtx& C, int cur, int E, in
                 nbv.y = (q & 1) ? bb.y : mx;
                 nbv.z = (q & 2) ? my : bb.z;
                 nbv.w = (q & 2) ? bb.w : my;
-                C.nb[nxt][cidx] = nbv;
-                C.nst[nxt][cidx] = run | bit;
-                C.ncn[nxt][cidx] = c;
+                C.nb(nxt)[cidx] = nbv;
+                C.nst(nxt)[cidx] = run | bit;
+                C.ncn(nxt)[cidx] = c;
                 if (c > 1) {
-                    C.expand[nxt][midx++] = cidx;
+                    C.expand(nxt)[midx++] = cidx;
                     if (c >= OCT_BIG) C.tmp[OT_BIGNEXT] = 1;
                 } else {
                     C.done[D + cidx - midx] = run | bit;
@@ -303,12 +313,12 @@ __device__ __forceinline__ int oct_pass(const OctCtx& C, int cur, int S, int E, 
     if (maybe_big) {
         for (int j = 0; j < E; ++j) {   // CTA-uniform
             const int i = C.proc[j];
-            const uint32_t cnt = C.ncn[cur][i];
+            const uint32_t cnt = C.ncn(cur)[i];
             if (cnt < OCT_BIG) continue;
-            const short4 bb = C.nb[cur][i];
-            const uint32_t st = C.nst[cur][i];
+            const short4 bb = C.nb(cur)[i];
+            const uint32_t st = C.nst(cur)[i];
             const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
-            oct_block_partition<0>(C, C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu, cnt, 4, mx,
+            oct_block_partition<0>(C, C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, 4, mx,
                                    my, 0.f, &C.cc[4 * j]);
             if (tid == 0) C.aux[j] = oct_child_code(&C.cc[4 * j]);
         }
@@ -316,13 +326,13 @@ __device__ __forceinline__ int oct_pass(const OctCtx& C, int cur, int S, int E, 
     if (tid == 0) C.tmp[OT_EPROC] = (uint32_t)E;
     for (int j = warp; j < E; j += OCT_WARPS) {
         const int i = C.proc[j];
-        const uint32_t cnt = C.ncn[cur][i];
+        const uint32_t cnt = C.ncn(cur)[i];
         if (cnt >= OCT_BIG) continue;
-        const short4 bb = C.nb[cur][i];
-        const uint32_t st = C.nst[cur][i];
+        const short4 bb = C.nb(cur)[i];
+        const uint32_t st = C.nst(cur)[i];
         const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
         uint32_t c[4];
-        oct_warp_partition(C.buf[st >> 31], C.buf[(st >> 31) ^ 1], st & 0x7fffffffu, cnt, mx, my, c);
+        oct_warp_partition(C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, mx, my, c);
         if (lane == 0) {
             C.cc[4 * j] = c[0]; C.cc[4 * j + 1] = c[1]; C.cc[4 * j + 2] = c[2]; C.cc[4 * j + 3] = c[3];
             C.aux[j] = oct_child_code(c);
@@ -359,8 +369,8 @@ __device__ __forceinline__ int oct_pass(const OctCtx& C, int cur, int S, int E, 
     // ---- (d) new list = reverse(creation order) ++ untouched nodes
     for (int j = tid; j < Eproc; j += OCT_THREADS) {
         const int i = C.proc[j];
-        const short4 bb = C.nb[cur][i];
-        const uint32_t st = C.nst[cur][i];
+        const short4 bb = C.nb(cur)[i];
+        const uint32_t st = C.nst(cur)[i];
         const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
         uint32_t run = (st & 0x7fffffffu);
         const uint32_t bit = (st & 0x80000000u) ^ 0x80000000u;
@@ -376,10 +386,10 @@ __device__ __forceinline__ int oct_pass(const OctCtx& C, int cur, int S, int E, 
                 nbv.y = (q & 1) ? bb.y : mx;
                 nbv.z = (q & 2) ? my : bb.z;
                 nbv.w = (q & 2) ? bb.w : my;
-                C.nb[nxt][pos] = nbv;
-                C.nst[nxt][pos] = run | bit;
-                C.ncn[nxt][pos] = c;
-                if (c > 1) C.expand[0][midx++] = pos;
+                C.nb(nxt)[pos] = nbv;
+                C.nst(nxt)[pos] = run | bit;
+                C.ncn(nxt)[pos] = c;
+                if (c > 1) C.expand(0)[midx++] = pos;
                 ++cidx;
             }
             run += c;
@@ -389,9 +399,9 @@ __device__ __forceinline__ int oct_pass(const OctCtx& C, int cur, int S, int E, 
         const uint32_t r = C.flag[i];
         if (C.flag[i + 1] != r) {
             const int pos = M + (int)r;
-            C.nb[nxt][pos] = C.nb[cur][i];
-            C.nst[nxt][pos] = C.nst[cur][i];
-            C.ncn[nxt][pos] = C.ncn[cur][i];
+            C.nb(nxt)[pos] = C.nb(cur)[i];
+            C.nst(nxt)[pos] = C.nst(cur)[i];
+            C.ncn(nxt)[pos] = C.ncn(cur)[i];
         }
     }
     __syncthreads();
@@ -425,19 +435,19 @@ __device__ __forceinline__ void oct_sort_expandable(const OctCtx& C, int cur, in
     const int tid = threadIdx.x;
     if (E <= 2 * OCT_THREADS) {
         for (int e = tid; e < E; e += OCT_THREADS)
-            C.sortk[e] = ((unsigned long long)C.ncn[cur][C.expand[0][e]] << 32) | (unsigned long long)(uint32_t)(e + 1);
+            C.sortk[e] = ((unsigned long long)C.ncn(cur)[C.expand(0)[e]] << 32) | (unsigned long long)(uint32_t)(e + 1);
         __syncthreads();
         for (int e = tid; e < E; e += OCT_THREADS) {
             const unsigned long long mine = C.sortk[e];
             int r = 0;
             for (int k = 0; k < E; ++k) r += C.sortk[k] > mine ? 1 : 0;
-            C.proc[r] = C.expand[0][e];
+            C.proc[r] = C.expand(0)[e];
         }
         __syncthreads();
         return;
     }
     for (int e = tid; e < NCP2; e += OCT_THREADS)
-        C.sortk[e] = e < E ? (((unsigned long long)C.ncn[cur][C.expand[0][e]] << 32) |
+        C.sortk[e] = e < E ? (((unsigned long long)C.ncn(cur)[C.expand(0)[e]] << 32) |
                               (unsigned long long)(uint32_t)(e + 1))
                            : 0ull;
     __syncthreads();
@@ -445,7 +455,7 @@ __device__ __forceinline__ void oct_sort_expandable(const OctCtx& C, int cur, in
     while (P2 < E) P2 <<= 1;
     oct_bitonic_desc(C.sortk, P2);
     for (int j = tid; j < E; j += OCT_THREADS)
-        C.proc[j] = C.expand[0][(uint32_t)(C.sortk[j] & 0xffffffffull) - 1u];
+        C.proc[j] = C.expand(0)[(uint32_t)(C.sortk[j] & 0xffffffffull) - 1u];
     __syncthreads();
 }
 
@@ -462,7 +472,7 @@ __host__ __device__ inline size_t oct_fixed_words(int NC, int NCP2, int CW) {
            + OCT_WARPS * 8 + 64;   // wc, tmp
 }
 
-__global__ void __launch_bounds__(OCT_THREADS)
+__global__ void __launch_bounds__(OCT_THREADS, OCT_MINB)
 k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcnt,
          const uint32_t* __restrict__ cellkeys, uint32_t* __restrict__ keysA,
          uint32_t* __restrict__ keysB, uint32_t* __restrict__ surv, uint32_t* __restrict__ survcnt,
@@ -475,16 +485,16 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
     OctCtx C;
     uint32_t* p = sm;
     C.sortk = reinterpret_cast<unsigned long long*>(p); p += 2 * (size_t)NCP2;
-    C.nb[0] = reinterpret_cast<short4*>(p); p += 2 * NC;
-    C.nb[1] = reinterpret_cast<short4*>(p); p += 2 * NC;
-    C.nst[0] = p; p += NC;
-    C.nst[1] = p; p += NC;
-    C.ncn[0] = p; p += NC;
-    C.ncn[1] = p; p += NC;
+    C.nb0 = reinterpret_cast<short4*>(p); p += 2 * NC;
+    C.nb1 = reinterpret_cast<short4*>(p); p += 2 * NC;
+    C.nst0 = p; p += NC;
+    C.nst1 = p; p += NC;
+    C.ncn0 = p; p += NC;
+    C.ncn1 = p; p += NC;
     C.cc = p; p += CW;
     C.proc = p; p += NC;
-    C.expand[0] = p; p += NC;
-    C.expand[1] = p; p += NC;
+    C.ex0 = p; p += NC;
+    C.ex1 = p; p += NC;
     C.done = p; p += NC;
     C.aux = p; p += NC + 2;
     C.flag = p; p += NC + 2;
@@ -503,17 +513,17 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
     if (tid == 0) cofs[ncells] = nk;
     __syncthreads();
     if ((int)nk <= key_words) {
-        C.buf[0] = smkeys;
-        C.buf[1] = smkeys + key_words;
+        C.buf0 = smkeys;
+        C.buf1 = smkeys + key_words;
     } else {
-        C.buf[0] = keysA + (size_t)frame * P.keys_total + L.key_off;
-        C.buf[1] = keysB + (size_t)frame * P.keys_total + L.key_off;
+        C.buf0 = keysA + (size_t)frame * P.keys_total + L.key_off;
+        C.buf1 = keysB + (size_t)frame * P.keys_total + L.key_off;
     }
     // thread per cell: a cell holds a handful of keys, and all cells' loads are in flight at once
     for (int c = tid; c < ncells; c += OCT_THREADS) {
         const uint32_t o = cofs[c], n = cofs[c + 1] - o;
         const uint32_t* s = ckeys + (size_t)c * L.cell_cap;
-        for (uint32_t k = 0; k < n; ++k) C.buf[0][o + k] = s[k];
+        for (uint32_t k = 0; k < n; ++k) C.buf0[o + k] = s[k];
     }
     __syncthreads();
 
@@ -523,26 +533,25 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
     const int Wd = L.max_bx - ORBX_FAST_BORDER, Hd = L.max_by - ORBX_FAST_BORDER;
     (void)Wd;
     uint32_t* rootcnt = C.tmp + 48;  // 8 words
-    oct_block_partition<1>(C, C.buf[0], C.buf[1], 0, nk, nIni, 0, 0, L.hx, rootcnt);
+    oct_block_partition<1>(C, C.buf0, C.buf1, 0, nk, nIni, 0, 0, L.hx, rootcnt);
     // roots in creation order = reversed list order (the list is rev(creation) ++ rev(done))
     if (tid == 0) {
-        uint32_t start[OCT_MAX_INI + 1];
-        start[0] = 0;
-        for (int i = 0; i < nIni; ++i) start[i + 1] = start[i] + rootcnt[i];
+        uint32_t start = nk;
         int s = 0, m = 0, d = 0;
         for (int i = nIni - 1; i >= 0; --i) {
             const uint32_t c = rootcnt[i];
+            start -= c;
             if (c == 0) continue;
             short4 b;
             b.x = (short)(int)(L.hx * (float)i);
             b.y = (short)(int)(L.hx * (float)(i + 1));
             b.z = 0;
             b.w = (short)Hd;
-            C.nb[0][s] = b;
-            C.nst[0][s] = start[i] | 0x80000000u;  // keys now live in buf[1]
-            C.ncn[0][s] = c;
-            if (c > 1) C.expand[0][m++] = (uint32_t)s;
-            else C.done[d++] = start[i] | 0x80000000u;
+            C.nb(0)[s] = b;
+            C.nst0[s] = start | 0x80000000u;  // keys now live in buf[1]
+            C.ncn(0)[s] = c;
+            if (c > 1) C.expand(0)[m++] = (uint32_t)s;
+            else C.done[d++] = start | 0x80000000u;
             ++s;
         }
         C.tmp[42] = (uint32_t)s;
@@ -579,15 +588,15 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
         for (int p2 = tid; p2 < S; p2 += OCT_THREADS) {
             if (p2 < M) {
                 const int c = M - 1 - p2;
-                C.nb[nxt][p2] = C.nb[cur][c];
-                C.nst[nxt][p2] = C.nst[cur][c];
-                C.ncn[nxt][p2] = C.ncn[cur][c];
+                C.nb(nxt)[p2] = C.nb(cur)[c];
+                C.nst(nxt)[p2] = C.nst(cur)[c];
+                C.ncn(nxt)[p2] = C.ncn(cur)[c];
             } else {
-                C.nst[nxt][p2] = C.done[Dbefore - 1 - (p2 - M)];
-                C.ncn[nxt][p2] = 1;
+                C.nst(nxt)[p2] = C.done[Dbefore - 1 - (p2 - M)];
+                C.ncn(nxt)[p2] = 1;
             }
         }
-        for (int e = tid; e < E; e += OCT_THREADS) C.expand[0][e] = (uint32_t)(M - 1) - C.expand[cur][e];
+        for (int e = tid; e < E; e += OCT_THREADS) C.expand(0)[e] = (uint32_t)(M - 1) - C.expand(cur)[e];
         __syncthreads();
         cur = nxt;
     }
@@ -600,7 +609,7 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
             const int prev2 = S;
             oct_sort_expandable(C, cur, Ecur, NCP2);
             int nm = 0;
-            S = oct_pass(C, cur, S, Ecur, true, N, &nm, nk >= OCT_BIG);
+            S = oct_pass(C, cur, S, Ecur, true, N, &nm, maybe_big);
             cur ^= 1;
             Ecur = nm;
             if (S >= N || S == prev2) finish = true;
@@ -612,10 +621,10 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
     const int Sout = min(S, L.surv_cap);
     // thread per node (a final node holds a few keys); nodes with many keys take a warp each
     for (int i = tid; i < Sout; i += OCT_THREADS) {
-        const uint32_t cnt = C.ncn[cur][i];
+        const uint32_t cnt = C.ncn(cur)[i];
         if (cnt > 64) continue;
-        const uint32_t st = C.nst[cur][i];
-        const uint32_t* src = C.buf[st >> 31] + (st & 0x7fffffffu);
+        const uint32_t st = C.nst(cur)[i];
+        const uint32_t* src = C.buf(st >> 31) + (st & 0x7fffffffu);
         uint32_t bestk = src[0];
         for (uint32_t k = 1; k < cnt; ++k) {
             const uint32_t v = src[k];
@@ -624,10 +633,10 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
         out[i] = bestk;
     }
     for (int i = warp; i < Sout; i += OCT_WARPS) {
-        const uint32_t cnt = C.ncn[cur][i];
+        const uint32_t cnt = C.ncn(cur)[i];
         if (cnt <= 64) continue;
-        const uint32_t st = C.nst[cur][i];
-        const uint32_t* src = C.buf[st >> 31] + (st & 0x7fffffffu);
+        const uint32_t st = C.nst(cur)[i];
+        const uint32_t* src = C.buf(st >> 31) + (st & 0x7fffffffu);
         unsigned long long best = 0;
         for (uint32_t k = lane; k < cnt; k += 32) {
             const unsigned long long v = ((unsigned long long)(src[k] >> 24) << 32) |
