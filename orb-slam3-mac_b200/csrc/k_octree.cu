@@ -217,6 +217,75 @@ __device__ __forceinline__ uint32_t oct_child_code(const uint32_t c[4]) {
     return v;
 }
 
+#ifndef OCT_SMALL
+#define OCT_SMALL 8
+#endif
+
+// Stable 4-way partition of a node with <= OCT_SMALL keys by ONE thread: counts and running
+// offsets are four byte lanes of one word.  Returns the packed counts.
+__device__ __forceinline__ uint32_t oct_thread_partition(const uint32_t* __restrict__ src,
+                                                         uint32_t* __restrict__ dst, uint32_t start,
+                                                         uint32_t cnt, int mx, int my) {
+    uint32_t cpack = 0;
+    for (uint32_t t = 0; t < cnt; ++t) cpack += 1u << (8 * oct_quadrant(src[start + t], mx, my));
+    uint32_t opack = (cpack << 8) + (cpack << 16) + (cpack << 24);   // exclusive prefix per byte lane
+    for (uint32_t t = 0; t < cnt; ++t) {
+        const uint32_t key = src[start + t];
+        const int sh = 8 * oct_quadrant(key, mx, my);
+        dst[start + ((opack >> sh) & 0xffu)] = key;
+        opack += 1u << sh;
+    }
+    return cpack;
+}
+
+// Step (a) of a pass: split the E nodes order[j] (reversed: order[E-1-j]) of array set `cur` by a
+// stable 4-way partition of their key ranges into the other key buffer; cc[4j..4j+3] = child
+// counts, aux[j] = #children | #multi-key children << 16.  Nodes with >= OCT_BIG keys take the
+// whole CTA, nodes with <= OCT_SMALL keys one thread, the rest one warp.  No trailing barrier.
+__device__ __forceinline__ void oct_split_nodes(const OctCtx& C, int cur, int E, bool maybe_big,
+                                                const uint32_t* order, bool reversed) {
+    const int tid = threadIdx.x, lane = orbx_lane(), warp = orbx_warp();
+    if (maybe_big) {
+        for (int j = 0; j < E; ++j) {   // CTA-uniform
+            const int i = order[reversed ? E - 1 - j : j];
+            const uint32_t cnt = C.ncn(cur)[i];
+            if (cnt < OCT_BIG) continue;
+            const short4 bb = C.nb(cur)[i];
+            const uint32_t st = C.nst(cur)[i];
+            const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
+            oct_block_partition<0>(C, C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, 4, mx,
+                                   my, 0.f, &C.cc[4 * j]);
+            if (tid == 0) C.aux[j] = oct_child_code(&C.cc[4 * j]);
+        }
+    }
+    for (int j = warp; j < E; j += OCT_WARPS) {
+        const int i = order[reversed ? E - 1 - j : j];
+        const uint32_t cnt = C.ncn(cur)[i];
+        if (cnt >= OCT_BIG || cnt <= OCT_SMALL) continue;
+        const short4 bb = C.nb(cur)[i];
+        const uint32_t st = C.nst(cur)[i];
+        const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
+        uint32_t c[4];
+        oct_warp_partition(C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, mx, my, c);
+        if (lane == 0) {
+            C.cc[4 * j] = c[0]; C.cc[4 * j + 1] = c[1]; C.cc[4 * j + 2] = c[2]; C.cc[4 * j + 3] = c[3];
+            C.aux[j] = oct_child_code(c);
+        }
+    }
+    for (int j = tid; j < E; j += OCT_THREADS) {
+        const int i = order[reversed ? E - 1 - j : j];
+        const uint32_t cnt = C.ncn(cur)[i];
+        if (cnt > OCT_SMALL) continue;
+        const short4 bb = C.nb(cur)[i];
+        const uint32_t st = C.nst(cur)[i];
+        const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
+        const uint32_t cp = oct_thread_partition(C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, mx, my);
+        uint32_t c[4] = {cp & 0xffu, (cp >> 8) & 0xffu, (cp >> 16) & 0xffu, cp >> 24};
+        C.cc[4 * j] = c[0]; C.cc[4 * j + 1] = c[1]; C.cc[4 * j + 2] = c[2]; C.cc[4 * j + 3] = c[3];
+        C.aux[j] = oct_child_code(c);
+    }
+}
+
 // Full pass (:597-661) in CREATION-ORDER form.  While only full passes run, the list is always
 //     reverse(children of the last pass, creation order) ++ reverse(done[0..Dbefore))
 // because the untouched nodes of a full pass are exactly the single-key ones, which the reference
@@ -231,33 +300,7 @@ __device__ __forceinline__ int oct_full_pass(const OctCtx& C, int cur, int E, in
     const int nxt = cur ^ 1;
     const int tid = threadIdx.x, lane = orbx_lane(), warp = orbx_warp();
     const uint32_t* mul = C.expand(cur);
-    if (maybe_big) {
-        for (int j = 0; j < E; ++j) {   // CTA-uniform
-            const int i = mul[E - 1 - j];
-            const uint32_t cnt = C.ncn(cur)[i];
-            if (cnt < OCT_BIG) continue;
-            const short4 bb = C.nb(cur)[i];
-            const uint32_t st = C.nst(cur)[i];
-            const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
-            oct_block_partition<0>(C, C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, 4, mx,
-                                   my, 0.f, &C.cc[4 * j]);
-            if (tid == 0) C.aux[j] = oct_child_code(&C.cc[4 * j]);
-        }
-    }
-    for (int j = warp; j < E; j += OCT_WARPS) {
-        const int i = mul[E - 1 - j];
-        const uint32_t cnt = C.ncn(cur)[i];
-        if (cnt >= OCT_BIG) continue;
-        const short4 bb = C.nb(cur)[i];
-        const uint32_t st = C.nst(cur)[i];
-        const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
-        uint32_t c[4];
-        oct_warp_partition(C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, mx, my, c);
-        if (lane == 0) {
-            C.cc[4 * j] = c[0]; C.cc[4 * j + 1] = c[1]; C.cc[4 * j + 2] = c[2]; C.cc[4 * j + 3] = c[3];
-            C.aux[j] = oct_child_code(c);
-        }
-    }
+    oct_split_nodes(C, cur, E, maybe_big, mul, true);
     __syncthreads();
     if (tid == 0) C.tmp[OT_BIGNEXT] = 0;
     const uint32_t tot = oct_scan(C.aux, E, C.tmp);
@@ -310,34 +353,8 @@ __device__ __forceinline__ int oct_pass(const OctCtx& C, int cur, int S, int E, 
 
     // ---- (a) split every node of the pass: stable 4-way partition into the other buffer;
     //      aux[j] = #children | #multi-key children << 16
-    if (maybe_big) {
-        for (int j = 0; j < E; ++j) {   // CTA-uniform
-            const int i = C.proc[j];
-            const uint32_t cnt = C.ncn(cur)[i];
-            if (cnt < OCT_BIG) continue;
-            const short4 bb = C.nb(cur)[i];
-            const uint32_t st = C.nst(cur)[i];
-            const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
-            oct_block_partition<0>(C, C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, 4, mx,
-                                   my, 0.f, &C.cc[4 * j]);
-            if (tid == 0) C.aux[j] = oct_child_code(&C.cc[4 * j]);
-        }
-    }
     if (tid == 0) C.tmp[OT_EPROC] = (uint32_t)E;
-    for (int j = warp; j < E; j += OCT_WARPS) {
-        const int i = C.proc[j];
-        const uint32_t cnt = C.ncn(cur)[i];
-        if (cnt >= OCT_BIG) continue;
-        const short4 bb = C.nb(cur)[i];
-        const uint32_t st = C.nst(cur)[i];
-        const int mx = bb.x + ((bb.y - bb.x + 1) >> 1), my = bb.z + ((bb.w - bb.z + 1) >> 1);
-        uint32_t c[4];
-        oct_warp_partition(C.buf(st >> 31), C.buf((st >> 31) ^ 1), st & 0x7fffffffu, cnt, mx, my, c);
-        if (lane == 0) {
-            C.cc[4 * j] = c[0]; C.cc[4 * j + 1] = c[1]; C.cc[4 * j + 2] = c[2]; C.cc[4 * j + 3] = c[3];
-            C.aux[j] = oct_child_code(c);
-        }
-    }
+    oct_split_nodes(C, cur, E, maybe_big, C.proc, false);
     __syncthreads();
 
     // ---- (b) creation indices: exclusive scan; early stop "size >= N" of the careful pass
