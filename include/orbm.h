@@ -149,7 +149,26 @@ int orbm_search_for_initialization(orbm_context* c, const orbm_frame_view* F1,
                                    const orbm_frame_view* F2, float* prev_matched, int32_t* matches12,
                                    int window_size, float nn_ratio, int check_orientation);
 
-/* Frame::GetFeaturesInArea (src/Frame.cc:645-714) on a frame view: writes up to cap indices in the
+/* One window query of Frame::GetFeaturesInArea(x, y, r, minLevel, maxLevel), src/Frame.cc:645. */
+typedef struct orbm_area_query {
+    float x, y, r;
+    int32_t min_level, max_level; /* as the reference's arguments (max_level < 0: no upper bound) */
+    int32_t valid;                /* 0: the caller's gates rejected this query, it gets an empty row */
+    int32_t desc_row;             /* row of the query descriptor matrix this query compares with */
+} orbm_area_query;
+
+/* Device-side AssignFeaturesToGrid + GetFeaturesInArea (src/Frame.cc:377-408, 645-726) for a batch
+ * of queries: builds the frame's 64 x 48 grid on the GPU and returns the candidate lists as CSR
+ * (row_ptr: nq + 1 ints; cand: keypoint indices in the reference's order) plus, when q_desc is not
+ * NULL, the Hamming distance of every (query, candidate) pair (dist: one uint16 per candidate).
+ * cap = capacity of cand / dist.  Returns nnz, or ORBX_E_CAPACITY with row_ptr filled when
+ * cap < nnz.  The three searches below use exactly this path. */
+int orbm_area_candidates(orbm_context* c, const orbm_frame_view* F, const orbm_area_query* q, int nq,
+                         const uint8_t* q_desc, int n_q_desc, int32_t* row_ptr, int32_t* cand,
+                         uint16_t* dist, int cap);
+
+/* Frame::GetFeaturesInArea (src/Frame.cc:645-714) on a frame view, HOST restatement kept for the
+ * parity tests of the candidate order: writes up to cap indices in the
  * reference's order (grid columns outer, rows inner, insertion order inside a cell); returns the
  * count.  Exposed for parity tests of the candidate order. */
 int orbm_features_in_area(const orbm_frame_view* F, float x, float y, float r, int min_level,

@@ -247,3 +247,173 @@ cudaError_t orbm_launch_stereo_rows(const orbx_keypoint* kl, const uint8_t* dl, 
                                                 max_d, best_idx, best_dist);
     return cudaGetLastError();
 }
+
+// ---- N2 / M7: Frame::AssignFeaturesToGrid + Frame::GetFeaturesInArea on the device ---------------
+// (src/Frame.cc:377-408, 645-726).  The 64 x 48 bucket grid of a frame is built by one CTA
+// (counting sort by cell, cell index = ix * 48 + iy, insertion order = keypoint index inside a
+// cell), then one warp per query walks the window's cells in the reference's order -- columns
+// outer, rows inner; the cells of one column are adjacent in the item array, so a column of the
+// window is ONE contiguous item range -- filters by octave range and |dx| < r && |dy| < r, and
+// compacts the survivors in order with ballots.  A count pass sizes the CSR rows; the fill pass
+// also evaluates the Hamming distance of every (query, candidate) pair, so the order-dependent
+// accept loops of M2-M4 only have to read (candidate, distance) lists.
+#define ORBM_GRID_CELLS (ORBM_GRID_COLS * ORBM_GRID_ROWS)
+
+struct OrbmGrid {
+    float min_x, min_y, w_inv, h_inv;
+};
+
+__global__ void __launch_bounds__(1024)
+k_grid_build(const orbx_keypoint* __restrict__ keys, int n, OrbmGrid G, int32_t* __restrict__ start,
+             int32_t* __restrict__ items, int32_t* __restrict__ cellof) {
+    __shared__ uint32_t cnt[ORBM_GRID_CELLS + 1];
+    __shared__ uint32_t cur[ORBM_GRID_CELLS];
+    __shared__ uint32_t tmp[64];
+    const int tid = threadIdx.x;
+    for (int c = tid; c <= ORBM_GRID_CELLS; c += blockDim.x) cnt[c] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += blockDim.x) {
+        // PosInGrid (:716-726): round, not floor; keypoints outside the grid are not inserted
+        const int px = (int)roundf((keys[i].x - G.min_x) * G.w_inv);
+        const int py = (int)roundf((keys[i].y - G.min_y) * G.h_inv);
+        int cell = -1;
+        if (px >= 0 && px < ORBM_GRID_COLS && py >= 0 && py < ORBM_GRID_ROWS) {
+            cell = px * ORBM_GRID_ROWS + py;
+            atomicAdd(&cnt[cell], 1u);
+        }
+        cellof[i] = cell;
+    }
+    __syncthreads();
+    const uint32_t total = block_excl_scan(cnt, ORBM_GRID_CELLS, tmp);
+    if (tid == 0) cnt[ORBM_GRID_CELLS] = total;
+    __syncthreads();
+    for (int c = tid; c <= ORBM_GRID_CELLS; c += blockDim.x) {
+        start[c] = (int32_t)cnt[c];
+        if (c < ORBM_GRID_CELLS) cur[c] = cnt[c];
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += blockDim.x) {
+        const int cell = cellof[i];
+        if (cell >= 0) items[atomicAdd(&cur[cell], 1u)] = i;
+    }
+    __syncthreads();
+    // restore insertion order (ascending keypoint index) inside every cell: a handful of items
+    for (int c = tid; c < ORBM_GRID_CELLS; c += blockDim.x) {
+        const int s = (int)cnt[c], e = (int)cnt[c + 1];
+        for (int a = s + 1; a < e; ++a) {
+            const int32_t v = items[a];
+            int b = a - 1;
+            while (b >= s && items[b] > v) {
+                items[b + 1] = items[b];
+                --b;
+            }
+            items[b + 1] = v;
+        }
+    }
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(256)
+k_area(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start,
+       const int32_t* __restrict__ items, OrbmGrid G, const orbm_area_query* __restrict__ Q, int nq,
+       int32_t* __restrict__ cnt, const int32_t* __restrict__ row_ptr, const uint4* __restrict__ qdesc,
+       const uint4* __restrict__ tdesc, int32_t* __restrict__ cand, uint16_t* __restrict__ dist) {
+    const int qi = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
+    if (qi >= nq) return;
+    const int lane = orbx_lane();
+    const uint32_t lt = orbx_lanemask_lt();
+    const orbm_area_query q = Q[qi];
+    int total = 0;
+    const float r = q.r;
+    // GetFeaturesInArea :652-676
+    const int c0 = max(0, (int)floorf((q.x - G.min_x - r) * G.w_inv));
+    const int c1 = min(ORBM_GRID_COLS - 1, (int)ceilf((q.x - G.min_x + r) * G.w_inv));
+    const int r0 = max(0, (int)floorf((q.y - G.min_y - r) * G.h_inv));
+    const int r1 = min(ORBM_GRID_ROWS - 1, (int)ceilf((q.y - G.min_y + r) * G.h_inv));
+    if (q.valid && c0 < ORBM_GRID_COLS && c1 >= 0 && r0 < ORBM_GRID_ROWS && r1 >= 0) {
+        const bool check_levels = (q.min_level > 0) || (q.max_level >= 0);
+        const int base = FILL ? row_ptr[qi] : 0;
+        uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+        if (FILL) {
+            a0 = __ldg(qdesc + 2 * (size_t)q.desc_row);
+            a1 = __ldg(qdesc + 2 * (size_t)q.desc_row + 1);
+        }
+        for (int ix = c0; ix <= c1; ++ix) {
+            if (r1 < r0) break;
+            const int s = __ldg(start + ix * ORBM_GRID_ROWS + r0);
+            const int e = __ldg(start + ix * ORBM_GRID_ROWS + r1 + 1);
+            for (int k0 = s; k0 < e; k0 += 32) {
+                const int k = k0 + lane;
+                bool ok = false;
+                int idx = 0;
+                if (k < e) {
+                    idx = __ldg(items + k);
+                    const orbx_keypoint kp = keys[idx];
+                    ok = true;
+                    if (check_levels) {
+                        if (kp.octave < q.min_level) ok = false;
+                        if (q.max_level >= 0 && kp.octave > q.max_level) ok = false;
+                    }
+                    const float dx = kp.x - q.x, dy = kp.y - q.y;
+                    if (!(fabsf(dx) < r && fabsf(dy) < r)) ok = false;
+                }
+                const uint32_t m = __ballot_sync(ORBX_FULL, ok);
+                if (FILL && ok) {
+                    const int pos = base + total + __popc(m & lt);
+                    cand[pos] = idx;
+                    dist[pos] = (uint16_t)hamming256(a0, a1, tdesc + 2 * (size_t)idx);
+                }
+                total += __popc(m);
+            }
+        }
+    }
+    if (!FILL && lane == 0) cnt[qi] = total;
+}
+
+// row_ptr[0..n] = exclusive scan of cnt[0..n) (one CTA)
+__global__ void __launch_bounds__(1024) k_rowptr_scan(const int32_t* __restrict__ cnt, int n, int32_t* __restrict__ row_ptr) {
+    __shared__ uint32_t part[1024];
+    __shared__ uint32_t tmp[64];
+    const int tid = threadIdx.x;
+    const int per = (n + 1023) / 1024;
+    const int b = min(tid * per, n), e = min(b + per, n);
+    uint32_t s = 0;
+    for (int i = b; i < e; ++i) s += (uint32_t)cnt[i];
+    part[tid] = s;
+    __syncthreads();
+    const uint32_t total = block_excl_scan(part, 1024, tmp);
+    uint32_t run = part[tid];
+    for (int i = b; i < e; ++i) {
+        row_ptr[i] = (int32_t)run;
+        run += (uint32_t)cnt[i];
+    }
+    if (tid == 0) row_ptr[n] = (int32_t)total;
+}
+
+cudaError_t orbm_launch_grid_build(const orbx_keypoint* keys, int n, float min_x, float min_y, float w_inv,
+                                   float h_inv, int32_t* start, int32_t* items, int32_t* cellof, cudaStream_t st) {
+    OrbmGrid G{min_x, min_y, w_inv, h_inv};
+    k_grid_build<<<1, 1024, 0, st>>>(keys, n, G, start, items, cellof);
+    return cudaGetLastError();
+}
+
+cudaError_t orbm_launch_area_count(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
+                                   float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
+                                   int nq, int32_t* cnt, int32_t* row_ptr, cudaStream_t st) {
+    OrbmGrid G{min_x, min_y, w_inv, h_inv};
+    k_area<false><<<(nq + 7) / 8, 256, 0, st>>>(keys, start, items, G, Q, nq, cnt, nullptr, nullptr, nullptr,
+                                                 nullptr, nullptr);
+    k_rowptr_scan<<<1, 1024, 0, st>>>(cnt, nq, row_ptr);
+    return cudaGetLastError();
+}
+
+cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
+                                  float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
+                                  int nq, const int32_t* row_ptr, const uint8_t* qdesc, const uint8_t* tdesc,
+                                  int32_t* cand, uint16_t* dist, cudaStream_t st) {
+    OrbmGrid G{min_x, min_y, w_inv, h_inv};
+    k_area<true><<<(nq + 7) / 8, 256, 0, st>>>(keys, start, items, G, Q, nq, nullptr, row_ptr,
+                                                reinterpret_cast<const uint4*>(qdesc),
+                                                reinterpret_cast<const uint4*>(tdesc), cand, dist);
+    return cudaGetLastError();
+}

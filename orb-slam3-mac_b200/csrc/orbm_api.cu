@@ -22,6 +22,15 @@
 
 cudaError_t orbm_launch_hamming_csr(const uint8_t* q, int nq, const uint8_t* t, const int32_t* row_ptr,
                                     const int32_t* cand, int nnz, uint16_t* dist, cudaStream_t st);
+cudaError_t orbm_launch_grid_build(const orbx_keypoint* keys, int n, float min_x, float min_y, float w_inv,
+                                   float h_inv, int32_t* start, int32_t* items, int32_t* cellof, cudaStream_t st);
+cudaError_t orbm_launch_area_count(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
+                                   float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
+                                   int nq, int32_t* cnt, int32_t* row_ptr, cudaStream_t st);
+cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
+                                  float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
+                                  int nq, const int32_t* row_ptr, const uint8_t* qdesc, const uint8_t* tdesc,
+                                  int32_t* cand, uint16_t* dist, cudaStream_t st);
 cudaError_t orbm_launch_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
                              int32_t* dist, cudaStream_t st);
 cudaError_t orbm_launch_stereo_refine(const orbx_keypoint* kl, int nl, const orbx_keypoint* kr,
@@ -69,7 +78,8 @@ struct DevBuf {
 struct orbm_context {
     int device = 0;
     cudaStream_t st = nullptr;
-    DevBuf q, t, rowptr, cand, dist, aux1, aux2, kl, kr, sc, isc, ur, dp, sd;
+    DevBuf q, t, rowptr, cand, dist, aux1, aux2, kl, kr, sc, isc, ur, dp, sd, gstart, gitems, gcell, aq, acnt;
+    std::vector<int32_t> h_rowptr, h_cand;   // candidate lists of the last layer-2 search
     std::vector<uint16_t> hdist;     // distances of the last layer-2 search
     long long last_pairs = 0;        // number of (query, candidate) pairs of the last search
 };
@@ -99,7 +109,8 @@ int orbm_destroy(orbm_context* c) {
     if (!c) return ORBX_OK;
     cudaSetDevice(c->device);
     if (c->st) cudaStreamSynchronize(c->st);
-    for (DevBuf* b : {&c->q, &c->t, &c->rowptr, &c->cand, &c->dist, &c->aux1, &c->aux2, &c->kl, &c->kr, &c->sc})
+    for (DevBuf* b : {&c->q, &c->t, &c->rowptr, &c->cand, &c->dist, &c->aux1, &c->aux2, &c->kl, &c->kr, &c->sc, &c->isc,
+                      &c->ur, &c->dp, &c->sd, &c->gstart, &c->gitems, &c->gcell, &c->aq, &c->acnt})
         b->release();
     if (c->st) cudaStreamDestroy(c->st);
     delete c;
@@ -339,18 +350,80 @@ int check_view(const orbm_frame_view* F) {
     return ORBX_OK;
 }
 
-// all (query, candidate) distances of a search, one batched launch
-int batched_distances(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t, int nt,
-                      const std::vector<int32_t>& row_ptr, const std::vector<int32_t>& cand) {
-    c->hdist.resize(cand.size());
-    c->last_pairs = (long long)cand.size();
-    if (cand.empty()) return ORBX_OK;
-    return orbm_hamming_csr(c, q, nq, t, nt, row_ptr.data(), cand.data(), (int)cand.size(), c->hdist.data());
+// Candidate generation + distances of a search on the device (N2): grid build, window queries in
+// the reference's order, Hamming distance per (query, candidate).  Leaves the CSR lists in
+// c->h_rowptr / c->h_cand and the distances in c->hdist.
+int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vector<orbm_area_query>& Q,
+                      const uint8_t* qdesc, int n_qdesc) {
+    const int nq = (int)Q.size();
+    c->h_rowptr.assign(nq + 1, 0);
+    c->h_cand.clear();
+    c->hdist.clear();
+    c->last_pairs = 0;
+    if (nq == 0 || F->n == 0) return ORBX_OK;
+    M_TRY(cudaSetDevice(c->device));
+    int r;
+    if ((r = c->kl.ensure((size_t)F->n * sizeof(orbx_keypoint))) || (r = c->t.ensure((size_t)F->n * 32)) ||
+        (r = c->q.ensure((size_t)std::max(n_qdesc, 1) * 32)) || (r = c->aq.ensure((size_t)nq * sizeof(orbm_area_query))) ||
+        (r = c->acnt.ensure((size_t)nq * 4)) || (r = c->rowptr.ensure((size_t)(nq + 1) * 4)) ||
+        (r = c->gstart.ensure((size_t)(ORBM_GRID_COLS * ORBM_GRID_ROWS + 1) * 4)) ||
+        (r = c->gitems.ensure((size_t)F->n * 4)) || (r = c->gcell.ensure((size_t)F->n * 4)))
+        return r;
+    M_TRY(cudaMemcpyAsync(c->kl.p, F->keys, (size_t)F->n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
+    M_TRY(cudaMemcpyAsync(c->t.p, F->desc, (size_t)F->n * 32, cudaMemcpyHostToDevice, c->st));
+    if (qdesc) M_TRY(cudaMemcpyAsync(c->q.p, qdesc, (size_t)n_qdesc * 32, cudaMemcpyHostToDevice, c->st));
+    M_TRY(cudaMemcpyAsync(c->aq.p, Q.data(), (size_t)nq * sizeof(orbm_area_query), cudaMemcpyHostToDevice, c->st));
+    const orbx_keypoint* dk = (const orbx_keypoint*)c->kl.p;
+    M_TRY(orbm_launch_grid_build(dk, F->n, F->min_x, F->min_y, F->grid_w_inv, F->grid_h_inv, (int32_t*)c->gstart.p,
+                                 (int32_t*)c->gitems.p, (int32_t*)c->gcell.p, c->st));
+    M_TRY(orbm_launch_area_count(dk, (const int32_t*)c->gstart.p, (const int32_t*)c->gitems.p, F->min_x, F->min_y,
+                                 F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
+                                 (int32_t*)c->acnt.p, (int32_t*)c->rowptr.p, c->st));
+    M_TRY(cudaMemcpyAsync(c->h_rowptr.data(), c->rowptr.p, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaStreamSynchronize(c->st));
+    const int nnz = c->h_rowptr[nq];
+    c->last_pairs = nnz;
+    if (nnz == 0) return ORBX_OK;
+    if ((r = c->cand.ensure((size_t)nnz * 4)) || (r = c->dist.ensure((size_t)nnz * 2))) return r;
+    M_TRY(orbm_launch_area_fill(dk, (const int32_t*)c->gstart.p, (const int32_t*)c->gitems.p, F->min_x, F->min_y,
+                                F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
+                                (const int32_t*)c->rowptr.p, qdesc ? (const uint8_t*)c->q.p : (const uint8_t*)c->t.p,
+                                (const uint8_t*)c->t.p, (int32_t*)c->cand.p, (uint16_t*)c->dist.p, c->st));
+    c->h_cand.resize(nnz);
+    c->hdist.resize(nnz);
+    M_TRY(cudaMemcpyAsync(c->h_cand.data(), c->cand.p, (size_t)nnz * 4, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaMemcpyAsync(c->hdist.data(), c->dist.p, (size_t)nnz * 2, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaStreamSynchronize(c->st));
+    return ORBX_OK;
 }
 
 }  // namespace
 
 extern "C" {
+
+int orbm_area_candidates(orbm_context* c, const orbm_frame_view* F, const orbm_area_query* q, int nq,
+                         const uint8_t* q_desc, int n_q_desc, int32_t* row_ptr, int32_t* cand, uint16_t* dist,
+                         int cap) {
+    int rc = check_view(F);
+    if (rc) return rc;
+    if (!c || nq < 0 || (nq && !q) || !row_ptr || cap < 0 || (q_desc && n_q_desc <= 0))
+        return orbx_set_error(ORBX_E_BAD_ARG, "bad argument");
+    for (int i = 0; i < nq; ++i)
+        if (q_desc && q[i].valid && (q[i].desc_row < 0 || q[i].desc_row >= n_q_desc))
+            return orbx_set_error(ORBX_E_BAD_ARG, "query %d: desc_row out of range", i);
+    std::vector<orbm_area_query> Q(q, q + nq);
+    if (!q_desc)
+        for (auto& e : Q) e.desc_row = 0;
+    if ((rc = device_candidates(c, F, Q, q_desc, n_q_desc))) return rc;
+    for (int i = 0; i <= nq; ++i) row_ptr[i] = c->h_rowptr[i];
+    const int nnz = c->h_rowptr[nq];
+    if (nnz > cap) return orbx_set_error(ORBX_E_CAPACITY, "%d candidates exceed the capacity %d", nnz, cap);
+    for (int k = 0; k < nnz; ++k) {
+        if (cand) cand[k] = c->h_cand[k];
+        if (dist && q_desc) dist[k] = c->hdist[k];
+    }
+    return nnz;
+}
 
 int orbm_features_in_area(const orbm_frame_view* F, float x, float y, float r, int min_level, int max_level,
                           int32_t* out, int cap) {
@@ -370,16 +443,15 @@ int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, 
     int rc = check_view(F);
     if (rc) return rc;
     if (!c || m < 0 || (m && (!mps || !mp_desc)) || !kp_obs || !kp_match) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
-    Grid g;
-    build_grid(F, g);
     for (int i = 0; i < F->n; ++i) kp_match[i] = -1;
     const bool bFactor = th != 1.0;
-    // pass 1: candidate lists (state independent)
-    std::vector<int32_t> row_ptr(m + 1, 0), cand;
+    // pass 1: window queries (state independent); candidates + distances come from the device
+    std::vector<orbm_area_query> Q(m);
     std::vector<float> rad(m, 0.f);
     for (int i = 0; i < m; ++i) {
         const orbm_map_point& p = mps[i];
-        row_ptr[i] = (int32_t)cand.size();
+        orbm_area_query& q = Q[i];
+        q = orbm_area_query{0.f, 0.f, 0.f, 0, 0, 0, i};
         if (!p.in_view) continue;
         if (far_points && p.depth > th_far) continue;
         if (p.bad) continue;
@@ -387,10 +459,11 @@ int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, 
         float r = ((double)p.view_cos > 0.998) ? 2.5f : 4.0f;  // RadiusByViewingCos, :220-226
         if (bFactor) r *= th;
         rad[i] = r * F->scale_factors[p.level];
-        features_in_area(F, g, p.proj_x, p.proj_y, rad[i], p.level - 1, p.level, cand);
+        q = orbm_area_query{p.proj_x, p.proj_y, rad[i], p.level - 1, p.level, 1, i};
     }
-    row_ptr[m] = (int32_t)cand.size();
-    if ((rc = batched_distances(c, mp_desc, m, F->desc, F->n, row_ptr, cand))) return rc;
+    if ((rc = device_candidates(c, F, Q, mp_desc, m))) return rc;
+    const std::vector<int32_t>& row_ptr = c->h_rowptr;
+    const std::vector<int32_t>& cand = c->h_cand;
     // pass 2: the reference's accept loop, original order (:54-147)
     int nmatches = 0;
     for (int i = 0; i < m; ++i) {
@@ -434,28 +507,28 @@ int orbm_search_by_projection_frames(orbm_context* c, const orbm_frame_view* cur
     int rc = check_view(cur);
     if (rc) return rc;
     if (!c || n_last < 0 || (n_last && (!last || !last_desc)) || !kp_obs || !kp_match) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
-    Grid g;
-    build_grid(cur, g);
     for (int i = 0; i < cur->n; ++i) kp_match[i] = -1;
     std::vector<int> rotHist[ORBM_HISTO_LENGTH];
     const float factor = 1.0f / ORBM_HISTO_LENGTH;
-    std::vector<int32_t> row_ptr(n_last + 1, 0), cand;
+    std::vector<orbm_area_query> Q(n_last);
     std::vector<float> rad(n_last, 0.f);
     for (int i = 0; i < n_last; ++i) {
         const orbm_last_obs& o = last[i];
-        row_ptr[i] = (int32_t)cand.size();
+        orbm_area_query& q = Q[i];
+        q = orbm_area_query{0.f, 0.f, 0.f, 0, 0, 0, i};
         if (!o.valid) continue;
         if (o.inv_z < 0) continue;
         if (o.u < cur->min_x || o.u > cur->max_x) continue;
         if (o.v < cur->min_y || o.v > cur->max_y) continue;
         if (o.octave < 0 || o.octave >= cur->nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "observation %d: octave out of range", i);
         rad[i] = th * cur->scale_factors[o.octave];
-        if (forward) features_in_area(cur, g, o.u, o.v, rad[i], o.octave, -1, cand);
-        else if (backward) features_in_area(cur, g, o.u, o.v, rad[i], 0, o.octave, cand);
-        else features_in_area(cur, g, o.u, o.v, rad[i], o.octave - 1, o.octave + 1, cand);
+        if (forward) q = orbm_area_query{o.u, o.v, rad[i], o.octave, -1, 1, i};
+        else if (backward) q = orbm_area_query{o.u, o.v, rad[i], 0, o.octave, 1, i};
+        else q = orbm_area_query{o.u, o.v, rad[i], o.octave - 1, o.octave + 1, 1, i};
     }
-    row_ptr[n_last] = (int32_t)cand.size();
-    if ((rc = batched_distances(c, last_desc, n_last, cur->desc, cur->n, row_ptr, cand))) return rc;
+    if ((rc = device_candidates(c, cur, Q, last_desc, n_last))) return rc;
+    const std::vector<int32_t>& row_ptr = c->h_rowptr;
+    const std::vector<int32_t>& cand = c->h_cand;
     int nmatches = 0;
     for (int i = 0; i < n_last; ++i) {
         if (row_ptr[i + 1] == row_ptr[i]) continue;
@@ -508,22 +581,20 @@ int orbm_search_for_initialization(orbm_context* c, const orbm_frame_view* F1, c
     int rc = check_view(F1);
     if (rc || (rc = check_view(F2))) return rc;
     if (!c || !prev_matched || !matches12) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
-    Grid g;
-    build_grid(F2, g);
     int nmatches = 0;
     for (int i = 0; i < F1->n; ++i) matches12[i] = -1;
     std::vector<int> rotHist[ORBM_HISTO_LENGTH];
     const float factor = 1.0f / ORBM_HISTO_LENGTH;
     std::vector<int> vMatchedDistance(F2->n, INT_MAX), vnMatches21(F2->n, -1);
-    std::vector<int32_t> row_ptr(F1->n + 1, 0), cand;
+    std::vector<orbm_area_query> Q(F1->n);
     for (int i1 = 0; i1 < F1->n; ++i1) {
-        row_ptr[i1] = (int32_t)cand.size();
         const int level1 = F1->keys[i1].octave;
-        if (level1 > 0) continue;
-        features_in_area(F2, g, prev_matched[2 * i1], prev_matched[2 * i1 + 1], (float)window_size, level1, level1, cand);
+        Q[i1] = orbm_area_query{prev_matched[2 * i1], prev_matched[2 * i1 + 1], (float)window_size, level1, level1,
+                                level1 > 0 ? 0 : 1, i1};
     }
-    row_ptr[F1->n] = (int32_t)cand.size();
-    if ((rc = batched_distances(c, F1->desc, F1->n, F2->desc, F2->n, row_ptr, cand))) return rc;
+    if ((rc = device_candidates(c, F2, Q, F1->desc, F1->n))) return rc;
+    const std::vector<int32_t>& row_ptr = c->h_rowptr;
+    const std::vector<int32_t>& cand = c->h_cand;
     for (int i1 = 0; i1 < F1->n; ++i1) {
         if (row_ptr[i1 + 1] == row_ptr[i1]) continue;
         int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;

@@ -13,7 +13,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import KP_DTYPE, check
-from ._lib_match import FrameView, LAST_OBS_DTYPE, MAP_POINT_DTYPE  # noqa: F401
+from ._lib_match import AREA_QUERY_DTYPE, FrameView, LAST_OBS_DTYPE, MAP_POINT_DTYPE  # noqa: F401
 
 FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48
 
@@ -73,6 +73,24 @@ class ORBmatcher:
             self.close()
         except Exception:
             pass
+
+    def area_candidates(self, F: "Frame", queries, q_desc=None, cap=None):
+        """Device-side AssignFeaturesToGrid + GetFeaturesInArea for a batch of window queries
+        (src/Frame.cc:377-408, 645-726): returns (row_ptr, cand, dist); dist is None without q_desc."""
+        q = np.ascontiguousarray(queries, AREA_QUERY_DTYPE)
+        nq = len(q)
+        row_ptr = np.zeros(nq + 1, np.int32)
+        qd = None if q_desc is None else np.ascontiguousarray(q_desc, np.uint8).reshape(-1, 32)
+        cap = int(cap) if cap is not None else max(1, nq * max(1, F.N))
+        cand = np.zeros(cap, np.int32)
+        dist = np.zeros(cap, np.uint16)
+        v = F.view()
+        n = self.lib.orbm_area_candidates(self.ctx, C.byref(v), q.ctypes.data, nq,
+                                          None if qd is None else qd.ctypes.data, 0 if qd is None else len(qd),
+                                          row_ptr.ctypes.data, cand.ctypes.data, dist.ctypes.data, cap)
+        if n < 0:
+            check(n)
+        return row_ptr, cand[:n].copy(), (None if qd is None else dist[:n].copy())
 
     # ---- layer 1 ------------------------------------------------------------------------------------
     def hamming_csr(self, q, t, row_ptr, cand):

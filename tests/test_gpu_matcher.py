@@ -226,3 +226,56 @@ def test_compute_stereo_matches_full_c2(matcher, mo, oracle_libs):
     finally:
         exl.close()
         exr.close()
+
+
+def test_device_grid_candidates_match_oracle_order(matcher, mo):
+    """N2: the device-built 64x48 grid and window queries return exactly the reference's candidate
+    lists (order = grid columns outer, rows inner, insertion order inside a cell, src/Frame.cc:682-684)
+    and the Hamming distance of every (query, candidate) pair; includes keypoints outside the grid,
+    windows that leave the image, invalid queries and every level-gate form."""
+    from orb_slam3_mac_b200._lib_match import AREA_QUERY_DTYPE
+    rng = np.random.default_rng(11)
+    n = 5000
+    from orb_slam3_mac_b200._lib import KP_DTYPE
+    keys = np.zeros(n, KP_DTYPE)
+    keys["x"] = rng.uniform(-20, 772, n).astype(np.float32)     # some land outside the grid
+    keys["y"] = rng.uniform(-20, 500, n).astype(np.float32)
+    keys["x"][:400] = np.round(keys["x"][:400])                 # crowded integer positions
+    keys["y"][:400] = np.round(keys["y"][:400] / 8) * 8
+    keys["octave"] = rng.integers(0, 8, n)
+    desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    F = _frame(keys, desc, 752, 480)
+    nq = 1200
+    q = np.zeros(nq, AREA_QUERY_DTYPE)
+    q["x"] = rng.uniform(-40, 800, nq).astype(np.float32)
+    q["y"] = rng.uniform(-40, 520, nq).astype(np.float32)
+    q["r"] = rng.choice(np.array([0.0, 2.5, 7.0, 24.0, 100.0, 900.0], np.float32), nq)
+    gates = [(-1, -1), (0, 0), (2, 3), (1, -1), (0, 7), (5, 2)]
+    for i in range(nq):
+        q["min_level"][i], q["max_level"][i] = gates[i % len(gates)]
+    q["valid"] = (rng.uniform(size=nq) > 0.1).astype(np.int32)
+    qdesc = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+    q["desc_row"] = rng.integers(0, 300, nq)
+    row_ptr, cand, dist = matcher.area_candidates(F, q, qdesc, cap=2_000_000)
+    assert row_ptr[0] == 0 and row_ptr[-1] == len(cand) and len(cand) > 20000
+    pop = np.array([bin(v).count("1") for v in range(256)], np.int32)
+    for i in range(nq):
+        got = cand[row_ptr[i]:row_ptr[i + 1]]
+        if not q["valid"][i]:
+            assert len(got) == 0
+            continue
+        want = mo.features_in_area(F, float(q["x"][i]), float(q["y"][i]), float(q["r"][i]),
+                                   int(q["min_level"][i]), int(q["max_level"][i]))
+        assert np.array_equal(got, want), i
+        if len(got):
+            d = pop[desc[got] ^ qdesc[q["desc_row"][i]]].sum(axis=1)
+            assert np.array_equal(dist[row_ptr[i]:row_ptr[i + 1]], d.astype(np.uint16)), i
+    # without descriptors only the lists come back; too small a capacity is an error, not a truncation
+    rp2, cand2, d2 = matcher.area_candidates(F, q, None, cap=2_000_000)
+    assert d2 is None and np.array_equal(rp2, row_ptr) and np.array_equal(cand2, cand)
+    with pytest.raises(Exception):
+        matcher.area_candidates(F, q, None, cap=10)
+    # empty frame / no queries
+    F0 = _frame(np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8), 752, 480)
+    rp0, c0, _ = matcher.area_candidates(F0, q[:5], None, cap=16)
+    assert not rp0.any() and len(c0) == 0
