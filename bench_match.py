@@ -1,0 +1,155 @@
+#!/usr/bin/env python
+"""Measurement of the matcher rows of SURVEY.md section 8 (M1-M7, N1, N2) -- companion of bench.py,
+which measures the extractor and carries the driver's JSON contract.
+
+For every case it prints one JSON line:
+  pairs           descriptor pairs the call compares (8 popc each)
+  device_ms       CUDA-event time around the call's kernels (orbm_last_device_ms), median
+  e2e_ms          wall time of the C-ABI call with HOST buffers (H2D + kernels + D2H + the host accept
+                  loop of the order-dependent searches), median
+  cpu_ms          the CPU oracle (oracle/match_oracle.cpp, one thread, the reference's loops) on the
+                  same snapshot, on this box's host cores
+  gpairs_per_s    pairs / device_ms; popc_frac = 8 * that / the measured POPC issue rate
+Inputs are frames extracted by the CUDA extractor from seeded synthetic images (synth.py).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def med(f, reps):
+    ts = []
+    out = None
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        out = f()
+        ts.append(time.perf_counter() - t0)
+    return float(np.median(ts)) * 1e3, out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=30)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+
+    importlib.import_module("orb_slam3_mac_b200")
+    from orb_slam3_mac_b200 import synth as S
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    from orb_slam3_mac_b200.matcher import Frame, ORBmatcher
+    from orb_slam3_mac_b200._lib_match import AREA_QUERY_DTYPE
+    mo = None
+    if not args.no_cpu:
+        from oracle import pyoracle
+        pyoracle.build("port")
+        mo = pyoracle.MatchOracle()
+
+    m = ORBmatcher(0.8, True)
+    lib, ctx = m.lib, m.ctx
+    peak = C.c_double()
+    lib.orbm_measure_popc_peak(ctx, C.byref(peak))
+    SF = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
+
+    def dev_ms():
+        ms, pairs = C.c_float(), C.c_longlong()
+        lib.orbm_last_device_ms(ctx, C.byref(ms), C.byref(pairs))
+        return float(ms.value), int(pairs.value)
+
+    def report(case, what, call, cpu_call):
+        call()  # warm-up (buffer growth)
+        dms = []
+        e2e, _ = med(lambda: (call(), dms.append(dev_ms()))[0], args.reps)
+        d = float(np.median([x[0] for x in dms]))
+        pairs = dms[-1][1]
+        cpu = None
+        if cpu_call is not None and mo is not None:
+            cpu, _ = med(cpu_call, 3)
+        gp = pairs / (d * 1e-3) * 1e-9 if d > 0 else None
+        print(json.dumps({"case": case, "what": what, "pairs": pairs, "device_ms": round(d, 4),
+                          "e2e_ms": round(e2e, 4), "cpu_ms": None if cpu is None else round(cpu, 3),
+                          "cpu_kind": "port, 1 thread", "gpairs_per_s": None if gp is None else round(gp, 2),
+                          "popc_peak_gpopc_per_s": round(peak.value, 1),
+                          "popc_frac": None if gp is None else round(8 * gp / peak.value, 4)}), flush=True)
+
+    def extract(img, nf):
+        ex = ORBextractor(nf, 1.2, 8, 20, 7, max_size=img.shape)
+        k, d = ex(img, (0, 0))[1:3]
+        return k, d
+
+    # ---- M6: fisheye stereo brute force 2-NN at C3 (1500 x 1500) and a large synthetic case ------
+    imgL, imgR = S.fisheye_pair(512, 5)
+    kL, dL = extract(imgL, 1500)
+    kR, dR = extract(imgR, 1500)
+    report("C3 knn2", f"cv::BFMatcher knnMatch k=2, {len(dL)} x {len(dR)} descriptors", lambda: m.knn2(dL, dR),
+           (lambda: mo.knn2(dL, dR)) if mo else None)
+    rng = np.random.default_rng(0)
+    bigq = rng.integers(0, 256, (16384, 32), dtype=np.uint8)
+    bigt = rng.integers(0, 256, (16384, 32), dtype=np.uint8)
+    report("knn2 16k x 16k", "same kernel at a size that fills the GPU", lambda: m.knn2(bigq, bigt), None)
+
+    # ---- M5 + N1: rectified stereo at C2 -------------------------------------------------------------
+    iL, iR = S.stereo_pair(480, 752, 3)
+    exL, exR = ORBextractor(1200, 1.2, 8, 20, 7), ORBextractor(1200, 1.2, 8, 20, 7)
+    kl, dl = exL(iL, (0, 0))[1:3]
+    kr, dr = exR(iR, (0, 0))[1:3]
+    FL, FR = Frame(kl, dl, 752, 480, SF), Frame(kr, dr, 752, 480, SF)
+    report("C2 stereo rows", f"ComputeStereoMatches Hamming arg-min, {len(kl)} x {len(kr)}",
+           lambda: m.stereo_rows(FL, FR, 0.0, 60.0), (lambda: mo.stereo_rows(FL, FR, 480, 0.0, 60.0)) if mo else None)
+    pl, pr = exL.device_pyramid(), exR.device_pyramid()
+    report("C2 ComputeStereoMatches", "rows + SAD refinement on the device-resident pyramids + median cut",
+           lambda: m.ComputeStereoMatches(FL, FR, pl, pr, 0.11, 47.9), None)
+
+    # ---- M2 + M7/N2: SearchByProjection(Frame, map points) at C4 ---------------------------------------
+    img0 = S.textured_noise(720, 1280, 7)
+    img1 = np.roll(img0, 3, axis=1)
+    k0, d0 = extract(img0, 2000)
+    k1, d1 = extract(img1, 2000)
+    mps, md = S.map_points_from_frame(k0, d0, 1280, 720, 10000, 7)
+    F = Frame(k1, d1, 1280, 720, SF)
+    report("C4 SearchByProjection", f"{len(mps)} map points vs {len(k1)} keypoints, th=1 (device grid + windows + distances, host accept loop)",
+           lambda: m.SearchByProjection(F, mps, md, 1.0, False, 30.0),
+           (lambda: mo.search_by_projection_points(F, mps, md, 1.0, False, 30.0, 0.8)) if mo else None)
+    report("C4 SearchByProjection th=3", "same, 3x window",
+           lambda: m.SearchByProjection(F, mps, md, 3.0, False, 30.0),
+           (lambda: mo.search_by_projection_points(F, mps, md, 3.0, False, 30.0, 0.8)) if mo else None)
+
+    # ---- M4: SearchForInitialization with the 5 x nFeatures extractor at C1 -----------------------------
+    a = S.textured_noise(480, 752, 21)
+    b = np.roll(a, 4, axis=1)
+    ka, da = extract(a, 5000)
+    kb, db = extract(b, 5000)
+    F1, F2 = Frame(ka, da, 752, 480, SF), Frame(kb, db, 752, 480, SF)
+    prev = np.stack([ka["x"], ka["y"]], axis=1).astype(np.float32)
+    report("C1 SearchForInitialization", f"{len(ka)} x {len(kb)} keypoints, 100-px windows at level 0",
+           lambda: m.SearchForInitialization(F1, F2, prev.copy(), 100),
+           (lambda: mo.search_for_initialization(F1, F2, prev.copy(), 100, 0.8, True)) if mo else None)
+
+    # ---- M3: SearchByProjection(CurrentFrame, LastFrame) ----------------------------------------------
+    lo, ld = S.last_frame_obs(k0, d0, 9)
+    report("C4 SearchByProjection frames", f"{len(lo)} last-frame observations vs {len(k1)} keypoints, th=15",
+           lambda: m.SearchByProjectionFrames(F, lo, ld, 15.0),
+           (lambda: mo.search_by_projection_frames(F, lo, ld, 15.0, False, False, 0.0, True)) if mo else None)
+
+    # ---- N2 alone: candidate lists without distances ---------------------------------------------------
+    q = np.zeros(len(mps), AREA_QUERY_DTYPE)
+    q["x"], q["y"], q["r"] = mps["proj_x"], mps["proj_y"], 4.0 * SF[np.clip(mps["level"], 0, 7)]
+    q["min_level"], q["max_level"], q["valid"] = mps["level"] - 1, mps["level"], 1
+    report("C4 grid + windows", f"AssignFeaturesToGrid + {len(q)} GetFeaturesInArea queries on the device",
+           lambda: m.area_candidates(F, q, None, cap=200_000), None)
+    m.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -167,6 +167,15 @@ int orbm_area_candidates(orbm_context* c, const orbm_frame_view* F, const orbm_a
                          const uint8_t* q_desc, int n_q_desc, int32_t* row_ptr, int32_t* cand,
                          uint16_t* dist, int cap);
 
+/* Measurement hook: device time between the first and the last kernel of the previous call on this
+ * context (CUDA events on its stream; for the searches this spans the candidate kernels and the
+ * row_ptr read-back between them) and the number of descriptor pairs it compared. */
+int orbm_last_device_ms(orbm_context* c, float* ms, long long* pairs);
+
+/* Measurement hook: the device's POPC issue rate in 1e9 popc/s (8 independent xor-popc-add chains
+ * per thread, all SMs), the peak the Hamming kernels are held against (8 popc per pair). */
+int orbm_measure_popc_peak(orbm_context* c, double* gpopc_per_s);
+
 /* Frame::GetFeaturesInArea (src/Frame.cc:645-714) on a frame view, HOST restatement kept for the
  * parity tests of the candidate order: writes up to cap indices in the
  * reference's order (grid columns outer, rows inner, insertion order inside a cell); returns the

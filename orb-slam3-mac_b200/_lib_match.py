@@ -35,6 +35,8 @@ ORBM_SYMBOLS = {
     "orbm_search_by_projection_frames": (_i, [_vp, _fv, _vp, _vp, _i, _f, _i, _i, _f, _i, _vp, _vp]),
     "orbm_search_for_initialization": (_i, [_vp, _fv, _fv, _vp, _vp, _i, _f, _i]),
     "orbm_area_candidates": (_i, [_vp, _fv, _vp, _i, _vp, _i, _vp, _vp, _vp, _i]),
+    "orbm_last_device_ms": (_i, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_longlong)]),
+    "orbm_measure_popc_peak": (_i, [_vp, C.POINTER(C.c_double)]),
     "orbm_features_in_area": (_i, [_fv, _f, _f, _f, _i, _i, _vp, _i]),
 }
 

@@ -417,3 +417,30 @@ cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* star
                                                 reinterpret_cast<const uint4*>(tdesc), cand, dist);
     return cudaGetLastError();
 }
+
+// ---- measurement helper: the device's POPC issue rate (the bound SURVEY 8(d) names for M1-M6) ----
+// Every thread runs 8 independent xor -> popc -> add chains; the result is written so that nothing
+// is optimised away.  Returns popc instructions per launch through *n_popc.
+__global__ void __launch_bounds__(256) k_popc_peak(uint32_t* __restrict__ out, int iters) {
+    uint32_t x[8], acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        x[k] = threadIdx.x * 2654435761u + k * 40503u + blockIdx.x;
+        acc[k] = 0;
+    }
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            acc[k] += __popc(x[k] ^ acc[k]);
+        }
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += acc[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+cudaError_t orbm_launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t st) {
+    k_popc_peak<<<blocks, 256, 0, st>>>(out, iters);
+    return cudaGetLastError();
+}

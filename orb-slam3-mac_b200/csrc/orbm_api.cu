@@ -31,6 +31,7 @@ cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* star
                                   float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
                                   int nq, const int32_t* row_ptr, const uint8_t* qdesc, const uint8_t* tdesc,
                                   int32_t* cand, uint16_t* dist, cudaStream_t st);
+cudaError_t orbm_launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t st);
 cudaError_t orbm_launch_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
                              int32_t* dist, cudaStream_t st);
 cudaError_t orbm_launch_stereo_refine(const orbx_keypoint* kl, int nl, const orbx_keypoint* kr,
@@ -78,6 +79,8 @@ struct DevBuf {
 struct orbm_context {
     int device = 0;
     cudaStream_t st = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // around the kernels of the last call (orbm_last_device_ms)
+    bool timed = false;
     DevBuf q, t, rowptr, cand, dist, aux1, aux2, kl, kr, sc, isc, ur, dp, sd, gstart, gitems, gcell, aq, acnt;
     std::vector<int32_t> h_rowptr, h_cand;   // candidate lists of the last layer-2 search
     std::vector<uint16_t> hdist;     // distances of the last layer-2 search
@@ -101,6 +104,11 @@ int orbm_create(int device, orbm_context** out) {
         delete c;
         return orbx_set_error(ORBX_E_CUDA, "cudaStreamCreate failed");
     }
+    if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
+        cudaStreamDestroy(c->st);
+        delete c;
+        return orbx_set_error(ORBX_E_CUDA, "cudaEventCreate failed");
+    }
     *out = c;
     return ORBX_OK;
 }
@@ -112,6 +120,8 @@ int orbm_destroy(orbm_context* c) {
     for (DevBuf* b : {&c->q, &c->t, &c->rowptr, &c->cand, &c->dist, &c->aux1, &c->aux2, &c->kl, &c->kr, &c->sc, &c->isc,
                       &c->ur, &c->dp, &c->sd, &c->gstart, &c->gitems, &c->gcell, &c->aq, &c->acnt})
         b->release();
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->st) cudaStreamDestroy(c->st);
     delete c;
     return ORBX_OK;
@@ -132,8 +142,12 @@ int orbm_hamming_csr(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t
     M_TRY(cudaMemcpyAsync(c->t.p, t, (size_t)nt * 32, cudaMemcpyHostToDevice, c->st));
     M_TRY(cudaMemcpyAsync(c->rowptr.p, row_ptr, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, c->st));
     M_TRY(cudaMemcpyAsync(c->cand.p, cand, (size_t)nnz * 4, cudaMemcpyHostToDevice, c->st));
+    c->last_pairs = nnz;
+    M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_hamming_csr((const uint8_t*)c->q.p, nq, (const uint8_t*)c->t.p, (const int32_t*)c->rowptr.p,
                                   (const int32_t*)c->cand.p, nnz, (uint16_t*)c->dist.p, c->st));
+    M_TRY(cudaEventRecord(c->ev1, c->st));
+    c->timed = true;
     M_TRY(cudaMemcpyAsync(dist_out, c->dist.p, (size_t)nnz * 2, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaStreamSynchronize(c->st));
     return ORBX_OK;
@@ -152,8 +166,12 @@ int orbm_knn2(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t, int n
         return r;
     M_TRY(cudaMemcpyAsync(c->q.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice, c->st));
     if (nt) M_TRY(cudaMemcpyAsync(c->t.p, t, (size_t)nt * 32, cudaMemcpyHostToDevice, c->st));
+    c->last_pairs = (long long)nq * nt;
+    M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_knn2((const uint8_t*)c->q.p, nq, (const uint8_t*)c->t.p, nt, (int32_t*)c->aux1.p,
                            (int32_t*)c->aux2.p, c->st));
+    M_TRY(cudaEventRecord(c->ev1, c->st));
+    c->timed = true;
     M_TRY(cudaMemcpyAsync(idx_out, c->aux1.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaMemcpyAsync(dist_out, c->aux2.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaStreamSynchronize(c->st));
@@ -186,9 +204,13 @@ int orbm_stereo_rows(orbm_context* c, const orbx_keypoint* kps_l, const uint8_t*
         M_TRY(cudaMemcpyAsync(c->kr.p, kps_r, (size_t)n_r * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
     }
     M_TRY(cudaMemcpyAsync(c->sc.p, scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice, c->st));
+    c->last_pairs = (long long)n_l * n_r;
+    M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_stereo_rows((const orbx_keypoint*)c->kl.p, (const uint8_t*)c->q.p, n_l,
                                   (const orbx_keypoint*)c->kr.p, (const uint8_t*)c->t.p, n_r, (const float*)c->sc.p,
                                   min_d, max_d, (int32_t*)c->aux1.p, (int32_t*)c->aux2.p, c->st));
+    M_TRY(cudaEventRecord(c->ev1, c->st));
+    c->timed = true;
     M_TRY(cudaMemcpyAsync(best_idx, c->aux1.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaMemcpyAsync(best_dist, c->aux2.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaStreamSynchronize(c->st));
@@ -239,6 +261,8 @@ int orbm_compute_stereo_matches(orbm_context* c, const orbx_keypoint* kps_l, con
     // :831-833
     const float minZ = mb, minD = 0, maxD = mbf / minZ;
     const int thOrbDist = (ORBM_TH_HIGH + ORBM_TH_LOW) / 2;   // :807
+    c->last_pairs = (long long)n_l * n_r;
+    M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_stereo_rows((const orbx_keypoint*)c->kl.p, (const uint8_t*)c->q.p, n_l,
                                   (const orbx_keypoint*)c->kr.p, (const uint8_t*)c->t.p, n_r, (const float*)c->sc.p,
                                   minD, maxD, (int32_t*)c->aux1.p, (int32_t*)c->aux2.p, c->st));
@@ -246,6 +270,8 @@ int orbm_compute_stereo_matches(orbm_context* c, const orbx_keypoint* kps_l, con
                                     (const int32_t*)c->aux1.p, (const int32_t*)c->aux2.p, pyr_l, pyr_r,
                                     (const float*)c->sc.p, (const float*)c->isc.p, thOrbDist, minD, maxD, mbf,
                                     (float*)c->ur.p, (float*)c->dp.p, (int32_t*)c->sd.p, c->st));
+    M_TRY(cudaEventRecord(c->ev1, c->st));
+    c->timed = true;
     std::vector<int32_t> sad(n_l);
     M_TRY(cudaMemcpyAsync(u_right, c->ur.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaMemcpyAsync(depth, c->dp.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
@@ -374,6 +400,7 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     if (qdesc) M_TRY(cudaMemcpyAsync(c->q.p, qdesc, (size_t)n_qdesc * 32, cudaMemcpyHostToDevice, c->st));
     M_TRY(cudaMemcpyAsync(c->aq.p, Q.data(), (size_t)nq * sizeof(orbm_area_query), cudaMemcpyHostToDevice, c->st));
     const orbx_keypoint* dk = (const orbx_keypoint*)c->kl.p;
+    M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_grid_build(dk, F->n, F->min_x, F->min_y, F->grid_w_inv, F->grid_h_inv, (int32_t*)c->gstart.p,
                                  (int32_t*)c->gitems.p, (int32_t*)c->gcell.p, c->st));
     M_TRY(orbm_launch_area_count(dk, (const int32_t*)c->gstart.p, (const int32_t*)c->gitems.p, F->min_x, F->min_y,
@@ -389,6 +416,8 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
                                 F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
                                 (const int32_t*)c->rowptr.p, qdesc ? (const uint8_t*)c->q.p : (const uint8_t*)c->t.p,
                                 (const uint8_t*)c->t.p, (int32_t*)c->cand.p, (uint16_t*)c->dist.p, c->st));
+    M_TRY(cudaEventRecord(c->ev1, c->st));
+    c->timed = true;
     c->h_cand.resize(nnz);
     c->hdist.resize(nnz);
     M_TRY(cudaMemcpyAsync(c->h_cand.data(), c->cand.p, (size_t)nnz * 4, cudaMemcpyDeviceToHost, c->st));
@@ -400,6 +429,40 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
 }  // namespace
 
 extern "C" {
+
+int orbm_last_device_ms(orbm_context* c, float* ms, long long* pairs) {
+    if (!c || !ms) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    *ms = 0.f;
+    if (pairs) *pairs = c->last_pairs;
+    if (!c->timed) return ORBX_OK;
+    M_TRY(cudaSetDevice(c->device));
+    M_TRY(cudaEventSynchronize(c->ev1));
+    M_TRY(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    return ORBX_OK;
+}
+
+int orbm_measure_popc_peak(orbm_context* c, double* gpopc_per_s) {
+    if (!c || !gpopc_per_s) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    M_TRY(cudaSetDevice(c->device));
+    cudaDeviceProp prop;
+    M_TRY(cudaGetDeviceProperties(&prop, c->device));
+    const int blocks = prop.multiProcessorCount * 8, iters = 4096;
+    int r;
+    if ((r = c->aux1.ensure((size_t)blocks * 256 * 4))) return r;
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        M_TRY(cudaEventRecord(c->ev0, c->st));
+        M_TRY(orbm_launch_popc_peak((uint32_t*)c->aux1.p, blocks, iters, c->st));
+        M_TRY(cudaEventRecord(c->ev1, c->st));
+        M_TRY(cudaEventSynchronize(c->ev1));
+        float ms = 0.f;
+        M_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    *gpopc_per_s = (double)blocks * 256 * 8 * iters / (best * 1e-3) * 1e-9;
+    c->timed = false;
+    return ORBX_OK;
+}
 
 int orbm_area_candidates(orbm_context* c, const orbm_frame_view* F, const orbm_area_query* q, int nq,
                          const uint8_t* q_desc, int n_q_desc, int32_t* row_ptr, int32_t* cand, uint16_t* dist,
