@@ -107,6 +107,11 @@ struct Slot {
     cudaEvent_t ev[6] = {};      // stage boundaries (ORBX_FLAG_STAGE_TIMING)
     OrbxSrc src{};               // level-0 source of the last run (for the debug taps)
     int run_w = 0, run_h = 0;
+    // CUDA graph of the kernel sequence for small batches (single-frame latency path)
+    cudaGraphExec_t gexec = nullptr;
+    unsigned long long g_epoch = 0, warm_epoch = 0;
+    int g_nframes = 0, g_launches = 0;
+    OrbxSrc g_src{};
 };
 
 }  // namespace
@@ -120,6 +125,7 @@ struct orbx_handle {
     uint8_t* tables = nullptr;  // device resize tables of `plan`
     size_t tables_bytes = 0;
     int pitch0_cap = 0;
+    unsigned long long epoch = 1;   // bumped whenever the plan or a device buffer changes
     std::vector<Slot> slots;
 };
 
@@ -383,6 +389,7 @@ int set_shape(orbx_handle* h, int w, int hgt) {
         return fail(ORBX_E_UNSUPPORTED, "quadtree working set exceeds shared memory (nfeatures too large)");
     if ((r = ensure_buffers(h, P))) return r;
     h->plan = P;
+    ++h->epoch;   // captured graphs hold the old plan and buffer addresses
     return ORBX_OK;
 }
 
@@ -393,10 +400,8 @@ int set_shape(orbx_handle* h, int w, int hgt) {
 // =================================================================================================
 namespace {
 
-// Enqueue the whole device pipeline for `nframes` frames whose level 0 is `src`.
-int enqueue_kernels(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes) {
+int launch_stages(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes, bool timing) {
     const OrbxPlan& P = h->plan;
-    const bool timing = (h->cfg.flags & ORBX_FLAG_STAGE_TIMING) != 0;
     s.launches = 0;
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[0], s.st));
     orbx_launch_pyramid(P, src, s.pyr, nframes, s.st, &s.launches);
@@ -413,6 +418,59 @@ int enqueue_kernels(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes) {
     CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.header, s.dest, s.kps, s.desc, nframes,
                                   s.st, &s.launches));
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[5], s.st));
+    return ORBX_OK;
+}
+
+// Enqueue the whole device pipeline for `nframes` frames whose level 0 is `src`.
+// Small batches (the single-frame latency path) replay a CUDA graph of the kernel sequence: the
+// second run of a (plan, buffers, nframes, source) combination on a slot captures it, later runs
+// launch the instantiated graph -- one launch instead of eleven, no host gaps between the levels.
+int enqueue_kernels(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes) {
+    const OrbxPlan& P = h->plan;
+    const bool timing = (h->cfg.flags & ORBX_FLAG_STAGE_TIMING) != 0;
+    // (only for the handle's own staging buffer: a caller-owned device source may change every call)
+    const bool graph_ok = !timing && !(h->cfg.flags & ORBX_FLAG_NO_GRAPH) && nframes <= ORBX_GRAPH_MAX_FRAMES &&
+                          src.img0 == s.img_in;
+    bool done = false;
+    if (graph_ok) {
+        const bool same = s.gexec && s.g_epoch == h->epoch && s.g_nframes == nframes && s.g_src.img0 == src.img0 &&
+                          s.g_src.pitch0 == src.pitch0 && s.g_src.stride0 == src.stride0;
+        if (!same && s.warm_epoch == h->epoch) {
+            if (s.gexec) {
+                cudaGraphExecDestroy(s.gexec);
+                s.gexec = nullptr;
+            }
+            cudaGraph_t g = nullptr;
+            if (cudaStreamBeginCapture(s.st, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+                const int r = launch_stages(h, s, src, nframes, false);
+                const cudaError_t e = cudaStreamEndCapture(s.st, &g);
+                if (r == ORBX_OK && e == cudaSuccess && g &&
+                    cudaGraphInstantiate(&s.gexec, g, 0) == cudaSuccess) {
+                    s.g_epoch = h->epoch;
+                    s.g_nframes = nframes;
+                    s.g_src = src;
+                    s.g_launches = s.launches;
+                } else {
+                    s.gexec = nullptr;
+                    cudaGetLastError();
+                }
+                if (g) cudaGraphDestroy(g);
+            } else {
+                cudaGetLastError();
+            }
+        }
+        if (s.gexec && s.g_epoch == h->epoch && s.g_nframes == nframes && s.g_src.img0 == src.img0 &&
+            s.g_src.pitch0 == src.pitch0 && s.g_src.stride0 == src.stride0) {
+            CUDA_TRY(cudaGraphLaunch(s.gexec, s.st));
+            s.launches = s.g_launches;
+            done = true;
+        }
+    }
+    if (!done) {
+        int r = launch_stages(h, s, src, nframes, timing);
+        if (r) return r;
+        s.warm_epoch = h->epoch;   // lazy one-time initialisation has run: the next call may capture
+    }
     s.src = src;
     s.run_w = P.w;
     s.run_h = P.h;
@@ -499,6 +557,7 @@ int orbx_destroy(orbx_handle* h) {
         if (s.h_header) cudaFreeHost(s.h_header);
         if (s.h_lap) cudaFreeHost(s.h_lap);
         for (int k = 0; k < 6; ++k) if (s.ev[k]) cudaEventDestroy(s.ev[k]);
+        if (s.gexec) cudaGraphExecDestroy(s.gexec);
         if (s.st) cudaStreamDestroy(s.st);
     }
     cudaFree(h->tables);
