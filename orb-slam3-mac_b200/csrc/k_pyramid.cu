@@ -72,7 +72,7 @@ struct RzArgs {
     const uint2* ytab;       // [dh] {s0, b0 | b1 << 16}, bottom source row = s0 + 1
     int spitch, dpitch;
     int sw, sh, dw, dh;
-    int warps_x, nbands;
+    int warps_x, nbands, rows;   // rows = output rows per warp (band height)
 };
 
 // Horizontal pass of one source row for the thread's 4 columns from its 4 loaded words,
@@ -128,7 +128,7 @@ k_resize_rows(const __grid_constant__ RzArgs A) {
         sel[2] = (uint32_t)o2 | ((uint32_t)min(o2 + 1, 7) << 4);
         sel[3] = (uint32_t)o3 | ((uint32_t)min(o3 + 1, 7) << 4);
     }
-    const int y0 = band * RZ_ROWS, y1 = min(y0 + RZ_ROWS, A.dh);
+    const int y0 = band * A.rows, y1 = min(y0 + A.rows, A.dh);
     uint8_t* drow = A.dst + (size_t)blockIdx.y * A.dst_fstride + (size_t)y0 * A.dpitch + x0;
     const uint2* yp = A.ytab + y0;
     uint2 yt = __ldg(yp);
@@ -235,7 +235,7 @@ __device__ __forceinline__ void rz_walk(const RzArgs& A, int band, int xbase, ui
     const int w_end = __reduce_max_sync(ORBX_FULL, wp[NP - 1] + 2);   // one past the last word needed
     const int nchunk = min((w_end - w_first + 3) >> 2, SLOT / 16);
 
-    const int y0 = band * RZ_ROWS, y1 = min(y0 + RZ_ROWS, A.dh);
+    const int y0 = band * A.rows, y1 = min(y0 + A.rows, A.dh);
     uint8_t* drow = A.dst + (size_t)blockIdx.y * A.dst_fstride + (size_t)y0 * A.dpitch + xc;
     const uint2* yp = A.ytab + y0;
     uint2 yt = __ldg(yp);
@@ -347,7 +347,12 @@ void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, in
             A.xa = reinterpret_cast<const uint32_t*>(D.xa);
             A.ytab = D.ytab;
             A.sw = S.w; A.sh = S.h; A.dw = D.w; A.dh = D.h;
-            A.nbands = (D.h + RZ_ROWS - 1) / RZ_ROWS;
+            // output rows per warp: RZ_ROWS when the launch fills the GPU anyway; small batches take
+            // shorter bands so that a level of one frame still spreads over the SMs (latency path)
+            A.rows = RZ_ROWS;
+            while (A.rows > 2 && (long long)nframes * ((D.w + 255) / 256) * ((D.h + A.rows - 1) / A.rows) < 148 * 16)
+                A.rows >>= 1;
+            A.nbands = (D.h + A.rows - 1) / A.rows;
             const bool aligned = ((uintptr_t)A.src % 16 == 0) && (A.spitch % 16 == 0) && (A.src_fstride % 16 == 0);
             const double ratio = (double)S.w / D.w;
             const bool async_ok = aligned && D.x_step_max <= 2 && ratio <= 1.7;
