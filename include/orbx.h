@@ -173,6 +173,27 @@ int orbx_debug_candidates(orbx_handle* h, int slot, int frame, int level, int32_
  * int32 triplets {x, y, response}, same coordinate convention.  Returns the count (or <0). */
 int orbx_debug_survivors(orbx_handle* h, int slot, int frame, int level, int32_t* xyr, int cap);
 
+/* ---- input stage: what the reference does to an image before ExtractORB ----------
+ * cvtColor(mImGray, mImGray, CV_{RGB,BGR,RGBA,BGRA}2GRAY)   src/Tracking.cc:354-379, 425-438, 479-492
+ * cv::remap(im, imRect, M1, M2, cv::INTER_LINEAR)            Examples/Stereo/stereo_euroc.cc:170-171
+ * fused in front of pyramid level 0 on the device.  Both settings persist on the handle and apply to
+ * every later extract / submit / extract_device call, whose `img` is then the RAW image (stride in
+ * bytes, >= w * channels); level 0 of the pyramid is the rectified gray image. */
+#define ORBX_IN_GRAY8 0 /* CV_8UC1 (default) */
+#define ORBX_IN_BGR8 1  /* CV_8UC3, mbRGB == false */
+#define ORBX_IN_RGB8 2  /* CV_8UC3, mbRGB == true */
+#define ORBX_IN_BGRA8 3 /* CV_8UC4 */
+#define ORBX_IN_RGBA8 4
+/* gray_bits: 15 = the luma coefficients of OpenCV >= 4 (9798, 19235, 3735, >> 15), 14 = those of
+ * OpenCV 2.4/3.x (4899, 9617, 1868, >> 14). */
+int orbx_set_input_format(orbx_handle* h, int format, int gray_bits);
+/* map_x / map_y: the CV_32FC1 maps of cv::initUndistortRectifyMap (stereo_euroc.cc:117-118), w x hgt
+ * floats each, rows map_stride_floats apart, for images of exactly that size; converted once to
+ * OpenCV's fixed point (cvRound(map * 32)) and kept on the device.  NULL maps switch the stage off.
+ * Source pixels outside the image read 0 (cv::remap's default BORDER_CONSTANT). */
+int orbx_set_rectify_maps(orbx_handle* h, const float* map_x, const float* map_y, int w, int hgt,
+                          size_t map_stride_floats);
+
 /* With ORBX_FLAG_STAGE_TIMING: device milliseconds of the last run on `slot`, measured with CUDA
  * events on the slot's stream: ms[0..4] = pyramid, FAST, quadtree, assemble, describe; ms[5] =
  * all kernels.  Returns the number of values written. */

@@ -290,6 +290,61 @@ static inline void gaussian7_sigma2_u8(const uint8_t* src, int rows, int cols, s
     }
 }
 
+// ---- cv::cvtColor(src, dst, CV_{BGR,RGB,BGRA,RGBA}2GRAY) for CV_8U --------------------------
+// Reference call sites: src/Tracking.cc:354-379, 425-438, 479-492.  Integer luma:
+//   bits = 15 (OpenCV 4.x, the one pinned here against cv2 4.13): (R*9798 + G*19235 + B*3735 + 2^14) >> 15
+//   bits = 14 (OpenCV 2.4/3.x, the fork's 3.4.1 build; published constants R2Y 4899, G2Y 9617,
+//              B2Y 1868, yuv_shift 14 -- not pinnable here): (R*4899 + G*9617 + B*1868 + 2^13) >> 14
+// channels = 3 or 4 (alpha ignored); rgb_order != 0 means the first channel is R.
+static inline void cvt_gray_u8(const uint8_t* src, int rows, int cols, size_t sstep, int channels,
+                               int rgb_order, int bits, uint8_t* dst, size_t dstep) {
+    const int cr = bits == 15 ? 9798 : 4899, cg = bits == 15 ? 19235 : 9617, cb = bits == 15 ? 3735 : 1868;
+    for (int y = 0; y < rows; ++y) {
+        const uint8_t* S = src + (size_t)y * sstep;
+        uint8_t* D = dst + (size_t)y * dstep;
+        for (int x = 0; x < cols; ++x) {
+            const int c0 = S[x * channels], c1 = S[x * channels + 1], c2 = S[x * channels + 2];
+            const int r = rgb_order ? c0 : c2, b = rgb_order ? c2 : c0;
+            D[x] = (uint8_t)((r * cr + c1 * cg + b * cb + (1 << (bits - 1))) >> bits);
+        }
+    }
+}
+
+// ---- cv::remap(src, dst, map1, map2, INTER_LINEAR) for CV_8UC{1,3,4}, CV_32FC1 maps ----------
+// Reference call site: Examples/Stereo/stereo_euroc.cc:170-171 (maps from initUndistortRectifyMap,
+// :117-118), BORDER_CONSTANT with value 0 (the default).  OpenCV's fixed-point path
+// (imgwarp.cpp remap -> remapBilinear): sx = cvRound(mapx * 32) with the product in float32,
+// integer part sx >> 5 (saturated to short), fraction sx & 31; the 32x32 weight table holds
+// round(wy*wx*32768) -- exact multiples of 32 -- so the pixel is
+//   (a00*v00 + a01*v01 + a10*v10 + a11*v11 + 512) >> 10,  a = (32-fx)(32-fy), fx(32-fy), (32-fx)fy, fx*fy
+// (the saturated entry of the zero-fraction case, {32767,0,0,1}, gives v00 as well); source
+// pixels outside the image read as 0.  Pinned bit-exact against cv2 4.13 in tests/test_oracle_prims.py.
+static inline void remap_linear_u8(const uint8_t* src, int srows, int scols, size_t sstep, int channels,
+                                   const float* mapx, const float* mapy, size_t mstep_floats, uint8_t* dst,
+                                   int drows, int dcols, size_t dstep) {
+    for (int y = 0; y < drows; ++y) {
+        uint8_t* D = dst + (size_t)y * dstep;
+        for (int x = 0; x < dcols; ++x) {
+            const int sx = cv_round(mapx[(size_t)y * mstep_floats + x] * 32.0f);
+            const int sy = cv_round(mapy[(size_t)y * mstep_floats + x] * 32.0f);
+            const int fx = sx & 31, fy = sy & 31;
+            int ix = sx >> 5, iy = sy >> 5;
+            ix = ix < -32768 ? -32768 : ix > 32767 ? 32767 : ix;
+            iy = iy < -32768 ? -32768 : iy > 32767 ? 32767 : iy;
+            const int a00 = (32 - fx) * (32 - fy), a01 = fx * (32 - fy), a10 = (32 - fx) * fy, a11 = fx * fy;
+            for (int c = 0; c < channels; ++c) {
+                int v[4];
+                for (int k = 0; k < 4; ++k) {
+                    const int xx = ix + (k & 1), yy = iy + (k >> 1);
+                    v[k] = (xx >= 0 && xx < scols && yy >= 0 && yy < srows)
+                               ? src[(size_t)yy * sstep + (size_t)xx * channels + c] : 0;
+                }
+                D[x * channels + c] = (uint8_t)((a00 * v[0] + a01 * v[1] + a10 * v[2] + a11 * v[3] + 512) >> 10);
+            }
+        }
+    }
+}
+
 // ---- cv::fastAtan2(y, x) -> degrees in [0, 360) --------------------------------------------
 // OpenCV core/mathfuncs_core: 7th-order odd polynomial, float32, no FMA contraction
 // (compile the including TU with -ffp-contract=off).

@@ -501,5 +501,13 @@ void orbo_prim_atan2(const float* y, const float* x, float* out, int n) {
     for (int i = 0; i < n; ++i) out[i] = cvprims::fast_atan2_deg(y[i], x[i]);
 }
 int orbo_prim_round(float v) { return cvprims::cv_round(v); }
+void orbo_prim_cvt_gray(const uint8_t* src, int h, int w, size_t sstep, int channels, int rgb_order, int bits,
+                        uint8_t* dst, size_t dstep) {
+    cvprims::cvt_gray_u8(src, h, w, sstep, channels, rgb_order, bits, dst, dstep);
+}
+void orbo_prim_remap(const uint8_t* src, int sh, int sw, size_t sstep, int channels, const float* mapx,
+                     const float* mapy, uint8_t* dst, int dh, int dw, size_t dstep) {
+    cvprims::remap_linear_u8(src, sh, sw, sstep, channels, mapx, mapy, (size_t)dw, dst, dh, dw, dstep);
+}
 
 }  // extern "C"

@@ -248,3 +248,29 @@ class MatchOracle:
         self.lib.orbo_knn2(C.c_void_p(q.ctypes.data), len(q), C.c_void_p(t.ctypes.data), len(t),
                            C.c_void_p(idx.ctypes.data), C.c_void_p(dist.ctypes.data))
         return idx, dist
+
+
+# ---- N4 input-stage primitives (oracle/cvprims.h: cvt_gray_u8, remap_linear_u8) ------------------------
+def cvt_gray(img: np.ndarray, rgb_order: bool, bits: int = 15) -> np.ndarray:
+    """cvtColor(img, CV_{BGR,RGB,BGRA,RGBA}2GRAY), src/Tracking.cc:354-379."""
+    lib = C.CDLL(PORT_SO)
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w, ch = img.shape
+    out = np.zeros((h, w), np.uint8)
+    lib.orbo_prim_cvt_gray(C.c_void_p(img.ctypes.data), h, w, C.c_size_t(img.strides[0]), ch, int(rgb_order), bits,
+                           C.c_void_p(out.ctypes.data), C.c_size_t(out.strides[0]))
+    return out
+
+
+def remap_linear(img: np.ndarray, map_x: np.ndarray, map_y: np.ndarray) -> np.ndarray:
+    """cv::remap(img, out, map_x, map_y, INTER_LINEAR), Examples/Stereo/stereo_euroc.cc:170-171."""
+    lib = C.CDLL(PORT_SO)
+    img = np.ascontiguousarray(img, np.uint8)
+    mx, my = np.ascontiguousarray(map_x, np.float32), np.ascontiguousarray(map_y, np.float32)
+    ch = 1 if img.ndim == 2 else img.shape[2]
+    h, w = mx.shape
+    out = np.zeros((h, w) if ch == 1 else (h, w, ch), np.uint8)
+    lib.orbo_prim_remap(C.c_void_p(img.ctypes.data), img.shape[0], img.shape[1], C.c_size_t(img.strides[0]), ch,
+                        C.c_void_p(mx.ctypes.data), C.c_void_p(my.ctypes.data), C.c_void_p(out.ctypes.data), h, w,
+                        C.c_size_t(out.strides[0]))
+    return out

@@ -68,6 +68,8 @@ ORBX_SYMBOLS = {
     "orbx_extract_device": (_i, [_vp, _i, _vp, _i, _i, _i, _sz, _sz, _vp, C.POINTER(_vp),
                                  C.POINTER(_vp), C.POINTER(_vp)]),
     "orbx_slot_stream": (_vp, [_vp, _i]),
+    "orbx_set_input_format": (_i, [_vp, _i, _i]),
+    "orbx_set_rectify_maps": (_i, [_vp, _vp, _vp, _i, _i, C.c_size_t]),
     "orbx_level_size": (_i, [_vp, _i, _i, _i, _ip, _ip]),
     "orbx_get_pyramid_level": (_i, [_vp, _i, _i, _i, _i, _vp, _sz]),
     "orbx_debug_candidates": (_i, [_vp, _i, _i, _i, _vp, _i]),

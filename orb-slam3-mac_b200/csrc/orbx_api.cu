@@ -22,6 +22,9 @@
 // kernel launchers (k_*.cu)
 void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes,
                          cudaStream_t st, int* launches);
+cudaError_t orbx_launch_input(const uint8_t* raw, long long raw_fstride, int raw_pitch, int w, int h, int channels,
+                              int rgb_order, int gray_bits, const uint2* map, uint8_t* dst, long long dst_fstride,
+                              int dst_pitch, int nframes, cudaStream_t st, int* launches);
 cudaError_t orbx_configure_fast(const OrbxPlan& P);
 cudaError_t orbx_launch_fast(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
                              uint32_t* cellcnt, uint32_t* cellkeys, int nframes, cudaStream_t st,
@@ -91,6 +94,8 @@ struct Slot {
     SlotCaps caps;
     cudaStream_t st = nullptr;
     uint8_t* img_in = nullptr;   // device staging of the H2D copy (level 0)
+    uint8_t* raw_in = nullptr;   // raw (colour / unrectified) frames when the input stage is on
+    size_t raw_cap = 0;
     uint8_t* pyr = nullptr;
     uint32_t *cellcnt = nullptr, *cellkeys = nullptr, *keysA = nullptr, *keysB = nullptr;
     uint32_t *surv = nullptr, *survcnt = nullptr, *dest = nullptr;
@@ -126,6 +131,12 @@ struct orbx_handle {
     size_t tables_bytes = 0;
     int pitch0_cap = 0;
     unsigned long long epoch = 1;   // bumped whenever the plan or a device buffer changes
+    // input stage (N4)
+    int in_format = ORBX_IN_GRAY8, gray_bits = 15;
+    uint2* d_map = nullptr;         // fixed-point rectification map, map_w x map_h entries
+    int map_w = 0, map_h = 0;
+    bool input_stage() const { return in_format != ORBX_IN_GRAY8 || d_map != nullptr; }
+    int channels() const { return in_format == ORBX_IN_GRAY8 ? 1 : (in_format <= ORBX_IN_RGB8 ? 3 : 4); }
     std::vector<Slot> slots;
 };
 
@@ -478,6 +489,23 @@ int enqueue_kernels(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes) {
     return ORBX_OK;
 }
 
+// N4: raw frames (device) -> rectified gray level 0 in s.img_in.  Returns the level-0 source.
+int run_input_stage(orbx_handle* h, Slot& s, const uint8_t* d_raw, long long raw_fstride, int raw_pitch, int w,
+                    int hgt, int nframes, OrbxSrc* src, int* launches) {
+    if (h->d_map && (h->map_w != w || h->map_h != hgt))
+        return fail(ORBX_E_BAD_ARG, "rectification maps are %dx%d, the image is %dx%d", h->map_w, h->map_h, w, hgt);
+    const int pitch0 = round_up(w, 16);
+    const long long fstride = (long long)pitch0 * hgt;
+    CUDA_TRY(orbx_launch_input(d_raw, raw_fstride, raw_pitch, w, hgt, h->channels(),
+                               h->in_format == ORBX_IN_RGB8 || h->in_format == ORBX_IN_RGBA8, h->gray_bits, h->d_map,
+                               s.img_in, fstride, pitch0, nframes, s.st, launches));
+    src->img0 = s.img_in;
+    src->pitch0 = pitch0;
+    src->stride0 = fstride;
+    src->_pad = 0;
+    return ORBX_OK;
+}
+
 int check_common(orbx_handle* h, int slot, int nframes, int w, int hgt) {
     if (!h) return fail(ORBX_E_BAD_ARG, "null handle");
     if (slot < 0 || slot >= (int)h->slots.size()) return fail(ORBX_E_BAD_ARG, "slot %d out of range", slot);
@@ -551,6 +579,7 @@ int orbx_destroy(orbx_handle* h) {
     cudaSetDevice(h->cfg.device);
     for (Slot& s : h->slots) {
         if (s.st) cudaStreamSynchronize(s.st);
+        cudaFree(s.raw_in);
         cudaFree(s.img_in); cudaFree(s.pyr); cudaFree(s.cellcnt); cudaFree(s.cellkeys);
         cudaFree(s.keysA); cudaFree(s.keysB); cudaFree(s.surv); cudaFree(s.survcnt);
         cudaFree(s.dest); cudaFree(s.header); cudaFree(s.kps); cudaFree(s.desc); cudaFree(s.lap_d);
@@ -561,6 +590,7 @@ int orbx_destroy(orbx_handle* h) {
         if (s.st) cudaStreamDestroy(s.st);
     }
     cudaFree(h->tables);
+    cudaFree(h->d_map);
     delete h;
     return ORBX_OK;
 }
@@ -617,14 +647,62 @@ int orbx_level_size(const orbx_handle* h, int w, int hgt, int level, int* lw, in
     return ORBX_OK;
 }
 
+int orbx_set_input_format(orbx_handle* h, int format, int gray_bits) {
+    if (!h) return fail(ORBX_E_BAD_ARG, "null handle");
+    if (format < ORBX_IN_GRAY8 || format > ORBX_IN_RGBA8) return fail(ORBX_E_BAD_TYPE, "unknown input format %d", format);
+    if (gray_bits != 14 && gray_bits != 15) return fail(ORBX_E_BAD_ARG, "gray_bits must be 14 or 15");
+    for (Slot& s : h->slots)
+        if (s.in_flight) return fail(ORBX_E_BUSY, "a slot has an un-waited submit");
+    h->in_format = format;
+    h->gray_bits = gray_bits;
+    return ORBX_OK;
+}
+
+int orbx_set_rectify_maps(orbx_handle* h, const float* map_x, const float* map_y, int w, int hgt,
+                          size_t map_stride_floats) {
+    if (!h) return fail(ORBX_E_BAD_ARG, "null handle");
+    for (Slot& s : h->slots)
+        if (s.in_flight) return fail(ORBX_E_BUSY, "a slot has an un-waited submit");
+    CUDA_TRY(cudaSetDevice(h->cfg.device));
+    int r;
+    if ((r = sync_all(h))) return r;
+    if (h->d_map) cudaFree(h->d_map);
+    h->d_map = nullptr;
+    h->map_w = h->map_h = 0;
+    if (!map_x && !map_y) return ORBX_OK;
+    if (!map_x || !map_y || w <= 0 || hgt <= 0 || map_stride_floats < (size_t)w)
+        return fail(ORBX_E_BAD_ARG, "bad rectification maps");
+    if (w > h->cfg.max_width || hgt > h->cfg.max_height)
+        return fail(ORBX_E_TOO_LARGE, "maps %dx%d exceed the handle's %dx%d", w, hgt, h->cfg.max_width, h->cfg.max_height);
+    // cv::remap's per-call conversion of CV_32FC1 maps, done once: sx = cvRound(map * INTER_TAB_SIZE)
+    // (float product, round half to even), integer part saturated to short, 5-bit fractions
+    std::vector<uint2> m((size_t)w * hgt);
+    for (int y = 0; y < hgt; ++y)
+        for (int x = 0; x < w; ++x) {
+            const int sx = (int)lrintf(map_x[(size_t)y * map_stride_floats + x] * 32.0f);
+            const int sy = (int)lrintf(map_y[(size_t)y * map_stride_floats + x] * 32.0f);
+            const int ix = std::min(32767, std::max(-32768, sx >> 5)), iy = std::min(32767, std::max(-32768, sy >> 5));
+            m[(size_t)y * w + x] = make_uint2(((uint32_t)ix & 0xffffu) | ((uint32_t)iy << 16),
+                                              (uint32_t)(sx & 31) | ((uint32_t)(sy & 31) << 8));
+        }
+    CUDA_TRY(cudaMalloc(&h->d_map, m.size() * sizeof(uint2)));
+    CUDA_TRY(cudaMemcpy(h->d_map, m.data(), m.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+    h->map_w = w;
+    h->map_h = hgt;
+    return ORBX_OK;
+}
+
 int orbx_extract_device(orbx_handle* h, int slot, const uint8_t* d_imgs, int nframes, int w, int hgt,
                         size_t pitch_bytes, size_t frame_stride_bytes, const int* lap,
                         const int32_t** d_header, const orbx_keypoint** d_kps, const uint8_t** d_desc) {
     int r = check_common(h, slot, nframes, w, hgt);
     if (r) return r;
     if (!d_imgs) return fail(ORBX_E_EMPTY_IMAGE, "null image");
-    if (((uintptr_t)d_imgs & 3) || (pitch_bytes & 3) || (frame_stride_bytes & 3) || pitch_bytes < (size_t)round_up(w, 4))
+    if (!h->input_stage() &&
+        (((uintptr_t)d_imgs & 3) || (pitch_bytes & 3) || (frame_stride_bytes & 3) || pitch_bytes < (size_t)round_up(w, 4)))
         return fail(ORBX_E_BAD_ARG, "device images need 4-byte aligned pointer/pitch/stride and pitch >= round_up(w,4)");
+    if (h->input_stage() && pitch_bytes < (size_t)w * h->channels())
+        return fail(ORBX_E_BAD_ARG, "pitch < width * channels");
     CUDA_TRY(cudaSetDevice(h->cfg.device));
     if ((r = set_shape(h, w, hgt))) return r;
     Slot& s = h->slots[slot];
@@ -634,7 +712,13 @@ int orbx_extract_device(orbx_handle* h, int slot, const uint8_t* d_imgs, int nfr
     src.pitch0 = (int)pitch_bytes;
     src.stride0 = (long long)frame_stride_bytes;
     src._pad = 0;
+    int in_launches = 0;
+    if (h->input_stage() &&
+        (r = run_input_stage(h, s, d_imgs, (long long)frame_stride_bytes, (int)pitch_bytes, w, hgt, nframes, &src,
+                             &in_launches)))
+        return r;
     if ((r = enqueue_kernels(h, s, src, nframes))) return r;
+    s.launches += in_launches;
     s.in_flight = true;
     s.u_n = s.u_mono = s.u_status = nullptr;
     s.cap = 0;
@@ -658,25 +742,55 @@ int orbx_submit_batch(orbx_handle* h, int slot, const uint8_t* const* imgs, int 
     if ((r = set_shape(h, w, hgt))) return r;
     Slot& s = h->slots[slot];
     const OrbxPlan& P = h->plan;
-    // H2D: one copy when the frames are contiguous and tightly packed at the device pitch
-    const int pitch0 = round_up(w, 16);
-    const size_t fstride = (size_t)pitch0 * hgt;
-    bool contiguous = stride_bytes == (size_t)pitch0;
-    for (int i = 1; i < nframes && contiguous; ++i) contiguous = imgs[i] == imgs[0] + (size_t)i * fstride;
-    if (contiguous) {
-        CUDA_TRY(cudaMemcpyAsync(s.img_in, imgs[0], fstride * nframes, cudaMemcpyHostToDevice, s.st));
-    } else {
-        for (int i = 0; i < nframes; ++i)
-            CUDA_TRY(cudaMemcpy2DAsync(s.img_in + (size_t)i * fstride, pitch0, imgs[i], stride_bytes, w, hgt,
-                                       cudaMemcpyHostToDevice, s.st));
-    }
-    if ((r = upload_lap(s, lap, nframes))) return r;
     OrbxSrc src;
-    src.img0 = s.img_in;
-    src.pitch0 = pitch0;
-    src.stride0 = (long long)fstride;
-    src._pad = 0;
+    int in_launches = 0;
+    if ((r = upload_lap(s, lap, nframes))) return r;
+    if (h->input_stage()) {
+        // raw frames -> s.raw_in (rows raw_pitch apart), then remap / luma into the level-0 staging
+        const int ch = h->channels();
+        if (stride_bytes < (size_t)w * ch) return fail(ORBX_E_BAD_ARG, "stride < width * channels");
+        const int raw_pitch = round_up(w * ch, 16);
+        const size_t raw_fstride = (size_t)raw_pitch * hgt;
+        const size_t need = raw_fstride * h->cfg.max_batch + 64;
+        if (s.raw_cap < need) {
+            CUDA_TRY(cudaStreamSynchronize(s.st));
+            if (s.raw_in) cudaFree(s.raw_in);
+            s.raw_in = nullptr;
+            s.raw_cap = 0;
+            CUDA_TRY(cudaMalloc(&s.raw_in, need));
+            s.raw_cap = need;
+        }
+        bool contiguous = stride_bytes == (size_t)raw_pitch;
+        for (int i = 1; i < nframes && contiguous; ++i) contiguous = imgs[i] == imgs[0] + (size_t)i * raw_fstride;
+        if (contiguous) {
+            CUDA_TRY(cudaMemcpyAsync(s.raw_in, imgs[0], raw_fstride * nframes, cudaMemcpyHostToDevice, s.st));
+        } else {
+            for (int i = 0; i < nframes; ++i)
+                CUDA_TRY(cudaMemcpy2DAsync(s.raw_in + (size_t)i * raw_fstride, raw_pitch, imgs[i], stride_bytes,
+                                           (size_t)w * ch, hgt, cudaMemcpyHostToDevice, s.st));
+        }
+        if ((r = run_input_stage(h, s, s.raw_in, (long long)raw_fstride, raw_pitch, w, hgt, nframes, &src, &in_launches)))
+            return r;
+    } else {
+        // H2D: one copy when the frames are contiguous and tightly packed at the device pitch
+        const int pitch0 = round_up(w, 16);
+        const size_t fstride = (size_t)pitch0 * hgt;
+        bool contiguous = stride_bytes == (size_t)pitch0;
+        for (int i = 1; i < nframes && contiguous; ++i) contiguous = imgs[i] == imgs[0] + (size_t)i * fstride;
+        if (contiguous) {
+            CUDA_TRY(cudaMemcpyAsync(s.img_in, imgs[0], fstride * nframes, cudaMemcpyHostToDevice, s.st));
+        } else {
+            for (int i = 0; i < nframes; ++i)
+                CUDA_TRY(cudaMemcpy2DAsync(s.img_in + (size_t)i * fstride, pitch0, imgs[i], stride_bytes, w, hgt,
+                                           cudaMemcpyHostToDevice, s.st));
+        }
+        src.img0 = s.img_in;
+        src.pitch0 = pitch0;
+        src.stride0 = (long long)fstride;
+        src._pad = 0;
+    }
     if ((r = enqueue_kernels(h, s, src, nframes))) return r;
+    s.launches += in_launches;
     // D2H: header, keypoints, descriptors (device rows are out_cap apart, caller rows cap apart)
     const int rows = std::min(cap, P.out_cap);
     CUDA_TRY(cudaMemcpyAsync(s.h_header, s.header, (size_t)nframes * 16, cudaMemcpyDeviceToHost, s.st));

@@ -30,6 +30,7 @@ class ORBextractor:
         self.nfeatures, self.scaleFactor, self.nlevels = nfeatures, scaleFactor, nlevels
         self.max_batch, self.n_slots = max_batch, n_slots
         self._keep = {}
+        self._channels = 1
 
     def close(self):
         if getattr(self, "h", None):
@@ -41,6 +42,28 @@ class ORBextractor:
             self.close()
         except Exception:
             pass
+
+    # ---- input stage (N4): cvtColor / cv::remap in front of level 0 ---------------------------------
+    FORMATS = {"gray": (0, 1), "bgr": (1, 3), "rgb": (2, 3), "bgra": (3, 4), "rgba": (4, 4)}
+
+    def set_input_format(self, fmt: str = "gray", gray_bits: int = 15):
+        """What Tracking::GrabImage* does with a colour image (src/Tracking.cc:354-379): later calls
+        take H x W x C images.  gray_bits: 15 = OpenCV >= 4 luma coefficients, 14 = OpenCV 2/3."""
+        code, ch = self.FORMATS[fmt]
+        check(self.lib.orbx_set_input_format(self.h, code, gray_bits))
+        self._channels = ch
+
+    def set_rectify_maps(self, map_x=None, map_y=None):
+        """cv::remap(im, imRect, M1, M2, INTER_LINEAR) of Examples/Stereo/stereo_euroc.cc:170-171 in
+        front of level 0; maps are the CV_32FC1 outputs of cv::initUndistortRectifyMap."""
+        if map_x is None:
+            check(self.lib.orbx_set_rectify_maps(self.h, None, None, 0, 0, 0))
+            return
+        mx = np.ascontiguousarray(map_x, np.float32)
+        my = np.ascontiguousarray(map_y, np.float32)
+        assert mx.shape == my.shape and mx.ndim == 2
+        check(self.lib.orbx_set_rectify_maps(self.h, mx.ctypes.data, my.ctypes.data, mx.shape[1], mx.shape[0],
+                                             mx.shape[1]))
 
     # ---- getters (include/ORBextractor.h:61-81) ------------------------------------------------
     def GetLevels(self) -> int:
@@ -83,9 +106,10 @@ class ORBextractor:
         a non-uint8 image raises (the reference asserts CV_8UC1, :1076)."""
         if image is None or image.size == 0:
             return -1, np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
-        if image.dtype != np.uint8 or image.ndim != 2:
-            raise OrbxError(_lib.ORBX_E_BAD_TYPE, "image must be 8-bit single channel")
-        if image.strides[1] != 1:
+        ch = self._channels
+        if image.dtype != np.uint8 or (ch == 1 and image.ndim != 2) or (ch > 1 and (image.ndim != 3 or image.shape[2] != ch)):
+            raise OrbxError(_lib.ORBX_E_BAD_TYPE, "image must be 8-bit with %d channel(s)" % ch)
+        if image.strides[1] != ch or (ch > 1 and image.strides[2] != 1):
             image = np.ascontiguousarray(image)
         cap = cap or self.max_keypoints()
         kps = np.zeros(cap, KP_DTYPE)
@@ -100,7 +124,7 @@ class ORBextractor:
         """images: list of equally-shaped uint8 arrays (or one [B,H,W] array)."""
         imgs = [np.ascontiguousarray(im) for im in images]
         B = len(imgs)
-        h, w = imgs[0].shape
+        h, w = imgs[0].shape[:2]
         cap = cap or self.max_keypoints()
         ptrs = (C.c_void_p * B)(*[im.ctypes.data for im in imgs])
         lap = None

@@ -208,3 +208,68 @@ def test_other_scale_factors_and_level_counts(oracle_libs, synth, scale, nlevels
         _compare_final(ref, got, (scale, nlevels))
     finally:
         ex.close()
+
+
+def _rect_maps(h, w, seed):
+    """A smooth lens-like warp around the identity whose sources leave the image at the borders."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+    cx, cy = np.float32(w / 2 + 3.7), np.float32(h / 2 - 2.2)
+    r2 = ((xx - cx) ** 2 + (yy - cy) ** 2) / np.float32(w * w)
+    k = np.float32(0.12)
+    mx = (cx + (xx - cx) * (1 + k * r2) + rng.uniform(-0.02, 0.02, (h, w))).astype(np.float32)
+    my = (cy + (yy - cy) * (1 + k * r2) + rng.uniform(-0.02, 0.02, (h, w))).astype(np.float32)
+    return mx, my
+
+
+@pytest.mark.parametrize("fmt,bits,rect", [("bgr", 15, False), ("rgb", 15, False), ("bgra", 15, False),
+                                           ("rgba", 14, False), ("gray", 15, True), ("bgr", 15, True),
+                                           ("rgba", 15, True), ("rgb", 14, True)])
+def test_input_stage_cvtcolor_and_rectification(oracle_libs, synth, fmt, bits, rect):
+    """N4: colour conversion (src/Tracking.cc:354-379) and stereo rectification
+    (Examples/Stereo/stereo_euroc.cc:170-171) fused in front of level 0: the level-0 image equals the
+    CPU oracle's remap-then-luma bit for bit, and the extraction equals the oracle extractor run on it."""
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    h, w = 480, 752
+    ch = {"gray": 1, "bgr": 3, "rgb": 3, "bgra": 4, "rgba": 4}[fmt]
+    rng = np.random.default_rng(ch * 10 + bits + rect)
+    base = synth.frame("noise", h, w, 31)
+    if ch == 1:
+        raw = base
+    else:
+        planes = [np.clip(base.astype(np.int32) + rng.integers(-40, 41, (h, w)), 0, 255).astype(np.uint8)
+                  for _ in range(3)]
+        if ch == 4:
+            planes.append(rng.integers(0, 256, (h, w), dtype=np.uint8))
+        raw = np.ascontiguousarray(np.stack(planes, axis=2))
+    want0 = raw
+    mx = my = None
+    if rect:
+        mx, my = _rect_maps(h, w, 5)
+        want0 = oracle_libs.remap_linear(want0, mx, my)
+    if ch > 1:
+        want0 = oracle_libs.cvt_gray(want0, fmt in ("rgb", "rgba"), bits)
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_size=(h, w), max_batch=3)
+    ex.set_input_format(fmt, bits)
+    if rect:
+        ex.set_rectify_maps(mx, my)
+    got = ex(raw, (0, 1000))
+    assert np.array_equal(ex.pyramid_level(0, (h, w)), want0)
+    ora = _oracle(oracle_libs, 1000)
+    _compare_final(ora(want0, (0, 1000)), got, (fmt, bits, rect))
+    # batched + strided raw rows
+    wide = np.zeros((h, w + 9) + raw.shape[2:], np.uint8)
+    wide[:, :w] = raw
+    res = ex.extract_batch([raw, wide[:, :w], raw], [(0, 1000)] * 3)
+    for r in res:
+        _compare_final(ora(want0, (0, 1000)), r, (fmt, "batch"))
+    _compare_final(ora(want0, (0, 1000)), ex(wide[:, :w], (0, 1000)), (fmt, "strided rows"))
+    # switching the stage off restores the plain path
+    ex.set_input_format("gray", 15)
+    ex.set_rectify_maps(None, None)
+    _compare_final(ora(base, (0, 1000)), ex(base, (0, 1000)), "plain again")
+    if rect:
+        with pytest.raises(Exception):
+            ex.set_rectify_maps(mx[:100], my[:100])
+            ex(base, (0, 1000))
+    ex.close()

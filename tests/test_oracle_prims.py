@@ -130,3 +130,61 @@ def test_fast_atan2_matches_cv2(lib):
 def test_cv_round_is_half_even(lib):
     for v, r in ((0.5, 0), (1.5, 2), (2.5, 2), (-0.5, 0), (-1.5, -2), (2.4999, 2), (3.5, 4)):
         assert lib.orbo_prim_round(v) == r
+
+
+@pytest.mark.parametrize("code,channels,rgb", [("COLOR_BGR2GRAY", 3, 0), ("COLOR_RGB2GRAY", 3, 1),
+                                               ("COLOR_BGRA2GRAY", 4, 0), ("COLOR_RGBA2GRAY", 4, 1)])
+def test_cvt_gray_matches_cv2(lib, code, channels, rgb):
+    """N4: cvtColor to gray (src/Tracking.cc:354-379).  cv2 4.13 uses the 15-bit coefficients."""
+    rng = np.random.default_rng(channels * 2 + rgb)
+    for shape in [(480, 752), (37, 53), (1, 1)]:
+        src = rng.integers(0, 256, size=shape + (channels,), dtype=np.uint8)
+        dst = np.zeros(shape, np.uint8)
+        lib.orbo_prim_cvt_gray(_p(src), shape[0], shape[1], C.c_size_t(src.strides[0]), channels, rgb, 15,
+                               _p(dst), C.c_size_t(dst.strides[0]))
+        assert np.array_equal(dst, cv2.cvtColor(src, getattr(cv2, code)))
+    # all 2^24 colours once
+    a = np.arange(1 << 24, dtype=np.uint32)
+    src = np.stack([a & 255, (a >> 8) & 255, a >> 16], axis=1).astype(np.uint8).reshape(4096, 4096, 3)
+    dst = np.zeros((4096, 4096), np.uint8)
+    lib.orbo_prim_cvt_gray(_p(src), 4096, 4096, C.c_size_t(src.strides[0]), 3, 0, 15, _p(dst),
+                           C.c_size_t(dst.strides[0]))
+    assert np.array_equal(dst, cv2.cvtColor(src, cv2.COLOR_BGR2GRAY))
+
+
+def _euroc_maps():
+    K = np.array([[458.654, 0, 367.215], [0, 457.296, 248.375], [0, 0, 1]])
+    D = np.array([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0])
+    R = np.array([[0.999966347530033, -0.001422739138722922, 0.008079580483432283],
+                  [0.001365741834644127, 0.9999741760894847, 0.007055629199258132],
+                  [-0.008089410156878961, -0.007044357138835809, 0.9999424675829176]])
+    P = np.array([[435.2046959714599, 0, 367.4517211914062], [0, 435.2046959714599, 252.2008514404297],
+                  [0, 0, 1]])
+    return cv2.initUndistortRectifyMap(K, D, R, P, (752, 480), cv2.CV_32F)
+
+
+@pytest.mark.parametrize("channels", [1, 3, 4])
+def test_remap_linear_matches_cv2(lib, channels):
+    """N4: cv::remap(INTER_LINEAR, BORDER_CONSTANT 0) with CV_32FC1 maps
+    (Examples/Stereo/stereo_euroc.cc:170-171): EuRoC rectification maps, noisy maps that leave the
+    image on every side, and exact half-way fractions (cvRound ties)."""
+    rng = np.random.default_rng(40 + channels)
+    cases = []
+    m1, m2 = _euroc_maps()
+    cases.append(((480, 752), m1, m2))
+    for (h, w), amp in [((120, 160), 0.5), ((120, 160), 60.0), ((33, 47), 8.0)]:
+        yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+        mx = (xx + 3.3 * np.sin(yy / 17) + rng.uniform(-amp, amp, (h, w))).astype(np.float32)
+        my = (yy + 2.7 * np.cos(xx / 23) + rng.uniform(-amp, amp, (h, w))).astype(np.float32)
+        cases.append(((h, w), mx, my))
+    yy, xx = np.mgrid[0:64, 0:64].astype(np.float32)
+    cases.append(((64, 64), xx + np.float32(1 / 64), yy + np.float32(3 / 64)))
+    cases.append(((64, 64), xx - np.float32(1 / 64) - 5, yy + np.float32(63 / 64)))
+    for (h, w), mx, my in cases:
+        shape = (h, w) if channels == 1 else (h, w, channels)
+        src = rng.integers(0, 256, size=shape, dtype=np.uint8)
+        mx, my = np.ascontiguousarray(mx), np.ascontiguousarray(my)
+        dst = np.zeros(shape, np.uint8)
+        lib.orbo_prim_remap(_p(src), h, w, C.c_size_t(src.strides[0]), channels, _p(mx), _p(my), _p(dst), h, w,
+                            C.c_size_t(dst.strides[0]))
+        assert np.array_equal(dst, cv2.remap(src, mx, my, cv2.INTER_LINEAR)), (h, w)
