@@ -256,12 +256,22 @@ def run_ours(args):
     frames = make_frames(cfg, B, min(B, 24))
     if rank:
         frames = np.roll(frames, 13 * rank, axis=2)
-    fbytes = B * h * w
+    ch = 3 if args.input.startswith("bgr") else 1
+    if ch == 3:   # three differently shifted copies of the gray frame as B, G, R
+        frames = np.ascontiguousarray(np.stack([frames, np.roll(frames, 1, axis=2), np.roll(frames, 2, axis=1)], axis=3))
+        _lib.check(lib.orbx_set_input_format(hd, 1, 15))
+    if args.input.endswith("rect"):   # a lens-like warp around the identity (EuRoC-sized distortion)
+        yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+        r2 = ((xx - w / 2) ** 2 + (yy - h / 2) ** 2) / np.float32(w * w)
+        mx = np.ascontiguousarray((w / 2 + (xx - w / 2) * (1 + 0.12 * r2)).astype(np.float32))
+        my = np.ascontiguousarray((h / 2 + (yy - h / 2) * (1 + 0.12 * r2)).astype(np.float32))
+        _lib.check(lib.orbx_set_rectify_maps(hd, mx.ctypes.data, my.ctypes.data, w, h, w))
+    fbytes = B * h * w * ch
     h_in = lib.orbx_host_alloc(fbytes)
     C.memmove(h_in, frames.ctypes.data, fbytes)
     d_in = torch.from_numpy(frames).cuda()
     lap = np.tile(np.array([0, 1000], np.int32), (B, 1))
-    ptrs = (C.c_void_p * B)(*[h_in + i * h * w for i in range(B)])
+    ptrs = (C.c_void_p * B)(*[h_in + i * h * w * ch for i in range(B)])
 
     # N > 1: two pipeline slots alternate so that the NCCL gather of step i (dedicated stream)
     # overlaps the kernels of step i+1 (north_star: NCCL only gathers results)
@@ -271,7 +281,7 @@ def run_ours(args):
     d_hdr, d_kps, d_desc = C.c_void_p(), C.c_void_p(), C.c_void_p()
 
     def step_device(sl=0):
-        _lib.check(lib.orbx_extract_device(hd, sl, d_in.data_ptr(), B, w, h, w, h * w, lap.ctypes.data,
+        _lib.check(lib.orbx_extract_device(hd, sl, d_in.data_ptr(), B, w, h, w * ch, h * w * ch, lap.ctypes.data,
                                            C.byref(d_hdr), C.byref(d_kps), C.byref(d_desc)))
         _lib.check(lib.orbx_wait(hd, sl))
 
@@ -323,13 +333,13 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    stage = np.zeros(6, np.float64)
-    ms6 = np.zeros(6, np.float32)
+    stage = np.zeros(7, np.float64)
+    ms6 = np.zeros(7, np.float32)
     launches = 0
     ev0.record(ext[0])
     for i in range(args.steps):
         one_step(i)
-        lib.orbx_last_stage_ms(hd, i % nsl, ms6.ctypes.data, 6)
+        lib.orbx_last_stage_ms(hd, i % nsl, ms6.ctypes.data, 7)
         stage += ms6
         launches += lib.orbx_last_launch_count(hd, i % nsl)
     # ev1 closes the region on a stream that has waited for every slot stream and the gathers
@@ -365,7 +375,7 @@ def run_ours(args):
 
     def submit(sl):
         o = outs[sl]
-        _lib.check(lib.orbx_submit_batch(hd, sl, ptrs, B, w, h, w, lap.ctypes.data, o["kps"], o["desc"], cap,
+        _lib.check(lib.orbx_submit_batch(hd, sl, ptrs, B, w, h, w * ch, lap.ctypes.data, o["kps"], o["desc"], cap,
                                          o["n"].ctypes.data, o["mono"].ctypes.data, o["st"].ctypes.data))
 
     for i in range(max(args.warmup, n_slots)):
@@ -389,7 +399,7 @@ def run_ours(args):
     # ---- single-frame latency (BASELINE.json: "p50 us/frame"): synchronous orbx_extract of one pinned
     # host frame, H2D + 11 launches + D2H, no batching -----------------------------------------------
     lat = None
-    if rank == 0:
+    if rank == 0 and args.input == "gray":
         n1, m1 = C.c_int(), C.c_int()
         o = outs[0]
 
@@ -437,6 +447,11 @@ def run_ours(args):
             gbs = ab[nm] * B / (stage[k] * 1e-3) / 1e9 if stage[k] > 0 else 0.0
             kernels[nm] = {"ms_per_launch_batch": round(float(stage[k]), 4), "alg_bytes_per_frame": int(ab[nm]),
                            "achieved_gbs": round(gbs, 1), "frac": round(gbs / peak, 4)}
+        if args.input != "gray":   # N4 input stage: raw bytes read once + level 0 written once (+ 8-byte map entries per batch)
+            ab["input"] = h * w * ch + h * w + (8 * h * w / B if args.input.endswith("rect") else 0)
+            gbs = ab["input"] * B / (stage[6] * 1e-3) / 1e9 if stage[6] > 0 else 0.0
+            kernels["input"] = {"ms_per_launch_batch": round(float(stage[6]), 4), "alg_bytes_per_frame": int(ab["input"]),
+                                "achieved_gbs": round(gbs, 1), "frac": round(gbs / peak, 4)}
         dom = max(names, key=lambda nm: kernels[nm]["ms_per_launch_batch"])
         # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
         # capture (profiles/traffic.json: per kernel, at the batch it was captured with)
@@ -461,7 +476,8 @@ def run_ours(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic",
-            "config": {"workload": workload_name(cfg, h, w), "frames_per_step_per_gpu": B,
+            "config": {"workload": workload_name(cfg, h, w) + ("" if args.input == "gray" else f" [raw input: {args.input}]"),
+                       "frames_per_step_per_gpu": B,
                        "l2_policy": f"inputs larger than L2: {B} distinct frames = {fbytes / 1e6:.0f} MB of input "
                                     f"plus {B} pyramids/scratch per step (126 MB L2)",
                        "parallelism": f"frames sharded over {world} GPU(s), independent streams; NCCL all_gather of result slabs only"
@@ -508,6 +524,9 @@ def main():
     ap.add_argument("--config", default="C1", choices=["C1", "C2", "C3", "C4", "C5"])
     ap.add_argument("--batch", type=int, default=0, help="frames per step per GPU (default: by config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--input", default="gray", choices=["gray", "bgr", "gray+rect", "bgr+rect"],
+                    help="raw input of the frames: the N4 input stage (cvtColor / cv::remap rectification) runs in "
+                         "front of level 0 for anything but 'gray' (the BASELINE.json configs are gray)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -23,7 +23,7 @@
 void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes,
                          cudaStream_t st, int* launches);
 cudaError_t orbx_launch_input(const uint8_t* raw, long long raw_fstride, int raw_pitch, int w, int h, int channels,
-                              int rgb_order, int gray_bits, const uint2* map, uint8_t* dst, long long dst_fstride,
+                              int rgb_order, int gray_bits, const uint4* map, uint8_t* dst, long long dst_fstride,
                               int dst_pitch, int nframes, cudaStream_t st, int* launches);
 cudaError_t orbx_configure_fast(const OrbxPlan& P);
 cudaError_t orbx_launch_fast(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
@@ -110,6 +110,8 @@ struct Slot {
     int nframes = 0, cap = 0, launches = 0;
     int *u_n = nullptr, *u_mono = nullptr, *u_status = nullptr;
     cudaEvent_t ev[6] = {};      // stage boundaries (ORBX_FLAG_STAGE_TIMING)
+    cudaEvent_t ev_in[2] = {};   // around the input stage (N4)
+    bool in_timed = false;
     OrbxSrc src{};               // level-0 source of the last run (for the debug taps)
     int run_w = 0, run_h = 0;
     // CUDA graph of the kernel sequence for small batches (single-frame latency path)
@@ -133,7 +135,7 @@ struct orbx_handle {
     unsigned long long epoch = 1;   // bumped whenever the plan or a device buffer changes
     // input stage (N4)
     int in_format = ORBX_IN_GRAY8, gray_bits = 15;
-    uint2* d_map = nullptr;         // fixed-point rectification map, map_w x map_h entries
+    uint4* d_map = nullptr;         // fixed-point rectification map, map_w x map_h entries (k_input.cu)
     int map_w = 0, map_h = 0;
     bool input_stage() const { return in_format != ORBX_IN_GRAY8 || d_map != nullptr; }
     int channels() const { return in_format == ORBX_IN_GRAY8 ? 1 : (in_format <= ORBX_IN_RGB8 ? 3 : 4); }
@@ -496,9 +498,13 @@ int run_input_stage(orbx_handle* h, Slot& s, const uint8_t* d_raw, long long raw
         return fail(ORBX_E_BAD_ARG, "rectification maps are %dx%d, the image is %dx%d", h->map_w, h->map_h, w, hgt);
     const int pitch0 = round_up(w, 16);
     const long long fstride = (long long)pitch0 * hgt;
+    const bool timing = (h->cfg.flags & ORBX_FLAG_STAGE_TIMING) != 0;
+    if (timing) CUDA_TRY(cudaEventRecord(s.ev_in[0], s.st));
     CUDA_TRY(orbx_launch_input(d_raw, raw_fstride, raw_pitch, w, hgt, h->channels(),
                                h->in_format == ORBX_IN_RGB8 || h->in_format == ORBX_IN_RGBA8, h->gray_bits, h->d_map,
                                s.img_in, fstride, pitch0, nframes, s.st, launches));
+    if (timing) CUDA_TRY(cudaEventRecord(s.ev_in[1], s.st));
+    s.in_timed = timing;
     src->img0 = s.img_in;
     src->pitch0 = pitch0;
     src->stride0 = fstride;
@@ -562,6 +568,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle** out) {
             break;
         }
         for (int k = 0; k < 6; ++k) cudaEventCreate(&s.ev[k]);
+        for (int k = 0; k < 2; ++k) cudaEventCreate(&s.ev_in[k]);
     }
     if (r == ORBX_OK) r = set_shape(h, cfg->max_width, cfg->max_height);
     if (r != ORBX_OK) {
@@ -586,6 +593,7 @@ int orbx_destroy(orbx_handle* h) {
         if (s.h_header) cudaFreeHost(s.h_header);
         if (s.h_lap) cudaFreeHost(s.h_lap);
         for (int k = 0; k < 6; ++k) if (s.ev[k]) cudaEventDestroy(s.ev[k]);
+        for (int k = 0; k < 2; ++k) if (s.ev_in[k]) cudaEventDestroy(s.ev_in[k]);
         if (s.gexec) cudaGraphExecDestroy(s.gexec);
         if (s.st) cudaStreamDestroy(s.st);
     }
@@ -637,7 +645,11 @@ int orbx_last_stage_ms(orbx_handle* h, int slot, float* ms, int n) {
     if (s.in_flight) return fail(ORBX_E_BUSY, "slot %d not waited", slot);
     for (int k = 0; k < 5 && k < n; ++k) CUDA_TRY(cudaEventElapsedTime(&ms[k], s.ev[k], s.ev[k + 1]));
     if (n > 5) CUDA_TRY(cudaEventElapsedTime(&ms[5], s.ev[0], s.ev[5]));
-    return n < 6 ? n : 6;
+    if (n > 6) {
+        ms[6] = 0.f;
+        if (s.in_timed && h->input_stage()) CUDA_TRY(cudaEventElapsedTime(&ms[6], s.ev_in[0], s.ev_in[1]));
+    }
+    return n < 7 ? n : 7;
 }
 
 int orbx_level_size(const orbx_handle* h, int w, int hgt, int level, int* lw, int* lh) {
@@ -676,17 +688,26 @@ int orbx_set_rectify_maps(orbx_handle* h, const float* map_x, const float* map_y
         return fail(ORBX_E_TOO_LARGE, "maps %dx%d exceed the handle's %dx%d", w, hgt, h->cfg.max_width, h->cfg.max_height);
     // cv::remap's per-call conversion of CV_32FC1 maps, done once: sx = cvRound(map * INTER_TAB_SIZE)
     // (float product, round half to even), integer part saturated to short, 5-bit fractions
-    std::vector<uint2> m((size_t)w * hgt);
+    // then everything frame independent is folded into the entry: taps clamped into the image, the
+    // weights of taps outside it zeroed (BORDER_CONSTANT 0)
+    std::vector<uint4> m((size_t)w * hgt);
     for (int y = 0; y < hgt; ++y)
         for (int x = 0; x < w; ++x) {
             const int sx = (int)lrintf(map_x[(size_t)y * map_stride_floats + x] * 32.0f);
             const int sy = (int)lrintf(map_y[(size_t)y * map_stride_floats + x] * 32.0f);
             const int ix = std::min(32767, std::max(-32768, sx >> 5)), iy = std::min(32767, std::max(-32768, sy >> 5));
-            m[(size_t)y * w + x] = make_uint2(((uint32_t)ix & 0xffffu) | ((uint32_t)iy << 16),
-                                              (uint32_t)(sx & 31) | ((uint32_t)(sy & 31) << 8));
+            const int fx = sx & 31, fy = sy & 31;
+            const bool x0 = ix >= 0 && ix < w, x1 = ix + 1 >= 0 && ix + 1 < w;
+            const bool y0 = iy >= 0 && iy < hgt, y1 = iy + 1 >= 0 && iy + 1 < hgt;
+            const uint32_t a00 = (x0 && y0) ? (32 - fx) * (32 - fy) : 0, a01 = (x1 && y0) ? fx * (32 - fy) : 0;
+            const uint32_t a10 = (x0 && y1) ? (32 - fx) * fy : 0, a11 = (x1 && y1) ? fx * fy : 0;
+            const int cx0 = std::min(w - 1, std::max(0, ix)), cx1 = std::min(w - 1, std::max(0, ix + 1));
+            const int cy0 = std::min(hgt - 1, std::max(0, iy)), cy1 = std::min(hgt - 1, std::max(0, iy + 1));
+            m[(size_t)y * w + x] = make_uint4((uint32_t)cx0 | ((uint32_t)cy0 << 16), a00 | (a01 << 16), a10 | (a11 << 16),
+                                              (uint32_t)(cx1 - cx0) | ((uint32_t)(cy1 - cy0) << 1));
         }
-    CUDA_TRY(cudaMalloc(&h->d_map, m.size() * sizeof(uint2)));
-    CUDA_TRY(cudaMemcpy(h->d_map, m.data(), m.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMalloc(&h->d_map, m.size() * sizeof(uint4)));
+    CUDA_TRY(cudaMemcpy(h->d_map, m.data(), m.size() * sizeof(uint4), cudaMemcpyHostToDevice));
     h->map_w = w;
     h->map_h = hgt;
     return ORBX_OK;
