@@ -143,6 +143,45 @@ int orbm_search_by_projection_frames(orbm_context* c, const orbm_frame_view* cur
                                      float th, int forward, int backward, float bf,
                                      int check_orientation, int32_t* kp_obs, int32_t* kp_match);
 
+/* ---- fisheye stereo frames (Frame::Nleft != -1; KannalaBrandt8 rigs, config C3) ------------------
+ * The frame holds the left keypoints in `F` (keys = mvKeys, n = Nleft, u_right = NULL) and the right
+ * camera's half here; descriptor rows, mvpMapPoints and therefore kp_obs / kp_match are indexed
+ * [0, Nleft) for the left and Nleft + j for right keypoint j, as in the reference. */
+typedef struct orbm_frame_right {
+    const orbx_keypoint* keys;     /* mvKeysRight (n records) */
+    const uint8_t* desc;           /* mDescriptors rows Nleft.. (n x 32) */
+    int32_t n;                     /* Nright */
+    const int32_t* left_to_right;  /* mvLeftToRightMatch (Nleft ints) or NULL = all -1 */
+    const int32_t* right_to_left;  /* mvRightToLeftMatch (Nright ints) or NULL = all -1 */
+} orbm_frame_right;
+
+/* The right-camera tracking fields of a map point (Frame::isInFrustum, src/Frame.cc:548-569). */
+typedef struct orbm_map_point_right {
+    float proj_x, proj_y;  /* mTrackProjXR, mTrackProjYR */
+    float view_cos;        /* mTrackViewCosR */
+    int32_t level;         /* mnTrackScaleLevelR (-1: none) */
+    uint8_t in_view;       /* mbTrackInViewR */
+    uint8_t _pad[3];
+} orbm_map_point_right;
+
+/* SearchByProjection(F, vpMapPoints, th, bFarPoints, thFarPoints) for a fisheye stereo frame:
+ * left branch src/ORBmatcher.cc:66-147 (no mvuRight gate; a match is mirrored onto
+ * mvLeftToRightMatch), right branch :149-215 (window in mGridRight, radius NOT scaled by th,
+ * mirrored onto mvRightToLeftMatch).  kp_obs / kp_match: Nleft + Nright ints. */
+int orbm_search_by_projection_points_stereo(orbm_context* c, const orbm_frame_view* F, const orbm_frame_right* R,
+                                            const orbm_map_point* mps, const orbm_map_point_right* mps_r,
+                                            const uint8_t* mp_desc, int m, float th, int far_points,
+                                            float th_far, float nn_ratio, int32_t* kp_obs, int32_t* kp_match);
+
+/* SearchByProjection(CurrentFrame, LastFrame, th, bMono) for a fisheye stereo current frame
+ * (src/ORBmatcher.cc:1965-2181): uv_right = 2 floats per observation, the projection of
+ * mTrl * x3Dc (:2090-2092).  kp_obs / kp_match: Nleft + Nright ints. */
+int orbm_search_by_projection_frames_stereo(orbm_context* c, const orbm_frame_view* cur, const orbm_frame_right* R,
+                                            const orbm_last_obs* last, const float* uv_right,
+                                            const uint8_t* last_desc, int n_last, float th, int forward,
+                                            int backward, int check_orientation, int32_t* kp_obs,
+                                            int32_t* kp_match);
+
 /* SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), src/ORBmatcher.cc:710-825.
  * prev_matched: F1.n (x, y) pairs, in/out.  matches12: F1.n ints, out.  Returns nmatches. */
 int orbm_search_for_initialization(orbm_context* c, const orbm_frame_view* F1,

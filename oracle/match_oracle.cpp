@@ -54,6 +54,20 @@ struct MapPointPod {  // orbm_map_point
     uint8_t in_view, bad, pad[2];
 };
 
+struct FrameRight {  // orbm_frame_right
+    const Kp* keys;
+    const uint8_t* desc;
+    int32_t n;
+    const int32_t* left_to_right;
+    const int32_t* right_to_left;
+};
+
+struct MapPointRightPod {  // orbm_map_point_right
+    float proj_x, proj_y, view_cos;
+    int32_t level;
+    uint8_t in_view, pad[3];
+};
+
 struct LastObs {  // orbm_last_obs
     float u, v, inv_z, angle;
     int32_t octave, observations;
@@ -530,6 +544,224 @@ int orbo_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx_o
         dist_out[2 * i + 1] = i2 < 0 ? -1 : b2;
     }
     return 0;
+}
+
+// The right camera's half of a fisheye stereo frame seen through the same grid geometry:
+// AssignFeaturesToGrid (src/Frame.cc:377-408) puts right keypoints into mGridRight with PosInGrid
+// of the frame's own bounds, GetFeaturesInArea(..., bRight = true) reads mGridRight / mvKeysRight.
+static FrameView right_half(const FrameView& F, const FrameRight& R) {
+    FrameView v = F;
+    v.keys = R.keys;
+    v.desc = R.desc;
+    v.n = R.n;
+    v.u_right = nullptr;
+    return v;
+}
+
+// src/ORBmatcher.cc:48-218 with F.Nleft != -1 (fisheye stereo): mvpMapPoints / descriptors are
+// indexed [0, Nleft) for the left and Nleft + j for the right camera.
+int orbo_search_by_projection_points_stereo(const FrameView* Fp, const FrameRight* Rp, const MapPointPod* mps,
+                                            const MapPointRightPod* mps_r, const uint8_t* mp_desc, int m, float th,
+                                            int bFarPoints, float thFarPoints, float mfNNratio, int32_t* kp_obs,
+                                            int32_t* kp_match) {
+    const FrameView& F = *Fp;
+    const FrameRight& R = *Rp;
+    const FrameView FR = right_half(F, R);
+    GridO G(F), GR(FR);
+    const int Nleft = F.n;
+    for (int i = 0; i < Nleft + R.n; ++i) kp_match[i] = -1;
+    int nmatches = 0, left = 0, right = 0;
+    const bool bFactor = th != 1.0;
+    for (int iMP = 0; iMP < m; iMP++) {
+        const MapPointPod& pMP = mps[iMP];
+        const MapPointRightPod& pR = mps_r[iMP];
+        if (!pMP.in_view && !pR.in_view) continue;
+        if (bFarPoints && pMP.depth > thFarPoints) continue;
+        if (pMP.bad) continue;
+        if (pMP.in_view) {
+            const int& nPredictedLevel = pMP.level;
+            float r = radius_by_viewing_cos(pMP.view_cos);
+            if (bFactor) r *= th;
+            const std::vector<size_t> vIndices = get_features_in_area(
+                F, G, pMP.proj_x, pMP.proj_y, r * F.scale_factors[nPredictedLevel], nPredictedLevel - 1, nPredictedLevel);
+            if (!vIndices.empty()) {
+                const uint8_t* MPdescriptor = mp_desc + (size_t)iMP * 32;
+                int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+                for (std::vector<size_t>::const_iterator vit = vIndices.begin(), vend = vIndices.end(); vit != vend; vit++) {
+                    const size_t idx = *vit;
+                    if (kp_obs[idx] > 0) continue;
+                    // (F.Nleft == -1 && F.mvuRight[idx] > 0) is false here
+                    const int dist = descriptor_distance(MPdescriptor, F.desc + idx * 32);
+                    if (dist < bestDist) {
+                        bestDist2 = bestDist;
+                        bestDist = dist;
+                        bestLevel2 = bestLevel;
+                        bestLevel = F.keys[idx].octave;   // idx < Nleft: mvKeys[idx]
+                        bestIdx = idx;
+                    } else if (dist < bestDist2) {
+                        bestLevel2 = F.keys[idx].octave;
+                        bestDist2 = dist;
+                    }
+                }
+                if (bestDist <= TH_HIGH) {
+                    if (bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2) continue;
+                    if (bestLevel != bestLevel2 || bestDist <= mfNNratio * bestDist2) {
+                        kp_match[bestIdx] = iMP;
+                        kp_obs[bestIdx] = pMP.observations;
+                        if (R.left_to_right && R.left_to_right[bestIdx] != -1) {
+                            kp_match[R.left_to_right[bestIdx] + Nleft] = iMP;
+                            kp_obs[R.left_to_right[bestIdx] + Nleft] = pMP.observations;
+                            nmatches++;
+                            right++;
+                        }
+                        nmatches++;
+                        left++;
+                    }
+                }
+            }
+        }
+        if (pR.in_view) {
+            const int& nPredictedLevel = pR.level;
+            if (nPredictedLevel != -1) {
+                float r = radius_by_viewing_cos(pR.view_cos);
+                const std::vector<size_t> vIndices = get_features_in_area(
+                    FR, GR, pR.proj_x, pR.proj_y, r * F.scale_factors[nPredictedLevel], nPredictedLevel - 1, nPredictedLevel);
+                if (vIndices.empty()) continue;
+                const uint8_t* MPdescriptor = mp_desc + (size_t)iMP * 32;
+                int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+                for (std::vector<size_t>::const_iterator vit = vIndices.begin(), vend = vIndices.end(); vit != vend; vit++) {
+                    const size_t idx = *vit;
+                    if (kp_obs[idx + Nleft] > 0) continue;
+                    const int dist = descriptor_distance(MPdescriptor, R.desc + idx * 32);
+                    if (dist < bestDist) {
+                        bestDist2 = bestDist;
+                        bestDist = dist;
+                        bestLevel2 = bestLevel;
+                        bestLevel = R.keys[idx].octave;
+                        bestIdx = idx;
+                    } else if (dist < bestDist2) {
+                        bestLevel2 = R.keys[idx].octave;
+                        bestDist2 = dist;
+                    }
+                }
+                if (bestDist <= TH_HIGH) {
+                    if (bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2) continue;
+                    if (R.right_to_left && R.right_to_left[bestIdx] != -1) {
+                        kp_match[R.right_to_left[bestIdx]] = iMP;
+                        kp_obs[R.right_to_left[bestIdx]] = pMP.observations;
+                        nmatches++;
+                        left++;
+                    }
+                    kp_match[bestIdx + Nleft] = iMP;
+                    kp_obs[bestIdx + Nleft] = pMP.observations;
+                    nmatches++;
+                    right++;
+                }
+            }
+        }
+    }
+    (void)left; (void)right;
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:1965-2181 with CurrentFrame.Nleft != -1.  uv_right[2i..2i+1] = project(mTrl * x3Dc).
+int orbo_search_by_projection_frames_stereo(const FrameView* Cp, const FrameRight* Rp, const LastObs* last,
+                                            const float* uv_right, const uint8_t* last_desc, int n_last, float th,
+                                            int bForward, int bBackward, int mbCheckOrientation, int32_t* kp_obs,
+                                            int32_t* kp_match) {
+    const FrameView& CurrentFrame = *Cp;
+    const FrameRight& R = *Rp;
+    const FrameView FR = right_half(CurrentFrame, R);
+    GridO G(CurrentFrame), GR(FR);
+    const int Nleft = CurrentFrame.n;
+    for (int i = 0; i < Nleft + R.n; ++i) kp_match[i] = -1;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) rotHist[i].reserve(500);
+    const float factor = 1.0f / HISTO_LENGTH;
+    for (int i = 0; i < n_last; i++) {
+        const LastObs& o = last[i];
+        if (!o.valid) continue;
+        const float invzc = o.inv_z;
+        if (invzc < 0) continue;
+        if (o.u < CurrentFrame.min_x || o.u > CurrentFrame.max_x) continue;
+        if (o.v < CurrentFrame.min_y || o.v > CurrentFrame.max_y) continue;
+        int nLastOctave = o.octave;
+        float radius = th * CurrentFrame.scale_factors[nLastOctave];
+        std::vector<size_t> vIndices2;
+        if (bForward) vIndices2 = get_features_in_area(CurrentFrame, G, o.u, o.v, radius, nLastOctave);
+        else if (bBackward) vIndices2 = get_features_in_area(CurrentFrame, G, o.u, o.v, radius, 0, nLastOctave);
+        else vIndices2 = get_features_in_area(CurrentFrame, G, o.u, o.v, radius, nLastOctave - 1, nLastOctave + 1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* dMP = last_desc + (size_t)i * 32;
+        {
+            int bestDist = 256, bestIdx2 = -1;
+            for (std::vector<size_t>::const_iterator vit = vIndices2.begin(), vend = vIndices2.end(); vit != vend; vit++) {
+                const size_t i2 = *vit;
+                if (kp_obs[i2] > 0) continue;
+                const int dist = descriptor_distance(dMP, CurrentFrame.desc + i2 * 32);
+                if (dist < bestDist) {
+                    bestDist = dist;
+                    bestIdx2 = i2;
+                }
+            }
+            if (bestDist <= TH_HIGH) {
+                kp_match[bestIdx2] = i;
+                kp_obs[bestIdx2] = o.observations;
+                nmatches++;
+                if (mbCheckOrientation) {
+                    float rot = o.angle - CurrentFrame.keys[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(bestIdx2);
+                }
+            }
+        }
+        {
+            const float ux = uv_right[2 * i], uy = uv_right[2 * i + 1];
+            std::vector<size_t> vR;
+            if (bForward) vR = get_features_in_area(FR, GR, ux, uy, radius, nLastOctave, -1);
+            else if (bBackward) vR = get_features_in_area(FR, GR, ux, uy, radius, 0, nLastOctave);
+            else vR = get_features_in_area(FR, GR, ux, uy, radius, nLastOctave - 1, nLastOctave + 1);
+            int bestDist = 256, bestIdx2 = -1;
+            for (std::vector<size_t>::const_iterator vit = vR.begin(), vend = vR.end(); vit != vend; vit++) {
+                const size_t i2 = *vit;
+                if (kp_obs[i2 + Nleft] > 0) continue;
+                const int dist = descriptor_distance(dMP, R.desc + i2 * 32);
+                if (dist < bestDist) {
+                    bestDist = dist;
+                    bestIdx2 = i2;
+                }
+            }
+            if (bestDist <= TH_HIGH) {
+                kp_match[bestIdx2 + Nleft] = i;
+                kp_obs[bestIdx2 + Nleft] = o.observations;
+                nmatches++;
+                if (mbCheckOrientation) {
+                    float rot = o.angle - R.keys[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(bestIdx2 + Nleft);
+                }
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i != ind1 && i != ind2 && i != ind3) {
+                for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                    kp_match[rotHist[i][j]] = -1;
+                    kp_obs[rotHist[i][j]] = -1;
+                    nmatches--;
+                }
+            }
+        }
+    }
+    return nmatches;
 }
 
 }  // extern "C"

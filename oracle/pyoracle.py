@@ -202,6 +202,30 @@ class MatchOracle:
             C.c_void_p(match.ctypes.data))
         return n, match, obs
 
+    def search_by_projection_points_stereo(self, F, R, mps, mps_r, mp_desc, th, far, th_far, nnratio, kp_obs=None):
+        n_all = F.N + R.N
+        obs = np.full(n_all, -1, np.int32) if kp_obs is None else np.ascontiguousarray(kp_obs, np.int32).copy()
+        match = np.zeros(n_all, np.int32)
+        v, r = F.view(), R.view()
+        n = self.lib.orbo_search_by_projection_points_stereo(
+            C.byref(v), C.byref(r), C.c_void_p(mps.ctypes.data), C.c_void_p(mps_r.ctypes.data),
+            C.c_void_p(mp_desc.ctypes.data), len(mps), C.c_float(th), int(far), C.c_float(th_far), C.c_float(nnratio),
+            C.c_void_p(obs.ctypes.data), C.c_void_p(match.ctypes.data))
+        return n, match, obs
+
+    def search_by_projection_frames_stereo(self, cur, R, last_obs, uv_right, last_desc, th, fwd, bwd, check_ori,
+                                           kp_obs=None):
+        n_all = cur.N + R.N
+        obs = np.full(n_all, -1, np.int32) if kp_obs is None else np.ascontiguousarray(kp_obs, np.int32).copy()
+        match = np.zeros(n_all, np.int32)
+        uvr = np.ascontiguousarray(uv_right, np.float32)
+        v, r = cur.view(), R.view()
+        n = self.lib.orbo_search_by_projection_frames_stereo(
+            C.byref(v), C.byref(r), C.c_void_p(last_obs.ctypes.data), C.c_void_p(uvr.ctypes.data),
+            C.c_void_p(last_desc.ctypes.data), len(last_obs), C.c_float(th), int(fwd), int(bwd), int(check_ori),
+            C.c_void_p(obs.ctypes.data), C.c_void_p(match.ctypes.data))
+        return n, match, obs
+
     def search_for_initialization(self, F1, F2, prev, window, nnratio, check_ori):
         prev = np.ascontiguousarray(prev, np.float32).reshape(-1, 2).copy()
         m12 = np.zeros(F1.N, np.int32)

@@ -18,12 +18,22 @@ MAP_POINT_DTYPE = np.dtype([("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_xr", "<
                             ("in_view", "u1"), ("bad", "u1"), ("_pad", "u1", (2,))])
 LAST_OBS_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("inv_z", "<f4"), ("angle", "<f4"),
                            ("octave", "<i4"), ("observations", "<i4"), ("valid", "u1"), ("_pad", "u1", (3,))])
+_fv = C.POINTER(FrameView)
+
+
+class FrameRight(C.Structure):  # orbm_frame_right
+    _fields_ = [("keys", C.c_void_p), ("desc", C.c_void_p), ("n", C.c_int32),
+                ("left_to_right", C.c_void_p), ("right_to_left", C.c_void_p)]
+
+
+MAP_POINT_RIGHT_DTYPE = np.dtype([("proj_x", "<f4"), ("proj_y", "<f4"), ("view_cos", "<f4"), ("level", "<i4"),
+                                  ("in_view", "u1"), ("_pad", "u1", (3,))])  # orbm_map_point_right
+assert MAP_POINT_RIGHT_DTYPE.itemsize == 20
 AREA_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"),
                              ("valid", "<i4"), ("desc_row", "<i4")])  # orbm_area_query
 assert MAP_POINT_DTYPE.itemsize == 32 and LAST_OBS_DTYPE.itemsize == 28 and AREA_QUERY_DTYPE.itemsize == 28
 
 _vp, _i, _f = C.c_void_p, C.c_int, C.c_float
-_fv = C.POINTER(FrameView)
 ORBM_SYMBOLS = {
     "orbm_create": (_i, [_i, C.POINTER(_vp)]),
     "orbm_destroy": (_i, [_vp]),
@@ -33,6 +43,10 @@ ORBM_SYMBOLS = {
     "orbm_compute_stereo_matches": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _f, _f, _vp, _vp]),
     "orbm_search_by_projection_points": (_i, [_vp, _fv, _vp, _vp, _i, _f, _i, _f, _f, _vp, _vp]),
     "orbm_search_by_projection_frames": (_i, [_vp, _fv, _vp, _vp, _i, _f, _i, _i, _f, _i, _vp, _vp]),
+    "orbm_search_by_projection_points_stereo": (_i, [_vp, _fv, C.POINTER(FrameRight), _vp, _vp, _vp, _i, _f, _i, _f, _f,
+                                                     _vp, _vp]),
+    "orbm_search_by_projection_frames_stereo": (_i, [_vp, _fv, C.POINTER(FrameRight), _vp, _vp, _vp, _i, _f, _i, _i, _i,
+                                                     _vp, _vp]),
     "orbm_search_for_initialization": (_i, [_vp, _fv, _fv, _vp, _vp, _i, _f, _i]),
     "orbm_area_candidates": (_i, [_vp, _fv, _vp, _i, _vp, _i, _vp, _vp, _vp, _i]),
     "orbm_last_device_ms": (_i, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_longlong)]),

@@ -638,6 +638,250 @@ int orbm_search_by_projection_frames(orbm_context* c, const orbm_frame_view* cur
     return nmatches;
 }
 
+namespace {
+
+// the right camera's half as a frame view over the same grid geometry (PosInGrid uses the frame's
+// bounds for both cameras, src/Frame.cc:377-408)
+orbm_frame_view right_view(const orbm_frame_view* F, const orbm_frame_right* R) {
+    orbm_frame_view v = *F;
+    v.keys = R->keys;
+    v.desc = R->desc;
+    v.n = R->n;
+    v.u_right = nullptr;
+    return v;
+}
+
+int check_right(const orbm_frame_right* R) {
+    if (!R || R->n < 0 || (R->n && (!R->keys || !R->desc))) return orbx_set_error(ORBX_E_BAD_ARG, "bad right-camera view");
+    return ORBX_OK;
+}
+
+struct Csr {
+    std::vector<int32_t> row_ptr, cand;
+    std::vector<uint16_t> dist;
+};
+
+void take_csr(orbm_context* c, Csr& o) {
+    o.row_ptr = c->h_rowptr;
+    o.cand = c->h_cand;
+    o.dist = c->hdist;
+}
+
+}  // namespace
+
+int orbm_search_by_projection_points_stereo(orbm_context* c, const orbm_frame_view* F, const orbm_frame_right* R,
+                                            const orbm_map_point* mps, const orbm_map_point_right* mps_r,
+                                            const uint8_t* mp_desc, int m, float th, int far_points, float th_far,
+                                            float nn_ratio, int32_t* kp_obs, int32_t* kp_match) {
+    int rc = check_view(F);
+    if (rc || (rc = check_right(R))) return rc;
+    if (!c || m < 0 || (m && (!mps || !mps_r || !mp_desc)) || !kp_obs || !kp_match)
+        return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    const int Nleft = F->n;
+    for (int i = 0; i < Nleft + R->n; ++i) kp_match[i] = -1;
+    const bool bFactor = th != 1.0;
+    // pass 1: the left and the right window of every map point (state independent)
+    std::vector<orbm_area_query> QL(m), QR(m);
+    for (int i = 0; i < m; ++i) {
+        const orbm_map_point& p = mps[i];
+        const orbm_map_point_right& pr = mps_r[i];
+        QL[i] = QR[i] = orbm_area_query{0.f, 0.f, 0.f, 0, 0, 0, i};
+        if (!p.in_view && !pr.in_view) continue;            // :57-58
+        if (far_points && p.depth > th_far) continue;
+        if (p.bad) continue;
+        if (p.in_view) {
+            if (p.level < 0 || p.level >= F->nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "map point %d: level out of range", i);
+            float r = ((double)p.view_cos > 0.998) ? 2.5f : 4.0f;
+            if (bFactor) r *= th;
+            QL[i] = orbm_area_query{p.proj_x, p.proj_y, r * F->scale_factors[p.level], p.level - 1, p.level, 1, i};
+        }
+        if (pr.in_view && pr.level != -1) {                  // :149-151
+            if (pr.level < 0 || pr.level >= F->nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "map point %d: right level out of range", i);
+            const float r = ((double)pr.view_cos > 0.998) ? 2.5f : 4.0f;   // not scaled by th (:152)
+            QR[i] = orbm_area_query{pr.proj_x, pr.proj_y, r * F->scale_factors[pr.level], pr.level - 1, pr.level, 1, i};
+        }
+    }
+    Csr L, Rr;
+    if ((rc = device_candidates(c, F, QL, mp_desc, m))) return rc;
+    take_csr(c, L);
+    const orbm_frame_view FR = right_view(F, R);
+    if ((rc = device_candidates(c, &FR, QR, mp_desc, m))) return rc;
+    take_csr(c, Rr);
+    c->last_pairs = (long long)L.cand.size() + (long long)Rr.cand.size();
+    // pass 2: the reference's accept loop in the original order
+    int nmatches = 0;
+    for (int i = 0; i < m; ++i) {
+        const orbm_map_point& p = mps[i];
+        if (L.row_ptr[i + 1] != L.row_ptr[i]) {              // mbTrackInView && !vIndices.empty()
+            int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+            for (int k = L.row_ptr[i]; k < L.row_ptr[i + 1]; ++k) {
+                const int idx = L.cand[k];
+                if (kp_obs[idx] > 0) continue;
+                const int dist = L.dist[k];
+                if (dist < bestDist) {
+                    bestDist2 = bestDist;
+                    bestDist = dist;
+                    bestLevel2 = bestLevel;
+                    bestLevel = F->keys[idx].octave;
+                    bestIdx = idx;
+                } else if (dist < bestDist2) {
+                    bestLevel2 = F->keys[idx].octave;
+                    bestDist2 = dist;
+                }
+            }
+            if (bestDist <= ORBM_TH_HIGH) {
+                if (bestLevel == bestLevel2 && bestDist > nn_ratio * bestDist2) continue;   // skips the right branch too (:125-126)
+                if (bestLevel != bestLevel2 || bestDist <= nn_ratio * bestDist2) {
+                    kp_match[bestIdx] = i;
+                    kp_obs[bestIdx] = p.observations;
+                    const int l2r = R->left_to_right ? R->left_to_right[bestIdx] : -1;
+                    if (l2r != -1) {                             // :131-135
+                        kp_match[l2r + Nleft] = i;
+                        kp_obs[l2r + Nleft] = p.observations;
+                        nmatches++;
+                    }
+                    nmatches++;
+                }
+            }
+        }
+        if (Rr.row_ptr[i + 1] == Rr.row_ptr[i]) continue;     // not in the right view, or vIndices.empty()
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int k = Rr.row_ptr[i]; k < Rr.row_ptr[i + 1]; ++k) {
+            const int idx = Rr.cand[k];
+            if (kp_obs[idx + Nleft] > 0) continue;
+            const int dist = Rr.dist[k];
+            if (dist < bestDist) {
+                bestDist2 = bestDist;
+                bestDist = dist;
+                bestLevel2 = bestLevel;
+                bestLevel = R->keys[idx].octave;
+                bestIdx = idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = R->keys[idx].octave;
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= ORBM_TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > nn_ratio * bestDist2) continue;
+            const int r2l = R->right_to_left ? R->right_to_left[bestIdx] : -1;
+            if (r2l != -1) {                                     // :201-205
+                kp_match[r2l] = i;
+                kp_obs[r2l] = p.observations;
+                nmatches++;
+            }
+            kp_match[bestIdx + Nleft] = i;
+            kp_obs[bestIdx + Nleft] = p.observations;
+            nmatches++;
+        }
+    }
+    return nmatches;
+}
+
+int orbm_search_by_projection_frames_stereo(orbm_context* c, const orbm_frame_view* cur, const orbm_frame_right* R,
+                                            const orbm_last_obs* last, const float* uv_right, const uint8_t* last_desc,
+                                            int n_last, float th, int forward, int backward, int check_orientation,
+                                            int32_t* kp_obs, int32_t* kp_match) {
+    int rc = check_view(cur);
+    if (rc || (rc = check_right(R))) return rc;
+    if (!c || n_last < 0 || (n_last && (!last || !last_desc || !uv_right)) || !kp_obs || !kp_match)
+        return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    const int Nleft = cur->n;
+    for (int i = 0; i < Nleft + R->n; ++i) kp_match[i] = -1;
+    std::vector<int> rotHist[ORBM_HISTO_LENGTH];
+    const float factor = 1.0f / ORBM_HISTO_LENGTH;
+    std::vector<orbm_area_query> QL(n_last), QR(n_last);
+    std::vector<char> live(n_last, 0);
+    for (int i = 0; i < n_last; ++i) {
+        const orbm_last_obs& o = last[i];
+        QL[i] = QR[i] = orbm_area_query{0.f, 0.f, 0.f, 0, 0, 0, i};
+        if (!o.valid) continue;
+        if (o.inv_z < 0) continue;
+        if (o.u < cur->min_x || o.u > cur->max_x) continue;
+        if (o.v < cur->min_y || o.v > cur->max_y) continue;
+        if (o.octave < 0 || o.octave >= cur->nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "observation %d: octave out of range", i);
+        const float radius = th * cur->scale_factors[o.octave];
+        const int mn = forward ? o.octave : backward ? 0 : o.octave - 1;
+        const int mx = forward ? -1 : backward ? o.octave : o.octave + 1;
+        QL[i] = orbm_area_query{o.u, o.v, radius, mn, mx, 1, i};
+        // the right window is searched whenever the left one is reached, wherever it lies (:2089-2107)
+        QR[i] = orbm_area_query{uv_right[2 * i], uv_right[2 * i + 1], radius, mn, mx, 1, i};
+        live[i] = 1;
+    }
+    Csr L, Rr;
+    if ((rc = device_candidates(c, cur, QL, last_desc, n_last))) return rc;
+    take_csr(c, L);
+    const orbm_frame_view FR = right_view(cur, R);
+    if ((rc = device_candidates(c, &FR, QR, last_desc, n_last))) return rc;
+    take_csr(c, Rr);
+    c->last_pairs = (long long)L.cand.size() + (long long)Rr.cand.size();
+    int nmatches = 0;
+    auto bin_of = [&](float rot, int* bin) {
+        if (rot < 0.0) rot += 360.0f;
+        int b = (int)roundf(rot * factor);
+        if (b == ORBM_HISTO_LENGTH) b = 0;
+        *bin = b;
+        return b >= 0 && b < ORBM_HISTO_LENGTH;
+    };
+    for (int i = 0; i < n_last; ++i) {
+        if (!live[i]) continue;
+        const orbm_last_obs& o = last[i];
+        // left camera: `if(vIndices2.empty()) continue;` skips the right camera as well (:2028-2029)
+        if (L.row_ptr[i + 1] == L.row_ptr[i]) continue;
+        {
+            int bestDist = 256, bestIdx2 = -1;
+            for (int k = L.row_ptr[i]; k < L.row_ptr[i + 1]; ++k) {
+                const int i2 = L.cand[k];
+                if (kp_obs[i2] > 0) continue;
+                const int dist = L.dist[k];
+                if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+            }
+            if (bestDist <= ORBM_TH_HIGH) {
+                kp_match[bestIdx2] = i;
+                kp_obs[bestIdx2] = o.observations;
+                nmatches++;
+                if (check_orientation) {
+                    int bin;
+                    if (!bin_of(o.angle - cur->keys[bestIdx2].angle, &bin)) return orbx_set_error(ORBX_E_BAD_ARG, "angle outside [0,360)");
+                    rotHist[bin].push_back(bestIdx2);
+                }
+            }
+        }
+        {
+            int bestDist = 256, bestIdx2 = -1;
+            for (int k = Rr.row_ptr[i]; k < Rr.row_ptr[i + 1]; ++k) {
+                const int i2 = Rr.cand[k];
+                if (kp_obs[i2 + Nleft] > 0) continue;
+                const int dist = Rr.dist[k];
+                if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+            }
+            if (bestDist <= ORBM_TH_HIGH) {
+                kp_match[bestIdx2 + Nleft] = i;
+                kp_obs[bestIdx2 + Nleft] = o.observations;
+                nmatches++;
+                if (check_orientation) {
+                    int bin;
+                    if (!bin_of(o.angle - R->keys[bestIdx2].angle, &bin)) return orbx_set_error(ORBX_E_BAD_ARG, "angle outside [0,360)");
+                    rotHist[bin].push_back(bestIdx2 + Nleft);
+                }
+            }
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, ORBM_HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+            if (i != ind1 && i != ind2 && i != ind3) {
+                for (size_t j = 0; j < rotHist[i].size(); j++) {
+                    kp_match[rotHist[i][j]] = -1;
+                    kp_obs[rotHist[i][j]] = -1;
+                    nmatches--;
+                }
+            }
+        }
+    }
+    return nmatches;
+}
+
 int orbm_search_for_initialization(orbm_context* c, const orbm_frame_view* F1, const orbm_frame_view* F2,
                                    float* prev_matched, int32_t* matches12, int window_size, float nn_ratio,
                                    int check_orientation) {

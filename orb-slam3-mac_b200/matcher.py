@@ -13,7 +13,8 @@ import numpy as np
 
 from . import _lib
 from ._lib import KP_DTYPE, check
-from ._lib_match import AREA_QUERY_DTYPE, FrameView, LAST_OBS_DTYPE, MAP_POINT_DTYPE  # noqa: F401
+from ._lib_match import (AREA_QUERY_DTYPE, FrameRight, FrameView, LAST_OBS_DTYPE, MAP_POINT_DTYPE,  # noqa: F401
+                         MAP_POINT_RIGHT_DTYPE)
 
 FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48
 
@@ -52,6 +53,26 @@ class Frame:
         if n < 0:
             check(n)
         return out[:n].copy()
+
+
+class RightHalf:
+    """The right camera's half of a fisheye stereo Frame (Nleft != -1): mvKeysRight, the descriptor rows
+    Nleft.., mvLeftToRightMatch, mvRightToLeftMatch."""
+
+    def __init__(self, keys, desc, left_to_right=None, right_to_left=None):
+        self.keys = np.ascontiguousarray(keys, KP_DTYPE)
+        self.desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        self.l2r = None if left_to_right is None else np.ascontiguousarray(left_to_right, np.int32)
+        self.r2l = None if right_to_left is None else np.ascontiguousarray(right_to_left, np.int32)
+
+    @property
+    def N(self):
+        return len(self.keys)
+
+    def view(self) -> FrameRight:
+        return FrameRight(self.keys.ctypes.data, self.desc.ctypes.data, len(self.keys),
+                          None if self.l2r is None else self.l2r.ctypes.data,
+                          None if self.r2l is None else self.r2l.ctypes.data)
 
 
 class ORBmatcher:
@@ -165,6 +186,41 @@ class ORBmatcher:
         n = self.lib.orbm_search_by_projection_frames(self.ctx, C.byref(v), lo.ctypes.data, last_desc.ctypes.data,
                                                       len(lo), th, int(bForward), int(bBackward), mbf,
                                                       int(self.mbCheckOrientation), obs.ctypes.data, match.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, match, obs
+
+    def SearchByProjectionStereo(self, F: Frame, R: RightHalf, map_points, map_points_right, mp_desc, th=1.0,
+                                 bFarPoints=False, thFarPoints=50.0, kp_obs=None):
+        """SearchByProjection(F, vpMapPoints, ...) on a fisheye stereo frame (src/ORBmatcher.cc:48-218 with
+        Nleft != -1).  Returns (nmatches, kp_match[Nleft+Nright], kp_obs[Nleft+Nright])."""
+        mps = np.ascontiguousarray(map_points, MAP_POINT_DTYPE)
+        mpr = np.ascontiguousarray(map_points_right, MAP_POINT_RIGHT_DTYPE)
+        mp_desc = np.ascontiguousarray(mp_desc, np.uint8).reshape(-1, 32)
+        n_all = F.N + R.N
+        obs = np.full(n_all, -1, np.int32) if kp_obs is None else np.ascontiguousarray(kp_obs, np.int32).copy()
+        match = np.zeros(n_all, np.int32)
+        v, r = F.view(), R.view()
+        n = self.lib.orbm_search_by_projection_points_stereo(
+            self.ctx, C.byref(v), C.byref(r), mps.ctypes.data, mpr.ctypes.data, mp_desc.ctypes.data, len(mps), th,
+            int(bFarPoints), thFarPoints, self.mfNNratio, obs.ctypes.data, match.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, match, obs
+
+    def SearchByProjectionFramesStereo(self, CurrentFrame: Frame, R: RightHalf, last_obs, uv_right, last_desc, th,
+                                       bForward=False, bBackward=False, kp_obs=None):
+        """SearchByProjection(CurrentFrame, LastFrame, th, bMono) with a fisheye stereo current frame."""
+        lo = np.ascontiguousarray(last_obs, LAST_OBS_DTYPE)
+        uvr = np.ascontiguousarray(uv_right, np.float32).reshape(-1, 2)
+        last_desc = np.ascontiguousarray(last_desc, np.uint8).reshape(-1, 32)
+        n_all = CurrentFrame.N + R.N
+        obs = np.full(n_all, -1, np.int32) if kp_obs is None else np.ascontiguousarray(kp_obs, np.int32).copy()
+        match = np.zeros(n_all, np.int32)
+        v, r = CurrentFrame.view(), R.view()
+        n = self.lib.orbm_search_by_projection_frames_stereo(
+            self.ctx, C.byref(v), C.byref(r), lo.ctypes.data, uvr.ctypes.data, last_desc.ctypes.data, len(lo), th,
+            int(bForward), int(bBackward), int(self.mbCheckOrientation), obs.ctypes.data, match.ctypes.data)
         if n < 0:
             check(n)
         return n, match, obs

@@ -279,3 +279,75 @@ def test_device_grid_candidates_match_oracle_order(matcher, mo):
     F0 = _frame(np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8), 752, 480)
     rp0, c0, _ = matcher.area_candidates(F0, q[:5], None, cap=16)
     assert not rp0.any() and len(c0) == 0
+
+
+def _fisheye_frame(extract, seed):
+    """A fisheye stereo frame (config C3): left/right extractions of a 512x512 pair and mutual
+    best-match tables standing in for mvLeftToRightMatch / mvRightToLeftMatch."""
+    from orb_slam3_mac_b200.matcher import RightHalf
+    imgL, imgR = S.fisheye_pair(512, seed)
+    _, kl, dl = extract(imgL, 1500, (0, 511))
+    _, kr, dr = extract(imgR, 1500, (0, 511))
+    rng = np.random.default_rng(seed)
+    n = min(len(kl), len(kr))
+    pairs = rng.permutation(n)[: n // 3]
+    l2r = np.full(len(kl), -1, np.int32)
+    r2l = np.full(len(kr), -1, np.int32)
+    tgt = rng.permutation(len(kr))[: len(pairs)]
+    l2r[pairs] = tgt
+    r2l[tgt] = pairs
+    return _frame(kl, dl, 512, 512), RightHalf(kr, dr, l2r, r2l), (kl, dl, kr, dr)
+
+
+@pytest.mark.parametrize("th,far,tables", [(1.0, False, True), (3.0, True, True), (1.0, False, False)])
+def test_search_by_projection_points_fisheye_stereo(matcher, mo, extract, th, far, tables):
+    """M2 with Frame::Nleft != -1 (src/ORBmatcher.cc:48-218): left branch mirrored through
+    mvLeftToRightMatch, right branch in mGridRight mirrored through mvRightToLeftMatch, one shared
+    mvpMapPoints state over Nleft + Nright."""
+    from orb_slam3_mac_b200._lib_match import MAP_POINT_RIGHT_DTYPE
+    from orb_slam3_mac_b200.matcher import RightHalf
+    F, R, (kl, dl, kr, dr) = _fisheye_frame(extract, 5)
+    if not tables:
+        R = RightHalf(kr, dr, None, None)
+    m = 6000
+    mps, md = S.map_points_from_frame(kl, dl, 512, 512, m, 11)
+    mr, mdr = S.map_points_from_frame(kr, dr, 512, 512, m, 12)
+    rng = np.random.default_rng(13)
+    # every other map point carries the right camera's descriptor, so that both branches find matches
+    use_r = rng.random(m) < 0.5
+    md = np.where(use_r[:, None], mdr, md)
+    mpr = np.zeros(m, MAP_POINT_RIGHT_DTYPE)
+    mpr["proj_x"], mpr["proj_y"], mpr["view_cos"] = mr["proj_x"], mr["proj_y"], mr["view_cos"]
+    mpr["level"] = np.where(rng.random(m) < 0.05, -1, mr["level"])
+    mpr["in_view"] = (rng.random(m) < 0.7).astype(np.uint8)
+    mps["in_view"] = (rng.random(m) < 0.7).astype(np.uint8)
+    obs0 = np.where(rng.random(F.N + R.N) < 0.2, rng.integers(0, 3, F.N + R.N), -1).astype(np.int32)
+    n, match, obs = matcher.SearchByProjectionStereo(F, R, mps, mpr, md, th, far, 30.0, kp_obs=obs0)
+    on, omatch, oobs = mo.search_by_projection_points_stereo(F, R, mps, mpr, md, th, far, 30.0, 0.8, kp_obs=obs0)
+    assert n == on and np.array_equal(match, omatch) and np.array_equal(obs, oobs)
+    assert (match[: F.N] >= 0).sum() > 100 and (match[F.N:] >= 0).sum() > 100
+
+
+@pytest.mark.parametrize("fwd,bwd,check", [(False, False, True), (True, False, True), (False, True, False)])
+def test_search_by_projection_frames_fisheye_stereo(mo, extract, fwd, bwd, check):
+    """M3 with CurrentFrame.Nleft != -1 (src/ORBmatcher.cc:1965-2181): the right camera is searched with
+    the projection of mTrl * x3Dc after the left one, rotation histogram over both halves."""
+    from orb_slam3_mac_b200.matcher import ORBmatcher
+    F, R, (kl, dl, kr, dr) = _fisheye_frame(extract, 6)
+    lo, ld = S.last_frame_obs(kl, dl, 21)
+    rng = np.random.default_rng(22)
+    # right-camera projections: near a right keypoint for half of the observations, anywhere otherwise
+    j = rng.integers(0, len(kr), len(lo))
+    uvr = np.stack([kr["x"][j] + rng.normal(0, 1.0, len(lo)), kr["y"][j] + rng.normal(0, 1.0, len(lo))], axis=1)
+    far = rng.random(len(lo)) < 0.5
+    uvr[far] = rng.uniform(-50, 560, (int(far.sum()), 2))
+    uvr = uvr.astype(np.float32)
+    ld = np.where((rng.random(len(lo)) < 0.4)[:, None], S.flip_bits(dr[j], 0.03, rng), ld)
+    lo["octave"] = np.where(far, lo["octave"], kr["octave"][j])
+    obs0 = np.where(rng.random(F.N + R.N) < 0.15, rng.integers(0, 3, F.N + R.N), -1).astype(np.int32)
+    m = ORBmatcher(0.9, check)
+    n, match, obs = m.SearchByProjectionFramesStereo(F, R, lo, uvr, ld, 7.0, fwd, bwd, kp_obs=obs0)
+    on, omatch, oobs = mo.search_by_projection_frames_stereo(F, R, lo, uvr, ld, 7.0, fwd, bwd, check, kp_obs=obs0)
+    m.close()
+    assert n == on and np.array_equal(match, omatch) and np.array_equal(obs, oobs)
+    assert (match[: F.N] >= 0).sum() > 100 and (match[F.N:] >= 0).sum() > 5
