@@ -182,6 +182,28 @@ int orbm_search_by_projection_frames_stereo(orbm_context* c, const orbm_frame_vi
                                             int backward, int check_orientation, int32_t* kp_obs,
                                             int32_t* kp_match);
 
+/* ---- SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches), src/ORBmatcher.cc:273-475 --
+ * Called on the tracking thread (src/Tracking.cc:1760, 2665).  One side of the search: descriptors,
+ * keypoints (only .angle is read) and the DBoW2::FeatureVector (node id -> feature indices) as CSR.
+ * Fisheye rigs pass the concatenation left ++ right, as mDescriptors is laid out. */
+typedef struct orbm_bow_view {
+    const orbx_keypoint* keys; /* n records */
+    const uint8_t* desc;       /* n x 32 */
+    int32_t n;
+    int32_t nnodes;
+    const uint32_t* node_ids;   /* FeatureVector keys, strictly ascending (nnodes) */
+    const int32_t* node_ptr;    /* nnodes + 1 offsets into node_items */
+    const uint32_t* node_items; /* feature indices of each node in the FeatureVector's order */
+} orbm_bow_view;
+
+/* kf_mp_ok[i] != 0: keyframe feature i has a map point that is not bad (:302-308).  f_nleft: F.Nleft
+ * (-1 for mono / rectified stereo).  matches (out, F.n ints): index of the keyframe feature whose map
+ * point was attached to frame feature j, else -1.  Returns nmatches.  The distances of all
+ * (keyframe feature, frame feature) pairs that share a vocabulary node are computed on the device in
+ * one launch; the accept loop, which depends on earlier acceptances (:323-324), runs on the host. */
+int orbm_search_by_bow(orbm_context* c, const orbm_bow_view* KF, const uint8_t* kf_mp_ok, const orbm_bow_view* F,
+                       int f_nleft, float nn_ratio, int check_orientation, int32_t* matches);
+
 /* SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), src/ORBmatcher.cc:710-825.
  * prev_matched: F1.n (x, y) pairs, in/out.  matches12: F1.n ints, out.  Returns nmatches. */
 int orbm_search_for_initialization(orbm_context* c, const orbm_frame_view* F1,

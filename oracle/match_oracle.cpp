@@ -24,6 +24,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <map>
 #include <vector>
 #include <algorithm>
 
@@ -66,6 +67,15 @@ struct MapPointRightPod {  // orbm_map_point_right
     float proj_x, proj_y, view_cos;
     int32_t level;
     uint8_t in_view, pad[3];
+};
+
+struct BowView {  // orbm_bow_view
+    const Kp* keys;
+    const uint8_t* desc;
+    int32_t n, nnodes;
+    const uint32_t* node_ids;
+    const int32_t* node_ptr;
+    const uint32_t* node_items;
 };
 
 struct LastObs {  // orbm_last_obs
@@ -758,6 +768,114 @@ int orbo_search_by_projection_frames_stereo(const FrameView* Cp, const FrameRigh
                     kp_obs[rotHist[i][j]] = -1;
                     nmatches--;
                 }
+            }
+        }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:273-475.  DBoW2::FeatureVector = std::map<NodeId, std::vector<unsigned int>>; the
+// snapshot carries its (key, vector) pairs in key order, rebuilt here into the same std::map so that
+// the iterator walk and the lower_bound calls are the reference's own.
+int orbo_search_by_bow(const BowView* KFp, const uint8_t* kf_mp_ok, const BowView* Fp, int Nleft, float mfNNratio,
+                       int mbCheckOrientation, int32_t* matches) {
+    const BowView& KF = *KFp;
+    const BowView& F = *Fp;
+    typedef std::map<unsigned int, std::vector<unsigned int> > FeatureVector;
+    FeatureVector vFeatVecKF, vFeatVecF;
+    for (int a = 0; a < KF.nnodes; ++a)
+        vFeatVecKF[KF.node_ids[a]] = std::vector<unsigned int>(KF.node_items + KF.node_ptr[a], KF.node_items + KF.node_ptr[a + 1]);
+    for (int b = 0; b < F.nnodes; ++b)
+        vFeatVecF[F.node_ids[b]] = std::vector<unsigned int>(F.node_items + F.node_ptr[b], F.node_items + F.node_ptr[b + 1]);
+    for (int i = 0; i < F.n; ++i) matches[i] = -1;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) rotHist[i].reserve(500);
+    const float factor = 1.0f / HISTO_LENGTH;
+    FeatureVector::const_iterator KFit = vFeatVecKF.begin(), Fit = vFeatVecF.begin();
+    FeatureVector::const_iterator KFend = vFeatVecKF.end(), Fend = vFeatVecF.end();
+    while (KFit != KFend && Fit != Fend) {
+        if (KFit->first == Fit->first) {
+            const std::vector<unsigned int> vIndicesKF = KFit->second;
+            const std::vector<unsigned int> vIndicesF = Fit->second;
+            for (size_t iKF = 0; iKF < vIndicesKF.size(); iKF++) {
+                const unsigned int realIdxKF = vIndicesKF[iKF];
+                if (!kf_mp_ok[realIdxKF]) continue;   // !pMP || pMP->isBad()
+                const uint8_t* dKF = KF.desc + (size_t)realIdxKF * 32;
+                int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+                int bestDist1R = 256, bestIdxFR = -1, bestDist2R = 256;
+                for (size_t iF = 0; iF < vIndicesF.size(); iF++) {
+                    const unsigned int realIdxF = vIndicesF[iF];
+                    if (matches[realIdxF] >= 0) continue;
+                    const int dist = descriptor_distance(dKF, F.desc + (size_t)realIdxF * 32);
+                    if (Nleft == -1) {
+                        if (dist < bestDist1) {
+                            bestDist2 = bestDist1;
+                            bestDist1 = dist;
+                            bestIdxF = realIdxF;
+                        } else if (dist < bestDist2) {
+                            bestDist2 = dist;
+                        }
+                    } else {
+                        if ((int)realIdxF < Nleft && dist < bestDist1) {
+                            bestDist2 = bestDist1;
+                            bestDist1 = dist;
+                            bestIdxF = realIdxF;
+                        } else if ((int)realIdxF < Nleft && dist < bestDist2) {
+                            bestDist2 = dist;
+                        }
+                        if ((int)realIdxF >= Nleft && dist < bestDist1R) {
+                            bestDist2R = bestDist1R;
+                            bestDist1R = dist;
+                            bestIdxFR = realIdxF;
+                        } else if ((int)realIdxF >= Nleft && dist < bestDist2R) {
+                            bestDist2R = dist;
+                        }
+                    }
+                }
+                if (bestDist1 <= TH_LOW) {
+                    if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                        matches[bestIdxF] = realIdxKF;
+                        if (mbCheckOrientation) {
+                            float rot = KF.keys[realIdxKF].angle - F.keys[bestIdxF].angle;
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back(bestIdxF);
+                        }
+                        nmatches++;
+                    }
+                    if (bestDist1R <= TH_LOW) {
+                        if (static_cast<float>(bestDist1R) < mfNNratio * static_cast<float>(bestDist2R) || true) {
+                            matches[bestIdxFR] = realIdxKF;
+                            if (mbCheckOrientation) {
+                                float rot = KF.keys[realIdxKF].angle - F.keys[bestIdxFR].angle;
+                                if (rot < 0.0) rot += 360.0f;
+                                int bin = round(rot * factor);
+                                if (bin == HISTO_LENGTH) bin = 0;
+                                rotHist[bin].push_back(bestIdxFR);
+                            }
+                            nmatches++;
+                        }
+                    }
+                }
+            }
+            KFit++;
+            Fit++;
+        } else if (KFit->first < Fit->first) {
+            KFit = vFeatVecKF.lower_bound(Fit->first);
+        } else {
+            Fit = vFeatVecF.lower_bound(KFit->first);
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+                matches[rotHist[i][j]] = -1;
+                nmatches--;
             }
         }
     }

@@ -226,6 +226,14 @@ class MatchOracle:
             C.c_void_p(obs.ctypes.data), C.c_void_p(match.ctypes.data))
         return n, match, obs
 
+    def search_by_bow(self, KF, kf_mp_ok, F, nleft, nnratio, check_ori):
+        ok = np.ascontiguousarray(kf_mp_ok, np.uint8)
+        matches = np.zeros(len(F.keys), np.int32)
+        kv, fv = KF.view(), F.view()
+        n = self.lib.orbo_search_by_bow(C.byref(kv), C.c_void_p(ok.ctypes.data), C.byref(fv), int(nleft),
+                                        C.c_float(nnratio), int(check_ori), C.c_void_p(matches.ctypes.data))
+        return n, matches
+
     def search_for_initialization(self, F1, F2, prev, window, nnratio, check_ori):
         prev = np.ascontiguousarray(prev, np.float32).reshape(-1, 2).copy()
         m12 = np.zeros(F1.N, np.int32)

@@ -21,6 +21,11 @@ LAST_OBS_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("inv_z", "<f4"), ("angle
 _fv = C.POINTER(FrameView)
 
 
+class BowView(C.Structure):  # orbm_bow_view
+    _fields_ = [("keys", C.c_void_p), ("desc", C.c_void_p), ("n", C.c_int32), ("nnodes", C.c_int32),
+                ("node_ids", C.c_void_p), ("node_ptr", C.c_void_p), ("node_items", C.c_void_p)]
+
+
 class FrameRight(C.Structure):  # orbm_frame_right
     _fields_ = [("keys", C.c_void_p), ("desc", C.c_void_p), ("n", C.c_int32),
                 ("left_to_right", C.c_void_p), ("right_to_left", C.c_void_p)]
@@ -47,6 +52,7 @@ ORBM_SYMBOLS = {
                                                      _vp, _vp]),
     "orbm_search_by_projection_frames_stereo": (_i, [_vp, _fv, C.POINTER(FrameRight), _vp, _vp, _vp, _i, _f, _i, _i, _i,
                                                      _vp, _vp]),
+    "orbm_search_by_bow": (_i, [_vp, C.POINTER(BowView), _vp, C.POINTER(BowView), _i, _f, _i, _vp]),
     "orbm_search_for_initialization": (_i, [_vp, _fv, _fv, _vp, _vp, _i, _f, _i]),
     "orbm_area_candidates": (_i, [_vp, _fv, _vp, _i, _vp, _i, _vp, _vp, _vp, _i]),
     "orbm_last_device_ms": (_i, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_longlong)]),

@@ -882,6 +882,115 @@ int orbm_search_by_projection_frames_stereo(orbm_context* c, const orbm_frame_vi
     return nmatches;
 }
 
+int orbm_search_by_bow(orbm_context* c, const orbm_bow_view* KF, const uint8_t* kf_mp_ok, const orbm_bow_view* F,
+                       int f_nleft, float nn_ratio, int check_orientation, int32_t* matches) {
+    if (!c || !KF || !F || !matches || KF->n < 0 || F->n < 0 || KF->nnodes < 0 || F->nnodes < 0 ||
+        (KF->n && (!KF->keys || !KF->desc || !kf_mp_ok)) || (F->n && (!F->keys || !F->desc)) ||
+        (KF->nnodes && (!KF->node_ids || !KF->node_ptr || !KF->node_items)) ||
+        (F->nnodes && (!F->node_ids || !F->node_ptr || !F->node_items)))
+        return orbx_set_error(ORBX_E_BAD_ARG, "bad argument");
+    for (int i = 0; i < F->n; ++i) matches[i] = -1;
+    // pass 1: walk the two sorted feature vectors like the reference (:291-449; lower_bound on a
+    // sorted key array) and list every (keyframe feature, frame feature) pair that shares a node
+    struct NodePair { int a, b; };
+    std::vector<NodePair> shared;
+    {
+        int a = 0, b = 0;
+        while (a < KF->nnodes && b < F->nnodes) {
+            if (KF->node_ids[a] == F->node_ids[b]) {
+                shared.push_back(NodePair{a, b});
+                ++a;
+                ++b;
+            } else if (KF->node_ids[a] < F->node_ids[b]) {
+                a = (int)(std::lower_bound(KF->node_ids, KF->node_ids + KF->nnodes, F->node_ids[b]) - KF->node_ids);
+            } else {
+                b = (int)(std::lower_bound(F->node_ids, F->node_ids + F->nnodes, KF->node_ids[a]) - F->node_ids);
+            }
+        }
+    }
+    std::vector<int32_t> row_ptr, cand, row_q;   // one row per (node, valid keyframe feature)
+    row_ptr.push_back(0);
+    for (const NodePair& np : shared) {
+        for (int ia = KF->node_ptr[np.a]; ia < KF->node_ptr[np.a + 1]; ++ia) {
+            const uint32_t realIdxKF = KF->node_items[ia];
+            if (realIdxKF >= (uint32_t)KF->n) return orbx_set_error(ORBX_E_BAD_ARG, "keyframe feature index out of range");
+            if (!kf_mp_ok[realIdxKF]) continue;
+            for (int ib = F->node_ptr[np.b]; ib < F->node_ptr[np.b + 1]; ++ib) {
+                if (F->node_items[ib] >= (uint32_t)F->n) return orbx_set_error(ORBX_E_BAD_ARG, "frame feature index out of range");
+                cand.push_back((int32_t)F->node_items[ib]);
+            }
+            row_q.push_back((int32_t)realIdxKF);
+            row_ptr.push_back((int32_t)cand.size());
+        }
+    }
+    // the CSR kernel takes one query descriptor per row: gather the rows' keyframe descriptors
+    const int nrows = (int)row_q.size();
+    std::vector<uint8_t> qdesc((size_t)nrows * 32);
+    for (int r = 0; r < nrows; ++r) memcpy(&qdesc[(size_t)r * 32], KF->desc + (size_t)row_q[r] * 32, 32);
+    c->hdist.assign(cand.size(), 0);
+    int rc;
+    if (!cand.empty() && (rc = orbm_hamming_csr(c, qdesc.data(), nrows, F->desc, F->n, row_ptr.data(), cand.data(),
+                                                (int)cand.size(), c->hdist.data())))
+        return rc;
+    c->last_pairs = (long long)cand.size();
+    // pass 2: the reference's accept loop over the precomputed distances
+    std::vector<int> rotHist[ORBM_HISTO_LENGTH];
+    const float factor = 1.0f / ORBM_HISTO_LENGTH;
+    int nmatches = 0;
+    auto push_rot = [&](int idxKF, int idxF) {
+        float rot = KF->keys[idxKF].angle - F->keys[idxF].angle;
+        if (rot < 0.0) rot += 360.0f;
+        int bin = (int)roundf(rot * factor);
+        if (bin == ORBM_HISTO_LENGTH) bin = 0;
+        if (bin < 0 || bin >= ORBM_HISTO_LENGTH) return false;
+        rotHist[bin].push_back(idxF);
+        return true;
+    };
+    for (int r = 0; r < nrows; ++r) {
+        const int realIdxKF = row_q[r];
+        int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+        int bestDist1R = 256, bestIdxFR = -1, bestDist2R = 256;
+        for (int k = row_ptr[r]; k < row_ptr[r + 1]; ++k) {
+            const int realIdxF = cand[k];
+            if (matches[realIdxF] >= 0) continue;
+            const int dist = c->hdist[k];
+            if (f_nleft == -1) {
+                if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+                else if (dist < bestDist2) bestDist2 = dist;
+            } else {
+                if (realIdxF < f_nleft && dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+                else if (realIdxF < f_nleft && dist < bestDist2) bestDist2 = dist;
+                if (realIdxF >= f_nleft && dist < bestDist1R) { bestDist2R = bestDist1R; bestDist1R = dist; bestIdxFR = realIdxF; }
+                else if (realIdxF >= f_nleft && dist < bestDist2R) bestDist2R = dist;
+            }
+        }
+        if (bestDist1 <= ORBM_TH_LOW) {
+            if ((float)bestDist1 < nn_ratio * (float)bestDist2) {
+                matches[bestIdxF] = realIdxKF;
+                if (check_orientation && !push_rot(realIdxKF, bestIdxF)) return orbx_set_error(ORBX_E_BAD_ARG, "angle outside [0,360)");
+                nmatches++;
+            }
+            if (bestDist1R <= ORBM_TH_LOW) {   // the ratio test is disabled in the reference ("|| true", :396)
+                matches[bestIdxFR] = realIdxKF;
+                if (check_orientation && !push_rot(realIdxKF, bestIdxFR)) return orbx_set_error(ORBX_E_BAD_ARG, "angle outside [0,360)");
+                nmatches++;
+            }
+        }
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, ORBM_HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {
+                matches[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
 int orbm_search_for_initialization(orbm_context* c, const orbm_frame_view* F1, const orbm_frame_view* F2,
                                    float* prev_matched, int32_t* matches12, int window_size, float nn_ratio,
                                    int check_orientation) {

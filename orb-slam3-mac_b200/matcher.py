@@ -13,7 +13,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import KP_DTYPE, check
-from ._lib_match import (AREA_QUERY_DTYPE, FrameRight, FrameView, LAST_OBS_DTYPE, MAP_POINT_DTYPE,  # noqa: F401
+from ._lib_match import (AREA_QUERY_DTYPE, BowView, FrameRight, FrameView, LAST_OBS_DTYPE, MAP_POINT_DTYPE,  # noqa: F401
                          MAP_POINT_RIGHT_DTYPE)
 
 FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48
@@ -53,6 +53,27 @@ class Frame:
         if n < 0:
             check(n)
         return out[:n].copy()
+
+
+class BowSide:
+    """One side of SearchByBoW: keypoints, descriptors and the DBoW2::FeatureVector as
+    {node id: [feature indices]} (fisheye rigs: left ++ right, as mDescriptors is laid out)."""
+
+    def __init__(self, keys, desc, feat_vec: dict):
+        self.keys = np.ascontiguousarray(keys, KP_DTYPE)
+        self.desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        ids = sorted(feat_vec)
+        self.node_ids = np.array(ids, np.uint32)
+        self.node_ptr = np.zeros(len(ids) + 1, np.int32)
+        items = []
+        for k, nid in enumerate(ids):
+            items.extend(int(v) for v in feat_vec[nid])
+            self.node_ptr[k + 1] = len(items)
+        self.node_items = np.array(items, np.uint32)
+
+    def view(self) -> BowView:
+        return BowView(self.keys.ctypes.data, self.desc.ctypes.data, len(self.keys), len(self.node_ids),
+                       self.node_ids.ctypes.data, self.node_ptr.ctypes.data, self.node_items.ctypes.data)
 
 
 class RightHalf:
@@ -224,6 +245,18 @@ class ORBmatcher:
         if n < 0:
             check(n)
         return n, match, obs
+
+    def SearchByBoW(self, KF: BowSide, kf_mp_ok, F: BowSide, Nleft: int = -1):
+        """SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches), src/ORBmatcher.cc:273-475.
+        Returns (nmatches, matches[F.N] = keyframe feature index or -1)."""
+        ok = np.ascontiguousarray(kf_mp_ok, np.uint8)
+        matches = np.zeros(len(F.keys), np.int32)
+        kv, fv = KF.view(), F.view()
+        n = self.lib.orbm_search_by_bow(self.ctx, C.byref(kv), ok.ctypes.data, C.byref(fv), int(Nleft), self.mfNNratio,
+                                        int(self.mbCheckOrientation), matches.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, matches
 
     def SearchForInitialization(self, F1: Frame, F2: Frame, vbPrevMatched, windowSize=10):
         """Returns (nmatches, vnMatches12[N1], updated vbPrevMatched[N1,2])."""

@@ -351,3 +351,39 @@ def test_search_by_projection_frames_fisheye_stereo(mo, extract, fwd, bwd, check
     m.close()
     assert n == on and np.array_equal(match, omatch) and np.array_equal(obs, oobs)
     assert (match[: F.N] >= 0).sum() > 100 and (match[F.N:] >= 0).sum() > 5
+
+
+def _feat_vec(keys, desc, rng, nnodes=120, drop=0.0):
+    """A stand-in for DBoW2's FeatureVector: node = coarse image cell of the keypoint (matching
+    features of two nearby frames mostly share a node), a few features moved to random nodes."""
+    node = (np.floor(keys["x"] / 64).astype(np.int64) * 16 + np.floor(keys["y"] / 64).astype(np.int64)) % nnodes
+    stray = rng.random(len(keys)) < 0.1
+    node[stray] = rng.integers(0, nnodes + 40, int(stray.sum()))
+    fv = {}
+    for i in rng.permutation(len(keys)):
+        if rng.random() < drop:
+            continue
+        fv.setdefault(int(node[i]) * 7 + 3, []).append(int(i))
+    return fv
+
+
+@pytest.mark.parametrize("check,nleft", [(True, -1), (False, -1), (True, 1)])
+def test_search_by_bow_keyframe_frame(mo, extract, check, nleft):
+    """N3: SearchByBoW(KeyFrame*, Frame&) (src/ORBmatcher.cc:273-475), mono and fisheye (Nleft != -1)
+    forms, node lists that only partly overlap (exercises the lower_bound walk)."""
+    from orb_slam3_mac_b200.matcher import BowSide, ORBmatcher
+    img0 = S.textured_noise(480, 752, 17)
+    img1 = np.roll(img0, 3, axis=1)
+    _, k0, d0 = extract(img0, 1500, (0, 0))
+    _, k1, d1 = extract(img1, 1500, (0, 0))
+    rng = np.random.default_rng(5 + nleft)
+    KF = BowSide(k0, d0, _feat_vec(k0, d0, rng, drop=0.05))
+    F = BowSide(k1, d1, _feat_vec(k1, d1, rng, drop=0.05))
+    ok = (rng.random(len(k0)) < 0.7).astype(np.uint8)
+    nl = -1 if nleft < 0 else len(k1) // 2
+    m = ORBmatcher(0.7, check)
+    n, matches = m.SearchByBoW(KF, ok, F, nl)
+    on, omatches = mo.search_by_bow(KF, ok, F, nl, 0.7, check)
+    m.close()
+    assert n == on and np.array_equal(matches, omatches)
+    assert n > 150 and (matches >= 0).sum() == n
