@@ -142,6 +142,23 @@ def main():
            lambda: m.SearchByProjectionFrames(F, lo, ld, 15.0),
            (lambda: mo.search_by_projection_frames(F, lo, ld, 15.0, False, False, 0.0, True)) if mo else None)
 
+    # ---- N3: SearchByBoW(KeyFrame*, Frame&) on the tracking thread ------------------------------------------
+    from orb_slam3_mac_b200.matcher import BowSide
+
+    def feat_vec(keys, rng):   # stand-in for DBoW2's FeatureVector: ~100 nodes, node = coarse image cell
+        node = np.floor(keys["x"] / 128).astype(np.int64) * 10 + np.floor(keys["y"] / 72).astype(np.int64)
+        fv = {}
+        for i in rng.permutation(len(keys)):
+            fv.setdefault(int(node[i]), []).append(int(i))
+        return fv
+
+    rb = np.random.default_rng(3)
+    KFs, Fs = BowSide(k0, d0, feat_vec(k0, rb)), BowSide(k1, d1, feat_vec(k1, rb))
+    okf = np.ones(len(k0), np.uint8)
+    report("C4 SearchByBoW", f"{len(k0)} keyframe features vs {len(k1)} frame features over {len(KFs.node_ids)} vocabulary nodes",
+           lambda: m.SearchByBoW(KFs, okf, Fs, -1),
+           (lambda: mo.search_by_bow(KFs, okf, Fs, -1, 0.8, True)) if mo else None)
+
     # ---- N2 alone: candidate lists without distances ---------------------------------------------------
     q = np.zeros(len(mps), AREA_QUERY_DTYPE)
     q["x"], q["y"], q["r"] = mps["proj_x"], mps["proj_y"], 4.0 * SF[np.clip(mps["level"], 0, 7)]
