@@ -273,3 +273,43 @@ def test_input_stage_cvtcolor_and_rectification(oracle_libs, synth, fmt, bits, r
             ex.set_rectify_maps(mx[:100], my[:100])
             ex(base, (0, 1000))
     ex.close()
+
+
+class _DevArray:
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+@pytest.mark.parametrize("pad", [0, 4, 12])
+def test_device_resident_frames_any_pitch(oracle_libs, synth, pad):
+    """orbx_extract_device: frames already in HBM (the `value` path of bench.py), rows `w + pad` bytes
+    apart.  A pitch that is not a multiple of 16 takes the plain-load pyramid kernel for level 1
+    (k_resize_rows) instead of the cp.async one; results must not depend on it."""
+    import ctypes as C
+    import torch
+    from orb_slam3_mac_b200 import _lib
+    from orb_slam3_mac_b200._lib import KP_DTYPE
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    h, w, B = 480, 752, 5
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_size=(h, w), max_batch=B)
+    kinds = ["noise", "checker", "lowtex", "black", "noise"]
+    imgs = [synth.frame(kinds[i], h, w, 40 + i) for i in range(B)]
+    slab = np.zeros((B, h, w + pad), np.uint8)
+    for i in range(B):
+        slab[i, :, :w] = imgs[i]
+    d = torch.from_numpy(slab).cuda()
+    lap = np.tile(np.array([0, 1000], np.int32), (B, 1))
+    hdr, kps, desc = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    _lib.check(ex.lib.orbx_extract_device(ex.h, 0, d.data_ptr(), B, w, h, w + pad, h * (w + pad), lap.ctypes.data,
+                                          C.byref(hdr), C.byref(kps), C.byref(desc)))
+    _lib.check(ex.lib.orbx_wait(ex.h, 0))
+    cap = ex.max_keypoints()
+    H = torch.as_tensor(_DevArray(hdr.value, B * 16), device="cuda").cpu().numpy().view(np.int32).reshape(B, 4)
+    K = torch.as_tensor(_DevArray(kps.value, B * cap * 28), device="cuda").cpu().numpy().view(KP_DTYPE).reshape(B, cap)
+    D = torch.as_tensor(_DevArray(desc.value, B * cap * 32), device="cuda").cpu().numpy().reshape(B, cap, 32)
+    ora = _oracle(oracle_libs, 1000)
+    for i in range(B):
+        n = int(H[i, 0])
+        assert H[i, 2] == 0
+        _compare_final(ora(imgs[i], (0, 1000)), (int(H[i, 1]), K[i, :n], D[i, :n]), ("device", pad, i))
+    ex.close()
