@@ -387,3 +387,76 @@ def test_search_by_bow_keyframe_frame(mo, extract, check, nleft):
     m.close()
     assert n == on and np.array_equal(matches, omatches)
     assert n > 150 and (matches >= 0).sum() == n
+
+
+class _ProductBackend:
+    """The CUDA matcher behind the oracle's method names (tests/golden/match_cases.py)."""
+
+    def __init__(self):
+        from orb_slam3_mac_b200.matcher import ORBmatcher
+        self.M = ORBmatcher
+
+    def _m(self, ratio, check):
+        return self.M(ratio, check)
+
+    def search_by_projection_points(self, F, mps, md, th, far, th_far, ratio):
+        m = self._m(ratio, True)
+        r = m.SearchByProjection(F, mps, md, th, far, th_far)
+        m.close()
+        return r
+
+    def search_by_projection_frames(self, F, lo, ld, th, fwd, bwd, mbf, check):
+        m = self._m(0.8, check)
+        r = m.SearchByProjectionFrames(F, lo, ld, th, fwd, bwd, mbf)
+        m.close()
+        return r
+
+    def search_for_initialization(self, F0, F1, prev, win, ratio, check):
+        m = self._m(ratio, check)
+        r = m.SearchForInitialization(F0, F1, prev, win)
+        m.close()
+        return r
+
+    def search_by_bow(self, KF, ok, F, nleft, ratio, check):
+        m = self._m(ratio, check)
+        r = m.SearchByBoW(KF, ok, F, nleft)
+        m.close()
+        return r
+
+    def search_by_projection_points_stereo(self, F, R, mps, mpr, md, th, far, th_far, ratio):
+        m = self._m(ratio, True)
+        r = m.SearchByProjectionStereo(F, R, mps, mpr, md, th, far, th_far)
+        m.close()
+        return r
+
+    def knn2(self, q, t):
+        m = self._m(0.8, True)
+        r = m.knn2(q, t)
+        m.close()
+        return r
+
+
+def test_cuda_matcher_and_input_stage_against_committed_goldens():
+    """The CUDA path against tests/golden/match_golden.json -- needs no oracle library: matcher hashes
+    frozen from the CPU oracle, input-stage hashes recorded from the real OpenCV (cv2 4.13)."""
+    import json
+    import os
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    from tests.golden import match_cases as mc
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "match_golden.json")))
+    assert mc.run_matcher_cases(_ProductBackend()) == gold["matcher"]
+    bgr, mx, my = mc.input_stage_case()
+    g = gold["input_stage"]
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_size=(480, 752))
+    ex.set_input_format("bgr", 15)
+    ex.set_rectify_maps(mx, my)
+    ex(bgr, (0, 0))
+    assert mc.sha(ex.pyramid_level(0, (480, 752))) == g["bgr_rect_gray"]
+    ex.set_input_format("gray", 15)
+    ex(bgr[:, :, 1].copy(), (0, 0))
+    assert mc.sha(ex.pyramid_level(0, (480, 752))) == g["rect_gray_only"]
+    ex.set_rectify_maps(None, None)
+    ex.set_input_format("rgb", 15)
+    ex(bgr, (0, 0))
+    assert mc.sha(ex.pyramid_level(0, (480, 752))) == g["rgb_gray"]
+    ex.close()

@@ -92,3 +92,19 @@ def test_features_in_area_oracle_vs_bruteforce_and_product(mo):
         assert np.array_equal(F.GetFeaturesInArea(x, y, r, mn, mx), got), it  # product host code
         total += len(got)
     assert total > 5000
+
+
+def test_oracle_matches_committed_goldens(mo, oracle_libs):
+    """tests/golden/match_golden.json: the matcher oracle has not drifted from the restatement the CUDA
+    path was validated against, and the oracle's input-stage primitives reproduce what the REAL OpenCV
+    (cv2.remap + cv2.cvtColor, recorded by make_golden_match.py) produced."""
+    import json
+    import os
+    from tests.golden import match_cases as mc
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "match_golden.json")))
+    assert mc.run_matcher_cases(mo) == gold["matcher"]
+    bgr, mx, my = mc.input_stage_case()
+    g = gold["input_stage"]
+    assert mc.sha(oracle_libs.cvt_gray(oracle_libs.remap_linear(bgr, mx, my), False, 15)) == g["bgr_rect_gray"]
+    assert mc.sha(oracle_libs.remap_linear(bgr[:, :, 1].copy(), mx, my)) == g["rect_gray_only"]
+    assert mc.sha(oracle_libs.cvt_gray(bgr, True, 15)) == g["rgb_gray"]
