@@ -219,8 +219,8 @@ def algorithmic_bytes(level_sizes, n_kp: float, n_cand: float, n_cells: int):
     return {
         "pyramid": (P - px[-1]) + (P - px[0]),        # read L0..L6 once, write L1..L7 once
         "fast": P + 4 * n_cand + 4 * n_cells,         # every level read once; 4 B per candidate/cell
-        "octree": 8 * n_cand + 4 * n_kp,              # latency-bound; reported for completeness
-        "assemble": 12 * n_kp,
+        "octree": 8 * n_cand + 4 * n_kp + 12 * n_kp,  # latency-bound; reported for completeness (quadtree + the
+                                                      # output layout in its tail: 12 B per keypoint)
         "describe": P + 48 * n_kp,                    # every level read once + 32 B desc + 16 B kp record
     }
 
@@ -480,9 +480,9 @@ def run_ours(args):
         else:
             peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
         ab = algorithmic_bytes(level_sizes, n_kp, n_cand, n_cells)
-        names = ["pyramid", "fast", "octree", "assemble", "describe"]
+        names = ["pyramid", "fast", "octree", "describe"]
         kernels = {}
-        for k, nm in enumerate(names):
+        for nm, k in zip(names, (0, 1, 2, 4)):   # stage slot 3 (the former assemble launch) is empty
             gbs = ab[nm] * B / (stage[k] * 1e-3) / 1e9 if stage[k] > 0 else 0.0
             kernels[nm] = {"ms_per_launch_batch": round(float(stage[k]), 4), "alg_bytes_per_frame": int(ab[nm]),
                            "achieved_gbs": round(gbs, 1), "frac": round(gbs / peak, 4)}

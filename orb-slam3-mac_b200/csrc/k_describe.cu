@@ -1,10 +1,7 @@
 // k_describe.cu -- E7 layout + E4 orientation + E5 blur + E6 rotated BRIEF, fused.
 //
-//   k_assemble   one CTA per frame: prefix over the levels' survivors, lapping-area test on the
-//                scaled x, stable TWO-ENDED compaction (ORBextractor.cc:1124-1144): a keypoint
-//                with lap0 <= pt.x <= lap1 goes to the back (stereoIndex--), others to the front
-//                (monoIndex++), both in level-major order.  Writes every survivor's output row
-//                and the frame header {n, monoIndex, status}.
+//   (E7, the two-ended output layout, is orbx_assemble_frame in orbx_device.cuh: it runs in the
+//   tail of k_octree, in the last CTA of a frame to finish.)
 //   k_describe   one warp per keypoint.  The 43x43 neighbourhood of the UN-blurred level is
 //                staged in shared memory once (4-byte cp.async; reflect-101 of the level at
 //                image borders, which is what GaussianBlur sees on the reference's clone(),
@@ -93,55 +90,6 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     return a;
 }
 
-__global__ void __launch_bounds__(256)
-k_assemble(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ surv,
-           const uint32_t* __restrict__ survcnt, const int* __restrict__ lap,
-           uint32_t* __restrict__ dest, int32_t* __restrict__ header) {
-    extern __shared__ __align__(16) uint32_t sm[];
-    uint32_t* flags = sm;               // [surv_total + 2]
-    uint32_t* tmp = sm + P.surv_total + 2;  // [64]
-    const int frame = blockIdx.x, tid = threadIdx.x;
-    const uint32_t* sc = survcnt + (size_t)frame * ORBX_MAX_LEVELS;
-    const uint32_t* sv = surv + (size_t)frame * P.surv_total;
-    const float lap0 = (float)lap[2 * frame], lap1 = (float)lap[2 * frame + 1];
-
-    int off[ORBX_MAX_LEVELS + 1];
-    off[0] = 0;
-    for (int l = 0; l < P.nlevels; ++l) off[l + 1] = off[l] + min((int)sc[l], P.lvl[l].surv_cap);
-    const int n = off[P.nlevels];
-
-    for (int idx = tid; idx < n; idx += blockDim.x) {
-        int l = 0;
-        while (idx >= off[l + 1]) ++l;
-        const uint32_t key = sv[P.lvl[l].surv_off + (idx - off[l])];
-        float x = (float)(ORBX_KEY_X(key) + ORBX_FAST_BORDER);
-        if (l != 0) x = __fmul_rn(x, P.lvl[l].scale);
-        flags[idx] = (x >= lap0 && x <= lap1) ? 1u : 0u;
-    }
-    __syncthreads();
-    const uint32_t nstereo = block_excl_scan(flags, n, tmp);
-    if (tid == 0) flags[n] = nstereo;
-    __syncthreads();
-    // one record per keypoint for k_describe: {key, output row | level << 24}
-    uint2* d = reinterpret_cast<uint2*>(dest) + (size_t)frame * P.surv_total;
-    for (int idx = tid; idx < n; idx += blockDim.x) {
-        const uint32_t sb = flags[idx];
-        const bool stereo = flags[idx + 1] != sb;
-        int l = 0;
-        while (idx >= off[l + 1]) ++l;
-        const uint32_t key = sv[P.lvl[l].surv_off + (idx - off[l])];
-        const uint32_t row = stereo ? (uint32_t)(n - 1) - sb : (uint32_t)idx - sb;
-        d[idx] = make_uint2(key, row | ((uint32_t)l << 24));
-    }
-    if (tid == 0) {
-        int32_t* h = header + 4 * (size_t)frame;
-        h[0] = n;
-        h[1] = n - (int)nstereo;
-        h[2] = n > P.out_cap ? ORBX_E_CAPACITY : ORBX_OK;
-        h[3] = 0;
-    }
-}
-
 __device__ __forceinline__ void cp_async4(uint32_t saddr, const void* g) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(saddr), "l"(g) : "memory");
 }
@@ -156,7 +104,7 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
     const int frame = blockIdx.y;
     const int idx = blockIdx.x * DESC_WARPS + warp;
 
-    // the keypoint's record, written by k_assemble: {key, output row | level << 24}
+    // the keypoint's record, written by orbx_assemble_frame: {key, output row | level << 24}
     if (idx >= min(header[4 * frame], P.surv_total)) return;
     const uint2 rec = __ldg(reinterpret_cast<const uint2*>(dest) + (size_t)frame * P.surv_total + idx);
     const uint32_t key = rec.x;
@@ -326,15 +274,6 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
         kp.class_id = -1;
         kps[(size_t)frame * P.out_cap + out_row] = kp;
     }
-}
-
-cudaError_t orbx_launch_assemble(const OrbxPlan& P, const uint32_t* surv, const uint32_t* survcnt,
-                                 const int* lap, uint32_t* dest, int32_t* header, int nframes,
-                                 cudaStream_t st, int* launches) {
-    const size_t sm_a = (size_t)(P.surv_total + 2 + 64) * 4;
-    k_assemble<<<nframes, 256, sm_a, st>>>(P, surv, survcnt, lap, dest, header);
-    ++*launches;
-    return cudaGetLastError();
 }
 
 cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,

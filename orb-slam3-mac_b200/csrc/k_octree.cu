@@ -492,7 +492,9 @@ __host__ __device__ inline size_t oct_fixed_words(int NC, int NCP2, int CW) {
 __global__ void __launch_bounds__(OCT_THREADS, OCT_MINB)
 k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcnt,
          const uint32_t* __restrict__ cellkeys, uint32_t* __restrict__ keysA,
-         uint32_t* __restrict__ keysB, uint32_t* __restrict__ surv, uint32_t* __restrict__ survcnt,
+         uint32_t* __restrict__ keysB, uint32_t* surv, uint32_t* survcnt,
+         const int* __restrict__ lap, uint32_t* __restrict__ dest, int32_t* __restrict__ header,
+         uint32_t* frame_done /* [nframes], zero between launches */,
          int NC, int NCP2, int CW, int key_words /* shared-memory words per key buffer */) {
     extern __shared__ __align__(16) uint32_t sm[];
     const int level = blockIdx.x, frame = blockIdx.y;
@@ -668,6 +670,19 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
         if (lane == 0) out[i] = src[0xffffffffu - (uint32_t)(best & 0xffffffffull)];
     }
     if (tid == 0) survcnt[(size_t)frame * ORBX_MAX_LEVELS + level] = (uint32_t)S;
+
+    // ---- E7 in the tail: the last CTA of the frame to get here lays out the frame's output --------
+    // (release: every thread publishes its survivors, then one ticket per CTA; acquire: the winner
+    // fences again and reads the other levels' results through L2)
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) C.tmp[45] = atomicAdd(&frame_done[frame], 1u) == gridDim.x - 1 ? 1u : 0u;
+    __syncthreads();
+    if (C.tmp[45] == 0) return;
+    __threadfence();
+    if (tid == 0) frame_done[frame] = 0;   // ready for the next launch on this slot
+    __syncthreads();                        // C.tmp is about to be reused as scan scratch
+    orbx_assemble_frame(P, surv, survcnt, lap, dest, header, frame, sm);
 }
 
 struct OctLaunchCfg {
@@ -697,6 +712,8 @@ OctLaunchCfg orbx_octree_cfg(const OrbxPlan& P) {
     kw &= ~3ll;
     c.key_words = (int)kw;
     c.smem = fixed + (size_t)kw * 8;
+    const size_t assemble = (size_t)(P.surv_total + 2 + 64) * 4;   // orbx_assemble_frame in the kernel's tail
+    if (c.smem < assemble) c.smem = assemble;
     return c;
 }
 
@@ -708,10 +725,12 @@ cudaError_t orbx_configure_octree(const OrbxPlan& P) {
 
 cudaError_t orbx_launch_octree(const OrbxPlan& P, const uint32_t* cellcnt, const uint32_t* cellkeys,
                                uint32_t* keysA, uint32_t* keysB, uint32_t* surv, uint32_t* survcnt,
+                               const int* lap, uint32_t* dest, int32_t* header, uint32_t* frame_done,
                                int nframes, cudaStream_t st, int* launches) {
     OctLaunchCfg c = orbx_octree_cfg(P);
     dim3 grid(P.nlevels, nframes);
-    k_octree<<<grid, OCT_THREADS, c.smem, st>>>(P, cellcnt, cellkeys, keysA, keysB, surv, survcnt, c.NC,
+    k_octree<<<grid, OCT_THREADS, c.smem, st>>>(P, cellcnt, cellkeys, keysA, keysB, surv, survcnt, lap, dest, header,
+                                               frame_done, c.NC,
                                                c.NCP2, c.CW, c.key_words);
     ++*launches;
     return cudaGetLastError();

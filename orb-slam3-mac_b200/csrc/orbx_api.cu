@@ -32,10 +32,8 @@ cudaError_t orbx_launch_fast(const OrbxPlan& P, const OrbxSrc& src, const uint8_
 cudaError_t orbx_configure_octree(const OrbxPlan& P);
 cudaError_t orbx_launch_octree(const OrbxPlan& P, const uint32_t* cellcnt, const uint32_t* cellkeys,
                                uint32_t* keysA, uint32_t* keysB, uint32_t* surv, uint32_t* survcnt,
+                               const int* lap, uint32_t* dest, int32_t* header, uint32_t* frame_done,
                                int nframes, cudaStream_t st, int* launches);
-cudaError_t orbx_launch_assemble(const OrbxPlan& P, const uint32_t* surv, const uint32_t* survcnt,
-                                 const int* lap, uint32_t* dest, int32_t* header, int nframes,
-                                 cudaStream_t st, int* launches);
 cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
                                  const int32_t* header, const uint32_t* dest,
                                  orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
@@ -87,7 +85,7 @@ namespace {
 
 struct SlotCaps {  // bytes currently allocated per device buffer
     size_t img_in = 0, pyr = 0, cellcnt = 0, cellkeys = 0, keysA = 0, keysB = 0, surv = 0, survcnt = 0,
-           dest = 0, header = 0, kps = 0, desc = 0, lap = 0;
+           dest = 0, header = 0, kps = 0, desc = 0, lap = 0, frame_done = 0;
 };
 
 struct Slot {
@@ -103,6 +101,7 @@ struct Slot {
     orbx_keypoint* kps = nullptr;
     uint8_t* desc = nullptr;
     int* lap_d = nullptr;
+    uint32_t* frame_done = nullptr;   // per-frame CTA tickets of k_octree (self-resetting)
     int32_t* h_header = nullptr;  // pinned
     int* h_lap = nullptr;         // pinned
     // in-flight bookkeeping
@@ -375,6 +374,10 @@ int ensure_buffers(orbx_handle* h, const OrbxPlan& P) {
         if ((r = grow(&s.kps, &c.kps, z.kps))) return r;
         if ((r = grow(&s.desc, &c.desc, z.desc))) return r;
         if ((r = grow(&s.lap_d, &c.lap, z.lap))) return r;
+        if (c.frame_done < z.lap) {
+            if ((r = grow(&s.frame_done, &c.frame_done, z.lap))) return r;
+            CUDA_TRY(cudaMemset(s.frame_done, 0, c.frame_done));
+        }
     }
     return ORBX_OK;
 }
@@ -422,11 +425,10 @@ int launch_stages(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes, bool
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[1], s.st));
     CUDA_TRY(orbx_launch_fast(P, src, s.pyr, s.cellcnt, s.cellkeys, nframes, s.st, &s.launches));
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[2], s.st));
-    CUDA_TRY(orbx_launch_octree(P, s.cellcnt, s.cellkeys, s.keysA, s.keysB, s.surv, s.survcnt, nframes,
-                                s.st, &s.launches));
+    // quadtree + (in its tail) the two-ended output layout of every frame
+    CUDA_TRY(orbx_launch_octree(P, s.cellcnt, s.cellkeys, s.keysA, s.keysB, s.surv, s.survcnt, s.lap_d, s.dest,
+                                s.header, s.frame_done, nframes, s.st, &s.launches));
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[3], s.st));
-    CUDA_TRY(orbx_launch_assemble(P, s.surv, s.survcnt, s.lap_d, s.dest, s.header, nframes, s.st,
-                                  &s.launches));
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[4], s.st));
     CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.header, s.dest, s.kps, s.desc, nframes,
                                   s.st, &s.launches));
@@ -590,6 +592,7 @@ int orbx_destroy(orbx_handle* h) {
         cudaFree(s.img_in); cudaFree(s.pyr); cudaFree(s.cellcnt); cudaFree(s.cellkeys);
         cudaFree(s.keysA); cudaFree(s.keysB); cudaFree(s.surv); cudaFree(s.survcnt);
         cudaFree(s.dest); cudaFree(s.header); cudaFree(s.kps); cudaFree(s.desc); cudaFree(s.lap_d);
+        cudaFree(s.frame_done);
         if (s.h_header) cudaFreeHost(s.h_header);
         if (s.h_lap) cudaFreeHost(s.h_lap);
         for (int k = 0; k < 6; ++k) if (s.ev[k]) cudaEventDestroy(s.ev[k]);

@@ -74,4 +74,67 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t* a, int n, uint32_t
     return total;
 }
 
+// E7 (ORBextractor.cc:1124-1144): prefix over the levels' survivors of ONE frame, lapping-area test
+// on the scaled x, stable TWO-ENDED compaction: a keypoint with lap0 <= pt.x <= lap1 goes to the
+// back (stereoIndex--), others to the front (monoIndex++), both in level-major order.  Writes one
+// record {key, output row | level << 24} per survivor for k_describe and the frame header
+// {n, monoIndex, status}.  Called by every thread of ONE CTA (the last quadtree CTA of the frame to
+// finish); surv / survcnt were written by other CTAs, hence the L2 loads.  sm: >= surv_total + 66 words.
+__device__ __forceinline__ void orbx_assemble_frame(const OrbxPlan& P, const uint32_t* surv,
+                                                    const uint32_t* survcnt, const int* __restrict__ lap,
+                                                    uint32_t* __restrict__ dest, int32_t* __restrict__ header,
+                                                    int frame, uint32_t* sm) {
+    uint32_t* flags = sm;                    // [surv_total + 2]
+    uint32_t* tmp = sm + P.surv_total + 2;   // [64]
+    const int tid = threadIdx.x;
+    const uint32_t* sc = survcnt + (size_t)frame * ORBX_MAX_LEVELS;
+    const uint32_t* sv = surv + (size_t)frame * P.surv_total;
+    const float lap0 = (float)lap[2 * frame], lap1 = (float)lap[2 * frame + 1];
+    int off[ORBX_MAX_LEVELS + 1];
+    off[0] = 0;
+#pragma unroll
+    for (int l = 0; l < ORBX_MAX_LEVELS; ++l)
+        off[l + 1] = off[l] + (l < P.nlevels ? min((int)__ldcg(sc + l), P.lvl[l].surv_cap) : 0);
+    const int n = off[ORBX_MAX_LEVELS];
+    for (int idx = tid; idx < n; idx += blockDim.x) {
+        int l = 0, base = 0;   // level of survivor idx and the first index of that level (selects: off[] stays in registers)
+#pragma unroll
+        for (int k = 1; k < ORBX_MAX_LEVELS; ++k) {
+            const bool ge = idx >= off[k] && k < P.nlevels;
+            l += ge ? 1 : 0;
+            base = ge ? off[k] : base;
+        }
+        const uint32_t key = __ldcg(sv + P.lvl[l].surv_off + (idx - base));
+        float x = (float)(ORBX_KEY_X(key) + ORBX_FAST_BORDER);
+        if (l != 0) x = __fmul_rn(x, P.lvl[l].scale);
+        flags[idx] = (x >= lap0 && x <= lap1) ? 1u : 0u;
+    }
+    __syncthreads();
+    const uint32_t nstereo = block_excl_scan(flags, n, tmp);
+    if (tid == 0) flags[n] = nstereo;
+    __syncthreads();
+    uint2* d = reinterpret_cast<uint2*>(dest) + (size_t)frame * P.surv_total;
+    for (int idx = tid; idx < n; idx += blockDim.x) {
+        const uint32_t sb = flags[idx];
+        const bool stereo = flags[idx + 1] != sb;
+        int l = 0, base = 0;   // level of survivor idx and the first index of that level (selects: off[] stays in registers)
+#pragma unroll
+        for (int k = 1; k < ORBX_MAX_LEVELS; ++k) {
+            const bool ge = idx >= off[k] && k < P.nlevels;
+            l += ge ? 1 : 0;
+            base = ge ? off[k] : base;
+        }
+        const uint32_t key = __ldcg(sv + P.lvl[l].surv_off + (idx - base));
+        const uint32_t row = stereo ? (uint32_t)(n - 1) - sb : (uint32_t)idx - sb;
+        d[idx] = make_uint2(key, row | ((uint32_t)l << 24));
+    }
+    if (tid == 0) {
+        int32_t* h = header + 4 * (size_t)frame;
+        h[0] = n;
+        h[1] = n - (int)nstereo;
+        h[2] = n > P.out_cap ? ORBX_E_CAPACITY : ORBX_OK;
+        h[3] = 0;
+    }
+}
+
 #endif  // ORBX_DEVICE_CUH
