@@ -2,16 +2,19 @@
 // (ORBextractor::ComputeKeyPointsOctTree, src/ORBextractor.cc:763-854; cv::FAST semantics as
 // pinned in oracle/cvprims.h against cv2 4.13).
 //
-// One warp owns one 30-px cell of one level of one frame (all levels in a single launch):
-//   1. the (wCell+6) x (hCell+6) tile is staged in shared memory with aligned 32-bit loads,
-//      a fixed lane -> (row offset, word) mapping (no per-word division);
+// One warp owns one 30-px cell of one level of one frame (all levels in a single launch); the
+// cell's geometry comes from a per-shape record table (OrbxPlan::cell_tab, one 16-byte load):
+//   1. the (wCell+6) x (hCell+6) tile is staged in shared memory with 16-byte cp.async chunks
+//      (aligned words when the caller's level-0 buffer is not 16-byte aligned), a fixed
+//      lane -> (row offset, chunk) mapping (no per-chunk division);
 //   2. REJECTION TEST, 8 pixels per lane per step: 64-bit shared loads of the centre row and of
 //      the rows 3 above / below, funnel shifts for the +-3 column neighbours, VABSDIFF4.U8 for
 //      |ring - c| on four pixels at once, and a carry-free per-byte "> th" flag
 //      (((d >> 1) & 0x7f) + K, bit 7).  A 9-arc contains one pixel of every opposite ring pair,
 //      so (|r0-c|>th or |r8-c|>th) and (|r4-c|>th or |r12-c|>th) is necessary; ~7 % of the
 //      pixels of a textured frame pass (the sign-aware scalar test passes 5.3 %);
-//   3. passing pixels are pushed (raster order, ballot/popc ranks) into a shared-memory ring;
+//   3. passing pixels go to a shared-memory ring in raster order (warp scan of the per-lane
+//      counts, each lane writes its own pixels);
 //      whenever 32 are queued the exact score = max over the 16 arcs of 9 of min(ring - c) /
 //      min(c - ring), minus 1 (cornerScore<16>) is evaluated by 32 busy lanes, for bright and
 //      dark arcs AT ONCE on packed s16x2 values (one IMAD builds {ring-c+256, c-ring+256};
@@ -30,15 +33,13 @@
 #endif
 #define FAST_Q 512       // ring of queued pixels (u16): <= 31 left over + 256 pushed per step
 #define FAST_CLIST 256   // corners kept for the sparse NMS pass
-#define FAST_HDR_BYTES (2 * (FAST_Q + FAST_CLIST) + 4 * FAST_WQ)
-#define FAST_WQ 64       // ring of flagged 8-pixel words (u32): <= 31 left over + 32 pushed per step
+#define FAST_HDR_BYTES (2 * (FAST_Q + FAST_CLIST))
 
 struct FastWarpSmem {
     uint8_t* tile;    // tile_pitch * tile_h, rows 8-byte aligned
     uint8_t* score;   // score_pitch * (dh + 2), 1-px zero frame around the detection region
     uint16_t* queue;  // FAST_Q entries: (tile row << 7) | tile byte column
     uint16_t* clist;  // FAST_CLIST entries, same encoding
-    uint32_t* wq;     // FAST_WQ entries: ((row << 7 | pair * 8) << 8) | 8-bit pass mask
     int xo;           // tile byte column of tile x = 0 (alignment slack of the staged words)
 };
 
@@ -113,26 +114,6 @@ __device__ __forceinline__ uint32_t fast_small_inv(int d) {
 }
 __device__ __forceinline__ int fast_small_div(int x, uint32_t inv) { return (int)(((uint32_t)x * inv) >> 16); }
 
-// Moves up to 32 word entries {row, pair, 8-bit pass mask} of the word ring into the pixel ring,
-// one entry per lane, pixels in raster order (warp scan of the popcounts).
-__device__ __forceinline__ int fast_expand(const FastWarpSmem& s, int wh, int take, int qtail) {
-    const int lane = orbx_lane();
-    uint32_t e = 0;
-    if (lane < take) e = s.wq[(wh + lane) & (FAST_WQ - 1)];
-    uint32_t nib = e & 0xffu;
-    const uint32_t cnt = __popc(nib);
-    const uint32_t incl = warp_incl_scan(cnt);
-    int at = qtail + (int)(incl - cnt);
-    const int ebase = (int)(e >> 8);  // (row << 7) | (pair * 8)
-    while (nib) {
-        const int k = __ffs(nib) - 1;
-        nib &= nib - 1;
-        s.queue[at & (FAST_Q - 1)] = (uint16_t)(ebase + k);
-        ++at;
-    }
-    return (int)__shfl_sync(ORBX_FULL, incl, 31);
-}
-
 // Computes the score map for threshold `th` (s = raw-1 stored where raw > th, else 0 kept) and
 // the raster-ordered corner list.  Returns the number of corners (may exceed FAST_CLIST).
 __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp, int dw, int dh, int th) {
@@ -155,7 +136,7 @@ __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp
         vhi = (uint32_t)(m >> 32);
     }
     const uint32_t K4 = (uint32_t)(128 - ((th + 1) >> 1)) * 0x01010101u;
-    int qhead = 0, qn = 0, wh = 0, wn = 0, ncorn = 0;
+    int qhead = 0, qn = 0, ncorn = 0;
     const uint8_t* row = s.tile + (3 + ro) * tp + pc * 8;
     const int rstep = rpi * tp;
     const int rend = 3 + dh;
@@ -177,34 +158,30 @@ __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp
             flo = v_lo & h_lo & vlo;
             fhi = v_hi & h_hi & vhi;
         }
-        // push the lane's word entry (bit k of the mask = pixel k of the pair); flags sit in bit
-        // 7 of each byte: one multiply gathers them into the top nibble
-        const bool has = (flo | fhi) != 0;
-        const uint32_t bal = __ballot_sync(ORBX_FULL, has);
-        if (bal) {
-            if (has) {
-                const uint32_t nib = ((flo * 0x00204081u) >> 28) | (((fhi * 0x00204081u) >> 24) & 0xf0u);
-                s.wq[(wh + wn + __popc(bal & orbx_lanemask_lt())) & (FAST_WQ - 1)] =
-                    ((uint32_t)((r << 7) | (pc * 8)) << 8) | nib;
+        // flags sit in bit 7 of each byte: one multiply per word gathers them into a nibble.
+        // Flagged pixels go straight to the pixel ring in raster order (lane order = (row, pair)
+        // order): warp scan of the per-lane counts, then each lane writes its own pixels.
+        const uint32_t nib0 = ((flo * 0x00204081u) >> 28) | (((fhi * 0x00204081u) >> 24) & 0xf0u);
+        if (__any_sync(ORBX_FULL, nib0 != 0)) {
+            uint32_t nib = nib0;
+            const uint32_t cnt = __popc(nib);
+            const uint32_t incl = warp_incl_scan(cnt);
+            int at = qhead + qn + (int)(incl - cnt);
+            const int ebase = (r << 7) | (pc * 8);
+            while (nib) {
+                const int k = __ffs(nib) - 1;
+                nib &= nib - 1;
+                s.queue[at & (FAST_Q - 1)] = (uint16_t)(ebase + k);
+                ++at;
             }
-            wn += __popc(bal);
+            qn += (int)__shfl_sync(ORBX_FULL, incl, 31);
             __syncwarp();
-            if (wn >= 32) {
-                qn += fast_expand(s, wh, 32, qhead + qn);
-                wh = (wh + 32) & (FAST_WQ - 1);
-                wn -= 32;
-                __syncwarp();
-                while (qn >= 32) {
-                    fast_drain(s, tp, sp, th, qhead, 32, ncorn);
-                    qhead = (qhead + 32) & (FAST_Q - 1);
-                    qn -= 32;
-                }
+            while (qn >= 32) {
+                fast_drain(s, tp, sp, th, qhead, 32, ncorn);
+                qhead = (qhead + 32) & (FAST_Q - 1);
+                qn -= 32;
             }
         }
-    }
-    if (wn > 0) {
-        qn += fast_expand(s, wh, wn, qhead + qn);
-        __syncwarp();
     }
     while (qn > 0) {
         const int take = min(qn, 32);
@@ -275,49 +252,61 @@ __device__ __forceinline__ int fast_nms_emit(const FastWarpSmem& s, int sp, int 
 __global__ void __launch_bounds__(FAST_WARPS * 32, FAST_MINB)
 k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t* __restrict__ pyr,
              uint32_t* __restrict__ cellcnt, uint32_t* __restrict__ cellkeys, int tile_pitch,
-             int score_pitch, int warp_smem_bytes) {
+             int score_pitch, int warp_smem_bytes, int score_off, int src16) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int warp = orbx_warp(), lane = orbx_lane();
     const int g = blockIdx.x * FAST_WARPS + warp;  // global cell index inside the frame
     if (g >= P.cells_total) return;
     const int frame = blockIdx.y;
 
-    int l = 0;
-    while (l + 1 < P.nlevels && g >= P.lvl[l + 1].cell_off) ++l;
-    const OrbxLevel& L = P.lvl[l];
-    const int c = g - L.cell_off;
-    const int ci = L.n_cols_inv ? (int)__umulhi((uint32_t)c, L.n_cols_inv) : c, cj = c - ci * L.n_cols;
-
+    // the cell's record (built once per shape on the host, ORBextractor.cc:787-804)
+    const uint4 rec = __ldg(P.cell_tab + g);
+    const int iniX = (int)(rec.x & 0xffffu), iniY = (int)(rec.x >> 16);
+    const int tw = (int)(rec.y & 0xffu), th_ = (int)((rec.y >> 8) & 0xffu), l = (int)(rec.y >> 16);
     uint32_t* cnt_out = cellcnt + (size_t)frame * P.cells_total + g;
-    uint32_t* slot = cellkeys + (size_t)frame * P.keys_total + L.key_off + (size_t)c * L.cell_cap;
-
-    // ORBextractor.cc:787-804
-    const int iniY = ORBX_FAST_BORDER + ci * L.h_cell;
-    const int iniX = ORBX_FAST_BORDER + cj * L.w_cell;
-    const int maxY = min(iniY + L.h_cell + 6, L.max_by);
-    const int maxX = min(iniX + L.w_cell + 6, L.max_bx);
-    const int tw = maxX - iniX, th_ = maxY - iniY;
-    if (iniY >= L.max_by - 3 || iniX >= L.max_bx - 6 || tw < 7 || th_ < 7) {
+    if (tw == 0) {
         if (lane == 0) *cnt_out = 0;
         return;
     }
+    uint32_t* slot = cellkeys + (size_t)frame * P.keys_total + rec.z;
+    const int maxX = iniX + tw;
     const int dw = tw - 6, dh = th_ - 6;  // detection region = tile pixels [3, t-4]
 
     FastWarpSmem s;
     uint8_t* base = smem + (size_t)warp * warp_smem_bytes;
     s.queue = reinterpret_cast<uint16_t*>(base);
     s.clist = s.queue + FAST_Q;
-    s.wq = reinterpret_cast<uint32_t*>(base + 2 * (FAST_Q + FAST_CLIST));
     s.tile = base + FAST_HDR_BYTES;
-    s.score = s.tile + ((tile_pitch * (P.max_tile_h + 1) + 15) & ~15);
+    s.score = s.tile + score_off;
 
-    // 1. stage the tile: aligned words covering [iniX & ~3, maxX); lane -> (row offset, word)
+    // 1. stage the tile with cp.async: 16-byte chunks covering [iniX & ~15, maxX) when the
+    //    level's rows are 16-byte aligned (every pyramid level; level 0 unless the caller's
+    //    device buffer is not), else aligned words; lane -> (row offset, chunk)
     int lpitch;
     const uint8_t* src = orbx_level_ptr(P, isrc, pyr, frame, l, &lpitch);
-    const int ax = iniX & ~3;
-    s.xo = iniX - ax;  // tile x -> smem byte x + xo
-    {
-        const int nw = (maxX - ax + 3) >> 2;   // <= tile_pitch / 4 <= 21
+    if (l != 0 || src16) {
+        const int ax = iniX & ~15;
+        s.xo = iniX - ax;  // tile x -> smem byte x + xo
+        const int nch = (maxX - ax + 15) >> 4;   // <= tile_pitch / 16 <= 7
+        const uint32_t inv = fast_small_inv(nch);
+        const int rpi = fast_small_div(32, inv);
+        const int ro = fast_small_div(lane, inv), cw = lane - ro * nch;
+        if (ro < rpi) {
+            const uint8_t* gp = src + (size_t)(iniY + ro) * lpitch + ax + 16 * cw;
+            uint32_t sa = (uint32_t)__cvta_generic_to_shared(s.tile + ro * tile_pitch + 16 * cw);
+            const size_t gstep = (size_t)rpi * lpitch;
+            const uint32_t tstep = (uint32_t)(rpi * tile_pitch);
+#pragma unroll 2
+            for (int r = ro; r < th_; r += rpi) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gp) : "memory");
+                gp += gstep;
+                sa += tstep;
+            }
+        }
+    } else {
+        const int ax = iniX & ~3;
+        s.xo = iniX - ax;
+        const int nw = (maxX - ax + 3) >> 2;   // <= 21
         const uint32_t inv = fast_small_inv(nw);
         const int rpi = fast_small_div(32, inv);
         const int ro = fast_small_div(lane, inv), cw = lane - ro * nw;
@@ -342,7 +331,7 @@ k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8
     asm volatile("cp.async.wait_all;" ::: "memory");
     __syncwarp();
 
-    const int xadd = 3 + cj * L.w_cell, yadd = 3 + ci * L.h_cell;
+    const int xadd = (int)(rec.w & 0xffffu), yadd = (int)(rec.w >> 16);
     const uint32_t dw_inv = 0;  // computed inside the (rare) dense NMS path
 
     int nc = fast_scores(s, tile_pitch, score_pitch, dw, dh, P.ini_th);
@@ -358,32 +347,39 @@ k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8
     if (lane == 0) *cnt_out = (uint32_t)n;
 }
 
-void orbx_fast_smem_layout(const OrbxPlan& P, int* tile_pitch, int* score_pitch, int* warp_bytes) {
-    // tile rows hold up to max_tile_w + 3 (alignment slack) bytes plus the 8-byte pair / +-1 word
-    // reach of the rejection test, rounded to 8 bytes
-    *tile_pitch = ((P.max_tile_w + 3 + 7) / 8) * 8;
+#ifndef FAST_PITCH_ODD
+#define FAST_PITCH_ODD 1
+#endif
+void orbx_fast_smem_layout(const OrbxPlan& P, int* tile_pitch, int* score_pitch, int* warp_bytes, int* score_off) {
+    // tile rows hold the 16-byte chunks covering up to 15 (alignment slack) + max_tile_w bytes;
+    // an odd number of chunks per row keeps rows r and r + 2 on different banks.  The 8-byte pair /
+    // +-1 word reach of the rejection test may run into the next row (one spare row is allocated;
+    // only bytes outside the detection region, which are masked, can come from there).
+    int tp = ((P.max_tile_w + 15 + 15) / 16) * 16;
+    if (FAST_PITCH_ODD && (tp / 16) % 2 == 0) tp += 16;
+    *tile_pitch = tp;
     *score_pitch = ((P.max_tile_w - 6 + 2 + 3) / 4) * 4;
-    // one spare tile row: the test may read the word after the last staged one
-    int bytes = FAST_HDR_BYTES + ((*tile_pitch * (P.max_tile_h + 1) + 15) & ~15) +
-                ((*score_pitch * (P.max_tile_h - 6 + 2) + 15) & ~15);
+    *score_off = (tp * (P.max_tile_h + 1) + 15) & ~15;
+    int bytes = FAST_HDR_BYTES + *score_off + ((*score_pitch * (P.max_tile_h - 6 + 2) + 15) & ~15);
     *warp_bytes = (bytes + 15) & ~15;
 }
 
 // Called once per (device, plan): opt in to the dynamic shared memory the plan needs.
 cudaError_t orbx_configure_fast(const OrbxPlan& P) {
-    int tp, sp, wb;
-    orbx_fast_smem_layout(P, &tp, &sp, &wb);
+    int tp, sp, wb, so;
+    orbx_fast_smem_layout(P, &tp, &sp, &wb, &so);
     return cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 wb * FAST_WARPS);
 }
 
 cudaError_t orbx_launch_fast(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr, uint32_t* cellcnt,
                              uint32_t* cellkeys, int nframes, cudaStream_t st, int* launches) {
-    int tp, sp, wb;
-    orbx_fast_smem_layout(P, &tp, &sp, &wb);
+    int tp, sp, wb, so;
+    orbx_fast_smem_layout(P, &tp, &sp, &wb, &so);
     const int smem = wb * FAST_WARPS;
+    const int src16 = ((((uintptr_t)src.img0) | (uintptr_t)src.stride0 | (uintptr_t)src.pitch0) & 15) == 0;
     dim3 grid((P.cells_total + FAST_WARPS - 1) / FAST_WARPS, nframes);
-    k_fast_cells<<<grid, FAST_WARPS * 32, smem, st>>>(P, src, pyr, cellcnt, cellkeys, tp, sp, wb);
+    k_fast_cells<<<grid, FAST_WARPS * 32, smem, st>>>(P, src, pyr, cellcnt, cellkeys, tp, sp, wb, so, src16);
     ++*launches;
     return cudaGetLastError();
 }

@@ -206,6 +206,15 @@ int build_plan(const orbx_handle* h, int w, int hgt, OrbxPlan* out, std::vector<
     int cell_off = 0, surv_off = 0;
     size_t tab_off = 0;
     if (tab_host) tab_host->clear();
+    auto put = [&](const void* p, size_t n) -> size_t {
+        size_t at = tab_off;
+        if (tab_host) {
+            tab_host->resize(at + ((n + 15) & ~(size_t)15));
+            memcpy(tab_host->data() + at, p, n);
+        }
+        tab_off += (n + 15) & ~(size_t)15;
+        return at;
+    };
     for (int l = 0; l < nl; ++l) {
         OrbxLevel& L = P.lvl[l];
         // ORBextractor.cc:1156-1157
@@ -260,15 +269,6 @@ int build_plan(const orbx_handle* h, int w, int hgt, OrbxPlan* out, std::vector<
             std::vector<short> xa, ya;
             linear_axis(P.lvl[l - 1].w, L.w, xo, xa);
             linear_axis(P.lvl[l - 1].h, L.h, yo, ya);
-            auto put = [&](const void* p, size_t n) -> size_t {
-                size_t at = tab_off;
-                if (tab_host) {
-                    tab_host->resize(at + ((n + 15) & ~(size_t)15));
-                    memcpy(tab_host->data() + at, p, n);
-                }
-                tab_off += (n + 15) & ~(size_t)15;
-                return at;
-            };
             // stored as offsets; patched to device pointers by the caller
             L.xofs = (const uint16_t*)put(xo.data(), xo.size() * 2);
             L.xa = (const short*)put(xa.data(), xa.size() * 2);
@@ -303,10 +303,33 @@ int build_plan(const orbx_handle* h, int w, int hgt, OrbxPlan* out, std::vector<
     P.surv_total = surv_off;
     P.out_cap = surv_off;
     if (P.max_tile_w > 80 || P.max_tile_h > 80) return fail(ORBX_E_UNSUPPORTED, "FAST cell larger than 74 px");
+    // per-cell records of the FAST kernel (ORBextractor.cc:787-804)
+    {
+        std::vector<uint32_t> ct((size_t)4 * P.cells_total, 0u);
+        for (int l = 0; l < nl; ++l) {
+            const OrbxLevel& L = P.lvl[l];
+            for (int ci = 0; ci < L.n_rows; ++ci)
+                for (int cj = 0; cj < L.n_cols; ++cj) {
+                    const int c = ci * L.n_cols + cj;
+                    uint32_t* r = &ct[(size_t)4 * (L.cell_off + c)];
+                    const int iniY = ORBX_FAST_BORDER + ci * L.h_cell, iniX = ORBX_FAST_BORDER + cj * L.w_cell;
+                    const int maxY = std::min(iniY + L.h_cell + 6, L.max_by), maxX = std::min(iniX + L.w_cell + 6, L.max_bx);
+                    int tw = maxX - iniX, th = maxY - iniY;
+                    if (iniY >= L.max_by - 3 || iniX >= L.max_bx - 6 || tw < 7 || th < 7) tw = th = 0;
+                    r[0] = (uint32_t)iniX | ((uint32_t)iniY << 16);
+                    r[1] = (uint32_t)tw | ((uint32_t)th << 8) | ((uint32_t)l << 16);
+                    r[2] = (uint32_t)(L.key_off + (long long)c * L.cell_cap);
+                    r[3] = (uint32_t)(3 + cj * L.w_cell) | ((uint32_t)(3 + ci * L.h_cell) << 16);
+                }
+        }
+        if (P.keys_total >= (1ll << 32)) return fail(ORBX_E_UNSUPPORTED, "key slab too large");
+        P.cell_tab = (const uint4*)put(ct.data(), ct.size() * 4);
+    }
     return ORBX_OK;
 }
 
 void patch_tables(OrbxPlan& P, uint8_t* dev_base) {
+    P.cell_tab = (const uint4*)(dev_base + (size_t)P.cell_tab);
     for (int l = 1; l < P.nlevels; ++l) {
         OrbxLevel& L = P.lvl[l];
         L.xofs = (const uint16_t*)(dev_base + (size_t)L.xofs);

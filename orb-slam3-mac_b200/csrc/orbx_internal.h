@@ -78,6 +78,12 @@ struct OrbxPlan {
     long long frame_stride;  // bytes of one frame's pyramid slab
     int max_tile_w, max_tile_h;  // FAST tile (cell + 6) maxima over levels
     int _pad;
+    // one record per FAST cell (all levels, cell_off order), built once per shape on the host:
+    //   x = iniX | iniY << 16          tile origin in the level (ORBextractor.cc:787-804)
+    //   y = tile_w | tile_h << 8 | level << 16     (tile_w == 0: the reference skips this cell)
+    //   z = first key slot of the cell inside a frame's cellkeys[]
+    //   w = xadd | yadd << 16          cell origin relative to the detection origin (16,16), + 3
+    const uint4* cell_tab;
     OrbxLevel lvl[ORBX_MAX_LEVELS];
 };
 
