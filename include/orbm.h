@@ -18,6 +18,13 @@
  *     orbm_search_by_projection_frames   ORBmatcher::SearchByProjection(Frame&, const Frame&..)
  *                                        src/ORBmatcher.cc:1965-2181 (Nleft == -1 branch)
  *     orbm_search_for_initialization     ORBmatcher::SearchForInitialization src/ORBmatcher.cc:710-825
+ *     orbm_search_by_bow / _bow_kf       SearchByBoW x2                     src/ORBmatcher.cc:273-475, 827-967
+ *     orbm_search_by_projection_sim3     SearchByProjection(pKF, Scw, ..) x2  :477-590, 592-708
+ *     orbm_search_by_projection_reloc    SearchByProjection(F, pKF, sAlreadyFound, ..)  :2183-2305
+ *     orbm_fuse                          Fuse x2 (the search part)          :1403-1613, 1615-1737
+ *     orbm_search_by_sim3                SearchBySim3                       :1739-1963
+ *     orbm_search_for_triangulation      SearchForTriangulation x2          :969-1210, 1212-1401
+ *     orbm_distinctive_descriptors       MapPoint::ComputeDistinctiveDescriptors  src/MapPoint.cc:330-404
  *     candidate generation               Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea
  *                                        src/Frame.cc:377-408, 716-726, 645-714
  *
@@ -203,6 +210,101 @@ typedef struct orbm_bow_view {
  * one launch; the accept loop, which depends on earlier acceptances (:323-324), runs on the host. */
 int orbm_search_by_bow(orbm_context* c, const orbm_bow_view* KF, const uint8_t* kf_mp_ok, const orbm_bow_view* F,
                        int f_nleft, float nn_ratio, int check_orientation, int32_t* matches);
+
+/* ---- SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12), src/ORBmatcher.cc:827-967 (LoopClosing) -----------
+ * mp_ok1 / mp_ok2 [i] != 0: feature i of that keyframe has a map point that is not bad (:868-872,
+ * :892-898).  n_un1 / n_un2: pKF->mvKeysUn.size() when pKF->NLeft != -1 (features with a larger index
+ * are skipped, :863-865, :887-889), else -1.  matches12 (out, KF1->n ints): index of the KF2 feature
+ * whose map point is assigned to KF1 feature i, else -1.  Returns nmatches. */
+int orbm_search_by_bow_kf(orbm_context* c, const orbm_bow_view* KF1, const uint8_t* mp_ok1, int n_un1,
+                          const orbm_bow_view* KF2, const uint8_t* mp_ok2, int n_un2, float nn_ratio,
+                          int check_orientation, int32_t* matches12);
+
+/* ---- searches that project map points into a keyframe / frame (LoopClosing, LocalMapping, reloc) ---
+ * One map point as those loops see it after their geometric gates (Sim3 / pose transform, positive
+ * depth, camera projection, IsInImage, distance-invariance range, viewing angle, PredictScale): the
+ * camera models and the map stay on the host, the caller passes the result. */
+typedef struct orbm_proj_point {
+    float u, v;      /* projection into the target image */
+    float ur;        /* Fuse: u - bf * invz (src/ORBmatcher.cc:1490); unused elsewhere */
+    float angle;     /* reloc SearchByProjection: pKF->mvKeysUn[i].angle (:2267); unused elsewhere */
+    int32_t level;   /* nPredictedLevel */
+    uint8_t valid;   /* 0: a gate before GetFeaturesInArea rejected the point (it is skipped) */
+    uint8_t _pad[3];
+} orbm_proj_point;
+
+/* SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming), src/ORBmatcher.cc:477-590, and
+ * its overload with vpPointsKFs / vpMatchedKF, :592-708 (same search; the caller maps kp_match back to
+ * vpPointsKFs).  Window = KeyFrame::GetFeaturesInArea(u, v, th * scale[level]) (src/KeyFrame.cc:770-814),
+ * keypoint octave in [level-1, level], skip keypoints with vpMatched[idx] != NULL, smallest distance
+ * (first wins), accepted when bestDist <= TH_LOW * ratioHamming.
+ * kp_taken (in, KF->n bytes): vpMatched[idx] != NULL on entry.  kp_match (out, KF->n ints): index of the
+ * point this call assigned to keypoint idx, else -1.  Returns nmatches. */
+int orbm_search_by_projection_sim3(orbm_context* c, const orbm_frame_view* KF, const orbm_proj_point* pts,
+                                   const uint8_t* mp_desc, int m, int th, float ratio_hamming,
+                                   const uint8_t* kp_taken, int32_t* kp_match);
+
+/* SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:2183-2305
+ * (relocalisation).  Point i = map point of keyframe feature i (valid = exists, not bad, not already
+ * found, inside the image bounds, inside its distance range).  Window with levels [level-1, level+1],
+ * skip keypoints with CurrentFrame.mvpMapPoints[i2] != NULL (kp_taken), accept bestDist <= orb_dist,
+ * rotation-histogram check on pts[i].angle - F.keys[i2].angle.  kp_match as above. */
+int orbm_search_by_projection_reloc(orbm_context* c, const orbm_frame_view* F, const orbm_proj_point* pts,
+                                    const uint8_t* mp_desc, int m, float th, int orb_dist,
+                                    int check_orientation, const uint8_t* kp_taken, int32_t* kp_match);
+
+/* The search of ORBmatcher::Fuse, both overloads: Fuse(pKF, vpMapPoints, th, bRight)
+ * src/ORBmatcher.cc:1403-1613 (inv_level_sigma2 != NULL: the chi-square reprojection gates :1543-1570,
+ * stereo form where KF->u_right[idx] >= 0) and Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) :1615-1737
+ * (inv_level_sigma2 == NULL).  For bRight the caller passes the right camera's view (keys =
+ * mvKeysRight, desc = rows NLeft.., u_right as the reference indexes it) and idx_offset = NLeft.
+ * best_idx[i] = keypoint (+ idx_offset) with the smallest distance among the gated candidates when that
+ * distance is <= TH_LOW, else -1; best_dist[i] likewise (256 when none).  The map-graph updates
+ * (Replace / AddObservation / AddMapPoint, :1588-1604) stay with the caller, in point order: the search
+ * itself does not depend on them.  Returns nFused (the number of points with best_idx >= 0). */
+int orbm_fuse(orbm_context* c, const orbm_frame_view* KF, const orbm_proj_point* pts, const uint8_t* mp_desc,
+              int m, float th, const float* inv_level_sigma2, int idx_offset, int32_t* best_idx,
+              int32_t* best_dist);
+
+/* SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th), src/ORBmatcher.cc:1739-1963.
+ * pts1[i] = map point of KF1 feature i projected into KF2 (valid = exists, not already matched, not
+ * bad, passed the gates :1790-1823), mp_desc1 = those points' descriptors (n1 x 32); pts2 / mp_desc2 the
+ * reverse direction (:1871-1935).  Each direction keeps the best keypoint (octave in [level-1, level])
+ * when its distance is <= TH_HIGH; a pair is accepted when both directions agree (:1941-1957).
+ * match12 (out, n1 ints): index of the agreeing KF2 feature, else -1.  Returns nFound. */
+int orbm_search_by_sim3(orbm_context* c, const orbm_frame_view* KF1, const orbm_frame_view* KF2,
+                        const orbm_proj_point* pts1, const uint8_t* mp_desc1, const orbm_proj_point* pts2,
+                        const uint8_t* mp_desc2, float th, int32_t* match12);
+
+/* The camera model's pair test of SearchForTriangulation: GeometricCamera::epipolarConstrain
+ * (src/ORBmatcher.cc:1112) or matchAndtriangulate (:1316) for KF1 feature idx1 and KF2 feature idx2;
+ * non-zero = the pair is geometrically consistent. */
+typedef int (*orbm_pair_test)(void* user, int32_t idx1, int32_t idx2);
+
+/* SearchForTriangulation, src/ORBmatcher.cc:969-1210 (epipolarConstrain, bOnlyStereo, bCoarse) and
+ * :1212-1401 (matchAndtriangulate).  has_mp1 / has_mp2 [i] != 0: pKF->GetMapPoint(i) != NULL.
+ * stereo1 / stereo2 (may be NULL = all 0): bStereo of each feature (:1046, :1073).  epipole != NULL
+ * enables the monocular epipole gate (:1096-1104; (ep.x, ep.y), tested against 100 * KF2 scale factor
+ * of kp2.octave); pass NULL for rigs with a second camera and for the second overload.
+ * Pair test, in this order: `test` (the caller's camera model) if not NULL; else F12 (row-major 3x3)
+ * with level_sigma2_2 = pKF2->mvLevelSigma2: the Pinhole::epipolarConstrain arithmetic
+ * (src/CameraModels/Pinhole.cpp:129-143); else every pair passes (bCoarse).
+ * matches12 (out, KF1->n ints): vMatches12.  Returns nmatches. */
+int orbm_search_for_triangulation(orbm_context* c, const orbm_bow_view* KF1, const uint8_t* has_mp1,
+                                  const uint8_t* stereo1, const orbm_bow_view* KF2, const uint8_t* has_mp2,
+                                  const uint8_t* stereo2, int only_stereo, const float* epipole,
+                                  const float* scale_factors2, int nlevels2, orbm_pair_test test, void* user,
+                                  const float* F12, const float* level_sigma2_2, int check_orientation,
+                                  int32_t* matches12);
+
+/* MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:330-404, for a batch of map points: group g
+ * owns the observed descriptors desc[group_ptr[g] .. group_ptr[g+1]) (rows of 32 bytes, in the order of
+ * the reference's vDescriptors).  best[g] = row (relative to the group) with the least median distance
+ * to the others -- median = sorted row of the N x N distance matrix at index (int)(0.5 * (N - 1)),
+ * first minimum wins -- or -1 for an empty group.  All distances, medians and the argmin run on the
+ * device (one warp per map point). */
+int orbm_distinctive_descriptors(orbm_context* c, const uint8_t* desc, const int32_t* group_ptr, int ngroups,
+                                 int32_t* best);
 
 /* SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), src/ORBmatcher.cc:710-825.
  * prev_matched: F1.n (x, y) pairs, in/out.  matches12: F1.n ints, out.  Returns nmatches. */

@@ -20,6 +20,9 @@
 //   search_init           SearchForInitialization                 src/ORBmatcher.cc:710-825
 //   stereo_rows           Frame::ComputeStereoMatches (Hamming part)      src/Frame.cc:802-885
 //   knn2                  BFMatcher(NORM_HAMMING).knnMatch(k=2)   src/Frame.cc:1146 (OpenCV semantics)
+//   N3 (LocalMapping / LoopClosing / reloc): SearchByBoW(KF,KF) :827-967, SearchByProjection(pKF,Scw,..) :477-708,
+//   reloc SearchByProjection :2183-2305, Fuse :1403-1737, SearchBySim3 :1739-1963, SearchForTriangulation :969-1401,
+//   MapPoint::ComputeDistinctiveDescriptors src/MapPoint.cc:330-404
 #include <climits>
 #include <cmath>
 #include <cstdint>
@@ -880,6 +883,412 @@ int orbo_search_by_bow(const BowView* KFp, const uint8_t* kf_mp_ok, const BowVie
         }
     }
     return nmatches;
+}
+
+// ---- the LocalMapping / LoopClosing / relocalisation searches ---------------------
+struct ProjPoint {  // orbm_proj_point
+    float u, v, ur, angle;
+    int32_t level;
+    uint8_t valid, pad[3];
+};
+
+typedef std::map<unsigned int, std::vector<unsigned int> > FeatVec;
+static FeatVec feat_vec_of(const BowView& V) {
+    FeatVec fv;
+    for (int a = 0; a < V.nnodes; ++a)
+        fv[V.node_ids[a]] = std::vector<unsigned int>(V.node_items + V.node_ptr[a], V.node_items + V.node_ptr[a + 1]);
+    return fv;
+}
+
+// src/ORBmatcher.cc:827-967.  n_un = mvKeysUn.size() when NLeft != -1, else -1.
+int orbo_search_by_bow_kf(const BowView* K1, const uint8_t* ok1, int n_un1, const BowView* K2, const uint8_t* ok2,
+                          int n_un2, float mfNNratio, int mbCheckOrientation, int32_t* vpMatches12) {
+    const FeatVec fv1 = feat_vec_of(*K1), fv2 = feat_vec_of(*K2);
+    for (int i = 0; i < K1->n; ++i) vpMatches12[i] = -1;
+    std::vector<bool> vbMatched2(K2->n, false);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int nmatches = 0;
+    FeatVec::const_iterator f1it = fv1.begin(), f2it = fv2.begin();
+    while (f1it != fv1.end() && f2it != fv2.end()) {
+        if (f1it->first == f2it->first) {
+            for (size_t i1 = 0; i1 < f1it->second.size(); i1++) {
+                const size_t idx1 = f1it->second[i1];
+                if (n_un1 != -1 && idx1 >= (size_t)n_un1) continue;
+                if (!ok1[idx1]) continue;
+                const uint8_t* d1 = K1->desc + idx1 * 32;
+                int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+                for (size_t i2 = 0; i2 < f2it->second.size(); i2++) {
+                    const size_t idx2 = f2it->second[i2];
+                    if (n_un2 != -1 && idx2 >= (size_t)n_un2) continue;
+                    if (vbMatched2[idx2] || !ok2[idx2]) continue;
+                    const int dist = descriptor_distance(d1, K2->desc + idx2 * 32);
+                    if (dist < bestDist1) {
+                        bestDist2 = bestDist1;
+                        bestDist1 = dist;
+                        bestIdx2 = (int)idx2;
+                    } else if (dist < bestDist2) {
+                        bestDist2 = dist;
+                    }
+                }
+                if (bestDist1 < TH_LOW) {
+                    if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                        vpMatches12[idx1] = bestIdx2;
+                        vbMatched2[bestIdx2] = true;
+                        if (mbCheckOrientation) {
+                            float rot = K1->keys[idx1].angle - K2->keys[bestIdx2].angle;
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back((int)idx1);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            f1it++;
+            f2it++;
+        } else if (f1it->first < f2it->first) {
+            f1it = fv1.lower_bound(f2it->first);
+        } else {
+            f2it = fv2.lower_bound(f1it->first);
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {
+                vpMatches12[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:477-590 and :592-708 (the loop body after the geometric gates).
+int orbo_search_by_projection_sim3(const FrameView* KFp, const ProjPoint* pts, const uint8_t* mp_desc, int m, int th,
+                                   float ratioHamming, const uint8_t* kp_taken, int32_t* kp_match) {
+    const FrameView& KF = *KFp;
+    const GridO G(KF);
+    std::vector<bool> vpMatched(KF.n);
+    for (int i = 0; i < KF.n; ++i) {
+        vpMatched[i] = kp_taken && kp_taken[i];
+        kp_match[i] = -1;
+    }
+    int nmatches = 0;
+    for (int iMP = 0; iMP < m; iMP++) {
+        if (!pts[iMP].valid) continue;
+        const int nPredictedLevel = pts[iMP].level;
+        const float radius = th * KF.scale_factors[nPredictedLevel];
+        const std::vector<size_t> vIndices = get_features_in_area(KF, G, pts[iMP].u, pts[iMP].v, radius);
+        if (vIndices.empty()) continue;
+        const uint8_t* dMP = mp_desc + (size_t)iMP * 32;
+        int bestDist = 256, bestIdx = -1;
+        for (std::vector<size_t>::const_iterator vit = vIndices.begin(); vit != vIndices.end(); vit++) {
+            const size_t idx = *vit;
+            if (vpMatched[idx]) continue;
+            const int kpLevel = KF.keys[idx].octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            const int dist = descriptor_distance(dMP, KF.desc + idx * 32);
+            if (dist < bestDist) {
+                bestDist = dist;
+                bestIdx = (int)idx;
+            }
+        }
+        if (bestDist <= TH_LOW * ratioHamming) {
+            vpMatched[bestIdx] = true;
+            kp_match[bestIdx] = iMP;
+            nmatches++;
+        }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:2183-2305 (the loop body after the gates :2210-2233).
+int orbo_search_by_projection_reloc(const FrameView* Fp, const ProjPoint* pts, const uint8_t* mp_desc, int m, float th,
+                                    int ORBdist, int mbCheckOrientation, const uint8_t* kp_taken, int32_t* kp_match) {
+    const FrameView& CF = *Fp;
+    const GridO G(CF);
+    std::vector<bool> has_mp(CF.n);
+    for (int i = 0; i < CF.n; ++i) {
+        has_mp[i] = kp_taken && kp_taken[i];
+        kp_match[i] = -1;
+    }
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int nmatches = 0;
+    for (int i = 0; i < m; i++) {
+        if (!pts[i].valid) continue;
+        const int nPredictedLevel = pts[i].level;
+        const float radius = th * CF.scale_factors[nPredictedLevel];
+        const std::vector<size_t> vIndices2 =
+            get_features_in_area(CF, G, pts[i].u, pts[i].v, radius, nPredictedLevel - 1, nPredictedLevel + 1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* dMP = mp_desc + (size_t)i * 32;
+        int bestDist = 256, bestIdx2 = -1;
+        for (size_t k = 0; k < vIndices2.size(); k++) {
+            const size_t i2 = vIndices2[k];
+            if (has_mp[i2]) continue;
+            const int dist = descriptor_distance(dMP, CF.desc + i2 * 32);
+            if (dist < bestDist) {
+                bestDist = dist;
+                bestIdx2 = (int)i2;
+            }
+        }
+        if (bestDist <= ORBdist) {
+            has_mp[bestIdx2] = true;
+            kp_match[bestIdx2] = i;
+            nmatches++;
+            if (mbCheckOrientation) {
+                float rot = pts[i].angle - CF.keys[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i != ind1 && i != ind2 && i != ind3) {
+                for (size_t j = 0; j < rotHist[i].size(); j++) {
+                    kp_match[rotHist[i][j]] = -1;
+                    nmatches--;
+                }
+            }
+        }
+    }
+    return nmatches;
+}
+
+// The search of Fuse: src/ORBmatcher.cc:1519-1585 (inv_sigma2 != NULL) and :1685-1717 (NULL).
+int orbo_fuse(const FrameView* KFp, const ProjPoint* pts, const uint8_t* mp_desc, int m, float th,
+              const float* mvInvLevelSigma2, int idx_offset, int32_t* best_idx, int32_t* best_dist) {
+    const FrameView& KF = *KFp;
+    const GridO G(KF);
+    int nFused = 0;
+    for (int i = 0; i < m; i++) {
+        best_idx[i] = -1;
+        best_dist[i] = 256;
+        if (!pts[i].valid) continue;
+        const int nPredictedLevel = pts[i].level;
+        const float radius = th * KF.scale_factors[nPredictedLevel];
+        const float u = pts[i].u, v = pts[i].v, ur = pts[i].ur;
+        const std::vector<size_t> vIndices = get_features_in_area(KF, G, u, v, radius);
+        if (vIndices.empty()) continue;
+        const uint8_t* dMP = mp_desc + (size_t)i * 32;
+        int bestDist = 256, bestIdx = -1;
+        for (std::vector<size_t>::const_iterator vit = vIndices.begin(); vit != vIndices.end(); vit++) {
+            size_t idx = *vit;
+            const Kp& kp = KF.keys[idx];
+            const int kpLevel = kp.octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            if (mvInvLevelSigma2) {
+                if (KF.u_right && KF.u_right[idx] >= 0) {
+                    const float kpx = kp.x, kpy = kp.y, kpr = KF.u_right[idx];
+                    const float ex = u - kpx, ey = v - kpy, er = ur - kpr;
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * mvInvLevelSigma2[kpLevel] > 7.8) continue;
+                } else {
+                    const float kpx = kp.x, kpy = kp.y;
+                    const float ex = u - kpx, ey = v - kpy;
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * mvInvLevelSigma2[kpLevel] > 5.99) continue;
+                }
+            }
+            const int dist = descriptor_distance(dMP, KF.desc + idx * 32);
+            if (dist < bestDist) {
+                bestDist = dist;
+                bestIdx = (int)idx + idx_offset;
+            }
+        }
+        if (bestDist <= TH_LOW) {
+            best_idx[i] = bestIdx;
+            best_dist[i] = bestDist;
+            nFused++;
+        }
+    }
+    return nFused;
+}
+
+// src/ORBmatcher.cc:1739-1963 (the two projection passes after their gates, then the agreement test).
+static void sim3_pass(const FrameView& KF, const ProjPoint* pts, const uint8_t* mp_desc, int n, float th,
+                      std::vector<int>& vnMatch) {
+    const GridO G(KF);
+    vnMatch.assign(n, -1);
+    for (int i1 = 0; i1 < n; i1++) {
+        if (!pts[i1].valid) continue;
+        const int nPredictedLevel = pts[i1].level;
+        const float radius = th * KF.scale_factors[nPredictedLevel];
+        const std::vector<size_t> vIndices = get_features_in_area(KF, G, pts[i1].u, pts[i1].v, radius);
+        if (vIndices.empty()) continue;
+        const uint8_t* dMP = mp_desc + (size_t)i1 * 32;
+        int bestDist = INT_MAX, bestIdx = -1;
+        for (size_t k = 0; k < vIndices.size(); k++) {
+            const size_t idx = vIndices[k];
+            const Kp& kp = KF.keys[idx];
+            if (kp.octave < nPredictedLevel - 1 || kp.octave > nPredictedLevel) continue;
+            const int dist = descriptor_distance(dMP, KF.desc + idx * 32);
+            if (dist < bestDist) {
+                bestDist = dist;
+                bestIdx = (int)idx;
+            }
+        }
+        if (bestDist <= TH_HIGH) vnMatch[i1] = bestIdx;
+    }
+}
+
+int orbo_search_by_sim3(const FrameView* KF1, const FrameView* KF2, const ProjPoint* pts1, const uint8_t* mp_desc1,
+                        const ProjPoint* pts2, const uint8_t* mp_desc2, float th, int32_t* match12) {
+    const int N1 = KF1->n, N2 = KF2->n;
+    std::vector<int> vnMatch1, vnMatch2;
+    sim3_pass(*KF2, pts1, mp_desc1, N1, th, vnMatch1);
+    sim3_pass(*KF1, pts2, mp_desc2, N2, th, vnMatch2);
+    int nFound = 0;
+    for (int i1 = 0; i1 < N1; i1++) {
+        match12[i1] = -1;
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0) {
+            const int idx1 = vnMatch2[idx2];
+            if (idx1 == i1) {
+                match12[i1] = idx2;
+                nFound++;
+            }
+        }
+    }
+    return nFound;
+}
+
+// src/ORBmatcher.cc:969-1210 and :1212-1401.  pair_ok: the camera model's epipolarConstrain /
+// matchAndtriangulate as a table lookup supplied by the test (row-major KF1.n x KF2.n bytes), NULL with
+// F12 != NULL: Pinhole::epipolarConstrain (src/CameraModels/Pinhole.cpp:129-143), both NULL: bCoarse.
+int orbo_search_for_triangulation(const BowView* K1, const uint8_t* has_mp1, const uint8_t* stereo1, const BowView* K2,
+                                  const uint8_t* has_mp2, const uint8_t* stereo2, int bOnlyStereo, const float* ep,
+                                  const float* mvScaleFactors2, const uint8_t* pair_ok, const float* F12,
+                                  const float* mvLevelSigma2_2, int mbCheckOrientation, int32_t* vMatches12) {
+    const FeatVec fv1 = feat_vec_of(*K1), fv2 = feat_vec_of(*K2);
+    int nmatches = 0;
+    std::vector<bool> vbMatched2(K2->n, false);
+    for (int i = 0; i < K1->n; ++i) vMatches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    FeatVec::const_iterator f1it = fv1.begin(), f2it = fv2.begin();
+    while (f1it != fv1.end() && f2it != fv2.end()) {
+        if (f1it->first == f2it->first) {
+            for (size_t i1 = 0; i1 < f1it->second.size(); i1++) {
+                const size_t idx1 = f1it->second[i1];
+                if (has_mp1[idx1]) continue;
+                const bool bStereo1 = stereo1 && stereo1[idx1];
+                if (bOnlyStereo)
+                    if (!bStereo1) continue;
+                const Kp& kp1 = K1->keys[idx1];
+                const uint8_t* d1 = K1->desc + idx1 * 32;
+                int bestDist = TH_LOW, bestIdx2 = -1;
+                for (size_t i2 = 0; i2 < f2it->second.size(); i2++) {
+                    const size_t idx2 = f2it->second[i2];
+                    if (vbMatched2[idx2] || has_mp2[idx2]) continue;
+                    const bool bStereo2 = stereo2 && stereo2[idx2];
+                    if (bOnlyStereo)
+                        if (!bStereo2) continue;
+                    const int dist = descriptor_distance(d1, K2->desc + idx2 * 32);
+                    if (dist > TH_LOW || dist > bestDist) continue;
+                    const Kp& kp2 = K2->keys[idx2];
+                    if (!bStereo1 && !bStereo2 && ep) {
+                        const float distex = ep[0] - kp2.x, distey = ep[1] - kp2.y;
+                        if (distex * distex + distey * distey < 100 * mvScaleFactors2[kp2.octave]) continue;
+                    }
+                    bool ok = true;
+                    if (pair_ok) {
+                        ok = pair_ok[idx1 * (size_t)K2->n + idx2] != 0;
+                    } else if (F12) {
+                        const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+                        const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+                        const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+                        const float num = a * kp2.x + b * kp2.y + c;
+                        const float den = a * a + b * b;
+                        if (den == 0) {
+                            ok = false;
+                        } else {
+                            const float dsqr = num * num / den;
+                            ok = dsqr < 3.84 * mvLevelSigma2_2[kp2.octave];
+                        }
+                    }
+                    if (ok) {
+                        bestIdx2 = (int)idx2;
+                        bestDist = dist;
+                    }
+                }
+                if (bestIdx2 >= 0) {
+                    const Kp& kp2 = K2->keys[bestIdx2];
+                    vMatches12[idx1] = bestIdx2;
+                    nmatches++;
+                    if (mbCheckOrientation) {
+                        float rot = kp1.angle - kp2.angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        rotHist[bin].push_back((int)idx1);
+                    }
+                }
+            }
+            f1it++;
+            f2it++;
+        } else if (f1it->first < f2it->first) {
+            f1it = fv1.lower_bound(f2it->first);
+        } else {
+            f2it = fv2.lower_bound(f1it->first);
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {
+                vMatches12[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
+// src/MapPoint.cc:330-404 for a batch of map points (group g = rows group_ptr[g] .. group_ptr[g+1]).
+int orbo_distinctive_descriptors(const uint8_t* desc, const int32_t* group_ptr, int ngroups, int32_t* best) {
+    for (int g = 0; g < ngroups; ++g) {
+        const uint8_t* vDescriptors = desc + (size_t)group_ptr[g] * 32;
+        const size_t N = (size_t)(group_ptr[g + 1] - group_ptr[g]);
+        if (N == 0) {
+            best[g] = -1;
+            continue;
+        }
+        std::vector<float> Distances(N * N);
+        for (size_t i = 0; i < N; i++) {
+            Distances[i * N + i] = 0;
+            for (size_t j = i + 1; j < N; j++) {
+                int distij = descriptor_distance(vDescriptors + i * 32, vDescriptors + j * 32);
+                Distances[i * N + j] = distij;
+                Distances[j * N + i] = distij;
+            }
+        }
+        int BestMedian = INT_MAX, BestIdx = 0;
+        for (size_t i = 0; i < N; i++) {
+            std::vector<int> vDists(Distances.begin() + i * N, Distances.begin() + i * N + N);
+            std::sort(vDists.begin(), vDists.end());
+            int median = vDists[0.5 * (N - 1)];
+            if (median < BestMedian) {
+                BestMedian = median;
+                BestIdx = (int)i;
+            }
+        }
+        best[g] = BestIdx;
+    }
+    return 0;
 }
 
 }  // extern "C"

@@ -272,6 +272,68 @@ class MatchOracle:
             C.c_void_p(d.ctypes.data))
         return u, d, n
 
+    # ---- SURVEY 8(f) N3 ----------------------------------------------------------------------------
+    @staticmethod
+    def _p(a):
+        return None if a is None else C.c_void_p(a.ctypes.data)
+
+    def search_by_bow_kf(self, KF1, ok1, KF2, ok2, n_un1, n_un2, nnratio, check_ori):
+        ok1, ok2 = np.ascontiguousarray(ok1, np.uint8), np.ascontiguousarray(ok2, np.uint8)
+        m12 = np.zeros(len(KF1.keys), np.int32)
+        v1, v2 = KF1.view(), KF2.view()
+        n = self.lib.orbo_search_by_bow_kf(C.byref(v1), self._p(ok1), int(n_un1), C.byref(v2), self._p(ok2), int(n_un2),
+                                           C.c_float(nnratio), int(check_ori), self._p(m12))
+        return n, m12
+
+    def search_by_projection_sim3(self, KF, pts, mp_desc, th, ratio, kp_taken=None):
+        taken = np.zeros(KF.N, np.uint8) if kp_taken is None else np.ascontiguousarray(kp_taken, np.uint8)
+        match = np.zeros(KF.N, np.int32)
+        v = KF.view()
+        n = self.lib.orbo_search_by_projection_sim3(C.byref(v), self._p(pts), self._p(mp_desc), len(pts), int(th),
+                                                    C.c_float(ratio), self._p(taken), self._p(match))
+        return n, match
+
+    def search_by_projection_reloc(self, F, pts, mp_desc, th, orb_dist, check_ori, kp_taken=None):
+        taken = np.zeros(F.N, np.uint8) if kp_taken is None else np.ascontiguousarray(kp_taken, np.uint8)
+        match = np.zeros(F.N, np.int32)
+        v = F.view()
+        n = self.lib.orbo_search_by_projection_reloc(C.byref(v), self._p(pts), self._p(mp_desc), len(pts), C.c_float(th),
+                                                     int(orb_dist), int(check_ori), self._p(taken), self._p(match))
+        return n, match
+
+    def fuse(self, KF, pts, mp_desc, th, inv_level_sigma2=None, idx_offset=0):
+        inv = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+        bi = np.zeros(len(pts), np.int32)
+        bd = np.zeros(len(pts), np.int32)
+        v = KF.view()
+        n = self.lib.orbo_fuse(C.byref(v), self._p(pts), self._p(mp_desc), len(pts), C.c_float(th), self._p(inv),
+                               int(idx_offset), self._p(bi), self._p(bd))
+        return n, bi, bd
+
+    def search_by_sim3(self, KF1, KF2, p1, d1, p2, d2, th):
+        m12 = np.zeros(KF1.N, np.int32)
+        v1, v2 = KF1.view(), KF2.view()
+        n = self.lib.orbo_search_by_sim3(C.byref(v1), C.byref(v2), self._p(p1), self._p(d1), self._p(p2), self._p(d2),
+                                         C.c_float(th), self._p(m12))
+        return n, m12
+
+    def search_for_triangulation(self, KF1, has1, st1, KF2, has2, st2, only_stereo, ep, sf2, pair_ok, F12, ls2,
+                                 check_ori):
+        m12 = np.zeros(len(KF1.keys), np.int32)
+        v1, v2 = KF1.view(), KF2.view()
+        n = self.lib.orbo_search_for_triangulation(C.byref(v1), self._p(has1), self._p(st1), C.byref(v2), self._p(has2),
+                                                   self._p(st2), int(only_stereo), self._p(ep), self._p(sf2),
+                                                   self._p(pair_ok), self._p(F12), self._p(ls2), int(check_ori),
+                                                   self._p(m12))
+        return n, m12
+
+    def distinctive_descriptors(self, desc, group_ptr):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        gp = np.ascontiguousarray(group_ptr, np.int32)
+        best = np.zeros(len(gp) - 1, np.int32)
+        self.lib.orbo_distinctive_descriptors(self._p(d), self._p(gp), len(gp) - 1, self._p(best))
+        return best
+
     def knn2(self, q, t):
         q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
         t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)

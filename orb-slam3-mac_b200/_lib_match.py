@@ -38,6 +38,11 @@ AREA_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("min_lev
                              ("valid", "<i4"), ("desc_row", "<i4")])  # orbm_area_query
 assert MAP_POINT_DTYPE.itemsize == 32 and LAST_OBS_DTYPE.itemsize == 28 and AREA_QUERY_DTYPE.itemsize == 28
 
+PROJ_POINT_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("ur", "<f4"), ("angle", "<f4"), ("level", "<i4"),
+                             ("valid", "u1"), ("_pad", "u1", (3,))])  # orbm_proj_point
+assert PROJ_POINT_DTYPE.itemsize == 24
+PAIR_TEST = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_int32)  # orbm_pair_test
+
 _vp, _i, _f = C.c_void_p, C.c_int, C.c_float
 ORBM_SYMBOLS = {
     "orbm_create": (_i, [_i, C.POINTER(_vp)]),
@@ -54,6 +59,14 @@ ORBM_SYMBOLS = {
                                                      _vp, _vp]),
     "orbm_search_by_bow": (_i, [_vp, C.POINTER(BowView), _vp, C.POINTER(BowView), _i, _f, _i, _vp]),
     "orbm_search_for_initialization": (_i, [_vp, _fv, _fv, _vp, _vp, _i, _f, _i]),
+    "orbm_search_by_bow_kf": (_i, [_vp, C.POINTER(BowView), _vp, _i, C.POINTER(BowView), _vp, _i, _f, _i, _vp]),
+    "orbm_search_by_projection_sim3": (_i, [_vp, _fv, _vp, _vp, _i, _i, _f, _vp, _vp]),
+    "orbm_search_by_projection_reloc": (_i, [_vp, _fv, _vp, _vp, _i, _f, _i, _i, _vp, _vp]),
+    "orbm_fuse": (_i, [_vp, _fv, _vp, _vp, _i, _f, _vp, _i, _vp, _vp]),
+    "orbm_search_by_sim3": (_i, [_vp, _fv, _fv, _vp, _vp, _vp, _vp, _f, _vp]),
+    "orbm_search_for_triangulation": (_i, [_vp, C.POINTER(BowView), _vp, _vp, C.POINTER(BowView), _vp, _vp, _i, _vp,
+                                           _vp, _i, _vp, _vp, _vp, _vp, _i, _vp]),
+    "orbm_distinctive_descriptors": (_i, [_vp, _vp, _vp, _i, _vp]),
     "orbm_area_candidates": (_i, [_vp, _fv, _vp, _i, _vp, _i, _vp, _vp, _vp, _i]),
     "orbm_last_device_ms": (_i, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_longlong)]),
     "orbm_measure_popc_peak": (_i, [_vp, C.POINTER(C.c_double)]),

@@ -444,3 +444,48 @@ cudaError_t orbm_launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStre
     k_popc_peak<<<blocks, 256, 0, st>>>(out, iters);
     return cudaGetLastError();
 }
+
+// ---- N3: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:330-404), batched --------------
+// One warp per map point (group of N observed descriptors).  Lane i walks rows i, i+32, ..: the
+// median of row i = the k-th smallest (k = (int)(0.5 * (N - 1)), the reference's index into the
+// sorted row, which includes d(i,i) = 0) of d(i, .), found by a 9-step binary search on the value
+// (distances are integers in [0, 256]) with the row's distances recomputed per step from L1 -- no
+// N x N matrix is stored.  The first row with the least median wins (packed key median << 20 | i,
+// warp min), as the reference's strict '<' scan does.
+__global__ void __launch_bounds__(128)
+k_distinctive(const uint4* __restrict__ desc, const int32_t* __restrict__ group_ptr, int ngroups,
+              int32_t* __restrict__ best) {
+    const int g = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
+    if (g >= ngroups) return;
+    const int lane = orbx_lane();
+    const int base = __ldg(group_ptr + g), N = __ldg(group_ptr + g + 1) - base;
+    if (N <= 0) {
+        if (lane == 0) best[g] = -1;
+        return;
+    }
+    const uint4* D = desc + 2 * (size_t)base;
+    const int k = (int)(0.5 * (double)(N - 1));
+    uint32_t key = 0xffffffffu;
+    for (int i = lane; i < N; i += 32) {
+        const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
+        // smallest v with #{j : d(i,j) <= v} >= k + 1
+        int lo = 0, hi = 256;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int cnt = 0;
+            for (int j = 0; j < N; ++j) cnt += hamming256(a0, a1, D + 2 * j) <= mid ? 1 : 0;
+            if (cnt >= k + 1) hi = mid; else lo = mid + 1;
+        }
+        key = min(key, ((uint32_t)lo << 20) | (uint32_t)i);
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) key = min(key, __shfl_xor_sync(ORBX_FULL, key, d));
+    if (lane == 0) best[g] = (int32_t)(key & 0xfffffu);
+}
+
+cudaError_t orbm_launch_distinctive(const uint8_t* desc, const int32_t* group_ptr, int ngroups, int32_t* best,
+                                    cudaStream_t st) {
+    if (ngroups <= 0) return cudaSuccess;
+    k_distinctive<<<(ngroups + 3) / 4, 128, 0, st>>>(reinterpret_cast<const uint4*>(desc), group_ptr, ngroups, best);
+    return cudaGetLastError();
+}

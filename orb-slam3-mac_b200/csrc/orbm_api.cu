@@ -1065,3 +1065,5 @@ int orbm_search_for_initialization(orbm_context* c, const orbm_frame_view* F1, c
 }
 
 }  // extern "C"
+
+#include "orbm_n3.inc"

@@ -14,7 +14,7 @@ import numpy as np
 from . import _lib
 from ._lib import KP_DTYPE, check
 from ._lib_match import (AREA_QUERY_DTYPE, BowView, FrameRight, FrameView, LAST_OBS_DTYPE, MAP_POINT_DTYPE,  # noqa: F401
-                         MAP_POINT_RIGHT_DTYPE)
+                         MAP_POINT_RIGHT_DTYPE, PAIR_TEST, PROJ_POINT_DTYPE)
 
 FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48
 
@@ -269,3 +269,116 @@ class ORBmatcher:
         if n < 0:
             check(n)
         return n, m12, prev
+
+    # ---- LocalMapping / LoopClosing / relocalisation searches -------------------------
+    @staticmethod
+    def _u8(a, n):
+        return np.zeros(n, np.uint8) if a is None else np.ascontiguousarray(a, np.uint8)
+
+    def SearchByBoWKF(self, KF1: BowSide, mp_ok1, KF2: BowSide, mp_ok2, n_un1: int = -1, n_un2: int = -1):
+        """SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12), src/ORBmatcher.cc:827-967.
+        Returns (nmatches, matches12[KF1.N] = KF2 feature index or -1)."""
+        ok1, ok2 = self._u8(mp_ok1, len(KF1.keys)), self._u8(mp_ok2, len(KF2.keys))
+        m12 = np.zeros(len(KF1.keys), np.int32)
+        v1, v2 = KF1.view(), KF2.view()
+        n = self.lib.orbm_search_by_bow_kf(self.ctx, C.byref(v1), ok1.ctypes.data, int(n_un1), C.byref(v2),
+                                           ok2.ctypes.data, int(n_un2), self.mfNNratio, int(self.mbCheckOrientation),
+                                           m12.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, m12
+
+    def SearchByProjectionSim3(self, KF: Frame, points, mp_desc, th: int, ratioHamming: float = 1.0, kp_taken=None):
+        """SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming), src/ORBmatcher.cc:477-708
+        (both overloads).  points: PROJ_POINT_DTYPE.  Returns (nmatches, kp_match[KF.N])."""
+        pts = np.ascontiguousarray(points, PROJ_POINT_DTYPE)
+        d = np.ascontiguousarray(mp_desc, np.uint8).reshape(-1, 32)
+        taken = self._u8(kp_taken, KF.N)
+        match = np.zeros(KF.N, np.int32)
+        v = KF.view()
+        n = self.lib.orbm_search_by_projection_sim3(self.ctx, C.byref(v), pts.ctypes.data, d.ctypes.data, len(pts),
+                                                    int(th), float(ratioHamming), taken.ctypes.data, match.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, match
+
+    def SearchByProjectionReloc(self, F: Frame, points, mp_desc, th: float, ORBdist: int, kp_taken=None):
+        """SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:2183-2305."""
+        pts = np.ascontiguousarray(points, PROJ_POINT_DTYPE)
+        d = np.ascontiguousarray(mp_desc, np.uint8).reshape(-1, 32)
+        taken = self._u8(kp_taken, F.N)
+        match = np.zeros(F.N, np.int32)
+        v = F.view()
+        n = self.lib.orbm_search_by_projection_reloc(self.ctx, C.byref(v), pts.ctypes.data, d.ctypes.data, len(pts),
+                                                     float(th), int(ORBdist), int(self.mbCheckOrientation),
+                                                     taken.ctypes.data, match.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, match
+
+    def Fuse(self, KF: Frame, points, mp_desc, th: float = 3.0, inv_level_sigma2=None, idx_offset: int = 0):
+        """The search of Fuse (src/ORBmatcher.cc:1403-1737): returns (nFused, best_idx[m], best_dist[m])."""
+        pts = np.ascontiguousarray(points, PROJ_POINT_DTYPE)
+        d = np.ascontiguousarray(mp_desc, np.uint8).reshape(-1, 32)
+        inv = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+        bi = np.zeros(len(pts), np.int32)
+        bd = np.zeros(len(pts), np.int32)
+        v = KF.view()
+        n = self.lib.orbm_fuse(self.ctx, C.byref(v), pts.ctypes.data, d.ctypes.data, len(pts), float(th),
+                               None if inv is None else inv.ctypes.data, int(idx_offset), bi.ctypes.data, bd.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, bi, bd
+
+    def SearchBySim3(self, KF1: Frame, KF2: Frame, points1, mp_desc1, points2, mp_desc2, th: float):
+        """SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th), src/ORBmatcher.cc:1739-1963.
+        Returns (nFound, match12[KF1.N])."""
+        p1 = np.ascontiguousarray(points1, PROJ_POINT_DTYPE)
+        p2 = np.ascontiguousarray(points2, PROJ_POINT_DTYPE)
+        d1 = np.ascontiguousarray(mp_desc1, np.uint8).reshape(-1, 32)
+        d2 = np.ascontiguousarray(mp_desc2, np.uint8).reshape(-1, 32)
+        assert len(p1) == KF1.N and len(p2) == KF2.N
+        m12 = np.zeros(KF1.N, np.int32)
+        v1, v2 = KF1.view(), KF2.view()
+        n = self.lib.orbm_search_by_sim3(self.ctx, C.byref(v1), C.byref(v2), p1.ctypes.data, d1.ctypes.data,
+                                         p2.ctypes.data, d2.ctypes.data, float(th), m12.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, m12
+
+    def SearchForTriangulation(self, KF1: BowSide, has_mp1, KF2: BowSide, has_mp2, stereo1=None, stereo2=None,
+                               bOnlyStereo=False, epipole=None, scale_factors2=None, pair_test=None, F12=None,
+                               level_sigma2_2=None):
+        """SearchForTriangulation, src/ORBmatcher.cc:969-1401 (both overloads).  pair_test(idx1, idx2) -> bool is
+        the camera model's epipolarConstrain / matchAndtriangulate.  Returns (nmatches, vMatches12[KF1.N])."""
+        h1, h2 = self._u8(has_mp1, len(KF1.keys)), self._u8(has_mp2, len(KF2.keys))
+        s1 = None if stereo1 is None else np.ascontiguousarray(stereo1, np.uint8)
+        s2 = None if stereo2 is None else np.ascontiguousarray(stereo2, np.uint8)
+        ep = None if epipole is None else np.ascontiguousarray(epipole, np.float32)
+        sf = None if scale_factors2 is None else np.ascontiguousarray(scale_factors2, np.float32)
+        f12 = None if F12 is None else np.ascontiguousarray(F12, np.float32).reshape(9)
+        ls2 = None if level_sigma2_2 is None else np.ascontiguousarray(level_sigma2_2, np.float32)
+        nlev = max(len(sf) if sf is not None else 0, len(ls2) if ls2 is not None else 0)
+        if sf is not None and ls2 is not None:
+            assert len(sf) == len(ls2)
+        cb = PAIR_TEST(lambda user, a, b: int(bool(pair_test(a, b)))) if pair_test is not None else None
+        m12 = np.zeros(len(KF1.keys), np.int32)
+        v1, v2 = KF1.view(), KF2.view()
+        p = lambda a: None if a is None else a.ctypes.data  # noqa: E731
+        n = self.lib.orbm_search_for_triangulation(
+            self.ctx, C.byref(v1), h1.ctypes.data, p(s1), C.byref(v2), h2.ctypes.data, p(s2), int(bOnlyStereo), p(ep),
+            p(sf), nlev, C.cast(cb, C.c_void_p) if cb is not None else None, None, p(f12), p(ls2),
+            int(self.mbCheckOrientation), m12.ctypes.data)
+        if n < 0:
+            check(n)
+        return n, m12
+
+    def ComputeDistinctiveDescriptors(self, desc, group_ptr):
+        """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:330-404) for a batch of map points.
+        Returns best[g] (row inside group g, -1 for an empty group)."""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        gp = np.ascontiguousarray(group_ptr, np.int32)
+        best = np.zeros(len(gp) - 1, np.int32)
+        check(self.lib.orbm_distinctive_descriptors(self.ctx, d.ctypes.data, gp.ctypes.data, len(gp) - 1,
+                                                    best.ctypes.data))
+        return best

@@ -1,0 +1,115 @@
+"""Seeded cases of the SURVEY 8(f) N3 searches (LocalMapping / LoopClosing / relocalisation), shared by
+the golden generator (make_golden_n3.py), the CPU test of the oracle and the GPU test of the CUDA path.
+run_n3_cases(backend) returns the raw result arrays of every case; golden file = their sha1 + counts."""
+import numpy as np
+
+from .match_cases import SF, feat_vec, frames, sha  # noqa: F401
+
+
+def proj_points(keys, rng, jitter=1.5, invalid=0.15, level_shift=True):
+    """Map points 'projected' next to the keypoints they came from (position + noise, predicted level =
+    octave or octave + 1, so both ends of the [level-1, level] gate are used)."""
+    from orb_slam3_mac_b200._lib_match import PROJ_POINT_DTYPE
+    n = len(keys)
+    p = np.zeros(n, PROJ_POINT_DTYPE)
+    p["u"] = (keys["x"] + rng.normal(0, jitter, n)).astype(np.float32)
+    p["v"] = (keys["y"] + rng.normal(0, jitter, n)).astype(np.float32)
+    p["ur"] = (p["u"] - rng.uniform(2, 40, n)).astype(np.float32)
+    p["angle"] = keys["angle"]
+    lvl = keys["octave"].astype(np.int32)
+    if level_shift:
+        lvl = np.minimum(lvl + (rng.random(n) < 0.4), 7)
+    p["level"] = lvl
+    p["valid"] = (rng.random(n) >= invalid).astype(np.uint8)
+    return p
+
+
+def n3_inputs(seed=11):
+    from orb_slam3_mac_b200 import synth as S
+    from orb_slam3_mac_b200.matcher import BowSide, Frame
+    rng = np.random.default_rng(seed)
+    (ka, da), (kb, db) = frames(seed, n=1600)
+    # B's keypoints re-observe A's: a[perm-inverse]; recover the correspondence by nearest position
+    ur_b = np.where(rng.random(len(kb)) < 0.5, kb["x"] - rng.uniform(2, 40, len(kb)), -1).astype(np.float32)
+    FA = Frame(ka, da, 752, 480, SF)
+    FB = Frame(kb, db, 752, 480, SF, u_right=ur_b)
+    FBm = Frame(kb, db, 752, 480, SF)
+    # points of A projected into B (B = A shifted by 3 px in x) and the reverse
+    pa = proj_points(ka, rng)
+    pa["u"] += 3.0
+    pb = proj_points(kb, rng)
+    pb["u"] -= 3.0
+    mpd_a = S.flip_bits(da, 0.04, rng)   # map-point descriptors differ a little from the keyframe's
+    mpd_b = S.flip_bits(db, 0.04, rng)
+    fva, fvb = feat_vec(ka, rng), feat_vec(kb, rng)
+    KA, KB = BowSide(ka, da, fva), BowSide(kb, db, fvb)
+    return dict(rng=rng, ka=ka, da=da, kb=kb, db=db, FA=FA, FB=FB, FBm=FBm, pa=pa, pb=pb, mpd_a=mpd_a, mpd_b=mpd_b,
+                KA=KA, KB=KB)
+
+
+def distinctive_case(seed=3):
+    """Observation groups of 0..70 descriptors: noisy copies of one descriptor plus outliers (ties between
+    medians are common, which exercises the first-minimum rule); one large group."""
+    from orb_slam3_mac_b200 import synth as S
+    rng = np.random.default_rng(seed)
+    sizes = list(rng.integers(0, 25, 300)) + [1, 2, 3, 33, 64, 70, 150, 0]
+    rows, ptr = [], [0]
+    for n in sizes:
+        if n:
+            base = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+            g = S.flip_bits(np.repeat(base, n, axis=0), 0.06, rng)
+            out = rng.random(n) < 0.15
+            g[out] = rng.integers(0, 256, (int(out.sum()), 32), dtype=np.uint8)
+            rows.append(g)
+        ptr.append(ptr[-1] + int(n))
+    return np.concatenate(rows), np.array(ptr, np.int32)
+
+
+def run_n3_cases(backend):
+    """backend: object with the oracle's N3 method names.  Returns {case: {name: array or int}}."""
+    I = n3_inputs()
+    rng = np.random.default_rng(99)
+    ka, kb, FA, FB, FBm = I["ka"], I["kb"], I["FA"], I["FB"], I["FBm"]
+    out = {}
+    ok1 = (rng.random(len(ka)) < 0.8).astype(np.uint8)
+    ok2 = (rng.random(len(kb)) < 0.8).astype(np.uint8)
+    for name, check, nu1, nu2 in (("bow_kf", True, -1, -1), ("bow_kf_nocheck_nleft", False, 1200, 1300)):
+        n, m12 = backend.search_by_bow_kf(I["KA"], ok1, I["KB"], ok2, nu1, nu2, 0.8, check)
+        out[name] = {"n": int(n), "m12": m12}
+    taken = (rng.random(len(kb)) < 0.2).astype(np.uint8)
+    for name, th, ratio in (("sim3_proj", 8, 1.0), ("sim3_proj_tight", 4, 0.8)):
+        n, match = backend.search_by_projection_sim3(FBm, I["pa"], I["mpd_a"], th, ratio, taken)
+        out[name] = {"n": int(n), "match": match}
+    for name, th, od, check in (("reloc", 10.0, 100, True), ("reloc_narrow", 3.0, 64, False)):
+        n, match = backend.search_by_projection_reloc(FBm, I["pa"], I["mpd_a"], th, od, check, taken)
+        out[name] = {"n": int(n), "match": match}
+    inv_sigma2 = (1.0 / (SF * SF)).astype(np.float32)
+    n, bi, bd = backend.fuse(FB, I["pa"], I["mpd_a"], 3.0, inv_sigma2, 0)
+    out["fuse_chi2"] = {"n": int(n), "idx": bi, "dist": bd}
+    n, bi, bd = backend.fuse(FBm, I["pa"], I["mpd_a"], 4.0, None, 5000)
+    out["fuse_sim3"] = {"n": int(n), "idx": bi, "dist": bd}
+    n, m12 = backend.search_by_sim3(FA, FBm, I["pa"], I["mpd_a"], I["pb"], I["mpd_b"], 7.5)
+    out["sim3"] = {"n": int(n), "m12": m12}
+    # triangulation: camera-model test as a table / pinhole F12 / coarse
+    has1 = (rng.random(len(ka)) < 0.5).astype(np.uint8)
+    has2 = (rng.random(len(kb)) < 0.5).astype(np.uint8)
+    st1 = (rng.random(len(ka)) < 0.5).astype(np.uint8)
+    st2 = (rng.random(len(kb)) < 0.5).astype(np.uint8)
+    pair_ok = (rng.random((len(ka), len(kb))) < 0.7).astype(np.uint8)
+    ep = np.array([400.0, 250.0], np.float32)
+    ls2 = (SF * SF).astype(np.float32)
+    # F12 of a pure x-translation between identical pinhole cameras: epipolar lines are image rows
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32) * np.float32(0.37)
+    n, m12 = backend.search_for_triangulation(I["KA"], has1, st1, I["KB"], has2, st2, False, ep, SF, pair_ok, None, None, True)
+    out["tri_table"] = {"n": int(n), "m12": m12}
+    n, m12 = backend.search_for_triangulation(I["KA"], has1, None, I["KB"], has2, None, False, ep, SF, None, F12, ls2, True)
+    out["tri_pinhole"] = {"n": int(n), "m12": m12}
+    n, m12 = backend.search_for_triangulation(I["KA"], has1, st1, I["KB"], has2, st2, True, None, None, None, None, None, False)
+    out["tri_coarse_stereo"] = {"n": int(n), "m12": m12}
+    d, gp = distinctive_case()
+    out["distinctive"] = {"best": backend.distinctive_descriptors(d, gp)}
+    return out
+
+
+def digest(res):
+    return {c: {k: (sha(v) if isinstance(v, np.ndarray) else v) for k, v in r.items()} for c, r in res.items()}

@@ -460,3 +460,70 @@ def test_cuda_matcher_and_input_stage_against_committed_goldens():
     ex(bgr, (0, 0))
     assert mc.sha(ex.pyramid_level(0, (480, 752))) == g["rgb_gray"]
     ex.close()
+
+
+class _ProductN3:
+    """The CUDA matcher behind the oracle's N3 method names (tests/golden/n3_cases.py)."""
+
+    def __init__(self):
+        from orb_slam3_mac_b200.matcher import ORBmatcher
+        self.M = ORBmatcher
+
+    def _run(self, ratio, check, f):
+        m = self.M(ratio, check)
+        try:
+            return f(m)
+        finally:
+            m.close()
+
+    def search_by_bow_kf(self, KF1, ok1, KF2, ok2, nu1, nu2, ratio, check):
+        return self._run(ratio, check, lambda m: m.SearchByBoWKF(KF1, ok1, KF2, ok2, nu1, nu2))
+
+    def search_by_projection_sim3(self, KF, pts, d, th, ratio, taken):
+        return self._run(0.8, True, lambda m: m.SearchByProjectionSim3(KF, pts, d, th, ratio, taken))
+
+    def search_by_projection_reloc(self, F, pts, d, th, od, check, taken):
+        return self._run(0.8, check, lambda m: m.SearchByProjectionReloc(F, pts, d, th, od, taken))
+
+    def fuse(self, KF, pts, d, th, inv, off):
+        return self._run(0.8, True, lambda m: m.Fuse(KF, pts, d, th, inv, off))
+
+    def search_by_sim3(self, KF1, KF2, p1, d1, p2, d2, th):
+        return self._run(0.8, True, lambda m: m.SearchBySim3(KF1, KF2, p1, d1, p2, d2, th))
+
+    def search_for_triangulation(self, KF1, has1, st1, KF2, has2, st2, only_stereo, ep, sf2, pair_ok, F12, ls2, check):
+        test = None if pair_ok is None else (lambda a, b: pair_ok[a, b])   # the camera model as a callback
+        return self._run(0.8, check, lambda m: m.SearchForTriangulation(KF1, has1, KF2, has2, st1, st2, only_stereo, ep,
+                                                                        sf2, test, F12, ls2))
+
+    def distinctive_descriptors(self, d, gp):
+        return self._run(0.8, True, lambda m: m.ComputeDistinctiveDescriptors(d, gp))
+
+
+def test_n3_searches_against_committed_goldens_and_oracle(oracle_libs):
+    """SURVEY 8(f) N3 through the C ABI: SearchByBoW(KF,KF), SearchByProjection(pKF,Scw,..) / reloc, Fuse x2,
+    SearchBySim3, SearchForTriangulation (callback, pinhole F12 and coarse forms), ComputeDistinctiveDescriptors.
+    Bit-exact against tests/golden/n3_golden.json (frozen from the CPU oracle) and, array by array, against the
+    oracle itself."""
+    import json
+    import os
+    from tests.golden import n3_cases as nc
+    got = nc.run_n3_cases(_ProductN3())
+    exp = nc.run_n3_cases(oracle_libs.MatchOracle())
+    for case, r in exp.items():
+        for k, v in r.items():
+            g = got[case][k]
+            assert (np.array_equal(g, v) if isinstance(v, np.ndarray) else g == v), (case, k)
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "n3_golden.json")))
+    assert nc.digest(got) == gold
+    assert got["sim3"]["n"] > 300 and got["fuse_chi2"]["n"] > 200 and got["tri_pinhole"]["n"] > 50
+
+
+def test_distinctive_descriptors_edge_cases(matcher):
+    """Empty batch, empty groups, single observations, identical descriptors (all medians 0 -> first row)."""
+    assert len(matcher.ComputeDistinctiveDescriptors(np.zeros((0, 32), np.uint8), np.zeros(1, np.int32))) == 0
+    rng = np.random.default_rng(4)
+    one = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+    d = np.concatenate([one, np.repeat(one, 5, axis=0), rng.integers(0, 256, (2, 32), dtype=np.uint8)])
+    gp = np.array([0, 0, 1, 6, 6, 8], np.int32)
+    assert matcher.ComputeDistinctiveDescriptors(d, gp).tolist() == [-1, 0, 0, -1, 0]

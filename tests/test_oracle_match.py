@@ -108,3 +108,30 @@ def test_oracle_matches_committed_goldens(mo, oracle_libs):
     assert mc.sha(oracle_libs.cvt_gray(oracle_libs.remap_linear(bgr, mx, my), False, 15)) == g["bgr_rect_gray"]
     assert mc.sha(oracle_libs.remap_linear(bgr[:, :, 1].copy(), mx, my)) == g["rect_gray_only"]
     assert mc.sha(oracle_libs.cvt_gray(bgr, True, 15)) == g["rgb_gray"]
+
+
+def test_n3_oracle_matches_committed_goldens(mo):
+    """tests/golden/n3_golden.json: the N3 restatements (SearchByBoW(KF,KF), Sim3 / reloc SearchByProjection, Fuse,
+    SearchBySim3, SearchForTriangulation, ComputeDistinctiveDescriptors) have not drifted from the results the CUDA
+    path is checked against on the GPU box."""
+    import json
+    import os
+    from tests.golden import n3_cases as nc
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "n3_golden.json")))
+    assert nc.digest(nc.run_n3_cases(mo)) == gold
+
+
+def test_distinctive_descriptors_oracle_vs_numpy(mo):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:330-404) restated a second time in numpy:
+    N x N popcount matrix, row sort, element (int)(0.5 * (N - 1)), first minimum."""
+    from tests.golden import n3_cases as nc
+    d, gp = nc.distinctive_case(8)
+    best = mo.distinctive_descriptors(d, gp)
+    for g in range(len(gp) - 1):
+        rows = d[gp[g]:gp[g + 1]]
+        if len(rows) == 0:
+            assert best[g] == -1
+            continue
+        D = np.unpackbits(rows[:, None, :] ^ rows[None, :, :], axis=2).sum(axis=2)
+        med = np.sort(D, axis=1)[:, int(0.5 * (len(rows) - 1))]
+        assert best[g] == int(np.argmin(med))
