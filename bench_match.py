@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Measurement of the matcher rows of SURVEY.md section 8 (M1-M7, N1, N2) -- companion of bench.py,
+"""Measurement of the matcher rows of SURVEY.md section 8 (M1-M7, N1, N2, N3) -- companion of bench.py,
 which measures the extractor and carries the driver's JSON contract.
 
 For every case it prints one JSON line:
@@ -158,6 +158,46 @@ def main():
     report("C4 SearchByBoW", f"{len(k0)} keyframe features vs {len(k1)} frame features over {len(KFs.node_ids)} vocabulary nodes",
            lambda: m.SearchByBoW(KFs, okf, Fs, -1),
            (lambda: mo.search_by_bow(KFs, okf, Fs, -1, 0.8, True)) if mo else None)
+
+    # ---- N3: LocalMapping / LoopClosing / relocalisation searches (C4-sized keyframes) ------------------
+    from tests.golden import n3_cases as nc
+    rp = np.random.default_rng(12)
+    KF1, KF2 = Frame(k0, d0, 1280, 720, SF), Frame(k1, d1, 1280, 720, SF)
+    p1, p2 = nc.proj_points(k0, rp), nc.proj_points(k1, rp)
+    md1, md2 = S.flip_bits(d0, 0.04, rp), S.flip_bits(d1, 0.04, rp)
+    ok1, ok2 = np.ones(len(k0), np.uint8), np.ones(len(k1), np.uint8)
+    report("C4 SearchByBoW(KF,KF)", f"{len(k0)} x {len(k1)} keyframe features over {len(KFs.node_ids)} vocabulary nodes",
+           lambda: m.SearchByBoWKF(KFs, ok1, Fs, ok2),
+           (lambda: mo.search_by_bow_kf(KFs, ok1, Fs, ok2, -1, -1, 0.8, True)) if mo else None)
+    report("C4 SearchByProjection(pKF,Scw)", f"{len(p1)} projected map points vs {len(k1)} keypoints, th=8",
+           lambda: m.SearchByProjectionSim3(KF2, p1, md1, 8, 1.0),
+           (lambda: mo.search_by_projection_sim3(KF2, p1, md1, 8, 1.0)) if mo else None)
+    report("C4 SearchByProjection reloc", f"{len(p1)} keyframe map points vs {len(k1)} keypoints, th=10, ORBdist=100",
+           lambda: m.SearchByProjectionReloc(KF2, p1, md1, 10.0, 100),
+           (lambda: mo.search_by_projection_reloc(KF2, p1, md1, 10.0, 100, True)) if mo else None)
+    inv2 = (1.0 / (SF * SF)).astype(np.float32)
+    report("C4 Fuse", f"{len(p1)} map points into a keyframe of {len(k1)} keypoints, th=3, chi-square gates",
+           lambda: m.Fuse(KF2, p1, md1, 3.0, inv2),
+           (lambda: mo.fuse(KF2, p1, md1, 3.0, inv2, 0)) if mo else None)
+    report("C4 SearchBySim3", f"{len(p1)} + {len(p2)} projected map points, both directions, th=7.5",
+           lambda: m.SearchBySim3(KF1, KF2, p1, md1, p2, md2, 7.5),
+           (lambda: mo.search_by_sim3(KF1, KF2, p1, md1, p2, md2, 7.5)) if mo else None)
+    F12 = (np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32) * np.float32(0.37))
+    ls2 = (SF * SF).astype(np.float32)
+    no1, no2 = np.zeros(len(k0), np.uint8), np.zeros(len(k1), np.uint8)
+    ep = np.array([640.0, 360.0], np.float32)
+    report("C4 SearchForTriangulation", f"{len(k0)} x {len(k1)} untracked features, pinhole epipolar test",
+           lambda: m.SearchForTriangulation(KFs, no1, Fs, no2, None, None, False, ep, SF, None, F12, ls2),
+           (lambda: mo.search_for_triangulation(KFs, no1, None, Fs, no2, None, False, ep, SF, None, F12, ls2, True)) if mo else None)
+    rs = np.random.default_rng(6)   # observation counts of a mature map: mostly 2..25, a tail up to 150
+    sizes = list(rs.integers(2, 26, 300)) + [40, 64, 100, 150]
+    dd, gp = nc.distinctive_case(5, sizes)
+    reps_g = 40   # ~12 k map points per call
+    dd = np.concatenate([dd] * reps_g)
+    gp = np.concatenate([[0]] + [gp[1:] + k * gp[-1] for k in range(reps_g)]).astype(np.int32)
+    report("ComputeDistinctiveDescriptors", f"{len(gp) - 1} map points, {len(dd)} observed descriptors (2..150 per point)",
+           lambda: m.ComputeDistinctiveDescriptors(dd, gp),
+           (lambda: mo.distinctive_descriptors(dd, gp)) if mo else None)
 
     # ---- N2 alone: candidate lists without distances ---------------------------------------------------
     q = np.zeros(len(mps), AREA_QUERY_DTYPE)

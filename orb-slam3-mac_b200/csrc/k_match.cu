@@ -446,12 +446,14 @@ cudaError_t orbm_launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStre
 }
 
 // ---- N3: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:330-404), batched --------------
-// One warp per map point (group of N observed descriptors).  Lane i walks rows i, i+32, ..: the
-// median of row i = the k-th smallest (k = (int)(0.5 * (N - 1)), the reference's index into the
-// sorted row, which includes d(i,i) = 0) of d(i, .), found by a 9-step binary search on the value
-// (distances are integers in [0, 256]) with the row's distances recomputed per step from L1 -- no
-// N x N matrix is stored.  The first row with the least median wins (packed key median << 20 | i,
-// warp min), as the reference's strict '<' scan does.
+// One warp per map point (group of N observed descriptors).  The median of row i is the k-th smallest
+// (k = (int)(0.5 * (N - 1)), the reference's index into the sorted row, which includes d(i,i) = 0) of
+// d(i, .).  N <= 256: the warp takes one row at a time, lane j holds d(i, j), d(i, j + 32), .. in
+// registers (each distance computed once), and the k-th smallest comes from a 9-step binary search on
+// the value (distances are integers in [0, 256]) with one REDUX per step.  Larger groups: lane i
+// walks rows i, i + 32, .. and recomputes its row per search step from L1 (no N x N matrix is ever
+// stored).  The first row with the least median wins, as the reference's strict '<' scan does.
+#define DIST_CHUNKS 8
 __global__ void __launch_bounds__(128)
 k_distinctive(const uint4* __restrict__ desc, const int32_t* __restrict__ group_ptr, int ngroups,
               int32_t* __restrict__ best) {
@@ -465,6 +467,34 @@ k_distinctive(const uint4* __restrict__ desc, const int32_t* __restrict__ group_
     }
     const uint4* D = desc + 2 * (size_t)base;
     const int k = (int)(0.5 * (double)(N - 1));
+    if (N <= 32 * DIST_CHUNKS) {
+        const int nch = (N + 31) >> 5;
+        int bestMed = 0x7fffffff, bestIdx = 0;
+        for (int i = 0; i < N; ++i) {
+            const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
+            int d[DIST_CHUNKS];
+#pragma unroll
+            for (int c = 0; c < DIST_CHUNKS; ++c) {
+                const int j = c * 32 + lane;
+                d[c] = (c < nch && j < N) ? hamming256(a0, a1, D + 2 * j) : 0x7fff;
+            }
+            int lo = 0, hi = 256;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                int cnt = 0;
+#pragma unroll
+                for (int c = 0; c < DIST_CHUNKS; ++c) cnt += d[c] <= mid ? 1 : 0;
+                cnt = __reduce_add_sync(ORBX_FULL, cnt);
+                if (cnt >= k + 1) hi = mid; else lo = mid + 1;
+            }
+            if (lo < bestMed) {
+                bestMed = lo;
+                bestIdx = i;
+            }
+        }
+        if (lane == 0) best[g] = bestIdx;
+        return;
+    }
     uint32_t key = 0xffffffffu;
     for (int i = lane; i < N; i += 32) {
         const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);

@@ -47,12 +47,14 @@ def n3_inputs(seed=11):
                 KA=KA, KB=KB)
 
 
-def distinctive_case(seed=3):
+def distinctive_case(seed=3, sizes=None):
     """Observation groups of 0..70 descriptors: noisy copies of one descriptor plus outliers (ties between
-    medians are common, which exercises the first-minimum rule); one large group."""
+    medians are common, which exercises the first-minimum rule); groups on both sides of the 256-row limit
+    of the register path."""
     from orb_slam3_mac_b200 import synth as S
     rng = np.random.default_rng(seed)
-    sizes = list(rng.integers(0, 25, 300)) + [1, 2, 3, 33, 64, 70, 150, 0]
+    if sizes is None:
+        sizes = list(rng.integers(0, 25, 300)) + [1, 2, 3, 33, 64, 70, 150, 0, 256, 257, 300]
     rows, ptr = [], [0]
     for n in sizes:
         if n:
