@@ -25,6 +25,7 @@
  *     orbm_search_by_sim3                SearchBySim3                       :1739-1963
  *     orbm_search_for_triangulation      SearchForTriangulation x2          :969-1210, 1212-1401
  *     orbm_distinctive_descriptors       MapPoint::ComputeDistinctiveDescriptors  src/MapPoint.cc:330-404
+ *     orbm_vocab_create / orbm_bow_transform   DBoW2 transform (Frame::ComputeBoW)  src/Frame.cc:729-736
  *     candidate generation               Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea
  *                                        src/Frame.cc:377-408, 716-726, 645-714
  *
@@ -305,6 +306,29 @@ int orbm_search_for_triangulation(orbm_context* c, const orbm_bow_view* KF1, con
  * device (one warp per map point). */
 int orbm_distinctive_descriptors(orbm_context* c, const uint8_t* desc, const int32_t* group_ptr, int ngroups,
                                  int32_t* best);
+
+/* ---- DBoW2 transform: Frame::ComputeBoW src/Frame.cc:729-736, KeyFrame::ComputeBoW ----
+ * DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> as POD (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h):
+ * node i = m_nodes[i] (node 0 = root); its children are child_ids[child_ptr[i] .. child_ptr[i+1]) in the order of
+ * Node::children; a node without children is a word with weight[i] (Node::weight) and word_id[i].  node_desc:
+ * n_nodes x 32 (Node::descriptor; the root's row is unused).  L = m_L.  weighting: 0 TF_IDF, 1 TF, 2 IDF,
+ * 3 BINARY (WeightingType); norm: what ScoringObject::mustNormalize returns -- 0 none, 1 L1, 2 L2 (ORBvoc.txt:
+ * k = 10, L = 6, TF_IDF, L1_NORM -> weighting 0, norm 1).  The tree stays resident on the context's device. */
+typedef struct orbm_vocabulary orbm_vocabulary;
+int orbm_vocab_create(orbm_context* c, int n_nodes, const int32_t* child_ptr, const uint32_t* child_ids,
+                      const uint8_t* node_desc, const double* weight, const uint32_t* word_id, int L, int weighting,
+                      int norm, orbm_vocabulary** out);
+int orbm_vocab_destroy(orbm_vocabulary* v);
+
+/* transform(features, v, fv, levelsup), TemplatedVocabulary.h:1139-1217: every feature descends the tree on the
+ * device (first child with the least FORB::distance per level, :1246-1266); the BowVector (word id -> summed
+ * weight, then normalised) and the FeatureVector (node at level L - levelsup -> feature indices) are assembled in
+ * feature order as the reference does, so the double sums are identical.  Outputs (capacity n each, fv_ptr n + 1):
+ * bow_ids ascending with bow_vals, *n_words; fv_node_ids ascending with the CSR fv_ptr / fv_items, *n_fv_nodes --
+ * the layout orbm_bow_view takes. */
+int orbm_bow_transform(orbm_context* c, const orbm_vocabulary* v, const uint8_t* desc, int n, int levelsup,
+                       uint32_t* bow_ids, double* bow_vals, int32_t* n_words, uint32_t* fv_node_ids,
+                       int32_t* fv_ptr, uint32_t* fv_items, int32_t* n_fv_nodes);
 
 /* SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), src/ORBmatcher.cc:710-825.
  * prev_matched: F1.n (x, y) pairs, in/out.  matches12: F1.n ints, out.  Returns nmatches. */

@@ -1291,4 +1291,81 @@ int orbo_distinctive_descriptors(const uint8_t* desc, const int32_t* group_ptr, 
     return 0;
 }
 
+// DBoW2 TemplatedVocabulary<FORB>::transform(features, v, fv, levelsup) with its per-feature descent
+// (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1139-1217, 1230-1275; BowVector.cpp addWeight / addIfNotExist /
+// normalize; FeatureVector.cpp addFeature) on the POD vocabulary of orbm_vocab_create.
+int orbo_bow_transform(int n_nodes, const int32_t* child_ptr, const uint32_t* child_ids, const uint8_t* node_desc,
+                       const double* weight, const uint32_t* word_id_of, int m_L, int m_weighting, int norm_kind,
+                       const uint8_t* features, int n, int levelsup, uint32_t* bow_ids, double* bow_vals,
+                       int32_t* n_words, uint32_t* fv_node_ids, int32_t* fv_ptr, uint32_t* fv_items,
+                       int32_t* n_fv_nodes) {
+    std::map<unsigned int, double> v;                       // BowVector
+    std::map<unsigned int, std::vector<unsigned int> > fv;  // FeatureVector
+    const bool must = norm_kind != 0;
+    for (int i_feature = 0; i_feature < n; ++i_feature) {
+        const uint8_t* feature = features + (size_t)i_feature * 32;
+        unsigned int nid = 0;
+        const int nid_level = m_L - levelsup;
+        unsigned int final_id = 0;
+        int current_level = 0;
+        do {
+            ++current_level;
+            const uint32_t* nodes = child_ids + child_ptr[final_id];
+            const int nchild = child_ptr[final_id + 1] - child_ptr[final_id];
+            final_id = nodes[0];
+            double best_d = descriptor_distance(feature, node_desc + (size_t)final_id * 32);
+            for (int c = 1; c < nchild; ++c) {
+                const unsigned int id = nodes[c];
+                double d = descriptor_distance(feature, node_desc + (size_t)id * 32);
+                if (d < best_d) {
+                    best_d = d;
+                    final_id = id;
+                }
+            }
+            if (current_level == nid_level) nid = final_id;
+        } while (child_ptr[final_id + 1] > child_ptr[final_id]);
+        const unsigned int id = word_id_of[final_id];
+        const double w = weight[final_id];
+        if (w > 0) {
+            std::map<unsigned int, double>::iterator vit = v.lower_bound(id);
+            if (vit != v.end() && !(id < vit->first)) {
+                if (m_weighting == 0 || m_weighting == 1) vit->second += w;   // addWeight; addIfNotExist keeps it
+            } else {
+                v.insert(vit, std::make_pair(id, w));
+            }
+            fv[nid].push_back(i_feature);
+        }
+    }
+    if ((m_weighting == 0 || m_weighting == 1) && !v.empty() && !must) {
+        const double nd = v.size();
+        for (std::map<unsigned int, double>::iterator vit = v.begin(); vit != v.end(); vit++) vit->second /= nd;
+    }
+    if (must) {
+        double norm = 0.0;
+        if (norm_kind == 1) {
+            for (std::map<unsigned int, double>::iterator it = v.begin(); it != v.end(); ++it) norm += fabs(it->second);
+        } else {
+            for (std::map<unsigned int, double>::iterator it = v.begin(); it != v.end(); ++it) norm += it->second * it->second;
+            norm = sqrt(norm);
+        }
+        if (norm > 0.0)
+            for (std::map<unsigned int, double>::iterator it = v.begin(); it != v.end(); ++it) it->second /= norm;
+    }
+    int k = 0;
+    for (std::map<unsigned int, double>::iterator it = v.begin(); it != v.end(); ++it, ++k) {
+        bow_ids[k] = it->first;
+        bow_vals[k] = it->second;
+    }
+    *n_words = k;
+    int a = 0, items = 0;
+    fv_ptr[0] = 0;
+    for (std::map<unsigned int, std::vector<unsigned int> >::iterator it = fv.begin(); it != fv.end(); ++it) {
+        fv_node_ids[a] = it->first;
+        for (size_t j = 0; j < it->second.size(); ++j) fv_items[items++] = it->second[j];
+        fv_ptr[++a] = items;
+    }
+    *n_fv_nodes = a;
+    return 0;
+}
+
 }  // extern "C"

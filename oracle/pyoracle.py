@@ -334,6 +334,21 @@ class MatchOracle:
         self.lib.orbo_distinctive_descriptors(self._p(d), self._p(gp), len(gp) - 1, self._p(best))
         return best
 
+    def bow_transform(self, voc, desc, levelsup):
+        """voc: orb_slam3_mac_b200.matcher.Vocabulary (host arrays only).  Returns (bow_ids, bow_vals,
+        fv_node_ids, fv_ptr, fv_items)."""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(d)
+        bi, bv = np.zeros(max(n, 1), np.uint32), np.zeros(max(n, 1), np.float64)
+        fn, fp, fi = np.zeros(max(n, 1), np.uint32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.uint32)
+        nw, nf = C.c_int32(), C.c_int32()
+        self.lib.orbo_bow_transform(len(voc.weight), self._p(voc.child_ptr), self._p(voc.child_ids), self._p(voc.node_desc),
+                                    self._p(voc.weight), self._p(voc.word_id), int(voc.L), int(voc.weighting),
+                                    int(voc.norm), self._p(d), n, int(levelsup), self._p(bi), self._p(bv), C.byref(nw),
+                                    self._p(fn), self._p(fp), self._p(fi), C.byref(nf))
+        return bi[:nw.value].copy(), bv[:nw.value].copy(), fn[:nf.value].copy(), fp[:nf.value + 1].copy(), \
+            fi[:fp[nf.value]].copy()
+
     def knn2(self, q, t):
         q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
         t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)

@@ -67,6 +67,10 @@ ORBM_SYMBOLS = {
     "orbm_search_for_triangulation": (_i, [_vp, C.POINTER(BowView), _vp, _vp, C.POINTER(BowView), _vp, _vp, _i, _vp,
                                            _vp, _i, _vp, _vp, _vp, _vp, _i, _vp]),
     "orbm_distinctive_descriptors": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "orbm_vocab_create": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, C.POINTER(_vp)]),
+    "orbm_vocab_destroy": (_i, [_vp]),
+    "orbm_bow_transform": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, C.POINTER(C.c_int32), _vp, _vp, _vp,
+                                C.POINTER(C.c_int32)]),
     "orbm_area_candidates": (_i, [_vp, _fv, _vp, _i, _vp, _i, _vp, _vp, _vp, _i]),
     "orbm_last_device_ms": (_i, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_longlong)]),
     "orbm_measure_popc_peak": (_i, [_vp, C.POINTER(C.c_double)]),

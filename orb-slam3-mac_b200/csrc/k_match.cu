@@ -519,3 +519,50 @@ cudaError_t orbm_launch_distinctive(const uint8_t* desc, const int32_t* group_pt
     k_distinctive<<<(ngroups + 3) / 4, 128, 0, st>>>(reinterpret_cast<const uint4*>(desc), group_ptr, ngroups, best);
     return cudaGetLastError();
 }
+
+// ---- N4 (second half): DBoW2 TemplatedVocabulary<FORB>::transform, the tree descent ---------------
+// (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1230-1275, called per feature by transform(features,
+// v, fv, levelsup) :1139-1217 from Frame::ComputeBoW, src/Frame.cc:729-736).  One warp per feature:
+// at every level the lanes take the node's children (k = 10 for ORBvoc: one round), FORB::distance =
+// the same 256-bit popcount, and the first child with the least distance wins (packed key
+// distance << 16 | position in Node::children, warp min = the reference's strict '<' scan).  The
+// vocabulary (child lists + 32-byte node descriptors, ~36 MB for the 10^6-word ORBvoc) stays resident in
+// HBM/L2.  leaf[i] = final node, nid[i] = the node passed at level L - levelsup (0 when that level is
+// <= 0 or the branch ends above it).
+__global__ void __launch_bounds__(128)
+k_bow_descend(const uint4* __restrict__ feat, int n, const int32_t* __restrict__ child_ptr,
+              const uint32_t* __restrict__ child_ids, const uint4* __restrict__ node_desc, int nid_level,
+              int32_t* __restrict__ leaf, int32_t* __restrict__ nid_out) {
+    const int i = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
+    if (i >= n) return;
+    const int lane = orbx_lane();
+    const uint4 a0 = __ldg(feat + 2 * i), a1 = __ldg(feat + 2 * i + 1);
+    uint32_t node = 0, nid = 0;
+    int level = 0;
+    for (;;) {
+        const int cp = __ldg(child_ptr + node), ce = __ldg(child_ptr + node + 1);
+        if (ce <= cp) break;   // leaf: a word
+        ++level;
+        uint32_t key = 0xffffffffu;
+        for (int r = lane; r < ce - cp; r += 32) {
+            const uint32_t id = __ldg(child_ids + cp + r);
+            key = min(key, ((uint32_t)hamming256(a0, a1, node_desc + 2 * (size_t)id) << 16) | (uint32_t)r);
+        }
+        key = __reduce_min_sync(ORBX_FULL, key);
+        node = __ldg(child_ids + cp + (int)(key & 0xffffu));
+        if (level == nid_level) nid = node;
+    }
+    if (lane == 0) {
+        leaf[i] = (int32_t)node;
+        nid_out[i] = (int32_t)nid;
+    }
+}
+
+cudaError_t orbm_launch_bow_descend(const uint8_t* feat, int n, const int32_t* child_ptr, const uint32_t* child_ids,
+                                    const uint8_t* node_desc, int nid_level, int32_t* leaf, int32_t* nid,
+                                    cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    k_bow_descend<<<(n + 3) / 4, 128, 0, st>>>(reinterpret_cast<const uint4*>(feat), n, child_ptr, child_ids,
+                                                reinterpret_cast<const uint4*>(node_desc), nid_level, leaf, nid);
+    return cudaGetLastError();
+}

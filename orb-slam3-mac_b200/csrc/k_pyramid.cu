@@ -331,6 +331,9 @@ k_resize_rows_async(const __grid_constant__ RzArgs A, int n8) {
     else rz_walk<4>(A, band, n8 * 256 + (wx - n8) * 128, ring);
 }
 
+#ifndef RZ_MIN_WARPS
+#define RZ_MIN_WARPS (148 * 16)
+#endif
 void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes, cudaStream_t st, int* launches) {
     for (int l = 1; l < P.nlevels; ++l) {
         const OrbxLevel& D = P.lvl[l];
@@ -350,7 +353,7 @@ void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, in
             // output rows per warp: RZ_ROWS when the launch fills the GPU anyway; small batches take
             // shorter bands so that a level of one frame still spreads over the SMs (latency path)
             A.rows = RZ_ROWS;
-            while (A.rows > 2 && (long long)nframes * ((D.w + 255) / 256) * ((D.h + A.rows - 1) / A.rows) < 148 * 16)
+            while (A.rows > 2 && (long long)nframes * ((D.w + 255) / 256) * ((D.h + A.rows - 1) / A.rows) < RZ_MIN_WARPS)
                 A.rows >>= 1;
             A.nbands = (D.h + A.rows - 1) / A.rows;
             const bool aligned = ((uintptr_t)A.src % 16 == 0) && (A.spitch % 16 == 0) && (A.src_fstride % 16 == 0);

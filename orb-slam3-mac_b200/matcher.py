@@ -76,6 +76,20 @@ class BowSide:
                        self.node_ids.ctypes.data, self.node_ptr.ctypes.data, self.node_items.ctypes.data)
 
 
+class Vocabulary:
+    """DBoW2::TemplatedVocabulary<FORB> as POD (include/orbm.h, orbm_vocab_create): children as CSR in the order of
+    Node::children, node descriptors, word weights and ids; weighting 0 = TF_IDF, norm 1 = L1 (ORBvoc)."""
+
+    def __init__(self, child_ptr, child_ids, node_desc, weight, word_id, L, weighting=0, norm=1):
+        self.child_ptr = np.ascontiguousarray(child_ptr, np.int32)
+        self.child_ids = np.ascontiguousarray(child_ids, np.uint32)
+        self.node_desc = np.ascontiguousarray(node_desc, np.uint8).reshape(-1, 32)
+        self.weight = np.ascontiguousarray(weight, np.float64)
+        self.word_id = np.ascontiguousarray(word_id, np.uint32)
+        self.L, self.weighting, self.norm = int(L), int(weighting), int(norm)
+        assert len(self.child_ptr) == len(self.weight) + 1 == len(self.node_desc) + 1
+
+
 class RightHalf:
     """The right camera's half of a fisheye stereo Frame (Nleft != -1): mvKeysRight, the descriptor rows
     Nleft.., mvLeftToRightMatch, mvRightToLeftMatch."""
@@ -382,3 +396,29 @@ class ORBmatcher:
         check(self.lib.orbm_distinctive_descriptors(self.ctx, d.ctypes.data, gp.ctypes.data, len(gp) - 1,
                                                     best.ctypes.data))
         return best
+
+    # ---- DBoW2 transform ---------------------------------------------------------------
+    def load_vocabulary(self, voc: Vocabulary):
+        """Uploads the vocabulary tree to the matcher's device (orbm_vocab_create); returns an opaque handle."""
+        h = C.c_void_p()
+        check(self.lib.orbm_vocab_create(self.ctx, len(voc.weight), voc.child_ptr.ctypes.data, voc.child_ids.ctypes.data,
+                                         voc.node_desc.ctypes.data, voc.weight.ctypes.data, voc.word_id.ctypes.data,
+                                         voc.L, voc.weighting, voc.norm, C.byref(h)))
+        return h
+
+    def free_vocabulary(self, h):
+        self.lib.orbm_vocab_destroy(h)
+
+    def transform(self, voc_handle, desc, levelsup=4):
+        """mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4), src/Frame.cc:729-736.
+        Returns (bow_ids, bow_vals, fv_node_ids, fv_ptr, fv_items)."""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(d)
+        bi, bv = np.zeros(max(n, 1), np.uint32), np.zeros(max(n, 1), np.float64)
+        fn, fp, fi = np.zeros(max(n, 1), np.uint32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.uint32)
+        nw, nf = C.c_int32(), C.c_int32()
+        check(self.lib.orbm_bow_transform(self.ctx, voc_handle, d.ctypes.data, n, int(levelsup), bi.ctypes.data,
+                                          bv.ctypes.data, C.byref(nw), fn.ctypes.data, fp.ctypes.data, fi.ctypes.data,
+                                          C.byref(nf)))
+        return bi[:nw.value].copy(), bv[:nw.value].copy(), fn[:nf.value].copy(), fp[:nf.value + 1].copy(), \
+            fi[:fp[nf.value]].copy()

@@ -110,8 +110,71 @@ def run_n3_cases(backend):
     out["tri_coarse_stereo"] = {"n": int(n), "m12": m12}
     d, gp = distinctive_case()
     out["distinctive"] = {"best": backend.distinctive_descriptors(d, gp)}
+    # N4: DBoW2 transform on a synthetic vocabulary (ragged and regular trees, every weighting / norm branch)
+    for name, ragged, L, levelsup, weighting, norm in (("bow_ragged_l2", True, 4, 2, 0, 1), ("bow_root", True, 4, 4, 0, 1),
+                                                       ("bow_regular_tf", False, 3, 1, 1, 0),
+                                                       ("bow_binary_l2", False, 3, 2, 3, 2), ("bow_idf", True, 4, 3, 2, 1)):
+        voc = synthetic_vocabulary(21 + L, 10, L, ragged)
+        voc.weighting, voc.norm = weighting, norm
+        f = bow_features(voc, 1500)
+        bi, bv, fn, fp, fi = backend.bow_transform(voc, f, levelsup)
+        out[name] = {"n_words": int(len(bi)), "n_nodes": int(len(fn)), "bow_ids": bi, "bow_vals": bv, "fv_nodes": fn,
+                     "fv_ptr": fp, "fv_items": fi}
     return out
 
 
 def digest(res):
     return {c: {k: (sha(v) if isinstance(v, np.ndarray) else v) for k, v in r.items()} for c, r in res.items()}
+
+
+def synthetic_vocabulary(seed=21, k=10, L=4, ragged=True):
+    """A DBoW2-shaped vocabulary (ORBvoc.txt is not available offline): k-ary tree of depth L built breadth first as
+    DBoW2 numbers its nodes, child descriptors = parent's with bits flipped (so descents are decided by small
+    distance differences and ties occur), random idf weights with a few stopped words (weight 0).  ragged: some
+    inner nodes have fewer than k children and some branches end early (words above level L)."""
+    from orb_slam3_mac_b200 import synth as S
+    from orb_slam3_mac_b200.matcher import Vocabulary
+    rng = np.random.default_rng(seed)
+    desc = [rng.integers(0, 256, 32, dtype=np.uint8)]
+    children = [[]]
+    level = [0]
+    frontier = [0]
+    for lv in range(1, L + 1):
+        nxt = []
+        for p in frontier:
+            if ragged and lv > 1 and rng.random() < 0.05:
+                continue   # p stays a leaf: a word above the last level
+            nc = k if not ragged or rng.random() < 0.8 else int(rng.integers(1, k))
+            for _ in range(nc):
+                nid = len(desc)
+                desc.append(S.flip_bits(desc[p][None, :], 0.12 if lv > 1 else 0.5, rng)[0])
+                children.append([])
+                level.append(lv)
+                children[p].append(nid)
+                nxt.append(nid)
+        frontier = nxt
+    n = len(desc)
+    child_ptr = np.zeros(n + 1, np.int32)
+    ids = []
+    for i in range(n):
+        ids.extend(children[i])
+        child_ptr[i + 1] = len(ids)
+    weight = np.zeros(n, np.float64)
+    word_id = np.zeros(n, np.uint32)
+    leaves = [i for i in range(n) if not children[i]]
+    for w, i in enumerate(leaves):
+        word_id[i] = w
+        weight[i] = 0.0 if rng.random() < 0.03 else float(rng.uniform(0.5, 9.0))
+    return Vocabulary(child_ptr, np.array(ids, np.uint32), np.stack(desc), weight, word_id, L)
+
+
+def bow_features(voc, n, seed=5):
+    """Descriptors near random vocabulary nodes (plus pure noise), duplicates included so words repeat."""
+    from orb_slam3_mac_b200 import synth as S
+    rng = np.random.default_rng(seed)
+    pick = rng.integers(1, len(voc.node_desc), n)
+    d = S.flip_bits(voc.node_desc[pick], 0.05, rng)
+    noise = rng.random(n) < 0.1
+    d[noise] = rng.integers(0, 256, (int(noise.sum()), 32), dtype=np.uint8)
+    d[n // 2:n // 2 + 40] = d[:40]
+    return d

@@ -499,10 +499,20 @@ class _ProductN3:
     def distinctive_descriptors(self, d, gp):
         return self._run(0.8, True, lambda m: m.ComputeDistinctiveDescriptors(d, gp))
 
+    def bow_transform(self, voc, desc, levelsup):
+        def f(m):
+            h = m.load_vocabulary(voc)
+            try:
+                return m.transform(h, desc, levelsup)
+            finally:
+                m.free_vocabulary(h)
+        return self._run(0.8, True, f)
+
 
 def test_n3_searches_against_committed_goldens_and_oracle(oracle_libs):
     """SURVEY 8(f) N3 through the C ABI: SearchByBoW(KF,KF), SearchByProjection(pKF,Scw,..) / reloc, Fuse x2,
-    SearchBySim3, SearchForTriangulation (callback, pinhole F12 and coarse forms), ComputeDistinctiveDescriptors.
+    SearchBySim3, SearchForTriangulation (callback, pinhole F12 and coarse forms), ComputeDistinctiveDescriptors, and the
+    DBoW2 transform of N4 (BowVector doubles bit-identical).
     Bit-exact against tests/golden/n3_golden.json (frozen from the CPU oracle) and, array by array, against the
     oracle itself."""
     import json
