@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Measurement of the matcher rows of SURVEY.md section 8 (M1-M7, N1, N2, N3) -- companion of bench.py,
+"""Measurement of the matcher rows of SURVEY.md section 8 (M1-M7, N1, N2, N3, N4's DBoW2 transform) -- companion of bench.py,
 which measures the extractor and carries the driver's JSON contract.
 
 For every case it prints one JSON line:
@@ -198,6 +198,31 @@ def main():
     report("ComputeDistinctiveDescriptors", f"{len(gp) - 1} map points, {len(dd)} observed descriptors (2..150 per point)",
            lambda: m.ComputeDistinctiveDescriptors(dd, gp),
            (lambda: mo.distinctive_descriptors(dd, gp)) if mo else None)
+
+    # ---- N4: DBoW2 transform with an ORBvoc-shaped vocabulary (k = 10, L = 6: 1.1 M nodes, 36 MB of descriptors) --
+    from orb_slam3_mac_b200.matcher import Vocabulary
+    rv = np.random.default_rng(31)
+    K, LV = 10, 6
+    descs = [rv.integers(0, 256, (1, 32), dtype=np.uint8)]
+    for lv in range(1, LV + 1):   # breadth first, as DBoW2 numbers its nodes
+        par = np.repeat(descs[-1], K, axis=0)
+        flip = np.packbits(rv.random((len(par), 256)) < (0.5 if lv == 1 else 0.12), axis=1)
+        descs.append(par ^ flip)
+    nd = np.concatenate(descs)
+    n_nodes = len(nd)
+    first = np.cumsum([0] + [len(d) for d in descs])      # first node id of each level
+    n_inner = int(first[LV])
+    child_ptr = np.concatenate([np.arange(n_inner + 1) * K, np.full(n_nodes - n_inner, n_inner * K)]).astype(np.int32)
+    child_ids = np.arange(1, n_nodes, dtype=np.uint32)     # node i's children are 1 + K i .. K + K i
+    weight = np.zeros(n_nodes)
+    weight[n_inner:] = rv.uniform(0.5, 9.0, n_nodes - n_inner)
+    word_id = np.zeros(n_nodes, np.uint32)
+    word_id[n_inner:] = np.arange(n_nodes - n_inner)
+    voc = Vocabulary(child_ptr, child_ids, nd, weight, word_id, LV)
+    vh = m.load_vocabulary(voc)
+    report("C4 DBoW2 transform", f"{len(d1)} descriptors through a k={K}, L={LV} vocabulary ({n_nodes} nodes), levelsup 4",
+           lambda: m.transform(vh, d1, 4), (lambda: mo.bow_transform(voc, d1, 4)) if mo else None)
+    m.free_vocabulary(vh)
 
     # ---- N2 alone: candidate lists without distances ---------------------------------------------------
     q = np.zeros(len(mps), AREA_QUERY_DTYPE)
