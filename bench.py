@@ -462,9 +462,15 @@ def run_ours(args):
         _lib.check(lib.orbx_create(C.byref(conf1), C.byref(h1)))
         s50, _, _ = p50(h1)
         lib.orbx_destroy(h1)
-        lat = {"p50_us": g50, "p90_us": g90, "samples": ns, "p50_us_stream_launches": s50,
+        conf1 = _lib.OrbxConfig(nf, 1.2, 8, 20, 7, w, h, 1, 1, local, 4)   # ORBX_FLAG_NO_FORK
+        _lib.check(lib.orbx_create(C.byref(conf1), C.byref(h1)))
+        c50, _, _ = p50(h1)
+        lib.orbx_destroy(h1)
+        lat = {"p50_us": g50, "p90_us": g90, "samples": ns, "p50_us_graph_chain": c50, "p50_us_stream_launches": s50,
                "what": "orbx_extract, one frame, pinned host in/out, synchronous (H2D + CUDA-graph replay of the "
-                       "kernel sequence + D2H); p50_us_stream_launches = same with plain stream launches"}
+                       "kernels + D2H); the graph forks one branch per pyramid level (FAST + quadtree of level l "
+                       "start as soon as level l exists); p50_us_graph_chain = the same kernels captured as one "
+                       "chain, p50_us_stream_launches = plain stream launches"}
 
     # ---- max over ranks ------------------------------------------------------------------------------
     t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=f"cuda:{local}")

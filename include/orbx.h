@@ -75,6 +75,7 @@ typedef struct orbx_config {
 #define ORBX_FLAG_NONE 0u
 #define ORBX_FLAG_STAGE_TIMING 1u /* record CUDA events at the stage boundaries (bench.py) */
 #define ORBX_FLAG_NO_GRAPH 2u     /* never replay a CUDA graph for small batches (A/B measurements) */
+#define ORBX_FLAG_NO_FORK 4u      /* capture that graph as one chain instead of one branch per pyramid level */
 #define ORBX_GRAPH_MAX_FRAMES 4   /* batches up to this size replay a captured graph of the kernels */
 
 typedef struct orbx_handle orbx_handle;

@@ -252,11 +252,11 @@ __device__ __forceinline__ int fast_nms_emit(const FastWarpSmem& s, int sp, int 
 __global__ void __launch_bounds__(FAST_WARPS * 32, FAST_MINB)
 k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t* __restrict__ pyr,
              uint32_t* __restrict__ cellcnt, uint32_t* __restrict__ cellkeys, int tile_pitch,
-             int score_pitch, int warp_smem_bytes, int score_off, int src16) {
+             int score_pitch, int warp_smem_bytes, int score_off, int src16, int cell_base, int cell_end) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int warp = orbx_warp(), lane = orbx_lane();
-    const int g = blockIdx.x * FAST_WARPS + warp;  // global cell index inside the frame
-    if (g >= P.cells_total) return;
+    const int g = cell_base + blockIdx.x * FAST_WARPS + warp;  // global cell index inside the frame
+    if (g >= cell_end) return;
     const int frame = blockIdx.y;
 
     // the cell's record (built once per shape on the host, ORBextractor.cc:787-804)
@@ -373,13 +373,16 @@ cudaError_t orbx_configure_fast(const OrbxPlan& P) {
 }
 
 cudaError_t orbx_launch_fast(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr, uint32_t* cellcnt,
-                             uint32_t* cellkeys, int nframes, cudaStream_t st, int* launches) {
+                             uint32_t* cellkeys, int nframes, cudaStream_t st, int* launches, int level) {
     int tp, sp, wb, so;
     orbx_fast_smem_layout(P, &tp, &sp, &wb, &so);
     const int smem = wb * FAST_WARPS;
     const int src16 = ((((uintptr_t)src.img0) | (uintptr_t)src.stride0 | (uintptr_t)src.pitch0) & 15) == 0;
-    dim3 grid((P.cells_total + FAST_WARPS - 1) / FAST_WARPS, nframes);
-    k_fast_cells<<<grid, FAST_WARPS * 32, smem, st>>>(P, src, pyr, cellcnt, cellkeys, tp, sp, wb, so, src16);
+    // level < 0: every level in one launch; else only that level's cells (the forked latency graph)
+    const int c0 = level < 0 ? 0 : P.lvl[level].cell_off;
+    const int c1 = level < 0 ? P.cells_total : c0 + P.lvl[level].n_cols * P.lvl[level].n_rows;
+    dim3 grid((c1 - c0 + FAST_WARPS - 1) / FAST_WARPS, nframes);
+    k_fast_cells<<<grid, FAST_WARPS * 32, smem, st>>>(P, src, pyr, cellcnt, cellkeys, tp, sp, wb, so, src16, c0, c1);
     ++*launches;
     return cudaGetLastError();
 }

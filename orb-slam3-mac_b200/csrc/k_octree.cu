@@ -495,9 +495,10 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
          uint32_t* __restrict__ keysB, uint32_t* surv, uint32_t* survcnt,
          const int* __restrict__ lap, uint32_t* __restrict__ dest, int32_t* __restrict__ header,
          uint32_t* frame_done /* [nframes], zero between launches */,
-         int NC, int NCP2, int CW, int key_words /* shared-memory words per key buffer */) {
+         int NC, int NCP2, int CW, int key_words /* shared-memory words per key buffer */,
+         int level_base /* first level of this launch (per-level launches of the latency graph) */) {
     extern __shared__ __align__(16) uint32_t sm[];
-    const int level = blockIdx.x, frame = blockIdx.y;
+    const int level = level_base + blockIdx.x, frame = blockIdx.y;
     const OrbxLevel& L = P.lvl[level];
     const int tid = threadIdx.x, lane = orbx_lane(), warp = orbx_warp();
 
@@ -676,7 +677,7 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
     // fences again and reads the other levels' results through L2)
     __threadfence();
     __syncthreads();
-    if (tid == 0) C.tmp[45] = atomicAdd(&frame_done[frame], 1u) == gridDim.x - 1 ? 1u : 0u;
+    if (tid == 0) C.tmp[45] = atomicAdd(&frame_done[frame], 1u) == (uint32_t)P.nlevels - 1 ? 1u : 0u;
     __syncthreads();
     if (C.tmp[45] == 0) return;
     __threadfence();
@@ -726,12 +727,14 @@ cudaError_t orbx_configure_octree(const OrbxPlan& P) {
 cudaError_t orbx_launch_octree(const OrbxPlan& P, const uint32_t* cellcnt, const uint32_t* cellkeys,
                                uint32_t* keysA, uint32_t* keysB, uint32_t* surv, uint32_t* survcnt,
                                const int* lap, uint32_t* dest, int32_t* header, uint32_t* frame_done,
-                               int nframes, cudaStream_t st, int* launches) {
+                               int nframes, cudaStream_t st, int* launches, int level) {
     OctLaunchCfg c = orbx_octree_cfg(P);
-    dim3 grid(P.nlevels, nframes);
+    // level < 0: one CTA per (level, frame); else only that level (the forked latency graph).  The
+    // frame ticket counts P.nlevels CTAs either way: the last level to finish lays out the frame.
+    dim3 grid(level < 0 ? P.nlevels : 1, nframes);
     k_octree<<<grid, OCT_THREADS, c.smem, st>>>(P, cellcnt, cellkeys, keysA, keysB, surv, survcnt, lap, dest, header,
                                                frame_done, c.NC,
-                                               c.NCP2, c.CW, c.key_words);
+                                               c.NCP2, c.CW, c.key_words, level < 0 ? 0 : level);
     ++*launches;
     return cudaGetLastError();
 }

@@ -334,7 +334,8 @@ k_resize_rows_async(const __grid_constant__ RzArgs A, int n8) {
 #ifndef RZ_MIN_WARPS
 #define RZ_MIN_WARPS (148 * 16)
 #endif
-void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes, cudaStream_t st, int* launches) {
+void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes, cudaStream_t st, int* launches,
+                         cudaEvent_t* level_done) {
     for (int l = 1; l < P.nlevels; ++l) {
         const OrbxLevel& D = P.lvl[l];
         const OrbxLevel& S = P.lvl[l - 1];
@@ -373,5 +374,6 @@ void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, in
             k_resize_level<<<grid, block, 0, st>>>(P, src, l, pyr);
         }
         ++*launches;
+        if (level_done) cudaEventRecord(level_done[l], st);   // level l is complete (forked latency graph)
     }
 }

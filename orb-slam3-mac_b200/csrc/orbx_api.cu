@@ -21,19 +21,19 @@
 
 // kernel launchers (k_*.cu)
 void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes,
-                         cudaStream_t st, int* launches);
+                         cudaStream_t st, int* launches, cudaEvent_t* level_done = nullptr);
 cudaError_t orbx_launch_input(const uint8_t* raw, long long raw_fstride, int raw_pitch, int w, int h, int channels,
                               int rgb_order, int gray_bits, const uint4* map, uint8_t* dst, long long dst_fstride,
                               int dst_pitch, int nframes, cudaStream_t st, int* launches);
 cudaError_t orbx_configure_fast(const OrbxPlan& P);
 cudaError_t orbx_launch_fast(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
                              uint32_t* cellcnt, uint32_t* cellkeys, int nframes, cudaStream_t st,
-                             int* launches);
+                             int* launches, int level = -1);
 cudaError_t orbx_configure_octree(const OrbxPlan& P);
 cudaError_t orbx_launch_octree(const OrbxPlan& P, const uint32_t* cellcnt, const uint32_t* cellkeys,
                                uint32_t* keysA, uint32_t* keysB, uint32_t* surv, uint32_t* survcnt,
                                const int* lap, uint32_t* dest, int32_t* header, uint32_t* frame_done,
-                               int nframes, cudaStream_t st, int* launches);
+                               int nframes, cudaStream_t st, int* launches, int level = -1);
 cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
                                  const int32_t* header, const uint32_t* dest,
                                  orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
@@ -104,6 +104,7 @@ struct Slot {
     uint32_t* frame_done = nullptr;   // per-frame CTA tickets of k_octree (self-resetting)
     int32_t* h_header = nullptr;  // pinned
     int* h_lap = nullptr;         // pinned
+    int lap_valid = 0;            // frames whose lapping area on the device equals h_lap
     // in-flight bookkeeping
     bool in_flight = false;
     int nframes = 0, cap = 0, launches = 0;
@@ -118,6 +119,9 @@ struct Slot {
     unsigned long long g_epoch = 0, warm_epoch = 0;
     int g_nframes = 0, g_launches = 0;
     OrbxSrc g_src{};
+    // forked form of that graph: one branch per pyramid level (created on first capture)
+    cudaStream_t aux[ORBX_MAX_LEVELS] = {};
+    cudaEvent_t ev_fork = nullptr, ev_lvl[ORBX_MAX_LEVELS] = {}, ev_join[ORBX_MAX_LEVELS] = {};
 };
 
 }  // namespace
@@ -396,7 +400,11 @@ int ensure_buffers(orbx_handle* h, const OrbxPlan& P) {
         if ((r = grow(&s.header, &c.header, z.header))) return r;
         if ((r = grow(&s.kps, &c.kps, z.kps))) return r;
         if ((r = grow(&s.desc, &c.desc, z.desc))) return r;
-        if ((r = grow(&s.lap_d, &c.lap, z.lap))) return r;
+        {
+            int* before = s.lap_d;
+            if ((r = grow(&s.lap_d, &c.lap, z.lap))) return r;
+            if (s.lap_d != before) s.lap_valid = 0;
+        }
         if (c.frame_done < z.lap) {
             if ((r = grow(&s.frame_done, &c.frame_done, z.lap))) return r;
             CUDA_TRY(cudaMemset(s.frame_done, 0, c.frame_done));
@@ -459,6 +467,37 @@ int launch_stages(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes, bool
     return ORBX_OK;
 }
 
+// The same stages as a fork-join, for capture into the latency graph: FAST and the quadtree run per
+// level, each level on its own branch as soon as its image exists (level 0 at once, level l after
+// pyramid launch l), while the pyramid chain continues on the main branch; describe joins them.  The
+// critical path of one frame drops from pyramid + FAST + quadtree to about max(pyramid chain + the
+// last level's FAST/quadtree, level 0's FAST + quadtree).  Results are identical: the kernels and
+// their per-level work are the same, only launch granularity and ordering between levels change.
+int launch_stages_forked(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes) {
+    const OrbxPlan& P = h->plan;
+    const int nl = P.nlevels;
+    if (!s.ev_fork) CUDA_TRY(cudaEventCreateWithFlags(&s.ev_fork, cudaEventDisableTiming));
+    for (int l = 0; l < nl; ++l) {
+        if (!s.aux[l]) CUDA_TRY(cudaStreamCreateWithFlags(&s.aux[l], cudaStreamNonBlocking));
+        if (!s.ev_lvl[l]) CUDA_TRY(cudaEventCreateWithFlags(&s.ev_lvl[l], cudaEventDisableTiming));
+        if (!s.ev_join[l]) CUDA_TRY(cudaEventCreateWithFlags(&s.ev_join[l], cudaEventDisableTiming));
+    }
+    s.launches = 0;
+    CUDA_TRY(cudaEventRecord(s.ev_fork, s.st));
+    orbx_launch_pyramid(P, src, s.pyr, nframes, s.st, &s.launches, s.ev_lvl);
+    CUDA_TRY(cudaGetLastError());
+    for (int l = 0; l < nl; ++l) {
+        CUDA_TRY(cudaStreamWaitEvent(s.aux[l], l == 0 ? s.ev_fork : s.ev_lvl[l], 0));
+        CUDA_TRY(orbx_launch_fast(P, src, s.pyr, s.cellcnt, s.cellkeys, nframes, s.aux[l], &s.launches, l));
+        CUDA_TRY(orbx_launch_octree(P, s.cellcnt, s.cellkeys, s.keysA, s.keysB, s.surv, s.survcnt, s.lap_d, s.dest,
+                                    s.header, s.frame_done, nframes, s.aux[l], &s.launches, l));
+        CUDA_TRY(cudaEventRecord(s.ev_join[l], s.aux[l]));
+    }
+    for (int l = 0; l < nl; ++l) CUDA_TRY(cudaStreamWaitEvent(s.st, s.ev_join[l], 0));
+    CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.header, s.dest, s.kps, s.desc, nframes, s.st, &s.launches));
+    return ORBX_OK;
+}
+
 // Enqueue the whole device pipeline for `nframes` frames whose level 0 is `src`.
 // Small batches (the single-frame latency path) replay a CUDA graph of the kernel sequence: the
 // second run of a (plan, buffers, nframes, source) combination on a slot captures it, later runs
@@ -480,7 +519,8 @@ int enqueue_kernels(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes) {
             }
             cudaGraph_t g = nullptr;
             if (cudaStreamBeginCapture(s.st, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
-                const int r = launch_stages(h, s, src, nframes, false);
+                const int r = (h->cfg.flags & ORBX_FLAG_NO_FORK) ? launch_stages(h, s, src, nframes, false)
+                                                                 : launch_stages_forked(h, s, src, nframes);
                 const cudaError_t e = cudaStreamEndCapture(s.st, &g);
                 if (r == ORBX_OK && e == cudaSuccess && g &&
                     cudaGraphInstantiate(&s.gexec, g, 0) == cudaSuccess) {
@@ -550,10 +590,16 @@ int check_common(orbx_handle* h, int slot, int nframes, int w, int hgt) {
 }
 
 int upload_lap(Slot& s, const int* lap, int nframes) {
+    // the lapping areas rarely change between calls: skip the copy when the device already holds them
+    bool same = s.lap_valid >= nframes;
     for (int i = 0; i < nframes; ++i) {
-        s.h_lap[2 * i] = lap ? lap[2 * i] : 0;
-        s.h_lap[2 * i + 1] = lap ? lap[2 * i + 1] : 0;
+        const int a = lap ? lap[2 * i] : 0, b = lap ? lap[2 * i + 1] : 0;
+        same = same && s.h_lap[2 * i] == a && s.h_lap[2 * i + 1] == b;
+        s.h_lap[2 * i] = a;
+        s.h_lap[2 * i + 1] = b;
     }
+    if (same) return ORBX_OK;
+    s.lap_valid = nframes;
     CUDA_TRY(cudaMemcpyAsync(s.lap_d, s.h_lap, (size_t)nframes * 8, cudaMemcpyHostToDevice, s.st));
     return ORBX_OK;
 }
@@ -621,6 +667,12 @@ int orbx_destroy(orbx_handle* h) {
         for (int k = 0; k < 6; ++k) if (s.ev[k]) cudaEventDestroy(s.ev[k]);
         for (int k = 0; k < 2; ++k) if (s.ev_in[k]) cudaEventDestroy(s.ev_in[k]);
         if (s.gexec) cudaGraphExecDestroy(s.gexec);
+        for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
+            if (s.aux[l]) cudaStreamDestroy(s.aux[l]);
+            if (s.ev_lvl[l]) cudaEventDestroy(s.ev_lvl[l]);
+            if (s.ev_join[l]) cudaEventDestroy(s.ev_join[l]);
+        }
+        if (s.ev_fork) cudaEventDestroy(s.ev_fork);
         if (s.st) cudaStreamDestroy(s.st);
     }
     cudaFree(h->tables);
