@@ -537,3 +537,46 @@ def test_distinctive_descriptors_edge_cases(matcher):
     d = np.concatenate([one, np.repeat(one, 5, axis=0), rng.integers(0, 256, (2, 32), dtype=np.uint8)])
     gp = np.array([0, 0, 1, 6, 6, 8], np.int32)
     assert matcher.ComputeDistinctiveDescriptors(d, gp).tolist() == [-1, 0, 0, -1, 0]
+
+
+def test_n3_empty_and_invalid_inputs(matcher):
+    """Ragged / empty inputs of the N3 and N4 entry points: no points, no valid points, empty keyframes, and the
+    argument errors (levels outside the scale table, foreign vocabulary ids) are reported, not executed."""
+    from orb_slam3_mac_b200._lib import KP_DTYPE, OrbxError
+    from orb_slam3_mac_b200._lib_match import PROJ_POINT_DTYPE
+    from orb_slam3_mac_b200.matcher import BowSide, Frame, Vocabulary
+    rng = np.random.default_rng(1)
+    k = np.zeros(50, KP_DTYPE)
+    k["x"], k["y"] = rng.uniform(20, 700, 50), rng.uniform(20, 400, 50)
+    d = rng.integers(0, 256, (50, 32), dtype=np.uint8)
+    F = Frame(k, d, 752, 480, SF)
+    none = np.zeros(0, PROJ_POINT_DTYPE)
+    assert matcher.SearchByProjectionSim3(F, none, np.zeros((0, 32), np.uint8), 5)[0] == 0
+    assert matcher.Fuse(F, none, np.zeros((0, 32), np.uint8))[0] == 0
+    pts = np.zeros(7, PROJ_POINT_DTYPE)            # all invalid: nothing may match
+    n, match = matcher.SearchByProjectionReloc(F, pts, d[:7], 10.0, 100)
+    assert n == 0 and (match == -1).all()
+    E = Frame(np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8), 752, 480, SF)
+    pts["valid"], pts["u"], pts["v"] = 1, 100, 100
+    n, bi, bd = matcher.Fuse(E, pts, d[:7])        # empty keyframe
+    assert n == 0 and (bi == -1).all() and (bd == 256).all()
+    assert matcher.SearchBySim3(E, E, none, np.zeros((0, 32), np.uint8), none, np.zeros((0, 32), np.uint8), 7.5)[0] == 0
+    pts["level"] = 8                                # outside the 8-entry scale table
+    with pytest.raises(OrbxError):
+        matcher.SearchByProjectionSim3(F, pts, d[:7], 5)
+    A = BowSide(k, d, {})                           # empty FeatureVector on one side
+    B = BowSide(k, d, {3: list(range(50))})
+    assert matcher.SearchByBoWKF(A, np.ones(50, np.uint8), B, np.ones(50, np.uint8))[0] == 0
+    assert matcher.SearchForTriangulation(B, np.ones(50, np.uint8), B, np.zeros(50, np.uint8))[0] == 0   # all tracked
+    n, m12 = matcher.SearchForTriangulation(B, np.zeros(50, np.uint8), B, np.zeros(50, np.uint8))         # coarse, self
+    assert n == 50 and (m12 == np.arange(50)).all()
+    bad = Vocabulary([0, 2, 2, 2], [1, 9], np.zeros((3, 32), np.uint8), [0, 1, 1], [0, 0, 1], 1)   # child id 9 of 3
+    with pytest.raises(OrbxError):
+        matcher.load_vocabulary(bad)
+    voc = Vocabulary([0, 2, 2, 2], [1, 2], d[:3], [0, 1.5, 2.5], [0, 0, 1], 1)
+    h = matcher.load_vocabulary(voc)
+    bi, bv, fn, fp, fi = matcher.transform(h, np.zeros((0, 32), np.uint8), 0)
+    assert len(bi) == 0 and len(fn) == 0 and fp.tolist() == [0]
+    bi, bv, fn, fp, fi = matcher.transform(h, d[1:3], 0)   # the two words themselves, levelsup 0 -> node = word node
+    assert bi.tolist() == [0, 1] and np.allclose(bv, [1.5 / 4.0, 2.5 / 4.0]) and fn.tolist() == [1, 2]
+    matcher.free_vocabulary(h)
