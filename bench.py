@@ -296,7 +296,22 @@ def run_ours(args):
     step_device(0)  # leaves d_hdr/d_kps/d_desc pointing at slot 0 for the statistics below
     gather = None
     comm = None
-    if world > 1:
+    sink = None
+    if world > 1 and args.gather == "fused":
+        # THE PRODUCT PATH for N > 1: no collective.  Rank 0 owns one result slab [slot][rank][frame]; every
+        # rank's k_describe writes its result rows into it in the same kernel that produces them -- peer memory
+        # over NVLink, mapped through a CUDA IPC handle that travels once through the process group.
+        from orb_slam3_mac_b200 import sharding
+        n_sink = sharding.sink_frames(nsl, world, B)
+        if rank == 0:
+            sink = sharding.ResultSink(local, n_sink, cap)
+            sharding.exchange_sink_handle(sink.export(), 0)
+        else:
+            sink = sharding.ResultSink(local, n_sink, cap, sharding.exchange_sink_handle(None, 0))
+        for sl in range(nsl):
+            _lib.check(lib.orbx_set_result_sink(hd, sl, sink.h, sharding.sink_first_frame(sl, rank, world, B)))
+    elif world > 1:
+        # baseline for A/B (--gather nccl): NCCL all_gather of the result slabs on a dedicated stream
         comm = torch.cuda.Stream(device=dev)
         g_hd = [torch.empty(world * B * 16, dtype=torch.uint8, device=dev) for _ in range(nsl)]
         g_kp = [torch.empty(world * B * cap * 28, dtype=torch.uint8, device=dev) for _ in range(nsl)]
@@ -391,6 +406,36 @@ def run_ours(args):
     dev_ms, stage_overlapped, launches, clocks = timed_pass(False, True)
     chained_ms, stage, _, _ = timed_pass(True, False)
     step_device(0)
+
+    gather_check = None
+    if sink is not None:
+        # parity of the fused gather (outside the timed region): every rank hashes a few frames of its LOCAL
+        # slab, rank 0 reads the same frames of every rank out of its sink and compares
+        import hashlib
+        from orb_slam3_mac_b200 import sharding
+        barrier()
+        hdr_l = torch.as_tensor(_DevArray(d_hdr.value, B * 16), device=dev).cpu().numpy().view(np.int32).reshape(B, 4)
+        kp_l = torch.as_tensor(_DevArray(d_kps.value, B * cap * 28), device=dev).cpu().numpy().reshape(B, cap * 28)
+        de_l = torch.as_tensor(_DevArray(d_desc.value, B * cap * 32), device=dev).cpu().numpy().reshape(B, cap * 32)
+        picks = sorted({0, 1, B // 2, B - 1})
+        mine = []
+        for f in picks:
+            n = int(hdr_l[f, 0])
+            mine.append((f, hdr_l[f].tolist(), hashlib.sha1(kp_l[f, :n * 28].tobytes() + de_l[f, :n * 32].tobytes()).hexdigest()))
+        allr = [None] * world
+        dist.all_gather_object(allr, mine)
+        if rank == 0:
+            bad = 0
+            for r in range(world):
+                for f, hdr4, digest in allr[r]:
+                    hs, ks, ds = sink.read_frame(sharding.sink_first_frame(0, r, world, B) + f)
+                    got = hashlib.sha1(ks.tobytes() + ds.tobytes()).hexdigest()
+                    bad += int(hs.tolist() != hdr4 or got != digest)
+            assert bad == 0, f"fused gather: {bad} frames in rank 0's sink differ from the producers' results"
+            gather_check = {"frames_checked": world * len(picks), "mismatches": bad}
+        barrier()
+        for sl in range(nsl):   # the e2e pass below returns results to each rank's own host buffers
+            _lib.check(lib.orbx_set_result_sink(hd, sl, None, 0))
 
     # keypoint / candidate statistics of the batch (for the algorithmic-byte figures)
     hdr = torch.as_tensor(_DevArray(d_hdr.value, B * 16), device=f"cuda:{local}").cpu().numpy().view(np.int32).reshape(B, 4)
@@ -531,7 +576,11 @@ def run_ours(args):
                        "frames_per_step_per_gpu": B,
                        "l2_policy": f"inputs larger than L2: {B} distinct frames = {fbytes / 1e6:.0f} MB of input "
                                     f"plus {B} pyramids/scratch per step (126 MB L2)",
-                       "parallelism": f"frames sharded over {world} GPU(s), independent streams; NCCL all_gather of result slabs only"
+                       "parallelism": (f"frames sharded over {world} GPU(s), independent streams, no collective: every rank's "
+                                       f"k_describe writes its result rows straight into rank 0's slab over NVLink peer "
+                                       f"memory (fused gather, orbx_set_result_sink)" if args.gather == "fused" else
+                                       f"frames sharded over {world} GPU(s), independent streams; NCCL all_gather of result "
+                                       f"slabs only (A/B baseline of the fused gather)")
                        if world > 1 else "1 GPU, batched launches on two alternating slots chained by events (the host enqueues step i+1 while step i runs)",
                        "keypoints_per_frame": round(n_kp, 1), "fast_candidates_per_frame": round(n_cand, 1)},
             "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": fbytes + B * 8,
@@ -542,6 +591,9 @@ def run_ours(args):
             "clocks": clocks,
             "latency": lat,
         }
+        if gather_check is not None:
+            line["gather"] = dict(gather_check, kind="fused into k_describe (peer stores over NVLink into rank 0's slab)",
+                                  bytes_per_step_per_gpu=int(B * (16 + n_kp * 60)))
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             ref = CpuReference(cfg, threads)
@@ -563,6 +615,12 @@ def run_ours(args):
     lib.orbx_host_free(h_in)
     lib.orbx_destroy(hd)
     if world > 1:
+        barrier()
+        if sink is not None and rank != 0:
+            sink.close()     # importers unmap first ...
+        barrier()
+        if sink is not None and rank == 0:
+            sink.close()     # ... then the owner frees
         dist.destroy_process_group()
 
 
@@ -575,6 +633,9 @@ def main():
     ap.add_argument("--config", default="C1", choices=["C1", "C2", "C3", "C4", "C5"])
     ap.add_argument("--batch", type=int, default=0, help="frames per step per GPU (default: by config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather", default="fused", choices=["fused", "nccl"],
+                    help="N > 1: result gather fused into k_describe over NVLink peer memory (default), or the NCCL "
+                         "all_gather baseline")
     ap.add_argument("--input", default="gray", choices=["gray", "bgr", "gray+rect", "bgr+rect"],
                     help="raw input of the frames: the N4 input stage (cvtColor / cv::remap rectification) runs in "
                          "front of level 0 for anything but 'gray' (the BASELINE.json configs are gray)")

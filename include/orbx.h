@@ -141,6 +141,31 @@ int orbx_extract_device(orbx_handle* h, int slot, const uint8_t* d_imgs, int nfr
 /* The CUDA stream (cudaStream_t) of a slot, for event timing by the caller. */
 void* orbx_slot_stream(orbx_handle* h, int slot);
 
+/* ---- multi-GPU: the result gather fused into the producing kernel -------------------
+ * Frames are sharded over GPUs as independent units; the only exchange is gathering the results.  A result
+ * sink is a slab on the gathering GPU -- [frames][4] headers {n, mono_index, status, 0}, [frames][cap]
+ * keypoints, [frames][cap][32] descriptors, cap = orbx_max_keypoints() -- that OTHER GPUs' k_describe
+ * kernels write into directly: every result row goes to the local slab and, in the same kernel, to frame
+ * first_frame + f of the sink (peer memory over NVLink when the sink lives on another GPU).  No collective
+ * follows the kernel; the gathering side reads the slab after the producers' streams have completed (stream
+ * synchronisation + a host barrier, or any event the application already has).
+ *   same process:   orbx_sink_create on the gathering device, orbx_set_result_sink on every handle (peer access
+ *                   is enabled on demand);
+ *   one process per GPU: orbx_sink_create + orbx_sink_export on the gathering rank, the 64-byte CUDA IPC handle
+ *                   travels through the application's own channel, orbx_sink_open on the other ranks. */
+typedef struct orbx_sink orbx_sink;
+int orbx_sink_create(int device, int frames, int cap, orbx_sink** out);
+int orbx_sink_export(orbx_sink* s, uint8_t handle[64]);
+int orbx_sink_open(int device, const uint8_t handle[64], int frames, int cap, orbx_sink** out);
+int orbx_sink_destroy(orbx_sink* s);
+/* Device pointers of the three arrays (valid on the creating / opening device). */
+int orbx_sink_pointers(orbx_sink* s, void** header, void** kps, void** desc);
+/* Host copy of one gathered frame (synchronises the sink's device first). */
+int orbx_sink_read_frame(orbx_sink* s, int frame, int32_t header[4], orbx_keypoint* kps, uint8_t* desc, int rows);
+/* Runs of `slot` write frame f of a batch to sink frame first_frame + f from now on (sink NULL: off).
+ * The sink must hold first_frame + max_batch frames of the handle's capacity. */
+int orbx_set_result_sink(orbx_handle* h, int slot, orbx_sink* sink, int first_frame);
+
 /* ---- pyramid access: ORBextractor::mvImagePyramid (include/ORBextractor.h:83), read by
  * Frame::ComputeStereoMatches (src/Frame.cc:809,899-918) ------------------------------------- */
 int orbx_level_size(const orbx_handle* h, int w, int hgt, int level, int* lw, int* lh);

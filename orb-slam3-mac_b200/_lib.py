@@ -76,6 +76,13 @@ ORBX_SYMBOLS = {
     "orbx_debug_survivors": (_i, [_vp, _i, _i, _i, _vp, _i]),
     "orbx_last_launch_count": (_i, [_vp, _i]),
     "orbx_last_stage_ms": (_i, [_vp, _i, _vp, _i]),
+    "orbx_sink_create": (_i, [_i, _i, _i, C.POINTER(_vp)]),
+    "orbx_sink_export": (_i, [_vp, _vp]),
+    "orbx_sink_open": (_i, [_i, _vp, _i, _i, C.POINTER(_vp)]),
+    "orbx_sink_destroy": (_i, [_vp]),
+    "orbx_sink_pointers": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)]),
+    "orbx_sink_read_frame": (_i, [_vp, _i, _vp, _vp, _vp, _i]),
+    "orbx_set_result_sink": (_i, [_vp, _i, _vp, _i]),
 }
 
 

@@ -98,12 +98,15 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 __global__ void __launch_bounds__(DESC_WARPS * 32)
 k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t* __restrict__ pyr,
            const int32_t* __restrict__ header, const uint32_t* __restrict__ dest,
-           orbx_keypoint* __restrict__ kps, uint8_t* __restrict__ desc) {
+           orbx_keypoint* __restrict__ kps, uint8_t* __restrict__ desc, const OrbxSinkArgs sink) {
     extern __shared__ __align__(16) uint32_t sm[];
     const int warp = orbx_warp(), lane = orbx_lane();
     const int frame = blockIdx.y;
     const int idx = blockIdx.x * DESC_WARPS + warp;
 
+    // fused result gather: the frame header also goes to the sink (rank 0's slab, peer-mapped over NVLink)
+    if (sink.hdr && blockIdx.x == 0 && threadIdx.x < 4)
+        sink.hdr[4 * (size_t)(sink.first_frame + frame) + threadIdx.x] = header[4 * frame + threadIdx.x];
     // the keypoint's record, written by orbx_assemble_frame: {key, output row | level << 24}
     if (idx >= min(header[4 * frame], P.surv_total)) return;
     const uint2 rec = __ldg(reinterpret_cast<const uint2*>(dest) + (size_t)frame * P.surv_total + idx);
@@ -257,6 +260,9 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
         byte |= (t0 < t1 ? 1u : 0u) << k;
     }
     desc[((size_t)frame * P.out_cap + out_row) * 32 + lane] = (uint8_t)byte;
+    // fused result gather: the same row straight into the gathering GPU's slab (one 32-byte write per
+    // keypoint over NVLink when the sink is peer memory) -- no collective follows the kernel
+    if (sink.desc) sink.desc[((size_t)(sink.first_frame + frame) * P.out_cap + out_row) * 32 + lane] = (uint8_t)byte;
 
     if (lane == 0) {
         orbx_keypoint kp;
@@ -273,13 +279,14 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
         kp.octave = l;
         kp.class_id = -1;
         kps[(size_t)frame * P.out_cap + out_row] = kp;
+        if (sink.kps) sink.kps[(size_t)(sink.first_frame + frame) * P.out_cap + out_row] = kp;
     }
 }
 
 cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
                                  const int32_t* header, const uint32_t* dest,
                                  orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
-                                 int* launches) {
+                                 int* launches, const OrbxSinkArgs& sink) {
     dim3 grid((P.surv_total + DESC_WARPS - 1) / DESC_WARPS, nframes);
     // once per device: shared-memory opt-in and the float pattern table
     static std::mutex mu;
@@ -296,7 +303,7 @@ cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const ui
             ready[dev] = true;
         }
     }
-    k_describe<<<grid, DESC_WARPS * 32, DESC_SMEM_BYTES, st>>>(P, src, pyr, header, dest, kps, desc);
+    k_describe<<<grid, DESC_WARPS * 32, DESC_SMEM_BYTES, st>>>(P, src, pyr, header, dest, kps, desc, sink);
     ++*launches;
     return cudaGetLastError();
 }

@@ -37,7 +37,7 @@ cudaError_t orbx_launch_octree(const OrbxPlan& P, const uint32_t* cellcnt, const
 cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
                                  const int32_t* header, const uint32_t* dest,
                                  orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
-                                 int* launches);
+                                 int* launches, const OrbxSinkArgs& sink);
 
 namespace {
 
@@ -120,6 +120,7 @@ struct Slot {
     int g_nframes = 0, g_launches = 0;
     OrbxSrc g_src{};
     // forked form of that graph: one branch per pyramid level (created on first capture)
+    OrbxSinkArgs sink{};         // fused result gather (orbx_set_result_sink); hdr == nullptr: off
     cudaStream_t aux[ORBX_MAX_LEVELS] = {};
     cudaEvent_t ev_fork = nullptr, ev_lvl[ORBX_MAX_LEVELS] = {}, ev_join[ORBX_MAX_LEVELS] = {};
 };
@@ -462,7 +463,7 @@ int launch_stages(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes, bool
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[3], s.st));
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[4], s.st));
     CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.header, s.dest, s.kps, s.desc, nframes,
-                                  s.st, &s.launches));
+                                  s.st, &s.launches, s.sink));
     if (timing) CUDA_TRY(cudaEventRecord(s.ev[5], s.st));
     return ORBX_OK;
 }
@@ -494,7 +495,7 @@ int launch_stages_forked(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframe
         CUDA_TRY(cudaEventRecord(s.ev_join[l], s.aux[l]));
     }
     for (int l = 0; l < nl; ++l) CUDA_TRY(cudaStreamWaitEvent(s.st, s.ev_join[l], 0));
-    CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.header, s.dest, s.kps, s.desc, nframes, s.st, &s.launches));
+    CUDA_TRY(orbx_launch_describe(P, src, s.pyr, s.header, s.dest, s.kps, s.desc, nframes, s.st, &s.launches, s.sink));
     return ORBX_OK;
 }
 
@@ -1074,6 +1075,152 @@ int orbx_debug_survivors(orbx_handle* h, int slot, int frame, int level, int32_t
         xyr[3 * i + 2] = ORBX_KEY_R(keys[i]);
     }
     return (int)n;
+}
+
+}  // extern "C"
+
+// =================================================================================================
+// fused multi-GPU result gather: result sinks
+// =================================================================================================
+struct orbx_sink {
+    int device = 0;        // device the pointers are valid on (the creator's, or the opener's)
+    int owner_device = -1; // device that holds the memory when it was created in this process
+    int frames = 0, cap = 0;
+    bool opened = false;   // mapped from another process through CUDA IPC
+    uint8_t* base = nullptr;
+    size_t off_kps = 0, off_desc = 0, bytes = 0;
+};
+
+namespace {
+void sink_layout(orbx_sink* k) {
+    k->off_kps = ((size_t)k->frames * 16 + 255) & ~(size_t)255;
+    k->off_desc = (k->off_kps + (size_t)k->frames * k->cap * sizeof(orbx_keypoint) + 255) & ~(size_t)255;
+    k->bytes = k->off_desc + (size_t)k->frames * k->cap * 32;
+}
+}  // namespace
+
+extern "C" {
+
+int orbx_sink_create(int device, int frames, int cap, orbx_sink** out) {
+    if (!out || frames < 1 || cap < 1) return fail(ORBX_E_BAD_ARG, "bad argument");
+    *out = nullptr;
+    CUDA_TRY(cudaSetDevice(device));
+    orbx_sink* k = new orbx_sink();
+    k->device = k->owner_device = device;
+    k->frames = frames;
+    k->cap = cap;
+    sink_layout(k);
+    // plain cudaMalloc (not a pool / VMM allocation): the block can be exported through CUDA IPC
+    cudaError_t e = cudaMalloc((void**)&k->base, k->bytes);
+    if (e == cudaSuccess) e = cudaMemset(k->base, 0, k->bytes);
+    if (e != cudaSuccess) {
+        const size_t bytes = k->bytes;
+        if (k->base) cudaFree(k->base);
+        delete k;
+        return fail(ORBX_E_CUDA, "sink allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+    }
+    *out = k;
+    return ORBX_OK;
+}
+
+int orbx_sink_export(orbx_sink* k, uint8_t handle[64]) {
+    if (!k || !handle || k->opened) return fail(ORBX_E_BAD_ARG, "bad sink");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    CUDA_TRY(cudaSetDevice(k->device));
+    cudaIpcMemHandle_t hnd;
+    CUDA_TRY(cudaIpcGetMemHandle(&hnd, k->base));
+    memcpy(handle, &hnd, 64);
+    return ORBX_OK;
+}
+
+int orbx_sink_open(int device, const uint8_t handle[64], int frames, int cap, orbx_sink** out) {
+    if (!out || !handle || frames < 1 || cap < 1) return fail(ORBX_E_BAD_ARG, "bad argument");
+    *out = nullptr;
+    CUDA_TRY(cudaSetDevice(device));
+    cudaIpcMemHandle_t hnd;
+    memcpy(&hnd, handle, 64);
+    void* p = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&p, hnd, cudaIpcMemLazyEnablePeerAccess));
+    orbx_sink* k = new orbx_sink();
+    k->device = device;
+    k->frames = frames;
+    k->cap = cap;
+    k->opened = true;
+    k->base = (uint8_t*)p;
+    sink_layout(k);
+    *out = k;
+    return ORBX_OK;
+}
+
+int orbx_sink_destroy(orbx_sink* k) {
+    if (!k) return ORBX_OK;
+    cudaSetDevice(k->device);
+    if (k->base) {
+        if (k->opened) cudaIpcCloseMemHandle(k->base);
+        else cudaFree(k->base);
+    }
+    delete k;
+    return ORBX_OK;
+}
+
+int orbx_sink_pointers(orbx_sink* k, void** header, void** kps, void** desc) {
+    if (!k) return fail(ORBX_E_BAD_ARG, "null sink");
+    if (header) *header = k->base;
+    if (kps) *kps = k->base + k->off_kps;
+    if (desc) *desc = k->base + k->off_desc;
+    return ORBX_OK;
+}
+
+int orbx_sink_read_frame(orbx_sink* k, int frame, int32_t header[4], orbx_keypoint* kps, uint8_t* desc, int rows) {
+    if (!k || frame < 0 || frame >= k->frames || rows < 0 || rows > k->cap) return fail(ORBX_E_BAD_ARG, "bad argument");
+    CUDA_TRY(cudaSetDevice(k->device));
+    CUDA_TRY(cudaDeviceSynchronize());
+    if (header) CUDA_TRY(cudaMemcpy(header, k->base + (size_t)frame * 16, 16, cudaMemcpyDeviceToHost));
+    if (kps && rows)
+        CUDA_TRY(cudaMemcpy(kps, k->base + k->off_kps + (size_t)frame * k->cap * sizeof(orbx_keypoint),
+                            (size_t)rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost));
+    if (desc && rows)
+        CUDA_TRY(cudaMemcpy(desc, k->base + k->off_desc + (size_t)frame * k->cap * 32, (size_t)rows * 32,
+                            cudaMemcpyDeviceToHost));
+    return ORBX_OK;
+}
+
+int orbx_set_result_sink(orbx_handle* h, int slot, orbx_sink* k, int first_frame) {
+    if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(ORBX_E_BAD_ARG, "bad slot");
+    Slot& s = h->slots[slot];
+    if (s.in_flight) return fail(ORBX_E_BUSY, "slot %d has an un-waited submit", slot);
+    CUDA_TRY(cudaSetDevice(h->cfg.device));
+    CUDA_TRY(cudaStreamSynchronize(s.st));
+    if (s.gexec) {   // the captured graph holds the old sink arguments
+        cudaGraphExecDestroy(s.gexec);
+        s.gexec = nullptr;
+    }
+    if (!k) {
+        s.sink = OrbxSinkArgs{};
+        return ORBX_OK;
+    }
+    const int cap = orbx_max_keypoints(h);
+    if (k->cap != cap) return fail(ORBX_E_BAD_ARG, "sink rows per frame (%d) differ from the handle's capacity (%d)", k->cap, cap);
+    if (first_frame < 0 || first_frame + h->cfg.max_batch > k->frames)
+        return fail(ORBX_E_BAD_ARG, "frames [%d, %d) do not fit the sink's %d frames", first_frame,
+                    first_frame + h->cfg.max_batch, k->frames);
+    if (!k->opened && k->owner_device != h->cfg.device) {
+        // same process, other GPU: map the owner's memory into this device (NVLink peer access)
+        int can = 0;
+        CUDA_TRY(cudaDeviceCanAccessPeer(&can, h->cfg.device, k->owner_device));
+        if (!can) return fail(ORBX_E_UNSUPPORTED, "device %d cannot access device %d", h->cfg.device, k->owner_device);
+        cudaError_t e = cudaDeviceEnablePeerAccess(k->owner_device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+            return fail(ORBX_E_CUDA, "cudaDeviceEnablePeerAccess failed: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+    } else if (k->opened && k->device != h->cfg.device) {
+        return fail(ORBX_E_BAD_ARG, "the sink was opened on device %d, the handle runs on %d", k->device, h->cfg.device);
+    }
+    s.sink.hdr = (int32_t*)k->base;
+    s.sink.kps = (orbx_keypoint*)(k->base + k->off_kps);
+    s.sink.desc = k->base + k->off_desc;
+    s.sink.first_frame = first_frame;
+    return ORBX_OK;
 }
 
 }  // extern "C"

@@ -96,4 +96,15 @@ struct OrbxSrc {
     int _pad;
 };
 
+// Result sink of the fused multi-GPU gather (orbx_set_result_sink): k_describe writes every result
+// row of frame f also to frame first_frame + f of these arrays (same capacity per frame as the local
+// slab), which live on the gathering GPU -- local memory, or peer memory mapped over NVLink.
+struct OrbxSinkArgs {
+    int32_t* hdr;          // [frames][4], nullptr = no sink
+    orbx_keypoint* kps;    // [frames][out_cap]
+    uint8_t* desc;         // [frames][out_cap][32]
+    int first_frame;
+    int _pad;
+};
+
 #endif  // ORBX_INTERNAL_H

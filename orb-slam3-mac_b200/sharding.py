@@ -37,3 +37,73 @@ def to_global_order(g: torch.Tensor, n_frames: int):
     world, n_local = g.shape[0], g.shape[1]
     inter = g.transpose(0, 1).reshape((world * n_local,) + tuple(g.shape[2:]))
     return inter[:n_frames]
+
+
+# ---- fused result gather (include/orbx.h, orbx_sink_*) ------------------------------------------------
+# The product path for N > 1 does not call a collective at all: every rank's k_describe writes its result
+# rows straight into ONE slab on the gathering rank (peer memory over NVLink).  The slab is laid out like
+# the output of an all_gather -- [slot][rank][local frame] -- so to_global_order applies unchanged.
+def sink_first_frame(slot: int, rank: int, world: int, batch: int) -> int:
+    """First sink frame of `rank`'s batch in pipeline slot `slot`."""
+    return (slot * world + rank) * batch
+
+
+def sink_frames(n_slots: int, world: int, batch: int) -> int:
+    return n_slots * world * batch
+
+
+def exchange_sink_handle(handle: bytes | None, src: int = 0, group=None) -> bytes:
+    """The gathering rank passes the 64-byte CUDA IPC handle of its sink (orbx_sink_export); every rank
+    returns it.  Uses the process group the application already has (NCCL on the GPU box, gloo in tests)."""
+    box = [handle if dist.get_rank(group) == src else None]
+    dist.broadcast_object_list(box, src=src, group=group)
+    h = box[0]
+    if not isinstance(h, (bytes, bytearray)) or len(h) != 64:
+        raise ValueError("sink handle must be 64 bytes")
+    return bytes(h)
+
+
+class ResultSink:
+    """ctypes wrapper of orbx_sink: created on the gathering device, or opened from an exported handle."""
+
+    def __init__(self, device: int, frames: int, cap: int, handle: bytes | None = None):
+        import ctypes as C
+        from . import _lib
+        self._C, self._lib_mod = C, _lib
+        self.lib = _lib.load()
+        self.frames, self.cap, self.device = int(frames), int(cap), int(device)
+        self.h = C.c_void_p()
+        if handle is None:
+            _lib.check(self.lib.orbx_sink_create(device, frames, cap, C.byref(self.h)))
+        else:
+            buf = (C.c_uint8 * 64).from_buffer_copy(handle)
+            _lib.check(self.lib.orbx_sink_open(device, buf, frames, cap, C.byref(self.h)))
+
+    def export(self) -> bytes:
+        C = self._C
+        buf = (C.c_uint8 * 64)()
+        self._lib_mod.check(self.lib.orbx_sink_export(self.h, buf))
+        return bytes(buf)
+
+    def pointers(self):
+        C = self._C
+        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self._lib_mod.check(self.lib.orbx_sink_pointers(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def read_frame(self, frame: int):
+        """-> (header[4] int32, keypoints[n], descriptors[n, 32]) of one gathered frame."""
+        import numpy as np
+        hdr = np.zeros(4, np.int32)
+        self._lib_mod.check(self.lib.orbx_sink_read_frame(self.h, frame, hdr.ctypes.data, None, None, 0))
+        n = int(min(max(hdr[0], 0), self.cap))
+        kps = np.zeros(n, self._lib_mod.KP_DTYPE)
+        desc = np.zeros((n, 32), np.uint8)
+        if n:
+            self._lib_mod.check(self.lib.orbx_sink_read_frame(self.h, frame, None, kps.ctypes.data, desc.ctypes.data, n))
+        return hdr, kps, desc
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.orbx_sink_destroy(self.h)
+            self.h = None

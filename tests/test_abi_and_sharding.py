@@ -116,3 +116,44 @@ def test_sharding_partition_is_exact():
             assert seen == list(range(n))
             for r in range(world):
                 assert all(sharding.frame_owner(i, world) == r for i in sharding.local_frames(n, world, r))
+
+
+def _sink_worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from orb_slam3_mac_b200 import sharding
+    # the gathering rank exports a (here: fake) 64-byte IPC handle, every rank must end up with it
+    h = sharding.exchange_sink_handle(bytes(range(64)) if rank == 0 else None, src=0)
+    B, slots = 6, 2
+    # what the fused gather does on the GPU box, replayed with a gloo gather: rank r "writes" its batch of slot sl
+    # to sink frames [first, first + B); the slab of a slot then reads like an all_gather output
+    slab = torch.full((sharding.sink_frames(slots, world, B),), -1, dtype=torch.int64)
+    mine = torch.tensor(sharding.local_frames(world * B, world, rank), dtype=torch.int64)
+    parts = [torch.zeros(B, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(parts, mine)
+    for sl in range(slots):
+        for r in range(world):
+            f0 = sharding.sink_first_frame(sl, r, world, B)
+            slab[f0:f0 + B] = parts[r] + 1000 * sl
+    ok = h == bytes(range(64))
+    for sl in range(slots):
+        region = slab[sl * world * B:(sl + 1) * world * B].view(world, B)
+        ok = ok and bool((sharding.to_global_order(region, world * B) == torch.arange(world * B) + 1000 * sl).all())
+    ret[rank] = ok
+    dist.destroy_process_group()
+
+
+def test_fused_gather_layout_and_handle_exchange_gloo_world2():
+    """Host logic of the fused result gather (orbx_sink_*): the IPC handle reaches every rank and the sink layout
+    [slot][rank][local frame] maps back to global frame order."""
+    world = 2
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    port = _free_port()
+    ctx = mp.get_context("spawn")
+    ps = [ctx.Process(target=_sink_worker, args=(r, world, port, ret)) for r in range(world)]
+    [p.start() for p in ps]
+    [p.join(120) for p in ps]
+    assert all(p.exitcode == 0 for p in ps)
+    assert ret.get(0) and ret.get(1)

@@ -313,3 +313,55 @@ def test_device_resident_frames_any_pitch(oracle_libs, synth, pad):
         assert H[i, 2] == 0
         _compare_final(ora(imgs[i], (0, 1000)), (int(H[i, 1]), K[i, :n], D[i, :n]), ("device", pad, i))
     ex.close()
+
+
+def _sink_roundtrip(synth, dev_handle, dev_sink):
+    """Batches of two slots written through the fused gather into a sink on `dev_sink` by a handle on `dev_handle`."""
+    import ctypes as C
+    from orb_slam3_mac_b200 import _lib, sharding
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    B = 5
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_size=(480, 752), max_batch=B, n_slots=2, device=dev_handle)
+    cap = ex.max_keypoints()
+    sink = sharding.ResultSink(dev_sink, sharding.sink_frames(2, 2, B), cap)
+    imgs = [synth.frame(["noise", "checker", "lowtex", "black"][i % 4], 480, 752, 40 + i) for i in range(B)]
+    laps = [(0, 0) if i % 2 else (100, 400) for i in range(B)]
+    ref = ex.extract_batch(imgs, laps)          # no sink yet: the slab stays zero
+    assert sink.read_frame(0)[0].tolist() == [0, 0, 0, 0]
+    first = sharding.sink_first_frame(0, 1, 2, B)   # this handle plays rank 1 of 2, slot 0
+    _lib.check(ex.lib.orbx_set_result_sink(ex.h, 0, sink.h, first))
+    res = ex.extract_batch(imgs, laps)
+    for i in range(B):
+        mono, kps, desc = res[i]
+        assert mono == ref[i][0] and np.array_equal(kps, ref[i][1]) and np.array_equal(desc, ref[i][2])
+        hdr, sk, sd = sink.read_frame(first + i)
+        assert hdr[0] == len(kps) and hdr[1] == mono and hdr[2] == 0
+        assert np.array_equal(sk, kps) and np.array_equal(sd, desc)
+    assert sink.read_frame(0)[0].tolist() == [0, 0, 0, 0]        # frames of other ranks untouched
+    # single frame (CUDA-graph path), then the sink switched off again
+    _lib.check(ex.lib.orbx_set_result_sink(ex.h, 0, sink.h, 0))
+    for _ in range(3):
+        mono, kps, desc = ex(imgs[0], laps[0])
+    hdr, sk, sd = sink.read_frame(0)
+    assert hdr[0] == len(kps) and np.array_equal(sk, kps) and np.array_equal(sd, desc)
+    _lib.check(ex.lib.orbx_set_result_sink(ex.h, 0, None, 0))
+    ex(imgs[1], laps[1])
+    assert np.array_equal(sink.read_frame(0)[1], kps)            # unchanged: the sink is off
+    with pytest.raises(_lib.OrbxError):                            # does not fit
+        _lib.check(ex.lib.orbx_set_result_sink(ex.h, 0, sink.h, sink.frames - B + 1))
+    sink.close()
+    ex.close()
+
+
+def test_fused_result_gather_sink_same_gpu(synth):
+    """orbx_set_result_sink: k_describe writes headers, keypoints and descriptors of every frame also into the
+    sink slab (here on the same GPU) -- bit-identical to the local results, other frames untouched."""
+    _sink_roundtrip(synth, 0, 0)
+
+
+def test_fused_result_gather_sink_peer_gpu(synth):
+    """The same with the sink on another GPU: the kernel's stores travel over NVLink peer access."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    _sink_roundtrip(synth, 1, 0)
