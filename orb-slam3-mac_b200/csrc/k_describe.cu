@@ -264,22 +264,25 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
     // keypoint over NVLink when the sink is peer memory) -- no collective follows the kernel
     if (sink.desc) sink.desc[((size_t)(sink.first_frame + frame) * P.out_cap + out_row) * 32 + lane] = (uint8_t)byte;
 
-    if (lane == 0) {
-        orbx_keypoint kp;
-        float x = (float)cx, y = (float)cy;
-        if (l != 0) {
-            x = __fmul_rn(x, L.scale);
-            y = __fmul_rn(y, L.scale);
-        }
-        kp.x = x;
-        kp.y = y;
-        kp.size = L.size;
-        kp.angle = angle;
-        kp.response = (float)ORBX_KEY_R(key);
-        kp.octave = l;
-        kp.class_id = -1;
-        kps[(size_t)frame * P.out_cap + out_row] = kp;
-        if (sink.kps) sink.kps[(size_t)(sink.first_frame + frame) * P.out_cap + out_row] = kp;
+    // the 28-byte keypoint record as ONE coalesced store: lane i < 7 writes word i (one 28-byte request
+    // instead of seven 4-byte ones -- it also travels over NVLink when a sink is set)
+    float x = (float)cx, y = (float)cy;
+    if (l != 0) {
+        x = __fmul_rn(x, L.scale);
+        y = __fmul_rn(y, L.scale);
+    }
+    uint32_t word = __float_as_uint(x);                       // pt.x
+    word = lane == 1 ? __float_as_uint(y) : word;             // pt.y
+    word = lane == 2 ? __float_as_uint(L.size) : word;        // size
+    word = lane == 3 ? __float_as_uint(angle) : word;         // angle
+    word = lane == 4 ? __float_as_uint((float)ORBX_KEY_R(key)) : word;   // response
+    word = lane == 5 ? (uint32_t)l : word;                    // octave
+    word = lane == 6 ? 0xffffffffu : word;                    // class_id = -1
+    if (lane < 7) {
+        static_assert(sizeof(orbx_keypoint) == 28, "cv::KeyPoint layout");
+        reinterpret_cast<uint32_t*>(kps + (size_t)frame * P.out_cap + out_row)[lane] = word;
+        if (sink.kps)
+            reinterpret_cast<uint32_t*>(sink.kps + (size_t)(sink.first_frame + frame) * P.out_cap + out_row)[lane] = word;
     }
 }
 
