@@ -498,7 +498,13 @@ k_octree(const __grid_constant__ OrbxPlan P, const uint32_t* __restrict__ cellcn
          int NC, int NCP2, int CW, int key_words /* shared-memory words per key buffer */,
          int level_base /* first level of this launch (per-level launches of the latency graph) */) {
     extern __shared__ __align__(16) uint32_t sm[];
+#ifdef OCT_FRAME_MAJOR
     const int level = level_base + blockIdx.x, frame = blockIdx.y;
+#else
+    // level-major launch order: the long level-0 CTAs of every frame start first, the short top levels fill
+    // the tail (longest-processing-time-first packing of the 8 very different per-level durations)
+    const int level = level_base + blockIdx.y, frame = blockIdx.x;
+#endif
     const OrbxLevel& L = P.lvl[level];
     const int tid = threadIdx.x, lane = orbx_lane(), warp = orbx_warp();
 
@@ -731,7 +737,11 @@ cudaError_t orbx_launch_octree(const OrbxPlan& P, const uint32_t* cellcnt, const
     OctLaunchCfg c = orbx_octree_cfg(P);
     // level < 0: one CTA per (level, frame); else only that level (the forked latency graph).  The
     // frame ticket counts P.nlevels CTAs either way: the last level to finish lays out the frame.
+#ifdef OCT_FRAME_MAJOR
     dim3 grid(level < 0 ? P.nlevels : 1, nframes);
+#else
+    dim3 grid(nframes, level < 0 ? P.nlevels : 1);
+#endif
     k_octree<<<grid, OCT_THREADS, c.smem, st>>>(P, cellcnt, cellkeys, keysA, keysB, surv, survcnt, lap, dest, header,
                                                frame_done, c.NC,
                                                c.NCP2, c.CW, c.key_words, level < 0 ? 0 : level);
