@@ -95,7 +95,10 @@ __device__ __forceinline__ void cp_async4(uint32_t saddr, const void* g) {
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-__global__ void __launch_bounds__(DESC_WARPS * 32)
+#ifndef DESC_MINB
+#define DESC_MINB 1
+#endif
+__global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB)
 k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t* __restrict__ pyr,
            const int32_t* __restrict__ header, const uint32_t* __restrict__ dest,
            orbx_keypoint* __restrict__ kps, uint8_t* __restrict__ desc, const OrbxSinkArgs sink) {
