@@ -446,77 +446,100 @@ cudaError_t orbm_launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStre
 }
 
 // ---- N3: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:330-404), batched --------------
-// One warp per map point (group of N observed descriptors).  The median of row i is the k-th smallest
+// A map point is a group of N observed descriptors.  The median of row i is the k-th smallest
 // (k = (int)(0.5 * (N - 1)), the reference's index into the sorted row, which includes d(i,i) = 0) of
-// d(i, .).  N <= 256: the warp takes one row at a time, lane j holds d(i, j), d(i, j + 32), .. in
-// registers (each distance computed once), and the k-th smallest comes from a 9-step binary search on
-// the value (distances are integers in [0, 256]) with one REDUX per step.  Larger groups: lane i
-// walks rows i, i + 32, .. and recomputes its row per search step from L1 (no N x N matrix is ever
-// stored).  The first row with the least median wins, as the reference's strict '<' scan does.
+// d(i, .).  The host cuts every group into work items of at most DIST_ITEM_ROWS rows (N <= 256) or 32
+// rows (larger groups), one warp per item, so that a 150-observation point does not leave one warp
+// running long after the two-observation points have finished.  N <= 256: the warp takes one row at a
+// time, lane j holds d(i, j), d(i, j + 32), .. in registers (each distance computed once), and the
+// k-th smallest comes from a 9-step binary search on the value (distances are integers in [0, 256])
+// with one vote or REDUX per step.  Larger groups: lane r takes row row0 + r and recomputes it per
+// search step from L1 (no N x N matrix is ever stored).  Every item folds (median << 20 | row) into
+// key[group] with atomicMin: the first row with the least median wins, as the reference's strict '<'
+// scan does.  key[] is preset to 0xffffffff, which also reads as the -1 of an empty group.
 #define DIST_CHUNKS 8
-__global__ void __launch_bounds__(128)
-k_distinctive(const uint4* __restrict__ desc, const int32_t* __restrict__ group_ptr, int ngroups,
-              int32_t* __restrict__ best) {
-    const int g = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
-    if (g >= ngroups) return;
-    const int lane = orbx_lane();
-    const int base = __ldg(group_ptr + g), N = __ldg(group_ptr + g + 1) - base;
-    if (N <= 0) {
-        if (lane == 0) best[g] = -1;
-        return;
+#ifndef DIST_ITEM_ROWS
+#define DIST_ITEM_ROWS 8
+#endif
+// NCH is a template parameter so that d[] stays in registers and the usual map point (a few to a few
+// tens of observations: NCH = 1) pays one compare + one vote per search step instead of eight compares
+// and a REDUX.
+template <int NCH>
+__device__ __forceinline__ uint32_t distinctive_rows(const uint4* __restrict__ D, int N, int k, int lane, int r0,
+                                                     int r1) {
+    uint32_t best = 0xffffffffu;
+    for (int i = r0; i < r1; ++i) {
+        const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
+        int d[NCH];
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            const int j = c * 32 + lane;
+            d[c] = j < N ? hamming256(a0, a1, D + 2 * j) : 0x7fff;
+        }
+        int lo = 0, hi = 256;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int cnt;
+            if (NCH == 1) {
+                cnt = __popc(__ballot_sync(ORBX_FULL, d[0] <= mid));
+            } else {
+                cnt = 0;
+#pragma unroll
+                for (int c = 0; c < NCH; ++c) cnt += d[c] <= mid ? 1 : 0;
+                cnt = __reduce_add_sync(ORBX_FULL, cnt);
+            }
+            if (cnt >= k + 1) hi = mid; else lo = mid + 1;
+        }
+        best = min(best, ((uint32_t)lo << 20) | (uint32_t)i);
     }
+    return best;
+}
+
+__global__ void __launch_bounds__(128)
+k_distinctive(const uint4* __restrict__ desc, const int32_t* __restrict__ group_ptr, const int2* __restrict__ items,
+              int nitems, uint32_t* __restrict__ key_out) {
+    const int it = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
+    if (it >= nitems) return;
+    const int lane = orbx_lane();
+    const int2 item = __ldg(items + it);   // x = group, y = first row of the item
+    const int g = item.x, r0 = item.y;
+    const int base = __ldg(group_ptr + g), N = __ldg(group_ptr + g + 1) - base;
     const uint4* D = desc + 2 * (size_t)base;
     const int k = (int)(0.5 * (double)(N - 1));
+    uint32_t key;
     if (N <= 32 * DIST_CHUNKS) {
-        const int nch = (N + 31) >> 5;
-        int bestMed = 0x7fffffff, bestIdx = 0;
-        for (int i = 0; i < N; ++i) {
+        const int r1 = min(N, r0 + DIST_ITEM_ROWS);
+        if (N <= 32) key = distinctive_rows<1>(D, N, k, lane, r0, r1);
+        else if (N <= 64) key = distinctive_rows<2>(D, N, k, lane, r0, r1);
+        else if (N <= 128) key = distinctive_rows<4>(D, N, k, lane, r0, r1);
+        else key = distinctive_rows<DIST_CHUNKS>(D, N, k, lane, r0, r1);
+    } else {
+        key = 0xffffffffu;
+        const int i = r0 + lane;
+        if (i < N) {
             const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
-            int d[DIST_CHUNKS];
-#pragma unroll
-            for (int c = 0; c < DIST_CHUNKS; ++c) {
-                const int j = c * 32 + lane;
-                d[c] = (c < nch && j < N) ? hamming256(a0, a1, D + 2 * j) : 0x7fff;
-            }
+            // smallest v with #{j : d(i,j) <= v} >= k + 1
             int lo = 0, hi = 256;
             while (lo < hi) {
                 const int mid = (lo + hi) >> 1;
                 int cnt = 0;
-#pragma unroll
-                for (int c = 0; c < DIST_CHUNKS; ++c) cnt += d[c] <= mid ? 1 : 0;
-                cnt = __reduce_add_sync(ORBX_FULL, cnt);
+                for (int j = 0; j < N; ++j) cnt += hamming256(a0, a1, D + 2 * j) <= mid ? 1 : 0;
                 if (cnt >= k + 1) hi = mid; else lo = mid + 1;
             }
-            if (lo < bestMed) {
-                bestMed = lo;
-                bestIdx = i;
-            }
+            key = ((uint32_t)lo << 20) | (uint32_t)i;
         }
-        if (lane == 0) best[g] = bestIdx;
-        return;
+        key = __reduce_min_sync(ORBX_FULL, key);
     }
-    uint32_t key = 0xffffffffu;
-    for (int i = lane; i < N; i += 32) {
-        const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
-        // smallest v with #{j : d(i,j) <= v} >= k + 1
-        int lo = 0, hi = 256;
-        while (lo < hi) {
-            const int mid = (lo + hi) >> 1;
-            int cnt = 0;
-            for (int j = 0; j < N; ++j) cnt += hamming256(a0, a1, D + 2 * j) <= mid ? 1 : 0;
-            if (cnt >= k + 1) hi = mid; else lo = mid + 1;
-        }
-        key = min(key, ((uint32_t)lo << 20) | (uint32_t)i);
-    }
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) key = min(key, __shfl_xor_sync(ORBX_FULL, key, d));
-    if (lane == 0) best[g] = (int32_t)(key & 0xfffffu);
+    if (lane == 0) atomicMin(key_out + g, key);
 }
 
-cudaError_t orbm_launch_distinctive(const uint8_t* desc, const int32_t* group_ptr, int ngroups, int32_t* best,
-                                    cudaStream_t st) {
-    if (ngroups <= 0) return cudaSuccess;
-    k_distinctive<<<(ngroups + 3) / 4, 128, 0, st>>>(reinterpret_cast<const uint4*>(desc), group_ptr, ngroups, best);
+int orbm_distinctive_item_rows() { return DIST_ITEM_ROWS; }
+
+cudaError_t orbm_launch_distinctive(const uint8_t* desc, const int32_t* group_ptr, const int32_t* items, int nitems,
+                                    uint32_t* key, cudaStream_t st) {
+    if (nitems <= 0) return cudaSuccess;
+    k_distinctive<<<(nitems + 3) / 4, 128, 0, st>>>(reinterpret_cast<const uint4*>(desc), group_ptr,
+                                                    reinterpret_cast<const int2*>(items), nitems, key);
     return cudaGetLastError();
 }
 

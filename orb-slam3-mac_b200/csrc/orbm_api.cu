@@ -85,6 +85,7 @@ struct orbm_context {
     DevBuf q, t, rowptr, cand, dist, aux1, aux2, kl, kr, sc, isc, ur, dp, sd, gstart, gitems, gcell, aq, acnt;
     std::vector<int32_t> h_rowptr, h_cand;   // candidate lists of the last layer-2 search
     std::vector<uint16_t> hdist;     // distances of the last layer-2 search
+    std::vector<int32_t> h_items;    // work items of the last orbm_distinctive_descriptors call
     long long last_pairs = 0;        // number of (query, candidate) pairs of the last search
 };
 
