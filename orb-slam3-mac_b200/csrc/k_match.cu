@@ -457,6 +457,9 @@ cudaError_t orbm_launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStre
 // search step from L1 (no N x N matrix is ever stored).  Every item folds (median << 20 | row) into
 // key[group] with atomicMin: the first row with the least median wins, as the reference's strict '<'
 // scan does.  key[] is preset to 0xffffffff, which also reads as the -1 of an empty group.
+#ifndef BOW_TOPK
+#define BOW_TOPK 4
+#endif
 #define DIST_CHUNKS 8
 #ifndef DIST_ITEM_ROWS
 #define DIST_ITEM_ROWS 8
@@ -540,6 +543,66 @@ cudaError_t orbm_launch_distinctive(const uint8_t* desc, const int32_t* group_pt
     if (nitems <= 0) return cudaSuccess;
     k_distinctive<<<(nitems + 3) / 4, 128, 0, st>>>(reinterpret_cast<const uint4*>(desc), group_ptr,
                                                     reinterpret_cast<const int2*>(items), nitems, key);
+    return cudaGetLastError();
+}
+
+// ---- SearchByBoW (both overloads): per-row distances + the K best candidates ------------------------
+// Row r = one feature of side A inside a vocabulary node both sides share; its candidates are side B's
+// features of that node, read in place from B's node_items (no expanded candidate list is uploaded).
+// rows[r] = {feature of A, first candidate in items[], candidate count, first slot in dist[]}.  One
+// warp per row: every distance is written to dist[] (the host's full-scan fallback), and the
+// BOW_TOPK smallest (distance << 20 | position in the row) of the candidates that pass the static gate
+// go to topk[r * BOW_TOPK ..], ascending, 0xffffffff = none.  Ascending (distance, position) is the
+// order in which the reference's strict '<' scans pick the best and second-best candidate, so the host
+// replays a row from these few keys unless most of them were matched by earlier rows.
+__global__ void __launch_bounds__(128)
+k_bow_topk(const uint4* __restrict__ A, const uint4* __restrict__ B, const uint32_t* __restrict__ items,
+           const int4* __restrict__ rows, int nrows, const uint8_t* __restrict__ gate_b,
+           uint16_t* __restrict__ dist, uint32_t* __restrict__ topk) {
+    const int r = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
+    if (r >= nrows) return;
+    const int lane = orbx_lane();
+    const int4 row = __ldg(rows + r);
+    const int len = row.z;
+    const uint32_t* it = items + row.y;
+    uint16_t* drow = dist + row.w;
+    const uint4 a0 = __ldg(A + 2 * (size_t)row.x), a1 = __ldg(A + 2 * (size_t)row.x + 1);
+    uint32_t mine = 0xffffffffu;   // key of position `lane` (rows of at most 32 candidates: the usual case)
+    for (int pos = lane; pos < len; pos += 32) {
+        const uint32_t f = __ldg(it + pos);
+        const int d = hamming256(a0, a1, B + 2 * (size_t)f);
+        drow[pos] = (uint16_t)d;
+        if (pos < 32 && (!gate_b || __ldg(gate_b + f))) mine = ((uint32_t)d << 20) | (uint32_t)pos;
+    }
+    uint32_t prev = 0;
+    for (int k = 0; k < BOW_TOPK; ++k) {
+        uint32_t m = mine;
+        if (len > 32) {   // long row: this lane's least key above the last one taken, from its own dist[] writes
+            m = 0xffffffffu;
+            for (int pos = lane; pos < len; pos += 32) {
+                const uint32_t key = ((uint32_t)drow[pos] << 20) | (uint32_t)pos;
+                if ((k == 0 || key > prev) && key < m && (!gate_b || __ldg(gate_b + __ldg(it + pos)))) m = key;
+            }
+        }
+        const uint32_t sel = __reduce_min_sync(ORBX_FULL, m);
+        if (lane == 0) topk[(size_t)r * BOW_TOPK + k] = sel;
+        if (mine == sel) mine = 0xffffffffu;
+        prev = sel;
+        if (sel == 0xffffffffu) {
+            if (lane == 0)
+                for (int j = k + 1; j < BOW_TOPK; ++j) topk[(size_t)r * BOW_TOPK + j] = 0xffffffffu;
+            break;
+        }
+    }
+}
+
+int orbm_bow_topk_k() { return BOW_TOPK; }
+
+cudaError_t orbm_launch_bow_topk(const uint8_t* A, const uint8_t* B, const uint32_t* items, const int32_t* rows, int nrows,
+                                 const uint8_t* gate_b, uint16_t* dist, uint32_t* topk, cudaStream_t st) {
+    if (nrows <= 0) return cudaSuccess;
+    k_bow_topk<<<(nrows + 3) / 4, 128, 0, st>>>(reinterpret_cast<const uint4*>(A), reinterpret_cast<const uint4*>(B), items,
+                                                reinterpret_cast<const int4*>(rows), nrows, gate_b, dist, topk);
     return cudaGetLastError();
 }
 

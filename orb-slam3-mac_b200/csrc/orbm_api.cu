@@ -77,6 +77,26 @@ struct DevBuf {
 
 }  // namespace
 
+// Developer probe (make EXTRA=-DORBM_TRACE): host-side phase times of a call, printed to stderr.
+#ifdef ORBM_TRACE
+#include <chrono>
+struct PhaseTimer {
+    const char* what;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    explicit PhaseTimer(const char* w) : what(w) {}
+    void mark(const char* phase) {
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[orbm %s] %s %.1f us\n", what, phase, std::chrono::duration<double, std::micro>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+#define ORBM_PHASE_BEGIN(w) PhaseTimer _pt(w)
+#define ORBM_PHASE(p) _pt.mark(p)
+#else
+#define ORBM_PHASE_BEGIN(w) do {} while (0)
+#define ORBM_PHASE(p) do {} while (0)
+#endif
+
 struct orbm_context {
     int device = 0;
     cudaStream_t st = nullptr;
@@ -85,6 +105,7 @@ struct orbm_context {
     DevBuf q, t, rowptr, cand, dist, aux1, aux2, kl, kr, sc, isc, ur, dp, sd, gstart, gitems, gcell, aq, acnt;
     std::vector<int32_t> h_rowptr, h_cand;   // candidate lists of the last layer-2 search
     std::vector<uint16_t> hdist;     // distances of the last layer-2 search
+    std::vector<uint32_t> h_topk;    // k_bow_topk's keys of the last SearchByBoW
     std::vector<int32_t> h_items;    // work items of the last orbm_distinctive_descriptors call
     long long last_pairs = 0;        // number of (query, candidate) pairs of the last search
 };
@@ -884,13 +905,17 @@ int orbm_search_by_projection_frames_stereo(orbm_context* c, const orbm_frame_vi
     return nmatches;
 }
 
-int orbm_search_by_bow(orbm_context* c, const orbm_bow_view* KF, const uint8_t* kf_mp_ok, const orbm_bow_view* F,
-                       int f_nleft, float nn_ratio, int check_orientation, int32_t* matches) {
+// SearchByBoW(KeyFrame*, Frame&) with every (row, candidate) pair expanded and scanned on the host: the
+// fisheye-rig form (f_nleft != -1, separate left / right bests); orbm_search_by_bow (orbm_n3.inc) answers
+// the usual form from k_bow_topk.
+static int search_by_bow_full(orbm_context* c, const orbm_bow_view* KF, const uint8_t* kf_mp_ok, const orbm_bow_view* F,
+                              int f_nleft, float nn_ratio, int check_orientation, int32_t* matches) {
     if (!c || !KF || !F || !matches || KF->n < 0 || F->n < 0 || KF->nnodes < 0 || F->nnodes < 0 ||
         (KF->n && (!KF->keys || !KF->desc || !kf_mp_ok)) || (F->n && (!F->keys || !F->desc)) ||
         (KF->nnodes && (!KF->node_ids || !KF->node_ptr || !KF->node_items)) ||
         (F->nnodes && (!F->node_ids || !F->node_ptr || !F->node_items)))
         return orbx_set_error(ORBX_E_BAD_ARG, "bad argument");
+    ORBM_PHASE_BEGIN("search_by_bow");
     for (int i = 0; i < F->n; ++i) matches[i] = -1;
     // pass 1: walk the two sorted feature vectors like the reference (:291-449; lower_bound on a
     // sorted key array) and list every (keyframe feature, frame feature) pair that shares a node
@@ -927,14 +952,17 @@ int orbm_search_by_bow(orbm_context* c, const orbm_bow_view* KF, const uint8_t* 
     }
     // the CSR kernel takes one query descriptor per row: gather the rows' keyframe descriptors
     const int nrows = (int)row_q.size();
+    ORBM_PHASE("csr");
     std::vector<uint8_t> qdesc((size_t)nrows * 32);
     for (int r = 0; r < nrows; ++r) memcpy(&qdesc[(size_t)r * 32], KF->desc + (size_t)row_q[r] * 32, 32);
     c->hdist.assign(cand.size(), 0);
+    ORBM_PHASE("gather");
     int rc;
     if (!cand.empty() && (rc = orbm_hamming_csr(c, qdesc.data(), nrows, F->desc, F->n, row_ptr.data(), cand.data(),
                                                 (int)cand.size(), c->hdist.data())))
         return rc;
     c->last_pairs = (long long)cand.size();
+    ORBM_PHASE("device");
     // pass 2: the reference's accept loop over the precomputed distances
     std::vector<int> rotHist[ORBM_HISTO_LENGTH];
     const float factor = 1.0f / ORBM_HISTO_LENGTH;
@@ -990,6 +1018,7 @@ int orbm_search_by_bow(orbm_context* c, const orbm_bow_view* KF, const uint8_t* 
             }
         }
     }
+    ORBM_PHASE("replay");
     return nmatches;
 }
 

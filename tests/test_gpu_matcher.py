@@ -389,6 +389,54 @@ def test_search_by_bow_keyframe_frame(mo, extract, check, nleft):
     assert n > 150 and (matches >= 0).sum() == n
 
 
+def _contested_node_case(n_a, n_b, step, seed):
+    """One vocabulary node in which n_a identical side-A descriptors compete for side-B descriptors at
+    Hamming distances 0, step, 2 * step, ..: row i finds the i nearest candidates already taken, so the
+    rows past the device's top-K list must be answered by the full scan of the row."""
+    from orb_slam3_mac_b200._lib import KP_DTYPE
+    from orb_slam3_mac_b200.matcher import BowSide
+    rng = np.random.default_rng(seed)
+    x = rng.integers(0, 256, 32, dtype=np.uint8)
+    da = np.repeat(x[None], n_a, axis=0)
+    bits = np.unpackbits(np.repeat(x[None], n_b, axis=0), axis=1)
+    for j in range(n_b):
+        flip = min(j * step, 256)
+        bits[j, :flip] ^= 1
+    db = np.packbits(bits, axis=1)
+    order = rng.permutation(n_b)            # candidates are not sorted by distance inside the node
+    db = db[order]
+
+    def keys(n):
+        k = np.zeros(n, KP_DTYPE)
+        k["x"], k["y"] = rng.uniform(20, 700, n), rng.uniform(20, 400, n)
+        k["angle"] = rng.uniform(0, 359, n).astype(np.float32)
+        return k
+    A = BowSide(keys(n_a), da, {7: list(range(n_a))})
+    B = BowSide(keys(n_b), db, {7: list(rng.permutation(n_b))})
+    return A, B
+
+
+@pytest.mark.parametrize("n_a,n_b,step", [(12, 10, 1), (12, 10, 9), (40, 70, 3), (6, 3, 2)])
+def test_search_by_bow_contested_node_full_scan(mo, n_a, n_b, step):
+    """Both SearchByBoW overloads when earlier rows have taken a row's nearest candidates (more of them than the
+    K keys k_bow_topk returns), with rows longer than a warp (70 candidates) and shorter than K (3)."""
+    from orb_slam3_mac_b200.matcher import ORBmatcher
+    A, B = _contested_node_case(n_a, n_b, step, 3 * n_a + step)
+    ok_a, ok_b = np.ones(n_a, np.uint8), np.ones(n_b, np.uint8)
+    ok_b[::7] = 0
+    for check in (False, True):
+        m = ORBmatcher(0.8, check)
+        n, matches = m.SearchByBoW(A, ok_a, B, -1)
+        on, omatches = mo.search_by_bow(A, ok_a, B, -1, 0.8, check)
+        assert n == on and np.array_equal(matches, omatches)
+        n2, m12 = m.SearchByBoWKF(A, ok_a, B, ok_b, -1, n_b - 2)
+        on2, om12 = mo.search_by_bow_kf(A, ok_a, B, ok_b, -1, n_b - 2, 0.8, check)
+        m.close()
+        assert n2 == on2 and np.array_equal(m12, om12)
+        if not check and step < 9:
+            assert n >= min(4, n_b)   # at least as many accepted rows as the top-K list is long
+
+
 class _ProductBackend:
     """The CUDA matcher behind the oracle's method names (tests/golden/match_cases.py)."""
 
