@@ -279,7 +279,9 @@ int orbm_search_by_sim3(orbm_context* c, const orbm_frame_view* KF1, const orbm_
 
 /* The camera model's pair test of SearchForTriangulation: GeometricCamera::epipolarConstrain
  * (src/ORBmatcher.cc:1112) or matchAndtriangulate (:1316) for KF1 feature idx1 and KF2 feature idx2;
- * non-zero = the pair is geometrically consistent. */
+ * non-zero = the pair is geometrically consistent.  It must be a pure predicate of (idx1, idx2): the
+ * library calls it for a row's candidates in order of preference (nearest first) until one passes, which
+ * is a subset of the pairs the reference's scan would test, in another order. */
 typedef int (*orbm_pair_test)(void* user, int32_t idx1, int32_t idx2);
 
 /* SearchForTriangulation, src/ORBmatcher.cc:969-1210 (epipolarConstrain, bOnlyStereo, bCoarse) and

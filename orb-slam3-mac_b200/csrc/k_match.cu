@@ -546,19 +546,21 @@ cudaError_t orbm_launch_distinctive(const uint8_t* desc, const int32_t* group_pt
     return cudaGetLastError();
 }
 
-// ---- SearchByBoW (both overloads): per-row distances + the K best candidates ------------------------
+// ---- SearchByBoW (both overloads), SearchForTriangulation: per-row distances + the K best candidates ----
 // Row r = one feature of side A inside a vocabulary node both sides share; its candidates are side B's
 // features of that node, read in place from B's node_items (no expanded candidate list is uploaded).
 // rows[r] = {feature of A, first candidate in items[], candidate count, first slot in dist[]}.  One
-// warp per row: every distance is written to dist[] (the host's full-scan fallback), and the
-// BOW_TOPK smallest (distance << 20 | position in the row) of the candidates that pass the static gate
-// go to topk[r * BOW_TOPK ..], ascending, 0xffffffff = none.  Ascending (distance, position) is the
-// order in which the reference's strict '<' scans pick the best and second-best candidate, so the host
-// replays a row from these few keys unless most of them were matched by earlier rows.
+// warp per row: every distance is written to dist[] (the host's full-scan fallback), and the K
+// smallest keys (distance << 20 | rank) of the candidates that pass the static gate and max_dist go to
+// topk[r * K ..], ascending, 0xffffffff = none.  rank = position in the row (SearchByBoW: strict '<'
+// scans, the first of equal distances wins) or len - 1 - position (SearchForTriangulation: its
+// 'dist > bestDist -> skip' scan lets the last of equal distances win).  Ascending keys are the order in
+// which the reference's scan would prefer the candidates, so the host replays a row from these few
+// keys unless they are all refused (matched by earlier rows / failing the epipolar test).
 __global__ void __launch_bounds__(128)
 k_bow_topk(const uint4* __restrict__ A, const uint4* __restrict__ B, const uint32_t* __restrict__ items,
-           const int4* __restrict__ rows, int nrows, const uint8_t* __restrict__ gate_b,
-           uint16_t* __restrict__ dist, uint32_t* __restrict__ topk) {
+           const int4* __restrict__ rows, int nrows, const uint8_t* __restrict__ gate_b, int K, int max_dist,
+           int last_wins, uint16_t* __restrict__ dist, uint32_t* __restrict__ topk) {
     const int r = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
     if (r >= nrows) return;
     const int lane = orbx_lane();
@@ -572,25 +574,27 @@ k_bow_topk(const uint4* __restrict__ A, const uint4* __restrict__ B, const uint3
         const uint32_t f = __ldg(it + pos);
         const int d = hamming256(a0, a1, B + 2 * (size_t)f);
         drow[pos] = (uint16_t)d;
-        if (pos < 32 && (!gate_b || __ldg(gate_b + f))) mine = ((uint32_t)d << 20) | (uint32_t)pos;
+        if (pos < 32 && d <= max_dist && (!gate_b || __ldg(gate_b + f)))
+            mine = ((uint32_t)d << 20) | (uint32_t)(last_wins ? len - 1 - pos : pos);
     }
     uint32_t prev = 0;
-    for (int k = 0; k < BOW_TOPK; ++k) {
+    for (int k = 0; k < K; ++k) {
         uint32_t m = mine;
         if (len > 32) {   // long row: this lane's least key above the last one taken, from its own dist[] writes
             m = 0xffffffffu;
             for (int pos = lane; pos < len; pos += 32) {
-                const uint32_t key = ((uint32_t)drow[pos] << 20) | (uint32_t)pos;
-                if ((k == 0 || key > prev) && key < m && (!gate_b || __ldg(gate_b + __ldg(it + pos)))) m = key;
+                const int d = drow[pos];
+                const uint32_t key = ((uint32_t)d << 20) | (uint32_t)(last_wins ? len - 1 - pos : pos);
+                if ((k == 0 || key > prev) && key < m && d <= max_dist && (!gate_b || __ldg(gate_b + __ldg(it + pos)))) m = key;
             }
         }
         const uint32_t sel = __reduce_min_sync(ORBX_FULL, m);
-        if (lane == 0) topk[(size_t)r * BOW_TOPK + k] = sel;
+        if (lane == 0) topk[(size_t)r * K + k] = sel;
         if (mine == sel) mine = 0xffffffffu;
         prev = sel;
         if (sel == 0xffffffffu) {
             if (lane == 0)
-                for (int j = k + 1; j < BOW_TOPK; ++j) topk[(size_t)r * BOW_TOPK + j] = 0xffffffffu;
+                for (int j = k + 1; j < K; ++j) topk[(size_t)r * K + j] = 0xffffffffu;
             break;
         }
     }
@@ -599,10 +603,12 @@ k_bow_topk(const uint4* __restrict__ A, const uint4* __restrict__ B, const uint3
 int orbm_bow_topk_k() { return BOW_TOPK; }
 
 cudaError_t orbm_launch_bow_topk(const uint8_t* A, const uint8_t* B, const uint32_t* items, const int32_t* rows, int nrows,
-                                 const uint8_t* gate_b, uint16_t* dist, uint32_t* topk, cudaStream_t st) {
+                                 const uint8_t* gate_b, int K, int max_dist, int last_wins, uint16_t* dist,
+                                 uint32_t* topk, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
     k_bow_topk<<<(nrows + 3) / 4, 128, 0, st>>>(reinterpret_cast<const uint4*>(A), reinterpret_cast<const uint4*>(B), items,
-                                                reinterpret_cast<const int4*>(rows), nrows, gate_b, dist, topk);
+                                                reinterpret_cast<const int4*>(rows), nrows, gate_b, K, max_dist,
+                                                last_wins, dist, topk);
     return cudaGetLastError();
 }
 

@@ -437,6 +437,33 @@ def test_search_by_bow_contested_node_full_scan(mo, n_a, n_b, step):
             assert n >= min(4, n_b)   # at least as many accepted rows as the top-K list is long
 
 
+@pytest.mark.parametrize("n_a,n_b,step,refuse", [(5, 30, 1, 12), (5, 30, 0, 20), (4, 70, 0, 0), (3, 6, 2, 5), (6, 40, 1, 40)])
+def test_search_for_triangulation_refused_candidates(mo, n_a, n_b, step, refuse):
+    """SearchForTriangulation when the pair test refuses a row's nearest candidates (more of them than the keys
+    k_bow_topk returns: full scan of the row), and with equal distances, where the reference's
+    'dist > bestDist -> continue' scan keeps the LAST accepted candidate of the node."""
+    from orb_slam3_mac_b200.matcher import ORBmatcher
+    A, B = _contested_node_case(n_a, n_b, step, 11 * n_a + refuse)
+    da = np.unpackbits(A.desc, axis=1).astype(np.int32)
+    db = np.unpackbits(B.desc, axis=1).astype(np.int32)
+    dist = (da[:, None, :] != db[None, :, :]).sum(axis=2)
+    order = np.argsort(dist, axis=1, kind="stable")
+    table = np.ones((n_a, n_b), np.uint8)
+    for i in range(n_a):
+        table[i, order[i, :refuse]] = 0      # the nearest `refuse` candidates fail the epipolar test
+        table[i, order[i, refuse::3]] = 0    # and every third of the rest
+    has1, has2 = np.zeros(n_a, np.uint8), np.zeros(n_b, np.uint8)
+    has2[1::5] = 1
+    for check in (False, True):
+        m = ORBmatcher(0.8, check)
+        n, m12 = m.SearchForTriangulation(A, has1, B, has2, pair_test=lambda a, b: table[a, b])
+        m.close()
+        on, om12 = mo.search_for_triangulation(A, has1, None, B, has2, None, False, None, None, table, None, None, check)
+        assert n == on and np.array_equal(m12, om12)
+    if refuse < n_b and step <= 1:
+        assert on > 0 or check
+
+
 class _ProductBackend:
     """The CUDA matcher behind the oracle's method names (tests/golden/match_cases.py)."""
 
