@@ -404,6 +404,7 @@ int check_view(const orbm_frame_view* F) {
 // c->h_rowptr / c->h_cand and the distances in c->hdist.
 int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vector<orbm_area_query>& Q,
                       const uint8_t* qdesc, int n_qdesc) {
+    ORBM_PHASE_BEGIN("device_candidates");
     const int nq = (int)Q.size();
     c->h_rowptr.assign(nq + 1, 0);
     c->h_cand.clear();
@@ -422,6 +423,7 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     M_TRY(cudaMemcpyAsync(c->t.p, F->desc, (size_t)F->n * 32, cudaMemcpyHostToDevice, c->st));
     if (qdesc) M_TRY(cudaMemcpyAsync(c->q.p, qdesc, (size_t)n_qdesc * 32, cudaMemcpyHostToDevice, c->st));
     M_TRY(cudaMemcpyAsync(c->aq.p, Q.data(), (size_t)nq * sizeof(orbm_area_query), cudaMemcpyHostToDevice, c->st));
+    ORBM_PHASE("uploads");
     const orbx_keypoint* dk = (const orbx_keypoint*)c->kl.p;
     M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_grid_build(dk, F->n, F->min_x, F->min_y, F->grid_w_inv, F->grid_h_inv, (int32_t*)c->gstart.p,
@@ -432,6 +434,7 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     M_TRY(cudaMemcpyAsync(c->h_rowptr.data(), c->rowptr.p, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaStreamSynchronize(c->st));
     const int nnz = c->h_rowptr[nq];
+    ORBM_PHASE("grid + count + sync");
     c->last_pairs = nnz;
     if (nnz == 0) return ORBX_OK;
     if ((r = c->cand.ensure((size_t)nnz * 4)) || (r = c->dist.ensure((size_t)nnz * 2))) return r;
@@ -446,6 +449,7 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     M_TRY(cudaMemcpyAsync(c->h_cand.data(), c->cand.p, (size_t)nnz * 4, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaMemcpyAsync(c->hdist.data(), c->dist.p, (size_t)nnz * 2, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaStreamSynchronize(c->st));
+    ORBM_PHASE("fill + download");
     return ORBX_OK;
 }
 
@@ -529,6 +533,7 @@ int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, 
     int rc = check_view(F);
     if (rc) return rc;
     if (!c || m < 0 || (m && (!mps || !mp_desc)) || !kp_obs || !kp_match) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    ORBM_PHASE_BEGIN("search_by_projection_points");
     for (int i = 0; i < F->n; ++i) kp_match[i] = -1;
     const bool bFactor = th != 1.0;
     // pass 1: window queries (state independent); candidates + distances come from the device
@@ -547,7 +552,9 @@ int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, 
         rad[i] = r * F->scale_factors[p.level];
         q = orbm_area_query{p.proj_x, p.proj_y, rad[i], p.level - 1, p.level, 1, i};
     }
+    ORBM_PHASE("queries");
     if ((rc = device_candidates(c, F, Q, mp_desc, m))) return rc;
+    ORBM_PHASE("device_candidates");
     const std::vector<int32_t>& row_ptr = c->h_rowptr;
     const std::vector<int32_t>& cand = c->h_cand;
     // pass 2: the reference's accept loop, original order (:54-147)
@@ -584,6 +591,7 @@ int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, 
             }
         }
     }
+    ORBM_PHASE("replay");
     return nmatches;
 }
 
