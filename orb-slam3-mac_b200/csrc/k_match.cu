@@ -612,6 +612,55 @@ cudaError_t orbm_launch_bow_topk(const uint8_t* A, const uint8_t* B, const uint3
     return cudaGetLastError();
 }
 
+// ---- window searches: the K best candidates of every CSR row -----------------------------------------
+// After k_area<1> has written a row's candidates (GetFeaturesInArea order) and distances, one warp per
+// row returns the K smallest (distance << 20 | position) keys, ascending, and the candidate each one
+// names (0xffffffff / -1 = none): the order in which a strict '<' best / second-best scan prefers the
+// candidates, so the host's accept loop reads K entries per row instead of the whole row.
+__global__ void __launch_bounds__(128)
+k_csr_topk(const int32_t* __restrict__ row_ptr, const int32_t* __restrict__ cand, const uint16_t* __restrict__ dist,
+           int nrows, int K, uint32_t* __restrict__ keys, int32_t* __restrict__ key_cand) {
+    const int r = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
+    if (r >= nrows) return;
+    const int lane = orbx_lane();
+    const int b = __ldg(row_ptr + r), len = __ldg(row_ptr + r + 1) - b;
+    uint32_t mine = 0xffffffffu;
+    if (lane < len) mine = ((uint32_t)__ldg(dist + b + lane) << 20) | (uint32_t)lane;
+    uint32_t prev = 0;
+    for (int k = 0; k < K; ++k) {
+        uint32_t m = mine;
+        if (len > 32) {
+            m = 0xffffffffu;
+            for (int pos = lane; pos < len; pos += 32) {
+                const uint32_t key = ((uint32_t)__ldg(dist + b + pos) << 20) | (uint32_t)pos;
+                if ((k == 0 || key > prev) && key < m) m = key;
+            }
+        }
+        const uint32_t sel = __reduce_min_sync(ORBX_FULL, m);
+        if (mine == sel) mine = 0xffffffffu;
+        prev = sel;
+        if (lane == 0) {
+            keys[(size_t)r * K + k] = sel;
+            key_cand[(size_t)r * K + k] = sel == 0xffffffffu ? -1 : __ldg(cand + b + (int)(sel & 0xfffffu));
+        }
+        if (sel == 0xffffffffu) {
+            if (lane == 0)
+                for (int j = k + 1; j < K; ++j) {
+                    keys[(size_t)r * K + j] = 0xffffffffu;
+                    key_cand[(size_t)r * K + j] = -1;
+                }
+            break;
+        }
+    }
+}
+
+cudaError_t orbm_launch_csr_topk(const int32_t* row_ptr, const int32_t* cand, const uint16_t* dist, int nrows, int K,
+                                 uint32_t* keys, int32_t* key_cand, cudaStream_t st) {
+    if (nrows <= 0) return cudaSuccess;
+    k_csr_topk<<<(nrows + 3) / 4, 128, 0, st>>>(row_ptr, cand, dist, nrows, K, keys, key_cand);
+    return cudaGetLastError();
+}
+
 // ---- N4 (second half): DBoW2 TemplatedVocabulary<FORB>::transform, the tree descent ---------------
 // (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1230-1275, called per feature by transform(features,
 // v, fv, levelsup) :1139-1217 from Frame::ComputeBoW, src/Frame.cc:729-736).  One warp per feature:

@@ -32,6 +32,8 @@ cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* star
                                   float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
                                   int nq, const int32_t* row_ptr, const uint8_t* qdesc, const uint8_t* tdesc,
                                   int32_t* cand, uint16_t* dist, cudaStream_t st);
+cudaError_t orbm_launch_csr_topk(const int32_t* row_ptr, const int32_t* cand, const uint16_t* dist, int nrows, int K,
+                                 uint32_t* keys, int32_t* key_cand, cudaStream_t st);
 cudaError_t orbm_launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t st);
 cudaError_t orbm_launch_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
                              int32_t* dist, cudaStream_t st);
@@ -97,6 +99,10 @@ struct PhaseTimer {
 #define ORBM_PHASE(p) do {} while (0)
 #endif
 
+#ifndef INIT_TOPK
+#define INIT_TOPK 4   // keys per row of SearchForInitialization (k_csr_topk)
+#endif
+
 struct orbm_context {
     int device = 0;
     cudaStream_t st = nullptr;
@@ -105,7 +111,9 @@ struct orbm_context {
     DevBuf q, t, rowptr, cand, dist, aux1, aux2, kl, kr, sc, isc, ur, dp, sd, gstart, gitems, gcell, aq, acnt;
     std::vector<int32_t> h_rowptr, h_cand;   // candidate lists of the last layer-2 search
     std::vector<uint16_t> hdist;     // distances of the last layer-2 search
-    std::vector<uint32_t> h_topk;    // k_bow_topk's keys of the last SearchByBoW
+    std::vector<uint32_t> h_topk;    // k_bow_topk's / k_csr_topk's keys of the last search
+    std::vector<int32_t> h_topc;     // k_csr_topk: the candidate each key names
+    bool have_full = true;           // h_cand / hdist hold the last search's full lists (top-K mode fetches them lazily)
     std::vector<int32_t> h_items;    // work items of the last orbm_distinctive_descriptors call
     long long last_pairs = 0;        // number of (query, candidate) pairs of the last search
 };
@@ -402,13 +410,18 @@ int check_view(const orbm_frame_view* F) {
 // Candidate generation + distances of a search on the device (N2): grid build, window queries in
 // the reference's order, Hamming distance per (query, candidate).  Leaves the CSR lists in
 // c->h_rowptr / c->h_cand and the distances in c->hdist.
+// topk > 0: the rows' full lists stay on the device (window_full_lists() fetches them on demand) and the
+// host gets k_csr_topk's topk best (distance, position) keys + candidates per row instead.
 int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vector<orbm_area_query>& Q,
-                      const uint8_t* qdesc, int n_qdesc) {
+                      const uint8_t* qdesc, int n_qdesc, int topk = 0) {
     ORBM_PHASE_BEGIN("device_candidates");
     const int nq = (int)Q.size();
     c->h_rowptr.assign(nq + 1, 0);
     c->h_cand.clear();
     c->hdist.clear();
+    c->have_full = true;
+    c->h_topk.assign((size_t)nq * topk, 0xffffffffu);
+    c->h_topc.assign((size_t)nq * topk, -1);
     c->last_pairs = 0;
     if (nq == 0 || F->n == 0) return ORBX_OK;
     M_TRY(cudaSetDevice(c->device));
@@ -442,6 +455,19 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
                                 F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
                                 (const int32_t*)c->rowptr.p, qdesc ? (const uint8_t*)c->q.p : (const uint8_t*)c->t.p,
                                 (const uint8_t*)c->t.p, (int32_t*)c->cand.p, (uint16_t*)c->dist.p, c->st));
+    if (topk > 0) {
+        if ((r = c->aux1.ensure((size_t)nq * topk * 4)) || (r = c->aux2.ensure((size_t)nq * topk * 4))) return r;
+        M_TRY(orbm_launch_csr_topk((const int32_t*)c->rowptr.p, (const int32_t*)c->cand.p, (const uint16_t*)c->dist.p, nq,
+                                   topk, (uint32_t*)c->aux1.p, (int32_t*)c->aux2.p, c->st));
+        M_TRY(cudaEventRecord(c->ev1, c->st));
+        c->timed = true;
+        c->have_full = false;
+        M_TRY(cudaMemcpyAsync(c->h_topk.data(), c->aux1.p, (size_t)nq * topk * 4, cudaMemcpyDeviceToHost, c->st));
+        M_TRY(cudaMemcpyAsync(c->h_topc.data(), c->aux2.p, (size_t)nq * topk * 4, cudaMemcpyDeviceToHost, c->st));
+        M_TRY(cudaStreamSynchronize(c->st));
+        ORBM_PHASE("fill + topk + download");
+        return ORBX_OK;
+    }
     M_TRY(cudaEventRecord(c->ev1, c->st));
     c->timed = true;
     c->h_cand.resize(nnz);
@@ -450,6 +476,20 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     M_TRY(cudaMemcpyAsync(c->hdist.data(), c->dist.p, (size_t)nnz * 2, cudaMemcpyDeviceToHost, c->st));
     M_TRY(cudaStreamSynchronize(c->st));
     ORBM_PHASE("fill + download");
+    return ORBX_OK;
+}
+
+// The full candidate / distance lists of the last top-K search (c->h_cand, c->hdist), fetched on the first
+// row that needs them.
+int window_full_lists(orbm_context* c) {
+    if (c->have_full) return ORBX_OK;
+    const int nnz = c->h_rowptr.back();
+    c->h_cand.resize(nnz);
+    c->hdist.resize(nnz);
+    M_TRY(cudaMemcpyAsync(c->h_cand.data(), c->cand.p, (size_t)nnz * 4, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaMemcpyAsync(c->hdist.data(), c->dist.p, (size_t)nnz * 2, cudaMemcpyDeviceToHost, c->st));
+    M_TRY(cudaStreamSynchronize(c->st));
+    c->have_full = true;
     return ORBX_OK;
 }
 
@@ -1047,18 +1087,51 @@ int orbm_search_for_initialization(orbm_context* c, const orbm_frame_view* F1, c
         Q[i1] = orbm_area_query{prev_matched[2 * i1], prev_matched[2 * i1 + 1], (float)window_size, level1, level1,
                                 level1 > 0 ? 0 : 1, i1};
     }
-    if ((rc = device_candidates(c, F2, Q, F1->desc, F1->n))) return rc;
+    // 100-pixel windows hold tens to hundreds of candidates per row: the accept loop reads the device's
+    // INIT_TOPK best keys per row and scans a row in full only when they cannot settle it
+    const int K = INIT_TOPK;
+    if ((rc = device_candidates(c, F2, Q, F1->desc, F1->n, K))) return rc;
     const std::vector<int32_t>& row_ptr = c->h_rowptr;
-    const std::vector<int32_t>& cand = c->h_cand;
     for (int i1 = 0; i1 < F1->n; ++i1) {
-        if (row_ptr[i1 + 1] == row_ptr[i1]) continue;
+        const int len = row_ptr[i1 + 1] - row_ptr[i1];
+        if (len == 0) continue;
         int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
-        for (int k = row_ptr[i1]; k < row_ptr[i1 + 1]; ++k) {
-            const int i2 = cand[k];
-            const int dist = c->hdist[k];
+        // :741-762: candidates already matched at a distance <= this one are skipped; of the others the
+        // first two in (distance, position) order are the scan's best and second best
+        const uint32_t* keys = &c->h_topk[(size_t)i1 * K];
+        const int32_t* kc = &c->h_topc[(size_t)i1 * K];
+        int found = 0, seen = 0, lastd = 0;
+        for (int k = 0; k < K && keys[k] != 0xffffffffu; ++k) {
+            ++seen;
+            const int dist = lastd = (int)(keys[k] >> 20);
+            const int i2 = kc[k];
             if (vMatchedDistance[i2] <= dist) continue;
-            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
-            else if (dist < bestDist2) bestDist2 = dist;
+            if (!found) {
+                bestDist = dist;
+                bestIdx2 = i2;
+                found = 1;
+            } else {
+                bestDist2 = dist;
+                found = 2;
+                break;
+            }
+        }
+        if (found < 2 && seen == K && len > K) {   // keys exhausted on a longer row
+            bool settled;
+            if (found == 0) settled = lastd > ORBM_TH_LOW;              // nothing acceptable is left
+            else if (bestDist > ORBM_TH_LOW) settled = true;
+            else if ((settled = bestDist < (float)lastd * nn_ratio)) bestDist2 = lastd;   // second best >= lastd
+            if (!settled) {
+                if ((rc = window_full_lists(c))) return rc;
+                bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+                for (int k = row_ptr[i1]; k < row_ptr[i1 + 1]; ++k) {
+                    const int i2 = c->h_cand[k];
+                    const int dist = c->hdist[k];
+                    if (vMatchedDistance[i2] <= dist) continue;
+                    if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+            }
         }
         if (bestDist <= ORBM_TH_LOW) {
             if (bestDist < (float)bestDist2 * nn_ratio) {

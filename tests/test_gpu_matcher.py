@@ -174,6 +174,32 @@ def test_search_for_initialization(mo, extract):
         m.close()
 
 
+@pytest.mark.parametrize("n_a,n_b,step", [(12, 10, 1), (9, 60, 2), (5, 3, 4), (20, 40, 0)])
+def test_search_for_initialization_contested_window(mo, n_a, n_b, step):
+    """SearchForInitialization when the frame-1 keypoints of one spot all prefer the same frame-2 keypoints: later
+    rows find their nearest candidates already matched at a smaller distance (more of them than the keys
+    k_csr_topk returns), so they take the full scan of the window; rows shorter than the key count and a window of
+    60 candidates (two warp rounds) included; step 0 = every distance equal."""
+    from orb_slam3_mac_b200._lib import KP_DTYPE
+    from orb_slam3_mac_b200.matcher import ORBmatcher
+    A, B = _contested_node_case(n_a, n_b, step, 5 * n_a + step)
+    rng = np.random.default_rng(n_a)
+    ka, kb = np.zeros(n_a, KP_DTYPE), np.zeros(n_b, KP_DTYPE)
+    ka["x"], ka["y"] = 300 + rng.uniform(-3, 3, n_a), 200 + rng.uniform(-3, 3, n_a)
+    kb["x"], kb["y"] = 300 + rng.uniform(-40, 40, n_b), 200 + rng.uniform(-40, 40, n_b)
+    ka["angle"], kb["angle"] = rng.uniform(0, 359, n_a), rng.uniform(0, 359, n_b)
+    F1, F2 = _frame(ka, A.desc, 752, 480), _frame(kb, B.desc, 752, 480)
+    prev = np.stack([ka["x"], ka["y"]], axis=1)
+    for check in (False, True):
+        m = ORBmatcher(0.8, check)
+        n, m12, pv = m.SearchForInitialization(F1, F2, prev, 100)
+        m.close()
+        on, om12, opv = mo.search_for_initialization(F1, F2, prev, 100, 0.8, check)
+        assert n == on and np.array_equal(m12, om12) and np.array_equal(pv, opv)
+    if step in (1, 2):
+        assert on >= 0 and (om12 >= 0).sum() == on
+
+
 def test_matcher_contexts_are_concurrent(mo):
     """Tracking, LocalMapping and LoopClosing construct ORBmatcher objects on three threads."""
     import threading
