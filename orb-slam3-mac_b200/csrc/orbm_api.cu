@@ -89,7 +89,7 @@ struct PhaseTimer {
     void mark(const char* phase) {
         auto t1 = std::chrono::steady_clock::now();
         fprintf(stderr, "[orbm %s] %s %.1f us\n", what, phase, std::chrono::duration<double, std::micro>(t1 - t0).count());
-        t0 = t1;
+        t0 = std::chrono::steady_clock::now();   // the print itself is not charged to the next phase
     }
 };
 #define ORBM_PHASE_BEGIN(w) PhaseTimer _pt(w)
