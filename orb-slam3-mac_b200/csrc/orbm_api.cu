@@ -116,7 +116,70 @@ struct orbm_context {
     bool have_full = true;           // h_cand / hdist hold the last search's full lists (top-K mode fetches them lazily)
     std::vector<int32_t> h_items;    // work items of the last orbm_distinctive_descriptors call
     long long last_pairs = 0;        // number of (query, candidate) pairs of the last search
+    // pinned staging arena (ctx_h2d / ctx_d2h / ctx_sync below)
+    uint8_t* pin = nullptr;
+    size_t pin_cap = 0, pin_used = 0, pin_want = 0;
+    struct PendingCopy { void* dst; const void* src; size_t bytes; };
+    std::vector<PendingCopy> pending;
 };
+
+// Host <-> device copies of a call go through one pinned arena per context: a caller's (pageable) array
+// is copied into the arena and sent with a truly asynchronous cudaMemcpyAsync, results land in the
+// arena and are handed to the caller's arrays by ctx_sync().  A pageable cudaMemcpyAsync is staged by
+// the driver synchronously, copy by copy (4-6 copies per search: most of a small search's 40-80 us);
+// from pinned memory the copies only queue.  Payloads that do not fit the arena take the direct path
+// and the arena grows at the next ctx_sync (nothing is in flight then).
+static const size_t ORBM_PIN_INIT = 2u << 20, ORBM_PIN_MAX = 32u << 20;
+// larger single copies go direct: the driver pipelines its own staging with the DMA, one memcpy here would not
+static const size_t ORBM_PIN_DIRECT = 1u << 20;
+
+static cudaError_t ctx_h2d(orbm_context* c, void* dst, const void* src, size_t bytes) {
+    if (bytes == 0) return cudaSuccess;
+    const size_t off = (c->pin_used + 63) & ~(size_t)63;
+    if (bytes > ORBM_PIN_DIRECT) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->st);
+    if (off + bytes > c->pin_cap) {
+        c->pin_want = std::max(c->pin_want, off + bytes);
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->st);
+    }
+    memcpy(c->pin + off, src, bytes);
+    c->pin_used = off + bytes;
+    return cudaMemcpyAsync(dst, c->pin + off, bytes, cudaMemcpyHostToDevice, c->st);
+}
+
+static cudaError_t ctx_d2h(orbm_context* c, void* dst, const void* src, size_t bytes) {
+    if (bytes == 0) return cudaSuccess;
+    const size_t off = (c->pin_used + 63) & ~(size_t)63;
+    if (bytes > ORBM_PIN_DIRECT) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->st);
+    if (off + bytes > c->pin_cap) {
+        c->pin_want = std::max(c->pin_want, off + bytes);
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->st);
+    }
+    c->pin_used = off + bytes;
+    c->pending.push_back(orbm_context::PendingCopy{dst, c->pin + off, bytes});
+    return cudaMemcpyAsync(c->pin + off, src, bytes, cudaMemcpyDeviceToHost, c->st);
+}
+
+// Waits for the context's stream, delivers the staged results and recycles the arena.
+static cudaError_t ctx_sync(orbm_context* c) {
+    cudaError_t e = cudaStreamSynchronize(c->st);
+    if (e == cudaSuccess)
+        for (const orbm_context::PendingCopy& pc : c->pending) memcpy(pc.dst, pc.src, pc.bytes);
+    c->pending.clear();
+    c->pin_used = 0;
+    if (e == cudaSuccess && c->pin_cap && c->pin_want > c->pin_cap && c->pin_cap < ORBM_PIN_MAX) {
+        size_t want = std::min(std::max(c->pin_want * 2, ORBM_PIN_INIT), ORBM_PIN_MAX);
+        uint8_t* np = nullptr;
+        if (cudaHostAlloc((void**)&np, want, cudaHostAllocDefault) == cudaSuccess) {
+            if (c->pin) cudaFreeHost(c->pin);
+            c->pin = np;
+            c->pin_cap = want;
+        } else {
+            cudaGetLastError();   // keep the arena we have
+        }
+    }
+    c->pin_want = 0;
+    return e;
+}
 
 extern "C" {
 
@@ -140,6 +203,11 @@ int orbm_create(int device, orbm_context** out) {
         delete c;
         return orbx_set_error(ORBX_E_CUDA, "cudaEventCreate failed");
     }
+    // the arena is an optimisation: without it every copy takes the direct (pageable) path
+#ifndef ORBM_NO_PIN   // A/B switch: every copy direct
+    if (cudaHostAlloc((void**)&c->pin, ORBM_PIN_INIT, cudaHostAllocDefault) == cudaSuccess) c->pin_cap = ORBM_PIN_INIT;
+    else cudaGetLastError();
+#endif
     *out = c;
     return ORBX_OK;
 }
@@ -147,13 +215,14 @@ int orbm_create(int device, orbm_context** out) {
 int orbm_destroy(orbm_context* c) {
     if (!c) return ORBX_OK;
     cudaSetDevice(c->device);
-    if (c->st) cudaStreamSynchronize(c->st);
+    if (c->st) ctx_sync(c);
     for (DevBuf* b : {&c->q, &c->t, &c->rowptr, &c->cand, &c->dist, &c->aux1, &c->aux2, &c->kl, &c->kr, &c->sc, &c->isc,
                       &c->ur, &c->dp, &c->sd, &c->gstart, &c->gitems, &c->gcell, &c->aq, &c->acnt})
         b->release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->st) cudaStreamDestroy(c->st);
+    if (c->pin) cudaFreeHost(c->pin);
     delete c;
     return ORBX_OK;
 }
@@ -169,18 +238,18 @@ int orbm_hamming_csr(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t
         (r = c->rowptr.ensure((size_t)(nq + 1) * 4)) || (r = c->cand.ensure((size_t)nnz * 4)) ||
         (r = c->dist.ensure((size_t)nnz * 2)))
         return r;
-    M_TRY(cudaMemcpyAsync(c->q.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice, c->st));
-    M_TRY(cudaMemcpyAsync(c->t.p, t, (size_t)nt * 32, cudaMemcpyHostToDevice, c->st));
-    M_TRY(cudaMemcpyAsync(c->rowptr.p, row_ptr, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, c->st));
-    M_TRY(cudaMemcpyAsync(c->cand.p, cand, (size_t)nnz * 4, cudaMemcpyHostToDevice, c->st));
+    M_TRY(ctx_h2d(c, c->q.p, q, (size_t)nq * 32));
+    M_TRY(ctx_h2d(c, c->t.p, t, (size_t)nt * 32));
+    M_TRY(ctx_h2d(c, c->rowptr.p, row_ptr, (size_t)(nq + 1) * 4));
+    M_TRY(ctx_h2d(c, c->cand.p, cand, (size_t)nnz * 4));
     c->last_pairs = nnz;
     M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_hamming_csr((const uint8_t*)c->q.p, nq, (const uint8_t*)c->t.p, (const int32_t*)c->rowptr.p,
                                   (const int32_t*)c->cand.p, nnz, (uint16_t*)c->dist.p, c->st));
     M_TRY(cudaEventRecord(c->ev1, c->st));
     c->timed = true;
-    M_TRY(cudaMemcpyAsync(dist_out, c->dist.p, (size_t)nnz * 2, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaStreamSynchronize(c->st));
+    M_TRY(ctx_d2h(c, dist_out, c->dist.p, (size_t)nnz * 2));
+    M_TRY(ctx_sync(c));
     return ORBX_OK;
 }
 
@@ -195,17 +264,17 @@ int orbm_knn2(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t, int n
     if ((r = c->q.ensure((size_t)nq * 32)) || (r = c->t.ensure((size_t)std::max(nt, 1) * 32)) ||
         (r = c->aux1.ensure((size_t)nq * 8)) || (r = c->aux2.ensure((size_t)nq * 8)))
         return r;
-    M_TRY(cudaMemcpyAsync(c->q.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice, c->st));
-    if (nt) M_TRY(cudaMemcpyAsync(c->t.p, t, (size_t)nt * 32, cudaMemcpyHostToDevice, c->st));
+    M_TRY(ctx_h2d(c, c->q.p, q, (size_t)nq * 32));
+    if (nt) M_TRY(ctx_h2d(c, c->t.p, t, (size_t)nt * 32));
     c->last_pairs = (long long)nq * nt;
     M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_knn2((const uint8_t*)c->q.p, nq, (const uint8_t*)c->t.p, nt, (int32_t*)c->aux1.p,
                            (int32_t*)c->aux2.p, c->st));
     M_TRY(cudaEventRecord(c->ev1, c->st));
     c->timed = true;
-    M_TRY(cudaMemcpyAsync(idx_out, c->aux1.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaMemcpyAsync(dist_out, c->aux2.p, (size_t)nq * 8, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaStreamSynchronize(c->st));
+    M_TRY(ctx_d2h(c, idx_out, c->aux1.p, (size_t)nq * 8));
+    M_TRY(ctx_d2h(c, dist_out, c->aux2.p, (size_t)nq * 8));
+    M_TRY(ctx_sync(c));
     return ORBX_OK;
 }
 
@@ -228,13 +297,13 @@ int orbm_stereo_rows(orbm_context* c, const orbx_keypoint* kps_l, const uint8_t*
         (r = c->sc.ensure((size_t)nlevels * 4)) || (r = c->aux1.ensure((size_t)n_l * 4)) ||
         (r = c->aux2.ensure((size_t)n_l * 4)))
         return r;
-    M_TRY(cudaMemcpyAsync(c->q.p, desc_l, (size_t)n_l * 32, cudaMemcpyHostToDevice, c->st));
-    M_TRY(cudaMemcpyAsync(c->kl.p, kps_l, (size_t)n_l * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
+    M_TRY(ctx_h2d(c, c->q.p, desc_l, (size_t)n_l * 32));
+    M_TRY(ctx_h2d(c, c->kl.p, kps_l, (size_t)n_l * sizeof(orbx_keypoint)));
     if (n_r) {
-        M_TRY(cudaMemcpyAsync(c->t.p, desc_r, (size_t)n_r * 32, cudaMemcpyHostToDevice, c->st));
-        M_TRY(cudaMemcpyAsync(c->kr.p, kps_r, (size_t)n_r * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
+        M_TRY(ctx_h2d(c, c->t.p, desc_r, (size_t)n_r * 32));
+        M_TRY(ctx_h2d(c, c->kr.p, kps_r, (size_t)n_r * sizeof(orbx_keypoint)));
     }
-    M_TRY(cudaMemcpyAsync(c->sc.p, scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice, c->st));
+    M_TRY(ctx_h2d(c, c->sc.p, scale_factors, (size_t)nlevels * 4));
     c->last_pairs = (long long)n_l * n_r;
     M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_stereo_rows((const orbx_keypoint*)c->kl.p, (const uint8_t*)c->q.p, n_l,
@@ -242,9 +311,9 @@ int orbm_stereo_rows(orbm_context* c, const orbx_keypoint* kps_l, const uint8_t*
                                   min_d, max_d, (int32_t*)c->aux1.p, (int32_t*)c->aux2.p, c->st));
     M_TRY(cudaEventRecord(c->ev1, c->st));
     c->timed = true;
-    M_TRY(cudaMemcpyAsync(best_idx, c->aux1.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaMemcpyAsync(best_dist, c->aux2.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaStreamSynchronize(c->st));
+    M_TRY(ctx_d2h(c, best_idx, c->aux1.p, (size_t)n_l * 4));
+    M_TRY(ctx_d2h(c, best_dist, c->aux2.p, (size_t)n_l * 4));
+    M_TRY(ctx_sync(c));
     return ORBX_OK;
 }
 
@@ -281,14 +350,14 @@ int orbm_compute_stereo_matches(orbm_context* c, const orbx_keypoint* kps_l, con
         (r = c->ur.ensure((size_t)n_l * 4)) || (r = c->dp.ensure((size_t)n_l * 4)) ||
         (r = c->sd.ensure((size_t)n_l * 4)))
         return r;
-    M_TRY(cudaMemcpyAsync(c->q.p, desc_l, (size_t)n_l * 32, cudaMemcpyHostToDevice, c->st));
-    M_TRY(cudaMemcpyAsync(c->kl.p, kps_l, (size_t)n_l * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
+    M_TRY(ctx_h2d(c, c->q.p, desc_l, (size_t)n_l * 32));
+    M_TRY(ctx_h2d(c, c->kl.p, kps_l, (size_t)n_l * sizeof(orbx_keypoint)));
     if (n_r) {
-        M_TRY(cudaMemcpyAsync(c->t.p, desc_r, (size_t)n_r * 32, cudaMemcpyHostToDevice, c->st));
-        M_TRY(cudaMemcpyAsync(c->kr.p, kps_r, (size_t)n_r * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
+        M_TRY(ctx_h2d(c, c->t.p, desc_r, (size_t)n_r * 32));
+        M_TRY(ctx_h2d(c, c->kr.p, kps_r, (size_t)n_r * sizeof(orbx_keypoint)));
     }
-    M_TRY(cudaMemcpyAsync(c->sc.p, scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice, c->st));
-    M_TRY(cudaMemcpyAsync(c->isc.p, inv_scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice, c->st));
+    M_TRY(ctx_h2d(c, c->sc.p, scale_factors, (size_t)nlevels * 4));
+    M_TRY(ctx_h2d(c, c->isc.p, inv_scale_factors, (size_t)nlevels * 4));
     // :831-833
     const float minZ = mb, minD = 0, maxD = mbf / minZ;
     const int thOrbDist = (ORBM_TH_HIGH + ORBM_TH_LOW) / 2;   // :807
@@ -304,10 +373,10 @@ int orbm_compute_stereo_matches(orbm_context* c, const orbx_keypoint* kps_l, con
     M_TRY(cudaEventRecord(c->ev1, c->st));
     c->timed = true;
     std::vector<int32_t> sad(n_l);
-    M_TRY(cudaMemcpyAsync(u_right, c->ur.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaMemcpyAsync(depth, c->dp.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaMemcpyAsync(sad.data(), c->sd.p, (size_t)n_l * 4, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaStreamSynchronize(c->st));
+    M_TRY(ctx_d2h(c, u_right, c->ur.p, (size_t)n_l * 4));
+    M_TRY(ctx_d2h(c, depth, c->dp.p, (size_t)n_l * 4));
+    M_TRY(ctx_d2h(c, sad.data(), c->sd.p, (size_t)n_l * 4));
+    M_TRY(ctx_sync(c));
     // :966-979: median of the accepted SAD distances, reject >= 1.5 * 1.4 * median
     std::vector<int32_t> acc;
     acc.reserve(n_l);
@@ -432,10 +501,10 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
         (r = c->gstart.ensure((size_t)(ORBM_GRID_COLS * ORBM_GRID_ROWS + 1) * 4)) ||
         (r = c->gitems.ensure((size_t)F->n * 4)) || (r = c->gcell.ensure((size_t)F->n * 4)))
         return r;
-    M_TRY(cudaMemcpyAsync(c->kl.p, F->keys, (size_t)F->n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
-    M_TRY(cudaMemcpyAsync(c->t.p, F->desc, (size_t)F->n * 32, cudaMemcpyHostToDevice, c->st));
-    if (qdesc) M_TRY(cudaMemcpyAsync(c->q.p, qdesc, (size_t)n_qdesc * 32, cudaMemcpyHostToDevice, c->st));
-    M_TRY(cudaMemcpyAsync(c->aq.p, Q.data(), (size_t)nq * sizeof(orbm_area_query), cudaMemcpyHostToDevice, c->st));
+    M_TRY(ctx_h2d(c, c->kl.p, F->keys, (size_t)F->n * sizeof(orbx_keypoint)));
+    M_TRY(ctx_h2d(c, c->t.p, F->desc, (size_t)F->n * 32));
+    if (qdesc) M_TRY(ctx_h2d(c, c->q.p, qdesc, (size_t)n_qdesc * 32));
+    M_TRY(ctx_h2d(c, c->aq.p, Q.data(), (size_t)nq * sizeof(orbm_area_query)));
     ORBM_PHASE("uploads");
     const orbx_keypoint* dk = (const orbx_keypoint*)c->kl.p;
     M_TRY(cudaEventRecord(c->ev0, c->st));
@@ -444,8 +513,8 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     M_TRY(orbm_launch_area_count(dk, (const int32_t*)c->gstart.p, (const int32_t*)c->gitems.p, F->min_x, F->min_y,
                                  F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
                                  (int32_t*)c->acnt.p, (int32_t*)c->rowptr.p, c->st));
-    M_TRY(cudaMemcpyAsync(c->h_rowptr.data(), c->rowptr.p, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaStreamSynchronize(c->st));
+    M_TRY(ctx_d2h(c, c->h_rowptr.data(), c->rowptr.p, (size_t)(nq + 1) * 4));
+    M_TRY(ctx_sync(c));
     const int nnz = c->h_rowptr[nq];
     ORBM_PHASE("grid + count + sync");
     c->last_pairs = nnz;
@@ -462,9 +531,9 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
         M_TRY(cudaEventRecord(c->ev1, c->st));
         c->timed = true;
         c->have_full = false;
-        M_TRY(cudaMemcpyAsync(c->h_topk.data(), c->aux1.p, (size_t)nq * topk * 4, cudaMemcpyDeviceToHost, c->st));
-        M_TRY(cudaMemcpyAsync(c->h_topc.data(), c->aux2.p, (size_t)nq * topk * 4, cudaMemcpyDeviceToHost, c->st));
-        M_TRY(cudaStreamSynchronize(c->st));
+        M_TRY(ctx_d2h(c, c->h_topk.data(), c->aux1.p, (size_t)nq * topk * 4));
+        M_TRY(ctx_d2h(c, c->h_topc.data(), c->aux2.p, (size_t)nq * topk * 4));
+        M_TRY(ctx_sync(c));
         ORBM_PHASE("fill + topk + download");
         return ORBX_OK;
     }
@@ -472,9 +541,9 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     c->timed = true;
     c->h_cand.resize(nnz);
     c->hdist.resize(nnz);
-    M_TRY(cudaMemcpyAsync(c->h_cand.data(), c->cand.p, (size_t)nnz * 4, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaMemcpyAsync(c->hdist.data(), c->dist.p, (size_t)nnz * 2, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaStreamSynchronize(c->st));
+    M_TRY(ctx_d2h(c, c->h_cand.data(), c->cand.p, (size_t)nnz * 4));
+    M_TRY(ctx_d2h(c, c->hdist.data(), c->dist.p, (size_t)nnz * 2));
+    M_TRY(ctx_sync(c));
     ORBM_PHASE("fill + download");
     return ORBX_OK;
 }
@@ -486,9 +555,9 @@ int window_full_lists(orbm_context* c) {
     const int nnz = c->h_rowptr.back();
     c->h_cand.resize(nnz);
     c->hdist.resize(nnz);
-    M_TRY(cudaMemcpyAsync(c->h_cand.data(), c->cand.p, (size_t)nnz * 4, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaMemcpyAsync(c->hdist.data(), c->dist.p, (size_t)nnz * 2, cudaMemcpyDeviceToHost, c->st));
-    M_TRY(cudaStreamSynchronize(c->st));
+    M_TRY(ctx_d2h(c, c->h_cand.data(), c->cand.p, (size_t)nnz * 4));
+    M_TRY(ctx_d2h(c, c->hdist.data(), c->dist.p, (size_t)nnz * 2));
+    M_TRY(ctx_sync(c));
     c->have_full = true;
     return ORBX_OK;
 }
