@@ -14,6 +14,7 @@
 //                   per left keypoint, gates evaluated per right keypoint, warp-min reduction.
 #include "orbx_device.cuh"
 #include "../../include/orbm.h"
+#include "orbm_internal.h"
 
 __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const uint4* __restrict__ b) {
     const uint4 b0 = __ldg(b), b1 = __ldg(b + 1);
@@ -658,6 +659,33 @@ cudaError_t orbm_launch_csr_topk(const int32_t* row_ptr, const int32_t* cand, co
                                  uint32_t* keys, int32_t* key_cand, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
     k_csr_topk<<<(nrows + 3) / 4, 128, 0, st>>>(row_ptr, cand, dist, nrows, K, keys, key_cand);
+    return cudaGetLastError();
+}
+
+// ---- upload scatter -------------------------------------------------------------------------------
+// A matcher call's inputs arrive as ONE copy of the context's pinned arena into its device mirror; this
+// kernel hands the segments to the buffers the search kernels read (orbm_api.cu, ctx_flush): one DMA
+// and one launch instead of a copy-engine operation per array.
+__global__ void __launch_bounds__(256)
+k_scatter(const __grid_constant__ OrbmScatter S) {
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+    for (int k = 0; k < S.n; ++k) {
+        const uint4* a = reinterpret_cast<const uint4*>(S.seg[k].src);
+        uint4* d = reinterpret_cast<uint4*>(S.seg[k].dst);
+        const size_t n16 = S.seg[k].bytes >> 4;
+        for (size_t i = tid; i < n16; i += nth) d[i] = a[i];
+        const uint32_t tail = S.seg[k].bytes & 15u;
+        if (tid < tail)
+            reinterpret_cast<uint8_t*>(S.seg[k].dst)[16 * n16 + tid] = reinterpret_cast<const uint8_t*>(S.seg[k].src)[16 * n16 + tid];
+    }
+}
+
+cudaError_t orbm_launch_scatter(const OrbmScatter& S, cudaStream_t st) {
+    if (S.n <= 0) return cudaSuccess;
+    size_t most = 0;
+    for (int k = 0; k < S.n; ++k) most = most > S.seg[k].bytes ? most : S.seg[k].bytes;
+    const int blocks = (int)((most / 16 + 255) / 256);
+    k_scatter<<<blocks < 1 ? 1 : (blocks > 296 ? 296 : blocks), 256, 0, st>>>(S);
     return cudaGetLastError();
 }
 

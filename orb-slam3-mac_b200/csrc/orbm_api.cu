@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "../../include/orbm.h"
+#include "orbm_internal.h"
 
 cudaError_t orbm_launch_hamming_csr(const uint8_t* q, int nq, const uint8_t* t, const int32_t* row_ptr,
                                     const int32_t* cand, int nnz, uint16_t* dist, cudaStream_t st);
@@ -34,6 +35,7 @@ cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* star
                                   int32_t* cand, uint16_t* dist, cudaStream_t st);
 cudaError_t orbm_launch_csr_topk(const int32_t* row_ptr, const int32_t* cand, const uint16_t* dist, int nrows, int K,
                                  uint32_t* keys, int32_t* key_cand, cudaStream_t st);
+cudaError_t orbm_launch_scatter(const OrbmScatter& S, cudaStream_t st);
 cudaError_t orbm_launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t st);
 cudaError_t orbm_launch_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
                              int32_t* dist, cudaStream_t st);
@@ -121,6 +123,9 @@ struct orbm_context {
     size_t pin_cap = 0, pin_used = 0, pin_want = 0;
     struct PendingCopy { void* dst; const void* src; size_t bytes; };
     std::vector<PendingCopy> pending;
+    DevBuf darena;                   // device mirror of the arena: uploads arrive in one copy (ctx_flush)
+    OrbmScatter up = {};                // staged uploads not yet sent (src = offset in the arena until ctx_flush)
+    size_t up_first = 0;
 };
 
 // Host <-> device copies of a call go through one pinned arena per context: a caller's (pageable) array
@@ -133,6 +138,37 @@ static const size_t ORBM_PIN_INIT = 2u << 20, ORBM_PIN_MAX = 32u << 20;
 // larger single copies go direct: the driver pipelines its own staging with the DMA, one memcpy here would not
 static const size_t ORBM_PIN_DIRECT = 1u << 20;
 
+// Sends the staged uploads: one copy of their span of the arena into the device mirror, one k_scatter
+// launch that hands the segments to their buffers.  Called before the first kernel of a search (every
+// kernel sequence starts at the ev0 record), before a download is queued and at the sync.
+static cudaError_t ctx_flush(orbm_context* c) {
+    if (c->up.n == 0) return cudaSuccess;
+#ifdef ORBM_NO_SCATTER   // A/B switch: a copy per segment
+    const bool mirror = false;
+#else
+    const bool mirror = c->darena.ensure(c->pin_cap) == ORBX_OK;
+#endif
+    if (!mirror) {   // no mirror: a copy per segment
+        cudaGetLastError();
+        for (int k = 0; k < c->up.n; ++k) {
+            cudaError_t e = cudaMemcpyAsync(c->up.seg[k].dst, c->pin + (uintptr_t)c->up.seg[k].src, c->up.seg[k].bytes,
+                                            cudaMemcpyHostToDevice, c->st);
+            if (e != cudaSuccess) return e;
+        }
+        c->up.n = 0;
+        return cudaSuccess;
+    }
+    const OrbmScatter::Seg& last = c->up.seg[c->up.n - 1];
+    const size_t end = (size_t)(uintptr_t)last.src + last.bytes;
+    cudaError_t e = cudaMemcpyAsync((uint8_t*)c->darena.p + c->up_first, c->pin + c->up_first, end - c->up_first,
+                                    cudaMemcpyHostToDevice, c->st);
+    if (e != cudaSuccess) return e;
+    for (int k = 0; k < c->up.n; ++k) c->up.seg[k].src = (const uint8_t*)c->darena.p + (uintptr_t)c->up.seg[k].src;
+    e = orbm_launch_scatter(c->up, c->st);
+    c->up.n = 0;
+    return e;
+}
+
 static cudaError_t ctx_h2d(orbm_context* c, void* dst, const void* src, size_t bytes) {
     if (bytes == 0) return cudaSuccess;
     const size_t off = (c->pin_used + 63) & ~(size_t)63;
@@ -143,11 +179,19 @@ static cudaError_t ctx_h2d(orbm_context* c, void* dst, const void* src, size_t b
     }
     memcpy(c->pin + off, src, bytes);
     c->pin_used = off + bytes;
-    return cudaMemcpyAsync(dst, c->pin + off, bytes, cudaMemcpyHostToDevice, c->st);
+    if (c->up.n == ORBM_SCATTER_MAX) {
+        cudaError_t e = ctx_flush(c);
+        if (e != cudaSuccess) return e;
+    }
+    if (c->up.n == 0) c->up_first = off;
+    c->up.seg[c->up.n++] = OrbmScatter::Seg{dst, (const void*)(uintptr_t)off, (uint32_t)bytes, 0};
+    return cudaSuccess;
 }
 
 static cudaError_t ctx_d2h(orbm_context* c, void* dst, const void* src, size_t bytes) {
     if (bytes == 0) return cudaSuccess;
+    cudaError_t ef = ctx_flush(c);
+    if (ef != cudaSuccess) return ef;
     const size_t off = (c->pin_used + 63) & ~(size_t)63;
     if (bytes > ORBM_PIN_DIRECT) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->st);
     if (off + bytes > c->pin_cap) {
@@ -161,16 +205,20 @@ static cudaError_t ctx_d2h(orbm_context* c, void* dst, const void* src, size_t b
 
 // Waits for the context's stream, delivers the staged results and recycles the arena.
 static cudaError_t ctx_sync(orbm_context* c) {
-    cudaError_t e = cudaStreamSynchronize(c->st);
+    cudaError_t e = ctx_flush(c);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
+    else cudaStreamSynchronize(c->st);
     if (e == cudaSuccess)
         for (const orbm_context::PendingCopy& pc : c->pending) memcpy(pc.dst, pc.src, pc.bytes);
     c->pending.clear();
     c->pin_used = 0;
+    c->up.n = 0;
     if (e == cudaSuccess && c->pin_cap && c->pin_want > c->pin_cap && c->pin_cap < ORBM_PIN_MAX) {
         size_t want = std::min(std::max(c->pin_want * 2, ORBM_PIN_INIT), ORBM_PIN_MAX);
         uint8_t* np = nullptr;
         if (cudaHostAlloc((void**)&np, want, cudaHostAllocDefault) == cudaSuccess) {
             if (c->pin) cudaFreeHost(c->pin);
+    c->darena.release();
             c->pin = np;
             c->pin_cap = want;
         } else {
@@ -243,6 +291,7 @@ int orbm_hamming_csr(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t
     M_TRY(ctx_h2d(c, c->rowptr.p, row_ptr, (size_t)(nq + 1) * 4));
     M_TRY(ctx_h2d(c, c->cand.p, cand, (size_t)nnz * 4));
     c->last_pairs = nnz;
+    M_TRY(ctx_flush(c));
     M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_hamming_csr((const uint8_t*)c->q.p, nq, (const uint8_t*)c->t.p, (const int32_t*)c->rowptr.p,
                                   (const int32_t*)c->cand.p, nnz, (uint16_t*)c->dist.p, c->st));
@@ -267,6 +316,7 @@ int orbm_knn2(orbm_context* c, const uint8_t* q, int nq, const uint8_t* t, int n
     M_TRY(ctx_h2d(c, c->q.p, q, (size_t)nq * 32));
     if (nt) M_TRY(ctx_h2d(c, c->t.p, t, (size_t)nt * 32));
     c->last_pairs = (long long)nq * nt;
+    M_TRY(ctx_flush(c));
     M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_knn2((const uint8_t*)c->q.p, nq, (const uint8_t*)c->t.p, nt, (int32_t*)c->aux1.p,
                            (int32_t*)c->aux2.p, c->st));
@@ -305,6 +355,7 @@ int orbm_stereo_rows(orbm_context* c, const orbx_keypoint* kps_l, const uint8_t*
     }
     M_TRY(ctx_h2d(c, c->sc.p, scale_factors, (size_t)nlevels * 4));
     c->last_pairs = (long long)n_l * n_r;
+    M_TRY(ctx_flush(c));
     M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_stereo_rows((const orbx_keypoint*)c->kl.p, (const uint8_t*)c->q.p, n_l,
                                   (const orbx_keypoint*)c->kr.p, (const uint8_t*)c->t.p, n_r, (const float*)c->sc.p,
@@ -362,6 +413,7 @@ int orbm_compute_stereo_matches(orbm_context* c, const orbx_keypoint* kps_l, con
     const float minZ = mb, minD = 0, maxD = mbf / minZ;
     const int thOrbDist = (ORBM_TH_HIGH + ORBM_TH_LOW) / 2;   // :807
     c->last_pairs = (long long)n_l * n_r;
+    M_TRY(ctx_flush(c));
     M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_stereo_rows((const orbx_keypoint*)c->kl.p, (const uint8_t*)c->q.p, n_l,
                                   (const orbx_keypoint*)c->kr.p, (const uint8_t*)c->t.p, n_r, (const float*)c->sc.p,
@@ -507,6 +559,7 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     M_TRY(ctx_h2d(c, c->aq.p, Q.data(), (size_t)nq * sizeof(orbm_area_query)));
     ORBM_PHASE("uploads");
     const orbx_keypoint* dk = (const orbx_keypoint*)c->kl.p;
+    M_TRY(ctx_flush(c));
     M_TRY(cudaEventRecord(c->ev0, c->st));
     M_TRY(orbm_launch_grid_build(dk, F->n, F->min_x, F->min_y, F->grid_w_inv, F->grid_h_inv, (int32_t*)c->gstart.p,
                                  (int32_t*)c->gitems.p, (int32_t*)c->gcell.p, c->st));
