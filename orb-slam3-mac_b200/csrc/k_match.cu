@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(256)
 k_area(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start,
        const int32_t* __restrict__ items, OrbmGrid G, const orbm_area_query* __restrict__ Q, int nq,
        int32_t* __restrict__ cnt, const int32_t* __restrict__ row_ptr, const uint4* __restrict__ qdesc,
-       const uint4* __restrict__ tdesc, int32_t* __restrict__ cand, uint16_t* __restrict__ dist) {
+       const uint4* __restrict__ tdesc, int32_t* __restrict__ cand, uint16_t* __restrict__ dist, int cap) {
     const int qi = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
     if (qi >= nq) return;
     const int lane = orbx_lane();
@@ -359,8 +359,8 @@ k_area(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start
                     if (!(fabsf(dx) < r && fabsf(dy) < r)) ok = false;
                 }
                 const uint32_t m = __ballot_sync(ORBX_FULL, ok);
-                if (FILL && ok) {
-                    const int pos = base + total + __popc(m & lt);
+                const int pos = base + total + __popc(m & lt);
+                if (FILL && ok && pos < cap) {   // cap: the lists were sized before the counts were known
                     cand[pos] = idx;
                     dist[pos] = (uint16_t)hamming256(a0, a1, tdesc + 2 * (size_t)idx);
                 }
@@ -403,7 +403,7 @@ cudaError_t orbm_launch_area_count(const orbx_keypoint* keys, const int32_t* sta
                                    int nq, int32_t* cnt, int32_t* row_ptr, cudaStream_t st) {
     OrbmGrid G{min_x, min_y, w_inv, h_inv};
     k_area<false><<<(nq + 7) / 8, 256, 0, st>>>(keys, start, items, G, Q, nq, cnt, nullptr, nullptr, nullptr,
-                                                 nullptr, nullptr);
+                                                 nullptr, nullptr, 0);
     k_rowptr_scan<<<1, 1024, 0, st>>>(cnt, nq, row_ptr);
     return cudaGetLastError();
 }
@@ -411,11 +411,11 @@ cudaError_t orbm_launch_area_count(const orbx_keypoint* keys, const int32_t* sta
 cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
                                   float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
                                   int nq, const int32_t* row_ptr, const uint8_t* qdesc, const uint8_t* tdesc,
-                                  int32_t* cand, uint16_t* dist, cudaStream_t st) {
+                                  int32_t* cand, uint16_t* dist, int cap, cudaStream_t st) {
     OrbmGrid G{min_x, min_y, w_inv, h_inv};
     k_area<true><<<(nq + 7) / 8, 256, 0, st>>>(keys, start, items, G, Q, nq, nullptr, row_ptr,
                                                 reinterpret_cast<const uint4*>(qdesc),
-                                                reinterpret_cast<const uint4*>(tdesc), cand, dist);
+                                                reinterpret_cast<const uint4*>(tdesc), cand, dist, cap);
     return cudaGetLastError();
 }
 
@@ -620,9 +620,9 @@ cudaError_t orbm_launch_bow_topk(const uint8_t* A, const uint8_t* B, const uint3
 // candidates, so the host's accept loop reads K entries per row instead of the whole row.
 __global__ void __launch_bounds__(128)
 k_csr_topk(const int32_t* __restrict__ row_ptr, const int32_t* __restrict__ cand, const uint16_t* __restrict__ dist,
-           int nrows, int K, uint32_t* __restrict__ keys, int32_t* __restrict__ key_cand) {
+           int nrows, int K, int cap, uint32_t* __restrict__ keys, int32_t* __restrict__ key_cand) {
     const int r = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
-    if (r >= nrows) return;
+    if (r >= nrows || __ldg(row_ptr + nrows) > cap) return;   // lists cut at cap: the host reruns with larger ones
     const int lane = orbx_lane();
     const int b = __ldg(row_ptr + r), len = __ldg(row_ptr + r + 1) - b;
     uint32_t mine = 0xffffffffu;
@@ -656,9 +656,9 @@ k_csr_topk(const int32_t* __restrict__ row_ptr, const int32_t* __restrict__ cand
 }
 
 cudaError_t orbm_launch_csr_topk(const int32_t* row_ptr, const int32_t* cand, const uint16_t* dist, int nrows, int K,
-                                 uint32_t* keys, int32_t* key_cand, cudaStream_t st) {
+                                 int cap, uint32_t* keys, int32_t* key_cand, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    k_csr_topk<<<(nrows + 3) / 4, 128, 0, st>>>(row_ptr, cand, dist, nrows, K, keys, key_cand);
+    k_csr_topk<<<(nrows + 3) / 4, 128, 0, st>>>(row_ptr, cand, dist, nrows, K, cap, keys, key_cand);
     return cudaGetLastError();
 }
 

@@ -32,9 +32,9 @@ cudaError_t orbm_launch_area_count(const orbx_keypoint* keys, const int32_t* sta
 cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
                                   float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
                                   int nq, const int32_t* row_ptr, const uint8_t* qdesc, const uint8_t* tdesc,
-                                  int32_t* cand, uint16_t* dist, cudaStream_t st);
+                                  int32_t* cand, uint16_t* dist, int cap, cudaStream_t st);
 cudaError_t orbm_launch_csr_topk(const int32_t* row_ptr, const int32_t* cand, const uint16_t* dist, int nrows, int K,
-                                 uint32_t* keys, int32_t* key_cand, cudaStream_t st);
+                                 int cap, uint32_t* keys, int32_t* key_cand, cudaStream_t st);
 cudaError_t orbm_launch_scatter(const OrbmScatter& S, cudaStream_t st);
 cudaError_t orbm_launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t st);
 cudaError_t orbm_launch_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
@@ -115,6 +115,7 @@ struct orbm_context {
     std::vector<uint16_t> hdist;     // distances of the last layer-2 search
     std::vector<uint32_t> h_topk;    // k_bow_topk's / k_csr_topk's keys of the last search
     std::vector<int32_t> h_topc;     // k_csr_topk: the candidate each key names
+    int nnz_hint = 0;                // pairs of the last window search: sizes the lists of the next one before its counts are known
     bool have_full = true;           // h_cand / hdist hold the last search's full lists (top-K mode fetches them lazily)
     std::vector<int32_t> h_items;    // work items of the last orbm_distinctive_descriptors call
     long long last_pairs = 0;        // number of (query, candidate) pairs of the last search
@@ -566,38 +567,66 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     M_TRY(orbm_launch_area_count(dk, (const int32_t*)c->gstart.p, (const int32_t*)c->gitems.p, F->min_x, F->min_y,
                                  F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
                                  (int32_t*)c->acnt.p, (int32_t*)c->rowptr.p, c->st));
-    M_TRY(ctx_d2h(c, c->h_rowptr.data(), c->rowptr.p, (size_t)(nq + 1) * 4));
-    M_TRY(ctx_sync(c));
-    const int nnz = c->h_rowptr[nq];
-    ORBM_PHASE("grid + count + sync");
-    c->last_pairs = nnz;
-    if (nnz == 0) return ORBX_OK;
-    if ((r = c->cand.ensure((size_t)nnz * 4)) || (r = c->dist.ensure((size_t)nnz * 2))) return r;
-    M_TRY(orbm_launch_area_fill(dk, (const int32_t*)c->gstart.p, (const int32_t*)c->gitems.p, F->min_x, F->min_y,
-                                F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
-                                (const int32_t*)c->rowptr.p, qdesc ? (const uint8_t*)c->q.p : (const uint8_t*)c->t.p,
-                                (const uint8_t*)c->t.p, (int32_t*)c->cand.p, (uint16_t*)c->dist.p, c->st));
-    if (topk > 0) {
-        if ((r = c->aux1.ensure((size_t)nq * topk * 4)) || (r = c->aux2.ensure((size_t)nq * topk * 4))) return r;
-        M_TRY(orbm_launch_csr_topk((const int32_t*)c->rowptr.p, (const int32_t*)c->cand.p, (const uint16_t*)c->dist.p, nq,
-                                   topk, (uint32_t*)c->aux1.p, (int32_t*)c->aux2.p, c->st));
+    // One blocking wait per search: the candidate / distance lists are sized from the last search's pair
+    // count (twice that, at least 4096) before this one's counts are known, k_area<1> writes inside that
+    // capacity, and the counts come back together with the results.  A search that outgrows the guess
+    // (first call, larger windows) reruns the fill with lists of the right size.
+    {
+        const size_t guess = std::max<size_t>(4096, 2 * (size_t)c->nnz_hint);
+        if ((r = c->cand.ensure(guess * 4)) || (r = c->dist.ensure(guess * 2))) return r;
+    }
+    if (topk > 0 && ((r = c->aux1.ensure((size_t)nq * topk * 4)) || (r = c->aux2.ensure((size_t)nq * topk * 4)))) return r;
+    int nnz = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+        const int cap = (int)std::min<size_t>({c->cand.cap / 4, c->dist.cap / 2, (size_t)INT_MAX});
+        M_TRY(orbm_launch_area_fill(dk, (const int32_t*)c->gstart.p, (const int32_t*)c->gitems.p, F->min_x, F->min_y,
+                                    F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
+                                    (const int32_t*)c->rowptr.p, qdesc ? (const uint8_t*)c->q.p : (const uint8_t*)c->t.p,
+                                    (const uint8_t*)c->t.p, (int32_t*)c->cand.p, (uint16_t*)c->dist.p, cap, c->st));
+        if (topk > 0)
+            M_TRY(orbm_launch_csr_topk((const int32_t*)c->rowptr.p, (const int32_t*)c->cand.p, (const uint16_t*)c->dist.p,
+                                       nq, topk, cap, (uint32_t*)c->aux1.p, (int32_t*)c->aux2.p, c->st));
         M_TRY(cudaEventRecord(c->ev1, c->st));
         c->timed = true;
-        c->have_full = false;
-        M_TRY(ctx_d2h(c, c->h_topk.data(), c->aux1.p, (size_t)nq * topk * 4));
-        M_TRY(ctx_d2h(c, c->h_topc.data(), c->aux2.p, (size_t)nq * topk * 4));
+        if (pass == 0) M_TRY(ctx_d2h(c, c->h_rowptr.data(), c->rowptr.p, (size_t)(nq + 1) * 4));
+        // without top-K the lists themselves are wanted: fetch what the last search would have needed (+ slack)
+        // now, the rest (if any) once the count is known
+        size_t spec = 0;
+        if (topk > 0) {
+            M_TRY(ctx_d2h(c, c->h_topk.data(), c->aux1.p, (size_t)nq * topk * 4));
+            M_TRY(ctx_d2h(c, c->h_topc.data(), c->aux2.p, (size_t)nq * topk * 4));
+        } else {
+            spec = pass == 0 ? std::min<size_t>({(size_t)cap, (size_t)c->nnz_hint + (size_t)c->nnz_hint / 8 + 1024, (size_t)65536})
+                             : (size_t)nnz;   // at most 384 KB fetched on a guess
+            c->h_cand.resize(spec);
+            c->hdist.resize(spec);
+            M_TRY(ctx_d2h(c, c->h_cand.data(), c->cand.p, spec * 4));
+            M_TRY(ctx_d2h(c, c->hdist.data(), c->dist.p, spec * 2));
+        }
         M_TRY(ctx_sync(c));
-        ORBM_PHASE("fill + topk + download");
-        return ORBX_OK;
+        nnz = c->h_rowptr[nq];
+        c->last_pairs = nnz;
+        c->nnz_hint = nnz;
+        if (nnz > cap) {   // the guess was too small: lists of the right size, fill again
+            if ((r = c->cand.ensure((size_t)nnz * 4)) || (r = c->dist.ensure((size_t)nnz * 2))) return r;
+            continue;
+        }
+        if (topk > 0) {
+            c->have_full = nnz == 0;
+        } else {
+            if ((size_t)nnz > spec) {   // the tail the speculative fetch did not cover
+                c->h_cand.resize(nnz);
+                c->hdist.resize(nnz);
+                M_TRY(ctx_d2h(c, c->h_cand.data() + spec, (const int32_t*)c->cand.p + spec, ((size_t)nnz - spec) * 4));
+                M_TRY(ctx_d2h(c, c->hdist.data() + spec, (const uint16_t*)c->dist.p + spec, ((size_t)nnz - spec) * 2));
+                M_TRY(ctx_sync(c));
+            }
+            c->h_cand.resize(nnz);
+            c->hdist.resize(nnz);
+        }
+        break;
     }
-    M_TRY(cudaEventRecord(c->ev1, c->st));
-    c->timed = true;
-    c->h_cand.resize(nnz);
-    c->hdist.resize(nnz);
-    M_TRY(ctx_d2h(c, c->h_cand.data(), c->cand.p, (size_t)nnz * 4));
-    M_TRY(ctx_d2h(c, c->hdist.data(), c->dist.p, (size_t)nnz * 2));
-    M_TRY(ctx_sync(c));
-    ORBM_PHASE("fill + download");
+    ORBM_PHASE("grid + count + fill + download");
     return ORBX_OK;
 }
 
