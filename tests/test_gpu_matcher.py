@@ -129,6 +129,32 @@ def test_search_by_projection_points_c4(matcher, mo, extract, th, far, u_right):
     assert n > 300
 
 
+def test_window_searches_of_changing_size_on_one_context(mo, extract):
+    """The window searches size their candidate lists from the previous search of the same context and fetch them on
+    that guess: a context that sees small, 10x larger, small again, then a 100-px-window search and back must return
+    the oracle's result every time (first call and growth: the fill reruns; moderate growth: the tail is fetched
+    after the count; shrink: the guess over-fetches)."""
+    from orb_slam3_mac_b200.matcher import ORBmatcher
+    img0 = S.textured_noise(720, 1280, 9)
+    img1 = np.roll(img0, 2, axis=1)
+    _, k0, d0 = extract(img0, 2000, (0, 1000))
+    _, k1, d1 = extract(img1, 2000, (0, 1000))
+    mps, md = S.map_points_from_frame(k0, d0, 1280, 720, 6000, 9)
+    F0, F = _frame(k0, d0, 1280, 720), _frame(k1, d1, 1280, 720)
+    prev = np.stack([k0["x"], k0["y"]], axis=1)
+    m = ORBmatcher(0.8, True)
+    for th in (1.0, 6.0, 1.0, None, 2.0, 1.3, 12.0, 1.0):
+        if th is None:
+            n, m12, pv = m.SearchForInitialization(F0, F, prev, 100)
+            on, om12, opv = mo.search_for_initialization(F0, F, prev, 100, 0.8, True)
+            assert n == on and np.array_equal(m12, om12) and np.array_equal(pv, opv)
+        else:
+            n, match, obs = m.SearchByProjection(F, mps, md, th, False, 30.0)
+            on, omatch, oobs = mo.search_by_projection_points(F, mps, md, th, False, 30.0, 0.8)
+            assert n == on and np.array_equal(match, omatch) and np.array_equal(obs, oobs), th
+    m.close()
+
+
 @pytest.mark.parametrize("fwd,bwd,check,u_right", [(False, False, True, False), (True, False, True, False),
                                                     (False, True, False, True)])
 def test_search_by_projection_frames(matcher, mo, extract, fwd, bwd, check, u_right):
