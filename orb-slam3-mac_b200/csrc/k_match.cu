@@ -696,12 +696,13 @@ cudaError_t orbm_launch_scatter(const OrbmScatter& S, cudaStream_t st) {
 // the same 256-bit popcount, and the first child with the least distance wins (packed key
 // distance << 16 | position in Node::children, warp min = the reference's strict '<' scan).  The
 // vocabulary (child lists + 32-byte node descriptors, ~36 MB for the 10^6-word ORBvoc) stays resident in
-// HBM/L2.  leaf[i] = final node, nid[i] = the node passed at level L - levelsup (0 when that level is
+// HBM/L2.  word_out / weight_out[i] = id and weight of the word reached, nid[i] = the node passed at level L - levelsup (0 when that level is
 // <= 0 or the branch ends above it).
 __global__ void __launch_bounds__(128)
 k_bow_descend(const uint4* __restrict__ feat, int n, const int32_t* __restrict__ child_ptr,
-              const uint32_t* __restrict__ child_ids, const uint4* __restrict__ node_desc, int nid_level,
-              int32_t* __restrict__ leaf, int32_t* __restrict__ nid_out) {
+              const uint32_t* __restrict__ child_ids, const uint4* __restrict__ node_desc,
+              const uint32_t* __restrict__ word_id, const double* __restrict__ weight, int nid_level,
+              uint32_t* __restrict__ word_out, double* __restrict__ weight_out, int32_t* __restrict__ nid_out) {
     const int i = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
     if (i >= n) return;
     const int lane = orbx_lane();
@@ -721,17 +722,20 @@ k_bow_descend(const uint4* __restrict__ feat, int n, const int32_t* __restrict__
         node = __ldg(child_ids + cp + (int)(key & 0xffffu));
         if (level == nid_level) nid = node;
     }
-    if (lane == 0) {
-        leaf[i] = (int32_t)node;
+    if (lane == 0) {   // the word's id and weight travel with the result: the host never indexes the 10^6-entry tables
+        word_out[i] = __ldg(word_id + node);
+        weight_out[i] = __ldg(weight + node);
         nid_out[i] = (int32_t)nid;
     }
 }
 
 cudaError_t orbm_launch_bow_descend(const uint8_t* feat, int n, const int32_t* child_ptr, const uint32_t* child_ids,
-                                    const uint8_t* node_desc, int nid_level, int32_t* leaf, int32_t* nid,
+                                    const uint8_t* node_desc, const uint32_t* word_id, const double* weight,
+                                    int nid_level, uint32_t* word_out, double* weight_out, int32_t* nid,
                                     cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
     k_bow_descend<<<(n + 3) / 4, 128, 0, st>>>(reinterpret_cast<const uint4*>(feat), n, child_ptr, child_ids,
-                                                reinterpret_cast<const uint4*>(node_desc), nid_level, leaf, nid);
+                                                reinterpret_cast<const uint4*>(node_desc), word_id, weight, nid_level,
+                                                word_out, weight_out, nid);
     return cudaGetLastError();
 }
