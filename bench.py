@@ -87,6 +87,12 @@ class ClockSampler:
                 self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
             self.nv = pynvml
             self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            # the first query of each kind can take tens of ms (driver-side set-up): pay that here, not inside
+            # a timed region that lasts under 100 ms
+            pynvml.nvmlDeviceGetClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            pynvml.nvmlDeviceGetPowerUsage(self.h)
+            (pynvml.nvmlDeviceGetCurrentClocksEventReasons if hasattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons")
+             else pynvml.nvmlDeviceGetCurrentClocksThrottleReasons)(self.h)
         except Exception as e:
             log("NVML unavailable, falling back to nvidia-smi:", e)
 
