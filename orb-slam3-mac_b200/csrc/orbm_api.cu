@@ -845,16 +845,19 @@ int orbm_search_by_projection_frames(orbm_context* c, const orbm_frame_view* cur
         if (row_ptr[i + 1] == row_ptr[i]) continue;
         const orbm_last_obs& o = last[i];
         int bestDist = 256, bestIdx2 = -1;
+        // selects instead of early-outs, as in SearchByProjection(Frame, map points) above (:2040-2056)
+        const float ur = o.u - bf * o.inv_z, radi = rad[i];
         for (int k = row_ptr[i]; k < row_ptr[i + 1]; ++k) {
             const int i2 = cand[k];
-            if (kp_obs[i2] > 0) continue;
-            if (cur->u_right && cur->u_right[i2] > 0) {
-                const float ur = o.u - bf * o.inv_z;
-                const float er = fabsf(ur - cur->u_right[i2]);
-                if (er > rad[i]) continue;
+            bool skip = kp_obs[i2] > 0;
+            if (cur->u_right) {
+                const float u2 = cur->u_right[i2];
+                skip |= (u2 > 0) & (fabsf(ur - u2) > radi);
             }
-            const int dist = c->hdist[k];
-            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+            const int dist = skip ? 0x10000 : (int)c->hdist[k];
+            const bool lt = dist < bestDist;
+            bestIdx2 = lt ? i2 : bestIdx2;
+            bestDist = lt ? dist : bestDist;
         }
         if (bestDist <= ORBM_TH_HIGH) {
             kp_match[bestIdx2] = i;
