@@ -264,42 +264,16 @@ struct OrbmGrid {
     float min_x, min_y, w_inv, h_inv;
 };
 
-__global__ void __launch_bounds__(1024)
-k_grid_build(const orbx_keypoint* __restrict__ keys, int n, OrbmGrid G, int32_t* __restrict__ start,
-             int32_t* __restrict__ items, int32_t* __restrict__ cellof) {
-    __shared__ uint32_t cnt[ORBM_GRID_CELLS + 1];
-    __shared__ uint32_t cur[ORBM_GRID_CELLS];
-    __shared__ uint32_t tmp[64];
-    const int tid = threadIdx.x;
-    for (int c = tid; c <= ORBM_GRID_CELLS; c += blockDim.x) cnt[c] = 0;
-    __syncthreads();
-    for (int i = tid; i < n; i += blockDim.x) {
-        // PosInGrid (:716-726): round, not floor; keypoints outside the grid are not inserted
-        const int px = (int)roundf((keys[i].x - G.min_x) * G.w_inv);
-        const int py = (int)roundf((keys[i].y - G.min_y) * G.h_inv);
-        int cell = -1;
-        if (px >= 0 && px < ORBM_GRID_COLS && py >= 0 && py < ORBM_GRID_ROWS) {
-            cell = px * ORBM_GRID_ROWS + py;
-            atomicAdd(&cnt[cell], 1u);
-        }
-        cellof[i] = cell;
-    }
-    __syncthreads();
-    const uint32_t total = block_excl_scan(cnt, ORBM_GRID_CELLS, tmp);
-    if (tid == 0) cnt[ORBM_GRID_CELLS] = total;
-    __syncthreads();
-    for (int c = tid; c <= ORBM_GRID_CELLS; c += blockDim.x) {
-        start[c] = (int32_t)cnt[c];
-        if (c < ORBM_GRID_CELLS) cur[c] = cnt[c];
-    }
-    __syncthreads();
-    for (int i = tid; i < n; i += blockDim.x) {
-        const int cell = cellof[i];
-        if (cell >= 0) items[atomicAdd(&cur[cell], 1u)] = i;
-    }
-    __syncthreads();
+// Frames of up to ORBM_GRID_SMEM_ITEMS keypoints (every config of BASELINE.json) keep the cell of each
+// keypoint in registers between the two passes and the item array in shared memory until it is sorted:
+// the kernel is one CTA's dependent chain, and every global round trip in it (cellof[], the insertion
+// sort on items[]) is a microsecond of a 12 us kernel.
+#define ORBM_GRID_SMEM_ITEMS 4096
+#define ORBM_GRID_PER_THREAD (ORBM_GRID_SMEM_ITEMS / 1024)
+
+__device__ __forceinline__ void grid_sort_cells(int32_t* items, const uint32_t* cnt, int tid, int nthreads) {
     // restore insertion order (ascending keypoint index) inside every cell: a handful of items
-    for (int c = tid; c < ORBM_GRID_CELLS; c += blockDim.x) {
+    for (int c = tid; c < ORBM_GRID_CELLS; c += nthreads) {
         const int s = (int)cnt[c], e = (int)cnt[c + 1];
         for (int a = s + 1; a < e; ++a) {
             const int32_t v = items[a];
@@ -311,6 +285,65 @@ k_grid_build(const orbx_keypoint* __restrict__ keys, int n, OrbmGrid G, int32_t*
             items[b + 1] = v;
         }
     }
+}
+
+__global__ void __launch_bounds__(1024)
+k_grid_build(const orbx_keypoint* __restrict__ keys, int n, OrbmGrid G, int32_t* __restrict__ start,
+             int32_t* __restrict__ items, int32_t* __restrict__ cellof) {
+    __shared__ uint32_t cnt[ORBM_GRID_CELLS + 1];
+    __shared__ uint32_t cur[ORBM_GRID_CELLS];
+    __shared__ uint32_t tmp[64];
+    __shared__ int32_t sitems[ORBM_GRID_SMEM_ITEMS];
+    const int tid = threadIdx.x;
+    const bool small = n <= ORBM_GRID_SMEM_ITEMS;
+    int mycell[ORBM_GRID_PER_THREAD];
+    for (int c = tid; c <= ORBM_GRID_CELLS; c += blockDim.x) cnt[c] = 0;
+    __syncthreads();
+    // PosInGrid (:716-726): round, not floor; keypoints outside the grid are not inserted
+    auto cell_of = [&](int i) {
+        const int px = (int)roundf((keys[i].x - G.min_x) * G.w_inv);
+        const int py = (int)roundf((keys[i].y - G.min_y) * G.h_inv);
+        return (px >= 0 && px < ORBM_GRID_COLS && py >= 0 && py < ORBM_GRID_ROWS) ? px * ORBM_GRID_ROWS + py : -1;
+    };
+    if (small) {
+#pragma unroll
+        for (int j = 0; j < ORBM_GRID_PER_THREAD; ++j) {
+            const int i = tid + j * 1024;
+            mycell[j] = i < n ? cell_of(i) : -1;
+            if (mycell[j] >= 0) atomicAdd(&cnt[mycell[j]], 1u);
+        }
+    } else {
+        for (int i = tid; i < n; i += blockDim.x) {
+            const int cell = cell_of(i);
+            if (cell >= 0) atomicAdd(&cnt[cell], 1u);
+            cellof[i] = cell;
+        }
+    }
+    __syncthreads();
+    const uint32_t total = block_excl_scan(cnt, ORBM_GRID_CELLS, tmp);
+    if (tid == 0) cnt[ORBM_GRID_CELLS] = total;
+    __syncthreads();
+    for (int c = tid; c <= ORBM_GRID_CELLS; c += blockDim.x) {
+        start[c] = (int32_t)cnt[c];
+        if (c < ORBM_GRID_CELLS) cur[c] = cnt[c];
+    }
+    __syncthreads();
+    if (small) {
+#pragma unroll
+        for (int j = 0; j < ORBM_GRID_PER_THREAD; ++j)
+            if (mycell[j] >= 0) sitems[atomicAdd(&cur[mycell[j]], 1u)] = tid + j * 1024;
+        __syncthreads();
+        grid_sort_cells(sitems, cnt, tid, blockDim.x);
+        __syncthreads();
+        for (int k = tid; k < (int)total; k += blockDim.x) items[k] = sitems[k];
+        return;
+    }
+    for (int i = tid; i < n; i += blockDim.x) {
+        const int cell = cellof[i];
+        if (cell >= 0) items[atomicAdd(&cur[cell], 1u)] = i;
+    }
+    __syncthreads();
+    grid_sort_cells(items, cnt, tid, blockDim.x);
 }
 
 template <bool FILL>
