@@ -356,6 +356,30 @@ int orbm_area_candidates(orbm_context* c, const orbm_frame_view* F, const orbm_a
                          const uint8_t* q_desc, int n_q_desc, int32_t* row_ptr, int32_t* cand,
                          uint16_t* dist, int cap);
 
+/* ---- window search without any allocation ----------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The same computation as orbm_area_candidates -- grid build, per-query candidate lists in
+ * GetFeaturesInArea order as CSR, the Hamming distance of every (query, candidate) pair -- but
+ *   - every input and output is a DEVICE pointer the caller owns (keys: n records, desc: n x 32, q: nq
+ *     queries, q_desc: the rows desc_row names, row_ptr: nq + 1 ints, cand / dist: cap entries);
+ *   - the work is enqueued on `stream` (a cudaStream_t, NULL = the default stream) and the call returns
+ *     without waiting; nnz = row_ptr[nq], pairs at positions >= cap are counted but not written;
+ *   - the scratch (cell of every keypoint, the 64 x 48 grid, per-query counts) is ONE file-scope
+ *     `static __device__` array of 274,688 bytes that every GPU loading the library holds until exit, so
+ *     sizes are bounded: n <= ORBM_STATIC_MAX_KEYS, nq <= ORBM_STATIC_MAX_QUERIES, else ORBX_E_TOO_LARGE;
+ *   - it calls no cudaMalloc / cudaFree / allocating library routine.  The first call on a device looks the
+ *     array's device address up (cudaGetSymbolAddress): make that call outside a graph capture.
+ * All calls on a device share the array and it keeps the previous call's contents (nothing in it has to
+ * start at zero; each call overwrites the ranges it reads).  Calls that overlap on the GPU -- two streams, or
+ * two captured graphs launched concurrently -- RACE on it: serialise them on one stream or with events. */
+#define ORBM_STATIC_MAX_KEYS 16384
+#define ORBM_STATIC_MAX_QUERIES 32768
+int orbm_area_candidates_static(int device, void* stream, const orbx_keypoint* d_keys, const uint8_t* d_desc,
+                                int n, float min_x, float min_y, float grid_w_inv, float grid_h_inv,
+                                const orbm_area_query* d_q, int nq, const uint8_t* d_q_desc, int32_t* d_row_ptr,
+                                int32_t* d_cand, uint16_t* d_dist, int cap);
+
 /* Measurement hook: device time between the first and the last kernel of the previous call on this
  * context (CUDA events on its stream; for the searches this spans the candidate kernels and the
  * row_ptr read-back between them) and the number of descriptor pairs it compared. */

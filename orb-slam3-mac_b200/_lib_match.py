@@ -44,6 +44,10 @@ assert PROJ_POINT_DTYPE.itemsize == 24
 PAIR_TEST = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.c_int32)  # orbm_pair_test
 
 _vp, _i, _f = C.c_void_p, C.c_int, C.c_float
+# limits of orbm_area_candidates_static (include/orbm.h)
+ORBM_STATIC_MAX_KEYS = 16384
+ORBM_STATIC_MAX_QUERIES = 32768
+
 ORBM_SYMBOLS = {
     "orbm_create": (_i, [_i, C.POINTER(_vp)]),
     "orbm_destroy": (_i, [_vp]),
@@ -72,6 +76,7 @@ ORBM_SYMBOLS = {
     "orbm_bow_transform": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, C.POINTER(C.c_int32), _vp, _vp, _vp,
                                 C.POINTER(C.c_int32)]),
     "orbm_area_candidates": (_i, [_vp, _fv, _vp, _i, _vp, _i, _vp, _vp, _vp, _i]),
+    "orbm_area_candidates_static": (_i, [_i, _vp, _vp, _vp, _i, _f, _f, _f, _f, _vp, _i, _vp, _vp, _vp, _vp, _i]),
     "orbm_last_device_ms": (_i, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_longlong)]),
     "orbm_measure_popc_peak": (_i, [_vp, C.POINTER(C.c_double)]),
     "orbm_features_in_area": (_i, [_fv, _f, _f, _f, _i, _i, _vp, _i]),

@@ -772,3 +772,82 @@ cudaError_t orbm_launch_bow_descend(const uint8_t* feat, int n, const int32_t* c
                                                 word_out, weight_out, nid);
     return cudaGetLastError();
 }
+
+// ---- orbm_area_candidates_static: the window search with its scratch in a static device array ------
+// No counterpart in the reference; added for callers that cannot
+// call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).  Same kernels as
+// orbm_area_candidates (k_grid_build -> k_area<count> -> k_rowptr_scan -> k_area<fill>); what that entry
+// point keeps in cudaMalloc'ed context buffers -- the cell of every keypoint, the 64 x 48 grid (start
+// offsets + item array) and the per-query candidate counts -- lives in the file-scope array below.
+// Every GPU that loads the library holds these 274,688 bytes until the process exits.
+#define ORBM_STATIC_START_INTS 3136   /* 64 * 48 + 1 = 3073 offsets, padded to a multiple of 64 ints */
+#define ORBM_STATIC_BYTES ((2 * ORBM_STATIC_MAX_KEYS + ORBM_STATIC_START_INTS + ORBM_STATIC_MAX_QUERIES) * 4)
+static __device__ __align__(256) uint8_t g_orbm_static_scratch[ORBM_STATIC_BYTES];
+
+#include <mutex>
+int orbx_set_error(int code, const char* fmt, ...);   // orbx_api.cu
+
+namespace {
+const int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+uint8_t* g_static_ptr[kStaticMaxDevices];   // device address of g_orbm_static_scratch, per device (0 = not looked up)
+}  // namespace
+
+extern "C" int orbm_area_candidates_static(int device, void* stream, const orbx_keypoint* d_keys,
+                                           const uint8_t* d_desc, int n, float min_x, float min_y,
+                                           float grid_w_inv, float grid_h_inv, const orbm_area_query* d_q, int nq,
+                                           const uint8_t* d_q_desc, int32_t* d_row_ptr, int32_t* d_cand,
+                                           uint16_t* d_dist, int cap) {
+    if (device < 0 || device >= kStaticMaxDevices || n < 0 || nq < 0 || cap < 0)
+        return orbx_set_error(ORBX_E_BAD_ARG, "orbm_area_candidates_static: bad argument");
+    if (n > ORBM_STATIC_MAX_KEYS)
+        return orbx_set_error(ORBX_E_TOO_LARGE, "orbm_area_candidates_static: %d keypoints > ORBM_STATIC_MAX_KEYS (%d)",
+                              n, ORBM_STATIC_MAX_KEYS);
+    if (nq > ORBM_STATIC_MAX_QUERIES)
+        return orbx_set_error(ORBX_E_TOO_LARGE, "orbm_area_candidates_static: %d queries > ORBM_STATIC_MAX_QUERIES (%d)",
+                              nq, ORBM_STATIC_MAX_QUERIES);
+    if (!d_row_ptr || (n && (!d_keys || !d_desc)) || (nq && (!d_q || !d_q_desc)) || (cap && (!d_cand || !d_dist)))
+        return orbx_set_error(ORBX_E_BAD_ARG, "orbm_area_candidates_static: null argument");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess)
+        return orbx_set_error(ORBX_E_CUDA, "cudaSetDevice(%d) failed: %s", device, cudaGetErrorString(e));
+    uint8_t* base;
+    {
+        // The array's name is a host-side stand-in in host code, not a device address: look the address up once
+        // per device, with that device current, and hand THAT to the kernels.
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        if (!g_static_ptr[device]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_orbm_static_scratch);
+            if (e != cudaSuccess || !p)
+                return orbx_set_error(ORBX_E_CUDA, "cudaGetSymbolAddress(g_orbm_static_scratch) failed on device %d: %s",
+                                      device, cudaGetErrorString(e));
+            g_static_ptr[device] = (uint8_t*)p;
+        }
+        base = g_static_ptr[device];
+    }
+    int32_t* cellof = (int32_t*)base;
+    int32_t* start = cellof + ORBM_STATIC_MAX_KEYS;
+    int32_t* items = start + ORBM_STATIC_START_INTS;
+    int32_t* cnt = items + ORBM_STATIC_MAX_KEYS;
+    cudaStream_t st = (cudaStream_t)stream;
+    const OrbmGrid G{min_x, min_y, grid_w_inv, grid_h_inv};
+    // Nothing in the scratch has to start at zero: k_grid_build writes all 3073 offsets and the items of
+    // every keypoint inside the grid (its counters are shared memory, cleared by the kernel), k_area<count>
+    // writes cnt[0..nq), and only those ranges are read back.  The previous call's contents beyond them stay.
+    k_grid_build<<<1, 1024, 0, st>>>(d_keys, n, G, start, items, cellof);
+    if (nq) {
+        k_area<false><<<(nq + 7) / 8, 256, 0, st>>>(d_keys, start, items, G, d_q, nq, cnt, nullptr, nullptr, nullptr,
+                                                     nullptr, nullptr, 0);
+    }
+    k_rowptr_scan<<<1, 1024, 0, st>>>(cnt, nq, d_row_ptr);
+    if (nq) {
+        k_area<true><<<(nq + 7) / 8, 256, 0, st>>>(d_keys, start, items, G, d_q, nq, nullptr, d_row_ptr,
+                                                    reinterpret_cast<const uint4*>(d_q_desc),
+                                                    reinterpret_cast<const uint4*>(d_desc), d_cand, d_dist, cap);
+    }
+    e = cudaGetLastError();
+    if (e != cudaSuccess)
+        return orbx_set_error(ORBX_E_CUDA, "orbm_area_candidates_static: launch failed: %s", cudaGetErrorString(e));
+    return ORBX_OK;
+}
