@@ -54,7 +54,7 @@ def main():
     if not args.no_cpu:
         from oracle import pyoracle
         pyoracle.build("port")
-        mo = pyoracle.MatchOracle()
+        mo = pyoracle.MatchOracle()   # the timed CPU arm: our port (the verbatim build is the parity checker)
 
     m = ORBmatcher(0.8, True)
     lib, ctx = m.lib, m.ctx

@@ -12,7 +12,7 @@
  *                        over every (query, candidate) pair of a CSR candidate list
  *     orbm_knn2          cv::BFMatcher(NORM_HAMMING).knnMatch(k=2) src/Frame.cc:43,1146
  *     orbm_stereo_rows   Frame::ComputeStereoMatches, Hamming part src/Frame.cc:802-885
- *   layer 2 (whole searches on POD snapshots; grid + CSR on the host, distances on the GPU)
+ *   layer 2 (whole searches on POD snapshots; grid, candidate lists and distances on the GPU)
  *     orbm_search_by_projection_points   ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&..)
  *                                        src/ORBmatcher.cc:48-218 (monocular/rectified branch)
  *     orbm_search_by_projection_frames   ORBmatcher::SearchByProjection(Frame&, const Frame&..)
@@ -388,13 +388,6 @@ int orbm_last_device_ms(orbm_context* c, float* ms, long long* pairs);
 /* Measurement hook: the device's POPC issue rate in 1e9 popc/s (8 independent xor-popc-add chains
  * per thread, all SMs), the peak the Hamming kernels are held against (8 popc per pair). */
 int orbm_measure_popc_peak(orbm_context* c, double* gpopc_per_s);
-
-/* Frame::GetFeaturesInArea (src/Frame.cc:645-714) on a frame view, HOST restatement kept for the
- * parity tests of the candidate order: writes up to cap indices in the
- * reference's order (grid columns outer, rows inner, insertion order inside a cell); returns the
- * count.  Exposed for parity tests of the candidate order. */
-int orbm_features_in_area(const orbm_frame_view* F, float x, float y, float r, int min_level,
-                          int max_level, int32_t* out, int cap);
 
 #ifdef __cplusplus
 }

@@ -454,6 +454,17 @@ inline Mat gemm(const Mat& A0, const Mat& B0, double alpha, int flags, const Mat
     assert(K == Kb);
     (void)Kb;
     if (C && beta == 0) C = nullptr;
+    // Pinned against cv2 (tests/test_oracle_cvshim.py) for the scale factors the compiled reference files
+    // produce: alpha = +-1 (or a power of two), beta in {0, +-1}.  cv2's rounding for other factors is not
+    // reproduced here, so they are refused instead of silently computed differently.
+    {
+        int e;
+        const double fa = std::frexp(std::fabs(alpha), &e);
+        if (fa != 0.5 || !(beta == 0 || beta == 1 || beta == -1 || !C)) {
+            fprintf(stderr, "cvshim: gemm with alpha = %g, beta = %g is not pinned against OpenCV\n", alpha, beta);
+            abort();
+        }
+    }
     assert(!C || (C->rows == M && C->cols == N && C->mtype == A0.mtype));
     Mat D(M, N, A0.mtype);
     const bool small = flags == 0 && K >= 2 && K <= 4 && (K == N || K == M);

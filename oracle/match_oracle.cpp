@@ -1,11 +1,14 @@
 // oracle/match_oracle.cpp -- TEST INFRASTRUCTURE ONLY (CPU oracle for the ORBmatcher path).
 //
-// PARITY UNPINNED BY THE REFERENCE BUILD: src/ORBmatcher.cc cannot be compiled here (it needs
-// Frame.h/KeyFrame.h -> Eigen, DBoW2, g2o, none installed), and the reference holds no tests or
-// golden vectors.  This file restates the reference loops line by line on POD snapshots of the
-// same data; what CAN be pinned is pinned in tests/: the distance against numpy popcount, the
-// 2-NN search against cv2.BFMatcher(NORM_HAMMING).knnMatch (the un-vendored OpenCV call at
-// src/Frame.cc:1146), the candidate order against a brute-force scan.
+// PINNED TO THE REFERENCE: every function here is checked, bit for bit, against the reference's own
+// src/ORBmatcher.cc / src/Frame.cc / src/MapPoint.cc / Thirdparty/DBoW2 compiled VERBATIM into
+// oracle/_ref/liborbmref.so (oracle/ref_match_capi.cpp drives it with the same POD snapshots) by
+// tests/test_oracle_match.py, tests/test_oracle_match_ref.py and the goldens in tests/golden/ (generated
+// from the verbatim build).  This restatement stays because it builds from this repo alone, is the timed
+// CPU arm of bench_match.py, and holds the one piece the reference has no separate function for
+// (orbo_stereo_rows, the Hamming half of Frame::ComputeStereoMatches; the whole function is pinned).
+// Additionally: the distance against numpy popcount, the 2-NN search against cv2.BFMatcher(NORM_HAMMING)
+// .knnMatch (the un-vendored OpenCV call at src/Frame.cc:1146), the candidate order against a brute-force scan.
 //
 // Every distance here is computed inline with the reference's SWAR popcount, sequentially, per
 // candidate -- the opposite decomposition of the product (which batches all distances on the GPU

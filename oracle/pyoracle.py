@@ -16,6 +16,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_SO = os.path.join(HERE, "_ref", "liborbref.so")
+MREF_SO = os.path.join(HERE, "_ref", "liborbmref.so")
 PORT_SO = os.path.join(HERE, "_build", "liborb_oracle.so")
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
@@ -29,6 +30,10 @@ def build(target: str = "all") -> None:
 
 def have_ref() -> bool:
     return os.path.exists(REF_SO)
+
+
+def have_mref() -> bool:
+    return os.path.exists(MREF_SO)
 
 
 def have_port() -> bool:
@@ -163,15 +168,44 @@ class OracleExtractor:
         return cands, survs
 
 
-# ---- matcher oracle (oracle/match_oracle.cpp, in liborb_oracle.so) --------------------------------
-class MatchOracle:
-    """CPU restatement of the reference's Hamming searches on the same POD snapshots the product
-    takes (struct layouts of include/orbm.h).  Frame objects are orb_slam3_mac_b200.matcher.Frame."""
+# ---- matcher oracle --------------------------------------------------------------------------------
+class _Renamed:
+    """liborbmref.so exports the orbo_* surface under the prefix orbr_."""
 
-    def __init__(self):
-        if not have_port():
-            build("port")
-        self.lib = C.CDLL(PORT_SO)
+    def __init__(self, lib):
+        self._lib = lib
+
+    def __getattr__(self, name):
+        return getattr(self._lib, "orbr_" + name[len("orbo_"):] if name.startswith("orbo_") else name)
+
+
+def canon_inv_z(a):
+    """inv_z values that survive float(1 / float(1 / inv_z)): what SearchByProjection(Cur, Last) computes from a
+    depth (src/ORBmatcher.cc:2001).  The reference-held oracle refuses other inputs."""
+    a = np.asarray(a, np.float32).copy()
+    for _ in range(4):
+        z = (1.0 / a.astype(np.float64)).astype(np.float32)
+        a = (1.0 / z.astype(np.float64)).astype(np.float32)
+    return a
+
+
+class MatchOracle:
+    """The reference's Hamming searches on the same POD snapshots the product takes (struct layouts of
+    include/orbm.h).  Frame objects are orb_slam3_mac_b200.matcher.Frame.
+      kind="port": oracle/match_oracle.cpp, our restatement (liborb_oracle.so);
+      kind="ref":  the reference's own src/ORBmatcher.cc / Frame.cc / MapPoint.cc / DBoW2, compiled verbatim
+                   (oracle/_ref/liborbmref.so through oracle/ref_match_capi.cpp)."""
+
+    def __init__(self, kind: str = "port"):
+        self.kind = kind
+        if kind == "ref":
+            if not have_mref():
+                build("mref")
+            self.lib = _Renamed(C.CDLL(MREF_SO))
+        else:
+            if not have_port():
+                build("port")
+            self.lib = C.CDLL(PORT_SO)
 
     def distance(self, a, b):
         return self.lib.orbo_descriptor_distance(C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data))
@@ -244,6 +278,8 @@ class MatchOracle:
         return n, m12, prev
 
     def stereo_rows(self, left, right, n_rows, min_d, max_d):
+        if self.kind == "ref":
+            raise NotImplementedError("the reference has no separate row search: use compute_stereo_matches")
         bi = np.zeros(left.N, np.int32)
         bd = np.zeros(left.N, np.int32)
         self.lib.orbo_stereo_rows(C.c_void_p(left.keys.ctypes.data), C.c_void_p(left.desc.ctypes.data), left.N,
@@ -269,7 +305,7 @@ class MatchOracle:
             C.c_void_p(right.keys.ctypes.data), C.c_void_p(right.desc.ctypes.data), right.N,
             C.c_void_p(left.scale_factors.ctypes.data), C.c_void_p(inv.ctypes.data), pl, sl, pr, sr, cr,
             int(keep[0].shape[0] - 38), C.c_float(mb), C.c_float(mbf), C.c_void_p(u.ctypes.data),
-            C.c_void_p(d.ctypes.data))
+            C.c_void_p(d.ctypes.data), *([nl] if self.kind == "ref" else []))
         return u, d, n
 
     # ---- SURVEY 8(f) N3 ----------------------------------------------------------------------------
@@ -301,13 +337,21 @@ class MatchOracle:
                                                      int(orb_dist), int(check_ori), self._p(taken), self._p(match))
         return n, match
 
-    def fuse(self, KF, pts, mp_desc, th, inv_level_sigma2=None, idx_offset=0):
+    def fuse(self, KF, pts, mp_desc, th, inv_level_sigma2=None, idx_offset=0, depth=None, bf=0.0):
+        """depth / bf: the camera-frame depth of every point and the keyframe's mbf, from which the caller derived
+        pts["ur"] = u - bf * (1 / depth) (src/ORBmatcher.cc:1490); only the reference-held oracle needs them."""
         inv = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
         bi = np.zeros(len(pts), np.int32)
         bd = np.zeros(len(pts), np.int32)
         v = KF.view()
+        extra = []
+        if self.kind == "ref":
+            dz = None if depth is None else np.ascontiguousarray(depth, np.float32)
+            assert inv is None or dz is not None, "the reference-held Fuse needs the points' depths"
+            extra = [self._p(dz), C.c_float(bf)]
         n = self.lib.orbo_fuse(C.byref(v), self._p(pts), self._p(mp_desc), len(pts), C.c_float(th), self._p(inv),
-                               int(idx_offset), self._p(bi), self._p(bd))
+                               int(idx_offset), self._p(bi), self._p(bd), *extra)
+        assert n >= 0, n
         return n, bi, bd
 
     def search_by_sim3(self, KF1, KF2, p1, d1, p2, d2, th):
@@ -318,13 +362,16 @@ class MatchOracle:
         return n, m12
 
     def search_for_triangulation(self, KF1, has1, st1, KF2, has2, st2, only_stereo, ep, sf2, pair_ok, F12, ls2,
-                                 check_ori):
+                                 check_ori, overload=1):
+        """overload 1: SearchForTriangulation(.., bOnlyStereo, bCoarse) src/ORBmatcher.cc:969; 2: the matchAndtriangulate
+        form :1212 (no stereo / epipole gates there: pass st1 = st2 = ep = None)."""
         m12 = np.zeros(len(KF1.keys), np.int32)
         v1, v2 = KF1.view(), KF2.view()
         n = self.lib.orbo_search_for_triangulation(C.byref(v1), self._p(has1), self._p(st1), C.byref(v2), self._p(has2),
                                                    self._p(st2), int(only_stereo), self._p(ep), self._p(sf2),
                                                    self._p(pair_ok), self._p(F12), self._p(ls2), int(check_ori),
-                                                   self._p(m12))
+                                                   self._p(m12), *([int(overload)] if self.kind == "ref" else []))
+        assert n >= 0, n
         return n, m12
 
     def distinctive_descriptors(self, desc, group_ptr):
@@ -354,6 +401,11 @@ class MatchOracle:
         t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
         idx = np.zeros((len(q), 2), np.int32)
         dist = np.zeros((len(q), 2), np.int32)
+        if self.kind == "ref":   # the reference calls cv::BFMatcher (src/Frame.cc:1146): here the shim's restatement of it
+            fd = np.zeros((len(q), 2), np.float32)
+            self.lib.orbo_shim_knn2(C.c_void_p(q.ctypes.data), len(q), C.c_void_p(t.ctypes.data), len(t),
+                                    C.c_void_p(idx.ctypes.data), C.c_void_p(fd.ctypes.data))
+            return idx, fd.astype(np.int32)
         self.lib.orbo_knn2(C.c_void_p(q.ctypes.data), len(q), C.c_void_p(t.ctypes.data), len(t),
                            C.c_void_p(idx.ctypes.data), C.c_void_p(dist.ctypes.data))
         return idx, dist

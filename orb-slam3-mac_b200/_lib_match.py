@@ -79,7 +79,6 @@ ORBM_SYMBOLS = {
     "orbm_area_candidates_static": (_i, [_i, _vp, _vp, _vp, _i, _f, _f, _f, _f, _vp, _i, _vp, _vp, _vp, _vp, _i]),
     "orbm_last_device_ms": (_i, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_longlong)]),
     "orbm_measure_popc_peak": (_i, [_vp, C.POINTER(C.c_double)]),
-    "orbm_features_in_area": (_i, [_fv, _f, _f, _f, _i, _i, _vp, _i]),
 }
 
 

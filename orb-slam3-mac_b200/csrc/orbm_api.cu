@@ -464,61 +464,6 @@ int orbm_compute_stereo_matches(orbm_context* c, const orbx_keypoint* kps_l, con
 // =================================================================================================
 namespace {
 
-// Frame::AssignFeaturesToGrid + PosInGrid (src/Frame.cc:377-408, 716-726): 64 x 48 buckets,
-// keypoint -> cell by ROUND (not floor); out-of-range keypoints are simply not inserted.
-struct Grid {
-    std::vector<int32_t> start;  // [64*48 + 1], cell index = ix * 48 + iy
-    std::vector<int32_t> items;  // keypoint indices, insertion (= index) order inside a cell
-};
-
-void build_grid(const orbm_frame_view* F, Grid& g) {
-    const int nc = ORBM_GRID_COLS * ORBM_GRID_ROWS;
-    std::vector<int32_t> cell(F->n, -1);
-    g.start.assign(nc + 1, 0);
-    for (int i = 0; i < F->n; ++i) {
-        const int px = (int)roundf((F->keys[i].x - F->min_x) * F->grid_w_inv);
-        const int py = (int)roundf((F->keys[i].y - F->min_y) * F->grid_h_inv);
-        if (px < 0 || px >= ORBM_GRID_COLS || py < 0 || py >= ORBM_GRID_ROWS) continue;
-        cell[i] = px * ORBM_GRID_ROWS + py;
-        ++g.start[cell[i] + 1];
-    }
-    for (int c = 0; c < nc; ++c) g.start[c + 1] += g.start[c];
-    g.items.assign(g.start[nc], 0);
-    std::vector<int32_t> fill(g.start.begin(), g.start.end() - 1);
-    for (int i = 0; i < F->n; ++i)
-        if (cell[i] >= 0) g.items[fill[cell[i]]++] = i;
-}
-
-// Frame::GetFeaturesInArea (src/Frame.cc:645-714); appends to `out` in the reference's order.
-void features_in_area(const orbm_frame_view* F, const Grid& g, float x, float y, float r, int minLevel,
-                      int maxLevel, std::vector<int32_t>& out) {
-    const float factorX = r, factorY = r;
-    const int nMinCellX = std::max(0, (int)floorf((x - F->min_x - factorX) * F->grid_w_inv));
-    if (nMinCellX >= ORBM_GRID_COLS) return;
-    const int nMaxCellX = std::min((int)ORBM_GRID_COLS - 1, (int)ceilf((x - F->min_x + factorX) * F->grid_w_inv));
-    if (nMaxCellX < 0) return;
-    const int nMinCellY = std::max(0, (int)floorf((y - F->min_y - factorY) * F->grid_h_inv));
-    if (nMinCellY >= ORBM_GRID_ROWS) return;
-    const int nMaxCellY = std::min((int)ORBM_GRID_ROWS - 1, (int)ceilf((y - F->min_y + factorY) * F->grid_h_inv));
-    if (nMaxCellY < 0) return;
-    const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
-    for (int ix = nMinCellX; ix <= nMaxCellX; ++ix) {
-        for (int iy = nMinCellY; iy <= nMaxCellY; ++iy) {
-            const int c = ix * ORBM_GRID_ROWS + iy;
-            for (int k = g.start[c]; k < g.start[c + 1]; ++k) {
-                const int idx = g.items[k];
-                const orbx_keypoint& kp = F->keys[idx];
-                if (bCheckLevels) {
-                    if (kp.octave < minLevel) continue;
-                    if (maxLevel >= 0 && kp.octave > maxLevel) continue;
-                }
-                const float distx = kp.x - x, disty = kp.y - y;
-                if (fabsf(distx) < factorX && fabsf(disty) < factorY) out.push_back(idx);
-            }
-        }
-    }
-}
-
 // ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:2307-2348)
 void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3) {
     int max1 = 0, max2 = 0, max3 = 0;
@@ -716,18 +661,6 @@ int orbm_area_candidates(orbm_context* c, const orbm_frame_view* F, const orbm_a
         if (dist && q_desc) dist[k] = c->hdist[k];
     }
     return nnz;
-}
-
-int orbm_features_in_area(const orbm_frame_view* F, float x, float y, float r, int min_level, int max_level,
-                          int32_t* out, int cap) {
-    int rc = check_view(F);
-    if (rc) return rc;
-    Grid g;
-    build_grid(F, g);
-    std::vector<int32_t> v;
-    features_in_area(F, g, x, y, r, min_level, max_level, v);
-    for (size_t i = 0; i < v.size() && out && (int)i < cap; ++i) out[i] = v[i];
-    return (int)v.size();
 }
 
 int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, const orbm_map_point* mps,

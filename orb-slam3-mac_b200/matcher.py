@@ -45,15 +45,6 @@ class Frame:
                          self.scale_factors.ctypes.data, len(self.scale_factors),
                          None if self.u_right is None else self.u_right.ctypes.data)
 
-    def GetFeaturesInArea(self, x, y, r, minLevel=-1, maxLevel=-1):
-        lib = _lib.load()
-        out = np.zeros(max(1, self.N), np.int32)
-        v = self.view()
-        n = lib.orbm_features_in_area(C.byref(v), x, y, r, minLevel, maxLevel, out.ctypes.data, len(out))
-        if n < 0:
-            check(n)
-        return out[:n].copy()
-
 
 class BowSide:
     """One side of SearchByBoW: keypoints, descriptors and the DBoW2::FeatureVector as

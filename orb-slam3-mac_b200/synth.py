@@ -167,7 +167,10 @@ def last_frame_obs(keys, desc, seed: int):
     lo = np.zeros(n, LAST_OBS_DTYPE)
     lo["u"] = keys["x"] + 3.0 + rng.normal(0, 1.0, n)
     lo["v"] = keys["y"] + rng.normal(0, 1.0, n)
-    lo["inv_z"] = rng.uniform(-0.02, 1.0, n)  # a few points behind the camera
+    inv_z = rng.uniform(-0.02, 1.0, n).astype(np.float32)  # a few points behind the camera
+    for _ in range(4):   # keep values that ARE float(1 / z) of a float depth z, as src/ORBmatcher.cc:2001 computes invzc
+        inv_z = (1.0 / (1.0 / inv_z.astype(np.float64)).astype(np.float32).astype(np.float64)).astype(np.float32)
+    lo["inv_z"] = inv_z
     lo["angle"] = keys["angle"]
     lo["octave"] = keys["octave"]
     lo["observations"] = rng.integers(0, 4, n)

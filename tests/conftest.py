@@ -20,6 +20,7 @@ def oracle_libs():
     from oracle import pyoracle as po
     po.build("port")
     po.build("ref")
+    po.build("mref")
     return po
 
 

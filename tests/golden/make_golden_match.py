@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """Generates tests/golden/match_golden.json (run in the build container):
-  * matcher cases (match_cases.run_matcher_cases) from the CPU oracle, oracle/match_oracle.cpp -- the
-    reference's ORBmatcher.cc cannot be compiled here (Eigen/DBoW2/g2o headers), so these goldens
-    freeze the restatement the CUDA path was validated against;
+  * matcher cases (match_cases.run_matcher_cases) from the REFERENCE'S OWN src/ORBmatcher.cc / Frame.cc,
+    compiled verbatim (oracle/_ref/liborbmref.so, MatchOracle("ref")); our restatement (MatchOracle("port"))
+    must agree before anything is written;
   * the input-stage case from the REAL OpenCV of this image (cv2.remap + cv2.cvtColor)."""
 import json
 import os
@@ -17,7 +17,9 @@ if __name__ == "__main__":
     from oracle import pyoracle as po
     from tests.golden import match_cases as mc
     po.build("port")
-    out = {"matcher": mc.run_matcher_cases(po.MatchOracle())}
+    po.build("mref")
+    out = {"matcher": mc.run_matcher_cases(po.MatchOracle("ref")), "source": "reference src/ORBmatcher.cc, verbatim"}
+    assert out["matcher"] == mc.run_matcher_cases(po.MatchOracle("port")), "port != reference"
     cv2.setNumThreads(1)
     bgr, mx, my = mc.input_stage_case()
     rect = cv2.remap(bgr, mx, my, cv2.INTER_LINEAR)

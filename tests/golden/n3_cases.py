@@ -6,6 +6,9 @@ import numpy as np
 from .match_cases import SF, feat_vec, frames, sha  # noqa: F401
 
 
+BF = np.float32(40.0)   # the keyframes' mbf in the Fuse cases
+
+
 def proj_points(keys, rng, jitter=1.5, invalid=0.15, level_shift=True):
     """Map points 'projected' next to the keypoints they came from (position + noise, predicted level =
     octave or octave + 1, so both ends of the [level-1, level] gate are used)."""
@@ -14,14 +17,16 @@ def proj_points(keys, rng, jitter=1.5, invalid=0.15, level_shift=True):
     p = np.zeros(n, PROJ_POINT_DTYPE)
     p["u"] = (keys["x"] + rng.normal(0, jitter, n)).astype(np.float32)
     p["v"] = (keys["y"] + rng.normal(0, jitter, n)).astype(np.float32)
-    p["ur"] = (p["u"] - rng.uniform(2, 40, n)).astype(np.float32)
+    # the point's camera-frame depth; Fuse derives ur = u - bf * (1 / z) from it in float32 (src/ORBmatcher.cc:1448-1490)
+    depth = rng.uniform(1.0, 20.0, n).astype(np.float32)
+    p["ur"] = p["u"] - BF * (np.float32(1) / depth)
     p["angle"] = keys["angle"]
     lvl = keys["octave"].astype(np.int32)
     if level_shift:
         lvl = np.minimum(lvl + (rng.random(n) < 0.4), 7)
     p["level"] = lvl
     p["valid"] = (rng.random(n) >= invalid).astype(np.uint8)
-    return p
+    return p, depth
 
 
 def n3_inputs(seed=11):
@@ -35,16 +40,18 @@ def n3_inputs(seed=11):
     FB = Frame(kb, db, 752, 480, SF, u_right=ur_b)
     FBm = Frame(kb, db, 752, 480, SF)
     # points of A projected into B (B = A shifted by 3 px in x) and the reverse
-    pa = proj_points(ka, rng)
+    pa, za = proj_points(ka, rng)
     pa["u"] += 3.0
-    pb = proj_points(kb, rng)
+    pa["ur"] += 3.0
+    pb, _ = proj_points(kb, rng)
     pb["u"] -= 3.0
     mpd_a = S.flip_bits(da, 0.04, rng)   # map-point descriptors differ a little from the keyframe's
     mpd_b = S.flip_bits(db, 0.04, rng)
     fva, fvb = feat_vec(ka, rng), feat_vec(kb, rng)
     KA, KB = BowSide(ka, da, fva), BowSide(kb, db, fvb)
+    pa["ur"] = pa["u"] - BF * (np.float32(1) / za)   # after the shift: exactly what the reference computes from (u, bf, z)
     return dict(rng=rng, ka=ka, da=da, kb=kb, db=db, FA=FA, FB=FB, FBm=FBm, pa=pa, pb=pb, mpd_a=mpd_a, mpd_b=mpd_b,
-                KA=KA, KB=KB)
+                KA=KA, KB=KB, za=za)
 
 
 def distinctive_case(seed=3, sizes=None):
@@ -86,7 +93,7 @@ def run_n3_cases(backend):
         n, match = backend.search_by_projection_reloc(FBm, I["pa"], I["mpd_a"], th, od, check, taken)
         out[name] = {"n": int(n), "match": match}
     inv_sigma2 = (1.0 / (SF * SF)).astype(np.float32)
-    n, bi, bd = backend.fuse(FB, I["pa"], I["mpd_a"], 3.0, inv_sigma2, 0)
+    n, bi, bd = backend.fuse(FB, I["pa"], I["mpd_a"], 3.0, inv_sigma2, 0, depth=I["za"], bf=float(BF))
     out["fuse_chi2"] = {"n": int(n), "idx": bi, "dist": bd}
     n, bi, bd = backend.fuse(FBm, I["pa"], I["mpd_a"], 4.0, None, 5000)
     out["fuse_sim3"] = {"n": int(n), "idx": bi, "dist": bd}
@@ -108,6 +115,10 @@ def run_n3_cases(backend):
     out["tri_pinhole"] = {"n": int(n), "m12": m12}
     n, m12 = backend.search_for_triangulation(I["KA"], has1, st1, I["KB"], has2, st2, True, None, None, None, None, None, False)
     out["tri_coarse_stereo"] = {"n": int(n), "m12": m12}
+    # the matchAndtriangulate overload (src/ORBmatcher.cc:1212-1401): no stereo / epipole gates
+    n, m12 = backend.search_for_triangulation(I["KA"], has1, None, I["KB"], has2, None, False, None, None, pair_ok, None, None, True,
+                                              overload=2)
+    out["tri_overload2"] = {"n": int(n), "m12": m12}
     d, gp = distinctive_case()
     out["distinctive"] = {"best": backend.distinctive_descriptors(d, gp)}
     # N4: DBoW2 transform on a synthetic vocabulary (ragged and regular trees, every weighting / norm branch)

@@ -1,6 +1,8 @@
-"""Parity of the CUDA Hamming searches (through the C ABI of include/orbm.h) against the CPU
-oracle on the same POD snapshots: distances, 2-NN, rectified-stereo arg-min, and the three
-order-dependent ORBmatcher searches.  Bar: bit-exact match indices and counts (north_star)."""
+"""Parity of the CUDA Hamming searches (through the C ABI of include/orbm.h) on the same POD snapshots against
+the REFERENCE'S OWN matcher code -- src/ORBmatcher.cc, src/Frame.cc, src/MapPoint.cc, DBoW2 compiled verbatim into
+oracle/_ref/liborbmref.so (MatchOracle("ref"); the prebuilt library travels to the GPU box) -- and, for the one
+piece the reference has no separate function for (the row search inside ComputeStereoMatches), against our
+restatement, which tests/test_oracle_match*.py pin to the reference.  Bar: bit-exact indices and counts."""
 import numpy as np
 import pytest
 
@@ -13,7 +15,12 @@ SF = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
 
 @pytest.fixture(scope="module")
 def mo(oracle_libs):
-    return oracle_libs.MatchOracle()
+    return oracle_libs.MatchOracle("ref" if oracle_libs.have_mref() else "port")
+
+
+@pytest.fixture(scope="module")
+def mo_port(oracle_libs):
+    return oracle_libs.MatchOracle("port")
 
 
 @pytest.fixture(scope="module")
@@ -94,7 +101,7 @@ def test_fisheye_stereo_knn2_c3(matcher, mo, extract):
     assert good.sum() > 100  # the pair really overlaps
 
 
-def test_stereo_rows_c2(matcher, mo, extract):
+def test_stereo_rows_c2(matcher, mo_port, extract):
     """Config C2: EuRoC stereo pair, 1200 features per image, lapping {0,0}."""
     for seed in (1, 2):
         l, r = S.stereo_pair(480, 752, seed)
@@ -103,7 +110,7 @@ def test_stereo_rows_c2(matcher, mo, extract):
         L, R = _frame(kl, dl, 752, 480), _frame(kr, dr, 752, 480)
         for min_d, max_d in ((0.0, 80.0), (0.0, 20.0), (5.0, 400.0)):
             bi, bd = matcher.stereo_rows(L, R, min_d, max_d)
-            oi, od = mo.stereo_rows(L, R, 480, min_d, max_d)
+            oi, od = mo_port.stereo_rows(L, R, 480, min_d, max_d)
             assert np.array_equal(bi, oi) and np.array_equal(bd, od)
         bi, bd = matcher.stereo_rows(L, R, 0.0, 80.0)
         assert (bd < 75).sum() > 200  # thOrbDist (src/Frame.cc:807): plenty of real matches
@@ -612,13 +619,14 @@ class _ProductN3:
     def search_by_projection_reloc(self, F, pts, d, th, od, check, taken):
         return self._run(0.8, check, lambda m: m.SearchByProjectionReloc(F, pts, d, th, od, taken))
 
-    def fuse(self, KF, pts, d, th, inv, off):
+    def fuse(self, KF, pts, d, th, inv, off, depth=None, bf=0.0):   # depth / bf: how the case derived pts["ur"]
         return self._run(0.8, True, lambda m: m.Fuse(KF, pts, d, th, inv, off))
 
     def search_by_sim3(self, KF1, KF2, p1, d1, p2, d2, th):
         return self._run(0.8, True, lambda m: m.SearchBySim3(KF1, KF2, p1, d1, p2, d2, th))
 
-    def search_for_triangulation(self, KF1, has1, st1, KF2, has2, st2, only_stereo, ep, sf2, pair_ok, F12, ls2, check):
+    def search_for_triangulation(self, KF1, has1, st1, KF2, has2, st2, only_stereo, ep, sf2, pair_ok, F12, ls2, check,
+                                 overload=1):   # both overloads are one entry point of the C ABI
         test = None if pair_ok is None else (lambda a, b: pair_ok[a, b])   # the camera model as a callback
         return self._run(0.8, check, lambda m: m.SearchForTriangulation(KF1, has1, KF2, has2, st1, st2, only_stereo, ep,
                                                                         sf2, test, F12, ls2))
@@ -640,13 +648,13 @@ def test_n3_searches_against_committed_goldens_and_oracle(oracle_libs):
     """SURVEY 8(f) N3 through the C ABI: SearchByBoW(KF,KF), SearchByProjection(pKF,Scw,..) / reloc, Fuse x2,
     SearchBySim3, SearchForTriangulation (callback, pinhole F12 and coarse forms), ComputeDistinctiveDescriptors, and the
     DBoW2 transform of N4 (BowVector doubles bit-identical).
-    Bit-exact against tests/golden/n3_golden.json (frozen from the CPU oracle) and, array by array, against the
-    oracle itself."""
+    Bit-exact against tests/golden/n3_golden.json (frozen from the reference's own code, make_golden_n3.py) and, array
+    by array, against the reference-held oracle (oracle/_ref/liborbmref.so) run here."""
     import json
     import os
     from tests.golden import n3_cases as nc
     got = nc.run_n3_cases(_ProductN3())
-    exp = nc.run_n3_cases(oracle_libs.MatchOracle())
+    exp = nc.run_n3_cases(oracle_libs.MatchOracle("ref" if oracle_libs.have_mref() else "port"))
     for case, r in exp.items():
         for k, v in r.items():
             g = got[case][k]
