@@ -171,8 +171,139 @@ class CpuReference:
 
     def describe(self, sample: str):
         return {"cores": self.threads, "kind": "reference" if self.kind == "ref" else "port",
-                "sample": sample + "; reference src/ORBextractor.cc compiled verbatim (-O3 -march=x86-64-v3), "
-                          "its OpenCV primitives restated in oracle/cvprims.h (scalar FAST/resize/blur)"}
+                "sample": sample + "; reference src/ORBextractor.cc compiled verbatim (-O3 -march=x86-64-v3 -ffp-contract=off; the "
+                          "reference's own flag is -march=native), its OpenCV primitives restated in oracle/cvprims.h "
+                          "(scalar FAST/resize/blur: see stage_guard / value_guarded for what real SIMD OpenCV changes), "
+                          "std::list nodes from a per-thread bump arena whose pages stay mapped between frames"}
+
+
+def _fast_cells(w: int, h: int):
+    """The per-cell FAST sub-images of one level, src/ORBextractor.cc:771-804: (x0, y0, x1, y1) per cell."""
+    min_x = min_y = 16
+    max_x, max_y = w - 16, h - 16
+    width, height = float(max_x - min_x), float(max_y - min_y)
+    n_cols, n_rows = int(width / 30), int(height / 30)
+    if n_cols < 1 or n_rows < 1:
+        return []
+    w_cell, h_cell = int(np.ceil(width / n_cols)), int(np.ceil(height / n_rows))
+    cells = []
+    for i in range(n_rows):
+        ini_y = min_y + i * h_cell
+        if ini_y >= max_y - 3:
+            continue
+        for j in range(n_cols):
+            ini_x = min_x + j * w_cell
+            if ini_x >= max_x - 6:
+                continue
+            cells.append((ini_x, ini_y, min(ini_x + w_cell + 6, max_x), min(ini_y + h_cell + 6, max_y)))
+    return cells
+
+
+def cpu_stage_guard(cfg: str, frames: np.ndarray, nframes: int = 4):
+    """BASELINE.md 4.4 / SURVEY 8(d): the strawman guard.  The timed CPU arm is the reference's ORBextractor.cc on
+    OUR scalar restatements of resize / FAST / GaussianBlur; real OpenCV has SIMD.  In the same run, single thread,
+    on the same frames: per-stage time of the shim primitives and of cv2's (cv2.setNumThreads(1)), over exactly the
+    calls the reference makes (7 resizes, one FAST per 30-px cell with the minThFAST rerun, 8 blurs).  cv2's FAST is
+    ALSO timed as one whole-level call (no Python call overhead per cell, less work than the cells' overlaps): the
+    smaller of the two is what the guard uses, so the guarded CPU figure errs towards a FASTER CPU.
+    Returns per-stage ms/frame and the factor by which real OpenCV primitives would shorten the reference frame."""
+    import ctypes as C2
+    from oracle import pyoracle as po
+    import orb_slam3_mac_b200 as pkg
+    try:
+        import cv2
+    except Exception as e:   # the image has cv2; say so if a box does not
+        return {"unavailable": f"cv2 import failed: {e}"}
+    cv2.setNumThreads(1)
+    if not po.have_port():
+        po.build("port")
+    lib = C2.CDLL(po.PORT_SO)
+    lib.orbo_prim_fast.restype = C2.c_int
+    nf = pkg.synth.NFEATURES[cfg]
+    ex = po.OracleExtractor(nf, 1.2, 8, 20, 7, kind="ref" if po.have_ref() else "port")
+    p = lambda a: C2.c_void_p(a.ctypes.data)
+    tm = {k: 0.0 for k in ("total_shim", "resize_shim", "resize_cv2", "fast_shim", "fast_cv2_cells", "fast_cv2_levels",
+                           "blur_shim", "blur_cv2")}
+    det = {th: cv2.FastFeatureDetector_create(th, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16) for th in (20, 7)}
+    ex(frames[0], (0, 1000))
+    insitu = None
+    if po.have_ref():   # seconds inside cv::resize / cv::FAST / cv::GaussianBlur of the timed extraction itself
+        rl = C2.CDLL(po.REF_SO)
+        rl.orbref_stage_clock.restype = None
+        insitu = np.zeros(3, np.float64)
+    for f in range(nframes):
+        img = np.ascontiguousarray(frames[f % len(frames)])
+        if insitu is not None:
+            rl.orbref_stage_clock(1, None)
+        t0 = time.perf_counter()
+        ex(img, (0, 1000))
+        tm["total_shim"] += time.perf_counter() - t0
+        if insitu is not None:
+            got = np.zeros(3, np.float64)
+            rl.orbref_stage_clock(0, p(got))
+            insitu += got
+        levels = [ex.level(l, 0) for l in range(8)]
+        # resize chain
+        t0 = time.perf_counter()
+        for l in range(1, 8):
+            dst = np.empty_like(levels[l])
+            lib.orbo_prim_resize(p(levels[l - 1]), levels[l - 1].shape[0], levels[l - 1].shape[1],
+                                 C2.c_size_t(levels[l - 1].strides[0]), p(dst), dst.shape[0], dst.shape[1],
+                                 C2.c_size_t(dst.strides[0]))
+        tm["resize_shim"] += time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for l in range(1, 8):
+            cv2.resize(levels[l - 1], (levels[l].shape[1], levels[l].shape[0]), interpolation=cv2.INTER_LINEAR)
+        tm["resize_cv2"] += time.perf_counter() - t0
+        # per-cell FAST with the minThFAST rerun of empty cells
+        out = np.zeros(3 * 64 * 64, np.int32)
+        cells = [(lv, c) for lv in levels for c in _fast_cells(lv.shape[1], lv.shape[0])]
+        t0 = time.perf_counter()
+        for lv, (x0, y0, x1, y1) in cells:
+            sub = lv[y0:y1, x0:x1]
+            if lib.orbo_prim_fast(p(sub), sub.shape[0], sub.shape[1], C2.c_size_t(lv.strides[0]), 20, p(out), 64 * 64) == 0:
+                lib.orbo_prim_fast(p(sub), sub.shape[0], sub.shape[1], C2.c_size_t(lv.strides[0]), 7, p(out), 64 * 64)
+        tm["fast_shim"] += time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for lv, (x0, y0, x1, y1) in cells:
+            sub = lv[y0:y1, x0:x1]
+            if not det[20].detect(sub):
+                det[7].detect(sub)
+        tm["fast_cv2_cells"] += time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for lv in levels:
+            det[20].detect(lv[16:lv.shape[0] - 16, 16:lv.shape[1] - 16])
+        tm["fast_cv2_levels"] += time.perf_counter() - t0
+        # 7x7 sigma-2 blur of every level
+        t0 = time.perf_counter()
+        for lv in levels:
+            dst = np.empty_like(lv)
+            lib.orbo_prim_blur(p(lv), lv.shape[0], lv.shape[1], C2.c_size_t(lv.strides[0]), p(dst), C2.c_size_t(dst.strides[0]))
+        tm["blur_shim"] += time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for lv in levels:
+            cv2.GaussianBlur(lv, (7, 7), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+        tm["blur_cv2"] += time.perf_counter() - t0
+    ms = {k: 1e3 * v / nframes for k, v in tm.items()}
+    standalone = {k: ms[k] for k in ("resize_shim", "fast_shim", "blur_shim")}
+    if insitu is not None:   # the standalone loops above carry ~5 us of ctypes overhead per call; these do not
+        ms["resize_shim"], ms["fast_shim"], ms["blur_shim"] = (1e3 * insitu / nframes).tolist()
+    fast_cv2 = min(ms["fast_cv2_cells"], ms["fast_cv2_levels"])
+    saved = (max(0.0, ms["resize_shim"] - ms["resize_cv2"]) + max(0.0, ms["fast_shim"] - fast_cv2) +
+             max(0.0, ms["blur_shim"] - ms["blur_cv2"]))
+    guarded = max(ms["total_shim"] - saved, 1e-3)
+    return {"threads": 1, "frames": nframes, "cv2": cv2.__version__,
+            "stage_ms_per_frame": {"resize": {"shim_ms": ms["resize_shim"], "cv2_ms": ms["resize_cv2"]},
+                                   "fast": {"shim_ms": ms["fast_shim"], "cv2_ms": fast_cv2,
+                                            "cv2_per_cell_calls_ms": ms["fast_cv2_cells"],
+                                            "cv2_whole_level_ms": ms["fast_cv2_levels"], "cells": len(cells)},
+                                   "blur": {"shim_ms": ms["blur_shim"], "cv2_ms": ms["blur_cv2"]}},
+            "shim_stage_source": "in situ (clock inside the shim's cv::resize / cv::FAST / cv::GaussianBlur during the timed "
+                                 "extraction)" if insitu is not None else "standalone loops over the same calls",
+            "shim_standalone_ms": standalone,
+            "frame_ms_shim": ms["total_shim"], "frame_ms_guarded": guarded, "speedup_if_real_opencv": ms["total_shim"] / guarded,
+            "what": "per stage the faster of {our scalar shim, cv2 single-thread}; the rest of the frame (quadtree, "
+                    "orientation, descriptors, glue) is the reference's own code either way"}
 
 
 def workload_name(cfg: str, h: int, w: int) -> str:
@@ -612,6 +743,12 @@ def run_ours(args):
             one = CpuReference(cfg, 1)
             one.run(frames, 2)
             cb["single_thread_value"] = 16 / one.run(frames, 16)
+            cb["nproc"] = os.cpu_count()
+            g = cpu_stage_guard(cfg, frames)
+            cb["stage_guard"] = g
+            if "speedup_if_real_opencv" in g:   # the CPU figure if every OpenCV primitive ran at cv2's single-thread speed
+                cb["value_guarded"] = cb["value"] * g["speedup_if_real_opencv"]
+                line["e2e"]["vs_cpu_guarded"] = line["e2e"]["value"] / cb["value_guarded"]
             line["cpu_baseline"] = cb
         print(json.dumps(line), flush=True)
 

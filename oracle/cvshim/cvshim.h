@@ -21,6 +21,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <iostream>
 #include <limits>
 #include <memory>
@@ -871,6 +872,30 @@ public:
 template <typename T>
 static inline FileStorage& operator<<(FileStorage& fs, const T&) { abort(); return fs; }
 
+// Optional per-thread stage clock (off by default): seconds spent inside the three OpenCV primitives that
+// dominate the extractor, measured in situ so bench.py's strawman guard can say what real OpenCV would change.
+struct StageClock {
+    bool on = false;
+    double resize = 0, fast = 0, blur = 0;
+};
+inline StageClock& stage_clock() {
+    static thread_local StageClock c;
+    return c;
+}
+struct StageTimer {
+    double* acc;
+    timespec t0;
+    explicit StageTimer(double* a) : acc(stage_clock().on ? a : nullptr) {
+        if (acc) clock_gettime(CLOCK_MONOTONIC, &t0);
+    }
+    ~StageTimer() {
+        if (!acc) return;
+        timespec t1;
+        clock_gettime(CLOCK_MONOTONIC, &t1);
+        *acc += (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+    }
+};
+
 // Optional per-thread observer of every cv::FAST call (used by oracle/ref_capi.cpp to dump the
 // per-cell candidate lists, which are locals of ComputeKeyPointsOctTree in the reference).
 struct FastObserver {
@@ -886,6 +911,7 @@ static inline void FAST(InputArray image, std::vector<KeyPoint>& keypoints, int 
                         bool nonmaxSuppression) {
     assert(nonmaxSuppression);
     (void)nonmaxSuppression;
+    StageTimer _st(&stage_clock().fast);
     Mat img = image.getMat();
     std::vector<cvprims::FastKp> v;
     cvprims::fast9_nms(img.data, img.rows, img.cols, img.step, threshold, v);
@@ -900,6 +926,7 @@ static inline void resize(InputArray src, OutputArray dst, Size dsize, double fx
                           int interpolation) {
     assert(fx == 0 && fy == 0 && interpolation == INTER_LINEAR);
     (void)fx; (void)fy; (void)interpolation;
+    StageTimer _st(&stage_clock().resize);
     Mat s = src.getMat();
     dst.create(dsize.height, dsize.width, CV_8UC1);
     Mat d = dst.getMat();
@@ -922,6 +949,7 @@ static inline void GaussianBlur(InputArray src, OutputArray dst, Size ksize, dou
     assert(ksize.width == 7 && ksize.height == 7 && sx == 2 && sy == 2 &&
            borderType == BORDER_REFLECT_101);
     (void)ksize; (void)sx; (void)sy; (void)borderType;
+    StageTimer _st(&stage_clock().blur);
     Mat s = src.getMat();
     dst.create(s.rows, s.cols, CV_8UC1);
     Mat d = dst.getMat();

@@ -42,10 +42,10 @@ inline Arena& tls() {
 }
 inline void reset() {
     Arena& a = tls();
-    if (a.base && a.used) {
-        // give the pages back; the reservation stays
-        madvise(a.base, a.used, MADV_DONTNEED);
-    }
+    // The pages stay mapped between frames (a per-frame madvise would put page faults and mmap-lock traffic
+    // into the timed CPU arm that a stock build with malloc does not pay); only an unusually large frame's
+    // worth is given back.
+    if (a.base && a.used > ((size_t)256 << 20)) madvise(a.base, a.used, MADV_DONTNEED);
     a.used = 0;
 }
 inline void* bump(size_t n) {

@@ -53,6 +53,19 @@ void orbref_destroy(void* h) { delete (Probe*)h; }
 // allocator-dependent behaviour of a stock build (used only to REPORT the difference rate).
 void orbref_set_malloc_mode(int use_malloc) { orb_arena::tls().enabled = !use_malloc; }
 
+// In-situ stage clock of the calling thread (cvshim.h StageClock): on != 0 starts it from zero; the call returns the
+// seconds accumulated so far inside cv::resize / cv::FAST / cv::GaussianBlur through out3 (may be NULL).
+void orbref_stage_clock(int on, double* out3) {
+    cv::StageClock& c = cv::stage_clock();
+    if (out3) {
+        out3[0] = c.resize;
+        out3[1] = c.fast;
+        out3[2] = c.blur;
+    }
+    c.on = on != 0;
+    c.resize = c.fast = c.blur = 0;
+}
+
 int orbref_tables(void* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
                   int* n_per_level) {
     Probe* p = (Probe*)h;

@@ -391,12 +391,14 @@ void orbx_fast_smem_layout(const OrbxPlan& P, int* tile_pitch, int* score_pitch,
     *warp_bytes = (bytes + 15) & ~15;
 }
 
-// Called once per (device, plan): opt in to the dynamic shared memory the plan needs.
+// Called per (device, plan).  The attribute belongs to the KERNEL on the device, not to the handle: a second handle
+// with a smaller plan must not lower it under a live handle with a larger one (mono builds an N- and a 5N-feature
+// extractor, src/Tracking.cc:206-212).  So it is always raised to the opt-in maximum; the plan's need is only checked.
 cudaError_t orbx_configure_fast(const OrbxPlan& P) {
     int tp, sp, wb, so;
     orbx_fast_smem_layout(P, &tp, &sp, &wb, &so);
-    return cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                wb * FAST_WARPS);
+    if (wb * FAST_WARPS > ORBX_MAX_DYN_SMEM) return cudaErrorInvalidConfiguration;
+    return cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, ORBX_MAX_DYN_SMEM);
 }
 
 cudaError_t orbx_launch_fast(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr, uint32_t* cellcnt,

@@ -726,8 +726,9 @@ OctLaunchCfg orbx_octree_cfg(const OrbxPlan& P) {
 
 cudaError_t orbx_configure_octree(const OrbxPlan& P) {
     OctLaunchCfg c = orbx_octree_cfg(P);
-    if (c.smem > 227 * 1024) return cudaErrorInvalidConfiguration;
-    return cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c.smem);
+    if (c.smem > ORBX_MAX_DYN_SMEM) return cudaErrorInvalidConfiguration;
+    // always the opt-in maximum: the attribute is per kernel and device, another live handle may need more than this plan
+    return cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, ORBX_MAX_DYN_SMEM);
 }
 
 cudaError_t orbx_launch_octree(const OrbxPlan& P, const uint32_t* cellcnt, const uint32_t* cellkeys,

@@ -1,3 +1,4 @@
+#define ORBX_MAX_DYN_SMEM (227 * 1024)   /* sm_100a: opt-in dynamic shared memory per CTA */
 // orbx_internal.h -- structures shared by the host runtime (orbx_api.cu) and the kernels.
 //
 // Data layout in HBM (per pipeline slot, B = max_batch frames; all sizes for one image shape):

@@ -164,6 +164,28 @@ def test_two_handles_concurrently(oracle_libs, synth):
     [e.close() for e in exs]
 
 
+def test_two_live_handles_with_different_plans(oracle_libs, synth):
+    """Mono ORB-SLAM3 keeps mpORBextractorLeft (N features) and mpIniORBextractor (5N) alive together
+    (src/Tracking.cc:206-212), and re-initialisation goes back to the 5N one.  The dynamic shared-memory opt-in is a
+    property of the kernel on the device, not of a handle: a 1000-feature handle setting its shape after a
+    5000-feature one must not lower it (k_octree needs ~95 KB at 5000 features, ~36 KB at 1000)."""
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    img = synth.textured_noise(600, 800, 4)       # not the default 752x480: every call goes through set_shape once
+    small = synth.textured_noise(480, 640, 5)
+    ini = ORBextractor(5000, 1.2, 8, 20, 7, max_size=(600, 800))
+    left = ORBextractor(1000, 1.2, 8, 20, 7, max_size=(600, 800))
+    o_ini, o_left = _oracle(oracle_libs, 5000), _oracle(oracle_libs, 1000)
+    try:
+        _compare_final(o_ini(img, (0, 1000)), ini(img, (0, 1000)), "ini first")
+        _compare_final(o_left(img, (0, 1000)), left(img, (0, 1000)), "left after ini")       # lowers nothing
+        _compare_final(o_ini(img, (0, 1000)), ini(img, (0, 1000)), "ini after left")         # the failing launch before the fix
+        _compare_final(o_left(small, (0, 1000)), left(small, (0, 1000)), "left, new shape")
+        _compare_final(o_ini(small, (0, 1000)), ini(small, (0, 1000)), "ini, new shape after left")
+    finally:
+        ini.close()
+        left.close()
+
+
 def test_against_committed_goldens(synth):
     """Integer stages against tests/golden/extractor_golden.json (hashes produced by the reference's
     own ORBextractor.cc in the build container) -- independent of any oracle library being present."""
