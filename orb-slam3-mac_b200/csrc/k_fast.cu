@@ -34,15 +34,28 @@
 #ifndef FAST_DIAG
 #define FAST_DIAG 0   // A/B: neutral on B200 (0.736 vs 0.738 ms): fewer exact scores, 52 more instructions per step
 #endif
+#ifndef FAST_BITMAP
+#define FAST_BITMAP 1    // 1: rejection writes a per-row flag bitmap, ONE ordered compaction per 32 detection rows;
+                         // 0: the round-1 scheme (per-step warp scan + per-lane push loop into a ring), kept for A/B
+#endif
+#if FAST_BITMAP
+#define FAST_Q 512       // queued pixels (u16) of one group of 32 detection rows; a group with more goes in chunks
+#define FAST_BM_PITCH 12 // bitmap bytes per detection row: 8 pixels per byte, <= 9 byte pairs (dw <= 59), word aligned
+#define FAST_BM_ROWS 64  // dh <= 59
+#define FAST_BM_BYTES (FAST_BM_PITCH * FAST_BM_ROWS)
+#else
 #define FAST_Q 512       // ring of queued pixels (u16): <= 31 left over + 256 pushed per step
+#define FAST_BM_BYTES 0
+#endif
 #define FAST_CLIST 256   // corners kept for the sparse NMS pass
-#define FAST_HDR_BYTES (2 * (FAST_Q + FAST_CLIST))
+#define FAST_HDR_BYTES (2 * (FAST_Q + FAST_CLIST) + FAST_BM_BYTES)
 
 struct FastWarpSmem {
     uint8_t* tile;    // tile_pitch * tile_h, rows 8-byte aligned
     uint8_t* score;   // score_pitch * (dh + 2), 1-px zero frame around the detection region
     uint16_t* queue;  // FAST_Q entries: (tile row << 7) | tile byte column
     uint16_t* clist;  // FAST_CLIST entries, same encoding
+    uint8_t* bitmap;  // FAST_BITMAP: flag bits of the detection rows, FAST_BM_PITCH bytes per row
     int xo;           // tile byte column of tile x = 0 (alignment slack of the staged words)
 };
 
@@ -90,7 +103,11 @@ __device__ __forceinline__ void fast_drain(const FastWarpSmem& s, int tp, int sp
     bool corner = false;
     int e = 0;
     if (lane < take) {
+#if FAST_BITMAP
+        e = s.queue[qhead + lane];
+#else
         e = s.queue[(qhead + lane) & (FAST_Q - 1)];
+#endif
         const int r = e >> 7, bc = e & 127;
         const int sc = fast_exact_score(s.tile + r * tp + bc, tp);
         if (sc >= th) {
@@ -112,9 +129,10 @@ __device__ __forceinline__ uint32_t fast_gt4(uint32_t d, uint32_t K4) {
 
 // q = x / d for 0 <= x < 64, 1 <= d <= 32 without an integer division: M = 2^16/d rounded up
 // (MUFU.RCP), exact because x * d * (M - 2^16/d) < 2^16.
-__device__ __forceinline__ uint32_t fast_small_inv(int d) {
-    return (uint32_t)(__frcp_ru((float)d) * 65536.f) + 1u;
-}
+__constant__ uint32_t c_fast_inv[33] = {
+    0,     65537, 32769, 21846, 16385, 13108, 10923, 9363, 8193, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4097,
+    3856,  3641,  3450,  3277,  3121,  2979,  2850,  2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115, 2049};
+__device__ __forceinline__ uint32_t fast_small_inv(int d) { return c_fast_inv[d]; }
 __device__ __forceinline__ int fast_small_div(int x, uint32_t inv) { return (int)(((uint32_t)x * inv) >> 16); }
 
 // Computes the score map for threshold `th` (s = raw-1 stored where raw > th, else 0 kept) and
@@ -139,7 +157,10 @@ __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp
         vhi = (uint32_t)(m >> 32);
     }
     const uint32_t K4 = (uint32_t)(128 - ((th + 1) >> 1)) * 0x01010101u;
-    int qhead = 0, qn = 0, ncorn = 0;
+    int ncorn = 0;
+#if !FAST_BITMAP
+    int qhead = 0, qn = 0;
+#endif
     const uint8_t* row = s.tile + (3 + ro) * tp + pc * 8;
     const int rstep = rpi * tp;
     const int rend = 3 + dh;
@@ -186,9 +207,54 @@ __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp
 #endif
         }
         // flags sit in bit 7 of each byte: one multiply per word gathers them into a nibble.
+        const uint32_t nib0 = ((flo * 0x00204081u) >> 28) | (((fhi * 0x00204081u) >> 24) & 0xf0u);
+#if FAST_BITMAP
+        // one byte per lane into the row bitmap: bit j of byte (pc - plo) of row r - 3 = tile byte column pc * 8 + j
+        if (active && r < rend) s.bitmap[(r - 3) * FAST_BM_PITCH + (pc - plo)] = (uint8_t)nib0;
+    }
+    __syncwarp();
+    // ORDERED COMPACTION, once per group of 32 detection rows: lane = row, its flags are <= 3 words (the bytes
+    // past the row's last pair are stale and masked); raster order = (row, word, bit) = lane-major, so one warp
+    // scan of the per-row counts gives every flagged pixel its position in the queue.  Then the exact score runs
+    // on full 32-lane batches.  A group with more flagged pixels than the queue holds goes in chunks.
+    const int nwords = (npair + 3) >> 2;
+    for (int g0 = 0; g0 < dh; g0 += 32) {
+        const int rr = g0 + lane;
+        uint32_t w[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            w[k] = 0;
+            if (rr < dh && k < nwords) {
+                const int nb = min(npair - 4 * k, 4);   // valid bytes of this word (>= 1)
+                w[k] = *reinterpret_cast<const uint32_t*>(s.bitmap + rr * FAST_BM_PITCH + 4 * k) &
+                       (0xffffffffu >> (32 - 8 * nb));
+            }
+        }
+        const uint32_t cnt = __popc(w[0]) + __popc(w[1]) + __popc(w[2]);
+        const uint32_t incl = warp_incl_scan(cnt);
+        const int total = (int)__shfl_sync(ORBX_FULL, incl, 31);
+        const int ebase = ((rr + 3) << 7) | (plo * 8);
+        for (int done = 0; done < total; done += FAST_Q) {
+            int at = (int)(incl - cnt) - done;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                uint32_t m = w[k];
+                while (m) {
+                    const int bit = __ffs(m) - 1;
+                    m &= m - 1;
+                    if ((unsigned)at < (unsigned)FAST_Q) s.queue[at] = (uint16_t)(ebase + 32 * k + bit);
+                    ++at;
+                }
+            }
+            __syncwarp();
+            const int nq = min(total - done, FAST_Q);
+            for (int q0 = 0; q0 < nq; q0 += 32) fast_drain(s, tp, sp, th, q0, min(nq - q0, 32), ncorn);
+            __syncwarp();
+        }
+    }
+#else
         // Flagged pixels go straight to the pixel ring in raster order (lane order = (row, pair)
         // order): warp scan of the per-lane counts, then each lane writes its own pixels.
-        const uint32_t nib0 = ((flo * 0x00204081u) >> 28) | (((fhi * 0x00204081u) >> 24) & 0xf0u);
         if (__any_sync(ORBX_FULL, nib0 != 0)) {
             uint32_t nib = nib0;
             const uint32_t cnt = __popc(nib);
@@ -216,6 +282,7 @@ __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp
         qhead = (qhead + take) & (FAST_Q - 1);
         qn -= take;
     }
+#endif
     __syncwarp();
     return ncorn;
 }
@@ -303,6 +370,7 @@ k_fast_cells(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8
     uint8_t* base = smem + (size_t)warp * warp_smem_bytes;
     s.queue = reinterpret_cast<uint16_t*>(base);
     s.clist = s.queue + FAST_Q;
+    s.bitmap = base + 2 * (FAST_Q + FAST_CLIST);
     s.tile = base + FAST_HDR_BYTES;
     s.score = s.tile + score_off;
 
