@@ -514,7 +514,8 @@ def run_ours(args):
     # kernel shares the GPU with the other slot's kernels).
     fin = comm if comm is not None else ext[0]
 
-    def timed_pass(chain, sample_clocks):
+    def timed_pass(chain, sample_clocks, steps=None):
+        steps = steps or args.steps
         mode["chain"] = chain
         for i in range(args.warmup):
             one_step(i)
@@ -528,7 +529,7 @@ def run_ours(args):
         acc["stage"][:] = 0
         acc["launches"] = 0
         e0.record(ext[0])
-        for i in range(args.steps):
+        for i in range(steps):
             one_step(i)
         for sl in range(nsl):
             finish(sl)
@@ -538,10 +539,21 @@ def run_ours(args):
         e1.record(fin)
         barrier()
         ck = smp.stop() if (smp and rank == 0) else None
-        return e0.elapsed_time(e1), acc["stage"] / args.steps, acc["launches"], ck
+        return e0.elapsed_time(e1), acc["stage"] / steps, acc["launches"], ck
 
     dev_ms, stage_overlapped, launches, clocks = timed_pass(False, True)
     chained_ms, stage, _, _ = timed_pass(True, False)
+    # the same step for >= 2 s: every kernel is issue-bound, i.e. proportional to the SM clock, so the value is also
+    # shown at whatever clock the GPU settles to under sustained load (clocks sampled over the whole region)
+    sustained = None
+    if args.sustain_s > 0:
+        k2 = max(args.steps, int(np.ceil(args.sustain_s * 1e3 / (dev_ms / args.steps))))
+        s_ms, _, _, s_clocks = timed_pass(False, True, steps=k2)
+        t2 = torch.tensor([s_ms], dtype=torch.float64, device=f"cuda:{local}")
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        sustained = {"value": k2 * B * world / (float(t2[0]) * 1e-3), "unit": UNIT, "steps": k2, "seconds": float(t2[0]) * 1e-3,
+                     "ms_per_step": float(t2[0]) / k2, "clocks": s_clocks}
     step_device(0)
 
     gather_check = None
@@ -727,6 +739,7 @@ def run_ours(args):
             "roofline": roofline,
             "clocks": clocks,
             "latency": lat,
+            "value_sustained": sustained,
         }
         if gather_check is not None:
             line["gather"] = dict(gather_check, kind="fused into k_describe (peer stores over NVLink into rank 0's slab)",
@@ -750,6 +763,19 @@ def run_ours(args):
                 cb["value_guarded"] = cb["value"] * g["speedup_if_real_opencv"]
                 line["e2e"]["vs_cpu_guarded"] = line["e2e"]["value"] / cb["value_guarded"]
             line["cpu_baseline"] = cb
+        if world == 1 and not args.no_extras:
+            # outside the timed C1 region: the composite configs as pipelines and the matcher rows, so that they are on
+            # the driver's record too (bench_pipelines.py / bench_match.py print the same standalone)
+            try:
+                import bench_pipelines
+                line["configs"] = bench_pipelines.run_pipelines(reps=30, cpu=not args.no_cpu_baseline, device=local)
+            except Exception as e:   # an extra must not cost the headline line
+                line["configs"] = {"error": repr(e)}
+            try:
+                import bench_match
+                line["matcher"] = bench_match.collect(reps=15, cpu=not args.no_cpu_baseline)
+            except Exception as e:
+                line["matcher"] = {"error": repr(e)}
         print(json.dumps(line), flush=True)
 
     for o in outs:
@@ -776,6 +802,8 @@ def main():
     ap.add_argument("--config", default="C1", choices=["C1", "C2", "C3", "C4", "C5"])
     ap.add_argument("--batch", type=int, default=0, help="frames per step per GPU (default: by config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the C2-C4 pipelines and the matcher rows")
+    ap.add_argument("--sustain-s", type=float, default=2.0, help="seconds of the value_sustained pass (0: skip)")
     ap.add_argument("--gather", default="fused", choices=["fused", "nccl"],
                     help="N > 1: result gather fused into k_describe over NVLink peer memory (default), or the NCCL "
                          "all_gather baseline")

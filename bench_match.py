@@ -39,11 +39,22 @@ def med(f, reps):
     return float(np.median(ts)) * 1e3, out
 
 
-def main():
+ROWS = []
+
+
+def collect(reps: int = 15, cpu: bool = True):
+    """The rows as a list (bench.py puts them under `matcher` in its JSON line)."""
+    ROWS.clear()
+    main(["--reps", str(reps), "--quiet"] + ([] if cpu else ["--no-cpu"]))
+    return list(ROWS)
+
+
+def main(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--reps", type=int, default=30)
     ap.add_argument("--no-cpu", action="store_true")
-    args = ap.parse_args()
+    ap.add_argument("--quiet", action="store_true")
+    args = ap.parse_args(argv)
 
     importlib.import_module("orb_slam3_mac_b200")
     from orb_slam3_mac_b200 import synth as S
@@ -77,11 +88,14 @@ def main():
         if cpu_call is not None and mo is not None:
             cpu, _ = med(cpu_call, 3)
         gp = pairs / (d * 1e-3) * 1e-9 if d > 0 else None
-        print(json.dumps({"case": case, "what": what, "pairs": pairs, "device_ms": round(d, 4),
-                          "e2e_ms": round(e2e, 4), "cpu_ms": None if cpu is None else round(cpu, 3),
-                          "cpu_kind": "port, 1 thread", "gpairs_per_s": None if gp is None else round(gp, 2),
-                          "popc_peak_gpopc_per_s": round(peak.value, 1),
-                          "popc_frac": None if gp is None else round(8 * gp / peak.value, 4)}), flush=True)
+        row = {"case": case, "what": what, "pairs": pairs, "device_ms": round(d, 4),
+               "e2e_ms": round(e2e, 4), "cpu_ms": None if cpu is None else round(cpu, 3),
+               "cpu_kind": "port, 1 thread", "gpairs_per_s": None if gp is None else round(gp, 2),
+               "popc_peak_gpopc_per_s": round(peak.value, 1),
+               "popc_frac": None if gp is None else round(8 * gp / peak.value, 4)}
+        ROWS.append(row)
+        if not args.quiet:
+            print(json.dumps(row), flush=True)
 
     def extract(img, nf):
         ex = ORBextractor(nf, 1.2, 8, 20, 7, max_size=img.shape)
@@ -125,6 +139,16 @@ def main():
            lambda: m.SearchByProjection(F, mps, md, 3.0, False, 30.0),
            (lambda: mo.search_by_projection_points(F, mps, md, 3.0, False, 30.0, 0.8)) if mo else None)
 
+    # the same searches on a device-resident frame (orbm_frame: keypoints, descriptors and grid uploaded / built once)
+    from orb_slam3_mac_b200.matcher import ResidentFrame
+    RF = ResidentFrame(m, F)
+    report("C4 SearchByProjection, resident frame", "same search, the frame stays on the device (no frame upload, no grid build)",
+           lambda: m.SearchByProjection(RF, mps, md, 1.0, False, 30.0), None)
+    lo_r, ld_r = S.last_frame_obs(k0, d0, 9)
+    report("C4 SearchByProjection frames, resident frame", "frame-to-frame search on the resident frame",
+           lambda: m.SearchByProjectionFrames(RF, lo_r, ld_r, 15.0), None)
+    RF.close()
+
     # ---- M4: SearchForInitialization with the 5 x nFeatures extractor at C1 -----------------------------
     a = S.textured_noise(480, 752, 21)
     b = np.roll(a, 4, axis=1)
@@ -163,7 +187,7 @@ def main():
     from tests.golden import n3_cases as nc
     rp = np.random.default_rng(12)
     KF1, KF2 = Frame(k0, d0, 1280, 720, SF), Frame(k1, d1, 1280, 720, SF)
-    p1, p2 = nc.proj_points(k0, rp), nc.proj_points(k1, rp)
+    p1, p2 = nc.proj_points(k0, rp)[0], nc.proj_points(k1, rp)[0]
     md1, md2 = S.flip_bits(d0, 0.04, rp), S.flip_bits(d1, 0.04, rp)
     ok1, ok2 = np.ones(len(k0), np.uint8), np.ones(len(k1), np.uint8)
     report("C4 SearchByBoW(KF,KF)", f"{len(k0)} x {len(k1)} keyframe features over {len(KFs.node_ids)} vocabulary nodes",

@@ -356,6 +356,37 @@ int orbm_area_candidates(orbm_context* c, const orbm_frame_view* F, const orbm_a
                          const uint8_t* q_desc, int n_q_desc, int32_t* row_ptr, int32_t* cand,
                          uint16_t* dist, int cap);
 
+/* ---- device-resident frames ---------------------------------------------------------
+ * A frame goes through two or three searches (TrackWithMotionModel's SearchByProjection, SearchLocalPoints,
+ * relocalisation): an orbm_frame keeps its undistorted keypoints (mvKeysUn), descriptors and the 64 x 48 grid of
+ * Frame::AssignFeaturesToGrid (src/Frame.cc:377-408) on the device, so a search uploads only its own queries.
+ * Use: pass orbm_frame_get_view(f) wherever a search takes an orbm_frame_view* -- the library recognises the
+ * address and skips the frame upload and the grid build.  Frames belong to their context (not to be shared between
+ * contexts or used after orbm_destroy, which destroys the ones still alive). */
+typedef struct orbm_frame orbm_frame;
+
+/* Camera intrinsics and OpenCV distortion coefficients (Frame::mK, Frame::mDistCoef: k1 k2 p1 p2 [k3]). */
+typedef struct orbm_camera {
+    float fx, fy, cx, cy;
+    float k1, k2, p1, p2, k3;
+} orbm_camera;
+
+/* From a host snapshot (the arrays are copied: they need not outlive the call). */
+int orbm_frame_upload(orbm_context* c, const orbm_frame_view* view, orbm_frame** out);
+
+/* From the extractor's DEVICE results (orbx_extract_device: d_keys = mvKeys, d_desc), without a round trip through
+ * the host: Frame::UndistortKeyPoints (src/Frame.cc:738-771: cv::undistortPoints with K, the distortion and P = K;
+ * skipped when cam is NULL or k1 == 0, as :740 does) and Frame::ComputeImageBounds (:773-800: the undistorted image
+ * corners) run on the device, then the grid is built there.  The view's keys are mvKeysUn (host copy kept by the
+ * frame: the accept loops read octaves), its bounds / grid pitch as the reference computes them, u_right NULL
+ * (orbm_frame_set_u_right attaches mvuRight after the stereo matcher ran). */
+int orbm_frame_from_device(orbm_context* c, const orbx_keypoint* d_keys, const uint8_t* d_desc, int n,
+                           const orbm_camera* cam, int width, int height, const float* scale_factors, int nlevels,
+                           orbm_frame** out);
+const orbm_frame_view* orbm_frame_get_view(const orbm_frame* f);
+int orbm_frame_set_u_right(orbm_frame* f, const float* u_right);
+int orbm_frame_destroy(orbm_frame* f);
+
 /* ---- window search without any allocation ----------------------------------------------------------
  * NO COUNTERPART IN THE REFERENCE: added for callers that cannot
  * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).

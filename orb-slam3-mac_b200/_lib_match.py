@@ -19,6 +19,8 @@ MAP_POINT_DTYPE = np.dtype([("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_xr", "<
 LAST_OBS_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("inv_z", "<f4"), ("angle", "<f4"),
                            ("octave", "<i4"), ("observations", "<i4"), ("valid", "u1"), ("_pad", "u1", (3,))])
 _fv = C.POINTER(FrameView)
+CAMERA_DTYPE = np.dtype([("fx", "<f4"), ("fy", "<f4"), ("cx", "<f4"), ("cy", "<f4"), ("k1", "<f4"), ("k2", "<f4"),
+                         ("p1", "<f4"), ("p2", "<f4"), ("k3", "<f4")])  # orbm_camera
 
 
 class BowView(C.Structure):  # orbm_bow_view
@@ -76,6 +78,11 @@ ORBM_SYMBOLS = {
     "orbm_bow_transform": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, C.POINTER(C.c_int32), _vp, _vp, _vp,
                                 C.POINTER(C.c_int32)]),
     "orbm_area_candidates": (_i, [_vp, _fv, _vp, _i, _vp, _i, _vp, _vp, _vp, _i]),
+    "orbm_frame_upload": (_i, [_vp, _fv, C.POINTER(_vp)]),
+    "orbm_frame_from_device": (_i, [_vp, _vp, _vp, _i, _vp, _i, _i, _vp, _i, C.POINTER(_vp)]),
+    "orbm_frame_get_view": (_vp, [_vp]),
+    "orbm_frame_set_u_right": (_i, [_vp, _vp]),
+    "orbm_frame_destroy": (_i, [_vp]),
     "orbm_area_candidates_static": (_i, [_i, _vp, _vp, _vp, _i, _f, _f, _f, _f, _vp, _i, _vp, _vp, _vp, _vp, _i]),
     "orbm_last_device_ms": (_i, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_longlong)]),
     "orbm_measure_popc_peak": (_i, [_vp, C.POINTER(C.c_double)]),

@@ -773,6 +773,70 @@ cudaError_t orbm_launch_bow_descend(const uint8_t* feat, int n, const int32_t* c
     return cudaGetLastError();
 }
 
+// ---- N2: Frame::UndistortKeyPoints + Frame::ComputeImageBounds on the device (src/Frame.cc:738-800) --------
+// cv::undistortPoints(mat, mat, K, distCoef, Mat(), K) with its default criteria: all arithmetic in double, five
+// fixed-point iterations of the inverse of (k1, k2, p1, p2, k3), then P = K (modules/calib3d undistort.dispatch.cpp
+// cvUndistortPointsInternal; restated and pinned bit-for-bit against cv2.undistortPoints in oracle/cvshim).  Every
+// operation is an explicit IEEE round-to-nearest intrinsic: a contracted multiply-add would round differently.
+// Thread i < n: keypoint i (pt replaced in the output record, the other fields copied); threads n .. n+3: the image
+// corners (0,0), (w,0), (0,h), (w,h) into corners_xy (ComputeImageBounds undistorts them the same way).
+struct OrbmCam {
+    double fx, fy, cx, cy, k1, k2, p1, p2, k3;
+};
+
+__device__ __forceinline__ void undistort_point(const OrbmCam& C, double u, double v, float* xo, float* yo) {
+    const double ifx = __ddiv_rn(1.0, C.fx), ify = __ddiv_rn(1.0, C.fy);
+    double x = __dmul_rn(__dsub_rn(u, C.cx), ifx), y = __dmul_rn(__dsub_rn(v, C.cy), ify);
+    const double x0 = x, y0 = y;
+    for (int j = 0; j < 5; ++j) {
+        const double r2 = __dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y));
+        // icdist = (1 + ((k[7]*r2 + k[6])*r2 + k[5])*r2) / (1 + ((k[4]*r2 + k[1])*r2 + k[0])*r2), k[5..7] = 0
+        const double num = 1.0;   // the rational model's numerator coefficients are zero
+        const double den = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(C.k3, r2), C.k2), r2), C.k1), r2));
+        const double icdist = __ddiv_rn(num, den);
+        if (icdist < 0) {
+            x = x0;
+            y = y0;
+            break;
+        }
+        // deltaX = 2*p1*x*y + p2*(r2 + 2*x*x) [+ 0*r2 + 0*r2*r2], evaluated left to right as the C expression
+        const double dX = __dadd_rn(__dmul_rn(__dmul_rn(__dmul_rn(2.0, C.p1), x), y),
+                                    __dmul_rn(C.p2, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, x), x))));
+        const double dY = __dadd_rn(__dmul_rn(C.p1, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, y), y))),
+                                    __dmul_rn(__dmul_rn(__dmul_rn(2.0, C.p2), x), y));
+        x = __dmul_rn(__dsub_rn(x0, dX), icdist);
+        y = __dmul_rn(__dsub_rn(y0, dY), icdist);
+    }
+    // P = K: xx = fx*x + 0*y + cx, yy = 0*x + fy*y + cy, ww = 1 / (0*x + 0*y + 1)
+    const double xx = __dadd_rn(__dadd_rn(__dmul_rn(C.fx, x), __dmul_rn(0.0, y)), C.cx);
+    const double yy = __dadd_rn(__dadd_rn(__dmul_rn(0.0, x), __dmul_rn(C.fy, y)), C.cy);
+    const double ww = __ddiv_rn(1.0, __dadd_rn(__dadd_rn(__dmul_rn(0.0, x), __dmul_rn(0.0, y)), 1.0));
+    *xo = (float)__dmul_rn(xx, ww);
+    *yo = (float)__dmul_rn(yy, ww);
+}
+
+__global__ void __launch_bounds__(128)
+k_undistort(const orbx_keypoint* __restrict__ keys, int n, OrbmCam C, float width, float height,
+            orbx_keypoint* __restrict__ keys_un, float* __restrict__ corners_xy) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        orbx_keypoint k = keys[i];
+        undistort_point(C, (double)k.x, (double)k.y, &k.x, &k.y);
+        keys_un[i] = k;
+    } else if (i < n + 4) {
+        const int c = i - n;
+        undistort_point(C, (c & 1) ? (double)width : 0.0, (c & 2) ? (double)height : 0.0, corners_xy + 2 * c,
+                        corners_xy + 2 * c + 1);
+    }
+}
+
+cudaError_t orbm_launch_undistort(const orbx_keypoint* keys, int n, const float* cam9, float width, float height,
+                                  orbx_keypoint* keys_un, float* corners_xy, cudaStream_t st) {
+    OrbmCam C{cam9[0], cam9[1], cam9[2], cam9[3], cam9[4], cam9[5], cam9[6], cam9[7], cam9[8]};
+    k_undistort<<<(n + 4 + 127) / 128, 128, 0, st>>>(keys, n, C, width, height, keys_un, corners_xy);
+    return cudaGetLastError();
+}
+
 // ---- orbm_area_candidates_static: the window search with its scratch in a static device array ------
 // No counterpart in the reference; added for callers that cannot
 // call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).  Same kernels as

@@ -17,6 +17,8 @@
 #include <cstring>
 #include <map>
 #include <string>
+#include <memory>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/orbm.h"
@@ -136,6 +138,23 @@ struct orbm_context {
     DevBuf darena;                   // device mirror of the arena: uploads arrive in one copy (ctx_flush)
     OrbmScatter up = {};                // staged uploads not yet sent (src = offset in the arena until ctx_flush)
     size_t up_first = 0;
+    std::unordered_map<const orbm_frame_view*, struct orbm_frame*> frames;   // device-resident frames of this context
+    std::vector<struct orbm_frame*> frame_pool;   // destroyed frames whose device buffers the next frame reuses (no cudaMalloc per frame)
+};
+
+cudaError_t orbm_launch_undistort(const orbx_keypoint* keys, int n, const float* cam9, float width, float height,
+                                  orbx_keypoint* keys_un, float* corners_xy, cudaStream_t st);
+
+// A frame whose (undistorted) keypoints, descriptors and 64 x 48 grid stay on the device across the two or three
+// searches it goes through (TrackWithMotionModel -> SearchLocalPoints -> relocalisation).  `view` is what the
+// searches take: its address is the frame's identity (device_candidates looks it up in c->frames).
+struct orbm_frame {
+    orbm_context* ctx = nullptr;
+    orbm_frame_view view = {};
+    DevBuf d_keys, d_desc, d_start, d_items, d_cell;
+    std::vector<orbx_keypoint> h_keys;   // mvKeysUn (the accept loops read octaves on the host)
+    std::vector<uint8_t> h_desc;
+    std::vector<float> h_scale, h_uright;
 };
 
 // Host <-> device copies of a call go through one pinned arena per context: a caller's (pageable) array
@@ -274,6 +293,12 @@ int orbm_destroy(orbm_context* c) {
     if (!c) return ORBX_OK;
     cudaSetDevice(c->device);
     if (c->st) ctx_sync(c);
+    while (!c->frames.empty()) orbm_frame_destroy(c->frames.begin()->second);   // frames die with their context
+    for (orbm_frame* f : c->frame_pool) {
+        for (DevBuf* b : {&f->d_keys, &f->d_desc, &f->d_start, &f->d_items, &f->d_cell}) b->release();
+        delete f;
+    }
+    c->frame_pool.clear();
     for (DevBuf* b : {&c->q, &c->t, &c->rowptr, &c->cand, &c->dist, &c->aux1, &c->aux2, &c->kl, &c->kr, &c->sc, &c->isc,
                       &c->ur, &c->dp, &c->sd, &c->gstart, &c->gitems, &c->gcell, &c->aq, &c->acnt})
         b->release();
@@ -501,25 +526,39 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     c->last_pairs = 0;
     if (nq == 0 || F->n == 0) return ORBX_OK;
     M_TRY(cudaSetDevice(c->device));
+    // a device-resident frame (orbm_frame_upload / orbm_frame_from_device): keypoints, descriptors and the grid are
+    // already there -- no upload of the frame, no grid build
+    const orbm_frame* RF = nullptr;
+    {
+        auto it = c->frames.find(F);
+        if (it != c->frames.end()) RF = it->second;
+    }
     int r;
-    if ((r = c->kl.ensure((size_t)F->n * sizeof(orbx_keypoint))) || (r = c->t.ensure((size_t)F->n * 32)) ||
-        (r = c->q.ensure((size_t)std::max(n_qdesc, 1) * 32)) || (r = c->aq.ensure((size_t)nq * sizeof(orbm_area_query))) ||
-        (r = c->acnt.ensure((size_t)nq * 4)) || (r = c->rowptr.ensure((size_t)(nq + 1) * 4)) ||
-        (r = c->gstart.ensure((size_t)(ORBM_GRID_COLS * ORBM_GRID_ROWS + 1) * 4)) ||
-        (r = c->gitems.ensure((size_t)F->n * 4)) || (r = c->gcell.ensure((size_t)F->n * 4)))
+    if ((r = c->q.ensure((size_t)std::max(n_qdesc, 1) * 32)) || (r = c->aq.ensure((size_t)nq * sizeof(orbm_area_query))) ||
+        (r = c->acnt.ensure((size_t)nq * 4)) || (r = c->rowptr.ensure((size_t)(nq + 1) * 4)))
         return r;
-    M_TRY(ctx_h2d(c, c->kl.p, F->keys, (size_t)F->n * sizeof(orbx_keypoint)));
-    M_TRY(ctx_h2d(c, c->t.p, F->desc, (size_t)F->n * 32));
+    if (!RF && ((r = c->kl.ensure((size_t)F->n * sizeof(orbx_keypoint))) || (r = c->t.ensure((size_t)F->n * 32)) ||
+                (r = c->gstart.ensure((size_t)(ORBM_GRID_COLS * ORBM_GRID_ROWS + 1) * 4)) ||
+                (r = c->gitems.ensure((size_t)F->n * 4)) || (r = c->gcell.ensure((size_t)F->n * 4))))
+        return r;
+    if (!RF) {
+        M_TRY(ctx_h2d(c, c->kl.p, F->keys, (size_t)F->n * sizeof(orbx_keypoint)));
+        M_TRY(ctx_h2d(c, c->t.p, F->desc, (size_t)F->n * 32));
+    }
     if (qdesc) M_TRY(ctx_h2d(c, c->q.p, qdesc, (size_t)n_qdesc * 32));
     M_TRY(ctx_h2d(c, c->aq.p, Q.data(), (size_t)nq * sizeof(orbm_area_query)));
     ORBM_PHASE("uploads");
-    const orbx_keypoint* dk = (const orbx_keypoint*)c->kl.p;
+    const orbx_keypoint* dk = RF ? (const orbx_keypoint*)RF->d_keys.p : (const orbx_keypoint*)c->kl.p;
+    const uint8_t* dt = RF ? (const uint8_t*)RF->d_desc.p : (const uint8_t*)c->t.p;
+    const int32_t* gstart = RF ? (const int32_t*)RF->d_start.p : (const int32_t*)c->gstart.p;
+    const int32_t* gitems = RF ? (const int32_t*)RF->d_items.p : (const int32_t*)c->gitems.p;
     M_TRY(ctx_flush(c));
     ORBM_PHASE("flush (one copy + scatter queued)");
     M_TRY(cudaEventRecord(c->ev0, c->st));
-    M_TRY(orbm_launch_grid_build(dk, F->n, F->min_x, F->min_y, F->grid_w_inv, F->grid_h_inv, (int32_t*)c->gstart.p,
-                                 (int32_t*)c->gitems.p, (int32_t*)c->gcell.p, c->st));
-    M_TRY(orbm_launch_area_count(dk, (const int32_t*)c->gstart.p, (const int32_t*)c->gitems.p, F->min_x, F->min_y,
+    if (!RF)
+        M_TRY(orbm_launch_grid_build(dk, F->n, F->min_x, F->min_y, F->grid_w_inv, F->grid_h_inv, (int32_t*)c->gstart.p,
+                                     (int32_t*)c->gitems.p, (int32_t*)c->gcell.p, c->st));
+    M_TRY(orbm_launch_area_count(dk, gstart, gitems, F->min_x, F->min_y,
                                  F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
                                  (int32_t*)c->acnt.p, (int32_t*)c->rowptr.p, c->st));
     // One blocking wait per search: the candidate / distance lists are sized from the last search's pair
@@ -534,10 +573,10 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     int nnz = 0;
     for (int pass = 0; pass < 2; ++pass) {
         const int cap = (int)std::min<size_t>({c->cand.cap / 4, c->dist.cap / 2, (size_t)INT_MAX});
-        M_TRY(orbm_launch_area_fill(dk, (const int32_t*)c->gstart.p, (const int32_t*)c->gitems.p, F->min_x, F->min_y,
+        M_TRY(orbm_launch_area_fill(dk, gstart, gitems, F->min_x, F->min_y,
                                     F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
-                                    (const int32_t*)c->rowptr.p, qdesc ? (const uint8_t*)c->q.p : (const uint8_t*)c->t.p,
-                                    (const uint8_t*)c->t.p, (int32_t*)c->cand.p, (uint16_t*)c->dist.p, cap, c->st));
+                                    (const int32_t*)c->rowptr.p, qdesc ? (const uint8_t*)c->q.p : dt,
+                                    dt, (int32_t*)c->cand.p, (uint16_t*)c->dist.p, cap, c->st));
         if (topk > 0)
             M_TRY(orbm_launch_csr_topk((const int32_t*)c->rowptr.p, (const int32_t*)c->cand.p, (const uint16_t*)c->dist.p,
                                        nq, topk, cap, (uint32_t*)c->aux1.p, (int32_t*)c->aux2.p, c->st));
@@ -661,6 +700,151 @@ int orbm_area_candidates(orbm_context* c, const orbm_frame_view* F, const orbm_a
         if (dist && q_desc) dist[k] = c->hdist[k];
     }
     return nnz;
+}
+
+// ---- device-resident frames -------------------------------------------------------
+static orbm_frame* frame_new(orbm_context* c) {
+    orbm_frame* f;
+    if (!c->frame_pool.empty()) {   // a frame per camera frame: its buffers come from the one that just retired
+        f = c->frame_pool.back();
+        c->frame_pool.pop_back();
+        f->view = orbm_frame_view{};
+        f->h_uright.clear();
+    } else {
+        f = new orbm_frame();
+    }
+    f->ctx = c;
+    return f;
+}
+static void frame_retire(orbm_context* c, orbm_frame* f) {
+    if (c->frame_pool.size() < 4) {
+        c->frame_pool.push_back(f);
+        return;
+    }
+    for (DevBuf* b : {&f->d_keys, &f->d_desc, &f->d_start, &f->d_items, &f->d_cell}) b->release();
+    delete f;
+}
+struct FrameGuard {   // a frame under construction goes back to the pool on an early return
+    orbm_context* c;
+    orbm_frame* f;
+    ~FrameGuard() { if (f) frame_retire(c, f); }
+    orbm_frame* release() { orbm_frame* r = f; f = nullptr; return r; }
+    orbm_frame* operator->() { return f; }
+    orbm_frame* get() { return f; }
+};
+
+static int frame_finish(orbm_context* c, orbm_frame* f, int n) {
+    // grid of the resident keypoints, built once (Frame::AssignFeaturesToGrid, src/Frame.cc:377-408)
+    int r;
+    if ((r = f->d_start.ensure((size_t)(ORBM_GRID_COLS * ORBM_GRID_ROWS + 1) * 4)) ||
+        (r = f->d_items.ensure((size_t)std::max(n, 1) * 4)) || (r = f->d_cell.ensure((size_t)std::max(n, 1) * 4)))
+        return r;
+    M_TRY(orbm_launch_grid_build((const orbx_keypoint*)f->d_keys.p, n, f->view.min_x, f->view.min_y, f->view.grid_w_inv,
+                                 f->view.grid_h_inv, (int32_t*)f->d_start.p, (int32_t*)f->d_items.p, (int32_t*)f->d_cell.p,
+                                 c->st));
+    M_TRY(cudaStreamSynchronize(c->st));
+    c->frames[&f->view] = f;
+    return ORBX_OK;
+}
+
+int orbm_frame_upload(orbm_context* c, const orbm_frame_view* view, orbm_frame** out) {
+    if (!c || !out) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    *out = nullptr;
+    int rc = check_view(view);
+    if (rc) return rc;
+    M_TRY(cudaSetDevice(c->device));
+    FrameGuard f{c, frame_new(c)};
+    const int n = view->n;
+    f->h_keys.assign(view->keys, view->keys + n);
+    f->h_desc.assign(view->desc, view->desc + (size_t)n * 32);
+    f->h_scale.assign(view->scale_factors, view->scale_factors + view->nlevels);
+    if (view->u_right) f->h_uright.assign(view->u_right, view->u_right + n);
+    f->view = *view;
+    f->view.keys = f->h_keys.data();
+    f->view.desc = f->h_desc.data();
+    f->view.scale_factors = f->h_scale.data();
+    f->view.u_right = view->u_right ? f->h_uright.data() : nullptr;
+    if ((rc = f->d_keys.ensure((size_t)std::max(n, 1) * sizeof(orbx_keypoint))) || (rc = f->d_desc.ensure((size_t)std::max(n, 1) * 32)))
+        return rc;
+    if (n) {
+        M_TRY(cudaMemcpyAsync(f->d_keys.p, f->h_keys.data(), (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, c->st));
+        M_TRY(cudaMemcpyAsync(f->d_desc.p, f->h_desc.data(), (size_t)n * 32, cudaMemcpyHostToDevice, c->st));
+    }
+    if ((rc = frame_finish(c, f.get(), n))) return rc;
+    *out = f.release();
+    return ORBX_OK;
+}
+
+int orbm_frame_from_device(orbm_context* c, const orbx_keypoint* d_keys, const uint8_t* d_desc, int n,
+                           const orbm_camera* cam, int width, int height, const float* scale_factors, int nlevels,
+                           orbm_frame** out) {
+    if (!c || !out || n < 0 || (n && (!d_keys || !d_desc)) || !scale_factors || nlevels < 1 || width < 1 || height < 1)
+        return orbx_set_error(ORBX_E_BAD_ARG, "orbm_frame_from_device: bad argument");
+    *out = nullptr;
+    M_TRY(cudaSetDevice(c->device));
+    FrameGuard f{c, frame_new(c)};
+    int rc;
+    if ((rc = f->d_keys.ensure((size_t)std::max(n, 1) * sizeof(orbx_keypoint))) || (rc = f->d_desc.ensure((size_t)std::max(n, 1) * 32)) ||
+        (rc = f->d_cell.ensure(64)))
+        return rc;
+    f->h_keys.resize(n);
+    f->h_desc.resize((size_t)n * 32);
+    f->h_scale.assign(scale_factors, scale_factors + nlevels);
+    float corners[8] = {0.f, 0.f, (float)width, 0.f, 0.f, (float)height, (float)width, (float)height};
+    const bool distorted = cam && cam->k1 != 0.0f;   // src/Frame.cc:740: mDistCoef.at<float>(0) == 0.0 -> mvKeysUn = mvKeys
+    if (distorted) {
+        const float cam9[9] = {cam->fx, cam->fy, cam->cx, cam->cy, cam->k1, cam->k2, cam->p1, cam->p2, cam->k3};
+        M_TRY(orbm_launch_undistort(d_keys, n, cam9, (float)width, (float)height, (orbx_keypoint*)f->d_keys.p,
+                                    (float*)f->d_cell.p, c->st));
+        M_TRY(cudaMemcpyAsync(corners, f->d_cell.p, sizeof(corners), cudaMemcpyDeviceToHost, c->st));
+        M_TRY(cudaStreamSynchronize(c->st));   // the bounds (and so the grid pitch) come from the undistorted corners
+    } else if (n) {
+        M_TRY(cudaMemcpyAsync(f->d_keys.p, d_keys, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyDeviceToDevice, c->st));
+    }
+    if (n) {
+        M_TRY(cudaMemcpyAsync(f->d_desc.p, d_desc, (size_t)n * 32, cudaMemcpyDeviceToDevice, c->st));
+        M_TRY(cudaMemcpyAsync(f->h_keys.data(), f->d_keys.p, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, c->st));
+        M_TRY(cudaMemcpyAsync(f->h_desc.data(), f->d_desc.p, (size_t)n * 32, cudaMemcpyDeviceToHost, c->st));
+    }
+    // Frame::ComputeImageBounds (src/Frame.cc:773-800) from the undistorted corners, then the grid pitch (:119-120)
+    orbm_frame_view& v = f->view;
+    v.keys = f->h_keys.data();
+    v.desc = f->h_desc.data();
+    v.n = n;
+    v.min_x = std::min(corners[0], corners[4]);
+    v.max_x = std::max(corners[2], corners[6]);
+    v.min_y = std::min(corners[1], corners[3]);
+    v.max_y = std::max(corners[5], corners[7]);
+    v.grid_w_inv = (float)ORBM_GRID_COLS / (v.max_x - v.min_x);
+    v.grid_h_inv = (float)ORBM_GRID_ROWS / (v.max_y - v.min_y);
+    v.scale_factors = f->h_scale.data();
+    v.nlevels = nlevels;
+    v.u_right = nullptr;
+    if ((rc = frame_finish(c, f.get(), n))) return rc;
+    *out = f.release();
+    return ORBX_OK;
+}
+
+const orbm_frame_view* orbm_frame_get_view(const orbm_frame* f) { return f ? &f->view : nullptr; }
+
+int orbm_frame_set_u_right(orbm_frame* f, const float* u_right) {
+    if (!f) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    if (u_right) {
+        f->h_uright.assign(u_right, u_right + f->view.n);
+        f->view.u_right = f->h_uright.data();
+    } else {
+        f->view.u_right = nullptr;
+    }
+    return ORBX_OK;
+}
+
+int orbm_frame_destroy(orbm_frame* f) {
+    if (!f) return ORBX_OK;
+    cudaSetDevice(f->ctx->device);
+    ctx_sync(f->ctx);
+    f->ctx->frames.erase(&f->view);
+    frame_retire(f->ctx, f);
+    return ORBX_OK;
 }
 
 int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, const orbm_map_point* mps,

@@ -13,7 +13,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import KP_DTYPE, check
-from ._lib_match import (AREA_QUERY_DTYPE, BowView, FrameRight, FrameView, LAST_OBS_DTYPE, MAP_POINT_DTYPE,  # noqa: F401
+from ._lib_match import (AREA_QUERY_DTYPE, BowView, CAMERA_DTYPE, FrameRight, FrameView, LAST_OBS_DTYPE, MAP_POINT_DTYPE,  # noqa: F401
                          MAP_POINT_RIGHT_DTYPE, PAIR_TEST, PROJ_POINT_DTYPE)
 
 FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48
@@ -44,6 +44,57 @@ class Frame:
                          self.bounds[1], self.bounds[2], self.bounds[3], self.grid_w_inv, self.grid_h_inv,
                          self.scale_factors.ctypes.data, len(self.scale_factors),
                          None if self.u_right is None else self.u_right.ctypes.data)
+
+
+class ResidentFrame:
+    """orbm_frame: a frame whose keypoints, descriptors and grid stay on the matcher's device across searches.
+    Takes the place of a Frame in every ORBmatcher call (view() returns the library's own view, whose address is
+    how the library recognises the frame)."""
+
+    def __init__(self, matcher: "ORBmatcher", frame: "Frame" = None, *, d_keys: int = 0, d_desc: int = 0, n: int = 0,
+                 camera=None, width: int = 0, height: int = 0, scale_factors=None):
+        self.lib, self._m = matcher.lib, matcher
+        self.h = C.c_void_p()
+        if frame is not None:
+            v = frame.view()
+            check(self.lib.orbm_frame_upload(matcher.ctx, C.byref(v), C.byref(self.h)))
+        else:
+            sf = np.ascontiguousarray(scale_factors, np.float32)
+            cam = None
+            if camera is not None:
+                cam = np.zeros(1, CAMERA_DTYPE)
+                for k, val in zip(CAMERA_DTYPE.names, camera):
+                    cam[k] = val
+            check(self.lib.orbm_frame_from_device(matcher.ctx, C.c_void_p(d_keys), C.c_void_p(d_desc), int(n),
+                                                  None if cam is None else cam.ctypes.data, int(width), int(height),
+                                                  sf.ctypes.data, len(sf), C.byref(self.h)))
+        self._vp = self.lib.orbm_frame_get_view(self.h)
+        v = self.view()
+        n = v.n
+        self.keys = np.ctypeslib.as_array(C.cast(v.keys, C.POINTER(C.c_uint8)), shape=(max(n, 1) * 28,))[:n * 28].view(KP_DTYPE) \
+            if n else np.zeros(0, KP_DTYPE)
+        self.desc = np.ctypeslib.as_array(C.cast(v.desc, C.POINTER(C.c_uint8)), shape=(max(n, 1) * 32,))[:n * 32].reshape(-1, 32) \
+            if n else np.zeros((0, 32), np.uint8)
+        self.bounds = (np.float32(v.min_x), np.float32(v.min_y), np.float32(v.max_x), np.float32(v.max_y))
+        self.grid_w_inv, self.grid_h_inv = np.float32(v.grid_w_inv), np.float32(v.grid_h_inv)
+        self.scale_factors = np.ctypeslib.as_array(C.cast(v.scale_factors, C.POINTER(C.c_float)), shape=(v.nlevels,))
+        self.u_right = None
+
+    @property
+    def N(self):
+        return len(self.keys)
+
+    def view(self) -> FrameView:
+        return FrameView.from_address(self._vp)
+
+    def set_u_right(self, u_right):
+        self.u_right = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        check(self.lib.orbm_frame_set_u_right(self.h, None if self.u_right is None else self.u_right.ctypes.data))
+
+    def close(self):
+        if getattr(self, "h", None) and self._m.ctx:
+            self.lib.orbm_frame_destroy(self.h)
+        self.h = None
 
 
 class BowSide:

@@ -715,3 +715,83 @@ def test_n3_empty_and_invalid_inputs(matcher):
     bi, bv, fn, fp, fi = matcher.transform(h, d[1:3], 0)   # the two words themselves, levelsup 0 -> node = word node
     assert bi.tolist() == [0, 1] and np.allclose(bv, [1.5 / 4.0, 2.5 / 4.0]) and fn.tolist() == [1, 2]
     matcher.free_vocabulary(h)
+
+
+def test_resident_frames_match_plain_frames(matcher, mo):
+    """orbm_frame_upload: a frame kept on the device (keypoints, descriptors, grid built once) gives exactly the
+    results of the per-call upload path and of the reference-held oracle, search after search."""
+    from orb_slam3_mac_b200.matcher import ResidentFrame
+    from tests.golden import match_cases as mc
+    (ka, da), (kb, db) = mc.frames(7, n=1700)
+    rng = np.random.default_rng(12)
+    ur = np.where(rng.random(len(kb)) < 0.5, kb["x"] - rng.uniform(1, 40, len(kb)), -1.0).astype(np.float32)
+    F = _frame(kb, db, 752, 480, u_right=ur)
+    RF = ResidentFrame(matcher, F)
+    RF.set_u_right(ur)
+    try:
+        mps, md = S.map_points_from_frame(ka, da, 752, 480, 6000, 5)
+        lo, ld = S.last_frame_obs(ka, da, 5)
+        obs0 = np.where(rng.random(len(kb)) < 0.2, rng.integers(0, 3, len(kb)), -1).astype(np.int32)
+        for rep in range(2):   # the resident grid serves every search of the frame
+            got = matcher.SearchByProjection(RF, mps, md, 3.0, True, 30.0, kp_obs=obs0)
+            want = mo.search_by_projection_points(F, mps, md, 3.0, True, 30.0, 0.8, kp_obs=obs0)
+            assert got[0] == want[0] and np.array_equal(got[1], want[1]) and np.array_equal(got[2], want[2])
+            got = matcher.SearchByProjectionFrames(RF, lo, ld, 7.0, False, False, 40.0, kp_obs=obs0)
+            want = mo.search_by_projection_frames(F, lo, ld, 7.0, False, False, 40.0, True, kp_obs=obs0)
+            assert got[0] == want[0] and np.array_equal(got[1], want[1]) and np.array_equal(got[2], want[2])
+        from orb_slam3_mac_b200._lib_match import AREA_QUERY_DTYPE
+        q = np.zeros(500, AREA_QUERY_DTYPE)
+        q["x"], q["y"], q["r"] = rng.uniform(0, 752, 500), rng.uniform(0, 480, 500), 30.0
+        q["min_level"], q["max_level"], q["valid"] = -1, -1, 1
+        a, b = matcher.area_candidates(RF, q, None, cap=500000), matcher.area_candidates(F, q, None, cap=500000)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    finally:
+        RF.close()
+
+
+def test_frame_from_device_undistorts_like_opencv(matcher, mo, oracle_libs):
+    """orbm_frame_from_device: extractor results that never leave the device -> Frame::UndistortKeyPoints +
+    ComputeImageBounds (src/Frame.cc:738-800) on the device -> grid -> search.  mvKeysUn and the bounds are
+    bit-identical to the real cv2.undistortPoints (what the reference calls), the searches to the reference-held
+    oracle on a Frame built from the same undistorted keypoints; without distortion the keypoints pass through."""
+    import torch
+    cv2 = pytest.importorskip("cv2")
+    from orb_slam3_mac_b200.matcher import Frame, ResidentFrame
+    from tests.golden import match_cases as mc
+    (ka, da), (kb, db) = mc.frames(9, n=1500)
+    d_keys = torch.from_numpy(kb.view(np.uint8).reshape(-1).copy()).cuda()
+    d_desc = torch.from_numpy(db.reshape(-1).copy()).cuda()
+    torch.cuda.synchronize()
+    cam = (458.654, 457.296, 367.215, 248.375, -0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.0)
+    RF = ResidentFrame(matcher, d_keys=d_keys.data_ptr(), d_desc=d_desc.data_ptr(), n=len(kb), camera=cam, width=752,
+                       height=480, scale_factors=SF)
+    try:
+        K = np.array([[cam[0], 0, cam[2]], [0, cam[1], cam[3]], [0, 0, 1]], np.float32)
+        dist = np.array(cam[4:8], np.float32)
+        pts = np.stack([kb["x"], kb["y"]], axis=1).reshape(-1, 1, 2).astype(np.float32)
+        want = cv2.undistortPoints(pts, K, dist, None, K).reshape(-1, 2)
+        assert np.array_equal(RF.keys["x"].view(np.uint32), want[:, 0].view(np.uint32))
+        assert np.array_equal(RF.keys["y"].view(np.uint32), want[:, 1].view(np.uint32))
+        for f in ("size", "angle", "response", "octave", "class_id"):
+            assert np.array_equal(RF.keys[f], kb[f])
+        c = cv2.undistortPoints(np.array([[0, 0], [752, 0], [0, 480], [752, 480]], np.float32).reshape(-1, 1, 2), K, dist,
+                                None, K).reshape(-1, 2)
+        bounds = (min(c[0, 0], c[2, 0]), min(c[0, 1], c[1, 1]), max(c[1, 0], c[3, 0]), max(c[2, 1], c[3, 1]))
+        assert tuple(float(b) for b in RF.bounds) == tuple(float(b) for b in bounds)
+        assert np.array_equal(RF.desc, db)
+        # the same frame as a host snapshot for the oracle
+        F = Frame(RF.keys.copy(), db, 752, 480, SF, bounds=bounds)
+        assert float(F.grid_w_inv) == float(RF.grid_w_inv) and float(F.grid_h_inv) == float(RF.grid_h_inv)
+        mps, md = S.map_points_from_frame(ka, da, 752, 480, 5000, 2)
+        got = matcher.SearchByProjection(RF, mps, md, 3.0, False, 30.0)
+        want = mo.search_by_projection_points(F, mps, md, 3.0, False, 30.0, 0.8)
+        assert got[0] == want[0] and got[0] > 100 and np.array_equal(got[1], want[1])
+    finally:
+        RF.close()
+    RF = ResidentFrame(matcher, d_keys=d_keys.data_ptr(), d_desc=d_desc.data_ptr(), n=len(kb), camera=None, width=752,
+                       height=480, scale_factors=SF)
+    try:
+        assert np.array_equal(RF.keys.view(np.uint8), kb.view(np.uint8))
+        assert tuple(float(b) for b in RF.bounds) == (0.0, 0.0, 752.0, 480.0)
+    finally:
+        RF.close()
