@@ -439,7 +439,7 @@ def run_ours(args):
         # rank's k_describe writes its result rows into it in the same kernel that produces them -- peer memory
         # over NVLink, mapped through a CUDA IPC handle that travels once through the process group.
         from orb_slam3_mac_b200 import sharding
-        n_sink = sharding.sink_frames(nsl, world, B)
+        n_sink = sharding.sink_frames(max(nsl, n_slots), world, B)   # the e2e pass uses n_slots pipeline slots
         if rank == 0:
             sink = sharding.ResultSink(local, n_sink, cap)
             sharding.exchange_sink_handle(sink.export(), 0)
@@ -583,8 +583,6 @@ def run_ours(args):
             assert bad == 0, f"fused gather: {bad} frames in rank 0's sink differ from the producers' results"
             gather_check = {"frames_checked": world * len(picks), "mismatches": bad}
         barrier()
-        for sl in range(nsl):   # the e2e pass below returns results to each rank's own host buffers
-            _lib.check(lib.orbx_set_result_sink(hd, sl, None, 0))
 
     # keypoint / candidate statistics of the batch (for the algorithmic-byte figures)
     hdr = torch.as_tensor(_DevArray(d_hdr.value, B * 16), device=f"cuda:{local}").cpu().numpy().view(np.int32).reshape(B, 4)
@@ -618,15 +616,106 @@ def run_ours(args):
     for sl in range(n_slots):
         _lib.check(lib.orbx_wait(hd, sl))
     barrier()
+
+    # N > 1: the fused gather stays ON in the e2e pass, with a consumer.  Every rank's batches also land in rank 0's
+    # slab (back-pressure on: a region is not overwritten before the consumer released it); rank 0 runs the consumer on
+    # its own stream: for every step, in global frame order (rank-major), wait for the region's completion word, reduce
+    # the region's frame headers on the device, release it.  After the timed region the per-(step, rank) sums are
+    # compared with what each rank says its batch holds: gather.mismatches counts per step, not once.
+    consumer = None
+    cons = {"sums": [], "error": None}
+    if sink is not None:
+        import threading
+        from orb_slam3_mac_b200 import sharding
+        for sl in range(n_slots):
+            _lib.check(lib.orbx_set_result_sink_ex(hd, sl, sink.h, sharding.sink_first_frame(sl, rank, world, B), 1))
+        barrier()
+        if rank == 0:
+            cstream = torch.cuda.Stream(device=dev)
+            hp, kp_, dp_ = C.c_void_p(), C.c_void_p(), C.c_void_p()
+            _lib.check(lib.orbx_sink_pointers(sink.h, C.byref(hp), C.byref(kp_), C.byref(dp_)))
+            hdr_all = torch.as_tensor(_DevArray(hp.value, n_sink * 16), device=dev).view(torch.int32).view(n_sink, 4)
+
+            with torch.cuda.stream(cstream):   # load the reduction kernel and fill the allocator's cache on this stream
+                for _ in range(3):              # BEFORE producers can park: a module load / cudaMalloc serialises behind
+                    warm = hdr_all[0:B, 0].sum()   # running kernels, i.e. behind a producer's back-pressure wait
+            cstream.synchronize()
+            del warm
+
+            def consume():
+                try:
+                    torch.cuda.set_device(local)
+                    with torch.cuda.stream(cstream):
+                        for i in range(args.steps):
+                            sl, e = i % n_slots, i // n_slots + 1
+                            for r in range(world):
+                                f0 = sharding.sink_first_frame(sl, r, world, B)
+                                _lib.check(lib.orbx_sink_wait(sink.h, f0, e, C.c_void_p(cstream.cuda_stream), 10000))
+                                cons["sums"].append(hdr_all[f0:f0 + B, 0].sum())
+                                _lib.check(lib.orbx_sink_release(sink.h, f0, e, C.c_void_p(cstream.cuda_stream)))
+                    cstream.synchronize()
+                except Exception as ex:   # reported in the line, never hangs the bench
+                    cons["error"] = repr(ex)
+
+            consumer = threading.Thread(target=consume, daemon=True)
+        barrier()
     t0 = time.perf_counter()
+    if consumer is not None:
+        consumer.start()
     for i in range(args.steps):
         sl = i % n_slots
         _lib.check(lib.orbx_wait(hd, sl))
         submit(sl)
     for sl in range(n_slots):
         _lib.check(lib.orbx_wait(hd, sl))
+    if consumer is not None:
+        consumer.join()
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
+    e2e_gather = None
+    if sink is not None:
+        mine = int(outs[0]["n"].sum())   # every step of a rank extracts the same batch
+        allsum = [None] * world
+        dist.all_gather_object(allsum, mine)
+        to = C.c_int()
+        ep = C.c_uint32()
+        timed_out = 0
+        for sl in range(n_slots):
+            _lib.check(lib.orbx_sink_epoch(hd, sl, C.byref(ep), C.byref(to)))
+            timed_out += to.value
+        tt = torch.tensor([timed_out], device=dev)
+        dist.all_reduce(tt)
+        if rank == 0:
+            got = [int(x) for x in torch.stack(cons["sums"]).cpu().tolist()] if cons["sums"] else []
+            want = [allsum[r] for _ in range(args.steps) for r in range(world)]
+            bad = sum(int(a != b) for a, b in zip(got, want)) + abs(len(got) - len(want))
+            e2e_gather = {"consumer": "rank 0, own stream: orbx_sink_wait -> header reduction of the region -> orbx_sink_release, "
+                                      "per (step, rank) in global frame order; back-pressure on",
+                          "regions_consumed": len(got), "mismatches": bad, "producer_timeouts": int(tt[0]),
+                          "error": cons["error"]}
+        barrier()
+        for sl in range(n_slots):
+            _lib.check(lib.orbx_set_result_sink(hd, sl, None, 0))
+
+    # ---- the link ceiling the e2e number is held against: bare pinned copies of one step's bytes (H2D of the frames,
+    # D2H of the result slab) on every rank at once, nothing else running -----------------------------------------------
+    d2h_bytes = B * (16 + cap * 60)
+    hb_in = torch.empty(fbytes, dtype=torch.uint8).pin_memory()
+    hb_out = torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory()
+    db_in = torch.empty(fbytes, dtype=torch.uint8, device=dev)
+    db_out = torch.empty(d2h_bytes, dtype=torch.uint8, device=dev)
+    cs1, cs2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    for it in range(2):
+        barrier()
+        tc = time.perf_counter()
+        for _ in range(10):
+            with torch.cuda.stream(cs1):
+                db_in.copy_(hb_in, non_blocking=True)
+            with torch.cuda.stream(cs2):
+                hb_out.copy_(db_out, non_blocking=True)
+        torch.cuda.synchronize()
+        ceil_s = (time.perf_counter() - tc) / 10
+    del hb_in, hb_out, db_in, db_out
     assert int(outs[0]["n"][0]) == int(hdr[0, 0]), "e2e result differs from the device-resident run"
 
     # ---- single-frame latency (BASELINE.json: "p50 us/frame"): synchronous orbx_extract of one pinned
@@ -667,10 +756,10 @@ def run_ours(args):
                        "chain, p50_us_stream_launches = plain stream launches"}
 
     # ---- max over ranks ------------------------------------------------------------------------------
-    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=f"cuda:{local}")
+    t = torch.tensor([dev_ms, e2e_s * 1e3, ceil_s * 1e3], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    dev_ms, e2e_ms, ceil_ms = float(t[0]), float(t[1]), float(t[2])
     total_frames = args.steps * B * world
 
     if rank == 0:
@@ -734,7 +823,12 @@ def run_ours(args):
                        "keypoints_per_frame": round(n_kp, 1), "fast_candidates_per_frame": round(n_cand, 1)},
             "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": fbytes + B * 8,
                     "d2h_bytes_per_step": B * (16 + cap * 60), "ms_per_step": e2e_ms / args.steps,
-                    "pipeline_slots": n_slots},
+                    "pipeline_slots": n_slots,
+                    "link_ceiling": {"value": B * world / (ceil_ms * 1e-3), "unit": UNIT, "ms_per_step": ceil_ms,
+                                     "what": "bare pinned H2D of one step's frames + D2H of its result slab on every rank "
+                                             "at once (max over ranks, 10 repeats), no kernels: the host feed's limit"},
+                    "efficiency_vs_link_ceiling": (total_frames / (e2e_ms * 1e-3)) / (B * world / (ceil_ms * 1e-3)),
+                    "gather": e2e_gather},
             "gpu_launches": int(launches),
             "roofline": roofline,
             "clocks": clocks,

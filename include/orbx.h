@@ -166,6 +166,28 @@ int orbx_sink_read_frame(orbx_sink* s, int frame, int32_t header[4], orbx_keypoi
  * The sink must hold first_frame + max_batch frames of the handle's capacity. */
 int orbx_set_result_sink(orbx_handle* h, int slot, orbx_sink* sink, int first_frame);
 
+/* Completion signal and back-pressure of the fused gather.  The region [first_frame, first_frame + max_batch) that a
+ * slot writes owns two words of the sink: `flag` and `ack`.  After batch e of the slot (e = 1, 2, ... since the sink
+ * was attached) is completely in the sink -- rows, headers -- the producer publishes e at flag (one tiny kernel behind
+ * k_describe on the slot's stream, release at system scope).  A consumer on the gathering GPU
+ *     orbx_sink_wait(sink, first_frame, e, stream, timeout_ms)
+ * either blocks until batch e has arrived (stream == NULL; ORBX_E_BUSY after timeout_ms) or orders everything enqueued
+ * later on `stream` (a cudaStream_t) behind its arrival, reads the region in frame order, and then
+ *     orbx_sink_release(sink, first_frame, e, stream)
+ * With ORBX_SINK_BACKPRESSURE the producer's k_describe of batch e + 1 does not start before batch e was released, so a
+ * slow consumer is never overwritten (a producer that waits for more than 2 s gives up and sets the slot's timed_out
+ * flag, see orbx_sink_epoch).  While a producer is parked, the consumer's side must not do anything that serialises
+ * behind running kernels: first launches of not-yet-loaded kernels (lazy module loading; the library pre-loads its
+ * own), cudaMalloc / cudaFree, pageable-memory copies.  Without the flag the producer never waits (the round-1 behaviour: the application
+ * orders consumer and producers itself). */
+#define ORBX_SINK_BACKPRESSURE 1
+int orbx_set_result_sink_ex(orbx_handle* h, int slot, orbx_sink* sink, int first_frame, int flags);
+int orbx_sink_wait(orbx_sink* s, int first_frame, uint32_t epoch, void* stream, int timeout_ms);
+int orbx_sink_release(orbx_sink* s, int first_frame, uint32_t epoch, void* stream);
+/* Batches the slot has sent to its sink so far (= the epoch of the last one); timed_out (may be NULL) = a back-pressure
+ * wait of this slot has given up since the sink was attached. */
+int orbx_sink_epoch(orbx_handle* h, int slot, uint32_t* epoch, int* timed_out);
+
 /* ---- pyramid access: ORBextractor::mvImagePyramid (include/ORBextractor.h:83), read by
  * Frame::ComputeStereoMatches (src/Frame.cc:809,899-918) ------------------------------------- */
 int orbx_level_size(const orbx_handle* h, int w, int hgt, int level, int* lw, int* lh);

@@ -83,6 +83,10 @@ ORBX_SYMBOLS = {
     "orbx_sink_pointers": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)]),
     "orbx_sink_read_frame": (_i, [_vp, _i, _vp, _vp, _vp, _i]),
     "orbx_set_result_sink": (_i, [_vp, _i, _vp, _i]),
+    "orbx_set_result_sink_ex": (_i, [_vp, _i, _vp, _i, _i]),
+    "orbx_sink_wait": (_i, [_vp, _i, C.c_uint32, _vp, _i]),
+    "orbx_sink_release": (_i, [_vp, _i, C.c_uint32, _vp]),
+    "orbx_sink_epoch": (_i, [_vp, _i, C.POINTER(C.c_uint32), C.POINTER(_i)]),
 }
 
 

@@ -289,6 +289,72 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
     }
 }
 
+// ---- fused gather: per-batch completion word and back-pressure ----------------------------------
+// A consumer on the gathering GPU cannot use the producers' streams; it needs to know when batch e of producer r is
+// complete in its slab, and a producer must not overwrite a region the consumer is still reading.  Both are two words
+// per region in the sink: flag (written by the producer after the batch, read by the consumer) and ack (the reverse).
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// wait until *word - need >= 0 (wrap-safe); returns false after timeout_ns
+__device__ __forceinline__ bool spin_until(const uint32_t* word, uint32_t need, unsigned long long timeout_ns) {
+    const unsigned long long t0 = global_ns();
+    while ((int32_t)(ld_acquire_sys(word) - need) < 0) {
+        __nanosleep(200);
+        if (global_ns() - t0 > timeout_ns) return false;
+    }
+    return true;
+}
+__global__ void k_sink_wait_ack(const uint32_t* ack, const uint32_t* epoch_dev, uint32_t* err) {
+    // everything this slot has produced so far (epoch_dev batches) must have been released by the consumer
+    if (!spin_until(ack, *epoch_dev, 2000000000ull)) *err = 1;
+}
+__global__ void k_sink_signal(uint32_t* flag, uint32_t* epoch_dev) {
+    const uint32_t e = *epoch_dev + 1;
+    *epoch_dev = e;
+    __threadfence_system();   // the batch's rows (written by the kernel before this one on the stream) before the flag
+    st_release_sys(flag, e);
+}
+__global__ void k_sink_wait_flag(const uint32_t* flag, uint32_t epoch, unsigned long long timeout_ns, uint32_t* err) {
+    if (!spin_until(flag, epoch, timeout_ns)) *err = 1;
+}
+__global__ void k_sink_release(uint32_t* ack, uint32_t epoch) {
+    __threadfence_system();
+    st_release_sys(ack, epoch);
+}
+// With CUDA's lazy module loading the FIRST launch of a kernel loads its code, and that load serialises behind kernels
+// already running on the device -- e.g. behind a producer parked in k_sink_wait_ack (measured: the consumer's first
+// k_sink_release waited 1.85 s, until the parked kernel timed out).  So all four are loaded when a sink is attached,
+// before anything can park.
+cudaError_t orbx_sink_preload() {
+    cudaFuncAttributes a;
+    cudaError_t e;
+    if ((e = cudaFuncGetAttributes(&a, k_sink_wait_ack)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&a, k_sink_signal)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&a, k_sink_wait_flag)) != cudaSuccess) return e;
+    return cudaFuncGetAttributes(&a, k_sink_release);
+}
+
+cudaError_t orbx_launch_sink_wait_flag(const uint32_t* flag, uint32_t epoch, unsigned long long timeout_ns, uint32_t* err,
+                                       cudaStream_t st) {
+    k_sink_wait_flag<<<1, 1, 0, st>>>(flag, epoch, timeout_ns, err);
+    return cudaGetLastError();
+}
+cudaError_t orbx_launch_sink_release(uint32_t* ack, uint32_t epoch, cudaStream_t st) {
+    k_sink_release<<<1, 1, 0, st>>>(ack, epoch);
+    return cudaGetLastError();
+}
+
 cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,
                                  const int32_t* header, const uint32_t* dest,
                                  orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
@@ -309,7 +375,15 @@ cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const ui
             ready[dev] = true;
         }
     }
+    if (sink.hdr && sink.ack) {
+        k_sink_wait_ack<<<1, 1, 0, st>>>(sink.ack, sink.epoch_dev, sink.err_dev);
+        ++*launches;
+    }
     k_describe<<<grid, DESC_WARPS * 32, DESC_SMEM_BYTES, st>>>(P, src, pyr, header, dest, kps, desc, sink);
     ++*launches;
+    if (sink.hdr && sink.flag) {
+        k_sink_signal<<<1, 1, 0, st>>>(sink.flag, sink.epoch_dev);
+        ++*launches;
+    }
     return cudaGetLastError();
 }

@@ -39,6 +39,11 @@ cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const ui
                                  orbx_keypoint* kps, uint8_t* desc, int nframes, cudaStream_t st,
                                  int* launches, const OrbxSinkArgs& sink);
 
+cudaError_t orbx_launch_sink_wait_flag(const uint32_t* flag, uint32_t epoch, unsigned long long timeout_ns, uint32_t* err,
+                                       cudaStream_t st);
+cudaError_t orbx_launch_sink_release(uint32_t* ack, uint32_t epoch, cudaStream_t st);
+cudaError_t orbx_sink_preload();
+
 namespace {
 
 thread_local std::string g_err = "";
@@ -121,6 +126,8 @@ struct Slot {
     OrbxSrc g_src{};
     // forked form of that graph: one branch per pyramid level (created on first capture)
     OrbxSinkArgs sink{};         // fused result gather (orbx_set_result_sink); hdr == nullptr: off
+    uint32_t* sink_words = nullptr;   // device: [0] batches sent to the sink (epoch), [1] back-pressure timeout flag
+    uint32_t sink_epoch = 0;          // host count of the same
     cudaStream_t aux[ORBX_MAX_LEVELS] = {};
     cudaEvent_t ev_fork = nullptr, ev_lvl[ORBX_MAX_LEVELS] = {}, ev_join[ORBX_MAX_LEVELS] = {};
 };
@@ -554,6 +561,7 @@ int enqueue_kernels(orbx_handle* h, Slot& s, const OrbxSrc& src, int nframes) {
     s.run_w = P.w;
     s.run_h = P.h;
     s.nframes = nframes;
+    if (s.sink.hdr) ++s.sink_epoch;   // k_sink_signal publishes the same count on the device side
     return ORBX_OK;
 }
 
@@ -663,6 +671,7 @@ int orbx_destroy(orbx_handle* h) {
         cudaFree(s.keysA); cudaFree(s.keysB); cudaFree(s.surv); cudaFree(s.survcnt);
         cudaFree(s.dest); cudaFree(s.header); cudaFree(s.kps); cudaFree(s.desc); cudaFree(s.lap_d);
         cudaFree(s.frame_done);
+        if (s.sink_words) cudaFree(s.sink_words);
         if (s.h_header) cudaFreeHost(s.h_header);
         if (s.h_lap) cudaFreeHost(s.h_lap);
         for (int k = 0; k < 6; ++k) if (s.ev[k]) cudaEventDestroy(s.ev[k]);
@@ -1088,12 +1097,19 @@ struct orbx_sink {
     int frames = 0, cap = 0;
     bool opened = false;   // mapped from another process through CUDA IPC
     uint8_t* base = nullptr;
-    size_t off_kps = 0, off_desc = 0, bytes = 0;
+    size_t off_sync = 0, off_kps = 0, off_desc = 0, bytes = 0;
+    cudaStream_t st = nullptr;     // for the blocking forms of orbx_sink_wait / orbx_sink_release
+    uint32_t* err = nullptr;       // device word: a wait timed out
+    uint8_t* pin = nullptr;        // pinned staging of orbx_sink_read_frame (a pageable D2H copy serialises behind
+                                   // running kernels, i.e. behind a producer parked in its back-pressure wait)
+    uint32_t* pin_err = nullptr;   // pinned copy of `err`
 };
 
 namespace {
 void sink_layout(orbx_sink* k) {
-    k->off_kps = ((size_t)k->frames * 16 + 255) & ~(size_t)255;
+    // [frames][4] headers | [frames][2] {flag, ack} completion words | keypoints | descriptors
+    k->off_sync = ((size_t)k->frames * 16 + 255) & ~(size_t)255;
+    k->off_kps = (k->off_sync + (size_t)k->frames * 8 + 255) & ~(size_t)255;
     k->off_desc = (k->off_kps + (size_t)k->frames * k->cap * sizeof(orbx_keypoint) + 255) & ~(size_t)255;
     k->bytes = k->off_desc + (size_t)k->frames * k->cap * 32;
 }
@@ -1155,6 +1171,10 @@ int orbx_sink_open(int device, const uint8_t handle[64], int frames, int cap, or
 int orbx_sink_destroy(orbx_sink* k) {
     if (!k) return ORBX_OK;
     cudaSetDevice(k->device);
+    if (k->st) cudaStreamDestroy(k->st);
+    if (k->err) cudaFree(k->err);
+    if (k->pin) cudaFreeHost(k->pin);
+    if (k->pin_err) cudaFreeHost(k->pin_err);
     if (k->base) {
         if (k->opened) cudaIpcCloseMemHandle(k->base);
         else cudaFree(k->base);
@@ -1162,6 +1182,8 @@ int orbx_sink_destroy(orbx_sink* k) {
     delete k;
     return ORBX_OK;
 }
+
+static int sink_sync_ptr(orbx_sink* k, int first_frame, uint32_t** sync);
 
 int orbx_sink_pointers(orbx_sink* k, void** header, void** kps, void** desc) {
     if (!k) return fail(ORBX_E_BAD_ARG, "null sink");
@@ -1173,19 +1195,34 @@ int orbx_sink_pointers(orbx_sink* k, void** header, void** kps, void** desc) {
 
 int orbx_sink_read_frame(orbx_sink* k, int frame, int32_t header[4], orbx_keypoint* kps, uint8_t* desc, int rows) {
     if (!k || frame < 0 || frame >= k->frames || rows < 0 || rows > k->cap) return fail(ORBX_E_BAD_ARG, "bad argument");
-    CUDA_TRY(cudaSetDevice(k->device));
-    CUDA_TRY(cudaDeviceSynchronize());
-    if (header) CUDA_TRY(cudaMemcpy(header, k->base + (size_t)frame * 16, 16, cudaMemcpyDeviceToHost));
+    // on the sink's own (non-blocking) stream, NOT a device-wide synchronisation: a producer may legitimately be
+    // parked in its back-pressure wait.  Completeness of the frame is the caller's business (orbx_sink_wait, or the
+    // producers' streams / a barrier as in round 1).
+    uint32_t* unused = nullptr;
+    int r = sink_sync_ptr(k, 0, &unused);
+    if (r) return r;
+    uint8_t* ph = k->pin;
+    uint8_t* pk = k->pin + 16;
+    uint8_t* pd = pk + (size_t)k->cap * sizeof(orbx_keypoint);
+    if (header) CUDA_TRY(cudaMemcpyAsync(ph, k->base + (size_t)frame * 16, 16, cudaMemcpyDeviceToHost, k->st));
     if (kps && rows)
-        CUDA_TRY(cudaMemcpy(kps, k->base + k->off_kps + (size_t)frame * k->cap * sizeof(orbx_keypoint),
-                            (size_t)rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost));
+        CUDA_TRY(cudaMemcpyAsync(pk, k->base + k->off_kps + (size_t)frame * k->cap * sizeof(orbx_keypoint),
+                                 (size_t)rows * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, k->st));
     if (desc && rows)
-        CUDA_TRY(cudaMemcpy(desc, k->base + k->off_desc + (size_t)frame * k->cap * 32, (size_t)rows * 32,
-                            cudaMemcpyDeviceToHost));
+        CUDA_TRY(cudaMemcpyAsync(pd, k->base + k->off_desc + (size_t)frame * k->cap * 32, (size_t)rows * 32,
+                                 cudaMemcpyDeviceToHost, k->st));
+    CUDA_TRY(cudaStreamSynchronize(k->st));
+    if (header) memcpy(header, ph, 16);
+    if (kps && rows) memcpy(kps, pk, (size_t)rows * sizeof(orbx_keypoint));
+    if (desc && rows) memcpy(desc, pd, (size_t)rows * 32);
     return ORBX_OK;
 }
 
 int orbx_set_result_sink(orbx_handle* h, int slot, orbx_sink* k, int first_frame) {
+    return orbx_set_result_sink_ex(h, slot, k, first_frame, 0);
+}
+
+int orbx_set_result_sink_ex(orbx_handle* h, int slot, orbx_sink* k, int first_frame, int flags) {
     if (!h || slot < 0 || slot >= (int)h->slots.size()) return fail(ORBX_E_BAD_ARG, "bad slot");
     Slot& s = h->slots[slot];
     if (s.in_flight) return fail(ORBX_E_BUSY, "slot %d has an un-waited submit", slot);
@@ -1216,10 +1253,82 @@ int orbx_set_result_sink(orbx_handle* h, int slot, orbx_sink* k, int first_frame
     } else if (k->opened && k->device != h->cfg.device) {
         return fail(ORBX_E_BAD_ARG, "the sink was opened on device %d, the handle runs on %d", k->device, h->cfg.device);
     }
+    CUDA_TRY(orbx_sink_preload());
+    if (!s.sink_words) CUDA_TRY(cudaMalloc((void**)&s.sink_words, 8));
+    CUDA_TRY(cudaMemset(s.sink_words, 0, 8));
+    s.sink_epoch = 0;
     s.sink.hdr = (int32_t*)k->base;
     s.sink.kps = (orbx_keypoint*)(k->base + k->off_kps);
     s.sink.desc = k->base + k->off_desc;
     s.sink.first_frame = first_frame;
+    // the region's completion words live in the sink: word 2 * first_frame = flag, + 1 = ack.  A region that is
+    // (re)attached starts a new count: the producer clears both (the consumer counts from 1 again).
+    uint32_t* sync = (uint32_t*)(k->base + k->off_sync) + 2 * (size_t)first_frame;
+    CUDA_TRY(cudaMemset(sync, 0, 8));
+    s.sink.flag = sync;
+    s.sink.ack = (flags & ORBX_SINK_BACKPRESSURE) ? sync + 1 : nullptr;
+    s.sink.epoch_dev = s.sink_words;
+    s.sink.err_dev = s.sink_words + 1;
+    return ORBX_OK;
+}
+
+int orbx_sink_epoch(orbx_handle* h, int slot, uint32_t* epoch, int* timed_out) {
+    if (!h || slot < 0 || slot >= (int)h->slots.size() || !epoch) return fail(ORBX_E_BAD_ARG, "bad argument");
+    Slot& s = h->slots[slot];
+    *epoch = s.sink_epoch;
+    if (timed_out) {
+        *timed_out = 0;
+        if (s.sink_words && !s.in_flight) {
+            uint32_t w[2] = {0, 0};
+            CUDA_TRY(cudaSetDevice(h->cfg.device));
+            CUDA_TRY(cudaMemcpy(w, s.sink_words, 8, cudaMemcpyDeviceToHost));
+            *timed_out = (int)w[1];
+        }
+    }
+    return ORBX_OK;
+}
+
+static int sink_sync_ptr(orbx_sink* k, int first_frame, uint32_t** sync) {
+    if (!k || first_frame < 0 || first_frame >= k->frames) return fail(ORBX_E_BAD_ARG, "bad sink region");
+    CUDA_TRY(cudaSetDevice(k->device));
+    if (!k->st) CUDA_TRY(cudaStreamCreateWithFlags(&k->st, cudaStreamNonBlocking));
+    if (!k->err) {
+        CUDA_TRY(cudaMalloc((void**)&k->err, 4));
+        CUDA_TRY(cudaMemsetAsync(k->err, 0, 4, k->st));
+        CUDA_TRY(cudaHostAlloc((void**)&k->pin_err, 4, cudaHostAllocDefault));
+        CUDA_TRY(cudaHostAlloc((void**)&k->pin, 16 + (size_t)k->cap * (sizeof(orbx_keypoint) + 32), cudaHostAllocDefault));
+        CUDA_TRY(cudaStreamSynchronize(k->st));
+    }
+    CUDA_TRY(orbx_sink_preload());
+    *sync = (uint32_t*)(k->base + k->off_sync) + 2 * (size_t)first_frame;
+    return ORBX_OK;
+}
+
+int orbx_sink_wait(orbx_sink* k, int first_frame, uint32_t epoch, void* stream, int timeout_ms) {
+    uint32_t* sync = nullptr;
+    int r = sink_sync_ptr(k, first_frame, &sync);
+    if (r) return r;
+    const unsigned long long ns = (unsigned long long)(timeout_ms > 0 ? timeout_ms : 2000) * 1000000ull;
+    cudaStream_t st = stream ? (cudaStream_t)stream : k->st;
+    CUDA_TRY(orbx_launch_sink_wait_flag(sync, epoch, ns, k->err, st));
+    if (stream) return ORBX_OK;   // ordered on the caller's stream: work enqueued after it sees the batch
+    CUDA_TRY(cudaMemcpyAsync(k->pin_err, k->err, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (*k->pin_err) {
+        CUDA_TRY(cudaMemsetAsync(k->err, 0, 4, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        return fail(ORBX_E_BUSY, "sink region %d: batch %u did not arrive within %d ms", first_frame, epoch, timeout_ms);
+    }
+    return ORBX_OK;
+}
+
+int orbx_sink_release(orbx_sink* k, int first_frame, uint32_t epoch, void* stream) {
+    uint32_t* sync = nullptr;
+    int r = sink_sync_ptr(k, first_frame, &sync);
+    if (r) return r;
+    cudaStream_t st = stream ? (cudaStream_t)stream : k->st;
+    CUDA_TRY(orbx_launch_sink_release(sync + 1, epoch, st));
+    if (!stream) CUDA_TRY(cudaStreamSynchronize(st));
     return ORBX_OK;
 }
 

@@ -106,6 +106,13 @@ struct OrbxSinkArgs {
     uint8_t* desc;         // [frames][out_cap][32]
     int first_frame;
     int _pad;
+    // completion signal of the fused gather: after the batch's rows are in the sink, the producer bumps its own
+    // device-side batch counter and publishes it at `flag` (a word of the sink, system scope); with back-pressure it
+    // first waits until the consumer has released the previous batch at `ack` (nullptr: no back-pressure)
+    uint32_t* flag;
+    const uint32_t* ack;
+    uint32_t* epoch_dev;   // this slot's batch counter (local device memory)
+    uint32_t* err_dev;     // set to 1 when the back-pressure wait timed out
 };
 
 #endif  // ORBX_INTERNAL_H

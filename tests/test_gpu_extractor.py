@@ -387,3 +387,61 @@ def test_fused_result_gather_sink_peer_gpu(synth):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
     _sink_roundtrip(synth, 1, 0)
+
+
+def test_sink_completion_signal_and_backpressure(synth):
+    """The fused gather has a consumer: orbx_sink_wait sees batch e of a region only after it is complete, and with
+    ORBX_SINK_BACKPRESSURE the producer does not overwrite a batch the consumer has not released."""
+    import ctypes as C
+    import time
+    from orb_slam3_mac_b200 import _lib, sharding
+    lib = _lib.load()
+    B, w, h = 4, 752, 480
+    conf = _lib.OrbxConfig(1000, 1.2, 8, 20, 7, w, h, B, 2, 0, 0)
+    hd = C.c_void_p()
+    _lib.check(lib.orbx_create(C.byref(conf), C.byref(hd)))
+    cap = lib.orbx_max_keypoints(hd)
+    sink = sharding.ResultSink(0, 2 * B, cap)
+    first = B   # the second region of the slab
+    frames = [np.stack([synth.frame(["noise", "checker"][i % 2], h, w, 60 + 10 * k + i) for i in range(B)]) for k in range(2)]
+    hin = [lib.orbx_host_alloc(B * h * w) for _ in range(2)]
+    for k in range(2):
+        C.memmove(hin[k], frames[k].ctypes.data, B * h * w)
+    kps, desc = lib.orbx_host_alloc(B * cap * 28), lib.orbx_host_alloc(B * cap * 32)
+    n, mono, st = np.zeros(B, np.int32), np.zeros(B, np.int32), np.zeros(B, np.int32)
+    lap = np.tile(np.array([0, 1000], np.int32), (B, 1))
+
+    def submit(k):
+        ptrs = (C.c_void_p * B)(*[hin[k] + i * h * w for i in range(B)])
+        _lib.check(lib.orbx_submit_batch(hd, 0, ptrs, B, w, h, w, lap.ctypes.data, kps, desc, cap, n.ctypes.data,
+                                         mono.ctypes.data, st.ctypes.data))
+
+    try:
+        _lib.check(lib.orbx_set_result_sink_ex(hd, 0, sink.h, first, 1))   # ORBX_SINK_BACKPRESSURE
+        assert lib.orbx_sink_wait(sink.h, first, 1, None, 50) == _lib.ORBX_E_BUSY      # nothing produced yet
+        submit(0)
+        _lib.check(lib.orbx_wait(hd, 0))
+        n1 = n.copy()
+        _lib.check(lib.orbx_sink_wait(sink.h, first, 1, None, 2000))                   # batch 1 is complete in the slab
+        for i in range(B):
+            assert sink.read_frame(first + i)[0][0] == n1[i]
+        # batch 2 while batch 1 is not released: the producer waits in front of k_describe
+        submit(1)
+        assert lib.orbx_sink_wait(sink.h, first, 2, None, 150) == _lib.ORBX_E_BUSY
+        hdr_now = sink.read_frame(first)[0]
+        assert hdr_now[0] == n1[0]                                                     # region still holds batch 1
+        _lib.check(lib.orbx_sink_release(sink.h, first, 1, None))
+        _lib.check(lib.orbx_sink_wait(sink.h, first, 2, None, 2000))
+        _lib.check(lib.orbx_wait(hd, 0))
+        for i in range(B):
+            assert sink.read_frame(first + i)[0][0] == n[i]
+        ep, to = C.c_uint32(), C.c_int()
+        _lib.check(lib.orbx_sink_epoch(hd, 0, C.byref(ep), C.byref(to)))
+        assert ep.value == 2 and to.value == 0
+        _lib.check(lib.orbx_sink_release(sink.h, first, 2, None))
+    finally:
+        lib.orbx_wait(hd, 0)
+        lib.orbx_destroy(hd)
+        sink.close()
+        for p in hin + [kps, desc]:
+            lib.orbx_host_free(p)
