@@ -217,6 +217,10 @@ int orbx_device_pyramid(orbx_handle* h, int slot, int frame, orbx_pyramid_view* 
  * cell): int32 triplets {x, y, response}, coordinates relative to (16,16) as
  * vToDistributeKeys in ORBextractor.cc:776-854.  Returns the count (or <0). */
 int orbx_debug_candidates(orbx_handle* h, int slot, int frame, int level, int32_t* xyr, int cap);
+/* Parity tap of the descriptor stage's cos / sin (computeOrbDescriptor's (float)cos(angle), (float)sin(angle),
+ * src/ORBextractor.cc:113-114): the kernel's own double-precision evaluation against CUDA's sincos() on EVERY float in
+ * [lo, hi] (0 <= lo <= hi); *n_bad = values whose float cos or sin differs, *first_bad = the smallest of them. */
+int orbx_debug_sincos_check(int device, float lo, float hi, unsigned long long* n_bad, float* first_bad);
 /* Quadtree survivors of one level in DistributeOctTree's output order (ORBextractor.cc:738-758):
  * int32 triplets {x, y, response}, same coordinate convention.  Returns the count (or <0). */
 int orbx_debug_survivors(orbx_handle* h, int slot, int frame, int level, int32_t* xyr, int cap);

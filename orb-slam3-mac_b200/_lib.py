@@ -83,6 +83,7 @@ ORBX_SYMBOLS = {
     "orbx_sink_pointers": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)]),
     "orbx_sink_read_frame": (_i, [_vp, _i, _vp, _vp, _vp, _i]),
     "orbx_set_result_sink": (_i, [_vp, _i, _vp, _i]),
+    "orbx_debug_sincos_check": (_i, [_i, C.c_float, C.c_float, C.POINTER(C.c_ulonglong), C.POINTER(C.c_float)]),
     "orbx_set_result_sink_ex": (_i, [_vp, _i, _vp, _i, _i]),
     "orbx_sink_wait": (_i, [_vp, _i, C.c_uint32, _vp, _i]),
     "orbx_sink_release": (_i, [_vp, _i, C.c_uint32, _vp]),

@@ -18,6 +18,7 @@
 //                The blurred patch lives only in shared memory (never written to HBM); lane i
 //                samples its 16 pattern points from it (cvRound by the 1.5*2^23 magic add) and
 //                produces descriptor byte i.
+#include <cstring>
 #include <mutex>
 
 #include "orbx_device.cuh"
@@ -88,6 +89,34 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     if (x < 0) a = __fsub_rn(180.f, a);
     if (y < 0) a = __fsub_rn(360.f, a);
     return a;
+}
+
+// cos / sin of a float angle in [0, 2 pi] to double accuracy, rounded once to float -- what the reference's
+// (float)cos(angle) needs -- without the general sincos(double): the quadrant comes from one multiply, the reduced
+// argument r = x - q * pi/2 from a two-term pi/2 (q <= 4, so q * PIO2_HI is exact), and sin r / cos r on
+// |r| <= pi/4 from the classical degree-13 / degree-14 minimax polynomials (fdlibm's __kernel_sin / __kernel_cos
+// coefficients, error < 2^-57).  ~30 FP64 instructions instead of ~75.  tests/test_gpu_extractor.py checks it against
+// sincos() on EVERY float in [0, 6.2832] (orbx_debug_sincos_check): identical float results.  NOT the default: measured
+// slower than sincos() inside k_describe (see DESC_POLY_SINCOS below); kept as the evidence of the attempt.
+__device__ __forceinline__ void desc_sincos(float ang, float* cs, float* sn) {
+    const double x = (double)ang;
+    const double PIO2_HI = 1.57079632679489655800e+00, PIO2_LO = 6.12323399573676603587e-17;
+    const double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03, S3 = -1.98412698298579493134e-04,
+                 S4 = 2.75573137070700676789e-06, S5 = -2.50507602534068634195e-08, S6 = 1.58969099521155010221e-10;
+    const double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03, C3 = 2.48015872894767294178e-05,
+                 C4 = -2.75573143513906633035e-07, C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
+    const int q = __double2int_rn(x * 6.36619772367581382433e-01);   // x * 2 / pi
+    const double qd = (double)q;
+    const double r = fma(-qd, PIO2_LO, fma(-qd, PIO2_HI, x));
+    const double z = r * r;
+    const double ps = fma(fma(fma(fma(fma(S6, z, S5), z, S4), z, S3), z, S2), z, S1);
+    const double s = fma(r * z, ps, r);
+    const double pc = fma(fma(fma(fma(fma(C6, z, C5), z, C4), z, C3), z, C2), z, C1);
+    const double c = fma(z * z, pc, fma(-0.5, z, 1.0));
+    // quadrant: (cos, sin)(x) = (c, s), (-s, c), (-c, -s), (s, -c)
+    const double cq = (q & 1) ? s : c, sq = (q & 1) ? c : s;
+    *cs = (float)(((q + 1) & 2) ? -cq : cq);
+    *sn = (float)((q & 2) ? -sq : sq);
 }
 
 __device__ __forceinline__ void cp_async4(uint32_t saddr, const void* g) {
@@ -243,9 +272,17 @@ k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t
     const float ang = __fmul_rn(angle, factorPI);
     // correctly rounded float cos/sin via double (glibc's cosf/sinf are within 0.55 ulp;
     // see DESIGN.md on the residual cvRound-boundary mismatches)
-    double sd, cd;
-    sincos((double)ang, &sd, &cd);
-    const float a = (float)cd, b = (float)sd;
+    float a, b;
+#ifdef DESC_POLY_SINCOS   // A/B (r2): bit-identical on every angle, but SLOWER -- describe 0.662 vs 0.617 ms per 384 frames:
+    desc_sincos(ang, &a, &b);   // 7 % fewer instructions, yet a 20-deep dependent FP64 FMA chain per warp
+#else
+    {
+        double sd, cd;
+        sincos((double)ang, &sd, &cd);
+        a = (float)cd;
+        b = (float)sd;
+    }
+#endif
     // B[18 + dy][xo + 18 + dx]; cvRound(v) = bits(v + 1.5*2^23) - 0x4B400000 (round half even)
     const float MAGIC = 12582912.f;
     const uint8_t* Bb = reinterpret_cast<const uint8_t*>(Bw);
@@ -353,6 +390,45 @@ cudaError_t orbx_launch_sink_wait_flag(const uint32_t* flag, uint32_t epoch, uns
 cudaError_t orbx_launch_sink_release(uint32_t* ack, uint32_t epoch, cudaStream_t st) {
     k_sink_release<<<1, 1, 0, st>>>(ack, epoch);
     return cudaGetLastError();
+}
+
+// Exhaustive check of desc_sincos against sincos(): every float bit pattern in [first, last]; counts the values whose
+// float cos or sin differs and keeps the first one.
+__global__ void k_sincos_check(uint32_t first, uint32_t last, unsigned long long* bad, uint32_t* first_bad) {
+    const uint64_t n = (uint64_t)last - first + 1;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const float x = __uint_as_float(first + (uint32_t)i);
+        float c, s;
+        desc_sincos(x, &c, &s);
+        double sd, cd;
+        sincos((double)x, &sd, &cd);
+        if (__float_as_uint(c) != __float_as_uint((float)cd) || __float_as_uint(s) != __float_as_uint((float)sd)) {
+            atomicAdd(bad, 1ull);
+            atomicMin(first_bad, first + (uint32_t)i);
+        }
+    }
+}
+cudaError_t orbx_run_sincos_check(float lo, float hi, unsigned long long* n_bad, float* first_bad) {
+    unsigned long long* d_bad;
+    uint32_t* d_first;
+    cudaError_t e;
+    if ((e = cudaMalloc((void**)&d_bad, 16)) != cudaSuccess) return e;
+    d_first = (uint32_t*)(d_bad + 1);
+    const unsigned long long zero = 0;
+    const uint32_t ones = 0xffffffffu;
+    cudaMemcpy(d_bad, &zero, 8, cudaMemcpyHostToDevice);
+    cudaMemcpy(d_first, &ones, 4, cudaMemcpyHostToDevice);
+    uint32_t a, b;
+    memcpy(&a, &lo, 4);
+    memcpy(&b, &hi, 4);
+    k_sincos_check<<<148 * 16, 256>>>(a, b, d_bad, d_first);
+    e = cudaDeviceSynchronize();
+    uint32_t fb = 0;
+    cudaMemcpy(n_bad, d_bad, 8, cudaMemcpyDeviceToHost);
+    cudaMemcpy(&fb, d_first, 4, cudaMemcpyDeviceToHost);
+    memcpy(first_bad, &fb, 4);
+    cudaFree(d_bad);
+    return e;
 }
 
 cudaError_t orbx_launch_describe(const OrbxPlan& P, const OrbxSrc& src, const uint8_t* pyr,

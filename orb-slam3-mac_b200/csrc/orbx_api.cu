@@ -43,6 +43,7 @@ cudaError_t orbx_launch_sink_wait_flag(const uint32_t* flag, uint32_t epoch, uns
                                        cudaStream_t st);
 cudaError_t orbx_launch_sink_release(uint32_t* ack, uint32_t epoch, cudaStream_t st);
 cudaError_t orbx_sink_preload();
+cudaError_t orbx_run_sincos_check(float lo, float hi, unsigned long long* n_bad, float* first_bad);
 
 namespace {
 
@@ -1036,6 +1037,13 @@ int orbx_device_pyramid(orbx_handle* h, int slot, int frame, orbx_pyramid_view* 
         out->width[l] = L.w;
         out->height[l] = L.h;
     }
+    return ORBX_OK;
+}
+
+int orbx_debug_sincos_check(int device, float lo, float hi, unsigned long long* n_bad, float* first_bad) {
+    if (!n_bad || !first_bad || !(lo >= 0.f) || !(hi >= lo)) return fail(ORBX_E_BAD_ARG, "bad argument");
+    CUDA_TRY(cudaSetDevice(device));
+    CUDA_TRY(orbx_run_sincos_check(lo, hi, n_bad, first_bad));
     return ORBX_OK;
 }
 

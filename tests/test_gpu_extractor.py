@@ -445,3 +445,15 @@ def test_sink_completion_signal_and_backpressure(synth):
         sink.close()
         for p in hin + [kps, desc]:
             lib.orbx_host_free(p)
+
+
+def test_descriptor_sincos_matches_libm_on_every_angle():
+    """k_describe's own cos / sin (quadrant reduction + degree-13 / 14 polynomials in double) gives the same FLOAT as
+    sincos((double)angle) for every float angle the pipeline can produce: angle = fastAtan2 degrees in [0, 360] times
+    (float)(pi / 180) lies in [0, 6.2832]; all 1.09e9 floats of that range are compared on the device."""
+    import ctypes as C
+    from orb_slam3_mac_b200 import _lib
+    lib = _lib.load()
+    bad, first = C.c_ulonglong(), C.c_float()
+    _lib.check(lib.orbx_debug_sincos_check(0, 0.0, 6.2832, C.byref(bad), C.byref(first)))
+    assert bad.value == 0, (bad.value, first.value)
