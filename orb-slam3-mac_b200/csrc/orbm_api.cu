@@ -55,12 +55,20 @@ cudaError_t orbm_launch_stereo_rows(const orbx_keypoint* kl, const uint8_t* dl, 
 // error string shared with orbx_api.cu (orbx_last_error_string reads it)
 int orbx_set_error(int code, const char* fmt, ...);
 
+// A failed CUDA call ends the API call early.  Copies that the call had already staged (ctx_h2d / ctx_d2h: scatter
+// segments, pending deliveries into the CALLER's arrays -- some of them stack locals of the failed call) must not
+// survive into the next call's ctx_sync: orbm_abort_staged() drains the stream and drops them.
+struct orbm_context;
+void orbm_abort_staged(orbm_context* c);
+static thread_local orbm_context* g_staging_ctx = nullptr;   // the context whose call is staging copies on this thread
 #define M_TRY(expr)                                                                              \
     do {                                                                                         \
         cudaError_t _e = (expr);                                                                 \
-        if (_e != cudaSuccess)                                                                   \
+        if (_e != cudaSuccess) {                                                                 \
+            if (g_staging_ctx) orbm_abort_staged(g_staging_ctx);                                 \
             return orbx_set_error(ORBX_E_CUDA, "%s failed: %s (%s:%d)", #expr,                  \
                                   cudaGetErrorString(_e), __FILE__, __LINE__);                   \
+        }                                                                                        \
     } while (0)
 
 namespace {
@@ -198,8 +206,18 @@ static cudaError_t ctx_flush(orbm_context* c) {
     return e;
 }
 
+void orbm_abort_staged(orbm_context* c) {
+    cudaStreamSynchronize(c->st);   // whatever was queued may still read the arena
+    cudaGetLastError();
+    c->pending.clear();
+    c->up.n = 0;
+    c->pin_used = 0;
+    g_staging_ctx = nullptr;
+}
+
 static cudaError_t ctx_h2d(orbm_context* c, void* dst, const void* src, size_t bytes) {
     if (bytes == 0) return cudaSuccess;
+    g_staging_ctx = c;
     const size_t off = (c->pin_used + 63) & ~(size_t)63;
     if (bytes > ORBM_PIN_DIRECT) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->st);
     if (off + bytes > c->pin_cap) {
@@ -219,6 +237,7 @@ static cudaError_t ctx_h2d(orbm_context* c, void* dst, const void* src, size_t b
 
 static cudaError_t ctx_d2h(orbm_context* c, void* dst, const void* src, size_t bytes) {
     if (bytes == 0) return cudaSuccess;
+    g_staging_ctx = c;
     cudaError_t ef = ctx_flush(c);
     if (ef != cudaSuccess) return ef;
     const size_t off = (c->pin_used + 63) & ~(size_t)63;
@@ -242,6 +261,7 @@ static cudaError_t ctx_sync(orbm_context* c) {
     c->pending.clear();
     c->pin_used = 0;
     c->up.n = 0;
+    g_staging_ctx = nullptr;
     if (e == cudaSuccess && c->pin_cap && c->pin_want > c->pin_cap && c->pin_cap < ORBM_PIN_MAX) {
         size_t want = std::min(std::max(c->pin_want * 2, ORBM_PIN_INIT), ORBM_PIN_MAX);
         uint8_t* np = nullptr;

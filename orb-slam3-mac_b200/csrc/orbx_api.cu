@@ -434,6 +434,11 @@ int set_shape(orbx_handle* h, int w, int hgt) {
     std::vector<uint8_t> tab;
     int r = build_plan(h, w, hgt, &P, &tab);
     if (r) return r;
+    // a new shape reallocates the buffers of EVERY slot: device pointers handed out for a slot that is still in flight
+    // (orbx_extract_device results, orbx_device_pyramid views, a sink) would dangle -- refuse instead
+    for (size_t i = 0; i < h->slots.size(); ++i)
+        if (h->slots[i].in_flight)
+            return fail(ORBX_E_BUSY, "image shape changes to %dx%d while slot %d has an un-waited submit", w, hgt, (int)i);
     if ((r = sync_all(h))) return r;
     size_t need = std::max(tab.size(), (size_t)256);
     if ((r = grow(&h->tables, &h->tables_bytes, need))) return r;
