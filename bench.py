@@ -865,6 +865,11 @@ def run_ours(args):
                 line["configs"] = bench_pipelines.run_pipelines(reps=30, cpu=not args.no_cpu_baseline, device=local)
             except Exception as e:   # an extra must not cost the headline line
                 line["configs"] = {"error": repr(e)}
+            try:   # C5 (1920x1080, 4000 features, batched) through this same script, as a short run of its own
+                if isinstance(line.get("configs"), dict):
+                    line["configs"]["C5"] = config_row("C5", steps=6, cpu=not args.no_cpu_baseline)
+            except Exception as e:
+                line["configs"]["C5"] = {"error": repr(e)}
             try:
                 import bench_match
                 line["matcher"] = bench_match.collect(reps=15, cpu=not args.no_cpu_baseline)
@@ -885,6 +890,27 @@ def run_ours(args):
         if sink is not None and rank == 0:
             sink.close()     # ... then the owner frees
         dist.destroy_process_group()
+
+
+def config_row(config: str, steps: int, cpu: bool) -> dict:
+    """One extraction-only config as a row of `configs`: a short run of this script on that config (its own process, same
+    timing rules), reduced to the figures a row carries."""
+    import subprocess
+    cmd = [sys.executable, os.path.abspath(__file__), "--config", config, "--steps", str(steps), "--warmup", "3",
+           "--no-extras", "--sustain-s", "0"] + ([] if cpu else ["--no-cpu-baseline"])
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, check=True).stdout
+    d = json.loads(out.strip().splitlines()[-1])
+    row = {"what": d["config"]["workload"], "unit": d["unit"], "value": d["value"], "ms_per_step": d["ms_per_step"],
+           "frames_per_step": d["config"].get("frames_per_step_per_gpu"), "e2e": d["e2e"]["value"],
+           "p50_us": (d.get("latency") or {}).get("p50_us"), "steps": d["steps"],
+           "stage_ms": {k: v["ms_per_launch_batch"] for k, v in d["roofline"]["kernels"].items()},
+           "roofline_frac": {k: v["frac"] for k, v in d["roofline"]["kernels"].items()}}
+    if "cpu_baseline" in d:
+        cb = d["cpu_baseline"]
+        row.update({"cpu_value": cb["value"], "cpu_threads": cb["cores"], "cpu_kind": cb["kind"],
+                    "cpu_value_guarded": cb.get("value_guarded"), "speedup": d["e2e"]["value"] / cb["value"],
+                    "speedup_guarded": d["e2e"].get("vs_cpu_guarded")})
+    return row
 
 
 def main():
