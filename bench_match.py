@@ -147,6 +147,20 @@ def main(argv=None):
     lo_r, ld_r = S.last_frame_obs(k0, d0, 9)
     report("C4 SearchByProjection frames, resident frame", "frame-to-frame search on the resident frame",
            lambda: m.SearchByProjectionFrames(RF, lo_r, ld_r, 15.0), None)
+    # ... and the map points' descriptors in a device-resident bank (orbm_bank): a call sends its window queries only
+    from orb_slam3_mac_b200.matcher import DescriptorBank
+    bank = DescriptorBank(m, len(md) + len(ld_r))
+    bank.write(0, md)
+    bank.write(len(md), ld_r)
+    rows_l = np.arange(len(md), len(md) + len(ld_r), dtype=np.int32)
+    want = m.SearchByProjection(RF, mps, md, 1.0, False, 30.0)
+    got = m.SearchByProjection(RF, mps, bank, 1.0, False, 30.0)
+    assert got[0] == want[0] and np.array_equal(got[1], want[1]), "bank search differs"
+    report("C4 SearchByProjection, resident frame + descriptor bank", "same search, map-point descriptors resident too",
+           lambda: m.SearchByProjection(RF, mps, bank, 1.0, False, 30.0), None)
+    report("C4 SearchByProjection frames, resident frame + descriptor bank", "frame-to-frame search, descriptors resident too",
+           lambda: m.SearchByProjectionFrames(RF, lo_r, bank, 15.0, rows=rows_l), None)
+    bank.close()
     RF.close()
 
     # ---- M4: SearchForInitialization with the 5 x nFeatures extractor at C1 -----------------------------

@@ -387,6 +387,38 @@ const orbm_frame_view* orbm_frame_get_view(const orbm_frame* f);
 int orbm_frame_set_u_right(orbm_frame* f, const float* u_right);
 int orbm_frame_destroy(orbm_frame* f);
 
+/* ---- device-resident descriptor rows ("banks") -------------------------------------------------------------
+ * A MapPoint keeps its descriptor (MapPoint::mDescriptor, read through pMP->GetDescriptor() at
+ * src/ORBmatcher.cc:80 and :2031) from one frame to the next, and tracking projects the same few thousand map points
+ * into every frame (SearchLocalPoints -> :48; TrackWithMotionModel -> :1965, the last frame's map points).  A bank
+ * keeps such 32-byte rows on the device: the *_bank searches below take, per query, the ROW of its descriptor instead
+ * of the descriptor itself, so a call uploads its window queries only (32 bytes less per query, and no copy of them
+ * on the host).  Results are identical to the host-descriptor entry points.
+ *   orbm_bank_create / _write / _destroy : rows owned by the bank; _write (row = e.g. the map point's slot; call it
+ *       where MapPoint::ComputeDistinctiveDescriptors stores a new mDescriptor, src/MapPoint.cc:402; the constructor
+ *       from a frame copies the keypoint's row, :109) returns when
+ *       the rows are in place and is ordered with the context's searches.
+ *   orbm_frame_bank : a resident frame's descriptors as a bank (row = keypoint index; a map point created from a
+ *       keypoint starts with that keypoint's descriptor); lives and dies with the frame.
+ * `rows` = the bank row per query, NULL for row i.  A bank belongs to the context that made it. */
+typedef struct orbm_bank orbm_bank;
+int orbm_bank_create(orbm_context* c, int capacity_rows, orbm_bank** out);
+int orbm_bank_write(orbm_bank* b, int first_row, int n, const uint8_t* desc);
+int orbm_bank_rows(const orbm_bank* b);
+int orbm_bank_destroy(orbm_bank* b);
+const orbm_bank* orbm_frame_bank(const orbm_frame* f);
+
+/* orbm_search_by_projection_points (src/ORBmatcher.cc:48-218) with the map points' descriptors in a bank. */
+int orbm_search_by_projection_points_bank(orbm_context* c, const orbm_frame_view* F, const orbm_map_point* mps,
+                                          const orbm_bank* bank, const int32_t* rows, int m, float th, int far_points,
+                                          float th_far, float nn_ratio, int32_t* kp_obs, int32_t* kp_match);
+/* orbm_search_by_projection_frames (src/ORBmatcher.cc:1965-2181) with the descriptors of the last frame's map
+ * points in a bank (rows = the bank row of each observation's map point). */
+int orbm_search_by_projection_frames_bank(orbm_context* c, const orbm_frame_view* cur, const orbm_last_obs* last,
+                                          const orbm_bank* bank, const int32_t* rows, int n_last, float th, int forward,
+                                          int backward, float bf, int check_orientation, int32_t* kp_obs,
+                                          int32_t* kp_match);
+
 /* ---- window search without any allocation ----------------------------------------------------------
  * NO COUNTERPART IN THE REFERENCE: added for callers that cannot
  * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).

@@ -83,6 +83,13 @@ ORBM_SYMBOLS = {
     "orbm_frame_get_view": (_vp, [_vp]),
     "orbm_frame_set_u_right": (_i, [_vp, _vp]),
     "orbm_frame_destroy": (_i, [_vp]),
+    "orbm_bank_create": (_i, [_vp, _i, C.POINTER(C.c_void_p)]),
+    "orbm_bank_write": (_i, [_vp, _i, _i, _vp]),
+    "orbm_bank_rows": (_i, [_vp]),
+    "orbm_bank_destroy": (_i, [_vp]),
+    "orbm_frame_bank": (_vp, [_vp]),
+    "orbm_search_by_projection_points_bank": (_i, [_vp, _fv, _vp, _vp, _vp, _i, _f, _i, _f, _f, _vp, _vp]),
+    "orbm_search_by_projection_frames_bank": (_i, [_vp, _fv, _vp, _vp, _vp, _i, _f, _i, _i, _f, _i, _vp, _vp]),
     "orbm_area_candidates_static": (_i, [_i, _vp, _vp, _vp, _i, _f, _f, _f, _f, _vp, _i, _vp, _vp, _vp, _vp, _i]),
     "orbm_last_device_ms": (_i, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_longlong)]),
     "orbm_measure_popc_peak": (_i, [_vp, C.POINTER(C.c_double)]),

@@ -136,6 +136,7 @@ struct orbm_context {
     std::vector<int32_t> h_topc;     // k_csr_topk: the candidate each key names
     int nnz_hint = 0;                // pairs of the last window search: sizes the lists of the next one before its counts are known
     bool have_full = true;           // h_cand / hdist hold the last search's full lists (top-K mode fetches them lazily)
+    std::vector<float> h_rad;        // window radius per query of the last SearchByProjection (the accept loop reads it)
     std::vector<int32_t> h_items;    // work items of the last orbm_distinctive_descriptors call
     long long last_pairs = 0;        // number of (query, candidate) pairs of the last search
     // pinned staging arena (ctx_h2d / ctx_d2h / ctx_sync below)
@@ -153,6 +154,16 @@ struct orbm_context {
 cudaError_t orbm_launch_undistort(const orbx_keypoint* keys, int n, const float* cam9, float width, float height,
                                   orbx_keypoint* keys_un, float* corners_xy, cudaStream_t st);
 
+// Descriptor rows that stay on the device across calls: the descriptors of the map points (one row per MapPoint,
+// rewritten when MapPoint::ComputeDistinctiveDescriptors changes it) or of a resident frame (orbm_frame_bank).  The
+// *_bank searches name their queries' descriptors by row instead of sending 32 bytes per query with every call.
+struct orbm_bank {
+    orbm_context* ctx = nullptr;
+    DevBuf buf;                   // rows owned by the bank (orbm_bank_create)
+    const uint8_t* d = nullptr;   // the rows: buf.p, or a resident frame's descriptors
+    int rows = 0;
+};
+
 // A frame whose (undistorted) keypoints, descriptors and 64 x 48 grid stay on the device across the two or three
 // searches it goes through (TrackWithMotionModel -> SearchLocalPoints -> relocalisation).  `view` is what the
 // searches take: its address is the frame's identity (device_candidates looks it up in c->frames).
@@ -163,6 +174,7 @@ struct orbm_frame {
     std::vector<orbx_keypoint> h_keys;   // mvKeysUn (the accept loops read octaves on the host)
     std::vector<uint8_t> h_desc;
     std::vector<float> h_scale, h_uright;
+    orbm_bank bank;   // view of d_desc (orbm_frame_bank)
 };
 
 // Host <-> device copies of a call go through one pinned arena per context: a caller's (pageable) array
@@ -233,6 +245,30 @@ static cudaError_t ctx_h2d(orbm_context* c, void* dst, const void* src, size_t b
     if (c->up.n == 0) c->up_first = off;
     c->up.seg[c->up.n++] = OrbmScatter::Seg{dst, (const void*)(uintptr_t)off, (uint32_t)bytes, 0};
     return cudaSuccess;
+}
+
+// Room for `bytes` of an upload to `dst` inside the arena, for a caller that builds the data in place (the window
+// queries of a search: no intermediate array, no memcpy).  nullptr when the arena cannot take it: the caller then
+// builds its own array and sends it with ctx_h2d.
+static void* ctx_stage(orbm_context* c, void* dst, size_t bytes) {
+    const size_t off = (c->pin_used + 63) & ~(size_t)63;
+    if (bytes == 0 || bytes > ORBM_PIN_DIRECT || c->up.n == ORBM_SCATTER_MAX) return nullptr;
+    if (off + bytes > c->pin_cap) {
+        c->pin_want = std::max(c->pin_want, off + bytes);
+        return nullptr;
+    }
+    g_staging_ctx = c;
+    c->pin_used = off + bytes;
+    if (c->up.n == 0) c->up_first = off;
+    c->up.seg[c->up.n++] = OrbmScatter::Seg{dst, (const void*)(uintptr_t)off, (uint32_t)bytes, 0};
+    return c->pin + off;
+}
+
+// Drops what a call has staged but not sent (an argument error found while the queries were being built).
+static void ctx_unstage(orbm_context* c) {
+    c->up.n = 0;
+    c->pin_used = 0;
+    g_staging_ctx = nullptr;
 }
 
 static cudaError_t ctx_d2h(orbm_context* c, void* dst, const void* src, size_t bytes) {
@@ -533,10 +569,11 @@ int check_view(const orbm_frame_view* F) {
 // c->h_rowptr / c->h_cand and the distances in c->hdist.
 // topk > 0: the rows' full lists stay on the device (window_full_lists() fetches them on demand) and the
 // host gets k_csr_topk's topk best (distance, position) keys + candidates per row instead.
-int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vector<orbm_area_query>& Q,
-                      const uint8_t* qdesc, int n_qdesc, int topk = 0) {
+// q_staged: the queries are already in the arena (stage_queries).  d_qdesc: the queries' descriptors are rows of a
+// device-resident bank (qdesc is then null and nothing is sent for them).
+int device_candidates(orbm_context* c, const orbm_frame_view* F, const orbm_area_query* Qp, int nq, bool q_staged,
+                      const uint8_t* qdesc, int n_qdesc, const uint8_t* d_qdesc, int topk = 0) {
     ORBM_PHASE_BEGIN("device_candidates");
-    const int nq = (int)Q.size();
     c->h_rowptr.assign(nq + 1, 0);
     c->h_cand.clear();
     c->hdist.clear();
@@ -544,7 +581,10 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     c->h_topk.assign((size_t)nq * topk, 0xffffffffu);
     c->h_topc.assign((size_t)nq * topk, -1);
     c->last_pairs = 0;
-    if (nq == 0 || F->n == 0) return ORBX_OK;
+    if (nq == 0 || F->n == 0) {
+        if (q_staged) ctx_unstage(c);
+        return ORBX_OK;
+    }
     M_TRY(cudaSetDevice(c->device));
     // a device-resident frame (orbm_frame_upload / orbm_frame_from_device): keypoints, descriptors and the grid are
     // already there -- no upload of the frame, no grid build
@@ -566,7 +606,7 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
         M_TRY(ctx_h2d(c, c->t.p, F->desc, (size_t)F->n * 32));
     }
     if (qdesc) M_TRY(ctx_h2d(c, c->q.p, qdesc, (size_t)n_qdesc * 32));
-    M_TRY(ctx_h2d(c, c->aq.p, Q.data(), (size_t)nq * sizeof(orbm_area_query)));
+    if (!q_staged) M_TRY(ctx_h2d(c, c->aq.p, Qp, (size_t)nq * sizeof(orbm_area_query)));
     ORBM_PHASE("uploads");
     const orbx_keypoint* dk = RF ? (const orbx_keypoint*)RF->d_keys.p : (const orbx_keypoint*)c->kl.p;
     const uint8_t* dt = RF ? (const uint8_t*)RF->d_desc.p : (const uint8_t*)c->t.p;
@@ -595,7 +635,8 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
         const int cap = (int)std::min<size_t>({c->cand.cap / 4, c->dist.cap / 2, (size_t)INT_MAX});
         M_TRY(orbm_launch_area_fill(dk, gstart, gitems, F->min_x, F->min_y,
                                     F->grid_w_inv, F->grid_h_inv, (const orbm_area_query*)c->aq.p, nq,
-                                    (const int32_t*)c->rowptr.p, qdesc ? (const uint8_t*)c->q.p : dt,
+                                    (const int32_t*)c->rowptr.p,
+                                    d_qdesc ? d_qdesc : (qdesc ? (const uint8_t*)c->q.p : dt),
                                     dt, (int32_t*)c->cand.p, (uint16_t*)c->dist.p, cap, c->st));
         if (topk > 0)
             M_TRY(orbm_launch_csr_topk((const int32_t*)c->rowptr.p, (const int32_t*)c->cand.p, (const uint16_t*)c->dist.p,
@@ -643,6 +684,30 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
         break;
     }
     ORBM_PHASE("tail");
+    return ORBX_OK;
+}
+
+int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vector<orbm_area_query>& Q,
+                      const uint8_t* qdesc, int n_qdesc, int topk = 0) {
+    return device_candidates(c, F, Q.data(), (int)Q.size(), false, qdesc, n_qdesc, nullptr, topk);
+}
+
+// The queries of a window search, built in place in the pinned arena when they fit (else in `own`).
+struct QueryBuf {
+    orbm_area_query* q = nullptr;
+    bool staged = false;
+    std::vector<orbm_area_query> own;
+};
+int stage_queries(orbm_context* c, int n, QueryBuf* b) {
+    int r;
+    M_TRY(cudaSetDevice(c->device));
+    if ((r = c->aq.ensure((size_t)std::max(n, 1) * sizeof(orbm_area_query)))) return r;
+    b->q = (orbm_area_query*)ctx_stage(c, c->aq.p, (size_t)n * sizeof(orbm_area_query));
+    b->staged = b->q != nullptr;
+    if (!b->staged) {
+        b->own.resize(n);
+        b->q = b->own.data();
+    }
     return ORBX_OK;
 }
 
@@ -764,6 +829,9 @@ static int frame_finish(orbm_context* c, orbm_frame* f, int n) {
                                  c->st));
     M_TRY(cudaStreamSynchronize(c->st));
     c->frames[&f->view] = f;
+    f->bank.ctx = c;
+    f->bank.d = (const uint8_t*)f->d_desc.p;
+    f->bank.rows = n;
     return ORBX_OK;
 }
 
@@ -867,33 +935,54 @@ int orbm_frame_destroy(orbm_frame* f) {
     return ORBX_OK;
 }
 
-int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, const orbm_map_point* mps,
-                                     const uint8_t* mp_desc, int m, float th, int far_points, float th_far,
-                                     float nn_ratio, int32_t* kp_obs, int32_t* kp_match) {
+}  // extern "C"
+
+namespace {
+
+int bank_row(const orbm_bank* bank, const int32_t* rows, int i, int* row) {
+    *row = rows ? rows[i] : i;
+    if (bank && (*row < 0 || *row >= bank->rows)) {
+        ctx_unstage(bank->ctx);
+        return orbx_set_error(ORBX_E_BAD_ARG, "query %d: descriptor row %d outside the bank's %d rows", i, *row, bank->rows);
+    }
+    return ORBX_OK;
+}
+
+// mp_desc (host rows, one per map point) or bank + rows (device-resident rows named per map point; rows == null: row i)
+int search_by_projection_points_impl(orbm_context* c, const orbm_frame_view* F, const orbm_map_point* mps,
+                                     const uint8_t* mp_desc, const orbm_bank* bank, const int32_t* rows, int m, float th,
+                                     int far_points, float th_far, float nn_ratio, int32_t* kp_obs, int32_t* kp_match) {
     int rc = check_view(F);
     if (rc) return rc;
-    if (!c || m < 0 || (m && (!mps || !mp_desc)) || !kp_obs || !kp_match) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    if (!c || m < 0 || (m && (!mps || (!mp_desc && !bank))) || !kp_obs || !kp_match) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    if (bank && bank->ctx != c) return orbx_set_error(ORBX_E_BAD_ARG, "the bank belongs to another context");
     ORBM_PHASE_BEGIN("search_by_projection_points");
     for (int i = 0; i < F->n; ++i) kp_match[i] = -1;
     const bool bFactor = th != 1.0;
-    // pass 1: window queries (state independent); candidates + distances come from the device
-    std::vector<orbm_area_query> Q(m);
-    std::vector<float> rad(m, 0.f);
+    // pass 1: window queries (state independent), written straight into the pinned arena; candidates + distances come
+    // from the device
+    QueryBuf qb;
+    if ((rc = stage_queries(c, m, &qb))) return rc;
+    orbm_area_query* Q = qb.q;
+    std::vector<float>& rad = c->h_rad;
+    rad.resize(m);
     for (int i = 0; i < m; ++i) {
         const orbm_map_point& p = mps[i];
-        orbm_area_query& q = Q[i];
-        q = orbm_area_query{0.f, 0.f, 0.f, 0, 0, 0, i};
-        if (!p.in_view) continue;
-        if (far_points && p.depth > th_far) continue;
-        if (p.bad) continue;
-        if (p.level < 0 || p.level >= F->nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "map point %d: level out of range", i);
+        int row;
+        if ((rc = bank_row(bank, rows, i, &row))) return rc;
+        const bool live = p.in_view && !(far_points && p.depth > th_far) && !p.bad;
+        if (live && (p.level < 0 || p.level >= F->nlevels)) {
+            ctx_unstage(c);
+            return orbx_set_error(ORBX_E_BAD_ARG, "map point %d: level out of range", i);
+        }
         float r = ((double)p.view_cos > 0.998) ? 2.5f : 4.0f;  // RadiusByViewingCos, :220-226
         if (bFactor) r *= th;
-        rad[i] = r * F->scale_factors[p.level];
-        q = orbm_area_query{p.proj_x, p.proj_y, rad[i], p.level - 1, p.level, 1, i};
+        rad[i] = live ? r * F->scale_factors[p.level] : 0.f;
+        Q[i] = live ? orbm_area_query{p.proj_x, p.proj_y, rad[i], p.level - 1, p.level, 1, row}
+                    : orbm_area_query{0.f, 0.f, 0.f, 0, 0, 0, row};
     }
     ORBM_PHASE("queries");
-    if ((rc = device_candidates(c, F, Q, mp_desc, m))) return rc;
+    if ((rc = device_candidates(c, F, Q, m, qb.staged, bank ? nullptr : mp_desc, bank ? 0 : m, bank ? bank->d : nullptr))) return rc;
     ORBM_PHASE("device_candidates");
     const std::vector<int32_t>& row_ptr = c->h_rowptr;
     const std::vector<int32_t>& cand = c->h_cand;
@@ -949,32 +1038,45 @@ int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, 
     return nmatches;
 }
 
-int orbm_search_by_projection_frames(orbm_context* c, const orbm_frame_view* cur, const orbm_last_obs* last,
-                                     const uint8_t* last_desc, int n_last, float th, int forward, int backward,
-                                     float bf, int check_orientation, int32_t* kp_obs, int32_t* kp_match) {
+int search_by_projection_frames_impl(orbm_context* c, const orbm_frame_view* cur, const orbm_last_obs* last,
+                                     const uint8_t* last_desc, const orbm_bank* bank, const int32_t* rows, int n_last,
+                                     float th, int forward, int backward, float bf, int check_orientation,
+                                     int32_t* kp_obs, int32_t* kp_match) {
     int rc = check_view(cur);
     if (rc) return rc;
-    if (!c || n_last < 0 || (n_last && (!last || !last_desc)) || !kp_obs || !kp_match) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    if (!c || n_last < 0 || (n_last && (!last || (!last_desc && !bank))) || !kp_obs || !kp_match) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    if (bank && bank->ctx != c) return orbx_set_error(ORBX_E_BAD_ARG, "the bank belongs to another context");
     for (int i = 0; i < cur->n; ++i) kp_match[i] = -1;
     std::vector<int> rotHist[ORBM_HISTO_LENGTH];
     const float factor = 1.0f / ORBM_HISTO_LENGTH;
-    std::vector<orbm_area_query> Q(n_last);
-    std::vector<float> rad(n_last, 0.f);
+    QueryBuf qb;
+    if ((rc = stage_queries(c, n_last, &qb))) return rc;
+    orbm_area_query* Q = qb.q;
+    std::vector<float>& rad = c->h_rad;
+    rad.resize(n_last);
     for (int i = 0; i < n_last; ++i) {
         const orbm_last_obs& o = last[i];
+        int row;
+        if ((rc = bank_row(bank, rows, i, &row))) return rc;
         orbm_area_query& q = Q[i];
-        q = orbm_area_query{0.f, 0.f, 0.f, 0, 0, 0, i};
+        q = orbm_area_query{0.f, 0.f, 0.f, 0, 0, 0, row};
+        rad[i] = 0.f;
         if (!o.valid) continue;
         if (o.inv_z < 0) continue;
         if (o.u < cur->min_x || o.u > cur->max_x) continue;
         if (o.v < cur->min_y || o.v > cur->max_y) continue;
-        if (o.octave < 0 || o.octave >= cur->nlevels) return orbx_set_error(ORBX_E_BAD_ARG, "observation %d: octave out of range", i);
+        if (o.octave < 0 || o.octave >= cur->nlevels) {
+            ctx_unstage(c);
+            return orbx_set_error(ORBX_E_BAD_ARG, "observation %d: octave out of range", i);
+        }
         rad[i] = th * cur->scale_factors[o.octave];
-        if (forward) q = orbm_area_query{o.u, o.v, rad[i], o.octave, -1, 1, i};
-        else if (backward) q = orbm_area_query{o.u, o.v, rad[i], 0, o.octave, 1, i};
-        else q = orbm_area_query{o.u, o.v, rad[i], o.octave - 1, o.octave + 1, 1, i};
+        if (forward) q = orbm_area_query{o.u, o.v, rad[i], o.octave, -1, 1, row};
+        else if (backward) q = orbm_area_query{o.u, o.v, rad[i], 0, o.octave, 1, row};
+        else q = orbm_area_query{o.u, o.v, rad[i], o.octave - 1, o.octave + 1, 1, row};
     }
-    if ((rc = device_candidates(c, cur, Q, last_desc, n_last))) return rc;
+    if ((rc = device_candidates(c, cur, Q, n_last, qb.staged, bank ? nullptr : last_desc, bank ? 0 : n_last,
+                                bank ? bank->d : nullptr)))
+        return rc;
     const std::vector<int32_t>& row_ptr = c->h_rowptr;
     const std::vector<int32_t>& cand = c->h_cand;
     int nmatches = 0;
@@ -1026,6 +1128,88 @@ int orbm_search_by_projection_frames(orbm_context* c, const orbm_frame_view* cur
     return nmatches;
 }
 
+}  // namespace
+
+extern "C" {
+
+int orbm_search_by_projection_points(orbm_context* c, const orbm_frame_view* F, const orbm_map_point* mps,
+                                     const uint8_t* mp_desc, int m, float th, int far_points, float th_far,
+                                     float nn_ratio, int32_t* kp_obs, int32_t* kp_match) {
+    if (m && !mp_desc) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    return search_by_projection_points_impl(c, F, mps, mp_desc, nullptr, nullptr, m, th, far_points, th_far, nn_ratio,
+                                            kp_obs, kp_match);
+}
+
+int orbm_search_by_projection_points_bank(orbm_context* c, const orbm_frame_view* F, const orbm_map_point* mps,
+                                          const orbm_bank* bank, const int32_t* rows, int m, float th, int far_points,
+                                          float th_far, float nn_ratio, int32_t* kp_obs, int32_t* kp_match) {
+    if (!bank) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    return search_by_projection_points_impl(c, F, mps, nullptr, bank, rows, m, th, far_points, th_far, nn_ratio, kp_obs,
+                                            kp_match);
+}
+
+int orbm_search_by_projection_frames(orbm_context* c, const orbm_frame_view* cur, const orbm_last_obs* last,
+                                     const uint8_t* last_desc, int n_last, float th, int forward, int backward,
+                                     float bf, int check_orientation, int32_t* kp_obs, int32_t* kp_match) {
+    if (n_last && !last_desc) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    return search_by_projection_frames_impl(c, cur, last, last_desc, nullptr, nullptr, n_last, th, forward, backward, bf,
+                                            check_orientation, kp_obs, kp_match);
+}
+
+int orbm_search_by_projection_frames_bank(orbm_context* c, const orbm_frame_view* cur, const orbm_last_obs* last,
+                                          const orbm_bank* bank, const int32_t* rows, int n_last, float th, int forward,
+                                          int backward, float bf, int check_orientation, int32_t* kp_obs,
+                                          int32_t* kp_match) {
+    if (!bank) return orbx_set_error(ORBX_E_BAD_ARG, "null argument");
+    return search_by_projection_frames_impl(c, cur, last, nullptr, bank, rows, n_last, th, forward, backward, bf,
+                                            check_orientation, kp_obs, kp_match);
+}
+
+// ---- descriptor banks ---------------------------------------------------------------------------------
+int orbm_bank_create(orbm_context* c, int capacity_rows, orbm_bank** out) {
+    if (!c || !out || capacity_rows < 1) return orbx_set_error(ORBX_E_BAD_ARG, "bad argument");
+    *out = nullptr;
+    M_TRY(cudaSetDevice(c->device));
+    orbm_bank* b = new orbm_bank();
+    b->ctx = c;
+    int rc = b->buf.ensure((size_t)capacity_rows * 32);
+    if (rc) {
+        delete b;
+        return rc;
+    }
+    b->d = (const uint8_t*)b->buf.p;
+    b->rows = capacity_rows;
+    *out = b;
+    return ORBX_OK;
+}
+
+int orbm_bank_write(orbm_bank* b, int first_row, int n, const uint8_t* desc) {
+    if (!b || !b->buf.p) return orbx_set_error(ORBX_E_BAD_ARG, "not a writable bank");
+    if (first_row < 0 || n < 0 || first_row > b->rows - n || (n && !desc)) return orbx_set_error(ORBX_E_BAD_ARG, "rows outside the bank");
+    if (n == 0) return ORBX_OK;
+    M_TRY(cudaSetDevice(b->ctx->device));
+    // on the context's stream, so that it is ordered with the searches; returns when the rows are in place
+    M_TRY(cudaMemcpyAsync((uint8_t*)b->buf.p + (size_t)first_row * 32, desc, (size_t)n * 32, cudaMemcpyHostToDevice, b->ctx->st));
+    M_TRY(cudaStreamSynchronize(b->ctx->st));
+    return ORBX_OK;
+}
+
+int orbm_bank_rows(const orbm_bank* b) { return b ? b->rows : orbx_set_error(ORBX_E_BAD_ARG, "null argument"); }
+
+int orbm_bank_destroy(orbm_bank* b) {
+    if (!b) return ORBX_OK;
+    if (!b->buf.p) return orbx_set_error(ORBX_E_BAD_ARG, "a frame's bank goes with its frame (orbm_frame_destroy)");
+    cudaSetDevice(b->ctx->device);
+    cudaStreamSynchronize(b->ctx->st);
+    b->buf.release();
+    delete b;
+    return ORBX_OK;
+}
+
+const orbm_bank* orbm_frame_bank(const orbm_frame* f) { return f ? &f->bank : nullptr; }
+
+}  // extern "C"
+
 namespace {
 
 // the right camera's half as a frame view over the same grid geometry (PosInGrid uses the frame's
@@ -1056,6 +1240,8 @@ void take_csr(orbm_context* c, Csr& o) {
 }
 
 }  // namespace
+
+extern "C" {
 
 int orbm_search_by_projection_points_stereo(orbm_context* c, const orbm_frame_view* F, const orbm_frame_right* R,
                                             const orbm_map_point* mps, const orbm_map_point_right* mps_r,

@@ -91,9 +91,41 @@ class ResidentFrame:
         self.u_right = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
         check(self.lib.orbm_frame_set_u_right(self.h, None if self.u_right is None else self.u_right.ctypes.data))
 
+    def bank(self) -> "DescriptorBank":
+        """This frame's descriptors as a bank (row = keypoint index)."""
+        return DescriptorBank(self._m, _view_of=self)
+
     def close(self):
         if getattr(self, "h", None) and self._m.ctx:
             self.lib.orbm_frame_destroy(self.h)
+        self.h = None
+
+
+class DescriptorBank:
+    """orbm_bank: 32-byte descriptor rows kept on the matcher's device (the map points' mDescriptor, one row per
+    MapPoint; or a resident frame's descriptors).  Pass it where a search takes descriptors, with `rows`."""
+
+    def __init__(self, matcher: "ORBmatcher", capacity: int = 0, *, _view_of: "ResidentFrame" = None):
+        self.lib, self._m, self._owner = matcher.lib, matcher, _view_of
+        if _view_of is not None:
+            self.h = C.c_void_p(self.lib.orbm_frame_bank(_view_of.h))
+            self._owned = False
+        else:
+            self.h = C.c_void_p()
+            check(self.lib.orbm_bank_create(matcher.ctx, int(capacity), C.byref(self.h)))
+            self._owned = True
+
+    @property
+    def rows(self) -> int:
+        return int(self.lib.orbm_bank_rows(self.h))
+
+    def write(self, first_row: int, desc):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        check(self.lib.orbm_bank_write(self.h, int(first_row), len(d), d.ctypes.data))
+
+    def close(self):
+        if getattr(self, "_owned", False) and self.h and self._m.ctx:
+            self.lib.orbm_bank_destroy(self.h)
         self.h = None
 
 
@@ -237,32 +269,47 @@ class ORBmatcher:
 
     # ---- layer 2 ------------------------------------------------------------------------------------
     def SearchByProjection(self, F: Frame, map_points, mp_desc, th=1.0, bFarPoints=False, thFarPoints=50.0,
-                           kp_obs=None):
+                           kp_obs=None, rows=None):
         """SearchByProjection(Frame&, vector<MapPoint*>&, th, bFarPoints, thFarPoints).
-        Returns (nmatches, kp_match[N], kp_obs[N])."""
+        mp_desc: the map points' descriptors [M, 32], or a DescriptorBank holding them on the device (rows = the bank
+        row of each map point, None for row i).  Returns (nmatches, kp_match[N], kp_obs[N])."""
         mps = np.ascontiguousarray(map_points, MAP_POINT_DTYPE)
-        mp_desc = np.ascontiguousarray(mp_desc, np.uint8).reshape(-1, 32)
         obs = np.full(F.N, -1, np.int32) if kp_obs is None else np.ascontiguousarray(kp_obs, np.int32).copy()
         match = np.zeros(F.N, np.int32)
         v = F.view()
-        n = self.lib.orbm_search_by_projection_points(self.ctx, C.byref(v), mps.ctypes.data, mp_desc.ctypes.data,
-                                                      len(mps), th, int(bFarPoints), thFarPoints, self.mfNNratio,
-                                                      obs.ctypes.data, match.ctypes.data)
+        if isinstance(mp_desc, DescriptorBank):
+            r = None if rows is None else np.ascontiguousarray(rows, np.int32)
+            n = self.lib.orbm_search_by_projection_points_bank(
+                self.ctx, C.byref(v), mps.ctypes.data, mp_desc.h, None if r is None else r.ctypes.data, len(mps), th,
+                int(bFarPoints), thFarPoints, self.mfNNratio, obs.ctypes.data, match.ctypes.data)
+        else:
+            mp_desc = np.ascontiguousarray(mp_desc, np.uint8).reshape(-1, 32)
+            n = self.lib.orbm_search_by_projection_points(self.ctx, C.byref(v), mps.ctypes.data, mp_desc.ctypes.data,
+                                                          len(mps), th, int(bFarPoints), thFarPoints, self.mfNNratio,
+                                                          obs.ctypes.data, match.ctypes.data)
         if n < 0:
             check(n)
         return n, match, obs
 
     def SearchByProjectionFrames(self, CurrentFrame: Frame, last_obs, last_desc, th, bForward=False,
-                                 bBackward=False, mbf=0.0, kp_obs=None):
-        """SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono)."""
+                                 bBackward=False, mbf=0.0, kp_obs=None, rows=None):
+        """SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono).
+        last_desc: one descriptor per observation [n_last, 32] (its map point's), or a DescriptorBank holding the map
+        points' descriptors with rows = the bank row of each observation's map point."""
         lo = np.ascontiguousarray(last_obs, LAST_OBS_DTYPE)
-        last_desc = np.ascontiguousarray(last_desc, np.uint8).reshape(-1, 32)
         obs = np.full(CurrentFrame.N, -1, np.int32) if kp_obs is None else np.ascontiguousarray(kp_obs, np.int32).copy()
         match = np.zeros(CurrentFrame.N, np.int32)
         v = CurrentFrame.view()
-        n = self.lib.orbm_search_by_projection_frames(self.ctx, C.byref(v), lo.ctypes.data, last_desc.ctypes.data,
-                                                      len(lo), th, int(bForward), int(bBackward), mbf,
-                                                      int(self.mbCheckOrientation), obs.ctypes.data, match.ctypes.data)
+        if isinstance(last_desc, DescriptorBank):
+            r = None if rows is None else np.ascontiguousarray(rows, np.int32)
+            n = self.lib.orbm_search_by_projection_frames_bank(
+                self.ctx, C.byref(v), lo.ctypes.data, last_desc.h, None if r is None else r.ctypes.data, len(lo), th,
+                int(bForward), int(bBackward), mbf, int(self.mbCheckOrientation), obs.ctypes.data, match.ctypes.data)
+        else:
+            last_desc = np.ascontiguousarray(last_desc, np.uint8).reshape(-1, 32)
+            n = self.lib.orbm_search_by_projection_frames(self.ctx, C.byref(v), lo.ctypes.data, last_desc.ctypes.data,
+                                                          len(lo), th, int(bForward), int(bBackward), mbf,
+                                                          int(self.mbCheckOrientation), obs.ctypes.data, match.ctypes.data)
         if n < 0:
             check(n)
         return n, match, obs

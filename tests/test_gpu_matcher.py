@@ -749,6 +749,93 @@ def test_resident_frames_match_plain_frames(matcher, mo):
         RF.close()
 
 
+def test_descriptor_banks_match_host_descriptors(matcher, mo):
+    """orbm_bank: the map points' descriptors kept on the device and named by row (pMP->GetDescriptor() at
+    src/ORBmatcher.cc:80 / :2031 becomes a row index).  Both bank searches, on a plain and on a resident frame, with
+    rows in a shuffled bank, row i (rows = NULL) and a frame's own bank, equal the reference-held oracle fed the
+    descriptors themselves; bad rows and foreign banks are refused."""
+    from orb_slam3_mac_b200._lib import OrbxError
+    from orb_slam3_mac_b200.matcher import DescriptorBank, ORBmatcher, ResidentFrame
+    from tests.golden import match_cases as mc
+    (ka, da), (kb, db) = mc.frames(11, n=1600)
+    rng = np.random.default_rng(21)
+    ur = np.where(rng.random(len(kb)) < 0.5, kb["x"] - rng.uniform(1, 40, len(kb)), -1.0).astype(np.float32)
+    F = _frame(kb, db, 752, 480, u_right=ur)
+    RF = ResidentFrame(matcher, F)
+    RF.set_u_right(ur)
+    mps, md = S.map_points_from_frame(ka, da, 752, 480, 5000, 4)
+    lo, ld = S.last_frame_obs(ka, da, 4)
+    obs0 = np.where(rng.random(len(kb)) < 0.2, rng.integers(0, 3, len(kb)), -1).astype(np.int32)
+    # one bank for every map point of the "map": the search's points sit at shuffled rows of it
+    cap = len(md) + len(ld) + 100
+    bank = DescriptorBank(matcher, cap)
+    rows_p = rng.permutation(cap)[:len(md)].astype(np.int32)
+    left = np.setdiff1d(np.arange(cap), rows_p)
+    rows_l = rng.permutation(left)[:len(ld)].astype(np.int32)
+    try:
+        assert bank.rows == cap
+        all_rows = np.zeros((cap, 32), np.uint8)
+        all_rows[rows_p] = md
+        all_rows[rows_l] = ld
+        bank.write(0, all_rows[:1000])      # written in pieces, as map points come and change
+        bank.write(1000, all_rows[1000:])
+        want_p = mo.search_by_projection_points(F, mps, md, 3.0, True, 30.0, 0.8, kp_obs=obs0)
+        want_f = mo.search_by_projection_frames(F, lo, ld, 7.0, False, False, 40.0, True, kp_obs=obs0)
+        assert want_p[0] > 100 and want_f[0] > 100
+        for frame in (F, RF, RF):
+            got = matcher.SearchByProjection(frame, mps, bank, 3.0, True, 30.0, kp_obs=obs0, rows=rows_p)
+            assert got[0] == want_p[0] and np.array_equal(got[1], want_p[1]) and np.array_equal(got[2], want_p[2])
+            got = matcher.SearchByProjectionFrames(frame, lo, bank, 7.0, False, False, 40.0, kp_obs=obs0, rows=rows_l)
+            assert got[0] == want_f[0] and np.array_equal(got[1], want_f[1]) and np.array_equal(got[2], want_f[2])
+        # a map point's descriptor changes (ComputeDistinctiveDescriptors): one row rewritten, the next search sees it
+        md2 = md.copy()
+        md2[7] = ~md2[7]
+        bank.write(int(rows_p[7]), md2[7:8])
+        got = matcher.SearchByProjection(RF, mps, bank, 3.0, True, 30.0, kp_obs=obs0, rows=rows_p)
+        want2 = mo.search_by_projection_points(F, mps, md2, 3.0, True, 30.0, 0.8, kp_obs=obs0)
+        assert got[0] == want2[0] and np.array_equal(got[1], want2[1])
+        # rows = NULL: row i
+        b2 = DescriptorBank(matcher, len(md))
+        b2.write(0, md)
+        got = matcher.SearchByProjection(RF, mps, b2, 1.0, False, 30.0)
+        want = mo.search_by_projection_points(F, mps, md, 1.0, False, 30.0, 0.8)
+        assert got[0] == want[0] and np.array_equal(got[1], want[1])
+        b2.close()
+        # a resident frame's own descriptors as a bank: map points created from its keypoints (src/MapPoint.cc:109)
+        RA = ResidentFrame(matcher, _frame(ka, da, 752, 480))
+        sel = rng.permutation(len(ka))[:900].astype(np.int32)
+        mps3, _ = S.map_points_from_frame(ka[sel], da[sel], 752, 480, 900, 6)
+        # (map_points_from_frame permutes and flips bits: the test only needs SOME points whose descriptors are rows)
+        got = matcher.SearchByProjection(RF, mps3, RA.bank(), 3.0, False, 30.0, rows=sel)
+        want = mo.search_by_projection_points(F, mps3, da[sel], 3.0, False, 30.0, 0.8)
+        assert got[0] == want[0] and np.array_equal(got[1], want[1])
+        # refusals
+        bad = rows_p.copy()
+        bad[3] = cap
+        with pytest.raises(OrbxError):
+            matcher.SearchByProjection(RF, mps, bank, 3.0, True, 30.0, rows=bad)
+        bad[3] = -1
+        with pytest.raises(OrbxError):
+            matcher.SearchByProjectionFrames(RF, lo, bank, 7.0, rows=bad[:len(lo)])
+        with pytest.raises(OrbxError):
+            bank.write(cap - 1, md[:2])
+        other = ORBmatcher(0.8, True, 0)
+        try:
+            with pytest.raises(OrbxError):
+                other.SearchByProjection(F, mps, bank, 3.0, True, 30.0, rows=rows_p)
+        finally:
+            other.close()
+        # the arena is clean after the refusals: the next search is right
+        got = matcher.SearchByProjection(RF, mps, bank, 3.0, True, 30.0, kp_obs=obs0, rows=rows_p)
+        assert got[0] == want2[0] and np.array_equal(got[1], want2[1])
+        got = matcher.SearchByProjection(RF, mps, md2, 3.0, True, 30.0, kp_obs=obs0)
+        assert got[0] == want2[0] and np.array_equal(got[1], want2[1])
+        RA.close()
+    finally:
+        bank.close()
+        RF.close()
+
+
 def test_frame_from_device_undistorts_like_opencv(matcher, mo, oracle_libs):
     """orbm_frame_from_device: extractor results that never leave the device -> Frame::UndistortKeyPoints +
     ComputeImageBounds (src/Frame.cc:738-800) on the device -> grid -> search.  mvKeysUn and the bounds are
