@@ -19,6 +19,8 @@
 // (band, column chunk) so that lanes are only idle at a level's right edge.
 // k_resize_level (one thread per 4 pixels of ONE row, byte loads) is kept for scale factors
 // whose source step exceeds 3 columns.
+#include <cstdlib>
+
 #include "orbx_device.cuh"
 
 __global__ void __launch_bounds__(256)
@@ -331,38 +333,102 @@ k_resize_rows_async(const __grid_constant__ RzArgs A, int n8) {
     else rz_walk<4>(A, band, n8 * 256 + (wx - n8) * 128, ring);
 }
 
+// ---- the coarse levels of a SMALL batch in one launch (single-frame latency path) ----------------------------------
+// For one frame the per-level launches of levels 4..7 are four dependent kernels of ~5 us each that are almost all
+// launch + first-load latency (211 k pixels together).  k_resize_tail runs them as phases of ONE launch: a thread-block
+// cluster per frame (RZ_TAIL_CLUSTER CTAs; the cluster's warps share a level's (band, column chunk) units), a
+// cluster barrier between levels.  A level is written to HBM/L2 as before and read back by the next phase through
+// cp.async.cg (L2, never a stale L1 line), after __threadfence() + barrier.cluster release/acquire.
+// MEASURED AND LEFT OFF (bit-exact, numbers in profiles/README.md): the single-frame p50 gets WORSE
+// (C1 102 -> 109 us from level 4, 129 us from level 2) -- eight SMs per frame instead of every SM per level, and the
+// FAST / quadtree branches of levels 4..7 all wait for the end of the launch instead of starting level by level.
+#ifndef RZ_TAIL_WARPS
+#define RZ_TAIL_WARPS 16
+#endif
+#ifndef RZ_TAIL_CLUSTER
+#define RZ_TAIL_CLUSTER 8
+#endif
+#define RZ_TAIL_MAX 6
+struct RzTail {
+    RzArgs a[RZ_TAIL_MAX];
+    int n8[RZ_TAIL_MAX];
+    int n;
+};
+
+__global__ void __launch_bounds__(RZ_TAIL_WARPS * 32)
+k_resize_tail(const __grid_constant__ RzTail T) {
+    __shared__ __align__(16) uint8_t ring_all[RZ_TAIL_WARPS * RZ_DEPTH * RzCfg<8>::SLOT_BYTES];
+    const int warp = threadIdx.x >> 5;
+    uint8_t* ring = ring_all + warp * (RZ_DEPTH * RzCfg<8>::SLOT_BYTES);
+    const int stride = gridDim.x * RZ_TAIL_WARPS;   // gridDim.x = the cluster's CTAs, blockIdx.y = frame
+    for (int p = 0; p < T.n; ++p) {
+        const RzArgs& A = T.a[p];
+        const int n8 = T.n8[p];
+        const int total = A.warps_x * A.nbands;
+        for (int gw = blockIdx.x * RZ_TAIL_WARPS + warp; gw < total; gw += stride) {
+            const int band = gw / A.warps_x, wx = gw - band * A.warps_x;
+            if (wx < n8) rz_walk<8>(A, band, wx * 256, ring);
+            else rz_walk<4>(A, band, n8 * 256 + (wx - n8) * 128, ring);
+            __syncwarp();   // every lane is done with the ring before the next unit stages into it
+        }
+        if (p + 1 < T.n) {
+            __threadfence();
+            asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+        }
+    }
+}
+
 #ifndef RZ_MIN_WARPS
 #define RZ_MIN_WARPS (148 * 16)
 #endif
+// Levels [from, nlevels) in one k_resize_tail launch when the batch is small and every one of them qualifies for the
+// cp.async kernel; returns the first level it did NOT take (nlevels when it ran, `from` when it did not).
+static bool rz_args(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes, int l, RzArgs* out, int* n8_out, bool* async_out);
+// OFF by default (measured slower, see the comment above): ORBX_TAIL_FROM=<first level, >= 2> switches it on for
+// launches of at most sms / cluster frames, ORBX_TAIL_BATCH=1 for every batch, ORBX_TAIL_CLUSTER=1|2|4|8 sets the
+// cluster size (developer A/B, tools/tail_ab.sh).
+static int rz_env(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+static int rz_tail_from() { static const int v = rz_env("ORBX_TAIL_FROM", 0); return v; }
+static int rz_tail_batch() { static const int v = rz_env("ORBX_TAIL_BATCH", 0); return v; }
+static int rz_tail_cluster() {
+    static const int v = [] { const int c = rz_env("ORBX_TAIL_CLUSTER", RZ_TAIL_CLUSTER); return (c == 1 || c == 2 || c == 4 || c == 8) ? c : RZ_TAIL_CLUSTER; }();
+    return v;
+}
+
 void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes, cudaStream_t st, int* launches,
                          cudaEvent_t* level_done) {
-    for (int l = 1; l < P.nlevels; ++l) {
+    // small batch: the coarse levels as phases of one cluster launch
+    int tail = P.nlevels;
+    RzTail T;
+    T.n = 0;
+    {
+        const int from = rz_tail_from();
+        int dev = 0, sms = 148;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+            cudaGetLastError();
+            sms = 148;
+        }
+        if (from >= 2 && from < P.nlevels && P.nlevels - from <= RZ_TAIL_MAX && (rz_tail_batch() || nframes * rz_tail_cluster() <= sms)) {
+            bool ok = true;
+            for (int l = from; l < P.nlevels && ok; ++l) {
+                bool async_ok = false;
+                ok = rz_args(P, src, pyr, nframes, l, &T.a[l - from], &T.n8[l - from], &async_ok) && async_ok;
+            }
+            if (ok) {
+                tail = from;
+                T.n = P.nlevels - from;
+            }
+        }
+    }
+    for (int l = 1; l < tail; ++l) {
         const OrbxLevel& D = P.lvl[l];
-        const OrbxLevel& S = P.lvl[l - 1];
-        if (D.x_step_max <= 3 && D.y_monotone && S.w >= 8 && S.h >= 2) {
-            RzArgs A;
-            A.src = l == 1 ? src.img0 : pyr + S.off;
-            A.src_fstride = l == 1 ? src.stride0 : P.frame_stride;
-            A.spitch = l == 1 ? src.pitch0 : S.pitch;
-            A.dst = pyr + D.off;
-            A.dst_fstride = P.frame_stride;
-            A.dpitch = D.pitch;
-            A.xofs = D.xofs;
-            A.xa = reinterpret_cast<const uint32_t*>(D.xa);
-            A.ytab = D.ytab;
-            A.sw = S.w; A.sh = S.h; A.dw = D.w; A.dh = D.h;
-            // output rows per warp: RZ_ROWS when the launch fills the GPU anyway; small batches take
-            // shorter bands so that a level of one frame still spreads over the SMs (latency path)
-            A.rows = RZ_ROWS;
-            while (A.rows > 2 && (long long)nframes * ((D.w + 255) / 256) * ((D.h + A.rows - 1) / A.rows) < RZ_MIN_WARPS)
-                A.rows >>= 1;
-            A.nbands = (D.h + A.rows - 1) / A.rows;
-            const bool aligned = ((uintptr_t)A.src % 16 == 0) && (A.spitch % 16 == 0) && (A.src_fstride % 16 == 0);
-            const double ratio = (double)S.w / D.w;
-            const bool async_ok = aligned && D.x_step_max <= 2 && ratio <= 1.7;
-            // 8 columns per thread need the 384-byte slot: 256 * ratio + 32 bytes
-            const int n8 = (async_ok && ratio <= 1.35) ? D.w / 256 : 0;
-            A.warps_x = async_ok ? n8 + (D.w - 256 * n8 + 127) / 128 : (D.w + 127) / 128;
+        RzArgs A;
+        int n8 = 0;
+        bool async_ok = false;
+        if (rz_args(P, src, pyr, nframes, l, &A, &n8, &async_ok)) {
             dim3 grid((A.warps_x * A.nbands + 7) / 8, nframes);
             if (async_ok)
                 k_resize_rows_async<<<grid, 256, 0, st>>>(A, n8);
@@ -376,4 +442,57 @@ void orbx_launch_pyramid(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, in
         ++*launches;
         if (level_done) cudaEventRecord(level_done[l], st);   // level l is complete (forked latency graph)
     }
+    if (T.n) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(rz_tail_cluster(), nframes);
+        cfg.blockDim = dim3(RZ_TAIL_WARPS * 32);
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = rz_tail_cluster();
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        cudaLaunchKernelEx(&cfg, k_resize_tail, T);
+        ++*launches;
+        if (level_done)
+            for (int l = tail; l < P.nlevels; ++l) cudaEventRecord(level_done[l], st);
+    }
+}
+
+// The (source level -> level l) step as k_resize_rows / k_resize_rows_async arguments; false when the level needs
+// k_resize_level (source step above 3 columns, non-monotone rows, tiny source).
+static bool rz_args(const OrbxPlan& P, const OrbxSrc& src, uint8_t* pyr, int nframes, int l, RzArgs* out, int* n8_out,
+                    bool* async_out) {
+    const OrbxLevel& D = P.lvl[l];
+    const OrbxLevel& S = P.lvl[l - 1];
+    if (!(D.x_step_max <= 3 && D.y_monotone && S.w >= 8 && S.h >= 2)) return false;
+    RzArgs A;
+    A.src = l == 1 ? src.img0 : pyr + S.off;
+    A.src_fstride = l == 1 ? src.stride0 : P.frame_stride;
+    A.spitch = l == 1 ? src.pitch0 : S.pitch;
+    A.dst = pyr + D.off;
+    A.dst_fstride = P.frame_stride;
+    A.dpitch = D.pitch;
+    A.xofs = D.xofs;
+    A.xa = reinterpret_cast<const uint32_t*>(D.xa);
+    A.ytab = D.ytab;
+    A.sw = S.w; A.sh = S.h; A.dw = D.w; A.dh = D.h;
+    // output rows per warp: RZ_ROWS when the launch fills the GPU anyway; small batches take
+    // shorter bands so that a level of one frame still spreads over the SMs (latency path)
+    A.rows = RZ_ROWS;
+    while (A.rows > 2 && (long long)nframes * ((D.w + 255) / 256) * ((D.h + A.rows - 1) / A.rows) < RZ_MIN_WARPS)
+        A.rows >>= 1;
+    A.nbands = (D.h + A.rows - 1) / A.rows;
+    const bool aligned = ((uintptr_t)A.src % 16 == 0) && (A.spitch % 16 == 0) && (A.src_fstride % 16 == 0);
+    const double ratio = (double)S.w / D.w;
+    const bool async_ok = aligned && D.x_step_max <= 2 && ratio <= 1.7;
+    // 8 columns per thread need the 384-byte slot: 256 * ratio + 32 bytes
+    const int n8 = (async_ok && ratio <= 1.35) ? D.w / 256 : 0;
+    A.warps_x = async_ok ? n8 + (D.w - 256 * n8 + 127) / 128 : (D.w + 127) / 128;
+    *out = A;
+    *n8_out = n8;
+    *async_out = async_ok;
+    return true;
 }
