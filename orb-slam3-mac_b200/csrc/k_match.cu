@@ -346,17 +346,15 @@ k_grid_build(const orbx_keypoint* __restrict__ keys, int n, OrbmGrid G, int32_t*
     grid_sort_cells(items, cnt, tid, blockDim.x);
 }
 
+// One window query by one warp: GetFeaturesInArea (src/Frame.cc:645-714) over the 64 x 48 grid.  FILL: candidates (in
+// the reference's order) and their Hamming distances go to cand / dist from position `base`; else they are counted.
 template <bool FILL>
-__global__ void __launch_bounds__(256)
-k_area(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start,
-       const int32_t* __restrict__ items, OrbmGrid G, const orbm_area_query* __restrict__ Q, int nq,
-       int32_t* __restrict__ cnt, const int32_t* __restrict__ row_ptr, const uint4* __restrict__ qdesc,
-       const uint4* __restrict__ tdesc, int32_t* __restrict__ cand, uint16_t* __restrict__ dist, int cap) {
-    const int qi = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
-    if (qi >= nq) return;
+__device__ __forceinline__ int area_walk(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start,
+                                         const int32_t* __restrict__ items, const OrbmGrid& G, const orbm_area_query& q,
+                                         int base, const uint4* __restrict__ qdesc, const uint4* __restrict__ tdesc,
+                                         int32_t* __restrict__ cand, uint16_t* __restrict__ dist, int cap) {
     const int lane = orbx_lane();
     const uint32_t lt = orbx_lanemask_lt();
-    const orbm_area_query q = Q[qi];
     int total = 0;
     const float r = q.r;
     // GetFeaturesInArea :652-676
@@ -366,22 +364,40 @@ k_area(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start
     const int r1 = min(ORBM_GRID_ROWS - 1, (int)ceilf((q.y - G.min_y + r) * G.h_inv));
     if (q.valid && c0 < ORBM_GRID_COLS && c1 >= 0 && r0 < ORBM_GRID_ROWS && r1 >= 0) {
         const bool check_levels = (q.min_level > 0) || (q.max_level >= 0);
-        const int base = FILL ? row_ptr[qi] : 0;
         uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
         if (FILL) {
             a0 = __ldg(qdesc + 2 * (size_t)q.desc_row);
             a1 = __ldg(qdesc + 2 * (size_t)q.desc_row + 1);
         }
-        for (int ix = c0; ix <= c1; ++ix) {
-            if (r1 < r0) break;
-            const int s = __ldg(start + ix * ORBM_GRID_ROWS + r0);
-            const int e = __ldg(start + ix * ORBM_GRID_ROWS + r1 + 1);
-            for (int k0 = s; k0 < e; k0 += 32) {
-                const int k = k0 + lane;
+        // A column of the window is ONE contiguous range of the cell-sorted item array.  Lane i fetches the range of
+        // column cb + i, a warp scan concatenates the ranges, and the items are then walked 32 at a time ACROSS the
+        // columns (item j's column by a 5-step search of the scan): a window of two or three short columns is one
+        // round of dependent loads (range -> item -> keypoint) instead of one per column.  Order = column, row, cell
+        // order = the reference's (:678-707).
+        for (int cb = c0; cb <= c1 && r0 <= r1; cb += 32) {
+            const int ix = cb + lane;
+            int s = 0, len = 0;
+            if (ix <= c1) {
+                s = __ldg(start + ix * ORBM_GRID_ROWS + r0);
+                len = __ldg(start + ix * ORBM_GRID_ROWS + r1 + 1) - s;
+            }
+            const int incl = (int)warp_incl_scan((uint32_t)len);
+            const int T = __shfl_sync(ORBX_FULL, incl, 31);
+            for (int j0 = 0; j0 < T; j0 += 32) {
+                const int j = j0 + lane;
+                int lo = 0, hi = 31;   // smallest lane whose inclusive count exceeds j
+#pragma unroll
+                for (int step = 0; step < 5; ++step) {
+                    const int mid = (lo + hi) >> 1;
+                    const int v = __shfl_sync(ORBX_FULL, incl, mid);
+                    if (v > j) hi = mid; else lo = mid + 1;
+                }
+                const int s_col = __shfl_sync(ORBX_FULL, s, lo), incl_col = __shfl_sync(ORBX_FULL, incl, lo);
+                const int len_col = __shfl_sync(ORBX_FULL, len, lo);
                 bool ok = false;
                 int idx = 0;
-                if (k < e) {
-                    idx = __ldg(items + k);
+                if (j < T) {
+                    idx = __ldg(items + s_col + (j - (incl_col - len_col)));
                     const orbx_keypoint kp = keys[idx];
                     ok = true;
                     if (check_levels) {
@@ -401,7 +417,46 @@ k_area(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start
             }
         }
     }
-    if (!FILL && lane == 0) cnt[qi] = total;
+    return total;
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(256)
+k_area(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start,
+       const int32_t* __restrict__ items, OrbmGrid G, const orbm_area_query* __restrict__ Q, int nq,
+       int32_t* __restrict__ cnt, const int32_t* __restrict__ row_ptr, const uint4* __restrict__ qdesc,
+       const uint4* __restrict__ tdesc, int32_t* __restrict__ cand, uint16_t* __restrict__ dist, int cap) {
+    const int qi = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
+    if (qi >= nq) return;
+    const orbm_area_query q = Q[qi];
+    const int total = area_walk<FILL>(keys, start, items, G, q, FILL ? row_ptr[qi] : 0, qdesc, tdesc, cand, dist, cap);
+    if (!FILL && orbx_lane() == 0) cnt[qi] = total;
+}
+
+// Count and fill in ONE launch (the two tracking searches): a warp counts its query's candidates, reserves their span
+// of cand / dist with one atomicAdd on a running counter and fills it.  Rows then sit in the lists in the order the
+// warps got there -- row_info[q] = {first position, count} instead of a CSR row pointer -- but a row's own candidates
+// keep the reference's order, which is all the accept loops depend on.  The counter is never reset: `counter0` is its
+// value before this launch (the host reads it back with the results), positions are relative to it.
+__global__ void __launch_bounds__(256)
+k_area_onepass(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start,
+               const int32_t* __restrict__ items, OrbmGrid G, const orbm_area_query* __restrict__ Q, int nq,
+               uint2* __restrict__ row_info, uint32_t* __restrict__ counter, uint32_t counter0,
+               const uint4* __restrict__ qdesc, const uint4* __restrict__ tdesc, int32_t* __restrict__ cand,
+               uint16_t* __restrict__ dist, int cap) {
+    const int qi = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
+    if (qi >= nq) return;
+    const orbm_area_query q = Q[qi];
+    const int total = area_walk<false>(keys, start, items, G, q, 0, qdesc, tdesc, cand, dist, cap);
+    uint32_t base = 0;
+    if (total) {   // (warp-uniform)
+        if (orbx_lane() == 0) base = atomicAdd(counter, (uint32_t)total) - counter0;
+        base = __shfl_sync(ORBX_FULL, base, 0);
+        // a span that would pass 2^31 is not written (cap < 2^31 drops it anyway; the host sees the total and reruns)
+        if (base < 0x7fffffffu - (uint32_t)total)
+            area_walk<true>(keys, start, items, G, q, (int)base, qdesc, tdesc, cand, dist, cap);
+    }
+    if (orbx_lane() == 0) row_info[qi] = make_uint2(base, (uint32_t)total);
 }
 
 // row_ptr[0..n] = exclusive scan of cnt[0..n) (one CTA)
@@ -449,6 +504,17 @@ cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* star
     k_area<true><<<(nq + 7) / 8, 256, 0, st>>>(keys, start, items, G, Q, nq, nullptr, row_ptr,
                                                 reinterpret_cast<const uint4*>(qdesc),
                                                 reinterpret_cast<const uint4*>(tdesc), cand, dist, cap);
+    return cudaGetLastError();
+}
+
+cudaError_t orbm_launch_area_onepass(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
+                                     float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
+                                     int nq, uint2* row_info, uint32_t* counter, uint32_t counter0, const uint8_t* qdesc,
+                                     const uint8_t* tdesc, int32_t* cand, uint16_t* dist, int cap, cudaStream_t st) {
+    OrbmGrid G{min_x, min_y, w_inv, h_inv};
+    k_area_onepass<<<(nq + 7) / 8, 256, 0, st>>>(keys, start, items, G, Q, nq, row_info, counter, counter0,
+                                                  reinterpret_cast<const uint4*>(qdesc),
+                                                  reinterpret_cast<const uint4*>(tdesc), cand, dist, cap);
     return cudaGetLastError();
 }
 

@@ -31,6 +31,10 @@ cudaError_t orbm_launch_grid_build(const orbx_keypoint* keys, int n, float min_x
 cudaError_t orbm_launch_area_count(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
                                    float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
                                    int nq, int32_t* cnt, int32_t* row_ptr, cudaStream_t st);
+cudaError_t orbm_launch_area_onepass(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
+                                     float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
+                                     int nq, uint2* row_info, uint32_t* counter, uint32_t counter0, const uint8_t* qdesc,
+                                     const uint8_t* tdesc, int32_t* cand, uint16_t* dist, int cap, cudaStream_t st);
 cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
                                   float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
                                   int nq, const int32_t* row_ptr, const uint8_t* qdesc, const uint8_t* tdesc,
@@ -146,7 +150,12 @@ struct orbm_context {
     std::vector<PendingCopy> pending;
     DevBuf darena;                   // device mirror of the arena: uploads arrive in one copy (ctx_flush)
     OrbmScatter up = {};                // staged uploads not yet sent (src = offset in the arena until ctx_flush)
-    size_t up_first = 0;
+    size_t up_first = 0, up_end = 0;    // span of the arena the next ctx_flush copies ([first, end), empty when end == 0)
+    // one-pass window search (device_candidates_onepass): {first position, count} per query, the running counter
+    std::vector<uint2> h_rowinfo;
+    DevBuf counter;
+    uint32_t counter_host = 0;          // the counter's value after the last search that used it
+    bool counter_known = false;         // false: zero it before the next use (first use, or a call that failed mid-way)
     std::unordered_map<const orbm_frame_view*, struct orbm_frame*> frames;   // device-resident frames of this context
     std::vector<struct orbm_frame*> frame_pool;   // destroyed frames whose device buffers the next frame reuses (no cudaMalloc per frame)
 };
@@ -191,7 +200,7 @@ static const size_t ORBM_PIN_DIRECT = 1u << 20;
 // launch that hands the segments to their buffers.  Called before the first kernel of a search (every
 // kernel sequence starts at the ev0 record), before a download is queued and at the sync.
 static cudaError_t ctx_flush(orbm_context* c) {
-    if (c->up.n == 0) return cudaSuccess;
+    if (c->up.n == 0 && c->up_end == 0) return cudaSuccess;
 #ifdef ORBM_NO_SCATTER   // A/B switch: a copy per segment
     const bool mirror = false;
 #else
@@ -205,13 +214,14 @@ static cudaError_t ctx_flush(orbm_context* c) {
             if (e != cudaSuccess) return e;
         }
         c->up.n = 0;
+        c->up_end = 0;
         return cudaSuccess;
     }
-    const OrbmScatter::Seg& last = c->up.seg[c->up.n - 1];
-    const size_t end = (size_t)(uintptr_t)last.src + last.bytes;
-    cudaError_t e = cudaMemcpyAsync((uint8_t*)c->darena.p + c->up_first, c->pin + c->up_first, end - c->up_first,
+    cudaError_t e = cudaMemcpyAsync((uint8_t*)c->darena.p + c->up_first, c->pin + c->up_first, c->up_end - c->up_first,
                                     cudaMemcpyHostToDevice, c->st);
+    c->up_end = 0;
     if (e != cudaSuccess) return e;
+    if (c->up.n == 0) return cudaSuccess;   // everything staged was read in place (ctx_stage_alias)
     for (int k = 0; k < c->up.n; ++k) c->up.seg[k].src = (const uint8_t*)c->darena.p + (uintptr_t)c->up.seg[k].src;
     e = orbm_launch_scatter(c->up, c->st);
     c->up.n = 0;
@@ -223,7 +233,9 @@ void orbm_abort_staged(orbm_context* c) {
     cudaGetLastError();
     c->pending.clear();
     c->up.n = 0;
+    c->up_end = 0;
     c->pin_used = 0;
+    c->counter_known = false;
     g_staging_ctx = nullptr;
 }
 
@@ -242,7 +254,8 @@ static cudaError_t ctx_h2d(orbm_context* c, void* dst, const void* src, size_t b
         cudaError_t e = ctx_flush(c);
         if (e != cudaSuccess) return e;
     }
-    if (c->up.n == 0) c->up_first = off;
+    if (c->up_end == 0) c->up_first = off;
+    c->up_end = off + bytes;
     c->up.seg[c->up.n++] = OrbmScatter::Seg{dst, (const void*)(uintptr_t)off, (uint32_t)bytes, 0};
     return cudaSuccess;
 }
@@ -259,14 +272,39 @@ static void* ctx_stage(orbm_context* c, void* dst, size_t bytes) {
     }
     g_staging_ctx = c;
     c->pin_used = off + bytes;
-    if (c->up.n == 0) c->up_first = off;
+    if (c->up_end == 0) c->up_first = off;
+    c->up_end = off + bytes;
     c->up.seg[c->up.n++] = OrbmScatter::Seg{dst, (const void*)(uintptr_t)off, (uint32_t)bytes, 0};
+    return c->pin + off;
+}
+
+// The same, for data the kernels read IN PLACE in the arena's device mirror: no scatter, the flush's one copy brings
+// it over.  *dev = where it will be on the device.  nullptr when the arena (or its mirror) cannot take it.
+static void* ctx_stage_alias(orbm_context* c, size_t bytes, const void** dev) {
+#ifdef ORBM_NO_SCATTER
+    return nullptr;
+#endif
+    const size_t off = (c->pin_used + 255) & ~(size_t)255;
+    if (bytes == 0 || bytes > ORBM_PIN_DIRECT || off + bytes > c->pin_cap) {
+        if (bytes && bytes <= ORBM_PIN_DIRECT) c->pin_want = std::max(c->pin_want, off + bytes);
+        return nullptr;
+    }
+    if (c->darena.ensure(c->pin_cap) != ORBX_OK) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    g_staging_ctx = c;
+    c->pin_used = off + bytes;
+    if (c->up_end == 0) c->up_first = off;
+    c->up_end = off + bytes;
+    *dev = (const uint8_t*)c->darena.p + off;
     return c->pin + off;
 }
 
 // Drops what a call has staged but not sent (an argument error found while the queries were being built).
 static void ctx_unstage(orbm_context* c) {
     c->up.n = 0;
+    c->up_end = 0;
     c->pin_used = 0;
     g_staging_ctx = nullptr;
 }
@@ -297,6 +335,7 @@ static cudaError_t ctx_sync(orbm_context* c) {
     c->pending.clear();
     c->pin_used = 0;
     c->up.n = 0;
+    c->up_end = 0;
     g_staging_ctx = nullptr;
     if (e == cudaSuccess && c->pin_cap && c->pin_want > c->pin_cap && c->pin_cap < ORBM_PIN_MAX) {
         size_t want = std::min(std::max(c->pin_want * 2, ORBM_PIN_INIT), ORBM_PIN_MAX);
@@ -356,7 +395,7 @@ int orbm_destroy(orbm_context* c) {
     }
     c->frame_pool.clear();
     for (DevBuf* b : {&c->q, &c->t, &c->rowptr, &c->cand, &c->dist, &c->aux1, &c->aux2, &c->kl, &c->kr, &c->sc, &c->isc,
-                      &c->ur, &c->dp, &c->sd, &c->gstart, &c->gitems, &c->gcell, &c->aq, &c->acnt})
+                      &c->ur, &c->dp, &c->sd, &c->gstart, &c->gitems, &c->gcell, &c->aq, &c->acnt, &c->counter, &c->darena})
         b->release();
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -694,20 +733,144 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
 
 // The queries of a window search, built in place in the pinned arena when they fit (else in `own`).
 struct QueryBuf {
-    orbm_area_query* q = nullptr;
+    orbm_area_query* q = nullptr;            // where the caller writes them
+    const orbm_area_query* dev = nullptr;    // staged: where the kernels will read them
     bool staged = false;
     std::vector<orbm_area_query> own;
 };
-int stage_queries(orbm_context* c, int n, QueryBuf* b) {
+// alias: the kernels read the queries in the arena's device mirror (no scatter launch); else they go to c->aq.
+int stage_queries(orbm_context* c, int n, QueryBuf* b, bool alias = false) {
     int r;
     M_TRY(cudaSetDevice(c->device));
     if ((r = c->aq.ensure((size_t)std::max(n, 1) * sizeof(orbm_area_query)))) return r;
-    b->q = (orbm_area_query*)ctx_stage(c, c->aq.p, (size_t)n * sizeof(orbm_area_query));
+    const void* dev = nullptr;
+    if (alias) b->q = (orbm_area_query*)ctx_stage_alias(c, (size_t)n * sizeof(orbm_area_query), &dev);
+    if (b->q) {
+        b->dev = (const orbm_area_query*)dev;
+    } else {
+        b->q = (orbm_area_query*)ctx_stage(c, c->aq.p, (size_t)n * sizeof(orbm_area_query));
+        b->dev = (const orbm_area_query*)c->aq.p;
+    }
     b->staged = b->q != nullptr;
     if (!b->staged) {
         b->own.resize(n);
         b->q = b->own.data();
+        b->dev = nullptr;
     }
+    return ORBX_OK;
+}
+
+// Candidates + distances of the two tracking searches in ONE kernel (k_area_onepass): no count launch, no row scan,
+// and -- with the queries (and host descriptors) read in place in the arena's mirror -- no scatter launch either:
+// one H2D copy, one kernel, the downloads.  Leaves {first position, count} per query in c->h_rowinfo and the lists
+// in c->h_cand / c->hdist (rows in the order the warps reserved them, a row's candidates in the reference's order).
+int device_candidates_onepass(orbm_context* c, const orbm_frame_view* F, const QueryBuf& qb, int nq, const uint8_t* qdesc,
+                              int n_qdesc, const uint8_t* d_qdesc) {
+    ORBM_PHASE_BEGIN("device_candidates_onepass");
+    c->h_rowinfo.assign(nq, make_uint2(0, 0));
+    c->h_cand.clear();
+    c->hdist.clear();
+    c->have_full = true;
+    c->last_pairs = 0;
+    if (nq == 0 || F->n == 0) {
+        if (qb.staged) ctx_unstage(c);
+        return ORBX_OK;
+    }
+    M_TRY(cudaSetDevice(c->device));
+    const orbm_frame* RF = nullptr;
+    {
+        auto it = c->frames.find(F);
+        if (it != c->frames.end()) RF = it->second;
+    }
+    int r;
+    if ((r = c->rowptr.ensure((size_t)nq * 8)) || (r = c->counter.ensure(64))) return r;
+    if (!RF && ((r = c->kl.ensure((size_t)F->n * sizeof(orbx_keypoint))) || (r = c->t.ensure((size_t)F->n * 32)) ||
+                (r = c->gstart.ensure((size_t)(ORBM_GRID_COLS * ORBM_GRID_ROWS + 1) * 4)) ||
+                (r = c->gitems.ensure((size_t)F->n * 4)) || (r = c->gcell.ensure((size_t)F->n * 4))))
+        return r;
+    if (!RF) {
+        M_TRY(ctx_h2d(c, c->kl.p, F->keys, (size_t)F->n * sizeof(orbx_keypoint)));
+        M_TRY(ctx_h2d(c, c->t.p, F->desc, (size_t)F->n * 32));
+    }
+    const orbx_keypoint* dk = RF ? (const orbx_keypoint*)RF->d_keys.p : (const orbx_keypoint*)c->kl.p;
+    const uint8_t* dt = RF ? (const uint8_t*)RF->d_desc.p : (const uint8_t*)c->t.p;
+    const int32_t* gstart = RF ? (const int32_t*)RF->d_start.p : (const int32_t*)c->gstart.p;
+    const int32_t* gitems = RF ? (const int32_t*)RF->d_items.p : (const int32_t*)c->gitems.p;
+    const uint8_t* dq = d_qdesc ? d_qdesc : dt;
+    if (!d_qdesc && qdesc) {   // host descriptors: into the mirror, read in place
+        const void* dev = nullptr;
+        void* h = ctx_stage_alias(c, (size_t)n_qdesc * 32, &dev);
+        if (h) {
+            memcpy(h, qdesc, (size_t)n_qdesc * 32);
+            dq = (const uint8_t*)dev;
+        } else {
+            if ((r = c->q.ensure((size_t)std::max(n_qdesc, 1) * 32))) return r;
+            M_TRY(ctx_h2d(c, c->q.p, qdesc, (size_t)n_qdesc * 32));
+            dq = (const uint8_t*)c->q.p;
+        }
+    }
+    const orbm_area_query* dQ = qb.dev;
+    if (!qb.staged) {
+        M_TRY(ctx_h2d(c, c->aq.p, qb.q, (size_t)nq * sizeof(orbm_area_query)));
+        dQ = (const orbm_area_query*)c->aq.p;
+    }
+    if (!c->counter_known) {
+        M_TRY(cudaMemsetAsync(c->counter.p, 0, 4, c->st));
+        c->counter_host = 0;
+        c->counter_known = true;
+    }
+    ORBM_PHASE("uploads");
+    M_TRY(ctx_flush(c));
+    ORBM_PHASE("flush");
+    M_TRY(cudaEventRecord(c->ev0, c->st));
+    if (!RF)
+        M_TRY(orbm_launch_grid_build(dk, F->n, F->min_x, F->min_y, F->grid_w_inv, F->grid_h_inv, (int32_t*)c->gstart.p,
+                                     (int32_t*)c->gitems.p, (int32_t*)c->gcell.p, c->st));
+    {   // lists sized from the last search's pair count, as in device_candidates
+        const size_t guess = std::max<size_t>(4096, 2 * (size_t)c->nnz_hint);
+        if ((r = c->cand.ensure(guess * 4)) || (r = c->dist.ensure(guess * 2))) return r;
+    }
+    uint32_t nnz = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+        const int cap = (int)std::min<size_t>({c->cand.cap / 4, c->dist.cap / 2, (size_t)0x3fffffff});
+        M_TRY(orbm_launch_area_onepass(dk, gstart, gitems, F->min_x, F->min_y, F->grid_w_inv, F->grid_h_inv, dQ, nq,
+                                       (uint2*)c->rowptr.p, (uint32_t*)c->counter.p, c->counter_host, dq, dt,
+                                       (int32_t*)c->cand.p, (uint16_t*)c->dist.p, cap, c->st));
+        M_TRY(cudaEventRecord(c->ev1, c->st));
+        c->timed = true;
+        uint32_t after = 0;
+        M_TRY(ctx_d2h(c, c->h_rowinfo.data(), c->rowptr.p, (size_t)nq * 8));
+        M_TRY(ctx_d2h(c, &after, c->counter.p, 4));
+        const size_t spec = pass == 0 ? std::min<size_t>({(size_t)cap, (size_t)c->nnz_hint + (size_t)c->nnz_hint / 8 + 1024, (size_t)65536})
+                                      : (size_t)nnz;
+        c->h_cand.resize(spec);
+        c->hdist.resize(spec);
+        M_TRY(ctx_d2h(c, c->h_cand.data(), c->cand.p, spec * 4));
+        M_TRY(ctx_d2h(c, c->hdist.data(), c->dist.p, spec * 2));
+        ORBM_PHASE("launch + downloads queued");
+        M_TRY(ctx_sync(c));
+        ORBM_PHASE("wait + deliver");
+        nnz = after - c->counter_host;
+        c->counter_host = after;
+        c->last_pairs = nnz;
+        c->nnz_hint = (int)std::min<uint32_t>(nnz, 0x3fffffffu);
+        if (nnz > (uint32_t)cap) {   // the guess was too small: lists of the right size, once more
+            if (nnz > 0x3fffffffu) return orbx_set_error(ORBX_E_CAPACITY, "%u candidate pairs", nnz);
+            if ((r = c->cand.ensure((size_t)nnz * 4)) || (r = c->dist.ensure((size_t)nnz * 2))) return r;
+            continue;
+        }
+        if ((size_t)nnz > spec) {   // the tail the speculative fetch did not cover
+            c->h_cand.resize(nnz);
+            c->hdist.resize(nnz);
+            M_TRY(ctx_d2h(c, c->h_cand.data() + spec, (const int32_t*)c->cand.p + spec, ((size_t)nnz - spec) * 4));
+            M_TRY(ctx_d2h(c, c->hdist.data() + spec, (const uint16_t*)c->dist.p + spec, ((size_t)nnz - spec) * 2));
+            M_TRY(ctx_sync(c));
+        }
+        c->h_cand.resize(nnz);
+        c->hdist.resize(nnz);
+        break;
+    }
+    ORBM_PHASE("tail");
     return ORBX_OK;
 }
 
@@ -962,7 +1125,7 @@ int search_by_projection_points_impl(orbm_context* c, const orbm_frame_view* F, 
     // pass 1: window queries (state independent), written straight into the pinned arena; candidates + distances come
     // from the device
     QueryBuf qb;
-    if ((rc = stage_queries(c, m, &qb))) return rc;
+    if ((rc = stage_queries(c, m, &qb, true))) return rc;
     orbm_area_query* Q = qb.q;
     std::vector<float>& rad = c->h_rad;
     rad.resize(m);
@@ -982,9 +1145,9 @@ int search_by_projection_points_impl(orbm_context* c, const orbm_frame_view* F, 
                     : orbm_area_query{0.f, 0.f, 0.f, 0, 0, 0, row};
     }
     ORBM_PHASE("queries");
-    if ((rc = device_candidates(c, F, Q, m, qb.staged, bank ? nullptr : mp_desc, bank ? 0 : m, bank ? bank->d : nullptr))) return rc;
+    if ((rc = device_candidates_onepass(c, F, qb, m, bank ? nullptr : mp_desc, bank ? 0 : m, bank ? bank->d : nullptr))) return rc;
     ORBM_PHASE("device_candidates");
-    const std::vector<int32_t>& row_ptr = c->h_rowptr;
+    const uint2* row = c->h_rowinfo.data();   // {first position, count} of each map point's candidates
     const std::vector<int32_t>& cand = c->h_cand;
     // pass 2: the reference's accept loop, original order (:54-147)
     int nmatches = 0;
@@ -998,7 +1161,7 @@ int search_by_projection_points_impl(orbm_context* c, const orbm_frame_view* F, 
     int n_live = 0;
     for (int i = 0; i < m; ++i) {
         live_rows[n_live] = i;
-        n_live += row_ptr[i + 1] != row_ptr[i];
+        n_live += row[i].y != 0;
     }
     const float* ur = F->u_right;
     const uint16_t* hd = c->hdist.data();
@@ -1007,7 +1170,7 @@ int search_by_projection_points_impl(orbm_context* c, const orbm_frame_view* F, 
         const orbm_map_point& p = mps[i];
         const float radi = rad[i];
         int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
-        for (int k = row_ptr[i]; k < row_ptr[i + 1]; ++k) {
+        for (int k = (int)row[i].x, ke = (int)(row[i].x + row[i].y); k < ke; ++k) {
             const int idx = cand[k];
             // :90-101: a keypoint whose map point has observations, or whose right coordinate is further
             // than the radius from the projection, is skipped = takes a distance nothing accepts
@@ -1050,7 +1213,7 @@ int search_by_projection_frames_impl(orbm_context* c, const orbm_frame_view* cur
     std::vector<int> rotHist[ORBM_HISTO_LENGTH];
     const float factor = 1.0f / ORBM_HISTO_LENGTH;
     QueryBuf qb;
-    if ((rc = stage_queries(c, n_last, &qb))) return rc;
+    if ((rc = stage_queries(c, n_last, &qb, true))) return rc;
     orbm_area_query* Q = qb.q;
     std::vector<float>& rad = c->h_rad;
     rad.resize(n_last);
@@ -1074,19 +1237,19 @@ int search_by_projection_frames_impl(orbm_context* c, const orbm_frame_view* cur
         else if (backward) q = orbm_area_query{o.u, o.v, rad[i], 0, o.octave, 1, row};
         else q = orbm_area_query{o.u, o.v, rad[i], o.octave - 1, o.octave + 1, 1, row};
     }
-    if ((rc = device_candidates(c, cur, Q, n_last, qb.staged, bank ? nullptr : last_desc, bank ? 0 : n_last,
-                                bank ? bank->d : nullptr)))
+    if ((rc = device_candidates_onepass(c, cur, qb, n_last, bank ? nullptr : last_desc, bank ? 0 : n_last,
+                                        bank ? bank->d : nullptr)))
         return rc;
-    const std::vector<int32_t>& row_ptr = c->h_rowptr;
+    const uint2* row = c->h_rowinfo.data();   // {first position, count} of each observation's candidates
     const std::vector<int32_t>& cand = c->h_cand;
     int nmatches = 0;
     for (int i = 0; i < n_last; ++i) {
-        if (row_ptr[i + 1] == row_ptr[i]) continue;
+        if (row[i].y == 0) continue;
         const orbm_last_obs& o = last[i];
         int bestDist = 256, bestIdx2 = -1;
         // selects instead of early-outs, as in SearchByProjection(Frame, map points) above (:2040-2056)
         const float ur = o.u - bf * o.inv_z, radi = rad[i];
-        for (int k = row_ptr[i]; k < row_ptr[i + 1]; ++k) {
+        for (int k = (int)row[i].x, ke = (int)(row[i].x + row[i].y); k < ke; ++k) {
             const int i2 = cand[k];
             bool skip = kp_obs[i2] > 0;
             if (cur->u_right) {
