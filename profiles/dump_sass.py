@@ -6,7 +6,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 tag = sys.argv[1] if len(sys.argv) > 1 else "r1"
 KERNELS = ["k_resize_rows_async", "k_resize_rows", "k_resize_level", "k_fast_cells", "k_octree",
            "k_describe", "k_hamming_csr", "k_knn2", "k_stereo_rows", "k_stereo_refine", "k_grid_build", "k_area",
-           "k_rowptr_scan", "k_input", "k_distinctive", "k_bow_descend", "k_bow_topk", "k_csr_topk"]
+           "k_area_onepass", "k_rowptr_scan", "k_input", "k_resize_tail", "k_undistort", "k_scatter", "k_distinctive", "k_bow_descend", "k_bow_topk", "k_csr_topk"]
 txt = subprocess.run(["cuobjdump", "-sass", os.path.join(ROOT, "orb-slam3-mac_b200", "liborbx_b200.so")],
                      capture_output=True, text=True).stdout
 os.makedirs(os.path.join(ROOT, "profiles", "sass"), exist_ok=True)
