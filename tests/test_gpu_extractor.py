@@ -109,6 +109,30 @@ def test_batch_matches_single_and_oracle(oracle_libs, synth):
     ex.close()
 
 
+@pytest.mark.parametrize("nf,h,w,B", [(1000, 480, 752, 48), (2000, 480, 752, 40), (5000, 240, 376, 40)])
+def test_large_batch_quadtree_cta_sizes(oracle_libs, synth, nf, h, w, B):
+    """k_octree is compiled for 128 / 256 / 512 threads and picked per LAUNCH (csrc/k_octree.cu): a launch of more
+    than 2 CTAs per SM goes by the plan's largest per-level quota (nf = 1000 -> 217 -> 128 threads, 2000 -> 434 -> 256,
+    5000 -> 1086 -> 512), a smaller one always takes 512.  A batch big enough for the first rule must give, frame for
+    frame, the bytes of the same frames extracted one at a time (second rule), and the oracle's results."""
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    kinds = ["noise", "checker", "lowtex", "noise"]
+    imgs = [synth.frame(kinds[i % 4], h, w, 100 + i) for i in range(B)]
+    laps = [(0, 1000) if i % 3 else (0, 0) for i in range(B)]
+    ex = ORBextractor(nf, 1.2, 8, 20, 7, max_size=(h, w), max_batch=B)
+    assert B * 8 > 2 * 148
+    res = ex.extract_batch(imgs, laps)
+    one = ORBextractor(nf, 1.2, 8, 20, 7, max_size=(h, w), max_batch=1)
+    for i in range(B):
+        mono, k, d = one(imgs[i], laps[i])
+        assert res[i][0] == mono and np.array_equal(res[i][1].view(np.uint8), k.view(np.uint8)) and np.array_equal(res[i][2], d), i
+    ora = _oracle(oracle_libs, nf)
+    for i in (0, 1, B - 1):
+        _compare_final(ora(imgs[i], laps[i]), res[i], ("large batch", nf, i))
+    one.close()
+    ex.close()
+
+
 def test_empty_and_bad_inputs():
     from orb_slam3_mac_b200 import _lib
     from orb_slam3_mac_b200.extractor import ORBextractor, OrbxError
