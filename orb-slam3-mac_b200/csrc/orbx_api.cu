@@ -268,8 +268,8 @@ int build_plan(const orbx_handle* h, int w, int hgt, OrbxPlan* out, std::vector<
         L.n_target = h->nper[l];
         const int Wd = L.max_bx - ORBX_FAST_BORDER, Hd = L.max_by - ORBX_FAST_BORDER;
         L.n_ini = (int)roundf((float)Wd / Hd);
-        if (L.n_ini < 1 || L.n_ini > 8)
-            return fail(ORBX_E_UNSUPPORTED, "level %d: nIni=%d (aspect ratio outside [0.5, 8.5)); the reference divides by zero for nIni=0", l, L.n_ini);
+        if (L.n_ini < 1 || L.n_ini > 64)
+            return fail(ORBX_E_UNSUPPORTED, "level %d: nIni=%d (aspect ratio outside [0.5, 64.5)); the reference divides by zero for nIni=0", l, L.n_ini);
         L.hx = (float)Wd / L.n_ini;
         L.node_cap = std::max(L.n_target + 3, 4 * L.n_ini) + 5;
         if (L.node_cap > 8192) return fail(ORBX_E_UNSUPPORTED, "more than 8184 features on one level");
