@@ -136,6 +136,8 @@ struct orbm_context {
     DevBuf q, t, rowptr, cand, dist, aux1, aux2, kl, kr, sc, isc, ur, dp, sd, gstart, gitems, gcell, aq, acnt;
     std::vector<int32_t> h_rowptr, h_cand;   // candidate lists of the last layer-2 search
     std::vector<uint16_t> hdist;     // distances of the last layer-2 search
+    std::vector<int32_t> h_cand2;    // (scratch of the CSR re-pack in device_candidates)
+    std::vector<uint16_t> hdist2;
     std::vector<uint32_t> h_topk;    // k_bow_topk's / k_csr_topk's keys of the last search
     std::vector<int32_t> h_topc;     // k_csr_topk: the candidate each key names
     int nnz_hint = 0;                // pairs of the last window search: sizes the lists of the next one before its counts are known
@@ -608,10 +610,54 @@ int check_view(const orbm_frame_view* F) {
 // c->h_rowptr / c->h_cand and the distances in c->hdist.
 // topk > 0: the rows' full lists stay on the device (window_full_lists() fetches them on demand) and the
 // host gets k_csr_topk's topk best (distance, position) keys + candidates per row instead.
+// The queries of a window search, built in place in the pinned arena when they fit (else in `own`).
+struct QueryBuf {
+    orbm_area_query* q = nullptr;            // where the caller writes them
+    const orbm_area_query* dev = nullptr;    // staged: where the kernels will read them
+    bool staged = false;
+    std::vector<orbm_area_query> own;
+};
+int device_candidates_onepass(orbm_context* c, const orbm_frame_view* F, const QueryBuf& qb, int nq, const uint8_t* qdesc,
+                              int n_qdesc, const uint8_t* d_qdesc);
+
 // q_staged: the queries are already in the arena (stage_queries).  d_qdesc: the queries' descriptors are rows of a
 // device-resident bank (qdesc is then null and nothing is sent for them).
+// Without top-K the lists come from the one-launch search (device_candidates_onepass) and are put into CSR order
+// here, on the host (a copy of nnz entries: a few microseconds against two launches and a scatter); with top-K
+// (SearchForInitialization) the count -> scan -> fill -> top-K chain below runs, whose lists stay on the device.
 int device_candidates(orbm_context* c, const orbm_frame_view* F, const orbm_area_query* Qp, int nq, bool q_staged,
                       const uint8_t* qdesc, int n_qdesc, const uint8_t* d_qdesc, int topk = 0) {
+#ifndef ORBM_NO_ONEPASS   // (A/B switch: the three-launch path for every search)
+    if (topk == 0) {
+        QueryBuf qb;
+        qb.q = const_cast<orbm_area_query*>(Qp);
+        qb.staged = q_staged;
+        qb.dev = q_staged ? (const orbm_area_query*)c->aq.p : nullptr;
+        int rc = device_candidates_onepass(c, F, qb, nq, qdesc, n_qdesc, d_qdesc);
+        if (rc) return rc;
+        c->h_topk.clear();
+        c->h_topc.clear();
+        c->h_rowptr.resize((size_t)nq + 1);
+        c->h_rowptr[0] = 0;
+        const uint2* row = c->h_rowinfo.data();
+        for (int i = 0; i < nq; ++i) c->h_rowptr[i + 1] = c->h_rowptr[i] + (int32_t)row[i].y;
+        const size_t nnz = (size_t)c->h_rowptr[nq];
+        c->h_cand2.resize(nnz);
+        c->hdist2.resize(nnz);
+        for (int i = 0; i < nq; ++i) {
+            const uint32_t s0 = row[i].x, n = row[i].y;
+            int32_t* dc = c->h_cand2.data() + c->h_rowptr[i];
+            uint16_t* dd = c->hdist2.data() + c->h_rowptr[i];
+            for (uint32_t k = 0; k < n; ++k) {
+                dc[k] = c->h_cand[s0 + k];
+                dd[k] = c->hdist[s0 + k];
+            }
+        }
+        c->h_cand.swap(c->h_cand2);
+        c->hdist.swap(c->hdist2);
+        return ORBX_OK;
+    }
+#endif
     ORBM_PHASE_BEGIN("device_candidates");
     c->h_rowptr.assign(nq + 1, 0);
     c->h_cand.clear();
@@ -731,13 +777,6 @@ int device_candidates(orbm_context* c, const orbm_frame_view* F, const std::vect
     return device_candidates(c, F, Q.data(), (int)Q.size(), false, qdesc, n_qdesc, nullptr, topk);
 }
 
-// The queries of a window search, built in place in the pinned arena when they fit (else in `own`).
-struct QueryBuf {
-    orbm_area_query* q = nullptr;            // where the caller writes them
-    const orbm_area_query* dev = nullptr;    // staged: where the kernels will read them
-    bool staged = false;
-    std::vector<orbm_area_query> own;
-};
 // alias: the kernels read the queries in the arena's device mirror (no scatter launch); else they go to c->aq.
 int stage_queries(orbm_context* c, int n, QueryBuf* b, bool alias = false) {
     int r;
@@ -811,6 +850,7 @@ int device_candidates_onepass(orbm_context* c, const orbm_frame_view* F, const Q
     }
     const orbm_area_query* dQ = qb.dev;
     if (!qb.staged) {
+        if ((r = c->aq.ensure((size_t)nq * sizeof(orbm_area_query)))) return r;
         M_TRY(ctx_h2d(c, c->aq.p, qb.q, (size_t)nq * sizeof(orbm_area_query)));
         dQ = (const orbm_area_query*)c->aq.p;
     }
