@@ -17,6 +17,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_SO = os.path.join(HERE, "_ref", "liborbref.so")
 MREF_SO = os.path.join(HERE, "_ref", "liborbmref.so")
+MDROP_SO = os.path.join(HERE, "_ref", "liborbmdrop.so")   # the same wrapper over the PRODUCT's C++ ORBmatcher drop-in
 PORT_SO = os.path.join(HERE, "_build", "liborb_oracle.so")
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
@@ -34,6 +35,10 @@ def have_ref() -> bool:
 
 def have_mref() -> bool:
     return os.path.exists(MREF_SO)
+
+
+def have_mdrop() -> bool:
+    return os.path.exists(MDROP_SO)
 
 
 def have_port() -> bool:
@@ -202,6 +207,13 @@ class MatchOracle:
             if not have_mref():
                 build("mref")
             self.lib = _Renamed(C.CDLL(MREF_SO))
+        elif kind == "drop":
+            # NOT an oracle: the reference's Frame / MapPoint objects driven through the product's C++ class
+            # orb-slam3-mac_b200/host/ORBmatcher.{h,cc} (-> liborbx_b200.so, needs a GPU); tests/test_cpp_dropin.py
+            # compares it with kind="ref".  Tracking searches only.
+            if not have_mdrop():
+                build("mdrop")
+            self.lib = _Renamed(C.CDLL(MDROP_SO))
         else:
             if not have_port():
                 build("port")

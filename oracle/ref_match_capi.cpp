@@ -584,6 +584,10 @@ int orbr_compute_stereo_matches(const Kp* mvKeys, const uint8_t* mDescriptors, i
 
 }  // extern "C"
 
+// ORBR_DROPIN (oracle/Makefile target `mdrop` -> oracle/_ref/liborbmdrop.so): the same wrapper, the same reference
+// Frame.cc / MapPoint.cc, but the class behind `ORBmatcher` is the PRODUCT's drop-in (orb-slam3-mac_b200/host/
+// ORBmatcher.{h,cc} -> liborbx_b200.so) instead of src/ORBmatcher.cc.  It wraps the tracking searches above; what
+// entry points below that need a method the drop-in does not wrap are left out of that build (#ifndef ORBR_DROPIN).
 // ---- SearchByBoW x2, Sim3 / reloc projections, Fuse x2, SearchBySim3, SearchForTriangulation x2 ----
 namespace {
 
@@ -665,6 +669,7 @@ int orbr_search_by_bow(const BowView* KFp, const uint8_t* kf_mp_ok, const BowVie
     return n;
 }
 
+#ifndef ORBR_DROPIN
 // SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12), src/ORBmatcher.cc:827-967.
 // n_un >= 0: that keyframe has NLeft != -1 and mvKeysUn.size() == n_un (:863-865, :887-889).
 int orbr_search_by_bow_kf(const BowView* K1, const uint8_t* ok1, int n_un1, const BowView* K2, const uint8_t* ok2, int n_un2,
@@ -684,7 +689,9 @@ int orbr_search_by_bow_kf(const BowView* K1, const uint8_t* ok1, int n_un1, cons
     for (int i = 0; i < K1->n; ++i) vpMatches12[i] = index_in(vp[i], mp2.get(), K2->n);
     return n;
 }
+#endif  // ORBR_DROPIN
 
+#ifndef ORBR_DROPIN
 // SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming), src/ORBmatcher.cc:477-590, AND its overload
 // with vpPointsKFs / vpMatchedKF, :592-708 (the wrapper runs both and refuses, -102, if they disagree).  Scw = I.
 // The first overload projects through pKF->mpCamera (:523), the second with the keyframe's fx, fy, cx, cy (:635-640):
@@ -717,7 +724,9 @@ int orbr_search_by_projection_sim3(const FrameView* KFp, const ProjPoint* pts, c
     for (int i = 0; i < F.N; ++i) kp_match[i] = index_in(vpMatched[i], mp.get(), m);
     return n;
 }
+#endif  // ORBR_DROPIN
 
+#ifndef ORBR_DROPIN
 // SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:2183-2305.
 // Point i = map point of keyframe feature i (its angle in pts[i].angle).
 int orbr_search_by_projection_reloc(const FrameView* Fp, const ProjPoint* pts, const uint8_t* mp_desc, int m, float th,
@@ -759,7 +768,9 @@ int orbr_search_by_projection_reloc(const FrameView* Fp, const ProjPoint* pts, c
     for (int i = 0; i < F.N; ++i) kp_match[i] = index_in(F.mvpMapPoints[i], mp.get(), m);
     return n;
 }
+#endif  // ORBR_DROPIN
 
+#ifndef ORBR_DROPIN
 // ORBmatcher::Fuse, both overloads.  mvInvLevelSigma2 != NULL: Fuse(pKF, vpMapPoints, th, bRight = false),
 // src/ORBmatcher.cc:1403-1613 -- point i sits at (i, 0, depth[i]) and the keyframe's mbf is `bf`, so the reference's
 // ur = uv.x - bf * invz (:1490) must reproduce pts[i].ur (else -100: the tests derive ur from depth that way).
@@ -825,7 +836,9 @@ int orbr_fuse(const FrameView* KFp, const ProjPoint* pts, const uint8_t* mp_desc
     }
     return total;
 }
+#endif  // ORBR_DROPIN
 
+#ifndef ORBR_DROPIN
 // SearchBySim3(pKF1, pKF2, vpMatches12, s12 = 1, R12 = I, t12 = 0, th), src/ORBmatcher.cc:1739-1963.  The projection there
 // is pinhole arithmetic on the keyframe's fx, fy, cx, cy (:1802-1806, :1882-1886), not a camera call: with fx = fy = 1,
 // cx = cy = 0 the point (u, v, 1) projects to exactly (u, v).
@@ -857,7 +870,9 @@ int orbr_search_by_sim3(const FrameView* KF1, const FrameView* KF2, const ProjPo
     for (int i = 0; i < N1; ++i) match12[i] = index_in(vpMatches12[i], mp2.get(), N2);
     return n;
 }
+#endif  // ORBR_DROPIN
 
+#ifndef ORBR_DROPIN
 // SearchForTriangulation, src/ORBmatcher.cc:969-1210 (overload == 1: epipolarConstrain, bOnlyStereo, bCoarse) and
 // :1212-1401 (overload == 2: matchAndtriangulate).  pair_ok != NULL: the camera model's pair test is that table;
 // else F12 != NULL (a skew-symmetric [t]x, -104 otherwise): the reference's own Pinhole::epipolarConstrain with
@@ -915,6 +930,7 @@ int orbr_search_for_triangulation(const BowView* K1, const uint8_t* has_mp1, con
     for (size_t k = 0; k < pairs.size(); ++k) vMatches12[pairs[k].first] = (int32_t)pairs[k].second;
     return n;
 }
+#endif  // ORBR_DROPIN
 
 }  // extern "C"
 

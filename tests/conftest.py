@@ -21,6 +21,7 @@ def oracle_libs():
     po.build("port")
     po.build("ref")
     po.build("mref")
+    po.build("mdrop")   # (not an oracle: the same wrapper over the product's C++ ORBmatcher, for tests/test_cpp_dropin.py)
     return po
 
 
