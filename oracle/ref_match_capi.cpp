@@ -669,7 +669,6 @@ int orbr_search_by_bow(const BowView* KFp, const uint8_t* kf_mp_ok, const BowVie
     return n;
 }
 
-#ifndef ORBR_DROPIN
 // SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12), src/ORBmatcher.cc:827-967.
 // n_un >= 0: that keyframe has NLeft != -1 and mvKeysUn.size() == n_un (:863-865, :887-889).
 int orbr_search_by_bow_kf(const BowView* K1, const uint8_t* ok1, int n_un1, const BowView* K2, const uint8_t* ok2, int n_un2,
@@ -689,7 +688,7 @@ int orbr_search_by_bow_kf(const BowView* K1, const uint8_t* ok1, int n_un1, cons
     for (int i = 0; i < K1->n; ++i) vpMatches12[i] = index_in(vp[i], mp2.get(), K2->n);
     return n;
 }
-#endif  // ORBR_DROPIN
+
 
 #ifndef ORBR_DROPIN
 // SearchByProjection(pKF, Scw, vpPoints, vpMatched, th, ratioHamming), src/ORBmatcher.cc:477-590, AND its overload

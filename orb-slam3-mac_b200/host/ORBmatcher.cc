@@ -273,6 +273,28 @@ int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpM
     return n;
 }
 
+// src/ORBmatcher.cc:827-967
+int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12) {
+    const std::vector<MapPoint*> vp1 = pKF1->GetMapPointMatches(), vp2 = pKF2->GetMapPointMatches();
+    vpMatches12 = std::vector<MapPoint*>(vp1.size(), static_cast<MapPoint*>(NULL));
+    const int n1 = (int)vp1.size(), n2 = (int)vp2.size();
+    std::vector<uint8_t> ok1(n1 > 0 ? n1 : 1, 0), ok2(n2 > 0 ? n2 : 1, 0);
+    for (int i = 0; i < n1; ++i) ok1[i] = (vp1[i] && !vp1[i]->isBad()) ? 1 : 0;   // :868-872
+    for (int i = 0; i < n2; ++i) ok2[i] = (vp2[i] && !vp2[i]->isBad()) ? 1 : 0;   // :892-898
+    const std::vector<cv::KeyPoint> none;
+    const BowSide A(pKF1->mvKeysUn, none, none, false, 0, pKF1->mDescriptors, n1, pKF1->mFeatVec);
+    const BowSide B(pKF2->mvKeysUn, none, none, false, 0, pKF2->mDescriptors, n2, pKF2->mFeatVec);
+    const int n_un1 = pKF1->NLeft != -1 ? (int)pKF1->mvKeysUn.size() : -1;   // :863-865
+    const int n_un2 = pKF2->NLeft != -1 ? (int)pKF2->mvKeysUn.size() : -1;   // :887-889
+    std::vector<int32_t> m12(n1 > 0 ? n1 : 1, -1);
+    const int n = orbm_search_by_bow_kf(Context(), &A.view, ok1.data(), n_un1, &B.view, ok2.data(), n_un2, mfNNratio,
+                                        mbCheckOrientation, m12.data());
+    if (n < 0) fail("orbm_search_by_bow_kf");
+    for (int i = 0; i < n1; ++i)
+        if (m12[i] >= 0) vpMatches12[i] = vp2[m12[i]];   // :925
+    return n;
+}
+
 // src/ORBmatcher.cc:710-825
 int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched,
                                         std::vector<int>& vnMatches12, int windowSize) {

@@ -10,8 +10,9 @@
 //   SearchByProjection(Frame& Current, const Frame& Last, ...)   :1965-2181 -> orbm_search_by_projection_frames[_stereo]
 //   SearchForInitialization                                      :710-825  -> orbm_search_for_initialization
 //   SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches)            :273-475  -> orbm_search_by_bow
+//   SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)               :827-967  -> orbm_search_by_bow_kf
 //
-// The LocalMapping / LoopClosing searches (SearchByBoW(KF, KF), the Sim3 / relocalisation SearchByProjection, Fuse x2,
+// The other LocalMapping / LoopClosing searches (the Sim3 / relocalisation SearchByProjection, Fuse x2,
 // SearchBySim3, SearchForTriangulation x2) have their C-ABI entry points too (include/orbm.h); INTEGRATION.md shows
 // their bindings, this class does not wrap them yet.
 //
@@ -53,6 +54,7 @@ public:
     // Brute force constrained to ORB that belong to the same vocabulary node (at a certain level)
     // Used in Relocalisation and Loop Detection
     int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);
+    int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);
 
     // Matching for the Map Initialization (only used in the monocular case)
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched,

@@ -159,4 +159,10 @@ def test_matcher_dropin_equals_reference_class(ref_and_dropin, synth, seed):
         want = ref.search_by_bow(KFs, ok, Fs, nleft, ratio, check)
         _same(want, drop.search_by_bow(KFs, ok, Fs, nleft, ratio, check))
         assert want[0] > 50
+    # SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12), incl. the fisheye keyframes' index limit (:863-865)
+    ok2 = (rng.random(len(kb)) < 0.7).astype(np.uint8)
+    for n_un1, n_un2, ratio, check in ((-1, -1, 0.8, True), (len(ka) - 200, len(kb) - 100, 0.8, True), (-1, -1, 0.9, False)):
+        want = ref.search_by_bow_kf(KFs, ok, Fs, ok2, n_un1, n_un2, ratio, check)
+        _same(want, drop.search_by_bow_kf(KFs, ok, Fs, ok2, n_un1, n_un2, ratio, check))
+        assert want[0] > 50
 
