@@ -400,7 +400,8 @@ int orbm_frame_destroy(orbm_frame* f);
  *       the rows are in place and is ordered with the context's searches.
  *   orbm_frame_bank : a resident frame's descriptors as a bank (row = keypoint index; a map point created from a
  *       keypoint starts with that keypoint's descriptor); lives and dies with the frame.
- * `rows` = the bank row per query, NULL for row i.  A bank belongs to the context that made it. */
+ * `rows` = the bank row per query, NULL for row i.  A bank belongs to the context that made it (orbm_destroy frees
+ * the banks that are still alive, as it does the frames). */
 typedef struct orbm_bank orbm_bank;
 int orbm_bank_create(orbm_context* c, int capacity_rows, orbm_bank** out);
 int orbm_bank_write(orbm_bank* b, int first_row, int n, const uint8_t* desc);

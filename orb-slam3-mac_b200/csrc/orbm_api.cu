@@ -159,6 +159,7 @@ struct orbm_context {
     uint32_t counter_host = 0;          // the counter's value after the last search that used it
     bool counter_known = false;         // false: zero it before the next use (first use, or a call that failed mid-way)
     std::unordered_map<const orbm_frame_view*, struct orbm_frame*> frames;   // device-resident frames of this context
+    std::vector<struct orbm_bank*> banks;         // descriptor banks of this context still alive (orbm_destroy frees them)
     std::vector<struct orbm_frame*> frame_pool;   // destroyed frames whose device buffers the next frame reuses (no cudaMalloc per frame)
 };
 
@@ -391,6 +392,7 @@ int orbm_destroy(orbm_context* c) {
     cudaSetDevice(c->device);
     if (c->st) ctx_sync(c);
     while (!c->frames.empty()) orbm_frame_destroy(c->frames.begin()->second);   // frames die with their context
+    while (!c->banks.empty()) orbm_bank_destroy(c->banks.back());               // ... and so do its descriptor banks
     for (orbm_frame* f : c->frame_pool) {
         for (DevBuf* b : {&f->d_keys, &f->d_desc, &f->d_start, &f->d_items, &f->d_cell}) b->release();
         delete f;
@@ -1382,6 +1384,7 @@ int orbm_bank_create(orbm_context* c, int capacity_rows, orbm_bank** out) {
     }
     b->d = (const uint8_t*)b->buf.p;
     b->rows = capacity_rows;
+    c->banks.push_back(b);
     *out = b;
     return ORBX_OK;
 }
@@ -1404,6 +1407,8 @@ int orbm_bank_destroy(orbm_bank* b) {
     if (!b->buf.p) return orbx_set_error(ORBX_E_BAD_ARG, "a frame's bank goes with its frame (orbm_frame_destroy)");
     cudaSetDevice(b->ctx->device);
     cudaStreamSynchronize(b->ctx->st);
+    std::vector<orbm_bank*>& v = b->ctx->banks;
+    v.erase(std::remove(v.begin(), v.end(), b), v.end());
     b->buf.release();
     delete b;
     return ORBX_OK;

@@ -823,8 +823,11 @@ def test_descriptor_banks_match_host_descriptors(matcher, mo):
         try:
             with pytest.raises(OrbxError):
                 other.SearchByProjection(F, mps, bank, 3.0, True, 30.0, rows=rows_p)
+            orphan = DescriptorBank(other, 64)   # never closed: orbm_destroy frees what its context still owns
+            orphan.write(0, md[:64])
         finally:
             other.close()
+        orphan.close()                           # (a no-op once the context is gone)
         # the arena is clean after the refusals: the next search is right
         got = matcher.SearchByProjection(RF, mps, bank, 3.0, True, 30.0, kp_obs=obs0, rows=rows_p)
         assert got[0] == want2[0] and np.array_equal(got[1], want2[1])
