@@ -795,6 +795,10 @@ def run_ours(args):
                 if e2 and e2.get("batch") == B and e2.get("config") == cfg:
                     kernels[nm]["traffic_bytes_per_launch"] = e2["dram_bytes_per_launch"]
                     kernels[nm]["alg_bytes_per_launch"] = int(ab[nm] * B)
+                    # what actually bounds these kernels (same ncu capture): instruction issue, not HBM
+                    if "issue_active_pct" in e2:
+                        kernels[nm]["issue_active_pct_ncu"] = e2["issue_active_pct"]
+                        kernels[nm]["warp_instructions_per_launch_ncu"] = e2.get("warp_instructions_per_launch")
         roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
                     "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": traffic, "peak_source": peak_src,
                     "kernels": kernels, "stage_ms_sum": round(float(stage[:5].sum()), 4),
