@@ -125,7 +125,7 @@ __device__ __forceinline__ void cp_async4(uint32_t saddr, const void* g) {
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 #ifndef DESC_MINB
-#define DESC_MINB 1
+#define DESC_MINB 12   // 40 registers (40 B of spill): 12 CTAs = 48 warps per SM; same-box A/B 0.618 (MINB 1, 63 regs) -> 0.600 ms
 #endif
 __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB)
 k_describe(const __grid_constant__ OrbxPlan P, const OrbxSrc isrc, const uint8_t* __restrict__ pyr,

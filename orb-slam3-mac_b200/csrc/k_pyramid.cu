@@ -322,7 +322,10 @@ __device__ __forceinline__ void rz_walk(const RzArgs& A, int band, int xbase, ui
 
 // warps_x = n8 + n4 warps per band: the first n8 take 256 columns each (8 per thread), the rest
 // 128 columns each (4 per thread), so that a level's width never leaves most of a warp idle.
-__global__ void __launch_bounds__(256)
+#ifndef RZ_MINB
+#define RZ_MINB 4   // 64 registers, no spill (A/B: 5 -> 48 regs + 88 B of spill 0.386 ms, 6 -> 40 regs 0.493 ms, against 0.314)
+#endif
+__global__ void __launch_bounds__(256, RZ_MINB)
 k_resize_rows_async(const __grid_constant__ RzArgs A, int n8) {
     __shared__ __align__(16) uint8_t ring_all[8 * RZ_DEPTH * RzCfg<8>::SLOT_BYTES];
     const int gw = blockIdx.x * 8 + (threadIdx.x >> 5);   // warp -> (band, column chunk)
