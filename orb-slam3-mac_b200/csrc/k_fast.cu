@@ -39,7 +39,9 @@
                          // 0: the round-1 scheme (per-step warp scan + per-lane push loop into a ring), kept for A/B
 #endif
 #if FAST_BITMAP
+#ifndef FAST_Q
 #define FAST_Q 512       // queued pixels (u16) of one group of 32 detection rows; a group with more goes in chunks
+#endif
 #define FAST_BM_PITCH 12 // bitmap bytes per detection row: 8 pixels per byte, <= 9 byte pairs (dw <= 59), word aligned
 #define FAST_BM_ROWS 64  // dh <= 59
 #define FAST_BM_BYTES (FAST_BM_PITCH * FAST_BM_ROWS)
