@@ -54,8 +54,11 @@ __host__ __device__ inline size_t oct_fixed_words(int NC, int NCP2, int CW, int 
 // levels, the 5 x nFeatures initialisation extractor) wants the passes themselves wide.  orbx_octree_threads() picks
 // per plan.  Same-box A/B (ms per launch batch, C1 / C5): 128 x 8 CTAs 0.163 / 0.513, 256 x 4 0.177 / 0.300,
 // 512 x 2 0.277 / 0.186.
+#ifndef OCT_MINB_128
+#define OCT_MINB_128 8
+#endif
 #define OCT_THREADS 128
-#define OCT_MINB 8
+#define OCT_MINB OCT_MINB_128
 #define OCT_NS oct128
 #include "k_octree_body.inc"
 #undef OCT_THREADS
