@@ -128,6 +128,21 @@ __device__ __forceinline__ void fast_drain(const FastWarpSmem& s, int tp, int sp
 __device__ __forceinline__ uint32_t fast_gt4(uint32_t d, uint32_t K4) {
     return ((d >> 1) & 0x7f7f7f7fu) + K4;
 }
+#ifndef FAST_GT_EXACT
+#define FAST_GT_EXACT 1
+#endif
+// Bit 7 of every byte: d1 > th OR d2 > th, for two words of packed absolute differences.
+// FAST_GT_EXACT: exact, K = max(127 - th, 0) replicated: the low seven bits plus K carry into bit 7 iff they exceed
+// th, and a difference of 128 or more has bit 7 set by itself (th >= 127: every d >= 128 is flagged, a superset);
+// two three-input LOP3 merge the four terms.  Else the round-1 form on halved differences (conservative by one grey
+// level for even th), K = 128 - ((th + 1) >> 1) replicated.
+__device__ __forceinline__ uint32_t fast_gt_or2(uint32_t d1, uint32_t d2, uint32_t K) {
+#if FAST_GT_EXACT
+    return (((d1 & 0x7f7f7f7fu) + K) | d1) | (((d2 & 0x7f7f7f7fu) + K) | d2);
+#else
+    return fast_gt4(d1, K) | fast_gt4(d2, K);
+#endif
+}
 
 // q = x / d for 0 <= x < 64, 1 <= d <= 32 without an integer division: M = 2^16/d rounded up
 // (MUFU.RCP), exact because x * d * (M - 2^16/d) < 2^16.
@@ -158,7 +173,11 @@ __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp
         vlo = (uint32_t)m;
         vhi = (uint32_t)(m >> 32);
     }
+#if FAST_GT_EXACT
+    const uint32_t K4 = (uint32_t)max(127 - th, 0) * 0x01010101u;
+#else
     const uint32_t K4 = (uint32_t)(128 - ((th + 1) >> 1)) * 0x01010101u;
+#endif
     int ncorn = 0;
 #if !FAST_BITMAP
     int qhead = 0, qn = 0;
@@ -177,10 +196,10 @@ __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp
             // pixels x-3 and x+3 of the eight centres
             const uint32_t wl = __funnelshift_r(l1, c.x, 8), wh_ = __funnelshift_r(c.x, c.y, 8);
             const uint32_t el = __funnelshift_r(c.x, c.y, 24), eh = __funnelshift_r(c.y, r1, 24);
-            const uint32_t v_lo = fast_gt4(__vabsdiffu4(up.x, c.x), K4) | fast_gt4(__vabsdiffu4(dn.x, c.x), K4);
-            const uint32_t h_lo = fast_gt4(__vabsdiffu4(wl, c.x), K4) | fast_gt4(__vabsdiffu4(el, c.x), K4);
-            const uint32_t v_hi = fast_gt4(__vabsdiffu4(up.y, c.y), K4) | fast_gt4(__vabsdiffu4(dn.y, c.y), K4);
-            const uint32_t h_hi = fast_gt4(__vabsdiffu4(wh_, c.y), K4) | fast_gt4(__vabsdiffu4(eh, c.y), K4);
+            const uint32_t v_lo = fast_gt_or2(__vabsdiffu4(up.x, c.x), __vabsdiffu4(dn.x, c.x), K4);
+            const uint32_t h_lo = fast_gt_or2(__vabsdiffu4(wl, c.x), __vabsdiffu4(el, c.x), K4);
+            const uint32_t v_hi = fast_gt_or2(__vabsdiffu4(up.y, c.y), __vabsdiffu4(dn.y, c.y), K4);
+            const uint32_t h_hi = fast_gt_or2(__vabsdiffu4(wh_, c.y), __vabsdiffu4(eh, c.y), K4);
             flo = v_lo & h_lo & vlo;
             fhi = v_hi & h_hi & vhi;
 #if FAST_DIAG
@@ -199,10 +218,10 @@ __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp
                 const uint32_t ne_lo = __funnelshift_r(u2.x, u2.y, 16), ne_hi = __funnelshift_r(u2.y, u2r, 16);
                 const uint32_t sw_lo = __funnelshift_r(d2l, d2.x, 16), sw_hi = __funnelshift_r(d2.x, d2.y, 16);
                 const uint32_t se_lo = __funnelshift_r(d2.x, d2.y, 16), se_hi = __funnelshift_r(d2.y, d2r, 16);
-                const uint32_t a_lo = fast_gt4(__vabsdiffu4(nw_lo, c.x), K4) | fast_gt4(__vabsdiffu4(se_lo, c.x), K4);
-                const uint32_t b_lo = fast_gt4(__vabsdiffu4(ne_lo, c.x), K4) | fast_gt4(__vabsdiffu4(sw_lo, c.x), K4);
-                const uint32_t a_hi = fast_gt4(__vabsdiffu4(nw_hi, c.y), K4) | fast_gt4(__vabsdiffu4(se_hi, c.y), K4);
-                const uint32_t b_hi = fast_gt4(__vabsdiffu4(ne_hi, c.y), K4) | fast_gt4(__vabsdiffu4(sw_hi, c.y), K4);
+                const uint32_t a_lo = fast_gt_or2(__vabsdiffu4(nw_lo, c.x), __vabsdiffu4(se_lo, c.x), K4);
+                const uint32_t b_lo = fast_gt_or2(__vabsdiffu4(ne_lo, c.x), __vabsdiffu4(sw_lo, c.x), K4);
+                const uint32_t a_hi = fast_gt_or2(__vabsdiffu4(nw_hi, c.y), __vabsdiffu4(se_hi, c.y), K4);
+                const uint32_t b_hi = fast_gt_or2(__vabsdiffu4(ne_hi, c.y), __vabsdiffu4(sw_hi, c.y), K4);
                 flo &= a_lo & b_lo;
                 fhi &= a_hi & b_hi;
             }

@@ -151,6 +151,30 @@ def test_wide_strips_more_than_eight_roots(oracle_libs, synth, h, w, nlevels, sc
         ex.close()
 
 
+@pytest.mark.parametrize("ini,mn", [(126, 100), (127, 126), (128, 127), (150, 130), (254, 200)])
+def test_fast_thresholds_around_128(oracle_libs, synth, ini, mn):
+    """The rejection test of k_fast_cells compares packed bytes: |p - c| > th through the low seven bits plus
+    max(127 - th, 0) and the byte's own bit 7 -- exact up to th = 126, every difference >= 128 flagged above
+    (a superset; the exact score decides).  High-contrast images, thresholds on both sides of 127."""
+    from orb_slam3_mac_b200.extractor import ORBextractor
+    okind = "ref" if oracle_libs.have_ref() else "port"
+    ora = oracle_libs.OracleExtractor(500, 1.2, 4, ini, mn, kind=okind)
+    ex = ORBextractor(500, 1.2, 4, ini, mn, max_size=(300, 400), max_batch=1)
+    try:
+        rng = np.random.default_rng(ini)
+        chk = synth.frame("checker", 300, 400, ini)
+        hard = np.where(rng.random((300, 400)) < 0.5, 0, 255).astype(np.uint8)                 # salt and pepper
+        blocks = np.kron(rng.integers(0, 2, (38, 50)), np.ones((8, 8))).astype(np.uint8)[:300, :400] * 255
+        total = 0
+        for img in (chk, hard, blocks):
+            ref = ora(img, (0, 0))
+            total += len(ref[1])
+            _compare_final(ref, ex(img, (0, 0)), (ini, mn))
+        assert total > 0 or ini > 200
+    finally:
+        ex.close()
+
+
 def test_empty_and_bad_inputs():
     from orb_slam3_mac_b200 import _lib
     from orb_slam3_mac_b200.extractor import ORBextractor, OrbxError
