@@ -152,6 +152,53 @@ __constant__ uint32_t c_fast_inv[33] = {
 __device__ __forceinline__ uint32_t fast_small_inv(int d) { return c_fast_inv[d]; }
 __device__ __forceinline__ int fast_small_div(int x, uint32_t inv) { return (int)(((uint32_t)x * inv) >> 16); }
 
+// The rejection test of eight adjacent detection pixels (one lane's 8-byte pair of a tile row): a FAST-9 corner needs
+// |p - c| > th for the pixel three above or three below AND for the one three left or three right (a 9-arc of the
+// 16-ring holds two ring-adjacent ones of those four).  Returns the eight flags as a byte.
+__device__ __forceinline__ uint32_t fast_reject8(const uint8_t* row, int tp, uint32_t K4, uint32_t vlo, uint32_t vhi) {
+    uint32_t flo, fhi;
+    const uint2 c = *reinterpret_cast<const uint2*>(row);
+    const uint2 up = *reinterpret_cast<const uint2*>(row - 3 * tp);
+    const uint2 dn = *reinterpret_cast<const uint2*>(row + 3 * tp);
+    const uint32_t l1 = *reinterpret_cast<const uint32_t*>(row - 4);
+    const uint32_t r1 = *reinterpret_cast<const uint32_t*>(row + 8);
+    // pixels x-3 and x+3 of the eight centres
+    const uint32_t wl = __funnelshift_r(l1, c.x, 8), wh_ = __funnelshift_r(c.x, c.y, 8);
+    const uint32_t el = __funnelshift_r(c.x, c.y, 24), eh = __funnelshift_r(c.y, r1, 24);
+    const uint32_t v_lo = fast_gt_or2(__vabsdiffu4(up.x, c.x), __vabsdiffu4(dn.x, c.x), K4);
+    const uint32_t h_lo = fast_gt_or2(__vabsdiffu4(wl, c.x), __vabsdiffu4(el, c.x), K4);
+    const uint32_t v_hi = fast_gt_or2(__vabsdiffu4(up.y, c.y), __vabsdiffu4(dn.y, c.y), K4);
+    const uint32_t h_hi = fast_gt_or2(__vabsdiffu4(wh_, c.y), __vabsdiffu4(eh, c.y), K4);
+    flo = v_lo & h_lo & vlo;
+    fhi = v_hi & h_hi & vhi;
+#if FAST_DIAG
+    // the two diagonal ring pairs (+-2, +-2) as well: a 9-arc also holds one pixel of each of
+    // them, and on textured frames this cuts the pixels that reach the exact score from ~10 %
+    // to ~3.4 % (evaluated only where the axis pairs left something)
+    if (flo | fhi) {
+        const uint2 u2 = *reinterpret_cast<const uint2*>(row - 2 * tp);
+        const uint2 d2 = *reinterpret_cast<const uint2*>(row + 2 * tp);
+        const uint32_t u2l = *reinterpret_cast<const uint32_t*>(row - 2 * tp - 4);
+        const uint32_t u2r = *reinterpret_cast<const uint32_t*>(row - 2 * tp + 8);
+        const uint32_t d2l = *reinterpret_cast<const uint32_t*>(row + 2 * tp - 4);
+        const uint32_t d2r = *reinterpret_cast<const uint32_t*>(row + 2 * tp + 8);
+        // (x-2, y-2) / (x+2, y+2) and (x+2, y-2) / (x-2, y+2) of the eight centres
+        const uint32_t nw_lo = __funnelshift_r(u2l, u2.x, 16), nw_hi = __funnelshift_r(u2.x, u2.y, 16);
+        const uint32_t ne_lo = __funnelshift_r(u2.x, u2.y, 16), ne_hi = __funnelshift_r(u2.y, u2r, 16);
+        const uint32_t sw_lo = __funnelshift_r(d2l, d2.x, 16), sw_hi = __funnelshift_r(d2.x, d2.y, 16);
+        const uint32_t se_lo = __funnelshift_r(d2.x, d2.y, 16), se_hi = __funnelshift_r(d2.y, d2r, 16);
+        const uint32_t a_lo = fast_gt_or2(__vabsdiffu4(nw_lo, c.x), __vabsdiffu4(se_lo, c.x), K4);
+        const uint32_t b_lo = fast_gt_or2(__vabsdiffu4(ne_lo, c.x), __vabsdiffu4(sw_lo, c.x), K4);
+        const uint32_t a_hi = fast_gt_or2(__vabsdiffu4(nw_hi, c.y), __vabsdiffu4(se_hi, c.y), K4);
+        const uint32_t b_hi = fast_gt_or2(__vabsdiffu4(ne_hi, c.y), __vabsdiffu4(sw_hi, c.y), K4);
+        flo &= a_lo & b_lo;
+        fhi &= a_hi & b_hi;
+    }
+#endif
+    // flags sit in bit 7 of each byte: one multiply per word gathers them into a nibble.
+    return ((flo * 0x00204081u) >> 28) | (((fhi * 0x00204081u) >> 24) & 0xf0u);
+}
+
 // Computes the score map for threshold `th` (s = raw-1 stored where raw > th, else 0 kept) and
 // the raster-ordered corner list.  Returns the number of corners (may exceed FAST_CLIST).
 __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp, int dw, int dh, int th) {
@@ -185,54 +232,19 @@ __device__ __forceinline__ int fast_scores(const FastWarpSmem& s, int tp, int sp
     const uint8_t* row = s.tile + (3 + ro) * tp + pc * 8;
     const int rstep = rpi * tp;
     const int rend = 3 + dh;
-    for (int r = 3 + ro; r < rend + ro; r += rpi, row += rstep) {   // r - ro is warp-uniform
-        uint32_t flo = 0, fhi = 0;
-        if (active && r < rend) {
-            const uint2 c = *reinterpret_cast<const uint2*>(row);
-            const uint2 up = *reinterpret_cast<const uint2*>(row - 3 * tp);
-            const uint2 dn = *reinterpret_cast<const uint2*>(row + 3 * tp);
-            const uint32_t l1 = *reinterpret_cast<const uint32_t*>(row - 4);
-            const uint32_t r1 = *reinterpret_cast<const uint32_t*>(row + 8);
-            // pixels x-3 and x+3 of the eight centres
-            const uint32_t wl = __funnelshift_r(l1, c.x, 8), wh_ = __funnelshift_r(c.x, c.y, 8);
-            const uint32_t el = __funnelshift_r(c.x, c.y, 24), eh = __funnelshift_r(c.y, r1, 24);
-            const uint32_t v_lo = fast_gt_or2(__vabsdiffu4(up.x, c.x), __vabsdiffu4(dn.x, c.x), K4);
-            const uint32_t h_lo = fast_gt_or2(__vabsdiffu4(wl, c.x), __vabsdiffu4(el, c.x), K4);
-            const uint32_t v_hi = fast_gt_or2(__vabsdiffu4(up.y, c.y), __vabsdiffu4(dn.y, c.y), K4);
-            const uint32_t h_hi = fast_gt_or2(__vabsdiffu4(wh_, c.y), __vabsdiffu4(eh, c.y), K4);
-            flo = v_lo & h_lo & vlo;
-            fhi = v_hi & h_hi & vhi;
-#if FAST_DIAG
-            // the two diagonal ring pairs (+-2, +-2) as well: a 9-arc also holds one pixel of each of
-            // them, and on textured frames this cuts the pixels that reach the exact score from ~10 %
-            // to ~3.4 % (evaluated only where the axis pairs left something)
-            if (flo | fhi) {
-                const uint2 u2 = *reinterpret_cast<const uint2*>(row - 2 * tp);
-                const uint2 d2 = *reinterpret_cast<const uint2*>(row + 2 * tp);
-                const uint32_t u2l = *reinterpret_cast<const uint32_t*>(row - 2 * tp - 4);
-                const uint32_t u2r = *reinterpret_cast<const uint32_t*>(row - 2 * tp + 8);
-                const uint32_t d2l = *reinterpret_cast<const uint32_t*>(row + 2 * tp - 4);
-                const uint32_t d2r = *reinterpret_cast<const uint32_t*>(row + 2 * tp + 8);
-                // (x-2, y-2) / (x+2, y+2) and (x+2, y-2) / (x-2, y+2) of the eight centres
-                const uint32_t nw_lo = __funnelshift_r(u2l, u2.x, 16), nw_hi = __funnelshift_r(u2.x, u2.y, 16);
-                const uint32_t ne_lo = __funnelshift_r(u2.x, u2.y, 16), ne_hi = __funnelshift_r(u2.y, u2r, 16);
-                const uint32_t sw_lo = __funnelshift_r(d2l, d2.x, 16), sw_hi = __funnelshift_r(d2.x, d2.y, 16);
-                const uint32_t se_lo = __funnelshift_r(d2.x, d2.y, 16), se_hi = __funnelshift_r(d2.y, d2r, 16);
-                const uint32_t a_lo = fast_gt_or2(__vabsdiffu4(nw_lo, c.x), __vabsdiffu4(se_lo, c.x), K4);
-                const uint32_t b_lo = fast_gt_or2(__vabsdiffu4(ne_lo, c.x), __vabsdiffu4(sw_lo, c.x), K4);
-                const uint32_t a_hi = fast_gt_or2(__vabsdiffu4(nw_hi, c.y), __vabsdiffu4(se_hi, c.y), K4);
-                const uint32_t b_hi = fast_gt_or2(__vabsdiffu4(ne_hi, c.y), __vabsdiffu4(sw_hi, c.y), K4);
-                flo &= a_lo & b_lo;
-                fhi &= a_hi & b_hi;
-            }
-#endif
-        }
-        // flags sit in bit 7 of each byte: one multiply per word gathers them into a nibble.
-        const uint32_t nib0 = ((flo * 0x00204081u) >> 28) | (((fhi * 0x00204081u) >> 24) & 0xf0u);
 #if FAST_BITMAP
-        // one byte per lane into the row bitmap: bit j of byte (pc - plo) of row r - 3 = tile byte column pc * 8 + j
-        if (active && r < rend) s.bitmap[(r - 3) * FAST_BM_PITCH + (pc - plo)] = (uint8_t)nib0;
+    // one byte per lane and row into the row bitmap: bit j of byte (pc - plo) of row r - 3 = tile byte column
+    // pc * 8 + j.  No warp collective inside: every lane walks its own rows.
+    if (active) {
+        uint8_t* bm = s.bitmap + ro * FAST_BM_PITCH + (pc - plo);
+        const int bstep = rpi * FAST_BM_PITCH;
+        for (int r = 3 + ro; r < rend; r += rpi, row += rstep, bm += bstep) *bm = (uint8_t)fast_reject8(row, tp, K4, vlo, vhi);
     }
+#else
+    for (int r = 3 + ro; r < rend + ro; r += rpi, row += rstep) {   // r - ro is warp-uniform
+        const uint32_t nib0 = (active && r < rend) ? fast_reject8(row, tp, K4, vlo, vhi) : 0u;
+#endif
+#if FAST_BITMAP
     __syncwarp();
     // ORDERED COMPACTION, once per group of 32 detection rows: lane = row, its flags are <= 3 words (the bytes
     // past the row's last pair are stale and masked); raster order = (row, word, bit) = lane-major, so one warp
