@@ -3,6 +3,8 @@ the REFERENCE'S OWN matcher code -- src/ORBmatcher.cc, src/Frame.cc, src/MapPoin
 oracle/_ref/liborbmref.so (MatchOracle("ref"); the prebuilt library travels to the GPU box) -- and, for the one
 piece the reference has no separate function for (the row search inside ComputeStereoMatches), against our
 restatement, which tests/test_oracle_match*.py pin to the reference.  Bar: bit-exact indices and counts."""
+import os
+
 import numpy as np
 import pytest
 
@@ -885,3 +887,52 @@ def test_frame_from_device_undistorts_like_opencv(matcher, mo, oracle_libs):
         assert tuple(float(b) for b in RF.bounds) == (0.0, 0.0, 752.0, 480.0)
     finally:
         RF.close()
+
+
+def _matcher_sweep(n, seed):
+    rng = np.random.default_rng(seed)
+    out = []
+    for i in range(n):
+        w, h = int(rng.integers(200, 1400)), int(rng.integers(160, 900))
+        out.append((i, w, h, int(rng.integers(300, 2500)), int(rng.integers(200, 8000)),
+                    float(rng.choice([1.0, 2.0, 3.0, 5.0])), float(rng.choice([3.0, 7.0, 15.0, 40.0])),
+                    bool(rng.integers(0, 2)), int(rng.integers(0, 3)), float(rng.choice([0.0, 20.0, 47.9]))))
+    return out
+
+
+# (ORBX_SWEEP_N / ORBX_SWEEP_SEED widen the sweep for a one-off soak; 200 further cases passed when this was written)
+@pytest.mark.parametrize("i,w,h,nkp,nmp,th,thf,far,motion,mbf",
+                         _matcher_sweep(int(os.environ.get("ORBX_SWEEP_N", "8")), int(os.environ.get("ORBX_SWEEP_SEED", "77"))))
+def test_random_tracking_search_sweep(matcher, mo, i, w, h, nkp, nmp, th, thf, far, motion, mbf):
+    """Both tracking searches on random frame sizes, keypoint / map-point counts, window factors, stereo gates and motion
+    directions (fixed seed), on a plain frame, a resident frame and with the descriptors in a bank: identical to the
+    reference-held oracle."""
+    from orb_slam3_mac_b200.matcher import DescriptorBank, ResidentFrame
+    from tests.golden import match_cases as mc
+    rng = np.random.default_rng(1000 + i)
+    (ka, da), (kb, db) = mc.frames(50 + i, n=nkp, w=w, h=h)
+    ur = np.where(rng.random(len(kb)) < 0.5, kb["x"] - rng.uniform(1, 40, len(kb)), -1.0).astype(np.float32) if mbf else None
+    F = _frame(kb, db, w, h, u_right=ur)
+    mps, md = S.map_points_from_frame(ka, da, w, h, nmp, i)
+    lo, ld = S.last_frame_obs(ka, da, i)
+    obs0 = np.where(rng.random(len(kb)) < 0.2, rng.integers(0, 3, len(kb)), -1).astype(np.int32)
+    fwd, bwd = motion == 1, motion == 2
+    want_p = mo.search_by_projection_points(F, mps, md, th, far, 30.0, 0.8, kp_obs=obs0)
+    want_f = mo.search_by_projection_frames(F, lo, ld, thf, fwd, bwd, mbf, True, kp_obs=obs0)
+    RF = ResidentFrame(matcher, F)
+    if ur is not None:
+        RF.set_u_right(ur)
+    bank = DescriptorBank(matcher, len(md) + len(ld))
+    try:
+        bank.write(0, md)
+        bank.write(len(md), ld)
+        rows_l = np.arange(len(md), len(md) + len(ld), dtype=np.int32)
+        for frame, dp, dl, rl in ((F, md, ld, None), (RF, md, ld, None), (RF, bank, bank, rows_l)):
+            got = matcher.SearchByProjection(frame, mps, dp, th, far, 30.0, kp_obs=obs0)
+            assert got[0] == want_p[0] and np.array_equal(got[1], want_p[1]) and np.array_equal(got[2], want_p[2])
+            got = matcher.SearchByProjectionFrames(frame, lo, dl, thf, fwd, bwd, mbf, kp_obs=obs0, rows=rl)
+            assert got[0] == want_f[0] and np.array_equal(got[1], want_f[1]) and np.array_equal(got[2], want_f[2])
+    finally:
+        bank.close()
+        RF.close()
+
