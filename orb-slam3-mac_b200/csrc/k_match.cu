@@ -348,7 +348,7 @@ k_grid_build(const orbx_keypoint* __restrict__ keys, int n, OrbmGrid G, int32_t*
 
 // One window query by one warp: GetFeaturesInArea (src/Frame.cc:645-714) over the 64 x 48 grid.  FILL: candidates (in
 // the reference's order) and their Hamming distances go to cand / dist from position `base`; else they are counted.
-template <bool FILL>
+template <bool FILL, bool PAIR = false>
 __device__ __forceinline__ int area_walk(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start,
                                          const int32_t* __restrict__ items, const OrbmGrid& G, const orbm_area_query& q,
                                          int base, const uint4* __restrict__ qdesc, const uint4* __restrict__ tdesc,
@@ -410,8 +410,13 @@ __device__ __forceinline__ int area_walk(const orbx_keypoint* __restrict__ keys,
                 const uint32_t m = __ballot_sync(ORBX_FULL, ok);
                 const int pos = base + total + __popc(m & lt);
                 if (FILL && ok && pos < cap) {   // cap: the lists were sized before the counts were known
-                    cand[pos] = idx;
-                    dist[pos] = (uint16_t)hamming256(a0, a1, tdesc + 2 * (size_t)idx);
+                    const uint32_t hd = (uint32_t)hamming256(a0, a1, tdesc + 2 * (size_t)idx);
+                    if (PAIR) {   // {candidate, distance} as one 8-byte record (`cand` is then a uint2 array)
+                        reinterpret_cast<uint2*>(cand)[pos] = make_uint2((uint32_t)idx, hd);
+                    } else {
+                        cand[pos] = idx;
+                        dist[pos] = (uint16_t)hd;
+                    }
                 }
                 total += __popc(m);
             }
@@ -442,11 +447,13 @@ __global__ void __launch_bounds__(256)
 k_area_onepass(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ start,
                const int32_t* __restrict__ items, OrbmGrid G, const orbm_area_query* __restrict__ Q, int nq,
                uint2* __restrict__ row_info, uint32_t* __restrict__ counter, uint32_t counter0,
-               const uint4* __restrict__ qdesc, const uint4* __restrict__ tdesc, int32_t* __restrict__ cand,
-               uint16_t* __restrict__ dist, int cap) {
+               const uint4* __restrict__ qdesc, const uint4* __restrict__ tdesc, uint2* __restrict__ pairs, int cap) {
+    // (row_info, the counter and the {candidate, distance} records live in ONE buffer: a single download brings them)
     const int qi = blockIdx.x * (blockDim.x >> 5) + orbx_warp();
     if (qi >= nq) return;
     const orbm_area_query q = Q[qi];
+    int32_t* cand = reinterpret_cast<int32_t*>(pairs);
+    uint16_t* dist = nullptr;
     const int total = area_walk<false>(keys, start, items, G, q, 0, qdesc, tdesc, cand, dist, cap);
     uint32_t base = 0;
     if (total) {   // (warp-uniform)
@@ -454,7 +461,7 @@ k_area_onepass(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict
         base = __shfl_sync(ORBX_FULL, base, 0);
         // a span that would pass 2^31 is not written (cap < 2^31 drops it anyway; the host sees the total and reruns)
         if (base < 0x7fffffffu - (uint32_t)total)
-            area_walk<true>(keys, start, items, G, q, (int)base, qdesc, tdesc, cand, dist, cap);
+            area_walk<true, true>(keys, start, items, G, q, (int)base, qdesc, tdesc, cand, dist, cap);
     }
     if (orbx_lane() == 0) row_info[qi] = make_uint2(base, (uint32_t)total);
 }
@@ -510,11 +517,11 @@ cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* star
 cudaError_t orbm_launch_area_onepass(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
                                      float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
                                      int nq, uint2* row_info, uint32_t* counter, uint32_t counter0, const uint8_t* qdesc,
-                                     const uint8_t* tdesc, int32_t* cand, uint16_t* dist, int cap, cudaStream_t st) {
+                                     const uint8_t* tdesc, uint2* pairs, int cap, cudaStream_t st) {
     OrbmGrid G{min_x, min_y, w_inv, h_inv};
     k_area_onepass<<<(nq + 7) / 8, 256, 0, st>>>(keys, start, items, G, Q, nq, row_info, counter, counter0,
                                                   reinterpret_cast<const uint4*>(qdesc),
-                                                  reinterpret_cast<const uint4*>(tdesc), cand, dist, cap);
+                                                  reinterpret_cast<const uint4*>(tdesc), pairs, cap);
     return cudaGetLastError();
 }
 

@@ -34,7 +34,7 @@ cudaError_t orbm_launch_area_count(const orbx_keypoint* keys, const int32_t* sta
 cudaError_t orbm_launch_area_onepass(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
                                      float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
                                      int nq, uint2* row_info, uint32_t* counter, uint32_t counter0, const uint8_t* qdesc,
-                                     const uint8_t* tdesc, int32_t* cand, uint16_t* dist, int cap, cudaStream_t st);
+                                     const uint8_t* tdesc, uint2* pairs, int cap, cudaStream_t st);
 cudaError_t orbm_launch_area_fill(const orbx_keypoint* keys, const int32_t* start, const int32_t* items,
                                   float min_x, float min_y, float w_inv, float h_inv, const orbm_area_query* Q,
                                   int nq, const int32_t* row_ptr, const uint8_t* qdesc, const uint8_t* tdesc,
@@ -155,7 +155,9 @@ struct orbm_context {
     size_t up_first = 0, up_end = 0;    // span of the arena the next ctx_flush copies ([first, end), empty when end == 0)
     // one-pass window search (device_candidates_onepass): {first position, count} per query, the running counter
     std::vector<uint2> h_rowinfo;
-    DevBuf counter;
+    std::vector<uint8_t> h_one;        // (fallback landing area of the one-buffer download)
+    bool hold_arena = false;           // a ctx_d2h_view is being read in place: ctx_sync keeps the arena as it is
+    DevBuf counter;                     // [counter | rows | records] of the one-launch search (device_candidates_onepass)
     uint32_t counter_host = 0;          // the counter's value after the last search that used it
     bool counter_known = false;         // false: zero it before the next use (first use, or a call that failed mid-way)
     std::unordered_map<const orbm_frame_view*, struct orbm_frame*> frames;   // device-resident frames of this context
@@ -239,6 +241,7 @@ void orbm_abort_staged(orbm_context* c) {
     c->up_end = 0;
     c->pin_used = 0;
     c->counter_known = false;
+    c->hold_arena = false;
     g_staging_ctx = nullptr;
 }
 
@@ -328,6 +331,41 @@ static cudaError_t ctx_d2h(orbm_context* c, void* dst, const void* src, size_t b
     return cudaMemcpyAsync(c->pin + off, src, bytes, cudaMemcpyDeviceToHost, c->st);
 }
 
+// A download the caller reads IN PLACE in the arena after ctx_sync (no second copy into an array of its own): *view
+// stays valid until the call stages again.  Falls back to nullptr when the arena cannot take it.
+static cudaError_t ctx_d2h_view(orbm_context* c, const void* src, size_t bytes, const uint8_t** view) {
+    *view = nullptr;
+    if (bytes == 0) return cudaSuccess;
+    g_staging_ctx = c;
+    cudaError_t ef = ctx_flush(c);
+    if (ef != cudaSuccess) return ef;
+    const size_t off = (c->pin_used + 63) & ~(size_t)63;
+    if (bytes > ORBM_PIN_DIRECT || off + bytes > c->pin_cap) {
+        c->pin_want = std::max(c->pin_want, off + bytes);
+        return cudaSuccess;
+    }
+    c->pin_used = off + bytes;
+    *view = c->pin + off;   // (the caller holds the arena: ArenaHold)
+    return cudaMemcpyAsync(c->pin + off, src, bytes, cudaMemcpyDeviceToHost, c->st);
+}
+
+// Replaces the arena by a larger one when the last call wanted more than it holds (nothing is in flight).
+static void ctx_grow(orbm_context* c) {
+    if (c->pin_cap && c->pin_want > c->pin_cap && c->pin_cap < ORBM_PIN_MAX) {
+        size_t want = std::min(std::max(c->pin_want * 2, ORBM_PIN_INIT), ORBM_PIN_MAX);
+        uint8_t* np = nullptr;
+        if (cudaHostAlloc((void**)&np, want, cudaHostAllocDefault) == cudaSuccess) {
+            if (c->pin) cudaFreeHost(c->pin);
+            c->darena.release();
+            c->pin = np;
+            c->pin_cap = want;
+        } else {
+            cudaGetLastError();   // keep the arena we have
+        }
+    }
+    c->pin_want = 0;
+}
+
 // Waits for the context's stream, delivers the staged results and recycles the arena.
 static cudaError_t ctx_sync(orbm_context* c) {
     cudaError_t e = ctx_flush(c);
@@ -340,19 +378,9 @@ static cudaError_t ctx_sync(orbm_context* c) {
     c->up.n = 0;
     c->up_end = 0;
     g_staging_ctx = nullptr;
-    if (e == cudaSuccess && c->pin_cap && c->pin_want > c->pin_cap && c->pin_cap < ORBM_PIN_MAX) {
-        size_t want = std::min(std::max(c->pin_want * 2, ORBM_PIN_INIT), ORBM_PIN_MAX);
-        uint8_t* np = nullptr;
-        if (cudaHostAlloc((void**)&np, want, cudaHostAllocDefault) == cudaSuccess) {
-            if (c->pin) cudaFreeHost(c->pin);
-    c->darena.release();
-            c->pin = np;
-            c->pin_cap = want;
-        } else {
-            cudaGetLastError();   // keep the arena we have
-        }
-    }
-    c->pin_want = 0;
+    if (c->hold_arena) return e;   // a view of the arena is being read: the reader calls ctx_grow when it is done
+    if (e == cudaSuccess) ctx_grow(c);
+    else c->pin_want = 0;
     return e;
 }
 
@@ -801,6 +829,18 @@ int stage_queries(orbm_context* c, int n, QueryBuf* b, bool alias = false) {
     return ORBX_OK;
 }
 
+// While a call reads staged data in place -- queries / descriptors in the arena's device mirror, results in the arena
+// itself -- neither may be replaced: ctx_sync leaves the arena alone, and it grows (if the call wanted more than it
+// holds) when the guard goes out of scope.
+struct ArenaHold {
+    orbm_context* c;
+    explicit ArenaHold(orbm_context* c_) : c(c_) { c->hold_arena = true; }
+    ~ArenaHold() {
+        c->hold_arena = false;
+        if (!g_staging_ctx) ctx_grow(c);   // (not between a failed call's staging and its abort)
+    }
+};
+
 // Candidates + distances of the two tracking searches in ONE kernel (k_area_onepass): no count launch, no row scan,
 // and -- with the queries (and host descriptors) read in place in the arena's mirror -- no scatter launch either:
 // one H2D copy, one kernel, the downloads.  Leaves {first position, count} per query in c->h_rowinfo and the lists
@@ -818,13 +858,23 @@ int device_candidates_onepass(orbm_context* c, const orbm_frame_view* F, const Q
         return ORBX_OK;
     }
     M_TRY(cudaSetDevice(c->device));
+    ArenaHold hold(c);
     const orbm_frame* RF = nullptr;
     {
         auto it = c->frames.find(F);
         if (it != c->frames.end()) RF = it->second;
     }
     int r;
-    if ((r = c->rowptr.ensure((size_t)nq * 8)) || (r = c->counter.ensure(64))) return r;
+    // ONE device buffer: [counter (64 B) | {first, count} per query | {candidate, distance} records]: one download
+    // brings the counter, the rows and the records the last search would have needed (+ slack)
+    const size_t rows_off = 64, pairs_off = rows_off + (((size_t)nq * 8 + 63) & ~(size_t)63);
+    auto ensure_one = [&](size_t records) -> int {
+        const size_t before = c->counter.cap;
+        int rr = c->counter.ensure(pairs_off + records * 8);
+        if (rr) return rr;
+        if (c->counter.cap != before) c->counter_known = false;   // a new buffer: its counter starts at an unknown value
+        return ORBX_OK;
+    };
     if (!RF && ((r = c->kl.ensure((size_t)F->n * sizeof(orbx_keypoint))) || (r = c->t.ensure((size_t)F->n * 32)) ||
                 (r = c->gstart.ensure((size_t)(ORBM_GRID_COLS * ORBM_GRID_ROWS + 1) * 4)) ||
                 (r = c->gitems.ensure((size_t)F->n * 4)) || (r = c->gcell.ensure((size_t)F->n * 4))))
@@ -856,11 +906,8 @@ int device_candidates_onepass(orbm_context* c, const orbm_frame_view* F, const Q
         M_TRY(ctx_h2d(c, c->aq.p, qb.q, (size_t)nq * sizeof(orbm_area_query)));
         dQ = (const orbm_area_query*)c->aq.p;
     }
-    if (!c->counter_known) {
-        M_TRY(cudaMemsetAsync(c->counter.p, 0, 4, c->st));
-        c->counter_host = 0;
-        c->counter_known = true;
-    }
+    // records sized from the last search's pair count, as in the three-launch path
+    if ((r = ensure_one(std::max<size_t>(4096, 2 * (size_t)c->nnz_hint)))) return r;
     ORBM_PHASE("uploads");
     M_TRY(ctx_flush(c));
     ORBM_PHASE("flush");
@@ -868,48 +915,64 @@ int device_candidates_onepass(orbm_context* c, const orbm_frame_view* F, const Q
     if (!RF)
         M_TRY(orbm_launch_grid_build(dk, F->n, F->min_x, F->min_y, F->grid_w_inv, F->grid_h_inv, (int32_t*)c->gstart.p,
                                      (int32_t*)c->gitems.p, (int32_t*)c->gcell.p, c->st));
-    {   // lists sized from the last search's pair count, as in device_candidates
-        const size_t guess = std::max<size_t>(4096, 2 * (size_t)c->nnz_hint);
-        if ((r = c->cand.ensure(guess * 4)) || (r = c->dist.ensure(guess * 2))) return r;
-    }
     uint32_t nnz = 0;
     for (int pass = 0; pass < 2; ++pass) {
-        const int cap = (int)std::min<size_t>({c->cand.cap / 4, c->dist.cap / 2, (size_t)0x3fffffff});
+        if (!c->counter_known) {
+            M_TRY(cudaMemsetAsync(c->counter.p, 0, 64, c->st));
+            c->counter_host = 0;
+            c->counter_known = true;
+        }
+        uint8_t* base = (uint8_t*)c->counter.p;
+        const int cap = (int)std::min<size_t>((c->counter.cap - pairs_off) / 8, (size_t)0x3fffffff);
         M_TRY(orbm_launch_area_onepass(dk, gstart, gitems, F->min_x, F->min_y, F->grid_w_inv, F->grid_h_inv, dQ, nq,
-                                       (uint2*)c->rowptr.p, (uint32_t*)c->counter.p, c->counter_host, dq, dt,
-                                       (int32_t*)c->cand.p, (uint16_t*)c->dist.p, cap, c->st));
+                                       (uint2*)(base + rows_off), (uint32_t*)base, c->counter_host, dq, dt,
+                                       (uint2*)(base + pairs_off), cap, c->st));
         M_TRY(cudaEventRecord(c->ev1, c->st));
         c->timed = true;
-        uint32_t after = 0;
-        M_TRY(ctx_d2h(c, c->h_rowinfo.data(), c->rowptr.p, (size_t)nq * 8));
-        M_TRY(ctx_d2h(c, &after, c->counter.p, 4));
         const size_t spec = pass == 0 ? std::min<size_t>({(size_t)cap, (size_t)c->nnz_hint + (size_t)c->nnz_hint / 8 + 1024, (size_t)65536})
                                       : (size_t)nnz;
-        c->h_cand.resize(spec);
-        c->hdist.resize(spec);
-        M_TRY(ctx_d2h(c, c->h_cand.data(), c->cand.p, spec * 4));
-        M_TRY(ctx_d2h(c, c->hdist.data(), c->dist.p, spec * 2));
-        ORBM_PHASE("launch + downloads queued");
+        const uint8_t* view = nullptr;
+        M_TRY(ctx_d2h_view(c, base, pairs_off + spec * 8, &view));
+        if (!view) {   // the arena cannot take it (first calls, very large searches): an array of this call's own
+            c->h_one.resize(pairs_off + spec * 8);
+            M_TRY(ctx_d2h(c, c->h_one.data(), base, pairs_off + spec * 8));
+        }
+        ORBM_PHASE("launch + download queued");
         M_TRY(ctx_sync(c));
-        ORBM_PHASE("wait + deliver");
+        ORBM_PHASE("wait");
+        const bool in_arena = view != nullptr;
+        if (!view) view = c->h_one.data();
+        uint32_t after;
+        memcpy(&after, view, 4);
         nnz = after - c->counter_host;
         c->counter_host = after;
         c->last_pairs = nnz;
         c->nnz_hint = (int)std::min<uint32_t>(nnz, 0x3fffffffu);
-        if (nnz > (uint32_t)cap) {   // the guess was too small: lists of the right size, once more
+        if (nnz > (uint32_t)cap) {   // the guess was too small: room for all of them, once more
             if (nnz > 0x3fffffffu) return orbx_set_error(ORBX_E_CAPACITY, "%u candidate pairs", nnz);
-            if ((r = c->cand.ensure((size_t)nnz * 4)) || (r = c->dist.ensure((size_t)nnz * 2))) return r;
+            if ((r = ensure_one(nnz))) return r;
             continue;
         }
-        if ((size_t)nnz > spec) {   // the tail the speculative fetch did not cover
-            c->h_cand.resize(nnz);
-            c->hdist.resize(nnz);
-            M_TRY(ctx_d2h(c, c->h_cand.data() + spec, (const int32_t*)c->cand.p + spec, ((size_t)nnz - spec) * 4));
-            M_TRY(ctx_d2h(c, c->hdist.data() + spec, (const uint16_t*)c->dist.p + spec, ((size_t)nnz - spec) * 2));
-            M_TRY(ctx_sync(c));
-        }
+        memcpy(c->h_rowinfo.data(), view + rows_off, (size_t)nq * 8);
         c->h_cand.resize(nnz);
         c->hdist.resize(nnz);
+        const size_t have = std::min<size_t>(nnz, spec);
+        const uint2* rec = reinterpret_cast<const uint2*>(view + pairs_off);
+        for (size_t k = 0; k < have; ++k) {
+            c->h_cand[k] = (int32_t)rec[k].x;
+            c->hdist[k] = (uint16_t)rec[k].y;
+        }
+        (void)in_arena;
+        if ((size_t)nnz > spec) {   // the tail the speculative fetch did not cover
+            c->h_one.resize(((size_t)nnz - spec) * 8);
+            M_TRY(ctx_d2h(c, c->h_one.data(), base + pairs_off + spec * 8, ((size_t)nnz - spec) * 8));
+            M_TRY(ctx_sync(c));
+            const uint2* rec2 = reinterpret_cast<const uint2*>(c->h_one.data());
+            for (size_t k = spec; k < nnz; ++k) {
+                c->h_cand[k] = (int32_t)rec2[k - spec].x;
+                c->hdist[k] = (uint16_t)rec2[k - spec].y;
+            }
+        }
         break;
     }
     ORBM_PHASE("tail");

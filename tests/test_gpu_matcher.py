@@ -907,6 +907,22 @@ def test_random_tracking_search_sweep(matcher, mo, i, w, h, nkp, nmp, th, thf, f
     """Both tracking searches on random frame sizes, keypoint / map-point counts, window factors, stereo gates and motion
     directions (fixed seed), on a plain frame, a resident frame and with the descriptors in a bank: identical to the
     reference-held oracle."""
+    _tracking_case(matcher, mo, i, w, h, nkp, nmp, th, thf, far, motion, mbf)
+
+
+def test_window_search_that_outgrows_lists_and_arena(mo):
+    """Found by the soak (seed 9, case 3): on a FRESH context a 40-px frame-to-frame window yields ~200 k pairs -- more
+    than the first guess of the lists (the search reruns) and more than the pinned arena holds (it grows).  The arena
+    and its device mirror, which the rerun still reads its queries from, must not be replaced between the two passes."""
+    from orb_slam3_mac_b200.matcher import ORBmatcher
+    m = ORBmatcher(0.8, True, 0)
+    try:
+        _tracking_case(m, mo, 3, 1196, 376, 2463, 2918, 5.0, 40.0, False, 2, 47.9)
+    finally:
+        m.close()
+
+
+def _tracking_case(matcher, mo, i, w, h, nkp, nmp, th, thf, far, motion, mbf):
     from orb_slam3_mac_b200.matcher import DescriptorBank, ResidentFrame
     from tests.golden import match_cases as mc
     rng = np.random.default_rng(1000 + i)
