@@ -111,12 +111,13 @@ def test_batch_matches_single_and_oracle(oracle_libs, synth):
     ex.close()
 
 
-@pytest.mark.parametrize("nf,h,w,B", [(1000, 480, 752, 48), (2000, 480, 752, 40), (5000, 240, 376, 40)])
+@pytest.mark.parametrize("nf,h,w,B", [(300, 240, 376, 300), (1000, 480, 752, 48), (2000, 480, 752, 40), (5000, 240, 376, 40)])
 def test_large_batch_quadtree_cta_sizes(oracle_libs, synth, nf, h, w, B):
-    """k_octree is compiled for 128 / 256 / 512 threads and picked per LAUNCH (csrc/k_octree.cu): a launch of more
-    than 2 CTAs per SM goes by the plan's largest per-level quota (nf = 1000 -> 217 -> 128 threads, 2000 -> 434 -> 256,
-    5000 -> 1086 -> 512), a smaller one always takes 512.  A batch big enough for the first rule must give, frame for
-    frame, the bytes of the same frames extracted one at a time (second rule), and the oracle's results."""
+    """k_octree is compiled for 128 / 256 / 512 threads and picked per LAUNCH (csrc/k_octree.cu): a launch of at most
+    2 CTAs per SM always takes 512; a larger one goes by the plan's largest per-level quota -- 128 threads for quotas
+    up to 240 when there are two full waves of them (300 frames x 8 levels here), 256 up to 650 (nf = 1000 at 48
+    frames, nf = 2000), 512 above (nf = 5000 -> 1086).  A batch must give, frame for frame, the bytes of the same frames
+    extracted one at a time (the 512-thread rule), and the oracle's results."""
     from orb_slam3_mac_b200.extractor import ORBextractor
     kinds = ["noise", "checker", "lowtex", "noise"]
     imgs = [synth.frame(kinds[i % 4], h, w, 100 + i) for i in range(B)]
